@@ -1,0 +1,141 @@
+"""ctypes binding of libfrx.so (include/frx.h).  There is no CPU fallback: if the shared
+library is missing, or no CUDA device is present when a context is created, this raises."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from pathlib import Path
+
+_PKG = Path(__file__).resolve().parent
+LIB_PATH = _PKG / "libfrx.so"
+
+FRX_U8, FRX_I16, FRX_U16, FRX_I32, FRX_U32, FRX_F32 = range(6)
+DTYPE_CODE = {"uint8": FRX_U8, "int16": FRX_I16, "uint16": FRX_U16, "int32": FRX_I32, "uint32": FRX_U32,
+              "float32": FRX_F32}
+CODE_DTYPE = {v: k for k, v in DTYPE_CODE.items()}
+PCM_REFERENCE, PCM_LOSSLESS, PCM_REFERENCE_SPATIAL = 0, 1, 2
+PCM_MODE = {"reference": PCM_REFERENCE, "lossless": PCM_LOSSLESS, "reference_spatial": PCM_REFERENCE_SPATIAL}
+NO_FRAME_TABLE = 0xFFFFFFFF
+
+E_INVALID, E_CUDA, E_NOMEM, E_UNSUPPORTED, E_OVERFLOW, E_BITSTREAM = -1, -2, -3, -4, -5, -6
+
+
+class FrxError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"libfrx error {code}: {msg}")
+        self.code = code
+
+
+class FrxUnsupported(FrxError):
+    """e.g. > 8 channels per stream: the reference raises pyflac.EncoderInitException here."""
+
+
+class Tile(C.Structure):
+    _fields_ = [("row_off", C.c_int32), ("col_off", C.c_int32), ("h", C.c_int32), ("w", C.c_int32),
+                ("first_band", C.c_int32), ("n_channels", C.c_int32)]
+
+
+class EncodeParams(C.Structure):
+    _fields_ = [("compression_level", C.c_int32), ("blocksize", C.c_int32), ("sample_rate", C.c_int32),
+                ("pcm_mode", C.c_int32)]
+
+
+class Raster(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("dtype", C.c_int32), ("bands", C.c_int32), ("height", C.c_int64),
+                ("width", C.c_int64), ("band_stride", C.c_int64), ("row_stride", C.c_int64)]
+
+
+class EncodeOut(C.Structure):
+    _fields_ = [("bytes", C.c_void_p), ("capacity", C.c_uint64), ("tile_offset", C.c_void_p),
+                ("tile_size", C.c_void_p), ("tile_minmax", C.c_void_p), ("frame_size", C.c_void_p),
+                ("frame_offset", C.c_void_p), ("total_bytes", C.c_void_p), ("status", C.c_void_p)]
+
+
+class DTile(C.Structure):
+    _fields_ = [("byte_offset", C.c_uint64), ("byte_size", C.c_uint64), ("out_offset", C.c_uint64),
+                ("out_band_stride", C.c_int64), ("out_row_stride", C.c_int64),
+                ("h", C.c_int32), ("w", C.c_int32), ("channels", C.c_int32), ("bps", C.c_int32),
+                ("dmin", C.c_double), ("dmax", C.c_double), ("first_frame", C.c_uint32), ("n_frames", C.c_uint32)]
+
+
+EXPORTS = ["frx_version", "frx_last_error", "frx_device_count", "frx_ctx_create", "frx_ctx_destroy",
+           "frx_encode_bound", "frx_pcm_bps", "frx_encode_tiles", "frx_decode_tiles", "frx_quantize",
+           "frx_dequantize", "frx_encode_tiles_host", "frx_decode_tiles_host", "frx_launch_count",
+           "frx_last_kernel_ms"]
+
+_lib = None
+
+
+def build(force: bool = False) -> Path:
+    """Compile libfrx.so for sm_100a with nvcc (csrc/Makefile)."""
+    src = _PKG / "csrc"
+    newest = max(p.stat().st_mtime for p in list(src.glob("*.cu")) + list(src.glob("*.cuh")) +
+                 [_PKG.parent / "include" / "frx.h"])
+    if force or not LIB_PATH.exists() or LIB_PATH.stat().st_mtime < newest:
+        subprocess.run(["make", "-C", str(src), "-j4"], check=True, capture_output=True)
+    return LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise FrxError(E_CUDA, f"{LIB_PATH} is missing: build it with flac_raster_b200._lib.build() "
+                                   "(nvcc, sm_100a). There is no CPU fallback.")
+        L = C.CDLL(str(LIB_PATH))
+        L.frx_version.restype = C.c_int
+        L.frx_last_error.restype = C.c_char_p
+        L.frx_device_count.restype = C.c_int
+        L.frx_ctx_create.restype = C.c_int
+        L.frx_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+        L.frx_ctx_destroy.restype = None
+        L.frx_ctx_destroy.argtypes = [C.c_void_p]
+        L.frx_encode_bound.restype = C.c_int
+        L.frx_encode_bound.argtypes = [C.POINTER(Tile), C.c_int32, C.c_int32, C.POINTER(EncodeParams),
+                                       C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.frx_pcm_bps.restype = C.c_int
+        L.frx_pcm_bps.argtypes = [C.c_int32, C.c_int32]
+        L.frx_encode_tiles.restype = C.c_int
+        L.frx_encode_tiles.argtypes = [C.c_void_p, C.POINTER(Raster), C.POINTER(Tile), C.c_int32,
+                                       C.POINTER(EncodeParams), C.POINTER(EncodeOut), C.c_void_p]
+        L.frx_decode_tiles.restype = C.c_int
+        L.frx_decode_tiles.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(DTile), C.c_int32, C.c_void_p,
+                                       C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.frx_quantize.restype = C.c_int
+        L.frx_quantize.argtypes = [C.c_void_p, C.POINTER(Raster), C.POINTER(Tile), C.c_int32, C.c_void_p, C.c_void_p,
+                                   C.c_void_p]
+        L.frx_dequantize.restype = C.c_int
+        L.frx_dequantize.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                     C.c_int32, C.c_double, C.c_double, C.c_void_p, C.c_void_p]
+        L.frx_encode_tiles_host.restype = C.c_int
+        L.frx_encode_tiles_host.argtypes = [C.c_void_p, C.POINTER(Raster), C.POINTER(Tile), C.c_int32,
+                                            C.POINTER(EncodeParams), C.POINTER(EncodeOut)]
+        L.frx_decode_tiles_host.restype = C.c_int
+        L.frx_decode_tiles_host.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(DTile), C.c_int32,
+                                            C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_uint64,
+                                            C.c_void_p]
+        L.frx_launch_count.restype = C.c_uint64
+        L.frx_launch_count.argtypes = [C.c_void_p]
+        L.frx_last_kernel_ms.restype = C.c_int
+        L.frx_last_kernel_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+        _lib = L
+    return _lib
+
+
+def check(rc: int):
+    if rc < 0:
+        msg = lib().frx_last_error().decode("utf-8", "replace")
+        if rc == E_UNSUPPORTED:
+            raise FrxUnsupported(rc, msg)
+        raise FrxError(rc, msg)
+    return rc
+
+
+def make_tiles(tiles) -> "C.Array[Tile]":
+    """tiles: iterable of (row_off, col_off, h, w, first_band, n_channels)."""
+    tiles = list(tiles)
+    arr = (Tile * len(tiles))()
+    for i, t in enumerate(tiles):
+        arr[i].row_off, arr[i].col_off, arr[i].h, arr[i].w, arr[i].first_band, arr[i].n_channels = (int(x) for x in t)
+    return arr

@@ -1,0 +1,541 @@
+// frx_api.cu -- the C-ABI of libfrx.so (include/frx.h): context, scratch, launch sequencing.
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <vector>
+
+#include "frx_internal.cuh"
+
+// ---- error handling ----------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+static int set_err(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+#define CK(call)                                                                                              \
+    do {                                                                                                      \
+        cudaError_t _e = (call);                                                                              \
+        if (_e != cudaSuccess) return set_err(FRX_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    } while (0)
+
+struct Buf {
+    void *p = nullptr;
+    size_t cap = 0;
+};
+
+struct frx_ctx {
+    int device = 0;
+    int sm_count = 148;
+    uint64_t launches = 0;
+    Buf tiles, prefix, unit_prefix, mmraw, quant, desc, misc, window, xpow, crctab, fsize, foff;
+    Buf dtiles, dprefix, fpos, scan_prefix, scan_tiles;
+    Buf h_raster, h_bytes, h_small, h_out;  // device staging for the *_host entry points
+    int window_len = -1;
+    int xpow_L = -1;
+    bool crctab_ready = false;
+    cudaEvent_t ev[4] = { nullptr, nullptr, nullptr, nullptr };
+    bool enc_timed = false, dec_timed = false;
+    int verify_crc = 1;
+};
+
+static int ensure(Buf &b, size_t bytes) {
+    if (bytes <= b.cap && b.p) return FRX_OK;
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr; b.cap = 0;
+    size_t want = bytes < 256 ? 256 : bytes;
+    cudaError_t e = cudaMalloc(&b.p, want);
+    if (e != cudaSuccess) return set_err(FRX_E_NOMEM, "cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e));
+    b.cap = want;
+    return FRX_OK;
+}
+#define ENSURE(buf, bytes) do { int _r = ensure(buf, bytes); if (_r) return _r; } while (0)
+
+extern "C" {
+
+int frx_version(void) { return FRX_VERSION_MAJOR * 100 + FRX_VERSION_MINOR; }
+const char *frx_last_error(void) { return g_err; }
+
+int frx_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int frx_ctx_create(int device, frx_ctx **out) {
+    if (!out) return set_err(FRX_E_INVALID, "out is NULL");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return set_err(FRX_E_CUDA, "no CUDA device available (%s); libfrx has no CPU fallback", cudaGetErrorString(e));
+    if (device < 0 || device >= n) return set_err(FRX_E_INVALID, "device %d out of range (0..%d)", device, n - 1);
+    CK(cudaSetDevice(device));
+    frx_ctx *c = new frx_ctx();
+    c->device = device;
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    c->sm_count = prop.multiProcessorCount;
+    for (int i = 0; i < 4; i++) CK(cudaEventCreate(&c->ev[i]));
+    *out = c;
+    return FRX_OK;
+}
+
+void frx_ctx_destroy(frx_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    Buf *all[] = { &c->tiles, &c->prefix, &c->unit_prefix, &c->mmraw, &c->quant, &c->desc, &c->misc, &c->window, &c->xpow,
+                   &c->crctab, &c->fsize, &c->foff, &c->dtiles, &c->dprefix, &c->fpos, &c->scan_prefix, &c->scan_tiles,
+                   &c->h_raster, &c->h_bytes, &c->h_small, &c->h_out };
+    for (Buf *b : all) if (b->p) cudaFree(b->p);
+    for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    delete c;
+}
+
+uint64_t frx_launch_count(const frx_ctx *c) { return c ? c->launches : 0; }
+
+int frx_last_kernel_ms(frx_ctx *c, float *enc_ms, float *dec_ms) {
+    if (!c) return set_err(FRX_E_INVALID, "ctx is NULL");
+    CK(cudaSetDevice(c->device));
+    if (enc_ms) { *enc_ms = 0.f; if (c->enc_timed) CK(cudaEventElapsedTime(enc_ms, c->ev[0], c->ev[1])); }
+    if (dec_ms) { *dec_ms = 0.f; if (c->dec_timed) CK(cudaEventElapsedTime(dec_ms, c->ev[2], c->ev[3])); }
+    return FRX_OK;
+}
+
+int frx_pcm_bps(int32_t dtype, int32_t pcm_mode) {
+    if (dtype < FRX_U8 || dtype > FRX_F32) return set_err(FRX_E_INVALID, "bad dtype %d", dtype);
+    return frx_bps_for(dtype, pcm_mode);
+}
+
+static int check_params(const frx_encode_params *p) {
+    if (!p) return set_err(FRX_E_INVALID, "params is NULL");
+    if (p->blocksize < 16 || p->blocksize > FRX_MAX_BLOCK)
+        return set_err(FRX_E_UNSUPPORTED, "blocksize %d outside 16..%d", p->blocksize, FRX_MAX_BLOCK);
+    if (p->compression_level < 0 || p->compression_level > 8) return set_err(FRX_E_INVALID, "compression_level %d outside 0..8", p->compression_level);
+    if (p->pcm_mode < 0 || p->pcm_mode > 2) return set_err(FRX_E_INVALID, "bad pcm_mode %d", p->pcm_mode);
+    if (p->sample_rate <= 0 || p->sample_rate > 655350) return set_err(FRX_E_INVALID, "bad sample_rate %d", p->sample_rate);
+    return FRX_OK;
+}
+
+static int check_tiles(const frx_tile *tiles, int n, int bands, long long H, long long W) {
+    if (!tiles || n <= 0) return set_err(FRX_E_INVALID, "no tiles");
+    for (int i = 0; i < n; i++) {
+        const frx_tile &t = tiles[i];
+        if (t.n_channels < 1 || t.n_channels > FRX_MAX_CH)
+            return set_err(FRX_E_UNSUPPORTED, "tile %d: %d channels; FLAC allows 1..8 per stream (EncoderInitException in the reference)", i, t.n_channels);
+        if (t.h <= 0 || t.w <= 0 || t.row_off < 0 || t.col_off < 0 || (bands >= 0 && (t.first_band < 0 || t.first_band + t.n_channels > bands)) ||
+            (H >= 0 && ((long long)t.row_off + t.h > H || (long long)t.col_off + t.w > W)))
+            return set_err(FRX_E_INVALID, "tile %d: window/bands outside the raster", i);
+    }
+    return FRX_OK;
+}
+
+static uint64_t frame_bytes_bound(int channels, int bps, int blocksize) {
+    return 16ull + (uint64_t)channels * (2ull + ((uint64_t)blocksize * bps + 7) / 8 + 1) + 2ull;
+}
+
+int frx_encode_bound(const frx_tile *tiles, int32_t n_tiles, int32_t dtype, const frx_encode_params *p, uint64_t *total_frames,
+                     uint64_t *max_bytes) {
+    int r = check_params(p);
+    if (r) return r;
+    r = check_tiles(tiles, n_tiles, -1, -1, -1);
+    if (r) return r;
+    if (dtype < FRX_U8 || dtype > FRX_F32) return set_err(FRX_E_INVALID, "bad dtype %d", dtype);
+    int bps = frx_bps_for(dtype, p->pcm_mode);
+    uint64_t nf = 0, nb = 0;
+    for (int i = 0; i < n_tiles; i++) {
+        uint64_t n = (uint64_t)tiles[i].h * tiles[i].w;
+        uint64_t f = (n + p->blocksize - 1) / p->blocksize;
+        nf += f;
+        nb += f * (16ull + 3ull * tiles[i].n_channels + 2ull) + (n * tiles[i].n_channels * bps + 7) / 8 + 8ull * f;
+    }
+    if (total_frames) *total_frames = nf;
+    if (max_bytes) *max_bytes = nb + 64;
+    return FRX_OK;
+}
+
+static int sample_rate_code(int sr) {
+    switch (sr) {
+        case 88200: return 1; case 176400: return 2; case 192000: return 3; case 8000: return 4; case 16000: return 5;
+        case 22050: return 6; case 24000: return 7; case 32000: return 8; case 44100: return 9; case 48000: return 10;
+        case 96000: return 11;
+    }
+    return sr <= 65535 ? 13 : 0;
+}
+
+static int qlp_precision_for(int bps, int blocksize) {  // libFLAC's automatic precision
+    if (bps < 16) { int p = 2 + bps / 2; return p < 5 ? 5 : p; }
+    if (bps == 16) {
+        if (blocksize <= 192) return 7; if (blocksize <= 384) return 8; if (blocksize <= 576) return 9;
+        if (blocksize <= 1152) return 10; if (blocksize <= 2304) return 11; if (blocksize <= 4608) return 12;
+        return 13;
+    }
+    if (blocksize <= 384) return 13;
+    if (blocksize <= 1152) return 14;
+    return 15;
+}
+
+// Everything the encode path needs on the device before the main kernel: tiles, prefixes, min/max.
+struct EncPrep {
+    uint32_t total_frames = 0;
+    int bps = 0;
+    int max_channels = 1;
+};
+
+static int encode_prepare(frx_ctx *c, const frx_raster &r, const frx_tile *tiles, int n_tiles, const frx_encode_params *p,
+                          EncPrep &prep, cudaStream_t st) {
+    std::vector<uint32_t> fprefix(n_tiles + 1), uprefix(n_tiles + 1);
+    const int unit_elems = 65536;
+    uint64_t nf = 0, nu = 0;
+    int maxc = 1;
+    for (int i = 0; i < n_tiles; i++) {
+        fprefix[i] = (uint32_t)nf; uprefix[i] = (uint32_t)nu;
+        uint64_t n = (uint64_t)tiles[i].h * tiles[i].w;
+        nf += (n + p->blocksize - 1) / p->blocksize;
+        int rpu = unit_elems / tiles[i].w; if (rpu < 1) rpu = 1;
+        uint64_t vrows = (uint64_t)tiles[i].n_channels * tiles[i].h;
+        nu += (vrows + rpu - 1) / rpu;
+        if (tiles[i].n_channels > maxc) maxc = tiles[i].n_channels;
+        if (nf > 0xFFFFFFF0ull || nu > 0x7FFFFFF0ull) return set_err(FRX_E_UNSUPPORTED, "too many frames in one call");
+    }
+    fprefix[n_tiles] = (uint32_t)nf; uprefix[n_tiles] = (uint32_t)nu;
+    prep.total_frames = (uint32_t)nf;
+    prep.bps = frx_bps_for(r.dtype, p->pcm_mode);
+    prep.max_channels = maxc;
+    ENSURE(c->tiles, sizeof(frx_tile) * n_tiles);
+    ENSURE(c->prefix, sizeof(uint32_t) * (n_tiles + 1));
+    ENSURE(c->unit_prefix, sizeof(uint32_t) * (n_tiles + 1));
+    ENSURE(c->mmraw, frx_minmax_raw_size() * n_tiles);
+    ENSURE(c->quant, sizeof(FrxQuant) * n_tiles);
+    CK(cudaMemcpyAsync(c->tiles.p, tiles, sizeof(frx_tile) * n_tiles, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(c->prefix.p, fprefix.data(), sizeof(uint32_t) * (n_tiles + 1), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(c->unit_prefix.p, uprefix.data(), sizeof(uint32_t) * (n_tiles + 1), cudaMemcpyHostToDevice, st));
+    // the vectors die at return: pageable async copies are staged before the call returns, but be explicit
+    CK(cudaStreamSynchronize(st));
+    CK(frx_launch_minmax(r, (const frx_tile *)c->tiles.p, (const uint32_t *)c->unit_prefix.p, n_tiles, (uint32_t)nu, unit_elems,
+                         c->mmraw.p, (FrxQuant *)c->quant.p, st));
+    c->launches += 3;
+    return FRX_OK;
+}
+
+static frx_raster normalise_raster(const frx_raster *in) {
+    frx_raster r = *in;
+    if (r.row_stride == 0) r.row_stride = r.width;
+    if (r.band_stride == 0) r.band_stride = r.height * r.width;
+    return r;
+}
+
+static int check_raster(const frx_raster *r) {
+    if (!r || !r->data) return set_err(FRX_E_INVALID, "raster is NULL");
+    if (r->dtype < FRX_U8 || r->dtype > FRX_F32) return set_err(FRX_E_INVALID, "bad raster dtype %d", r->dtype);
+    if (r->bands < 1 || r->height < 1 || r->width < 1) return set_err(FRX_E_INVALID, "bad raster shape");
+    return FRX_OK;
+}
+
+int frx_encode_tiles(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *tiles, int32_t n_tiles, const frx_encode_params *p,
+                     const frx_encode_out *out, void *stream) {
+    if (!c) return set_err(FRX_E_INVALID, "ctx is NULL");
+    int rc = check_params(p); if (rc) return rc;
+    rc = check_raster(raster_dev); if (rc) return rc;
+    if (!out || !out->bytes) return set_err(FRX_E_INVALID, "out->bytes is NULL");
+    frx_raster r = normalise_raster(raster_dev);
+    rc = check_tiles(tiles, n_tiles, r.bands, r.height, r.width); if (rc) return rc;
+    if (p->pcm_mode == FRX_PCM_REFERENCE_SPATIAL && r.dtype == FRX_U32)
+        return set_err(FRX_E_UNSUPPORTED, "reference --spatial mapping yields a float64 array for uint32 input, which pyFLAC rejects (bps 64)");
+    CK(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    EncPrep prep;
+    rc = encode_prepare(c, r, tiles, n_tiles, p, prep, st); if (rc) return rc;
+
+    // window (tukey 0.5, libFLAC's definition) and CRC shift table
+    if (c->window_len != p->blocksize) {
+        std::vector<float> w(p->blocksize, 1.0f);
+        int L = p->blocksize, Np = (int)(0.5f / 2.0f * L) - 1;
+        if (Np > 0)
+            for (int n = 0; n <= Np; n++) {
+                w[n] = (float)(0.5f - 0.5f * cosf((float)(M_PI * n / Np)));
+                w[L - Np - 1 + n] = (float)(0.5f - 0.5f * cosf((float)(M_PI * (n + Np) / Np)));
+            }
+        ENSURE(c->window, sizeof(float) * L);
+        CK(cudaMemcpy(c->window.p, w.data(), sizeof(float) * L, cudaMemcpyHostToDevice));
+        c->window_len = L;
+    }
+    const uint64_t fb = frame_bytes_bound(prep.max_channels, prep.bps, p->blocksize);
+    const int frame_words = (int)((fb + 3) / 4) + 4;
+    int Lc = (int)((fb + FRX_ENC_THREADS - 1) / FRX_ENC_THREADS);
+    Lc = (Lc + 3) & ~3;
+    if (c->xpow_L != Lc) {
+        // x^(8*Lc*j) mod P for j = 0..255
+        uint32_t x8L = 1;  // x^0
+        {
+            uint32_t base = 2;  // x
+            uint32_t e = 8u * (uint32_t)Lc;
+            uint32_t acc = 1;
+            while (e) { if (e & 1u) acc = frx_gf16_mulmod(acc, base); base = frx_gf16_mulmod(base, base); e >>= 1; }
+            x8L = acc;
+        }
+        std::vector<uint16_t> xp(FRX_ENC_THREADS);
+        uint32_t cur = 1;
+        for (int j = 0; j < FRX_ENC_THREADS; j++) { xp[j] = (uint16_t)cur; cur = frx_gf16_mulmod(cur, x8L); }
+        ENSURE(c->xpow, sizeof(uint16_t) * FRX_ENC_THREADS);
+        CK(cudaMemcpy(c->xpow.p, xp.data(), sizeof(uint16_t) * FRX_ENC_THREADS, cudaMemcpyHostToDevice));
+        c->xpow_L = Lc;
+    }
+    ENSURE(c->desc, sizeof(uint64_t) * (size_t)prep.total_frames);
+    ENSURE(c->misc, 64);
+    uint32_t *frame_size = out->frame_size;
+    uint64_t *frame_offset = out->frame_offset;
+    if (!frame_size) { ENSURE(c->fsize, sizeof(uint32_t) * (size_t)prep.total_frames); frame_size = (uint32_t *)c->fsize.p; }
+    if (!frame_offset) { ENSURE(c->foff, sizeof(uint64_t) * (size_t)prep.total_frames); frame_offset = (uint64_t *)c->foff.p; }
+    CK(cudaMemsetAsync(c->desc.p, 0, sizeof(uint64_t) * (size_t)prep.total_frames, st));
+    CK(cudaMemsetAsync(c->misc.p, 0, 64, st));
+    if (out->status) CK(cudaMemsetAsync(out->status, 0, sizeof(int32_t), st));
+
+    static const int lvl_lpc[9] = { 0, 0, 0, 6, 8, 8, 8, 12, 12 };
+    static const int lvl_po[9] = { 3, 3, 3, 4, 4, 5, 6, 6, 6 };
+    EncArgs a;
+    memset(&a, 0, sizeof(a));
+    a.raster = r.data; a.H = r.height; a.W = r.width; a.band_stride = r.band_stride; a.row_stride = r.row_stride;
+    a.tiles = (const frx_tile *)c->tiles.p; a.frame_prefix = (const uint32_t *)c->prefix.p; a.quant = (const FrxQuant *)c->quant.p;
+    a.window = (const float *)c->window.p; a.crc_xpow = (const uint16_t *)c->xpow.p;
+    a.bytes = out->bytes; a.capacity = out->capacity; a.frame_size = frame_size; a.frame_offset = frame_offset;
+    a.desc = (uint64_t *)c->desc.p; a.ticket = (uint32_t *)c->misc.p;
+    a.status = out->status ? out->status : (int32_t *)((char *)c->misc.p + 16);
+    a.total_bytes = out->total_bytes ? out->total_bytes : (uint64_t *)((char *)c->misc.p + 32);
+    a.total_frames = prep.total_frames; a.n_tiles = n_tiles; a.blocksize = p->blocksize; a.bps = prep.bps; a.pcm_mode = p->pcm_mode;
+    a.sr_code = sample_rate_code(p->sample_rate); a.sample_rate = p->sample_rate;
+    a.max_lpc_order = lvl_lpc[p->compression_level]; a.max_po = lvl_po[p->compression_level];
+    a.qlp_precision = qlp_precision_for(prep.bps, p->blocksize);
+    a.frame_words = frame_words; a.crc_chunk = Lc;
+    if (frx_enc_smem_bytes(frame_words) > 227 * 1024) return set_err(FRX_E_UNSUPPORTED, "frame buffer does not fit shared memory");
+    CK(cudaEventRecord(c->ev[0], st));
+    CK(frx_launch_encode(a, r.dtype, c->sm_count, st));
+    CK(cudaEventRecord(c->ev[1], st));
+    c->enc_timed = true;
+    CK(frx_launch_tile_index((const uint32_t *)c->prefix.p, frame_size, frame_offset, (const FrxQuant *)c->quant.p, r.dtype, n_tiles,
+                             out->tile_offset, out->tile_size, out->tile_minmax, st));
+    c->launches += 2;
+    return FRX_OK;
+}
+
+int frx_quantize(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *tile, int32_t pcm_mode, int32_t *pcm_dev, double *minmax_dev,
+                 void *stream) {
+    if (!c) return set_err(FRX_E_INVALID, "ctx is NULL");
+    int rc = check_raster(raster_dev); if (rc) return rc;
+    if (!pcm_dev) return set_err(FRX_E_INVALID, "pcm_dev is NULL");
+    frx_raster r = normalise_raster(raster_dev);
+    rc = check_tiles(tile, 1, r.bands, r.height, r.width); if (rc) return rc;
+    CK(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    frx_encode_params p = { 5, 4096, 44100, pcm_mode };
+    rc = check_params(&p); if (rc) return rc;
+    EncPrep prep;
+    rc = encode_prepare(c, r, tile, 1, &p, prep, st); if (rc) return rc;
+    CK(frx_launch_quantize(r, *tile, (const FrxQuant *)c->quant.p, pcm_mode, pcm_dev, minmax_dev, st));
+    c->launches += minmax_dev ? 2 : 1;
+    return FRX_OK;
+}
+
+
+static int decode_core(frx_ctx *c, const uint8_t *bytes_dev, uint64_t n_bytes, const frx_dtile *tiles, int32_t n_tiles,
+                       const uint32_t *frame_size_dev, int32_t blocksize, int32_t out_dtype, int32_t pcm_mode, void *out_dev,
+                       int32_t *tile_status_dev, cudaStream_t st) {
+    if (!bytes_dev || !tiles || n_tiles <= 0 || !out_dev || !tile_status_dev) return set_err(FRX_E_INVALID, "NULL argument");
+    if (blocksize < 16 || blocksize > 65535) return set_err(FRX_E_INVALID, "bad blocksize %d", blocksize);
+    if (out_dtype < FRX_U8 || out_dtype > FRX_F32) return set_err(FRX_E_INVALID, "bad out_dtype %d", out_dtype);
+    std::vector<uint32_t> dprefix(n_tiles + 1), sprefix;
+    std::vector<int32_t> stiles;
+    uint64_t nf = 0, nu = 0;
+    for (int i = 0; i < n_tiles; i++) {
+        const frx_dtile &t = tiles[i];
+        if (t.channels < 1 || t.channels > FRX_MAX_CH || t.h <= 0 || t.w <= 0 || (t.bps != 16 && t.bps != 32 && t.bps != 8 && t.bps != 24 && t.bps != 12 && t.bps != 20))
+            return set_err(FRX_E_INVALID, "tile %d: bad geometry/bps", i);
+        if (t.byte_offset + t.byte_size > n_bytes) return set_err(FRX_E_INVALID, "tile %d: byte range outside the buffer", i);
+        uint64_t expect = ((uint64_t)t.h * t.w + blocksize - 1) / blocksize;
+        if (t.n_frames != expect) return set_err(FRX_E_INVALID, "tile %d: n_frames %u != ceil(h*w/blocksize) %llu", i, t.n_frames, (unsigned long long)expect);
+        if (t.first_frame != 0xFFFFFFFFu && !frame_size_dev) return set_err(FRX_E_INVALID, "tile %d needs frame_size", i);
+        dprefix[i] = (uint32_t)nf;
+        nf += t.n_frames;
+        if (t.first_frame == 0xFFFFFFFFu) {
+            sprefix.push_back((uint32_t)nu);
+            stiles.push_back(i);
+            nu += (t.byte_size + 4095) / 4096;
+        }
+        if (nf > 0xFFFFFFF0ull || nu > 0x7FFFFFF0ull) return set_err(FRX_E_UNSUPPORTED, "too many frames in one call");
+    }
+    dprefix[n_tiles] = (uint32_t)nf;
+    sprefix.push_back((uint32_t)nu);
+    ENSURE(c->dtiles, sizeof(frx_dtile) * n_tiles);
+    ENSURE(c->dprefix, sizeof(uint32_t) * (n_tiles + 1));
+    ENSURE(c->fpos, sizeof(uint64_t) * (size_t)(nf + 1));
+    ENSURE(c->scan_prefix, sizeof(uint32_t) * sprefix.size());
+    ENSURE(c->scan_tiles, sizeof(int32_t) * (stiles.size() + 1));
+    if (!c->crctab_ready) {
+        uint16_t tab[1024];
+        frx_make_crc16_tables(tab);
+        ENSURE(c->crctab, sizeof(tab));
+        CK(cudaMemcpy(c->crctab.p, tab, sizeof(tab), cudaMemcpyHostToDevice));
+        c->crctab_ready = true;
+    }
+    CK(cudaMemcpyAsync(c->dtiles.p, tiles, sizeof(frx_dtile) * n_tiles, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(c->dprefix.p, dprefix.data(), sizeof(uint32_t) * (n_tiles + 1), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(c->scan_prefix.p, sprefix.data(), sizeof(uint32_t) * sprefix.size(), cudaMemcpyHostToDevice, st));
+    if (!stiles.empty()) CK(cudaMemcpyAsync(c->scan_tiles.p, stiles.data(), sizeof(int32_t) * stiles.size(), cudaMemcpyHostToDevice, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaMemsetAsync(tile_status_dev, 0, sizeof(int32_t) * n_tiles, st));
+    DecArgs a;
+    memset(&a, 0, sizeof(a));
+    a.bytes = bytes_dev; a.n_bytes = n_bytes; a.tiles = (const frx_dtile *)c->dtiles.p; a.dprefix = (const uint32_t *)c->dprefix.p;
+    a.frame_pos = (uint64_t *)c->fpos.p; a.frame_size = frame_size_dev; a.crc_tab = (const uint16_t *)c->crctab.p;
+    a.out = out_dev; a.tile_status = tile_status_dev; a.total_frames = (uint32_t)nf; a.n_tiles = n_tiles; a.blocksize = blocksize;
+    a.pcm_mode = pcm_mode; a.verify_crc = c->verify_crc;
+    CK(frx_launch_frame_pos(a, st));
+    c->launches += 1;
+    if (!stiles.empty()) {
+        CK(frx_launch_discover(a, (const uint32_t *)c->scan_prefix.p, (const int32_t *)c->scan_tiles.p, (int)stiles.size(), (uint32_t)nu, st));
+        c->launches += 1;
+    }
+    CK(cudaEventRecord(c->ev[2], st));
+    CK(frx_launch_decode(a, out_dtype, st));
+    CK(cudaEventRecord(c->ev[3], st));
+    c->dec_timed = true;
+    c->launches += 1;
+    return FRX_OK;
+}
+
+int frx_decode_tiles(frx_ctx *c, const uint8_t *bytes_dev, uint64_t n_bytes, const frx_dtile *tiles, int32_t n_tiles,
+                     const uint32_t *frame_size_dev, int32_t blocksize, int32_t out_dtype, int32_t pcm_mode, void *out_dev,
+                     int32_t *tile_status_dev, void *stream) {
+    if (!c) return set_err(FRX_E_INVALID, "ctx is NULL");
+    CK(cudaSetDevice(c->device));
+    return decode_core(c, bytes_dev, n_bytes, tiles, n_tiles, frame_size_dev, blocksize, out_dtype, pcm_mode, out_dev, tile_status_dev,
+                       (cudaStream_t)stream);
+}
+
+int frx_dequantize(frx_ctx *c, const int32_t *pcm_dev, int32_t h, int32_t w, int32_t channels, int32_t bps, int32_t out_dtype,
+                   int32_t pcm_mode, double dmin, double dmax, void *out_dev, void *stream) {
+    if (!c) return set_err(FRX_E_INVALID, "ctx is NULL");
+    if (!pcm_dev || !out_dev || h <= 0 || w <= 0 || channels < 1) return set_err(FRX_E_INVALID, "bad argument");
+    if (out_dtype < FRX_U8 || out_dtype > FRX_F32) return set_err(FRX_E_INVALID, "bad out_dtype %d", out_dtype);
+    CK(cudaSetDevice(c->device));
+    CK(frx_launch_dequantize(pcm_dev, h, w, channels, bps, out_dtype, pcm_mode, dmin, dmax, out_dev, (cudaStream_t)stream));
+    c->launches += 1;
+    return FRX_OK;
+}
+
+// ---- host-buffer entry points: stage, run, fetch ---------------------------------------------
+int frx_encode_tiles_host(frx_ctx *c, const frx_raster *raster_host, const frx_tile *tiles, int32_t n_tiles,
+                          const frx_encode_params *p, const frx_encode_out *out) {
+    if (!c) return set_err(FRX_E_INVALID, "ctx is NULL");
+    int rc = check_params(p); if (rc) return rc;
+    rc = check_raster(raster_host); if (rc) return rc;
+    if (!out || !out->bytes) return set_err(FRX_E_INVALID, "out->bytes is NULL");
+    frx_raster r = normalise_raster(raster_host);
+    rc = check_tiles(tiles, n_tiles, r.bands, r.height, r.width); if (rc) return rc;
+    CK(cudaSetDevice(c->device));
+    uint64_t total_frames = 0, max_bytes = 0;
+    rc = frx_encode_bound(tiles, n_tiles, r.dtype, p, &total_frames, &max_bytes); if (rc) return rc;
+    const size_t esz = (size_t)frx_dtype_size(r.dtype);
+    // H2D: the band range the tiles touch, row range likewise (dense copy of the covering box)
+    long long r0 = r.height, r1 = 0, b0 = r.bands, b1 = 0;
+    for (int i = 0; i < n_tiles; i++) {
+        if (tiles[i].row_off < r0) r0 = tiles[i].row_off;
+        if (tiles[i].row_off + tiles[i].h > r1) r1 = tiles[i].row_off + tiles[i].h;
+        if (tiles[i].first_band < b0) b0 = tiles[i].first_band;
+        if (tiles[i].first_band + tiles[i].n_channels > b1) b1 = tiles[i].first_band + tiles[i].n_channels;
+    }
+    const long long rows = r1 - r0, nb = b1 - b0;
+    const size_t plane = (size_t)rows * (size_t)r.width;
+    ENSURE(c->h_raster, plane * (size_t)nb * esz);
+    cudaStream_t st = 0;
+    for (long long b = 0; b < nb; b++) {
+        const char *src = (const char *)r.data + ((size_t)(b0 + b) * (size_t)r.band_stride + (size_t)r0 * (size_t)r.row_stride) * esz;
+        CK(cudaMemcpy2DAsync((char *)c->h_raster.p + (size_t)b * plane * esz, (size_t)r.width * esz, src, (size_t)r.row_stride * esz,
+                             (size_t)r.width * esz, (size_t)rows, cudaMemcpyHostToDevice, st));
+    }
+    std::vector<frx_tile> lt(tiles, tiles + n_tiles);
+    for (auto &t : lt) { t.row_off -= (int32_t)r0; t.first_band -= (int32_t)b0; }
+    frx_raster rd = r;
+    rd.data = c->h_raster.p; rd.bands = (int32_t)nb; rd.height = rows; rd.row_stride = r.width; rd.band_stride = (long long)plane;
+    // device outputs
+    uint64_t cap = out->capacity < max_bytes ? out->capacity : max_bytes;
+    ENSURE(c->h_bytes, cap + 16);
+    size_t small = sizeof(uint64_t) * 2 * (size_t)n_tiles + sizeof(double) * 2 * (size_t)n_tiles + sizeof(uint32_t) * (size_t)total_frames +
+                   sizeof(uint64_t) * (size_t)total_frames + 64;
+    ENSURE(c->h_small, small);
+    char *sp = (char *)c->h_small.p;
+    frx_encode_out od;
+    memset(&od, 0, sizeof(od));
+    od.bytes = (uint8_t *)c->h_bytes.p; od.capacity = cap;
+    od.total_bytes = (uint64_t *)sp; sp += 16;
+    od.status = (int32_t *)sp; sp += 16;
+    od.tile_offset = (uint64_t *)sp; sp += sizeof(uint64_t) * n_tiles;
+    od.tile_size = (uint64_t *)sp; sp += sizeof(uint64_t) * n_tiles;
+    od.tile_minmax = (double *)sp; sp += sizeof(double) * 2 * n_tiles;
+    od.frame_offset = (uint64_t *)sp; sp += sizeof(uint64_t) * total_frames;
+    od.frame_size = (uint32_t *)sp;
+    rc = frx_encode_tiles(c, &rd, lt.data(), n_tiles, p, &od, st); if (rc) return rc;
+    uint64_t total = 0;
+    int32_t status = 0;
+    CK(cudaMemcpyAsync(&total, od.total_bytes, sizeof(total), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&status, od.status, sizeof(status), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (out->total_bytes) *out->total_bytes = total;
+    if (out->status) *out->status = status;
+    if (status) return set_err(status, "output capacity %llu too small (need %llu)", (unsigned long long)out->capacity, (unsigned long long)total);
+    CK(cudaMemcpyAsync(out->bytes, od.bytes, total, cudaMemcpyDeviceToHost, st));
+    if (out->tile_offset) CK(cudaMemcpyAsync(out->tile_offset, od.tile_offset, sizeof(uint64_t) * n_tiles, cudaMemcpyDeviceToHost, st));
+    if (out->tile_size) CK(cudaMemcpyAsync(out->tile_size, od.tile_size, sizeof(uint64_t) * n_tiles, cudaMemcpyDeviceToHost, st));
+    if (out->tile_minmax) CK(cudaMemcpyAsync(out->tile_minmax, od.tile_minmax, sizeof(double) * 2 * n_tiles, cudaMemcpyDeviceToHost, st));
+    if (out->frame_offset) CK(cudaMemcpyAsync(out->frame_offset, od.frame_offset, sizeof(uint64_t) * total_frames, cudaMemcpyDeviceToHost, st));
+    if (out->frame_size) CK(cudaMemcpyAsync(out->frame_size, od.frame_size, sizeof(uint32_t) * total_frames, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return FRX_OK;
+}
+
+int frx_decode_tiles_host(frx_ctx *c, const uint8_t *bytes_host, uint64_t n_bytes, const frx_dtile *tiles, int32_t n_tiles,
+                          const uint32_t *frame_size_host, int32_t blocksize, int32_t out_dtype, int32_t pcm_mode, void *out_host,
+                          uint64_t out_elems, int32_t *tile_status_host) {
+    if (!c) return set_err(FRX_E_INVALID, "ctx is NULL");
+    if (!bytes_host || !out_host || !tiles || n_tiles <= 0) return set_err(FRX_E_INVALID, "NULL argument");
+    if (out_dtype < FRX_U8 || out_dtype > FRX_F32) return set_err(FRX_E_INVALID, "bad out_dtype %d", out_dtype);
+    CK(cudaSetDevice(c->device));
+    cudaStream_t st = 0;
+    const size_t esz = (size_t)frx_dtype_size(out_dtype);
+    uint64_t nfs = 0;
+    for (int i = 0; i < n_tiles; i++)
+        if (tiles[i].first_frame != 0xFFFFFFFFu && (uint64_t)tiles[i].first_frame + tiles[i].n_frames > nfs) nfs = (uint64_t)tiles[i].first_frame + tiles[i].n_frames;
+    ENSURE(c->h_bytes, n_bytes + 16);
+    ENSURE(c->h_out, out_elems * esz + 16);
+    ENSURE(c->h_small, sizeof(uint32_t) * (size_t)nfs + sizeof(int32_t) * (size_t)n_tiles + 64);
+    uint32_t *fs_dev = nullptr;
+    int32_t *status_dev = (int32_t *)c->h_small.p;
+    CK(cudaMemcpyAsync(c->h_bytes.p, bytes_host, n_bytes, cudaMemcpyHostToDevice, st));
+    if (nfs) {
+        if (!frame_size_host) return set_err(FRX_E_INVALID, "frame_size_host is NULL");
+        fs_dev = (uint32_t *)((char *)c->h_small.p + (((size_t)n_tiles * 4 + 63) & ~(size_t)63));
+        ENSURE(c->h_small, (((size_t)n_tiles * 4 + 63) & ~(size_t)63) + sizeof(uint32_t) * (size_t)nfs + 64);
+        status_dev = (int32_t *)c->h_small.p;
+        fs_dev = (uint32_t *)((char *)c->h_small.p + (((size_t)n_tiles * 4 + 63) & ~(size_t)63));
+        CK(cudaMemcpyAsync(fs_dev, frame_size_host, sizeof(uint32_t) * (size_t)nfs, cudaMemcpyHostToDevice, st));
+    }
+    int rc = decode_core(c, (const uint8_t *)c->h_bytes.p, n_bytes, tiles, n_tiles, fs_dev, blocksize, out_dtype, pcm_mode, c->h_out.p,
+                         status_dev, st);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(out_host, c->h_out.p, out_elems * esz, cudaMemcpyDeviceToHost, st));
+    std::vector<int32_t> status(n_tiles);
+    CK(cudaMemcpyAsync(status.data(), status_dev, sizeof(int32_t) * n_tiles, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    int worst = 0;
+    for (int i = 0; i < n_tiles; i++) {
+        if (tile_status_host) tile_status_host[i] = status[i];
+        if (status[i] && !worst) worst = status[i];
+    }
+    if (worst) return set_err(worst, "decode failed for at least one tile (status %d)", worst);
+    return FRX_OK;
+}
+
+}  // extern "C"

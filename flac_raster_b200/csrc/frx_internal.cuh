@@ -1,0 +1,67 @@
+// frx_internal.cuh -- argument blocks and launcher prototypes shared by the libfrx translation units.
+#pragma once
+#include "frx_common.cuh"
+
+struct EncArgs {
+    const void *raster;
+    long long H, W, band_stride, row_stride;
+    const frx_tile *tiles;
+    const uint32_t *frame_prefix;
+    const FrxQuant *quant;
+    const float *window;
+    const uint16_t *crc_xpow;
+    uint8_t *bytes;
+    uint64_t capacity;
+    uint32_t *frame_size;
+    uint64_t *frame_offset;
+    uint64_t *desc;
+    uint32_t *ticket;
+    int32_t *status;
+    uint64_t *total_bytes;
+    uint32_t total_frames;
+    int n_tiles;
+    int blocksize;
+    int bps;
+    int pcm_mode;
+    int sr_code;
+    int sample_rate;
+    int max_lpc_order;
+    int max_po;
+    int qlp_precision;
+    int frame_words;
+    int crc_chunk;
+};
+struct DecArgs {
+    const uint8_t *bytes;
+    uint64_t n_bytes;
+    const frx_dtile *tiles;
+    const uint32_t *dprefix;
+    uint64_t *frame_pos;
+    const uint32_t *frame_size;
+    const uint16_t *crc_tab;
+    void *out;
+    int32_t *tile_status;
+    uint32_t total_frames;
+    int n_tiles;
+    int blocksize;
+    int pcm_mode;
+    int verify_crc;
+};
+size_t frx_enc_smem_bytes(int frame_words);
+size_t frx_minmax_raw_size();
+cudaError_t frx_launch_minmax(const frx_raster &r, const frx_tile *tiles_dev, const uint32_t *unit_prefix_dev, int n_tiles,
+                              uint32_t total_units, int unit_elems, void *mm_raw, FrxQuant *quant, cudaStream_t st);
+cudaError_t frx_launch_encode(const EncArgs &a, int dtype, int sm_count, cudaStream_t st);
+cudaError_t frx_launch_tile_index(const uint32_t *frame_prefix, const uint32_t *frame_size, const uint64_t *frame_offset,
+                                  const FrxQuant *q, int dtype, int n_tiles, uint64_t *tile_offset, uint64_t *tile_size,
+                                  double *tile_minmax, cudaStream_t st);
+cudaError_t frx_launch_quantize(const frx_raster &r, const frx_tile &t, const FrxQuant *q, int mode, int32_t *pcm, double *minmax,
+                                cudaStream_t st);
+void frx_make_crc16_tables(uint16_t *tab);
+cudaError_t frx_launch_frame_pos(const DecArgs &a, cudaStream_t st);
+cudaError_t frx_launch_discover(const DecArgs &a, const uint32_t *unit_prefix, const int32_t *unit_tiles, int n_scan_tiles,
+                                uint32_t total_units, cudaStream_t st);
+cudaError_t frx_launch_decode(const DecArgs &a, int out_dtype, cudaStream_t st);
+cudaError_t frx_launch_dequantize(const int32_t *pcm, int h, int w, int channels, int bps, int out_dtype, int mode, double dmin,
+                                  double dmax, void *out, cudaStream_t st);
+

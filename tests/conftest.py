@@ -1,0 +1,31 @@
+import os
+import sys
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+GOLDEN = ROOT / "tests" / "golden"
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run with -m gpu on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def golden():
+    import numpy as np
+    return np.load(GOLDEN / "quant_golden.npz")
+
+
+@pytest.fixture(scope="session")
+def codec():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from flac_raster_b200.codec import Codec
+    c = Codec(0)
+    yield c
+    c.close()

@@ -1,0 +1,219 @@
+"""GPU parity tests: the CUDA path (through the C-ABI) against the CPU oracle."""
+import numpy as np
+import pytest
+
+import oracle
+from oracle import quant
+from tests.helpers import check_encode_against_oracle, tiles_for
+
+pytestmark = pytest.mark.gpu
+
+
+def _torch_raster(a):
+    import torch
+    tmap = {"uint16": torch.uint16, "uint32": torch.uint32}
+    if str(a.dtype) in tmap:
+        signed = a.view({"uint16": np.int16, "uint32": np.int32}[str(a.dtype)])
+        return torch.from_numpy(signed.copy()).cuda().view(tmap[str(a.dtype)])
+    return torch.from_numpy(a.copy()).cuda()
+
+
+def _encode(codec, raster_np, tiles, **kw):
+    import torch
+    t = _torch_raster(np.ascontiguousarray(raster_np))
+    res = codec.encode_tiles(t, tiles, **kw)
+    torch.cuda.synchronize()
+    assert int(res.status.item()) == 0
+    total = int(res.total_bytes.item())
+    return (res, res.bytes[:total].cpu().numpy(), res.tile_offset.cpu().numpy(), res.tile_size.cpu().numpy(),
+            res.tile_minmax.cpu().numpy(), res.frame_size.cpu().numpy())
+
+
+@pytest.mark.parametrize("name", ["rgb", "dem", "ms", "u8_small", "u8_narrow", "u16_12bit", "u16_full", "i16_dem",
+                                  "i16_wrap", "i16_neg", "i32_mid", "i32_wide", "u32_mid", "const_u16", "f32_norm",
+                                  "f32_dem", "f32_overflow"])
+def test_quantize_matches_reference(codec, golden, name):
+    """P1: frx_quantize == RasterFLACConverter._normalize_to_audio + pyFLAC astype(int32) (golden from the reference)."""
+    import torch
+    r = golden[f"in_{name}"]
+    bands, h, w = r.shape
+    pcm, mm = codec.quantize(_torch_raster(r), (0, 0, h, w, 0, bands))
+    torch.cuda.synchronize()
+    want = golden[f"audio_{name}"].astype(np.int32).reshape(-1, bands)
+    assert np.array_equal(pcm.cpu().numpy(), want)
+    mmw = golden[f"minmax_{name}"]
+    got = mm.cpu().numpy()
+    assert np.array_equal(got, mmw, equal_nan=True)
+
+
+@pytest.mark.parametrize("name", ["rgb", "dem", "ms", "u8_small", "u16_12bit", "u16_full", "i16_dem", "i16_wrap",
+                                  "i32_mid", "u32_mid", "const_u16", "f32_norm", "f32_dem"])
+def test_dequantize_matches_reference(codec, golden, name):
+    """P3: frx_dequantize == FileDecoder (/32768, top 16 bits) + _denormalize_from_audio (golden from the reference)."""
+    import torch
+    r = golden[f"in_{name}"]
+    bands, h, w = r.shape
+    audio = golden[f"audio_{name}"]
+    bps = audio.dtype.itemsize * 8
+    pcm = torch.from_numpy(audio.astype(np.int32).reshape(-1, bands).copy()).cuda()
+    mm = golden[f"minmax_{name}"]
+    out = codec.dequantize(pcm, h, w, bands, bps, str(r.dtype), float(mm[0]), float(mm[1]))
+    torch.cuda.synchronize()
+    got = out.cpu().view({"uint16": torch.int16, "uint32": torch.int32}.get(str(r.dtype), out.dtype)).numpy().view(r.dtype)
+    assert np.array_equal(got, golden[f"denorm_{name}"], equal_nan=True)
+
+
+@pytest.mark.parametrize("name,tile", [("rgb", 256), ("rgb", 100), ("dem", 512), ("dem", 256), ("ms", 200), ("ms", 64),
+                                       ("u16_12bit", 64), ("i16_dem", 96), ("i32_mid", 50), ("f32_dem", 48),
+                                       ("f32_norm", 64), ("const_u16", 16), ("u8_narrow", 40), ("i16_wrap", 8),
+                                       ("u32_mid", 20), ("f32_overflow", 12)])
+def test_encode_streams_decode_to_reference_pcm(codec, golden, name, tile):
+    """P1+P2 and the <= 2 % size gate on the fixtures and seeded cases, all bands as channels."""
+    r = golden[f"in_{name}"]
+    tiles = tiles_for(r, tile, "all")
+    _, data, toff, tsize, tmm, fsize = _encode(codec, r, tiles)
+    check_encode_against_oracle(r, tiles, data, toff, tsize, tmm, fsize)
+
+
+def test_rgb_fixture_size_gate(codec, golden):
+    """frames for the G1 PCM must be <= 1.02 x 178 857 B (libFLAC 1.4.3 level 5)."""
+    r = golden["in_rgb"]
+    tiles = [(0, 0, 256, 256, 0, 3)]
+    _, data, toff, tsize, tmm, fsize = _encode(codec, r, tiles)
+    assert int(tsize[0]) <= 182434, int(tsize[0])
+
+
+@pytest.mark.parametrize("level", [0, 3, 8])
+def test_levels(codec, golden, level):
+    r = golden["in_dem"]
+    tiles = tiles_for(r, 256, "all")
+    _, data, toff, tsize, tmm, fsize = _encode(codec, r, tiles, level=level)
+    check_encode_against_oracle(r, tiles, data, toff, tsize, tmm, fsize, level=level, size_margin=1.03)
+
+
+def _roundtrip_decode(codec, r, tiles, res, pcm_mode="reference"):
+    import torch
+    from flac_raster_b200.codec import make_dtiles
+    bands, H, W = r.shape
+    entries = []
+    out_elems = 0
+    toff = res.tile_offset.cpu().numpy(); tsize = res.tile_size.cpu().numpy(); mm = res.tile_minmax.cpu().numpy()
+    ff = 0
+    for i, (r0, c0, h, w, b0, nch) in enumerate(tiles):
+        nfr = (h * w + 4095) // 4096
+        entries.append(dict(byte_offset=toff[i], byte_size=tsize[i], out_offset=out_elems, out_band_stride=h * w,
+                            out_row_stride=w, h=h, w=w, channels=nch, bps=res.bps, dmin=mm[i, 0], dmax=mm[i, 1],
+                            first_frame=ff, n_frames=nfr))
+        ff += nfr
+        out_elems += nch * h * w
+    from flac_raster_b200.codec import _tdtype
+    out = torch.zeros(out_elems, dtype=_tdtype(str(r.dtype)), device="cuda")
+    status = codec.decode_tiles(res.bytes, make_dtiles(entries), out, out_dtype=str(r.dtype), frame_size=res.frame_size,
+                                pcm_mode=pcm_mode, n_bytes=int(res.total_bytes.item()))
+    torch.cuda.synchronize()
+    assert not status.cpu().numpy().any(), status.cpu().numpy()
+    flat = out.cpu().view({"uint16": torch.int16, "uint32": torch.int32}.get(str(r.dtype), out.dtype)).numpy().view(r.dtype)
+    return flat, entries
+
+
+@pytest.mark.parametrize("name,tile", [("rgb", 256), ("rgb", 100), ("dem", 256), ("ms", 64), ("u16_12bit", 64),
+                                       ("i32_mid", 50), ("f32_dem", 48), ("u8_narrow", 40), ("const_u16", 16)])
+def test_gpu_decode_matches_reference_roundtrip(codec, golden, name, tile):
+    """P3 end to end: GPU decode of our own streams == reference flac_to_tiff output on the same PCM."""
+    r = golden[f"in_{name}"]
+    tiles = tiles_for(r, tile, "all")
+    res, *_ = _encode(codec, r, tiles)
+    flat, entries = _roundtrip_decode(codec, r, tiles, res)
+    for (r0, c0, h, w, b0, nch), e in zip(tiles, entries):
+        block = r[b0:b0 + nch, r0:r0 + h, c0:c0 + w]
+        pcm_ref, bps, dmin, dmax, _ = quant.reference_pcm(block)
+        want = quant.reference_decode_raster(pcm_ref, bps, h, w, nch, r.dtype, dmin, dmax)
+        got = flat[e["out_offset"]: e["out_offset"] + nch * h * w].reshape(nch, h, w)
+        assert np.array_equal(got, want.reshape(nch, h, w), equal_nan=True)
+
+
+@pytest.mark.parametrize("name", ["u16_full", "i16_dem", "u8_small", "i32_wide", "f32_overflow", "u32_mid"])
+def test_lossless_mode_roundtrip(codec, golden, name):
+    r = golden[f"in_{name}"]
+    tiles = tiles_for(r, 64, "all")
+    res, *_ = _encode(codec, r, tiles, pcm_mode="lossless")
+    flat, entries = _roundtrip_decode(codec, r, tiles, res, pcm_mode="lossless")
+    for (r0, c0, h, w, b0, nch), e in zip(tiles, entries):
+        block = r[b0:b0 + nch, r0:r0 + h, c0:c0 + w]
+        got = flat[e["out_offset"]: e["out_offset"] + nch * h * w].reshape(nch, h, w)
+        assert np.array_equal(got.view(np.uint8 if r.dtype.itemsize == 1 else got.dtype).tobytes(), np.ascontiguousarray(block).tobytes())
+
+
+def test_decode_reference_fixture_rgb(codec, golden):
+    """Our decoder on a libFLAC-1.4.3-produced file (no frame table -> sync discovery): G1 -> G3."""
+    import torch
+    from pathlib import Path
+    from flac_raster_b200 import flacmeta
+    from flac_raster_b200.codec import make_dtiles
+    data = (Path(__file__).parent / "golden" / "sample_rgb.flac").read_bytes()
+    hdr = flacmeta.parse_header(data)
+    si = hdr.streaminfo
+    n = len(data) - hdr.first_frame_offset
+    e = dict(byte_offset=hdr.first_frame_offset, byte_size=n, out_offset=0, out_band_stride=256 * 256, out_row_stride=256,
+             h=256, w=256, channels=si.channels, bps=si.bps, dmin=1.0, dmax=255.0, first_frame=None, n_frames=16)
+    buf = torch.from_numpy(np.frombuffer(data, dtype=np.uint8).copy()).cuda()
+    out = torch.zeros(3 * 256 * 256, dtype=torch.uint8, device="cuda")
+    status = codec.decode_tiles(buf, make_dtiles([e]), out, out_dtype="uint8")
+    torch.cuda.synchronize()
+    assert int(status[0].item()) == 0
+    assert np.array_equal(out.cpu().numpy().reshape(3, 256, 256), golden["fixture_rgb"])
+
+
+def test_decode_reference_fixture_dem_spatial(codec):
+    """G4: four concatenated bps-32 streams, all-zero PCM."""
+    import torch
+    from pathlib import Path
+    from flac_raster_b200 import flacmeta
+    from flac_raster_b200.codec import make_dtiles
+    data = (Path(__file__).parent / "golden" / "sample_dem.flac").read_bytes()
+    starts = [0, 10426, 18880, 27334]
+    entries = []
+    for i, s in enumerate(starts):
+        hdr = flacmeta.parse_header(data, s)
+        end = starts[i + 1] if i + 1 < 4 else len(data)
+        entries.append(dict(byte_offset=hdr.first_frame_offset, byte_size=end - hdr.first_frame_offset, out_offset=i * 65536,
+                            out_band_stride=65536, out_row_stride=256, h=256, w=256, channels=1, bps=32, dmin=0.0,
+                            dmax=0.0, first_frame=None, n_frames=16))
+    buf = torch.from_numpy(np.frombuffer(data, dtype=np.uint8).copy()).cuda()
+    out = torch.full((4 * 65536,), 7, dtype=torch.int32, device="cuda")
+    status = codec.decode_tiles(buf, make_dtiles(entries), out, out_dtype="int32", pcm_mode="lossless")
+    torch.cuda.synchronize()
+    assert not status.cpu().numpy().any()
+    assert int(out.abs().max().item()) == 0
+
+
+def test_host_entry_points_roundtrip(codec, golden):
+    from flac_raster_b200.codec import make_dtiles
+    r = golden["in_dem"]
+    tiles = tiles_for(r, 256, "all")
+    res = codec.encode_tiles_host(r, tiles)
+    total = int(res.total_bytes[0])
+    check_encode_against_oracle(r, tiles, res.bytes[:total], res.tile_offset, res.tile_size, res.tile_minmax, res.frame_size)
+    entries, ff, oe = [], 0, 0
+    for i, (r0, c0, h, w, b0, nch) in enumerate(tiles):
+        nfr = (h * w + 4095) // 4096
+        entries.append(dict(byte_offset=res.tile_offset[i], byte_size=res.tile_size[i], out_offset=oe, out_band_stride=h * w,
+                            out_row_stride=w, h=h, w=w, channels=nch, bps=res.bps, dmin=res.tile_minmax[i, 0],
+                            dmax=res.tile_minmax[i, 1], first_frame=ff, n_frames=nfr))
+        ff += nfr; oe += nch * h * w
+    out = np.zeros(oe, dtype=r.dtype)
+    status = codec.decode_tiles_host(res.bytes[:total], make_dtiles(entries), out, frame_size=res.frame_size.astype(np.uint32))
+    assert not status.any()
+    for (r0, c0, h, w, b0, nch), e in zip(tiles, entries):
+        block = r[b0:b0 + nch, r0:r0 + h, c0:c0 + w]
+        pcm_ref, bps, dmin, dmax, _ = quant.reference_pcm(block)
+        want = quant.reference_decode_raster(pcm_ref, bps, h, w, nch, r.dtype, dmin, dmax)
+        assert np.array_equal(out[e["out_offset"]: e["out_offset"] + nch * h * w].reshape(nch, h, w), want.reshape(nch, h, w))
+
+
+def test_more_than_8_channels_is_rejected(codec):
+    import torch
+    from flac_raster_b200._lib import FrxUnsupported
+    t = torch.zeros((12, 64, 64), dtype=torch.int16, device="cuda")
+    with pytest.raises(FrxUnsupported):
+        codec.encode_tiles(t, [(0, 0, 64, 64, 0, 12)])
