@@ -195,7 +195,10 @@ class Codec:
 
     # ---- host path (what a pyflac-style caller binds) -----------------------------------------
     def encode_tiles_host(self, raster: np.ndarray, tiles, level: int = 5, blocksize: int = 4096,
-                          sample_rate: int = 44100, pcm_mode: str = "reference") -> EncodeResult:
+                          sample_rate: int = 44100, pcm_mode: str = "reference",
+                          out: EncodeResult | None = None) -> EncodeResult:
+        """Host buffers in, host buffers out (numpy; pass views of pinned torch tensors for full PCIe speed).
+        `out` lets the caller reuse (pinned) output arrays across calls."""
         raster = np.ascontiguousarray(raster)
         dtype = str(raster.dtype)
         bands, H, W = raster.shape
@@ -203,13 +206,14 @@ class Codec:
         n = len(arr)
         p = self._params(level, blocksize, sample_rate, pcm_mode)
         nf, nb = self.encode_bound(tiles, dtype, level, blocksize, sample_rate, pcm_mode)
-        res = EncodeResult(bytes=np.empty(nb, dtype=np.uint8), tile_offset=np.zeros(n, dtype=np.int64),
+        res = out if out is not None else EncodeResult(bytes=np.empty(nb, dtype=np.uint8), tile_offset=np.zeros(n, dtype=np.int64),
                            tile_size=np.zeros(n, dtype=np.int64), tile_minmax=np.zeros((n, 2), dtype=np.float64),
                            frame_size=np.zeros(nf, dtype=np.int32), frame_offset=np.zeros(nf, dtype=np.int64),
                            total_bytes=np.zeros(1, dtype=np.int64), status=np.zeros(1, dtype=np.int32),
                            frames_per_tile=np.array([(t.h * t.w + blocksize - 1) // blocksize for t in arr],
                                                     dtype=np.int64),
                            bps=pcm_bps(dtype, pcm_mode), blocksize=blocksize)
+        nb = int(res.bytes.size)
         o = L.EncodeOut(res.bytes.ctypes.data, nb, res.tile_offset.ctypes.data, res.tile_size.ctypes.data,
                         res.tile_minmax.ctypes.data, res.frame_size.ctypes.data, res.frame_offset.ctypes.data,
                         res.total_bytes.ctypes.data, res.status.ctypes.data)
