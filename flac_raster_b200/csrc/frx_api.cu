@@ -55,6 +55,17 @@ static int ensure(Buf &b, size_t bytes) {
 }
 #define ENSURE(buf, bytes) do { int _r = ensure(buf, bytes); if (_r) return _r; } while (0)
 
+static int ensure_crctab(frx_ctx *c) {
+    if (!c->crctab_ready) {
+        uint16_t tab[1024];
+        frx_make_crc16_tables(tab);
+        ENSURE(c->crctab, sizeof(tab));
+        CK(cudaMemcpy(c->crctab.p, tab, sizeof(tab), cudaMemcpyHostToDevice));
+        c->crctab_ready = true;
+    }
+    return FRX_OK;
+}
+
 extern "C" {
 
 int frx_version(void) { return FRX_VERSION_MAJOR * 100 + FRX_VERSION_MINOR; }
@@ -265,24 +276,23 @@ int frx_encode_tiles(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *t
     }
     const uint64_t fb = frame_bytes_bound(prep.max_channels, prep.bps, p->blocksize);
     const int frame_words = (int)((fb + 3) / 4) + 4;
-    int Lc = (int)((fb + FRX_ENC_THREADS - 1) / FRX_ENC_THREADS);
-    Lc = (Lc + 3) & ~3;
-    if (c->xpow_L != Lc) {
-        // x^(8*Lc*j) mod P for j = 0..255
-        uint32_t x8L = 1;  // x^0
-        {
-            uint32_t base = 2;  // x
-            uint32_t e = 8u * (uint32_t)Lc;
-            uint32_t acc = 1;
+    if (c->xpow_L != 1) {
+        // x^(32 * 2^lg * j) mod P for lg = 0..10, j = 0..63 (CRC chunk combine, frx_encode.cu)
+        std::vector<uint16_t> xp(11 * 64);
+        for (int lg = 0; lg <= 10; lg++) {
+            uint32_t base = 2, e = 32u << lg, acc = 1;   // x^(32 * 2^lg)
             while (e) { if (e & 1u) acc = frx_gf16_mulmod(acc, base); base = frx_gf16_mulmod(base, base); e >>= 1; }
-            x8L = acc;
+            uint32_t cur = 1;
+            for (int j = 0; j < 64; j++) { xp[lg * 64 + j] = (uint16_t)cur; cur = frx_gf16_mulmod(cur, acc); }
         }
-        std::vector<uint16_t> xp(FRX_ENC_THREADS);
-        uint32_t cur = 1;
-        for (int j = 0; j < FRX_ENC_THREADS; j++) { xp[j] = (uint16_t)cur; cur = frx_gf16_mulmod(cur, x8L); }
-        ENSURE(c->xpow, sizeof(uint16_t) * FRX_ENC_THREADS);
-        CK(cudaMemcpy(c->xpow.p, xp.data(), sizeof(uint16_t) * FRX_ENC_THREADS, cudaMemcpyHostToDevice));
-        c->xpow_L = Lc;
+        ENSURE(c->xpow, sizeof(uint16_t) * xp.size());
+        CK(cudaMemcpy(c->xpow.p, xp.data(), sizeof(uint16_t) * xp.size(), cudaMemcpyHostToDevice));
+        c->xpow_L = 1;
+    }
+    if (frame_words > 64 * 1024 * 4) return set_err(FRX_E_UNSUPPORTED, "frame too large for the CRC chunk tables");
+    {
+        int rc2 = ensure_crctab(c);
+        if (rc2) return rc2;
     }
     ENSURE(c->desc, sizeof(uint64_t) * (size_t)prep.total_frames);
     ENSURE(c->misc, 64);
@@ -309,7 +319,7 @@ int frx_encode_tiles(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *t
     a.sr_code = sample_rate_code(p->sample_rate); a.sample_rate = p->sample_rate;
     a.max_lpc_order = lvl_lpc[p->compression_level]; a.max_po = lvl_po[p->compression_level];
     a.qlp_precision = qlp_precision_for(prep.bps, p->blocksize);
-    a.frame_words = frame_words; a.crc_chunk = Lc;
+    a.frame_words = frame_words; a.dtype = r.dtype; a.crc_tab = (const uint16_t *)c->crctab.p;
     if (frx_enc_smem_bytes(frame_words) > 227 * 1024) return set_err(FRX_E_UNSUPPORTED, "frame buffer does not fit shared memory");
     CK(cudaEventRecord(c->ev[0], st));
     CK(frx_launch_encode(a, r.dtype, c->sm_count, st));
@@ -373,13 +383,7 @@ static int decode_core(frx_ctx *c, const uint8_t *bytes_dev, uint64_t n_bytes, c
     ENSURE(c->fpos, sizeof(uint64_t) * (size_t)(nf + 1));
     ENSURE(c->scan_prefix, sizeof(uint32_t) * sprefix.size());
     ENSURE(c->scan_tiles, sizeof(int32_t) * (stiles.size() + 1));
-    if (!c->crctab_ready) {
-        uint16_t tab[1024];
-        frx_make_crc16_tables(tab);
-        ENSURE(c->crctab, sizeof(tab));
-        CK(cudaMemcpy(c->crctab.p, tab, sizeof(tab), cudaMemcpyHostToDevice));
-        c->crctab_ready = true;
-    }
+    { int rc2 = ensure_crctab(c); if (rc2) return rc2; }
     CK(cudaMemcpyAsync(c->dtiles.p, tiles, sizeof(frx_dtile) * n_tiles, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(c->dprefix.p, dprefix.data(), sizeof(uint32_t) * (n_tiles + 1), cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(c->scan_prefix.p, sprefix.data(), sizeof(uint32_t) * sprefix.size(), cudaMemcpyHostToDevice, st));

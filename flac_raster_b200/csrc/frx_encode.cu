@@ -142,7 +142,8 @@ __global__ void frx_tile_index_kernel(const uint32_t *frame_prefix, const uint32
 }
 
 // ------------------------------------------------------------------------------------------
-// bit writer into the zero-initialised shared frame buffer (big-endian 32-bit words)
+// bit writer into the zero-initialised shared frame buffer (big-endian 32-bit words).  A thread's first and
+// last words may be shared with its neighbours (atomicOr); the words in between are its own (plain stores).
 // ------------------------------------------------------------------------------------------
 struct BitW {
     uint32_t *buf;
@@ -183,226 +184,290 @@ struct BitW {
 };
 
 // ------------------------------------------------------------------------------------------
-// block-wide helpers (256 threads)
+// warp helpers
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t warp_sum_u32(uint32_t v) {
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
-    return v;
-}
+#define FULLMASK 0xFFFFFFFFu
 __device__ __forceinline__ uint64_t warp_sum_u64(uint64_t v) {
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULLMASK, v, o);
     return v;
 }
 __device__ __forceinline__ double warp_sum_f64(double v) {
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULLMASK, v, o);
     return v;
 }
-
-struct EncShared {
-    // per-frame
-    uint32_t frame_idx;
-    uint32_t bitpos;        // running bit position in the frame buffer
-    uint64_t out_offset;
-    // per-subframe decisions
-    int wasted;
-    int type;               // 0 const 1 verbatim 2 fixed 3 lpc
-    int order;
-    int po;                 // partition order
-    int rice2;
-    int shift, precision;
-    int lpc_ok;
-    int lpc_order;
-    int32_t qlp[FRX_MAX_LPC];
-    uint32_t kparam[2][64];  // candidate 0 = fixed, 1 = lpc
-    int cand_po[2];
-    uint64_t cand_bits[2];
-    // reductions
-    uint64_t red64[NWARPS][8];
-    uint32_t red32[NWARPS][8];
-    double autoc[FRX_MAX_LPC + 1];
-    uint64_t psum[2][128];
-    uint64_t tabs[2][FRX_ENC_THREADS];  // per-thread sum|r| for the two candidates
-    uint32_t scan[NWARPS];
-    uint32_t crc_part[NWARPS];
-    float acpart[FRX_MAX_LPC + 1][FRX_ENC_THREADS];
-};
+// sum of 32 u32 values as u64 with two redux.sync (low / high halves cannot overflow)
+__device__ __forceinline__ uint64_t warp_sum_u32_wide(uint32_t v) {
+    uint32_t lo = __reduce_add_sync(FULLMASK, v & 0xFFFFu);
+    uint32_t hi = __reduce_add_sync(FULLMASK, v >> 16);
+    return (uint64_t)lo + ((uint64_t)hi << 16);
+}
+__device__ __forceinline__ uint32_t zigzag(int32_t r) { return ((uint32_t)r << 1) ^ (uint32_t)(r >> 31); }
 
 // libFLAC-style Rice cost estimate from the partition sum (oracle/flac_oracle.c rice_bits_estimate)
 __device__ __forceinline__ uint64_t rice_estimate(uint32_t k, uint32_t n, uint64_t s) {
     return 4ull + (uint64_t)(1 + k) * n + (k ? (s >> (k - 1)) : (s << 1)) - (n >> 1);
 }
+// smallest k with (n << k) >= s, capped at kmax  (libFLAC: rice parameter from the partition mean)
+__device__ __forceinline__ uint32_t rice_param(uint32_t n, uint64_t s, uint32_t kmax) {
+    if (n == 0 || s <= (uint64_t)n) return 0;
+    int k = (64 - __clzll((long long)s)) - (32 - __clz((int)n)) - 1;  // floor(log2 s) - floor(log2 n) - 1
+    if (k < 0) k = 0;
+    while (((uint64_t)n << k) < s) k++;  // at most 2 iterations
+    return (uint32_t)k > kmax ? kmax : (uint32_t)k;
+}
 
-// One warp analyses one candidate: partition sums from per-thread sums, Rice parameter per
-// partition, bits per partition order, best order.  tpb = threads per block-partition at po_max.
-__device__ void analyse_partitions(EncShared &sh, int cand, int nsamp, int pred_order, int po_max, uint32_t k_limit) {
+// ------------------------------------------------------------------------------------------
+// shared state of one encoder CTA
+// ------------------------------------------------------------------------------------------
+struct EncSmall {
+    uint32_t idx[2];         // ticket double buffer
+    uint32_t bitpos;         // running bit position in the frame buffer
+    uint32_t tailw;          // the frame's last partial word (CRC tail)
+    uint64_t out_offset;
+    // per-subframe decisions
+    int wasted, magbits, fixed_order, is_const, lean;
+    int lpc_ok, lpc_order, shift, precision, lpc_narrow, lpc_valid;
+    int32_t qlp[FRX_MAX_LPC];
+    int32_t warm[FRX_MAX_LPC];
+    uint32_t kparam[2][64];  // candidate 0 = fixed, 1 = lpc
+    int cand_po[2], cand_rice2[2];
+    uint64_t cand_bits[2];
+    uint64_t fsum[5];
+    // reductions
+    uint64_t red64[NWARPS][5];
+    uint32_t red32[NWARPS][4];
+    double autoc[FRX_MAX_LPC + 1];
+    uint32_t scan[NWARPS];
+    uint32_t crc_part[2];
+    uint16_t crc_tab[4][256];
+};
+#define ENC_UNION_BYTES 17408  // pcm[4096 + 255 pad + 1] int32  ==  acpart[13][256] float + tabs[2][256] u64
+#define ENC_SMALL_BYTES ((sizeof(EncSmall) + 15) & ~(size_t)15)
+#define CRC_THREADS 64
+
+// One warp analyses one candidate: partition sums from the per-thread |r| sums, Rice parameter per partition,
+// estimated bits per partition order, best order.  Lane p owns finest-level partition p (2p, 2p+1 when po_max == 6);
+// coarser levels are built with shuffles, so partition q of level L lives in lane q << (F - L).
+__device__ void analyse_partitions(EncSmall &sh, const uint64_t *tabs, int cand, int nsamp, int pred_order, int po_max, uint32_t kmax) {
     const int lane = threadIdx.x & 31;
-    uint64_t *ps = sh.psum[cand];
-    const uint64_t *tabs = sh.tabs[cand];
-    int np = 1 << po_max;
-    int tpp = (nsamp >> po_max) / FRX_SPT;  // threads per partition (>=1 unless po_max == 0)
-    if (po_max == 0) {
-        int nthr = (nsamp + FRX_SPT - 1) / FRX_SPT;
-        uint64_t s = 0;
-        for (int t = lane; t < nthr; t += 32) s += tabs[t];
-        s = warp_sum_u64(s);
-        if (lane == 0) ps[0] = s;
-    } else {
-        for (int p = lane; p < np; p += 32) {
-            uint64_t s = 0;
-            for (int t = 0; t < tpp; t++) s += tabs[p * tpp + t];
-            ps[p] = s;
-        }
-    }
-    __syncwarp();
-    // merge down: level po stored at offset (sum of 2^j for j in (po, po_max])
-    int off = 0;
-    for (int po = po_max - 1; po >= 0; po--) {
-        int n2 = 1 << po;
-        for (int p = lane; p < n2; p += 32) ps[off + np + p] = ps[off + 2 * p] + ps[off + 2 * p + 1];
-        off += np;
-        np = n2;
-        __syncwarp();
-    }
-    // cost per level
+    const int F = po_max > 5 ? 5 : po_max;               // finest level held one-per-lane
+    const int nthr = (nsamp + FRX_SPT - 1) / FRX_SPT;
+    uint64_t sum = 0, sumB = 0;                          // sumB: second half when po_max == 6
     uint64_t best = ~0ull;
     int best_po = 0;
-    off = 0;
-    for (int po = po_max; po >= 0; po--) {
-        int n2 = 1 << po;
-        uint64_t bits = 0;
-        for (int p = lane; p < n2; p += 32) {
-            uint32_t n = (uint32_t)(nsamp >> po) - (p == 0 ? (uint32_t)pred_order : 0u);
-            uint64_t s = ps[off + p];
-            uint32_t k = 0;
-            while (k < k_limit - 1 && ((uint64_t)n << k) < s) k++;
-            bits += rice_estimate(k, n, s);
-        }
-        bits = warp_sum_u64(bits) + 6;
-        if (bits < best) { best = bits; best_po = po; }
-        off += n2;
+    uint32_t kbest0 = 0, kbest1 = 0;
+    if (po_max == 6) {
+        const int tpp = (nsamp >> 6) / FRX_SPT;          // threads per level-6 partition
+        for (int t = 0; t < tpp; t++) { sum += tabs[(2 * lane) * tpp + t]; sumB += tabs[(2 * lane + 1) * tpp + t]; }
+        uint32_t n0 = (uint32_t)(nsamp >> 6) - (lane == 0 ? (uint32_t)pred_order : 0u), n1 = (uint32_t)(nsamp >> 6);
+        uint32_t k0 = rice_param(n0, sum, kmax), k1 = rice_param(n1, sumB, kmax);
+        uint64_t b = rice_estimate(k0, n0, sum) + rice_estimate(k1, n1, sumB);
+        b = warp_sum_u64(b) + 6;
+        best = b; best_po = 6; kbest0 = k0; kbest1 = k1;
+        sum += sumB;
+    } else if (F == 0) {
+        for (int t = lane; t < nthr; t += 32) sum += tabs[t];
+        sum = warp_sum_u64(sum);
+    } else {
+        const int tpp = (nsamp >> F) / FRX_SPT;          // threads per finest partition (>= 1)
+        if (lane < (1 << F))
+            for (int t = 0; t < tpp; t++) sum += tabs[lane * tpp + t];
     }
-    // store params of the best level
-    off = 0;
-    for (int po = po_max; po > best_po; po--) off += 1 << po;
-    for (int p = lane; p < (1 << best_po); p += 32) {
-        uint32_t n = (uint32_t)(nsamp >> best_po) - (p == 0 ? (uint32_t)pred_order : 0u);
-        uint64_t s = ps[off + p];
+    // levels F .. 0
+    for (int L = F; L >= 0; L--) {
+        const int step = 1 << (F - L);                   // lanes that are multiples of step hold level-L partitions
+        const bool mine = (lane & (step - 1)) == 0 && lane < (1 << F);
+        const int p = lane >> (F - L);
+        uint32_t n = (uint32_t)(nsamp >> L) - (p == 0 ? (uint32_t)pred_order : 0u);
         uint32_t k = 0;
-        while (k < k_limit - 1 && ((uint64_t)n << k) < s) k++;
-        sh.kparam[cand][p] = k;
+        uint64_t b = 0;
+        if (mine) { k = rice_param(n, sum, kmax); b = rice_estimate(k, n, sum); }
+        b = warp_sum_u64(b) + 6;
+        if (b < best) { best = b; best_po = L; kbest0 = k; }
+        if (L > 0) {
+            uint64_t o = __shfl_down_sync(FULLMASK, sum, step);
+            sum += o;                                    // valid in lanes that are multiples of 2*step
+        }
     }
-    if (lane == 0) { sh.cand_po[cand] = best_po; sh.cand_bits[cand] = best; }
+    // publish parameters of the best level
+    if (best_po == 6) { sh.kparam[cand][2 * lane] = kbest0; sh.kparam[cand][2 * lane + 1] = kbest1; }
+    else {
+        const int step = 1 << (F - best_po);
+        if ((lane & (step - 1)) == 0 && lane < (1 << F)) sh.kparam[cand][lane >> (F - best_po)] = kbest0;
+    }
+    uint32_t big = __ballot_sync(FULLMASK, kbest0 >= 15u || (best_po == 6 && kbest1 >= 15u));
+    if (lane == 0) { sh.cand_po[cand] = best_po; sh.cand_bits[cand] = best; sh.cand_rice2[cand] = big ? 1 : 0; }
     __syncwarp();
 }
 
-// LPC residual of this thread's samples; ORD taps.  s[HIST + i] is sample i of the thread.
-template <int ORD, bool WIDE>
-__device__ __forceinline__ void lpc_residual_thread(const int32_t *s, const int32_t *q, int shift, int32_t *r, uint32_t &bad) {
+// ------------------------------------------------------------------------------------------
+// K1: tile cut + band -> channel gather + PCM quantise, coalesced (thread t takes samples t, t+256, ...)
+// ------------------------------------------------------------------------------------------
+template <int DT>
+__device__ __forceinline__ void enc_load(const EncArgs &a, const frx_tile &t, const FrxQuant &qz, int ch, uint32_t s0, int nsamp,
+                                         int32_t *pcm, int tid) {
+    typedef typename FrxElem<DT>::T T;
+    const T *band = (const T *)a.raster + (long long)(t.first_band + ch) * a.band_stride + (long long)t.row_off * a.row_stride + t.col_off;
+    const uint32_t w = (uint32_t)t.w;
+    uint32_t sidx = s0 + (uint32_t)tid;
+    uint32_t row = sidx / w, col = sidx - row * w;
+    T raw[FRX_SPT];
 #pragma unroll
-    for (int i = 0; i < FRX_SPT; i++) {
-        if (WIDE) {
-            long long acc = 0;
-#pragma unroll
-            for (int j = 0; j < ORD; j++) acc += (long long)q[j] * (long long)s[HIST + i - 1 - j];
-            long long rr = (long long)s[HIST + i] - (acc >> shift);
-            if (rr <= (long long)INT32_MIN || rr > (long long)INT32_MAX) bad |= 1u << i;
-            r[i] = (int32_t)rr;
-        } else {
-            int32_t acc = 0;
-#pragma unroll
-            for (int j = 0; j < ORD; j++) acc += q[j] * s[HIST + i - 1 - j];
-            r[i] = s[HIST + i] - (acc >> shift);
+    for (int k = 0; k < FRX_SPT; k++) {
+        const int i = tid + k * FRX_ENC_THREADS;
+        raw[k] = (i < nsamp) ? __ldg(band + (long long)row * a.row_stride + col) : (T)0;
+        col += FRX_ENC_THREADS;
+        if (col >= w) {
+            if (w >= FRX_ENC_THREADS) { col -= w; row++; }
+            else { uint32_t q = col / w; row += q; col -= q * w; }
         }
     }
-}
-
-template <bool WIDE>
-__device__ __forceinline__ void lpc_residual_dispatch(int order, const int32_t *s, const int32_t *q, int shift, int32_t *r, uint32_t &bad) {
-    switch (order) {
-        case 1: lpc_residual_thread<1, WIDE>(s, q, shift, r, bad); break;
-        case 2: lpc_residual_thread<2, WIDE>(s, q, shift, r, bad); break;
-        case 3: lpc_residual_thread<3, WIDE>(s, q, shift, r, bad); break;
-        case 4: lpc_residual_thread<4, WIDE>(s, q, shift, r, bad); break;
-        case 5: lpc_residual_thread<5, WIDE>(s, q, shift, r, bad); break;
-        case 6: lpc_residual_thread<6, WIDE>(s, q, shift, r, bad); break;
-        case 7: lpc_residual_thread<7, WIDE>(s, q, shift, r, bad); break;
-        case 8: lpc_residual_thread<8, WIDE>(s, q, shift, r, bad); break;
-        case 9: lpc_residual_thread<9, WIDE>(s, q, shift, r, bad); break;
-        case 10: lpc_residual_thread<10, WIDE>(s, q, shift, r, bad); break;
-        case 11: lpc_residual_thread<11, WIDE>(s, q, shift, r, bad); break;
-        default: lpc_residual_thread<12, WIDE>(s, q, shift, r, bad); break;
+#pragma unroll
+    for (int k = 0; k < FRX_SPT; k++) {
+        const int i = tid + k * FRX_ENC_THREADS;
+        pcm[PCM_PAD(i)] = (i < nsamp) ? frx_quant<DT>(raw[k], qz, a.pcm_mode) : 0;
     }
 }
 
-template <bool WIDE>
-__device__ __forceinline__ void fixed_residual_thread(int order, const int32_t *s, int32_t *r, uint32_t &bad) {
+// residual of one sample, lean paths (no overflow possible by construction)
+template <int ORD>
+__device__ __forceinline__ int32_t lpc_res32(const int32_t *s, int i, const int32_t *q, int shift) {
+    int32_t acc = 0;
+#pragma unroll
+    for (int j = 0; j < ORD; j++) acc += q[j] * s[i - 1 - j];
+    return s[i] - (acc >> shift);
+}
+template <int ORD>
+__device__ __forceinline__ long long lpc_res64(const int32_t *s, int i, const int32_t *q, int shift) {
+    long long acc = 0;
+#pragma unroll
+    for (int j = 0; j < ORD; j++) acc += (long long)q[j] * (long long)s[i - 1 - j];
+    return (long long)s[i] - (acc >> shift);
+}
+
+// All 16 residuals of this thread for LPC order ORD.  MODE 0: 32-bit accumulate, 1: 64-bit accumulate (result
+// known to fit), 2: 64-bit with range check (fat data).  Returns a bitmask of samples whose residual does not fit.
+template <int ORD, int MODE, int HISTN>
+__device__ __forceinline__ uint32_t lpc_residuals(const int32_t *s, const int32_t *q, int shift, int32_t *r) {
+    uint32_t bad = 0;
 #pragma unroll
     for (int i = 0; i < FRX_SPT; i++) {
-        const int32_t *p = s + HIST + i;
-        if (WIDE) {
-            long long a = p[0], b = p[-1], c = p[-2], d = p[-3], e = p[-4], rr;
+        if (MODE == 0) r[i] = lpc_res32<ORD>(s, HISTN + i, q, shift);
+        else {
+            long long rr = lpc_res64<ORD>(s, HISTN + i, q, shift);
+            if (MODE == 2 && (rr <= (long long)INT32_MIN || rr > (long long)INT32_MAX)) bad |= 1u << i;
+            r[i] = (int32_t)rr;
+        }
+    }
+    return bad;
+}
+template <int MODE, int HISTN>
+__device__ __forceinline__ uint32_t lpc_residuals_dispatch(int order, const int32_t *s, const int32_t *q, int shift, int32_t *r) {
+    switch (order) {
+        case 1: return lpc_residuals<1, MODE, HISTN>(s, q, shift, r);
+        case 2: return lpc_residuals<2, MODE, HISTN>(s, q, shift, r);
+        case 3: return lpc_residuals<3, MODE, HISTN>(s, q, shift, r);
+        case 4: return lpc_residuals<4, MODE, HISTN>(s, q, shift, r);
+        default: break;
+    }
+    if (HISTN >= 8) {
+        switch (order) {
+            case 5: return lpc_residuals<5, MODE, HISTN>(s, q, shift, r);
+            case 6: return lpc_residuals<6, MODE, HISTN>(s, q, shift, r);
+            case 7: return lpc_residuals<7, MODE, HISTN>(s, q, shift, r);
+            case 8: return lpc_residuals<8, MODE, HISTN>(s, q, shift, r);
+            default: break;
+        }
+    }
+    if (HISTN >= 12) {
+        switch (order) {
+            case 9: return lpc_residuals<9, MODE, HISTN>(s, q, shift, r);
+            case 10: return lpc_residuals<10, MODE, HISTN>(s, q, shift, r);
+            case 11: return lpc_residuals<11, MODE, HISTN>(s, q, shift, r);
+            default: return lpc_residuals<12, MODE, HISTN>(s, q, shift, r);
+        }
+    }
+    return 0;
+}
+
+// fixed-order residuals; WIDE64: 64-bit with range check
+template <bool WIDE64, int HISTN>
+__device__ __forceinline__ uint32_t fixed_residuals(int order, const int32_t *s, int32_t *r) {
+    uint32_t bad = 0;
+#pragma unroll
+    for (int i = 0; i < FRX_SPT; i++) {
+        const int32_t *p = s + HISTN + i;
+        if (WIDE64) {
+            long long A = p[0], B = p[-1], C = p[-2], D = p[-3], E = p[-4], rr;
             switch (order) {
-                case 0: rr = a; break;
-                case 1: rr = a - b; break;
-                case 2: rr = a - 2 * b + c; break;
-                case 3: rr = a - 3 * b + 3 * c - d; break;
-                default: rr = a - 4 * b + 6 * c - 4 * d + e; break;
+                case 0: rr = A; break;
+                case 1: rr = A - B; break;
+                case 2: rr = A - 2 * B + C; break;
+                case 3: rr = A - 3 * B + 3 * C - D; break;
+                default: rr = A - 4 * B + 6 * C - 4 * D + E; break;
             }
             if (rr <= (long long)INT32_MIN || rr > (long long)INT32_MAX) bad |= 1u << i;
             r[i] = (int32_t)rr;
         } else {
-            int32_t a = p[0], b = p[-1], c = p[-2], d = p[-3], e = p[-4], rr;
+            int32_t A = p[0], B = p[-1], C = p[-2], D = p[-3], E = p[-4], rr;
             switch (order) {
-                case 0: rr = a; break;
-                case 1: rr = a - b; break;
-                case 2: rr = a - 2 * b + c; break;
-                case 3: rr = a - 3 * b + 3 * c - d; break;
-                default: rr = a - 4 * b + 6 * c - 4 * d + e; break;
+                case 0: rr = A; break;
+                case 1: rr = A - B; break;
+                case 2: rr = A - 2 * B + C; break;
+                case 3: rr = A - 3 * B + 3 * C - D; break;
+                default: rr = A - 4 * B + 6 * C - 4 * D + E; break;
             }
             r[i] = rr;
         }
     }
+    return bad;
 }
 
-__device__ __forceinline__ uint32_t zigzag(int32_t r) { return ((uint32_t)r << 1) ^ (uint32_t)(r >> 31); }
-
 // ------------------------------------------------------------------------------------------
-// The frame encoder
+// The frame encoder.  WIDE: PCM wider than 16 bits (64-bit LPC accumulate, RICE2).  HISTN: history samples a thread
+// keeps = the largest LPC order of the compression level (4 when the level has no LPC stage).
 // ------------------------------------------------------------------------------------------
-template <int DT, bool WIDE>
-__global__ void __launch_bounds__(FRX_ENC_THREADS) frx_encode_kernel(const EncArgs a) {
-    typedef typename FrxElem<DT>::T T;
+template <bool WIDE, int HISTN>
+__global__ void __launch_bounds__(FRX_ENC_THREADS, 2) frx_encode_kernel(const EncArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    EncShared &sh = *reinterpret_cast<EncShared *>(smem_raw);
-    int32_t *pcm = reinterpret_cast<int32_t *>(smem_raw + ((sizeof(EncShared) + 15) & ~(size_t)15));
-    uint32_t *bits = reinterpret_cast<uint32_t *>(pcm + (FRX_MAX_BLOCK + (FRX_MAX_BLOCK >> 4) + 32));
+    EncSmall &sh = *reinterpret_cast<EncSmall *>(smem_raw);
+    unsigned char *ureg = smem_raw + ENC_SMALL_BYTES;
+    int32_t *pcm = reinterpret_cast<int32_t *>(ureg);
+    float *acpart = reinterpret_cast<float *>(ureg);                          // [13][256]
+    uint64_t *tabs = reinterpret_cast<uint64_t *>(ureg + 13 * FRX_ENC_THREADS * 4);  // [2][256]
+    uint32_t *bits = reinterpret_cast<uint32_t *>(ureg + ENC_UNION_BYTES);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const T *base = (const T *)a.raster;
-    const uint32_t k_limit = a.bps > 16 ? 31u : 15u;  // RICE2 only for bps > 16 (libFLAC)
+    const uint32_t kmax = a.bps > 16 ? 30u : 14u;  // RICE2 only for bps > 16 (libFLAC)
+    const int g0 = tid * FRX_SPT;                  // first sample index of this thread
+
+    for (int i = tid; i < a.frame_words; i += FRX_ENC_THREADS) bits[i] = 0u;
+    for (int i = tid; i < 1024; i += FRX_ENC_THREADS) (&sh.crc_tab[0][0])[i] = a.crc_tab[i];
+    if (tid == 0) sh.idx[0] = atomicAdd(a.ticket, 1u);
+    int par = 0;
 
     for (;;) {
-        __syncthreads();
-        if (tid == 0) sh.frame_idx = atomicAdd(a.ticket, 1u);
-        // zero the frame buffer
-        for (int i = tid; i < a.frame_words; i += FRX_ENC_THREADS) bits[i] = 0u;
-        __syncthreads();
-        const uint32_t f = sh.frame_idx;
+        __syncthreads();  // S0: previous frame left the buffers clean; ticket visible
+        const uint32_t f = sh.idx[par];
         if (f >= a.total_frames) break;
+        if (tid == 0) sh.idx[par ^ 1] = atomicAdd(a.ticket, 1u);  // prefetch the next ticket (tickets stay ordered per CTA)
+        par ^= 1;
 
         // ---- locate tile / frame ----
         int lo = 0, hi = a.n_tiles;
         while (hi - lo > 1) {
             int mid = (lo + hi) >> 1;
-            if (a.frame_prefix[mid] <= f) lo = mid; else hi = mid;
+            if (__ldg(&a.frame_prefix[mid]) <= f) lo = mid; else hi = mid;
         }
         const frx_tile t = a.tiles[lo];
         const FrxQuant qz = a.quant[lo];
         const uint32_t fj = f - a.frame_prefix[lo];
         const long long tile_n = (long long)t.h * t.w;
-        const long long s0 = (long long)fj * a.blocksize;
-        const int nsamp = (int)min((long long)a.blocksize, tile_n - s0);
+        const uint32_t s0 = fj * (uint32_t)a.blocksize;
+        const int nsamp = (int)min((long long)a.blocksize, tile_n - (long long)s0);
         const int nthr = (nsamp + FRX_SPT - 1) / FRX_SPT;
+        const int nv = min(FRX_SPT, max(0, nsamp - g0));  // valid samples of this thread
+        const bool full = (nsamp == a.blocksize);
 
         // ---- frame header (thread 0) ----
         if (tid == 0) {
@@ -442,166 +507,207 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS) frx_encode_kernel(const EncAr
 
         // ================= per channel =================
         for (int ch = 0; ch < t.n_channels; ch++) {
-            __syncthreads();
-            // ---- K1: gather + quantise (coalesced: thread t takes samples t, t+256, ...) ----
-            {
-                const T *band = base + (long long)(t.first_band + ch) * a.band_stride + (long long)t.row_off * a.row_stride + t.col_off;
-                long long sidx = s0 + tid;
-                int row = (int)(sidx / t.w);
-                int col = (int)(sidx - (long long)row * t.w);
-                for (int i = tid; i < FRX_MAX_BLOCK; i += FRX_ENC_THREADS) {
-                    int32_t v = 0;
-                    if (i < nsamp) {
-                        T d = band[(long long)row * a.row_stride + col];
-                        v = frx_quant<DT>(d, qz, a.pcm_mode);
-                    }
-                    pcm[PCM_PAD(i)] = v;
-                    col += FRX_ENC_THREADS;
-                    while (col >= t.w) { col -= t.w; row++; }
-                }
+          bool force_verbatim = false;
+          for (;;) {  // second pass only when the Rice-coded subframe would not beat VERBATIM (then it is redone as VERBATIM)
+            __syncthreads();  // S2: union region free, bitpos visible
+            switch (a.dtype) {
+                case FRX_U8: enc_load<FRX_U8>(a, t, qz, ch, s0, nsamp, pcm, tid); break;
+                case FRX_I16: enc_load<FRX_I16>(a, t, qz, ch, s0, nsamp, pcm, tid); break;
+                case FRX_U16: enc_load<FRX_U16>(a, t, qz, ch, s0, nsamp, pcm, tid); break;
+                case FRX_I32: enc_load<FRX_I32>(a, t, qz, ch, s0, nsamp, pcm, tid); break;
+                case FRX_U32: enc_load<FRX_U32>(a, t, qz, ch, s0, nsamp, pcm, tid); break;
+                default: enc_load<FRX_F32>(a, t, qz, ch, s0, nsamp, pcm, tid); break;
             }
-            __syncthreads();
-            // ---- registers: HIST history + 16 samples ----
-            int32_t s[HIST + FRX_SPT];
-            const int g0 = tid * FRX_SPT;  // first sample index of this thread
+            __syncthreads();  // S3
+            // ---- registers: HISTN history + 16 samples ----
+            int32_t s[HISTN + FRX_SPT];
 #pragma unroll
-            for (int i = 0; i < HIST + FRX_SPT; i++) {
-                int g = g0 - HIST + i;
-                s[i] = (g >= 0 && g < FRX_MAX_BLOCK) ? pcm[PCM_PAD(g)] : 0;
+            for (int i = 0; i < HISTN + FRX_SPT; i++) {
+                int g = g0 - HISTN + i;
+                s[i] = (g >= 0) ? pcm[PCM_PAD(g)] : 0;
             }
-            // ---- wasted bits ----
-            uint32_t orv = 0;
+            uint32_t orv = 0, ora = 0;
 #pragma unroll
-            for (int i = 0; i < FRX_SPT; i++) orv |= (uint32_t)s[HIST + i];
-            for (int o = 16; o > 0; o >>= 1) orv |= __shfl_xor_sync(0xFFFFFFFFu, orv, o);
-            if (lane == 0) sh.red32[warp][0] = orv;
-            __syncthreads();
-            int wasted = 0;
+            for (int i = 0; i < FRX_SPT; i++) { orv |= (uint32_t)s[HISTN + i]; ora |= (uint32_t)abs(s[HISTN + i]); }
+            orv = __reduce_or_sync(FULLMASK, orv);
+            ora = __reduce_or_sync(FULLMASK, ora);
+            // ---- K2 (lean): fixed-order trial in 32-bit, sum |e_k| over samples g >= k ----
+            uint32_t fa0 = 0, fa1 = 0, fa2 = 0, fa3 = 0, fa4 = 0;
             {
-                uint32_t all = 0;
-#pragma unroll
-                for (int w2 = 0; w2 < NWARPS; w2++) all |= sh.red32[w2][0];
-                wasted = all ? (__ffs((int)all) - 1) : 0;
-                if (wasted) {
-#pragma unroll
-                    for (int i = 0; i < HIST + FRX_SPT; i++) s[i] >>= wasted;
-                }
-            }
-            const int sbps = a.bps - wasted;
-
-            // ---- K2: fixed-order trial (sum |e_k| over samples g >= k) ----
-            uint64_t fsum[5];
-            uint32_t fbad = 0;
-            {
-                uint64_t acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0, acc4 = 0;
+                const bool first = (tid == 0);
+                int32_t dm1 = s[HISTN - 1] - s[HISTN - 2], dm2 = s[HISTN - 2] - s[HISTN - 3], dm3 = s[HISTN - 3] - s[HISTN - 4];
+                int32_t d1p = dm1, d2p = dm1 - dm2, d3p = (dm1 - dm2) - (dm2 - dm3);
 #pragma unroll
                 for (int i = 0; i < FRX_SPT; i++) {
-                    int g = g0 + i;
-                    if (g < nsamp) {
-                        const int32_t *p = s + HIST + i;
-                        if (WIDE) {
-                            long long A = p[0], B = p[-1], C = p[-2], D = p[-3], E = p[-4];
-                            long long e0 = A, e1 = A - B, e2 = A - 2 * B + C, e3 = A - 3 * B + 3 * C - D, e4 = A - 4 * B + 6 * C - 4 * D + E;
-                            unsigned long long a0 = (unsigned long long)llabs(e0), a1 = (unsigned long long)llabs(e1), a2 = (unsigned long long)llabs(e2),
-                                               a3 = (unsigned long long)llabs(e3), a4 = (unsigned long long)llabs(e4);
-                            acc0 += a0;
-                            if (a0 > 0x7FFFFFFFull) fbad |= 1u;
-                            if (g >= 1) { acc1 += a1; if (a1 > 0x7FFFFFFFull) fbad |= 2u; }
-                            if (g >= 2) { acc2 += a2; if (a2 > 0x7FFFFFFFull) fbad |= 4u; }
-                            if (g >= 3) { acc3 += a3; if (a3 > 0x7FFFFFFFull) fbad |= 8u; }
-                            if (g >= 4) { acc4 += a4; if (a4 > 0x7FFFFFFFull) fbad |= 16u; }
-                        } else {
-                            int32_t A = p[0], B = p[-1], C = p[-2], D = p[-3], E = p[-4];
-                            int32_t e0 = A, e1 = A - B, e2 = e1 - (B - C), e3 = e2 - (B - 2 * C + D), e4 = e3 - (B - 3 * C + 3 * D - E);
-                            acc0 += (uint32_t)abs(e0);
-                            if (g >= 1) acc1 += (uint32_t)abs(e1);
-                            if (g >= 2) acc2 += (uint32_t)abs(e2);
-                            if (g >= 3) acc3 += (uint32_t)abs(e3);
-                            if (g >= 4) acc4 += (uint32_t)abs(e4);
-                        }
+                    int32_t x = s[HISTN + i];
+                    int32_t d1 = x - s[HISTN + i - 1];
+                    int32_t d2 = d1 - d1p, d3 = d2 - d2p, d4 = d3 - d3p;
+                    d1p = d1; d2p = d2; d3p = d3;
+                    if (i < nv) {
+                        fa0 += (uint32_t)abs(x);
+                        if (i >= 1 || !first) fa1 += (uint32_t)abs(d1);
+                        if (i >= 2 || !first) fa2 += (uint32_t)abs(d2);
+                        if (i >= 3 || !first) fa3 += (uint32_t)abs(d3);
+                        if (i >= 4 || !first) fa4 += (uint32_t)abs(d4);
                     }
                 }
-                acc0 = warp_sum_u64(acc0); acc1 = warp_sum_u64(acc1); acc2 = warp_sum_u64(acc2);
-                acc3 = warp_sum_u64(acc3); acc4 = warp_sum_u64(acc4);
-                for (int o = 16; o > 0; o >>= 1) fbad |= __shfl_xor_sync(0xFFFFFFFFu, fbad, o);
+            }
+            {
+                uint64_t w0 = warp_sum_u32_wide(fa0), w1 = warp_sum_u32_wide(fa1), w2 = warp_sum_u32_wide(fa2),
+                         w3 = warp_sum_u32_wide(fa3), w4 = warp_sum_u32_wide(fa4);
                 if (lane == 0) {
-                    sh.red64[warp][0] = acc0; sh.red64[warp][1] = acc1; sh.red64[warp][2] = acc2;
-                    sh.red64[warp][3] = acc3; sh.red64[warp][4] = acc4; sh.red32[warp][1] = fbad;
+                    sh.red64[warp][0] = w0; sh.red64[warp][1] = w1; sh.red64[warp][2] = w2; sh.red64[warp][3] = w3; sh.red64[warp][4] = w4;
+                    sh.red32[warp][0] = orv; sh.red32[warp][1] = ora;
                 }
             }
-            // ---- K3: windowed autocorrelation partials ----
-            const int max_lpc = min(a.max_lpc_order, nsamp - 1);
+            __syncthreads();  // S4: every thread holds its samples; pcm may be overwritten by acpart
+            // ---- K3: windowed autocorrelation partials (float within the thread, double across threads) ----
+            const int max_lpc = min(min(a.max_lpc_order, HISTN), nsamp - 1);
             if (max_lpc > 0) {
-                float xw[HIST + FRX_SPT];
-                const bool table = (nsamp == a.blocksize);
+                float xw[HISTN + FRX_SPT];
+                if (full) {
+                    const float4 *w4 = reinterpret_cast<const float4 *>(a.window + g0);
 #pragma unroll
-                for (int i = 0; i < HIST + FRX_SPT; i++) {
-                    int g = g0 - HIST + i;
-                    float wv = 0.f;
-                    if (g >= 0 && g < nsamp) {
-                        if (table) wv = a.window[g];
-                        else {
-                            // tukey(0.5) of length nsamp
-                            int Np = (int)(0.25f * (float)nsamp) - 1;
+                    for (int v = 0; v < FRX_SPT / 4; v++) {
+                        float4 wv = __ldg(w4 + v);
+                        xw[HISTN + 4 * v] = (float)s[HISTN + 4 * v] * wv.x; xw[HISTN + 4 * v + 1] = (float)s[HISTN + 4 * v + 1] * wv.y;
+                        xw[HISTN + 4 * v + 2] = (float)s[HISTN + 4 * v + 2] * wv.z; xw[HISTN + 4 * v + 3] = (float)s[HISTN + 4 * v + 3] * wv.w;
+                    }
+                    if (tid > 0) {
+                        const float4 *h4 = reinterpret_cast<const float4 *>(a.window + g0 - HISTN);
+#pragma unroll
+                        for (int v = 0; v < HISTN / 4; v++) {
+                            float4 wv = __ldg(h4 + v);
+                            xw[4 * v] = (float)s[4 * v] * wv.x; xw[4 * v + 1] = (float)s[4 * v + 1] * wv.y;
+                            xw[4 * v + 2] = (float)s[4 * v + 2] * wv.z; xw[4 * v + 3] = (float)s[4 * v + 3] * wv.w;
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < HISTN; i++) xw[i] = 0.f;
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < HISTN + FRX_SPT; i++) {
+                        int g = g0 - HISTN + i;
+                        float wv = 0.f;
+                        if (g >= 0 && g < nsamp) {
+                            int Np = (int)(0.25f * (float)nsamp) - 1;  // tukey(0.5) of length nsamp
                             wv = 1.0f;
                             if (Np > 0) {
                                 if (g <= Np) wv = 0.5f - 0.5f * cospif((float)g / (float)Np);
                                 else if (g >= nsamp - Np - 1) wv = 0.5f - 0.5f * cospif((float)(g - (nsamp - Np - 1) + Np) / (float)Np);
                             }
                         }
+                        xw[i] = (float)s[i] * wv;
                     }
-                    xw[i] = (float)s[i] * wv;
+                }
+                float ac[HISTN + 1];
+#pragma unroll
+                for (int lag = 0; lag <= HISTN; lag++) ac[lag] = 0.f;
+#pragma unroll
+                for (int i = 0; i < FRX_SPT; i++) {
+#pragma unroll
+                    for (int lag = 0; lag <= HISTN; lag++) ac[lag] = fmaf(xw[HISTN + i], xw[HISTN + i - lag], ac[lag]);
                 }
 #pragma unroll
-                for (int lag = 0; lag <= FRX_MAX_LPC; lag++) {
-                    float acc = 0.f;
-                    if (lag <= max_lpc) {
-#pragma unroll
-                        for (int i = 0; i < FRX_SPT; i++) acc = fmaf(xw[HIST + i], xw[HIST + i - lag], acc);
-                    }
-                    sh.acpart[lag][tid] = acc;
-                }
+                for (int lag = 0; lag <= HISTN; lag++) acpart[lag * FRX_ENC_THREADS + tid] = ac[lag];
             }
-            __syncthreads();
+            __syncthreads();  // S5
             // warp w reduces lags w, w+8 (double accumulation across threads)
             for (int lag = warp; lag <= max_lpc; lag += NWARPS) {
                 double d = 0.0;
 #pragma unroll
-                for (int j = 0; j < FRX_ENC_THREADS / 32; j++) d += (double)sh.acpart[lag][lane + 32 * j];
+                for (int j = 0; j < FRX_ENC_THREADS / 32; j++) d += (double)acpart[lag * FRX_ENC_THREADS + lane + 32 * j];
                 d = warp_sum_f64(d);
                 if (lane == 0) sh.autoc[lag] = d;
             }
-            // fixed totals
-            for (int o5 = 0; o5 < 5; o5++) {
+            // warp 7: block totals of the fixed trial, wasted bits, magnitude, order decision
+            if (warp == NWARPS - 1) {
                 uint64_t tot = 0;
-#pragma unroll
-                for (int w2 = 0; w2 < NWARPS; w2++) tot += sh.red64[w2][o5];
-                fsum[o5] = tot;
-            }
-            {
-                uint32_t fb = 0;
-#pragma unroll
-                for (int w2 = 0; w2 < NWARPS; w2++) fb |= sh.red32[w2][1];
-                fbad = fb;
-            }
-            __syncthreads();
-
-            // ---- constant? (sum |e1| over g>=1 is zero) ----
-            const bool is_const = (nsamp >= 1) && (fsum[1] == 0) && !(fbad & 2u);
-            int fixed_order = -1;
-            if (!is_const && nsamp > 4) {
-                uint64_t bestv = ~0ull;
-                for (int o5 = 0; o5 < 5; o5++) {
-                    // sums for order k skip k samples; compare per-sample averages fairly by adding nothing (negligible)
-                    if (!((fbad >> o5) & 1u) && fsum[o5] < bestv) { bestv = fsum[o5]; fixed_order = o5; }
+                uint32_t o32 = 0;
+                if (lane < 5) { for (int w2 = 0; w2 < NWARPS; w2++) tot += sh.red64[w2][lane]; }
+                else if (lane < 7) { for (int w2 = 0; w2 < NWARPS; w2++) o32 |= sh.red32[w2][lane - 5]; }
+                const uint32_t all_or = __shfl_sync(FULLMASK, o32, 5), all_abs = __shfl_sync(FULLMASK, o32, 6);
+                const int wasted = all_or ? (__ffs((int)all_or) - 1) : 0;
+                const int magbits = 32 - __clz((int)all_abs);  // bits of the largest magnitude (0 for silence)
+                const bool lean = !WIDE || magbits <= 23;
+                const uint64_t f1 = __shfl_sync(FULLMASK, tot, 1);
+                // best fixed order among lanes 0..4 (lowest order wins ties)
+                uint64_t bestv = (lane < 5) ? tot : ~0ull;
+                int besto = lane;
+                for (int o = 1; o < 8; o <<= 1) {
+                    uint64_t ov = __shfl_xor_sync(FULLMASK, bestv, o);
+                    int oo = __shfl_xor_sync(FULLMASK, besto, o);
+                    if (ov < bestv || (ov == bestv && oo < besto)) { bestv = ov; besto = oo; }
+                }
+                if (lane < 5) sh.fsum[lane] = tot;
+                if (lane == 0) {
+                    sh.wasted = wasted; sh.magbits = magbits; sh.lean = lean ? 1 : 0;
+                    sh.is_const = (f1 == 0) ? 1 : 0;   // sum |s[g]-s[g-1]| == 0  <=>  all samples equal
+                    sh.fixed_order = (nsamp > 4) ? besto : -1;
                 }
             }
-
+            __syncthreads();  // S6
+            const int wasted = sh.wasted;
+            const bool lean = sh.lean != 0;
+            const int sbps = a.bps - wasted;
+            if (wasted) {
+#pragma unroll
+                for (int i = 0; i < HISTN + FRX_SPT; i++) s[i] >>= wasted;
+            }
+            // ---- fat data (|s| >= 2^23: lossless int32/float bit patterns): redo the fixed trial in 64-bit ----
+            if (WIDE && !lean) {
+                uint64_t acc[5] = { 0, 0, 0, 0, 0 };
+                uint32_t fbad = 0;
+#pragma unroll
+                for (int i = 0; i < FRX_SPT; i++) {
+                    int g = g0 + i;
+                    if (i < nv) {
+                        const int32_t *p = s + HISTN + i;
+                        long long A = p[0], B = p[-1], C = p[-2], D = p[-3], E = p[-4];
+                        long long e[5] = { A, A - B, A - 2 * B + C, A - 3 * B + 3 * C - D, A - 4 * B + 6 * C - 4 * D + E };
+#pragma unroll
+                        for (int o = 0; o < 5; o++) {
+                            if (g >= o) {
+                                unsigned long long av = (unsigned long long)llabs(e[o]);
+                                acc[o] += av;
+                                if (av > 0x7FFFFFFFull) fbad |= 1u << o;
+                            }
+                        }
+                    }
+                }
+#pragma unroll
+                for (int o = 0; o < 5; o++) acc[o] = warp_sum_u64(acc[o]);
+                fbad = __reduce_or_sync(FULLMASK, fbad);
+                if (lane == 0) {
+#pragma unroll
+                    for (int o = 0; o < 5; o++) sh.red64[warp][o] = acc[o];
+                    sh.red32[warp][2] = fbad;
+                }
+                __syncthreads();
+                if (tid == 0) {
+                    uint64_t bestv = ~0ull;
+                    int besto = -1;
+                    uint32_t fb = 0;
+                    for (int w2 = 0; w2 < NWARPS; w2++) fb |= sh.red32[w2][2];
+                    for (int o = 0; o < 5; o++) {
+                        uint64_t tot = 0;
+                        for (int w2 = 0; w2 < NWARPS; w2++) tot += sh.red64[w2][o];
+                        sh.fsum[o] = tot;
+                        if (!((fb >> o) & 1u) && tot < bestv) { bestv = tot; besto = o; }
+                    }
+                    sh.is_const = (sh.fsum[1] == 0 && !(fb & 2u)) ? 1 : 0;
+                    sh.fixed_order = (nsamp > 4) ? besto : -1;
+                }
+                // (published by the S7 barrier below)
+            }
             // ---- K4: Levinson-Durbin, order pick, coefficient quantisation (thread 0) ----
             if (tid == 0) {
                 sh.lpc_ok = 0;
-                if (!is_const && max_lpc > 0 && nsamp > 4 && sh.autoc[0] != 0.0) {
-                    double lpc[FRX_MAX_LPC], err = sh.autoc[0];
+                const bool is_const0 = sh.is_const != 0;  // lean: warp 7 before S6; fat: this thread, just above
+                const double a0 = sh.autoc[0];
+                if (!is_const0 && max_lpc > 0 && nsamp > 4 && a0 != 0.0) {
+                    double lpc[FRX_MAX_LPC], err = a0;
                     double errs[FRX_MAX_LPC];
                     double coefs[FRX_MAX_LPC][FRX_MAX_LPC];
                     int mo = max_lpc;
@@ -622,10 +728,10 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS) frx_encode_kernel(const EncAr
                         errs[i] = err;
                         if (!(err > 0.0)) { mo = i + 1; break; }
                     }
-                    // expected bits per order
+                    // expected bits per order (the autocorrelation was taken before the wasted-bit shift)
                     double best_bits = 1e300;
                     int best = 1;
-                    const double scale = 0.5 / (double)nsamp;
+                    const double scale = 0.5 / (double)nsamp * (wasted ? ldexp(1.0, -2 * wasted) : 1.0);
                     for (int o = 1; o <= mo; o++) {
                         double e = errs[o - 1];
                         double bpsr = e > 0.0 ? fmax(0.0, 0.5 * log2(scale * e)) : 0.0;
@@ -649,85 +755,111 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS) frx_encode_kernel(const EncAr
                             if (shift >= 0) {
                                 const int qmax = (1 << (precision - 1)) - 1, qmin = -(1 << (precision - 1));
                                 double error = 0.0;
+                                long long sumabs = 0;
                                 for (int j = 0; j < order; j++) {
                                     error += coefs[order - 1][j] * (double)(1 << shift);
                                     long long qq = llrint(error);
                                     if (qq > qmax) qq = qmax; else if (qq < qmin) qq = qmin;
                                     error -= (double)qq;
                                     sh.qlp[j] = (int32_t)qq;
+                                    sumabs += qq < 0 ? -qq : qq;
                                 }
                                 for (int j = order; j < FRX_MAX_LPC; j++) sh.qlp[j] = 0;
-                                sh.lpc_order = order; sh.shift = shift; sh.precision = precision; sh.lpc_ok = 1;
+                                sh.lpc_order = order; sh.shift = shift; sh.precision = precision;
+                                int ok = 1, narrow = 1;
+                                if (WIDE) {
+                                    // |prediction sum| <= sumabs * 2^mag; the residual bound decides which arithmetic is safe
+                                    const int mag = sh.magbits - wasted;
+                                    const long long M = 1ll << (mag < 0 ? 0 : mag);
+                                    narrow = (sumabs * M < (1ll << 31)) ? 1 : 0;
+                                    if (lean) {
+                                        long long Bnd = M + ((sumabs * M) >> shift) + 1;
+                                        if (Bnd >= (1ll << 27)) ok = 0;  // keeps 32-bit residual sums exact; such wild predictors never win anyway
+                                    }
+                                }
+                                sh.lpc_narrow = narrow;
+                                sh.lpc_ok = ok;
                             }
                         }
                     }
                 }
             }
-            __syncthreads();
-
-            // ---- K5: residuals of both candidates, per-thread |r| sums ----
-            int32_t r_lpc[FRX_SPT];
+            __syncthreads();  // S7
+            // ---- K5: per-thread |r| sums of the two candidates (tabs lives where acpart was: S7 passed) ----
+            const int fixed_order = sh.fixed_order;
+            const bool is_const = sh.is_const != 0;
             const bool lpc_try = sh.lpc_ok != 0;
             const int lpc_order = sh.lpc_order;
-            {
-                uint32_t badm = 0;
-                bool bad = false;
-                uint64_t ab = 0;
-                if (lpc_try) {
-                    int32_t q[FRX_MAX_LPC];
+            const int lshift = sh.shift;
+            int32_t q[HISTN];
 #pragma unroll
-                    for (int j = 0; j < FRX_MAX_LPC; j++) q[j] = sh.qlp[j];
-                    lpc_residual_dispatch<WIDE>(lpc_order, s, q, sh.shift, r_lpc, badm);
+            for (int j = 0; j < HISTN; j++) q[j] = sh.qlp[j];
+            const int lmode = !WIDE ? 0 : (lean ? (sh.lpc_narrow ? 0 : 1) : 2);
+            {
+                uint64_t ab = 0;
+                bool bad = false;
+                if (lpc_try) {
+                    int32_t r[FRX_SPT];
+                    uint32_t badm = 0;
+                    if (lmode == 0) badm = lpc_residuals_dispatch<0, HISTN>(lpc_order, s, q, lshift, r);
+                    else if (WIDE && lmode == 1) badm = lpc_residuals_dispatch<1, HISTN>(lpc_order, s, q, lshift, r);
+                    else if (WIDE) badm = lpc_residuals_dispatch<2, HISTN>(lpc_order, s, q, lshift, r);
+                    uint32_t ab32 = 0;
 #pragma unroll
                     for (int i = 0; i < FRX_SPT; i++) {
-                        int g = g0 + i;
-                        if (g < lpc_order || g >= nsamp) r_lpc[i] = 0;
-                        else if ((badm >> i) & 1u) bad = true;
-                        ab += (uint32_t)abs(r_lpc[i]);
+                        const bool valid = (i < nv) && (g0 + i >= lpc_order);
+                        if (valid) {
+                            if ((badm >> i) & 1u) bad = true;
+                            if (WIDE && !lean) ab += (uint32_t)abs(r[i]); else ab32 += (uint32_t)abs(r[i]);
+                        }
                     }
+                    if (!(WIDE && !lean)) ab = ab32;
                 }
-                sh.tabs[1][tid] = ab;
-                unsigned anybad = __ballot_sync(0xFFFFFFFFu, bad);
-                if (lane == 0) sh.red32[warp][2] = anybad ? 1u : 0u;
-                // fixed candidate sums
+                tabs[FRX_ENC_THREADS + tid] = ab;
+                if (WIDE && !lean) {
+                    unsigned anybad = __ballot_sync(FULLMASK, bad);
+                    if (lane == 0) sh.red32[warp][3] = anybad ? 1u : 0u;
+                }
                 uint64_t fb = 0;
                 if (fixed_order >= 0) {
-                    int32_t rf[FRX_SPT];
-                    uint32_t badf = 0;
-                    fixed_residual_thread<WIDE>(fixed_order, s, rf, badf);
+                    if (WIDE && !lean) {
+                        int32_t rf[FRX_SPT];
+                        (void)fixed_residuals<true, HISTN>(fixed_order, s, rf);
 #pragma unroll
-                    for (int i = 0; i < FRX_SPT; i++) {
-                        int g = g0 + i;
-                        if (g >= fixed_order && g < nsamp) fb += (uint32_t)abs(rf[i]);
+                        for (int i = 0; i < FRX_SPT; i++)
+                            if (i < nv && g0 + i >= fixed_order) fb += (uint32_t)abs(rf[i]);
+                    } else {
+                        uint32_t sel = fixed_order == 0 ? fa0 : fixed_order == 1 ? fa1 : fixed_order == 2 ? fa2 : fixed_order == 3 ? fa3 : fa4;
+                        fb = sel >> wasted;  // all samples are multiples of 2^wasted, so the sums scale exactly
                     }
                 }
-                sh.tabs[0][tid] = fb;
+                tabs[tid] = fb;
             }
-            __syncthreads();
+            __syncthreads();  // S8
             // ---- K6: Rice partition analysis, warp 0 = fixed, warp 1 = lpc ----
             int po_max = 0;
             {
-                int tz = __ffs(nsamp) - 1;          // trailing zeros of the block size
+                int tz = __ffs(nsamp) - 1;               // trailing zeros of the block size
                 po_max = min(a.max_po, max(0, tz - 4));  // partitions stay multiples of 16 samples
                 while (po_max > 0 && (nsamp >> po_max) <= FRX_MAX_LPC) po_max--;
             }
             bool lpc_valid = lpc_try;
-            {
+            if (WIDE && !lean && lpc_try) {
                 uint32_t b = 0;
 #pragma unroll
-                for (int w2 = 0; w2 < NWARPS; w2++) b |= sh.red32[w2][2];
+                for (int w2 = 0; w2 < NWARPS; w2++) b |= sh.red32[w2][3];
                 if (b) lpc_valid = false;
             }
-            if (warp == 0 && fixed_order >= 0) analyse_partitions(sh, 0, nsamp, fixed_order, po_max, k_limit);
-            if (warp == 1 && lpc_valid) analyse_partitions(sh, 1, nsamp, lpc_order, po_max, k_limit);
-            __syncthreads();
+            if (warp == 0 && fixed_order >= 0) analyse_partitions(sh, tabs, 0, nsamp, fixed_order, po_max, kmax);
+            if (warp == 1 && lpc_valid) analyse_partitions(sh, tabs + FRX_ENC_THREADS, 1, nsamp, lpc_order, po_max, kmax);
+            __syncthreads();  // S9
 
             // ---- choose ----
             const uint64_t verb_bits = 8ull + (uint64_t)wasted + (uint64_t)nsamp * (uint64_t)sbps;
             int type = 1, order = 0, cand = 0;
             uint64_t best_bits = verb_bits;
             if (is_const) { type = 0; best_bits = 8ull + wasted + sbps; }
-            else {
+            else if (!force_verbatim) {
                 if (fixed_order >= 0) {
                     uint64_t b = 8ull + wasted + (uint64_t)fixed_order * sbps + sh.cand_bits[0];
                     if (b < best_bits) { best_bits = b; type = 2; order = fixed_order; cand = 0; }
@@ -738,57 +870,57 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS) frx_encode_kernel(const EncAr
                 }
             }
 
-            // ---- K7: exact bit count per thread, block scan, pack ----
+            // ---- K7a: winner's residuals (zig-zag folded), exact bit count per thread, block scan ----
             const uint32_t sub_start = sh.bitpos;
-            int32_t r[FRX_SPT];
+            uint32_t u[FRX_SPT];
             int po = 0;
             uint32_t kk = 0;
             int psize = nsamp;
             bool rice2 = false;
+            uint32_t mybits = 0;
             if (type >= 2) {
                 po = sh.cand_po[cand];
                 psize = nsamp >> po;
                 kk = sh.kparam[cand][min(g0 / psize, (1 << po) - 1)];
-                // RICE2 iff any parameter needs 5 bits
-                bool big = false;
-                for (int p = 0; p < (1 << po); p++) big |= (sh.kparam[cand][p] >= 15u);
-                rice2 = big;
+                rice2 = sh.cand_rice2[cand] != 0;
+                int32_t r[FRX_SPT];
                 if (type == 3) {
-#pragma unroll
-                    for (int i = 0; i < FRX_SPT; i++) r[i] = r_lpc[i];
+                    if (lmode == 0) (void)lpc_residuals_dispatch<0, HISTN>(order, s, q, lshift, r);
+                    else if (WIDE) (void)lpc_residuals_dispatch<1, HISTN>(order, s, q, lshift, r);
                 } else {
-                    uint32_t badf = 0;
-                    fixed_residual_thread<WIDE>(order, s, r, badf);
+                    if (WIDE && !lean) (void)fixed_residuals<true, HISTN>(order, s, r);
+                    else (void)fixed_residuals<false, HISTN>(order, s, r);
                 }
-            }
-            uint32_t mybits = 0;
-            if (type >= 2) {
-                if (tid < nthr) {
 #pragma unroll
-                    for (int i = 0; i < FRX_SPT; i++) {
-                        int g = g0 + i;
-                        if (g >= order && g < nsamp) mybits += (zigzag(r[i]) >> kk) + 1u + kk;
-                    }
-                    if (g0 % psize == 0) mybits += rice2 ? 5u : 4u;
-                    if (tid == 0) {
-                        mybits += 8u + (wasted ? (uint32_t)wasted : 0u) + (uint32_t)order * (uint32_t)sbps + 6u;
-                        if (type == 3) mybits += 9u + (uint32_t)order * (uint32_t)sh.precision;
-                    }
+                for (int i = 0; i < FRX_SPT; i++) {
+                    u[i] = zigzag(r[i]);
+                    if (i < nv && g0 + i >= order) mybits += (u[i] >> kk) + 1u + kk;
+                }
+                if (tid < nthr && g0 % psize == 0) mybits += rice2 ? 5u : 4u;
+                if (tid == 0) {
+                    mybits += 8u + (uint32_t)wasted + (uint32_t)order * (uint32_t)sbps + 6u;
+                    if (type == 3) mybits += 9u + (uint32_t)order * (uint32_t)sh.precision;
+#pragma unroll
+                    for (int i = 0; i < HISTN; i++) sh.warm[i] = s[HISTN + i];
                 }
             } else if (type == 1) {
-                if (tid < nthr) mybits = (uint32_t)min(FRX_SPT, nsamp - g0) * (uint32_t)sbps;
+                const uint32_t smask = sbps >= 32 ? 0xFFFFFFFFu : ((1u << sbps) - 1u);
+#pragma unroll
+                for (int i = 0; i < FRX_SPT; i++) u[i] = (uint32_t)s[HISTN + i] & smask;
+                mybits = (uint32_t)nv * (uint32_t)sbps;
                 if (tid == 0) mybits += 8u + (uint32_t)wasted;
             } else {
+                u[0] = (uint32_t)s[HISTN] & (sbps >= 32 ? 0xFFFFFFFFu : ((1u << sbps) - 1u));
                 if (tid == 0) mybits = 8u + (uint32_t)wasted + (uint32_t)sbps;
             }
-            // block exclusive scan of mybits
             uint32_t incl = mybits;
+#pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
-                uint32_t n = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+                uint32_t n = __shfl_up_sync(FULLMASK, incl, o);
                 if (lane >= o) incl += n;
             }
             if (lane == 31) sh.scan[warp] = incl;
-            __syncthreads();
+            __syncthreads();  // S10
             uint32_t wbase = 0, total = 0;
 #pragma unroll
             for (int w2 = 0; w2 < NWARPS; w2++) {
@@ -797,17 +929,11 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS) frx_encode_kernel(const EncAr
                 total += v;
             }
             uint32_t start = sub_start + wbase + incl - mybits;
-            // Rice-coded size must beat verbatim, else fall back (keeps the frame inside its buffer)
-            if (type >= 2 && (uint64_t)total >= verb_bits) {
-                type = 1;
-                mybits = (tid < nthr) ? (uint32_t)min(FRX_SPT, nsamp - g0) * (uint32_t)sbps : 0u;
-                start = sub_start + 8u + (uint32_t)wasted + (uint32_t)min(g0, nsamp) * (uint32_t)sbps;
-                if (tid == 0) { mybits += 8u + (uint32_t)wasted; start = sub_start; }
-                total = (uint32_t)verb_bits;
-            }
-            __syncthreads();  // all reads of sh.scan / sh.bitpos done
-            if (tid == 0) sh.bitpos = sub_start + total;
+            // Rice-coded size must beat verbatim, else redo the subframe as VERBATIM (keeps the frame inside its buffer)
+            if (type >= 2 && (uint64_t)total >= verb_bits) { force_verbatim = true; continue; }
+            if (tid == 0) sh.bitpos = sub_start + total;  // next read of bitpos is behind the next S2
 
+            // ---- K7b: pack ----
             if (mybits) {
                 BitW bw;
                 bw.init(bits, start);
@@ -819,14 +945,14 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS) frx_encode_kernel(const EncAr
                 }
                 const uint32_t smask = sbps >= 32 ? 0xFFFFFFFFu : ((1u << sbps) - 1u);
                 if (type == 0) {
-                    if (tid == 0) bw.put((uint32_t)s[HIST] & smask, sbps);
+                    if (tid == 0) bw.put(u[0], sbps);
                 } else if (type == 1) {
 #pragma unroll
                     for (int i = 0; i < FRX_SPT; i++)
-                        if (g0 + i < nsamp) bw.put((uint32_t)s[HIST + i] & smask, sbps);
+                        if (i < nv) bw.put(u[i], sbps);
                 } else {
                     if (tid == 0) {
-                        for (int i = 0; i < order; i++) bw.put((uint32_t)s[HIST + i] & smask, sbps);
+                        for (int i = 0; i < order; i++) bw.put((uint32_t)sh.warm[i] & smask, sbps);
                         if (type == 3) {
                             bw.put((uint32_t)(sh.precision - 1), 4);
                             bw.put((uint32_t)sh.shift & 31u, 5);
@@ -839,53 +965,42 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS) frx_encode_kernel(const EncAr
                     const uint32_t kmask = kk ? ((1u << kk) - 1u) : 0u;
 #pragma unroll
                     for (int i = 0; i < FRX_SPT; i++) {
-                        int g = g0 + i;
-                        if (g >= order && g < nsamp) {
-                            uint32_t u = zigzag(r[i]);
-                            uint32_t q = u >> kk;
-                            uint32_t code = (1u << kk) | (u & kmask);
-                            if (q + 1u + kk <= 32u) bw.put(code, (int)(q + 1u + kk));
-                            else { bw.skip(q); bw.put(code, (int)(kk + 1u)); }
+                        if (i < nv && g0 + i >= order) {
+                            uint32_t uq = u[i] >> kk;
+                            uint32_t code = (1u << kk) | (u[i] & kmask);
+                            if (uq + 1u + kk <= 32u) bw.put(code, (int)(uq + 1u + kk));
+                            else { bw.skip(uq); bw.put(code, (int)(kk + 1u)); }
                         }
                     }
                 }
                 bw.finish();
             }
+            break;
+          }
         }  // channels
-        __syncthreads();
+        __syncthreads();  // Sa: every subframe is packed
 
-        // ---- frame footer: pad to byte, CRC-16 ----
-        const uint32_t body_bits = (sh.bitpos + 7u) & ~7u;
-        const uint32_t body_bytes = body_bits >> 3;
-        {
-            // left-padded chunking: virtual length 256*L, thread t owns virtual bytes [tL, tL+L)
-            const int L = a.crc_chunk;
-            const int padv = FRX_ENC_THREADS * L - (int)body_bytes;
-            uint32_t c = 0;
-            int v0 = tid * L, v1 = v0 + L;
-            int b0 = max(0, v0 - padv), b1 = v1 - padv;
-            for (int b = b0; b < b1; b++) {
-                uint32_t byte = (bits[b >> 2] >> (24 - 8 * (b & 3))) & 0xFFu;
-                c ^= byte << 8;
-#pragma unroll
-                for (int i = 0; i < 8; i++) c = (c & 0x8000u) ? ((c << 1) ^ 0x8005u) & 0xFFFFu : (c << 1) & 0xFFFFu;
-            }
-            // shift by (255 - t) chunks
-            if (c) c = frx_gf16_mulmod(c, (uint32_t)a.crc_xpow[FRX_ENC_THREADS - 1 - tid]);
-            for (int o = 16; o > 0; o >>= 1) c ^= __shfl_xor_sync(0xFFFFFFFFu, c, o);
-            if (lane == 0) sh.crc_part[warp] = c;
-        }
-        __syncthreads();
+        // ---- frame footer: pad to byte, CRC-16 over the body (warps 6,7), byte offset by look-back (warp 0) ----
+        const uint32_t body_bytes = (sh.bitpos + 7u) >> 3;
         const uint32_t nbytes = body_bytes + 2u;
-        if (tid == 0) {
+        if (warp >= NWARPS - 2) {
+            const int ct = tid - (FRX_ENC_THREADS - CRC_THREADS);   // 0..63
+            const uint32_t nw = body_bytes >> 2;                   // whole words
+            uint32_t per = (nw + CRC_THREADS - 1) / CRC_THREADS;
+            int lg = per <= 1 ? 0 : 32 - __clz((int)per - 1);      // Lw = 2^lg words per CRC thread
+            const uint32_t Lw = 1u << lg;
+            const int padw = (int)(CRC_THREADS * Lw) - (int)nw;    // virtual leading zero words
+            int w0 = ct * (int)Lw - padw, w1 = w0 + (int)Lw;
+            if (w0 < 0) w0 = 0;
             uint32_t c = 0;
-            for (int w2 = 0; w2 < NWARPS; w2++) c ^= sh.crc_part[w2];
-            // append big-endian CRC-16 at byte body_bytes
-            for (int k2 = 0; k2 < 2; k2++) {
-                uint32_t byte = k2 == 0 ? (c >> 8) : (c & 0xFFu);
-                uint32_t b = body_bytes + (uint32_t)k2;
-                bits[b >> 2] |= byte << (24 - 8 * (b & 3));
+            for (int wi = w0; wi < w1; wi++) {
+                uint32_t x = bits[wi] ^ (c << 16);
+                c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
             }
+            if (c) c = frx_gf16_mulmod(c, (uint32_t)a.crc_xpow[lg * CRC_THREADS + (CRC_THREADS - 1 - ct)]);
+            c = __reduce_xor_sync(FULLMASK, c);
+            if (lane == 0) sh.crc_part[warp - (NWARPS - 2)] = c;
+            if (ct == 0) sh.tailw = bits[nw];
         }
         // ---- K8: decoupled look-back for the byte offset (warp 0) ----
         if (warp == 0) {
@@ -900,8 +1015,8 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS) frx_encode_kernel(const EncAr
                     long long idx = pos - lane;
                     uint64_t v = idx >= 0 ? frx_ld_acquire_u64(&a.desc[idx]) : FLAG_P;
                     uint32_t flag = (uint32_t)(v >> 62);
-                    uint32_t notready = __ballot_sync(0xFFFFFFFFu, flag == 0u);
-                    uint32_t isp = __ballot_sync(0xFFFFFFFFu, flag == 2u);
+                    uint32_t notready = __ballot_sync(FULLMASK, flag == 0u);
+                    uint32_t isp = __ballot_sync(FULLMASK, flag == 2u);
                     int firstp = isp ? (__ffs((int)isp) - 1) : 32;
                     uint32_t need = firstp < 32 ? (firstp == 31 ? 0xFFFFFFFFu : ((2u << firstp) - 1u)) : 0xFFFFFFFFu;
                     if (notready & need) { __nanosleep(40); continue; }
@@ -919,7 +1034,7 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS) frx_encode_kernel(const EncAr
                 if (f == a.total_frames - 1 && a.total_bytes) *a.total_bytes = exclusive + nbytes;
             }
         }
-        __syncthreads();
+        __syncthreads();  // Sb
         // ---- copy the frame to its final place ----
         {
             const uint64_t off = sh.out_offset;
@@ -927,10 +1042,20 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS) frx_encode_kernel(const EncAr
                 if (tid == 0) atomicExch(a.status, FRX_E_OVERFLOW);
             } else {
                 uint8_t *dst = a.bytes + off;
-                const uint32_t head = min(nbytes, (uint32_t)((4u - (uint32_t)((uintptr_t)dst & 3u)) & 3u));
-                // head bytes
+                if (tid == FRX_ENC_THREADS - 1) {
+                    // finish the CRC over the <= 3 tail bytes and store it big-endian behind the body
+                    uint32_t c = sh.crc_part[0] ^ sh.crc_part[1];
+                    const uint32_t tw = sh.tailw;
+                    for (uint32_t b = 0; b < (body_bytes & 3u); b++) {
+                        uint32_t byte = (tw >> (24 - 8 * b)) & 0xFFu;
+                        c = ((c << 8) ^ sh.crc_tab[0][((c >> 8) ^ byte) & 0xFFu]) & 0xFFFFu;
+                    }
+                    dst[body_bytes] = (uint8_t)(c >> 8);
+                    dst[body_bytes + 1] = (uint8_t)c;
+                }
+                const uint32_t head = min(body_bytes, (uint32_t)((4u - (uint32_t)((uintptr_t)dst & 3u)) & 3u));
                 if (tid < (int)head) dst[tid] = (uint8_t)((bits[tid >> 2] >> (24 - 8 * (tid & 3))) & 0xFFu);
-                const uint32_t nwords = (nbytes - head) >> 2;
+                const uint32_t nwords = (body_bytes - head) >> 2;
                 uint32_t *dw = reinterpret_cast<uint32_t *>(dst + head);
                 const uint32_t sh8 = head * 8u;
                 for (uint32_t j = tid; j < nwords; j += FRX_ENC_THREADS) {
@@ -940,12 +1065,14 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS) frx_encode_kernel(const EncAr
                     dw[j] = frx_bswap32(v);
                 }
                 const uint32_t tail0 = head + (nwords << 2);
-                if (tid < (int)(nbytes - tail0)) {
+                if (tid < (int)(body_bytes - tail0)) {
                     uint32_t b = tail0 + (uint32_t)tid;
                     dst[b] = (uint8_t)((bits[b >> 2] >> (24 - 8 * (b & 3))) & 0xFFu);
                 }
             }
         }
+        __syncthreads();  // Sz: all reads of the frame buffer done
+        for (uint32_t j = tid; j <= (body_bytes >> 2); j += FRX_ENC_THREADS) bits[j] = 0u;
     }
 }
 
@@ -979,8 +1106,7 @@ __global__ void frx_minmax_out_kernel(const FrxQuant *q, int dtype, double *mm) 
 // host launchers (called from frx_api.cu)
 // ------------------------------------------------------------------------------------------
 size_t frx_enc_smem_bytes(int frame_words) {
-    return ((sizeof(EncShared) + 15) & ~(size_t)15) + sizeof(int32_t) * (FRX_MAX_BLOCK + (FRX_MAX_BLOCK >> 4) + 32) +
-           sizeof(uint32_t) * (size_t)frame_words;
+    return ENC_SMALL_BYTES + ENC_UNION_BYTES + sizeof(uint32_t) * (size_t)frame_words;
 }
 
 size_t frx_minmax_raw_size() { return sizeof(MinMaxRaw); }
@@ -1009,33 +1135,36 @@ cudaError_t frx_launch_minmax(const frx_raster &r, const frx_tile *tiles_dev, co
     return cudaErrorInvalidValue;
 }
 
-template <int DT, bool WIDE>
+template <bool WIDE, int HISTN>
 static cudaError_t launch_encode_t(const EncArgs &a, int sm_count, cudaStream_t st) {
     size_t smem = frx_enc_smem_bytes(a.frame_words);
-    cudaError_t e = cudaFuncSetAttribute(frx_encode_kernel<DT, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(frx_encode_kernel<WIDE, HISTN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(frx_encode_kernel<WIDE, HISTN>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e != cudaSuccess) return e;
     int occ = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, frx_encode_kernel<DT, WIDE>, FRX_ENC_THREADS, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, frx_encode_kernel<WIDE, HISTN>, FRX_ENC_THREADS, smem);
     if (e != cudaSuccess) return e;
     if (occ < 1) return cudaErrorLaunchOutOfResources;
-    long long grid = (long long)sm_count * occ;
+    long long grid = (long long)sm_count * occ;   // persistent: every CTA resident, tickets hand out the frames in order
     if (grid > (long long)a.total_frames) grid = a.total_frames;
     if (grid < 1) grid = 1;
-    frx_encode_kernel<DT, WIDE><<<(unsigned)grid, FRX_ENC_THREADS, smem, st>>>(a);
+    frx_encode_kernel<WIDE, HISTN><<<(unsigned)grid, FRX_ENC_THREADS, smem, st>>>(a);
     return cudaGetLastError();
 }
 
 cudaError_t frx_launch_encode(const EncArgs &a, int dtype, int sm_count, cudaStream_t st) {
+    (void)dtype;
     const bool wide = a.bps > 16;
-    switch (dtype) {
-        case FRX_U8: return wide ? launch_encode_t<FRX_U8, true>(a, sm_count, st) : launch_encode_t<FRX_U8, false>(a, sm_count, st);
-        case FRX_I16: return wide ? launch_encode_t<FRX_I16, true>(a, sm_count, st) : launch_encode_t<FRX_I16, false>(a, sm_count, st);
-        case FRX_U16: return wide ? launch_encode_t<FRX_U16, true>(a, sm_count, st) : launch_encode_t<FRX_U16, false>(a, sm_count, st);
-        case FRX_I32: return launch_encode_t<FRX_I32, true>(a, sm_count, st);
-        case FRX_U32: return launch_encode_t<FRX_U32, true>(a, sm_count, st);
-        case FRX_F32: return launch_encode_t<FRX_F32, true>(a, sm_count, st);
+    const int hist = a.max_lpc_order <= 4 ? 4 : (a.max_lpc_order <= 8 ? 8 : 12);
+    if (wide) {
+        if (hist == 4) return launch_encode_t<true, 4>(a, sm_count, st);
+        if (hist == 8) return launch_encode_t<true, 8>(a, sm_count, st);
+        return launch_encode_t<true, 12>(a, sm_count, st);
     }
-    return cudaErrorInvalidValue;
+    if (hist == 4) return launch_encode_t<false, 4>(a, sm_count, st);
+    if (hist == 8) return launch_encode_t<false, 8>(a, sm_count, st);
+    return launch_encode_t<false, 12>(a, sm_count, st);
 }
 
 cudaError_t frx_launch_tile_index(const uint32_t *frame_prefix, const uint32_t *frame_size, const uint64_t *frame_offset,

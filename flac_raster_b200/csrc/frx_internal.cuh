@@ -9,7 +9,8 @@ struct EncArgs {
     const uint32_t *frame_prefix;
     const FrxQuant *quant;
     const float *window;
-    const uint16_t *crc_xpow;
+    const uint16_t *crc_xpow;   // [11][64]: x^(32 * 2^lg * j) mod P, j = chunks that follow a CRC thread's chunk
+    const uint16_t *crc_tab;    // [4][256] slicing-by-4 CRC-16 tables
     uint8_t *bytes;
     uint64_t capacity;
     uint32_t *frame_size;
@@ -29,7 +30,7 @@ struct EncArgs {
     int max_po;
     int qlp_precision;
     int frame_words;
-    int crc_chunk;
+    int dtype;
 };
 struct DecArgs {
     const uint8_t *bytes;
