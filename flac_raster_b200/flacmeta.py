@@ -47,6 +47,7 @@ class FlacHeader:
     comments: list = field(default_factory=list)  # [(KEY, value)] in file order
     first_frame_offset: int = 0
     blocks: list = field(default_factory=list)    # [(type, offset, length)]
+    applications: dict = field(default_factory=dict)  # {4-byte id: payload}
 
     def get(self, key: str, default=None):
         key = key.upper()
@@ -75,12 +76,32 @@ def pack_vorbis_comment(comments, vendor: str = VENDOR) -> bytes:
     return b"".join(out)
 
 
-def build_header(si: StreamInfo, comments=None, padding: int = 0, vendor: str = VENDOR) -> bytes:
-    """fLaC + STREAMINFO [+ VORBIS_COMMENT] [+ PADDING]."""
+FRAME_TABLE_APP_ID = b"frxT"
+
+
+def pack_frame_table(blocksize: int, frame_sizes) -> bytes:
+    """APPLICATION 'frxT' payload: u8 version, u32 blocksize, u32 n, u32 sizes[n] (big-endian).
+    Lets the batched decoder skip frame discovery; other readers skip the block."""
+    sizes = [int(x) for x in frame_sizes]
+    return struct.pack(">BII", 1, int(blocksize), len(sizes)) + struct.pack(f">{len(sizes)}I", *sizes)
+
+
+def unpack_frame_table(payload: bytes):
+    ver, blocksize, n = struct.unpack(">BII", payload[:9])
+    if ver != 1 or len(payload) < 9 + 4 * n:
+        raise ValueError("bad frxT frame table")
+    return blocksize, list(struct.unpack(f">{n}I", payload[9:9 + 4 * n]))
+
+
+def build_header(si: StreamInfo, comments=None, padding=None, vendor: str = VENDOR, applications=None) -> bytes:
+    """fLaC + STREAMINFO [+ APPLICATION...] [+ VORBIS_COMMENT] [+ PADDING]."""
     blocks = [(BLOCK_STREAMINFO, si.pack())]
+    for app_id, payload in (applications or {}).items():
+        assert len(app_id) == 4
+        blocks.append((BLOCK_APPLICATION, bytes(app_id) + payload))
     if comments is not None:
         blocks.append((BLOCK_VORBIS_COMMENT, pack_vorbis_comment(comments, vendor)))
-    if padding > 0:
+    if padding is not None:  # a zero-length PADDING block is legal
         blocks.append((BLOCK_PADDING, b"\0" * padding))
     out = [b"fLaC"]
     for i, (t, p) in enumerate(blocks):
@@ -96,6 +117,7 @@ def parse_header(data: bytes, offset: int = 0) -> FlacHeader:
     hdr = None
     last = False
     blocks = []
+    apps = {}
     vendor, comments = "", []
     while not last:
         if pos + 4 > len(data):
@@ -111,6 +133,8 @@ def parse_header(data: bytes, offset: int = 0) -> FlacHeader:
             if btype != BLOCK_STREAMINFO or blen != 34:
                 raise ValueError("first metadata block is not STREAMINFO")
             hdr = StreamInfo.unpack(data[pos:pos + 34])
+        elif btype == BLOCK_APPLICATION and blen >= 4:
+            apps[bytes(data[pos:pos + 4])] = bytes(data[pos + 4:pos + blen])
         elif btype == BLOCK_VORBIS_COMMENT:
             q = pos
             vl = struct.unpack("<I", data[q:q + 4])[0]; q += 4
@@ -122,4 +146,4 @@ def parse_header(data: bytes, offset: int = 0) -> FlacHeader:
                 k, _, v = e.partition("=")
                 comments.append((k, v))
         pos += blen
-    return FlacHeader(hdr, vendor, comments, pos, blocks)
+    return FlacHeader(hdr, vendor, comments, pos, blocks, apps)

@@ -14,6 +14,7 @@ GDAL_NODATA 42113.  That covers every fixture the reference ships (test_data/*.t
 """
 from __future__ import annotations
 
+import io
 import struct
 from collections import namedtuple
 from pathlib import Path
@@ -125,7 +126,7 @@ def _np_dtype(sample_format, bits, bo):
 class DatasetReader:
     def __init__(self, path):
         self.name = str(path)
-        self._f = open(path, "rb")
+        self._f = io.open(path, "rb")
         self._parse()
 
     # ---- parsing -----------------------------------------------------------------
@@ -402,7 +403,7 @@ class DatasetWriter:
                 if len(ool) & 1:
                     ool += b"\0"
             ifd += struct.pack("<HHQ" if big else "<HHI", tag, typ, cnt) + field
-        with open(self.name, "wb") as f:
+        with io.open(self.name, "wb") as f:
             if big:
                 f.write(b"II" + struct.pack("<HHHQ", 43, 8, 0, 16))
                 f.write(struct.pack("<Q", len(entries)) + ifd + struct.pack("<Q", 0))
