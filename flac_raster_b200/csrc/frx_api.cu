@@ -275,21 +275,25 @@ int frx_encode_tiles(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *t
         c->window_len = L;
     }
     const uint64_t fb = frame_bytes_bound(prep.max_channels, prep.bps, p->blocksize);
-    const int frame_words = (int)((fb + 3) / 4) + 4;
-    if (c->xpow_L != 1) {
-        // x^(32 * 2^lg * j) mod P for lg = 0..10, j = 0..63 (CRC chunk combine, frx_encode.cu)
-        std::vector<uint16_t> xp(11 * 64);
-        for (int lg = 0; lg <= 10; lg++) {
-            uint32_t base = 2, e = 32u << lg, acc = 1;   // x^(32 * 2^lg)
+    const int frame_words = (int)((fb + 3) / 4) + 8;
+    if (c->xpow_L != 2) {
+        // CRC chunk combine tables (frx_encode.cu): x^(128 * Lq * j) mod P for Lq = 1..FRX_CRC_MAXLQ, j = 0..255; x^(-32 z), z = 0..3
+        std::vector<uint16_t> xp(FRX_CRC_MAXLQ * 256 + 4);
+        for (int lq = 1; lq <= FRX_CRC_MAXLQ; lq++) {
+            uint32_t base = 2, e = 128u * lq, acc = 1;
             while (e) { if (e & 1u) acc = frx_gf16_mulmod(acc, base); base = frx_gf16_mulmod(base, base); e >>= 1; }
             uint32_t cur = 1;
-            for (int j = 0; j < 64; j++) { xp[lg * 64 + j] = (uint16_t)cur; cur = frx_gf16_mulmod(cur, acc); }
+            for (int j = 0; j < 256; j++) { xp[(lq - 1) * 256 + j] = (uint16_t)cur; cur = frx_gf16_mulmod(cur, acc); }
         }
+        uint32_t inv32 = 0xC002u;                       // x^-1: x * (x^15 + x^14 + x) = P + 1
+        for (int i = 0; i < 5; i++) inv32 = frx_gf16_mulmod(inv32, inv32);   // x^-32
+        uint32_t cur = 1;
+        for (int z = 0; z < 4; z++) { xp[FRX_CRC_MAXLQ * 256 + z] = (uint16_t)cur; cur = frx_gf16_mulmod(cur, inv32); }
         ENSURE(c->xpow, sizeof(uint16_t) * xp.size());
         CK(cudaMemcpy(c->xpow.p, xp.data(), sizeof(uint16_t) * xp.size(), cudaMemcpyHostToDevice));
-        c->xpow_L = 1;
+        c->xpow_L = 2;
     }
-    if (frame_words > 64 * 1024 * 4) return set_err(FRX_E_UNSUPPORTED, "frame too large for the CRC chunk tables");
+    if (frame_words > FRX_CRC_MAXLQ * 256 * 4) return set_err(FRX_E_UNSUPPORTED, "frame too large for the CRC chunk tables");
     {
         int rc2 = ensure_crctab(c);
         if (rc2) return rc2;
@@ -310,7 +314,7 @@ int frx_encode_tiles(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *t
     memset(&a, 0, sizeof(a));
     a.raster = r.data; a.H = r.height; a.W = r.width; a.band_stride = r.band_stride; a.row_stride = r.row_stride;
     a.tiles = (const frx_tile *)c->tiles.p; a.frame_prefix = (const uint32_t *)c->prefix.p; a.quant = (const FrxQuant *)c->quant.p;
-    a.window = (const float *)c->window.p; a.crc_xpow = (const uint16_t *)c->xpow.p;
+    a.window = (const float *)c->window.p; a.crc_xpow = (const uint16_t *)c->xpow.p; a.crc_xinv = a.crc_xpow + FRX_CRC_MAXLQ * 256;
     a.bytes = out->bytes; a.capacity = out->capacity; a.frame_size = frame_size; a.frame_offset = frame_offset;
     a.desc = (uint64_t *)c->desc.p; a.ticket = (uint32_t *)c->misc.p;
     a.status = out->status ? out->status : (int32_t *)((char *)c->misc.p + 16);
@@ -320,6 +324,10 @@ int frx_encode_tiles(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *t
     a.max_lpc_order = lvl_lpc[p->compression_level]; a.max_po = lvl_po[p->compression_level];
     a.qlp_precision = qlp_precision_for(prep.bps, p->blocksize);
     a.frame_words = frame_words; a.dtype = r.dtype; a.crc_tab = (const uint16_t *)c->crctab.p;
+    {
+        const long long esz = frx_dtype_size(r.dtype);
+        a.tma_ok = (((uintptr_t)r.data & 15u) == 0 && (r.band_stride * esz) % 16 == 0 && (r.row_stride * esz) % 16 == 0) ? 1 : 0;
+    }
     if (frx_enc_smem_bytes(frame_words) > 227 * 1024) return set_err(FRX_E_UNSUPPORTED, "frame buffer does not fit shared memory");
     CK(cudaEventRecord(c->ev[0], st));
     CK(frx_launch_encode(a, r.dtype, c->sm_count, st));

@@ -7,7 +7,8 @@
 
 #define FRX_MAX_CH 8
 #define FRX_MAX_LPC 12          // libFLAC levels 0..8 never exceed order 12 (dump:6926-6934)
-#define FRX_ENC_THREADS 256     // one CTA per frame; 16 samples per thread at blocksize 4096
+#define FRX_ENC_THREADS 256     // compute threads of an encoder CTA: one CTA per frame, 16 samples per thread at blocksize 4096
+#define FRX_ENC_CTA 288         // + one control warp (tickets, TMA prefetch, frame header, look-back)
 #define FRX_SPT 16              // samples per thread
 #define FRX_MAX_BLOCK 4096      // FRX_ENC_THREADS * FRX_SPT
 
@@ -48,8 +49,10 @@ struct FrxQuant {
     float fmin, fmax;       // float32: min/max (NaN propagates like np.min)
     double range;           // (double)(T)(dmax - dmin), wrapped in the raster dtype (converter.py:72)
     int degenerate;         // dmax == dmin  -> zeros (converter.py:73-75)
-    int pad;
+    int flags;              // FRX_QF_*
 };
+#define FRX_QF_F32_SAFE 1   // float32 reference mode: no NaN and |x| * 8388607 < 2^31 for the whole stream, so the
+                            // x86 "integer indefinite" check of frx_trunc_i32f can never fire
 
 // raw element -> int64 (integers) ; floats handled separately
 template <int DT> struct FrxElem;
@@ -76,6 +79,7 @@ __device__ __forceinline__ int32_t frx_quant_ref(typename FrxElem<DT>::T d, cons
     if (DT == FRX_F32) {
         // float data "as-is"; float32 array * python int 8388607 stays float32 (NEP 50)
         float y = __fmul_rn((float)d, 8388607.0f);
+        if (q.flags & FRX_QF_F32_SAFE) return __float2int_rz(y);
         return frx_trunc_i32f(y);
     } else {
         if (q.degenerate) return 0;

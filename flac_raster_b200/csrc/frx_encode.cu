@@ -2,7 +2,9 @@
 //
 // Kernels (SURVEY.md section 8a ids):
 //   K0  frx_minmax_kernel        per-stream min/max                      (converter.py:67-68, 152-153)
-//   K1..K8 frx_encode_kernel     one CTA per 4096-sample frame, persistent grid, ticket-ordered:
+//   K1..K8 frx_encode_kernel     one CTA per 4096-sample frame, persistent grid, ticket-ordered; 8 compute warps plus one
+//        control warp that takes tickets, stages the next raw samples with TMA bulk copies (mbarrier pipeline), builds the
+//        frame header and runs the look-back while the compute warps pack and checksum:
 //        K1 tile cut + band->channel gather + PCM quantise            (converter.py:56-86, 185-194; cli.py:691-699)
 //        K2 fixed-order 0..4 trial            K3 windowed autocorrelation
 //        K4 Levinson-Durbin + order pick + coefficient quantisation    K5 residual
@@ -19,8 +21,7 @@
 #include "frx_internal.cuh"
 
 #define HIST FRX_MAX_LPC
-#define NWARPS (FRX_ENC_THREADS / 32)
-#define PCM_PAD(i) ((i) + ((i) >> 4))
+#define NWARPS (FRX_ENC_THREADS / 32)   // compute warps
 
 
 // ------------------------------------------------------------------------------------------
@@ -109,10 +110,14 @@ __global__ void frx_quant_setup_kernel(const MinMaxRaw *mm, FrxQuant *q, int n, 
     if (i >= n) return;
     FrxQuant o;
     o.imin = mm[i].imin; o.imax = mm[i].imax;
-    o.fmin = 0.f; o.fmax = 0.f; o.range = 1.0; o.degenerate = 0; o.pad = 0;
+    o.fmin = 0.f; o.fmax = 0.f; o.range = 1.0; o.degenerate = 0; o.flags = 0;
     if (dtype == FRX_F32) {
         if (mm[i].has_nan) { o.fmin = CUDART_NAN_F; o.fmax = CUDART_NAN_F; }
-        else { o.fmin = frx_float_unordered(mm[i].fmin_o); o.fmax = frx_float_unordered(mm[i].fmax_o); }
+        else {
+            o.fmin = frx_float_unordered(mm[i].fmin_o); o.fmax = frx_float_unordered(mm[i].fmax_o);
+            const double m = fmax(fabs((double)o.fmin), fabs((double)o.fmax));
+            if (m * 8388607.0 < 2147483000.0) o.flags |= FRX_QF_F32_SAFE;
+        }
     } else {
         o.degenerate = !(o.imax > o.imin);
         switch (dtype) {
@@ -219,36 +224,83 @@ __device__ __forceinline__ uint32_t rice_param(uint32_t n, uint64_t s, uint32_t 
 // ------------------------------------------------------------------------------------------
 // shared state of one encoder CTA
 // ------------------------------------------------------------------------------------------
+#define FD_SLOTS 4
+#define STOP_FRAME 0xFFFFFFFFu
+#define RAW_PAD 128                              // front pad: thread 0's history read stays inside the buffer
+#define RAW_STAGE_BYTES (FRX_MAX_BLOCK * 4)
+#define RAW_STRIDE (RAW_PAD + RAW_STAGE_BYTES)
+#define TABS_BYTES (6 * FRX_ENC_THREADS * 8)     // |e| sums per thread: fixed orders 0..4 + the LPC candidate
+
+struct FrameDesc {                               // written by the control warp, read by the compute warps
+    uint32_t f, fj, s0;
+    int32_t nsamp;
+    frx_tile t;
+    uint32_t hdr[4];
+    uint32_t hdr_bits;
+    int32_t tma;                                 // 1: raw samples staged by TMA bulk copies; 0: compute warps gather them
+    int32_t tile_idx, pad;
+    FrxQuant q;
+};
+
 struct EncSmall {
-    uint32_t idx[2];         // ticket double buffer
-    uint32_t bitpos;         // running bit position in the frame buffer
-    uint32_t tailw;          // the frame's last partial word (CRC tail)
-    uint64_t out_offset;
+    uint64_t full[2], empty[2];                  // raw stage pipeline (mbarriers)
+    uint64_t sized[FD_SLOTS], placed[FD_SLOTS];  // frame size known -> look-back -> byte offset known
+    FrameDesc fd[FD_SLOTS];
+    uint32_t frame_bytes[FD_SLOTS];
+    uint64_t out_offset[FD_SLOTS];
     // per-subframe decisions
     int wasted, magbits, fixed_order, is_const, lean;
-    int lpc_ok, lpc_order, shift, precision, lpc_narrow, lpc_valid;
+    int lpc_ok, lpc_order, shift, precision, lpc_narrow;
     int32_t qlp[FRX_MAX_LPC];
     int32_t warm[FRX_MAX_LPC];
-    uint32_t kparam[2][64];  // candidate 0 = fixed, 1 = lpc
+    uint32_t kparam[2][64];                      // candidate 0 = fixed, 1 = lpc
     int cand_po[2], cand_rice2[2];
     uint64_t cand_bits[2];
-    uint64_t fsum[5];
     // reductions
-    uint64_t red64[NWARPS][5];
-    uint32_t red32[NWARPS][4];
-    double autoc[FRX_MAX_LPC + 1];
-    uint32_t scan[NWARPS];
-    uint32_t crc_part[2];
+    uint64_t wfix[NWARPS][5];
+    uint32_t wor[NWARPS][2];
+    uint32_t wbad[NWARPS][2];
+    float wac[NWARPS][FRX_MAX_LPC + 1];
+    float autoc[FRX_MAX_LPC + 1];
+    uint32_t scan[NWARPS], scan2[NWARPS];
+    uint32_t crc_part[NWARPS];
     uint16_t crc_tab[4][256];
 };
-#define ENC_UNION_BYTES 17408  // pcm[4096 + 255 pad + 1] int32  ==  acpart[13][256] float + tabs[2][256] u64
-#define ENC_SMALL_BYTES ((sizeof(EncSmall) + 15) & ~(size_t)15)
-#define CRC_THREADS 64
+#define ENC_SMALL_BYTES ((sizeof(EncSmall) + 127) & ~(size_t)127)
+
+// ------------------------------------------------------------------------------------------
+// mbarrier / TMA (bulk async copy) / named barrier primitives
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *b, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *b, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *b, uint32_t parity) {
+    while (!mbar_try_wait(b, parity)) {}
+}
+// TMA 1-D bulk copy global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void compute_sync() { asm volatile("bar.sync 1, %0;" ::"n"(FRX_ENC_THREADS) : "memory"); }
 
 // One warp analyses one candidate: partition sums from the per-thread |r| sums, Rice parameter per partition,
 // estimated bits per partition order, best order.  Lane p owns finest-level partition p (2p, 2p+1 when po_max == 6);
 // coarser levels are built with shuffles, so partition q of level L lives in lane q << (F - L).
-__device__ void analyse_partitions(EncSmall &sh, const uint64_t *tabs, int cand, int nsamp, int pred_order, int po_max, uint32_t kmax) {
+__device__ __noinline__ void analyse_partitions(EncSmall &sh, const uint64_t *tabs, int cand, int nsamp, int pred_order, int po_max, uint32_t kmax, int rsh) {
     const int lane = threadIdx.x & 31;
     const int F = po_max > 5 ? 5 : po_max;               // finest level held one-per-lane
     const int nthr = (nsamp + FRX_SPT - 1) / FRX_SPT;
@@ -258,7 +310,7 @@ __device__ void analyse_partitions(EncSmall &sh, const uint64_t *tabs, int cand,
     uint32_t kbest0 = 0, kbest1 = 0;
     if (po_max == 6) {
         const int tpp = (nsamp >> 6) / FRX_SPT;          // threads per level-6 partition
-        for (int t = 0; t < tpp; t++) { sum += tabs[(2 * lane) * tpp + t]; sumB += tabs[(2 * lane + 1) * tpp + t]; }
+        for (int t = 0; t < tpp; t++) { sum += tabs[(2 * lane) * tpp + t] >> rsh; sumB += tabs[(2 * lane + 1) * tpp + t] >> rsh; }
         uint32_t n0 = (uint32_t)(nsamp >> 6) - (lane == 0 ? (uint32_t)pred_order : 0u), n1 = (uint32_t)(nsamp >> 6);
         uint32_t k0 = rice_param(n0, sum, kmax), k1 = rice_param(n1, sumB, kmax);
         uint64_t b = rice_estimate(k0, n0, sum) + rice_estimate(k1, n1, sumB);
@@ -266,12 +318,12 @@ __device__ void analyse_partitions(EncSmall &sh, const uint64_t *tabs, int cand,
         best = b; best_po = 6; kbest0 = k0; kbest1 = k1;
         sum += sumB;
     } else if (F == 0) {
-        for (int t = lane; t < nthr; t += 32) sum += tabs[t];
+        for (int t = lane; t < nthr; t += 32) sum += tabs[t] >> rsh;
         sum = warp_sum_u64(sum);
     } else {
         const int tpp = (nsamp >> F) / FRX_SPT;          // threads per finest partition (>= 1)
         if (lane < (1 << F))
-            for (int t = 0; t < tpp; t++) sum += tabs[lane * tpp + t];
+            for (int t = 0; t < tpp; t++) sum += tabs[lane * tpp + t] >> rsh;
     }
     // levels F .. 0
     for (int L = F; L >= 0; L--) {
@@ -301,31 +353,258 @@ __device__ void analyse_partitions(EncSmall &sh, const uint64_t *tabs, int cand,
 }
 
 // ------------------------------------------------------------------------------------------
-// K1: tile cut + band -> channel gather + PCM quantise, coalesced (thread t takes samples t, t+256, ...)
+// K1: raw staging buffer -> registers -> PCM.  Thread t owns samples [16t, 16t+16) and reads HISTN samples of
+// history in front of them, with the widest aligned shared-memory loads the byte offsets allow.
 // ------------------------------------------------------------------------------------------
+template <int NWORDS, int ALIGNB>
+__device__ __forceinline__ void lds_words(const unsigned char *p, uint32_t *w) {
+    if (ALIGNB == 16) {
+#pragma unroll
+        for (int k = 0; k < NWORDS / 4; k++) {
+            uint4 v = *reinterpret_cast<const uint4 *>(p + 16 * k);
+            w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
+        }
+    } else if (ALIGNB == 8) {
+#pragma unroll
+        for (int k = 0; k < NWORDS / 2; k++) {
+            uint2 v = *reinterpret_cast<const uint2 *>(p + 8 * k);
+            w[2 * k] = v.x; w[2 * k + 1] = v.y;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < NWORDS; k++) w[k] = *reinterpret_cast<const uint32_t *>(p + 4 * k);
+    }
+}
 template <int DT>
-__device__ __forceinline__ void enc_load(const EncArgs &a, const frx_tile &t, const FrxQuant &qz, int ch, uint32_t s0, int nsamp,
-                                         int32_t *pcm, int tid) {
+__device__ __forceinline__ typename FrxElem<DT>::T elem_of(const uint32_t *w, int i) {
+    typedef typename FrxElem<DT>::T T;
+    if (sizeof(T) == 4) {
+        if (DT == FRX_F32) return (T)__uint_as_float(w[i]);
+        return (T)w[i];
+    } else if (sizeof(T) == 2) {
+        return (T)((w[i >> 1] >> ((i & 1) * 16)) & 0xFFFFu);
+    } else {
+        return (T)((w[i >> 2] >> ((i & 3) * 8)) & 0xFFu);
+    }
+}
+
+template <int DT, int HISTN>
+__device__ __forceinline__ void load_samples(const unsigned char *stage, const FrxQuant &qz, int mode, int tid, int32_t *s) {
+    typedef typename FrxElem<DT>::T T;
+    constexpr int ESZ = (int)sizeof(T);
+    constexpr int HB = HISTN * ESZ;                          // history bytes (multiple of 4)
+    constexpr int HALIGN = (HB % 16 == 0) ? 16 : ((HB % 8 == 0) ? 8 : 4);
+    constexpr int HW = HB / 4, OW = 16 * ESZ / 4;
+    uint32_t w[HW + OW];
+    const unsigned char *p = stage + (size_t)(16 * tid) * ESZ;
+    lds_words<HW, HALIGN>(p - HB, w);
+    lds_words<OW, (ESZ == 1 ? 16 : 16)>(p, w + HW);
+    if (mode == FRX_PCM_REFERENCE) {
+#pragma unroll
+        for (int i = 0; i < HISTN + FRX_SPT; i++) s[i] = frx_quant_ref<DT>(elem_of<DT>(w, i), qz);
+    } else if (mode == FRX_PCM_LOSSLESS) {
+#pragma unroll
+        for (int i = 0; i < HISTN + FRX_SPT; i++) s[i] = frx_quant_lossless<DT>(elem_of<DT>(w, i));
+    } else {
+#pragma unroll
+        for (int i = 0; i < HISTN + FRX_SPT; i++) s[i] = frx_quant_spatial<DT>(elem_of<DT>(w, i));
+    }
+}
+
+// generic gather (edge tiles whose rows are not 16-byte multiples): coalesced element loads into the raw stage
+template <int DT>
+__device__ __forceinline__ void gather_raw(const EncArgs &a, const frx_tile &t, int ch, uint32_t s0, int nsamp, unsigned char *stage, int tid) {
     typedef typename FrxElem<DT>::T T;
     const T *band = (const T *)a.raster + (long long)(t.first_band + ch) * a.band_stride + (long long)t.row_off * a.row_stride + t.col_off;
+    T *dst = reinterpret_cast<T *>(stage);
     const uint32_t w = (uint32_t)t.w;
     uint32_t sidx = s0 + (uint32_t)tid;
     uint32_t row = sidx / w, col = sidx - row * w;
-    T raw[FRX_SPT];
-#pragma unroll
-    for (int k = 0; k < FRX_SPT; k++) {
-        const int i = tid + k * FRX_ENC_THREADS;
-        raw[k] = (i < nsamp) ? __ldg(band + (long long)row * a.row_stride + col) : (T)0;
+    for (int i = tid; i < nsamp; i += FRX_ENC_THREADS) {
+        dst[i] = __ldg(band + (long long)row * a.row_stride + col);
         col += FRX_ENC_THREADS;
-        if (col >= w) {
-            if (w >= FRX_ENC_THREADS) { col -= w; row++; }
-            else { uint32_t q = col / w; row += q; col -= q * w; }
+        if (col >= w) { uint32_t q = col / w; row += q; col -= q * w; }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// control warp pieces
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ int frame_header_bytes(uint8_t *hb, int nsamp, int sr_code, int sample_rate, int channels, int bps, uint32_t fj) {
+    int n = 0, bs_code, bs_extra = 0;
+    switch (nsamp) {
+        case 192: bs_code = 1; break; case 576: bs_code = 2; break; case 1152: bs_code = 3; break;
+        case 2304: bs_code = 4; break; case 4608: bs_code = 5; break; case 256: bs_code = 8; break;
+        case 512: bs_code = 9; break; case 1024: bs_code = 10; break; case 2048: bs_code = 11; break;
+        case 4096: bs_code = 12; break; case 8192: bs_code = 13; break; case 16384: bs_code = 14; break;
+        case 32768: bs_code = 15; break;
+        default: if (nsamp <= 256) { bs_code = 6; bs_extra = 1; } else { bs_code = 7; bs_extra = 2; }
+    }
+    const int sz_code = bps == 16 ? 4 : (bps == 32 ? 7 : (bps == 8 ? 1 : (bps == 24 ? 6 : 0)));
+    hb[n++] = 0xFF; hb[n++] = 0xF8;
+    hb[n++] = (uint8_t)((bs_code << 4) | sr_code);
+    hb[n++] = (uint8_t)(((channels - 1) << 4) | (sz_code << 1));
+    const uint32_t v = fj;
+    if (v < 0x80u) hb[n++] = (uint8_t)v;
+    else if (v < 0x800u) { hb[n++] = (uint8_t)(0xC0 | (v >> 6)); hb[n++] = (uint8_t)(0x80 | (v & 0x3F)); }
+    else if (v < 0x10000u) { hb[n++] = (uint8_t)(0xE0 | (v >> 12)); hb[n++] = (uint8_t)(0x80 | ((v >> 6) & 0x3F)); hb[n++] = (uint8_t)(0x80 | (v & 0x3F)); }
+    else if (v < 0x200000u) { hb[n++] = (uint8_t)(0xF0 | (v >> 18)); hb[n++] = (uint8_t)(0x80 | ((v >> 12) & 0x3F)); hb[n++] = (uint8_t)(0x80 | ((v >> 6) & 0x3F)); hb[n++] = (uint8_t)(0x80 | (v & 0x3F)); }
+    else if (v < 0x4000000u) { hb[n++] = (uint8_t)(0xF8 | (v >> 24)); hb[n++] = (uint8_t)(0x80 | ((v >> 18) & 0x3F)); hb[n++] = (uint8_t)(0x80 | ((v >> 12) & 0x3F)); hb[n++] = (uint8_t)(0x80 | ((v >> 6) & 0x3F)); hb[n++] = (uint8_t)(0x80 | (v & 0x3F)); }
+    else { hb[n++] = (uint8_t)(0xFC | (v >> 30)); hb[n++] = (uint8_t)(0x80 | ((v >> 24) & 0x3F)); hb[n++] = (uint8_t)(0x80 | ((v >> 18) & 0x3F)); hb[n++] = (uint8_t)(0x80 | ((v >> 12) & 0x3F)); hb[n++] = (uint8_t)(0x80 | ((v >> 6) & 0x3F)); hb[n++] = (uint8_t)(0x80 | (v & 0x3F)); }
+    if (bs_extra == 1) hb[n++] = (uint8_t)(nsamp - 1);
+    else if (bs_extra == 2) { hb[n++] = (uint8_t)((nsamp - 1) >> 8); hb[n++] = (uint8_t)(nsamp - 1); }
+    if (sr_code == 13) { hb[n++] = (uint8_t)(sample_rate >> 8); hb[n++] = (uint8_t)sample_rate; }
+    uint32_t c = 0;
+    for (int i = 0; i < n; i++) c = frx_crc8_byte(c, hb[i]);
+    hb[n++] = (uint8_t)c;
+    for (int i = n; i < 16; i++) hb[i] = 0;
+    return n;
+}
+
+// lane 0 of the control warp: everything the compute warps need to know about frame f
+__device__ __noinline__ void build_frame_desc(const EncArgs &a, FrameDesc &d, uint32_t f, int &ti) {
+    // tickets grow monotonically inside a CTA: walk forward from the cached tile, fall back to bisection for long jumps
+    int steps = 0;
+    while (f >= __ldg(&a.frame_prefix[ti + 1])) {
+        ti++;
+        if (++steps == 8) {
+            int lo = ti, hi = a.n_tiles;
+            while (hi - lo > 1) {
+                int mid = (lo + hi) >> 1;
+                if (__ldg(&a.frame_prefix[mid]) <= f) lo = mid; else hi = mid;
+            }
+            ti = lo;
+            break;
         }
     }
+    const frx_tile t = a.tiles[ti];
+    const uint32_t fj = f - __ldg(&a.frame_prefix[ti]);
+    const long long tile_n = (long long)t.h * t.w;
+    const uint32_t s0 = fj * (uint32_t)a.blocksize;
+    const int nsamp = (int)min((long long)a.blocksize, tile_n - (long long)s0);
+    d.f = f; d.fj = fj; d.s0 = s0; d.nsamp = nsamp; d.t = t; d.tile_idx = ti;
+    d.q = a.quant[ti];
+    const int epv = 16 / frx_dtype_size(a.dtype);            // elements per 16 bytes
+    d.tma = (a.tma_ok && (t.w % epv) == 0 && (t.col_off % epv) == 0) ? 1 : 0;
+    uint8_t hb[16];
+    const int n = frame_header_bytes(hb, nsamp, a.sr_code, a.sample_rate, t.n_channels, a.bps, fj);
 #pragma unroll
-    for (int k = 0; k < FRX_SPT; k++) {
-        const int i = tid + k * FRX_ENC_THREADS;
-        pcm[PCM_PAD(i)] = (i < nsamp) ? frx_quant<DT>(raw[k], qz, a.pcm_mode) : 0;
+    for (int wv = 0; wv < 4; wv++)
+        d.hdr[wv] = ((uint32_t)hb[4 * wv] << 24) | ((uint32_t)hb[4 * wv + 1] << 16) | ((uint32_t)hb[4 * wv + 2] << 8) | hb[4 * wv + 3];
+    d.hdr_bits = (uint32_t)n * 8u;
+}
+
+// K8: decoupled look-back over the frame sizes (whole control warp; 128 descriptors per round trip)
+__device__ __forceinline__ uint64_t lookback(const EncArgs &a, uint32_t f, uint32_t nbytes, int lane) {
+    const uint64_t FLAG_A = 1ull << 62, FLAG_P = 2ull << 62, VMASK = (1ull << 62) - 1;
+    uint64_t exclusive = 0;
+    if (f == 0) {
+        if (lane == 0) frx_st_release_u64(&a.desc[0], FLAG_P | (uint64_t)nbytes);
+        return 0;
+    }
+    if (lane == 0) frx_st_release_u64(&a.desc[f], FLAG_A | (uint64_t)nbytes);
+    long long pos = (long long)f - 1;
+    for (;;) {
+        uint64_t v[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const long long idx = pos - 32 * k - lane;
+            v[k] = idx >= 0 ? frx_ld_acquire_u64(&a.desc[idx]) : FLAG_P;
+        }
+        bool done = false, retry = false;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (done || retry) continue;
+            const uint32_t flag = (uint32_t)(v[k] >> 62);
+            const uint32_t notready = __ballot_sync(FULLMASK, flag == 0u);
+            const uint32_t isp = __ballot_sync(FULLMASK, flag == 2u);
+            const int firstp = isp ? (__ffs((int)isp) - 1) : 32;
+            const uint32_t need = firstp >= 31 ? 0xFFFFFFFFu : ((2u << firstp) - 1u);
+            if (notready & need) { retry = true; continue; }   // restart from `pos` (already-summed windows were consumed)
+            const uint64_t contrib = (lane <= firstp) ? (v[k] & VMASK) : 0ull;
+            exclusive += warp_sum_u64(contrib);
+            if (firstp < 32) done = true; else pos -= 32;
+        }
+        if (done) break;
+        if (retry) __nanosleep(20);
+    }
+    if (lane == 0) frx_st_release_u64(&a.desc[f], FLAG_P | (exclusive + (uint64_t)nbytes));
+    return exclusive;
+}
+
+__device__ __noinline__ void control_warp(const EncArgs &a, EncSmall &sh, unsigned char *raw, int lane) {
+    const int esz = frx_dtype_size(a.dtype);
+    uint32_t ticket_next = 0;
+    if (lane == 0) ticket_next = atomicAdd(a.ticket, 1u);
+    ticket_next = __shfl_sync(FULLMASK, ticket_next, 0);
+    uint32_t unit_iss = 0, fseq_iss = 0, fseq_lb = 0;
+    int ch_iss = 0, nch_cur = 0, ti = 0;
+    bool have_frame = false, stop_issued = false;
+    for (;;) {
+        // ---- 1. frames whose size is known: look-back, publish the byte offset ----
+        if (fseq_lb < fseq_iss + (have_frame ? 1u : 0u)) {
+            const int slot = (int)(fseq_lb & (FD_SLOTS - 1));
+            if (mbar_try_wait(&sh.sized[slot], (fseq_lb / FD_SLOTS) & 1u)) {
+                const uint32_t f = sh.fd[slot].f;
+                const uint32_t nbytes = sh.frame_bytes[slot];
+                const uint64_t off = lookback(a, f, nbytes, lane);
+                if (lane == 0) {
+                    sh.out_offset[slot] = off;
+                    if (a.frame_size) a.frame_size[f] = nbytes;
+                    if (a.frame_offset) a.frame_offset[f] = off;
+                    if (f == a.total_frames - 1 && a.total_bytes) *a.total_bytes = off + nbytes;
+                    mbar_arrive(&sh.placed[slot]);
+                }
+                __syncwarp();
+                fseq_lb++;
+                continue;
+            }
+        }
+        if (stop_issued) {
+            if (fseq_lb == fseq_iss) break;
+            continue;
+        }
+        // ---- 2. next unit (frame, channel) into the raw stage ring ----
+        const int stage = (int)(unit_iss & 1u);
+        if (!mbar_try_wait(&sh.empty[stage], ((unit_iss >> 1) & 1u) ^ 1u)) continue;
+        if (!have_frame) {
+            const int slot = (int)(fseq_iss & (FD_SLOTS - 1));
+            if (ticket_next >= a.total_frames) {
+                if (lane == 0) { sh.fd[slot].f = STOP_FRAME; mbar_arrive(&sh.full[stage]); }
+                __syncwarp();
+                stop_issued = true;
+                continue;
+            }
+            if (lane == 0) build_frame_desc(a, sh.fd[slot], ticket_next, ti);
+            __syncwarp();
+            nch_cur = sh.fd[slot].t.n_channels;
+            if (lane == 0) ticket_next = atomicAdd(a.ticket, 1u);
+            ticket_next = __shfl_sync(FULLMASK, ticket_next, 0);
+            have_frame = true;
+            ch_iss = 0;
+        }
+        {
+            const FrameDesc &d = sh.fd[fseq_iss & (FD_SLOTS - 1)];
+            unsigned char *dst = raw + (size_t)stage * RAW_STRIDE + RAW_PAD;
+            if (d.tma) {
+                const long long w = d.t.w;
+                const long long s0 = d.s0, s1 = s0 + d.nsamp;
+                const long long row0 = s0 / w, row1 = (s1 - 1) / w;
+                const unsigned char *band = (const unsigned char *)a.raster +
+                    ((long long)(d.t.first_band + ch_iss) * a.band_stride + (long long)d.t.row_off * a.row_stride + d.t.col_off) * esz;
+                if (lane == 0) mbar_arrive_expect_tx(&sh.full[stage], (uint32_t)d.nsamp * (uint32_t)esz);
+                __syncwarp();
+                for (long long r = row0 + lane; r <= row1; r += 32) {
+                    const long long b0 = max(s0, r * w), b1 = min(s1, (r + 1) * w);
+                    bulk_g2s(dst + (b0 - s0) * esz, band + (r * a.row_stride + (b0 - r * w)) * esz, (uint32_t)((b1 - b0) * esz), &sh.full[stage]);
+                }
+            } else if (lane == 0) {
+                mbar_arrive(&sh.full[stage]);
+            }
+            __syncwarp();
+            unit_iss++;
+            if (++ch_iss == nch_cur) { have_frame = false; fseq_iss++; }
+        }
     }
 }
 
@@ -424,152 +703,303 @@ __device__ __forceinline__ uint32_t fixed_residuals(int order, const int32_t *s,
 }
 
 // ------------------------------------------------------------------------------------------
+// per-thread pieces of the subframe search
+// ------------------------------------------------------------------------------------------
+// K2 fixed-order trial, 32-bit: sum |e_k| over the thread's 16 samples for k = 0..4 (history in s[HISTN-4..HISTN-1])
+template <int HISTN>
+__device__ __forceinline__ void fixed_trial32(const int32_t *s, uint32_t *fa) {
+    int32_t dm1 = s[HISTN - 1] - s[HISTN - 2], dm2 = s[HISTN - 2] - s[HISTN - 3], dm3 = s[HISTN - 3] - s[HISTN - 4];
+    int32_t d1p = dm1, d2p = dm1 - dm2, d3p = (dm1 - dm2) - (dm2 - dm3);
+    uint32_t f0 = 0, f1 = 0, f2 = 0, f3 = 0, f4 = 0;
+#pragma unroll
+    for (int i = 0; i < FRX_SPT; i++) {
+        const int32_t x = s[HISTN + i];
+        const int32_t d1 = x - s[HISTN + i - 1];
+        const int32_t d2 = d1 - d1p, d3 = d2 - d2p, d4 = d3 - d3p;
+        d1p = d1; d2p = d2; d3p = d3;
+        f0 += (uint32_t)abs(x); f1 += (uint32_t)abs(d1); f2 += (uint32_t)abs(d2); f3 += (uint32_t)abs(d3); f4 += (uint32_t)abs(d4);
+    }
+    fa[0] = f0; fa[1] = f1; fa[2] = f2; fa[3] = f3; fa[4] = f4;
+}
+// the terms of thread 0 that lie in the warm-up region (sample index < order), computed exactly like the loop above does
+// with a zero history; subtracting them leaves sum |e_k| over samples k..n-1
+template <int HISTN>
+__device__ __forceinline__ void fixed_trial32_warmup(const int32_t *s, uint32_t *sub) {
+    const int32_t x0 = s[HISTN], x1 = s[HISTN + 1], x2 = s[HISTN + 2], x3 = s[HISTN + 3];
+    const int32_t a1 = x0, b1 = x1 - x0, c1 = x2 - x1, e1 = x3 - x2;      // d1[0..3]
+    const int32_t a2 = a1, b2 = b1 - a1, c2 = c1 - b1, e2 = e1 - c1;      // d2[0..3]
+    const int32_t a3 = a2, b3 = b2 - a2, c3 = c2 - b2;                    // d3[0..2]
+    const int32_t a4 = a3, b4 = b3 - a3, c4 = c3 - b3, e3 = e2 - c2, e4 = e3 - c3;  // d4[0..3]
+    sub[0] = 0;
+    sub[1] = (uint32_t)abs(a1);
+    sub[2] = (uint32_t)abs(a2) + (uint32_t)abs(b2);
+    sub[3] = (uint32_t)abs(a3) + (uint32_t)abs(b3) + (uint32_t)abs(c3);
+    sub[4] = (uint32_t)abs(a4) + (uint32_t)abs(b4) + (uint32_t)abs(c4) + (uint32_t)abs(e4);
+}
+
+// tukey(0.5) window value of sample g in a block of n samples (libFLAC's definition; short frames only)
+__device__ __forceinline__ float tukey_half(int g, int n) {
+    const int Np = (int)(0.25f * (float)n) - 1;
+    if (Np <= 0) return 1.0f;
+    if (g <= Np) return 0.5f - 0.5f * cospif((float)g / (float)Np);
+    if (g >= n - Np - 1) return 0.5f - 0.5f * cospif((float)(g - (n - Np - 1) + Np) / (float)Np);
+    return 1.0f;
+}
+
+// K4 on one thread, float32: Levinson-Durbin, expected-bits order pick, coefficient quantisation (libFLAC's scheme with
+// error feedback).  The decisions are ours; the bitstream stays exact because the residual is computed from the
+// quantised integers.
+template <bool WIDE>
+__device__ __noinline__ void lpc_design(EncSmall &sh, const float *autoc, int max_lpc, int nsamp, int wasted, int sbps, int qlp_precision,
+                                        int magbits, bool lean) {
+    sh.lpc_ok = 0;
+    const float a0 = autoc[0];
+    if (!(a0 > 0.f)) return;
+    float lpc[FRX_MAX_LPC], coefs[FRX_MAX_LPC][FRX_MAX_LPC], errs[FRX_MAX_LPC];
+    float err = 1.0f;                                  // normalised: autoc / autoc[0]
+    const float inv0 = 1.0f / a0;
+    int mo = max_lpc;
+    for (int i = 0; i < mo; i++) {
+        float r = -autoc[i + 1] * inv0;
+        for (int j = 0; j < i; j++) r -= lpc[j] * (autoc[i - j] * inv0);
+        r /= err;
+        lpc[i] = r;
+        int j;
+        for (j = 0; j < (i >> 1); j++) {
+            const float tmp = lpc[j];
+            lpc[j] += r * lpc[i - 1 - j];
+            lpc[i - 1 - j] += r * tmp;
+        }
+        if (i & 1) lpc[j] += lpc[j] * r;
+        err *= (1.0f - r * r);
+        for (j = 0; j <= i; j++) coefs[i][j] = -lpc[j];
+        errs[i] = err;
+        if (!(err > 0.f)) { mo = i + 1; break; }
+    }
+    // expected bits per order; errs are relative to autoc[0] (taken before the wasted-bit shift)
+    float best_bits = 3.0e38f;
+    int best = 1;
+    const float lscale = __log2f(a0) + __log2f(0.5f / (float)nsamp) - 2.0f * (float)wasted;
+    for (int o = 1; o <= mo; o++) {
+        const float e = errs[o - 1];
+        const float bpsr = e > 0.f ? fmaxf(0.f, 0.5f * (__log2f(e) + lscale)) : 0.f;
+        const float b = bpsr * (float)(nsamp - o) + (float)(o * (sbps + qlp_precision));
+        if (b < best_bits) { best_bits = b; best = o; }
+    }
+    const int order = best;
+    int precision = qlp_precision;
+    if (!WIDE) {
+        const int lim = 32 - sbps - (31 - __clz(order));
+        if (lim < precision) precision = lim;
+    }
+    if (precision < 5) return;
+    float cmax = 0.f;
+    for (int j = 0; j < order; j++) cmax = fmaxf(cmax, fabsf(coefs[order - 1][j]));
+    if (!(cmax > 0.f)) return;
+    int e2;
+    (void)frexpf(cmax, &e2);
+    int shift = (precision - 1) - (e2 - 1) - 1;
+    if (shift > 15) shift = 15;
+    if (shift < 0) return;
+    const int qmax = (1 << (precision - 1)) - 1, qmin = -(1 << (precision - 1));
+    float error = 0.f;
+    long long sumabs = 0;
+    const float scale = (float)(1 << shift);
+    for (int j = 0; j < order; j++) {
+        error += coefs[order - 1][j] * scale;
+        int qq = __float2int_rn(error);
+        if (qq > qmax) qq = qmax; else if (qq < qmin) qq = qmin;
+        error -= (float)qq;
+        sh.qlp[j] = qq;
+        sumabs += qq < 0 ? -qq : qq;
+    }
+    for (int j = order; j < FRX_MAX_LPC; j++) sh.qlp[j] = 0;
+    sh.lpc_order = order; sh.shift = shift; sh.precision = precision;
+    int ok = 1, narrow = 1;
+    if (WIDE) {
+        // |prediction sum| <= sumabs * 2^mag; the residual bound decides which arithmetic is safe
+        const int mag = magbits - wasted;
+        const long long M = 1ll << (mag < 0 ? 0 : mag);
+        narrow = (sumabs * M < (1ll << 31)) ? 1 : 0;
+        if (lean) {
+            const long long Bnd = M + ((sumabs * M) >> shift) + 1;
+            if (Bnd >= (1ll << 27)) ok = 0;   // keeps 32-bit residual sums exact; such wild predictors never win anyway
+        }
+    }
+    sh.lpc_narrow = narrow;
+    sh.lpc_ok = ok;
+}
+
+// K7b: Rice-code the thread's residuals.  `skip` leading samples are warm-up (thread 0 only), `nv` samples are valid.
+__device__ __forceinline__ void pack_rice(BitW &bw, const uint32_t *u, uint32_t kk, int skip, int nv) {
+    const uint32_t kmask = kk ? ((1u << kk) - 1u) : 0u;
+#pragma unroll
+    for (int i = 0; i < FRX_SPT; i++) {
+        if (i >= skip && i < nv) {
+            const uint32_t uq = u[i] >> kk;
+            const uint32_t code = (1u << kk) | (u[i] & kmask);
+            if (uq + 1u + kk <= 32u) bw.put(code, (int)(uq + 1u + kk));
+            else { bw.skip(uq); bw.put(code, (int)(kk + 1u)); }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // The frame encoder.  WIDE: PCM wider than 16 bits (64-bit LPC accumulate, RICE2).  HISTN: history samples a thread
 // keeps = the largest LPC order of the compression level (4 when the level has no LPC stage).
+// 8 compute warps (one frame at a time, 16 samples per thread) + 1 control warp.
 // ------------------------------------------------------------------------------------------
 template <bool WIDE, int HISTN>
-__global__ void __launch_bounds__(FRX_ENC_THREADS, 2) frx_encode_kernel(const EncArgs a) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+__global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArgs a) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     EncSmall &sh = *reinterpret_cast<EncSmall *>(smem_raw);
-    unsigned char *ureg = smem_raw + ENC_SMALL_BYTES;
-    int32_t *pcm = reinterpret_cast<int32_t *>(ureg);
-    float *acpart = reinterpret_cast<float *>(ureg);                          // [13][256]
-    uint64_t *tabs = reinterpret_cast<uint64_t *>(ureg + 13 * FRX_ENC_THREADS * 4);  // [2][256]
-    uint32_t *bits = reinterpret_cast<uint32_t *>(ureg + ENC_UNION_BYTES);
+    unsigned char *raw = smem_raw + ENC_SMALL_BYTES;
+    uint64_t *tabs = reinterpret_cast<uint64_t *>(raw + 2 * RAW_STRIDE);
+    uint32_t *bits = reinterpret_cast<uint32_t *>(raw + 2 * RAW_STRIDE + TABS_BYTES);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < a.frame_words; i += FRX_ENC_CTA) bits[i] = 0u;
+    for (int i = tid; i < 1024; i += FRX_ENC_CTA) (&sh.crc_tab[0][0])[i] = a.crc_tab[i];
+    if (tid == 0) {
+        for (int i = 0; i < 2; i++) { mbar_init(&sh.full[i], 1); mbar_init(&sh.empty[i], NWARPS); }
+        for (int i = 0; i < FD_SLOTS; i++) { mbar_init(&sh.sized[i], 1); mbar_init(&sh.placed[i], 1); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+    if (warp == NWARPS) { control_warp(a, sh, raw, lane); return; }
+
     const uint32_t kmax = a.bps > 16 ? 30u : 14u;  // RICE2 only for bps > 16 (libFLAC)
     const int g0 = tid * FRX_SPT;                  // first sample index of this thread
-
-    for (int i = tid; i < a.frame_words; i += FRX_ENC_THREADS) bits[i] = 0u;
-    for (int i = tid; i < 1024; i += FRX_ENC_THREADS) (&sh.crc_tab[0][0])[i] = a.crc_tab[i];
-    if (tid == 0) sh.idx[0] = atomicAdd(a.ticket, 1u);
-    int par = 0;
+    uint32_t unit = 0, fseq = 0;
 
     for (;;) {
-        __syncthreads();  // S0: previous frame left the buffers clean; ticket visible
-        const uint32_t f = sh.idx[par];
-        if (f >= a.total_frames) break;
-        if (tid == 0) sh.idx[par ^ 1] = atomicAdd(a.ticket, 1u);  // prefetch the next ticket (tickets stay ordered per CTA)
-        par ^= 1;
-
-        // ---- locate tile / frame ----
-        int lo = 0, hi = a.n_tiles;
-        while (hi - lo > 1) {
-            int mid = (lo + hi) >> 1;
-            if (__ldg(&a.frame_prefix[mid]) <= f) lo = mid; else hi = mid;
-        }
-        const frx_tile t = a.tiles[lo];
-        const FrxQuant qz = a.quant[lo];
-        const uint32_t fj = f - a.frame_prefix[lo];
-        const long long tile_n = (long long)t.h * t.w;
-        const uint32_t s0 = fj * (uint32_t)a.blocksize;
-        const int nsamp = (int)min((long long)a.blocksize, tile_n - (long long)s0);
+        // ---- next frame: its descriptor is valid once the first raw stage of the frame is full ----
+        const int slot = (int)(fseq & (FD_SLOTS - 1));
+        mbar_wait(&sh.full[unit & 1u], (unit >> 1) & 1u);
+        const FrameDesc &fd = sh.fd[slot];
+        const uint32_t f = fd.f;
+        if (f == STOP_FRAME) break;
+        const frx_tile t = fd.t;
+        const uint32_t s0 = fd.s0;
+        const int nsamp = fd.nsamp;
+        const bool use_tma = fd.tma != 0;
         const int nthr = (nsamp + FRX_SPT - 1) / FRX_SPT;
         const int nv = min(FRX_SPT, max(0, nsamp - g0));  // valid samples of this thread
-        const bool full = (nsamp == a.blocksize);
-
-        // ---- frame header (thread 0) ----
-        if (tid == 0) {
-            uint8_t hb[16];
-            int n = 0;
-            int bs_code, bs_extra = 0;
-            switch (nsamp) {
-                case 192: bs_code = 1; break; case 576: bs_code = 2; break; case 1152: bs_code = 3; break;
-                case 2304: bs_code = 4; break; case 4608: bs_code = 5; break; case 256: bs_code = 8; break;
-                case 512: bs_code = 9; break; case 1024: bs_code = 10; break; case 2048: bs_code = 11; break;
-                case 4096: bs_code = 12; break; case 8192: bs_code = 13; break; case 16384: bs_code = 14; break;
-                case 32768: bs_code = 15; break;
-                default: if (nsamp <= 256) { bs_code = 6; bs_extra = 1; } else { bs_code = 7; bs_extra = 2; }
-            }
-            int sz_code = a.bps == 16 ? 4 : (a.bps == 32 ? 7 : (a.bps == 8 ? 1 : (a.bps == 24 ? 6 : 0)));
-            hb[n++] = 0xFF; hb[n++] = 0xF8;
-            hb[n++] = (uint8_t)((bs_code << 4) | a.sr_code);
-            hb[n++] = (uint8_t)(((t.n_channels - 1) << 4) | (sz_code << 1));
-            uint32_t v = fj;
-            if (v < 0x80u) hb[n++] = (uint8_t)v;
-            else if (v < 0x800u) { hb[n++] = (uint8_t)(0xC0 | (v >> 6)); hb[n++] = (uint8_t)(0x80 | (v & 0x3F)); }
-            else if (v < 0x10000u) { hb[n++] = (uint8_t)(0xE0 | (v >> 12)); hb[n++] = (uint8_t)(0x80 | ((v >> 6) & 0x3F)); hb[n++] = (uint8_t)(0x80 | (v & 0x3F)); }
-            else if (v < 0x200000u) { hb[n++] = (uint8_t)(0xF0 | (v >> 18)); hb[n++] = (uint8_t)(0x80 | ((v >> 12) & 0x3F)); hb[n++] = (uint8_t)(0x80 | ((v >> 6) & 0x3F)); hb[n++] = (uint8_t)(0x80 | (v & 0x3F)); }
-            else if (v < 0x4000000u) { hb[n++] = (uint8_t)(0xF8 | (v >> 24)); hb[n++] = (uint8_t)(0x80 | ((v >> 18) & 0x3F)); hb[n++] = (uint8_t)(0x80 | ((v >> 12) & 0x3F)); hb[n++] = (uint8_t)(0x80 | ((v >> 6) & 0x3F)); hb[n++] = (uint8_t)(0x80 | (v & 0x3F)); }
-            else { hb[n++] = (uint8_t)(0xFC | (v >> 30)); hb[n++] = (uint8_t)(0x80 | ((v >> 24) & 0x3F)); hb[n++] = (uint8_t)(0x80 | ((v >> 18) & 0x3F)); hb[n++] = (uint8_t)(0x80 | ((v >> 12) & 0x3F)); hb[n++] = (uint8_t)(0x80 | ((v >> 6) & 0x3F)); hb[n++] = (uint8_t)(0x80 | (v & 0x3F)); }
-            if (bs_extra == 1) hb[n++] = (uint8_t)(nsamp - 1);
-            else if (bs_extra == 2) { hb[n++] = (uint8_t)((nsamp - 1) >> 8); hb[n++] = (uint8_t)(nsamp - 1); }
-            if (a.sr_code == 13) { hb[n++] = (uint8_t)(a.sample_rate >> 8); hb[n++] = (uint8_t)a.sample_rate; }
-            uint32_t c = 0;
-            for (int i = 0; i < n; i++) c = frx_crc8_byte(c, hb[i]);
-            hb[n++] = (uint8_t)c;
-            for (int i = n; i < 16; i++) hb[i] = 0;
-            for (int wv = 0; wv < 4; wv++)
-                bits[wv] = ((uint32_t)hb[4 * wv] << 24) | ((uint32_t)hb[4 * wv + 1] << 16) | ((uint32_t)hb[4 * wv + 2] << 8) | hb[4 * wv + 3];
-            sh.bitpos = (uint32_t)n * 8u;
+        const bool full = (nsamp == a.blocksize) && (a.blocksize == FRX_MAX_BLOCK);
+        uint32_t bitpos = fd.hdr_bits;
+        if (tid < 4) bits[tid] = fd.hdr[tid];
+        int po_max;
+        {
+            const int tz = __ffs(nsamp) - 1;               // trailing zeros of the block size
+            po_max = min(a.max_po, max(0, tz - 4));        // partitions stay multiples of 16 samples
+            while (po_max > 0 && (nsamp >> po_max) <= FRX_MAX_LPC) po_max--;
         }
+        const int max_lpc = min(min(a.max_lpc_order, HISTN), nsamp - 1);
 
         // ================= per channel =================
         for (int ch = 0; ch < t.n_channels; ch++) {
-          bool force_verbatim = false;
-          for (;;) {  // second pass only when the Rice-coded subframe would not beat VERBATIM (then it is redone as VERBATIM)
-            __syncthreads();  // S2: union region free, bitpos visible
-            switch (a.dtype) {
-                case FRX_U8: enc_load<FRX_U8>(a, t, qz, ch, s0, nsamp, pcm, tid); break;
-                case FRX_I16: enc_load<FRX_I16>(a, t, qz, ch, s0, nsamp, pcm, tid); break;
-                case FRX_U16: enc_load<FRX_U16>(a, t, qz, ch, s0, nsamp, pcm, tid); break;
-                case FRX_I32: enc_load<FRX_I32>(a, t, qz, ch, s0, nsamp, pcm, tid); break;
-                case FRX_U32: enc_load<FRX_U32>(a, t, qz, ch, s0, nsamp, pcm, tid); break;
-                default: enc_load<FRX_F32>(a, t, qz, ch, s0, nsamp, pcm, tid); break;
+            const int stage = (int)(unit & 1u);
+            unsigned char *stg = raw + (size_t)stage * RAW_STRIDE + RAW_PAD;
+            if (ch > 0) mbar_wait(&sh.full[stage], (unit >> 1) & 1u);
+            if (!use_tma) {
+                switch (a.dtype) {
+                    case FRX_U8: gather_raw<FRX_U8>(a, t, ch, s0, nsamp, stg, tid); break;
+                    case FRX_I16: gather_raw<FRX_I16>(a, t, ch, s0, nsamp, stg, tid); break;
+                    case FRX_U16: gather_raw<FRX_U16>(a, t, ch, s0, nsamp, stg, tid); break;
+                    case FRX_I32: gather_raw<FRX_I32>(a, t, ch, s0, nsamp, stg, tid); break;
+                    case FRX_U32: gather_raw<FRX_U32>(a, t, ch, s0, nsamp, stg, tid); break;
+                    default: gather_raw<FRX_F32>(a, t, ch, s0, nsamp, stg, tid); break;
+                }
+                compute_sync();
             }
-            __syncthreads();  // S3
-            // ---- registers: HISTN history + 16 samples ----
+            // ---- K1: registers = HISTN history + 16 samples, quantised to PCM ----
             int32_t s[HISTN + FRX_SPT];
-#pragma unroll
-            for (int i = 0; i < HISTN + FRX_SPT; i++) {
-                int g = g0 - HISTN + i;
-                s[i] = (g >= 0) ? pcm[PCM_PAD(g)] : 0;
+            {
+                const FrxQuant qz = fd.q;
+                switch (a.dtype) {
+                    case FRX_U8: load_samples<FRX_U8, HISTN>(stg, qz, a.pcm_mode, tid, s); break;
+                    case FRX_I16: load_samples<FRX_I16, HISTN>(stg, qz, a.pcm_mode, tid, s); break;
+                    case FRX_U16: load_samples<FRX_U16, HISTN>(stg, qz, a.pcm_mode, tid, s); break;
+                    case FRX_I32: load_samples<FRX_I32, HISTN>(stg, qz, a.pcm_mode, tid, s); break;
+                    case FRX_U32: load_samples<FRX_U32, HISTN>(stg, qz, a.pcm_mode, tid, s); break;
+                    default: load_samples<FRX_F32, HISTN>(stg, qz, a.pcm_mode, tid, s); break;
+                }
             }
+            // the raw stage may be refilled as soon as every warp has its samples in registers
+            if (!use_tma) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sh.empty[stage]);
+            unit++;
+            if (tid == 0) {
+#pragma unroll
+                for (int i = 0; i < HISTN; i++) s[i] = 0;
+            }
+            if (!full) {
+#pragma unroll
+                for (int i = 0; i < HISTN + FRX_SPT; i++)
+                    if (g0 - HISTN + i >= nsamp) s[i] = 0;
+            }
+            // ---- wasted bits / magnitude ----
             uint32_t orv = 0, ora = 0;
 #pragma unroll
-            for (int i = 0; i < FRX_SPT; i++) { orv |= (uint32_t)s[HISTN + i]; ora |= (uint32_t)abs(s[HISTN + i]); }
+            for (int i = 0; i < FRX_SPT; i++) {
+                orv |= (uint32_t)s[HISTN + i];
+                if (WIDE) ora |= (uint32_t)(s[HISTN + i] ^ (s[HISTN + i] >> 31));
+            }
             orv = __reduce_or_sync(FULLMASK, orv);
-            ora = __reduce_or_sync(FULLMASK, ora);
+            if (WIDE) ora = __reduce_or_sync(FULLMASK, ora);
             // ---- K2 (lean): fixed-order trial in 32-bit, sum |e_k| over samples g >= k ----
-            uint32_t fa0 = 0, fa1 = 0, fa2 = 0, fa3 = 0, fa4 = 0;
-            {
-                const bool first = (tid == 0);
+            uint32_t fa[5];
+            fixed_trial32<HISTN>(s, fa);
+            if (tid == 0) {
+                uint32_t sub[5];
+                fixed_trial32_warmup<HISTN>(s, sub);
+#pragma unroll
+                for (int o = 1; o < 5; o++) fa[o] -= sub[o];
+            }
+            if (!full && nv < FRX_SPT) {
+                // partial or empty thread of a short frame: redo with per-sample masks
                 int32_t dm1 = s[HISTN - 1] - s[HISTN - 2], dm2 = s[HISTN - 2] - s[HISTN - 3], dm3 = s[HISTN - 3] - s[HISTN - 4];
                 int32_t d1p = dm1, d2p = dm1 - dm2, d3p = (dm1 - dm2) - (dm2 - dm3);
 #pragma unroll
+                for (int o = 0; o < 5; o++) fa[o] = 0;
+#pragma unroll
                 for (int i = 0; i < FRX_SPT; i++) {
-                    int32_t x = s[HISTN + i];
-                    int32_t d1 = x - s[HISTN + i - 1];
-                    int32_t d2 = d1 - d1p, d3 = d2 - d2p, d4 = d3 - d3p;
+                    const int32_t x = s[HISTN + i];
+                    const int32_t d1 = x - s[HISTN + i - 1];
+                    const int32_t d2 = d1 - d1p, d3 = d2 - d2p, d4 = d3 - d3p;
                     d1p = d1; d2p = d2; d3p = d3;
                     if (i < nv) {
-                        fa0 += (uint32_t)abs(x);
-                        if (i >= 1 || !first) fa1 += (uint32_t)abs(d1);
-                        if (i >= 2 || !first) fa2 += (uint32_t)abs(d2);
-                        if (i >= 3 || !first) fa3 += (uint32_t)abs(d3);
-                        if (i >= 4 || !first) fa4 += (uint32_t)abs(d4);
+                        const int g = g0 + i;
+                        fa[0] += (uint32_t)abs(x);
+                        if (g >= 1) fa[1] += (uint32_t)abs(d1);
+                        if (g >= 2) fa[2] += (uint32_t)abs(d2);
+                        if (g >= 3) fa[3] += (uint32_t)abs(d3);
+                        if (g >= 4) fa[4] += (uint32_t)abs(d4);
                     }
                 }
             }
+#pragma unroll
+            for (int o = 0; o < 5; o++) tabs[o * FRX_ENC_THREADS + tid] = fa[o];
             {
-                uint64_t w0 = warp_sum_u32_wide(fa0), w1 = warp_sum_u32_wide(fa1), w2 = warp_sum_u32_wide(fa2),
-                         w3 = warp_sum_u32_wide(fa3), w4 = warp_sum_u32_wide(fa4);
+                uint64_t w5[5];
+#pragma unroll
+                for (int o = 0; o < 5; o++) w5[o] = WIDE ? warp_sum_u32_wide(fa[o]) : (uint64_t)__reduce_add_sync(FULLMASK, fa[o]);
                 if (lane == 0) {
-                    sh.red64[warp][0] = w0; sh.red64[warp][1] = w1; sh.red64[warp][2] = w2; sh.red64[warp][3] = w3; sh.red64[warp][4] = w4;
-                    sh.red32[warp][0] = orv; sh.red32[warp][1] = ora;
+#pragma unroll
+                    for (int o = 0; o < 5; o++) sh.wfix[warp][o] = w5[o];
+                    sh.wor[warp][0] = orv; sh.wor[warp][1] = ora;
                 }
             }
-            __syncthreads();  // S4: every thread holds its samples; pcm may be overwritten by acpart
-            // ---- K3: windowed autocorrelation partials (float within the thread, double across threads) ----
-            const int max_lpc = min(min(a.max_lpc_order, HISTN), nsamp - 1);
+            // ---- K3: windowed autocorrelation partials (float within the warp) ----
             if (max_lpc > 0) {
                 float xw[HISTN + FRX_SPT];
                 if (full) {
                     const float4 *w4 = reinterpret_cast<const float4 *>(a.window + g0);
 #pragma unroll
                     for (int v = 0; v < FRX_SPT / 4; v++) {
-                        float4 wv = __ldg(w4 + v);
+                        const float4 wv = __ldg(w4 + v);
                         xw[HISTN + 4 * v] = (float)s[HISTN + 4 * v] * wv.x; xw[HISTN + 4 * v + 1] = (float)s[HISTN + 4 * v + 1] * wv.y;
                         xw[HISTN + 4 * v + 2] = (float)s[HISTN + 4 * v + 2] * wv.z; xw[HISTN + 4 * v + 3] = (float)s[HISTN + 4 * v + 3] * wv.w;
                     }
@@ -577,7 +1007,7 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS, 2) frx_encode_kernel(const En
                         const float4 *h4 = reinterpret_cast<const float4 *>(a.window + g0 - HISTN);
 #pragma unroll
                         for (int v = 0; v < HISTN / 4; v++) {
-                            float4 wv = __ldg(h4 + v);
+                            const float4 wv = __ldg(h4 + v);
                             xw[4 * v] = (float)s[4 * v] * wv.x; xw[4 * v + 1] = (float)s[4 * v + 1] * wv.y;
                             xw[4 * v + 2] = (float)s[4 * v + 2] * wv.z; xw[4 * v + 3] = (float)s[4 * v + 3] * wv.w;
                         }
@@ -588,17 +1018,8 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS, 2) frx_encode_kernel(const En
                 } else {
 #pragma unroll
                     for (int i = 0; i < HISTN + FRX_SPT; i++) {
-                        int g = g0 - HISTN + i;
-                        float wv = 0.f;
-                        if (g >= 0 && g < nsamp) {
-                            int Np = (int)(0.25f * (float)nsamp) - 1;  // tukey(0.5) of length nsamp
-                            wv = 1.0f;
-                            if (Np > 0) {
-                                if (g <= Np) wv = 0.5f - 0.5f * cospif((float)g / (float)Np);
-                                else if (g >= nsamp - Np - 1) wv = 0.5f - 0.5f * cospif((float)(g - (nsamp - Np - 1) + Np) / (float)Np);
-                            }
-                        }
-                        xw[i] = (float)s[i] * wv;
+                        const int g = g0 - HISTN + i;
+                        xw[i] = (g >= 0 && g < nsamp) ? (float)s[i] * tukey_half(g, nsamp) : 0.f;
                     }
                 }
                 float ac[HISTN + 1];
@@ -610,66 +1031,90 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS, 2) frx_encode_kernel(const En
                     for (int lag = 0; lag <= HISTN; lag++) ac[lag] = fmaf(xw[HISTN + i], xw[HISTN + i - lag], ac[lag]);
                 }
 #pragma unroll
-                for (int lag = 0; lag <= HISTN; lag++) acpart[lag * FRX_ENC_THREADS + tid] = ac[lag];
-            }
-            __syncthreads();  // S5
-            // warp w reduces lags w, w+8 (double accumulation across threads)
-            for (int lag = warp; lag <= max_lpc; lag += NWARPS) {
-                double d = 0.0;
+                for (int lag = 0; lag <= HISTN; lag++) {
+                    float v = ac[lag];
 #pragma unroll
-                for (int j = 0; j < FRX_ENC_THREADS / 32; j++) d += (double)acpart[lag * FRX_ENC_THREADS + lane + 32 * j];
-                d = warp_sum_f64(d);
-                if (lane == 0) sh.autoc[lag] = d;
+                    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULLMASK, v, o);
+                    if (lane == 0) sh.wac[warp][lag] = v;
+                }
             }
-            // warp 7: block totals of the fixed trial, wasted bits, magnitude, order decision
-            if (warp == NWARPS - 1) {
+            compute_sync();  // SA: per-warp partials and tabs[0..4] are in shared memory
+            // ---- warp 0: fixed-order decision + Rice search of the fixed candidate; warp 1: LPC design ----
+            if (warp == 0) {
                 uint64_t tot = 0;
                 uint32_t o32 = 0;
-                if (lane < 5) { for (int w2 = 0; w2 < NWARPS; w2++) tot += sh.red64[w2][lane]; }
-                else if (lane < 7) { for (int w2 = 0; w2 < NWARPS; w2++) o32 |= sh.red32[w2][lane - 5]; }
-                const uint32_t all_or = __shfl_sync(FULLMASK, o32, 5), all_abs = __shfl_sync(FULLMASK, o32, 6);
+                if (lane < 5) { for (int w2 = 0; w2 < NWARPS; w2++) tot += sh.wfix[w2][lane]; }
+                else if (lane < 7) { for (int w2 = 0; w2 < NWARPS; w2++) o32 |= sh.wor[w2][lane - 5]; }
+                const uint32_t all_or = __shfl_sync(FULLMASK, o32, 5);
                 const int wasted = all_or ? (__ffs((int)all_or) - 1) : 0;
-                const int magbits = 32 - __clz((int)all_abs);  // bits of the largest magnitude (0 for silence)
-                const bool lean = !WIDE || magbits <= 23;
                 const uint64_t f1 = __shfl_sync(FULLMASK, tot, 1);
-                // best fixed order among lanes 0..4 (lowest order wins ties)
-                uint64_t bestv = (lane < 5) ? tot : ~0ull;
+                uint64_t bestv = (lane < 5) ? tot : ~0ull;   // best fixed order among lanes 0..4 (lowest order wins ties)
                 int besto = lane;
                 for (int o = 1; o < 8; o <<= 1) {
-                    uint64_t ov = __shfl_xor_sync(FULLMASK, bestv, o);
-                    int oo = __shfl_xor_sync(FULLMASK, besto, o);
+                    const uint64_t ov = __shfl_xor_sync(FULLMASK, bestv, o);
+                    const int oo = __shfl_xor_sync(FULLMASK, besto, o);
                     if (ov < bestv || (ov == bestv && oo < besto)) { bestv = ov; besto = oo; }
                 }
-                if (lane < 5) sh.fsum[lane] = tot;
+                besto = __shfl_sync(FULLMASK, besto, 0);
+                const int fixed_order = (nsamp > 4) ? besto : -1;
                 if (lane == 0) {
-                    sh.wasted = wasted; sh.magbits = magbits; sh.lean = lean ? 1 : 0;
+                    sh.wasted = wasted;
                     sh.is_const = (f1 == 0) ? 1 : 0;   // sum |s[g]-s[g-1]| == 0  <=>  all samples equal
-                    sh.fixed_order = (nsamp > 4) ? besto : -1;
+                    sh.fixed_order = fixed_order;
+                }
+                if (fixed_order >= 0) analyse_partitions(sh, tabs + fixed_order * FRX_ENC_THREADS, 0, nsamp, fixed_order, po_max, kmax, wasted);
+            } else if (warp == 1) {
+                uint32_t o32 = 0;
+                if (lane < 2) { for (int w2 = 0; w2 < NWARPS; w2++) o32 |= sh.wor[w2][lane]; }
+                const uint32_t all_or = __shfl_sync(FULLMASK, o32, 0), all_abs = __shfl_sync(FULLMASK, o32, 1);
+                const int wasted = all_or ? (__ffs((int)all_or) - 1) : 0;
+                const int magbits = WIDE ? 32 - __clz((int)all_abs) : 15;  // bits of the largest magnitude
+                const bool lean = !WIDE || magbits <= 23;
+                float acs = 0.f;
+                if (lane <= max_lpc) { for (int w2 = 0; w2 < NWARPS; w2++) acs += sh.wac[w2][lane]; }
+                float *autoc = sh.autoc;
+                if (lane <= FRX_MAX_LPC) autoc[lane] = acs;
+                __syncwarp();
+                if (lane == 0) {
+                    sh.magbits = magbits; sh.lean = lean ? 1 : 0;
+                    sh.lpc_ok = 0;
+                    if (max_lpc > 0 && nsamp > 4)
+                        lpc_design<WIDE>(sh, autoc, max_lpc, nsamp, wasted, a.bps - wasted, a.qlp_precision, magbits, lean);
                 }
             }
-            __syncthreads();  // S6
+            compute_sync();  // SB
             const int wasted = sh.wasted;
             const bool lean = sh.lean != 0;
             const int sbps = a.bps - wasted;
+            int fixed_order = sh.fixed_order;
+            bool is_const = sh.is_const != 0;
             if (wasted) {
 #pragma unroll
                 for (int i = 0; i < HISTN + FRX_SPT; i++) s[i] >>= wasted;
             }
-            // ---- fat data (|s| >= 2^23: lossless int32/float bit patterns): redo the fixed trial in 64-bit ----
+            bool lpc_try = sh.lpc_ok != 0;
+            const int lpc_order = sh.lpc_order;
+            const int lshift = sh.shift;
+            int32_t r[FRX_SPT];
+            const int lmode = !WIDE ? 0 : (lean ? (sh.lpc_narrow ? 0 : 1) : 2);
+            int32_t q[HISTN];
+#pragma unroll
+            for (int j = 0; j < HISTN; j++) q[j] = sh.qlp[j];
             if (WIDE && !lean) {
+                // ---- fat data (|s| > 2^23: lossless int32 / float bit patterns): 64-bit fixed trial, range-checked LPC ----
                 uint64_t acc[5] = { 0, 0, 0, 0, 0 };
                 uint32_t fbad = 0;
 #pragma unroll
                 for (int i = 0; i < FRX_SPT; i++) {
-                    int g = g0 + i;
+                    const int g = g0 + i;
                     if (i < nv) {
                         const int32_t *p = s + HISTN + i;
-                        long long A = p[0], B = p[-1], C = p[-2], D = p[-3], E = p[-4];
-                        long long e[5] = { A, A - B, A - 2 * B + C, A - 3 * B + 3 * C - D, A - 4 * B + 6 * C - 4 * D + E };
+                        const long long A = p[0], B = p[-1], C = p[-2], D = p[-3], E = p[-4];
+                        const long long e[5] = { A, A - B, A - 2 * B + C, A - 3 * B + 3 * C - D, A - 4 * B + 6 * C - 4 * D + E };
 #pragma unroll
                         for (int o = 0; o < 5; o++) {
                             if (g >= o) {
-                                unsigned long long av = (unsigned long long)llabs(e[o]);
+                                const unsigned long long av = (unsigned long long)llabs(e[o]);
                                 acc[o] += av;
                                 if (av > 0x7FFFFFFFull) fbad |= 1u << o;
                             }
@@ -677,282 +1122,200 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS, 2) frx_encode_kernel(const En
                     }
                 }
 #pragma unroll
+                for (int o = 0; o < 5; o++) tabs[o * FRX_ENC_THREADS + tid] = acc[o];
+#pragma unroll
                 for (int o = 0; o < 5; o++) acc[o] = warp_sum_u64(acc[o]);
                 fbad = __reduce_or_sync(FULLMASK, fbad);
-                if (lane == 0) {
-#pragma unroll
-                    for (int o = 0; o < 5; o++) sh.red64[warp][o] = acc[o];
-                    sh.red32[warp][2] = fbad;
-                }
-                __syncthreads();
-                if (tid == 0) {
-                    uint64_t bestv = ~0ull;
-                    int besto = -1;
-                    uint32_t fb = 0;
-                    for (int w2 = 0; w2 < NWARPS; w2++) fb |= sh.red32[w2][2];
-                    for (int o = 0; o < 5; o++) {
-                        uint64_t tot = 0;
-                        for (int w2 = 0; w2 < NWARPS; w2++) tot += sh.red64[w2][o];
-                        sh.fsum[o] = tot;
-                        if (!((fb >> o) & 1u) && tot < bestv) { bestv = tot; besto = o; }
-                    }
-                    sh.is_const = (sh.fsum[1] == 0 && !(fb & 2u)) ? 1 : 0;
-                    sh.fixed_order = (nsamp > 4) ? besto : -1;
-                }
-                // (published by the S7 barrier below)
-            }
-            // ---- K4: Levinson-Durbin, order pick, coefficient quantisation (thread 0) ----
-            if (tid == 0) {
-                sh.lpc_ok = 0;
-                const bool is_const0 = sh.is_const != 0;  // lean: warp 7 before S6; fat: this thread, just above
-                const double a0 = sh.autoc[0];
-                if (!is_const0 && max_lpc > 0 && nsamp > 4 && a0 != 0.0) {
-                    double lpc[FRX_MAX_LPC], err = a0;
-                    double errs[FRX_MAX_LPC];
-                    double coefs[FRX_MAX_LPC][FRX_MAX_LPC];
-                    int mo = max_lpc;
-                    for (int i = 0; i < mo; i++) {
-                        double r = -sh.autoc[i + 1];
-                        for (int j = 0; j < i; j++) r -= lpc[j] * sh.autoc[i - j];
-                        r /= err;
-                        lpc[i] = r;
-                        int j;
-                        for (j = 0; j < (i >> 1); j++) {
-                            double tmp = lpc[j];
-                            lpc[j] += r * lpc[i - 1 - j];
-                            lpc[i - 1 - j] += r * tmp;
-                        }
-                        if (i & 1) lpc[j] += lpc[j] * r;
-                        err *= (1.0 - r * r);
-                        for (j = 0; j <= i; j++) coefs[i][j] = -lpc[j];
-                        errs[i] = err;
-                        if (!(err > 0.0)) { mo = i + 1; break; }
-                    }
-                    // expected bits per order (the autocorrelation was taken before the wasted-bit shift)
-                    double best_bits = 1e300;
-                    int best = 1;
-                    const double scale = 0.5 / (double)nsamp * (wasted ? ldexp(1.0, -2 * wasted) : 1.0);
-                    for (int o = 1; o <= mo; o++) {
-                        double e = errs[o - 1];
-                        double bpsr = e > 0.0 ? fmax(0.0, 0.5 * log2(scale * e)) : 0.0;
-                        double b = bpsr * (double)(nsamp - o) + (double)(o * (sbps + a.qlp_precision));
-                        if (b < best_bits) { best_bits = b; best = o; }
-                    }
-                    int order = best;
-                    int precision = a.qlp_precision;
-                    if (!WIDE) {
-                        int lim = 32 - sbps - (31 - __clz(order));
-                        if (lim < precision) precision = lim;
-                    }
-                    if (precision >= 5) {
-                        double cmax = 0.0;
-                        for (int j = 0; j < order; j++) cmax = fmax(cmax, fabs(coefs[order - 1][j]));
-                        if (cmax > 0.0) {
-                            int e2;
-                            (void)frexp(cmax, &e2);
-                            int shift = (precision - 1) - (e2 - 1) - 1;
-                            if (shift > 15) shift = 15;
-                            if (shift >= 0) {
-                                const int qmax = (1 << (precision - 1)) - 1, qmin = -(1 << (precision - 1));
-                                double error = 0.0;
-                                long long sumabs = 0;
-                                for (int j = 0; j < order; j++) {
-                                    error += coefs[order - 1][j] * (double)(1 << shift);
-                                    long long qq = llrint(error);
-                                    if (qq > qmax) qq = qmax; else if (qq < qmin) qq = qmin;
-                                    error -= (double)qq;
-                                    sh.qlp[j] = (int32_t)qq;
-                                    sumabs += qq < 0 ? -qq : qq;
-                                }
-                                for (int j = order; j < FRX_MAX_LPC; j++) sh.qlp[j] = 0;
-                                sh.lpc_order = order; sh.shift = shift; sh.precision = precision;
-                                int ok = 1, narrow = 1;
-                                if (WIDE) {
-                                    // |prediction sum| <= sumabs * 2^mag; the residual bound decides which arithmetic is safe
-                                    const int mag = sh.magbits - wasted;
-                                    const long long M = 1ll << (mag < 0 ? 0 : mag);
-                                    narrow = (sumabs * M < (1ll << 31)) ? 1 : 0;
-                                    if (lean) {
-                                        long long Bnd = M + ((sumabs * M) >> shift) + 1;
-                                        if (Bnd >= (1ll << 27)) ok = 0;  // keeps 32-bit residual sums exact; such wild predictors never win anyway
-                                    }
-                                }
-                                sh.lpc_narrow = narrow;
-                                sh.lpc_ok = ok;
-                            }
-                        }
-                    }
-                }
-            }
-            __syncthreads();  // S7
-            // ---- K5: per-thread |r| sums of the two candidates (tabs lives where acpart was: S7 passed) ----
-            const int fixed_order = sh.fixed_order;
-            const bool is_const = sh.is_const != 0;
-            const bool lpc_try = sh.lpc_ok != 0;
-            const int lpc_order = sh.lpc_order;
-            const int lshift = sh.shift;
-            int32_t q[HISTN];
-#pragma unroll
-            for (int j = 0; j < HISTN; j++) q[j] = sh.qlp[j];
-            const int lmode = !WIDE ? 0 : (lean ? (sh.lpc_narrow ? 0 : 1) : 2);
-            {
-                uint64_t ab = 0;
                 bool bad = false;
+                uint64_t ab = 0;
                 if (lpc_try) {
-                    int32_t r[FRX_SPT];
-                    uint32_t badm = 0;
-                    if (lmode == 0) badm = lpc_residuals_dispatch<0, HISTN>(lpc_order, s, q, lshift, r);
-                    else if (WIDE && lmode == 1) badm = lpc_residuals_dispatch<1, HISTN>(lpc_order, s, q, lshift, r);
-                    else if (WIDE) badm = lpc_residuals_dispatch<2, HISTN>(lpc_order, s, q, lshift, r);
-                    uint32_t ab32 = 0;
+                    const uint32_t badm = lpc_residuals_dispatch<2, HISTN>(lpc_order, s, q, lshift, r);
 #pragma unroll
                     for (int i = 0; i < FRX_SPT; i++) {
-                        const bool valid = (i < nv) && (g0 + i >= lpc_order);
-                        if (valid) {
+                        if (i < nv && g0 + i >= lpc_order) {
                             if ((badm >> i) & 1u) bad = true;
-                            if (WIDE && !lean) ab += (uint32_t)abs(r[i]); else ab32 += (uint32_t)abs(r[i]);
+                            ab += (uint32_t)abs(r[i]);
                         }
                     }
-                    if (!(WIDE && !lean)) ab = ab32;
                 }
-                tabs[FRX_ENC_THREADS + tid] = ab;
-                if (WIDE && !lean) {
-                    unsigned anybad = __ballot_sync(FULLMASK, bad);
-                    if (lane == 0) sh.red32[warp][3] = anybad ? 1u : 0u;
+                tabs[5 * FRX_ENC_THREADS + tid] = ab;
+                const unsigned anybad = __ballot_sync(FULLMASK, bad);
+                if (lane == 0) {
+#pragma unroll
+                    for (int o = 0; o < 5; o++) sh.wfix[warp][o] = acc[o];
+                    sh.wbad[warp][0] = fbad; sh.wbad[warp][1] = anybad ? 1u : 0u;
                 }
-                uint64_t fb = 0;
-                if (fixed_order >= 0) {
-                    if (WIDE && !lean) {
-                        int32_t rf[FRX_SPT];
-                        (void)fixed_residuals<true, HISTN>(fixed_order, s, rf);
+                compute_sync();
+                if (warp == 0) {
+                    uint32_t fb = 0;
+                    for (int w2 = 0; w2 < NWARPS; w2++) fb |= sh.wbad[w2][0];
+                    uint64_t bestv = ~0ull, f1 = 0;
+                    int besto = -1;
+                    for (int o = 0; o < 5; o++) {
+                        uint64_t tot = 0;
+                        for (int w2 = 0; w2 < NWARPS; w2++) tot += sh.wfix[w2][o];
+                        if (o == 1) f1 = tot;
+                        if (!((fb >> o) & 1u) && tot < bestv) { bestv = tot; besto = o; }
+                    }
+                    const int fo = (nsamp > 4) ? besto : -1;
+                    if (lane == 0) { sh.is_const = (f1 == 0 && !(fb & 2u)) ? 1 : 0; sh.fixed_order = fo; }
+                    if (fo >= 0) analyse_partitions(sh, tabs + fo * FRX_ENC_THREADS, 0, nsamp, fo, po_max, kmax, 0);
+                } else if (warp == 1) {
+                    uint32_t b = 0;
+                    for (int w2 = 0; w2 < NWARPS; w2++) b |= sh.wbad[w2][1];
+                    const bool valid = lpc_try && !b;
+                    if (lane == 0) sh.lpc_ok = valid ? 1 : 0;
+                    if (valid) analyse_partitions(sh, tabs + 5 * FRX_ENC_THREADS, 1, nsamp, lpc_order, po_max, kmax, 0);
+                }
+                compute_sync();
+                fixed_order = sh.fixed_order;
+                is_const = sh.is_const != 0;
+                lpc_try = sh.lpc_ok != 0;
+            } else {
+                // ---- K5: LPC residuals (kept in registers) and their |r| sums ----
+                if (lpc_try) {
+                    if (lmode == 0) (void)lpc_residuals_dispatch<0, HISTN>(lpc_order, s, q, lshift, r);
+                    else if (WIDE) (void)lpc_residuals_dispatch<1, HISTN>(lpc_order, s, q, lshift, r);
+                    uint32_t ab = 0;
+#pragma unroll
+                    for (int i = 0; i < FRX_SPT; i++) ab += (uint32_t)abs(r[i]);
+                    if (tid == 0 || (!full && nv < FRX_SPT)) {
+                        ab = 0;
 #pragma unroll
                         for (int i = 0; i < FRX_SPT; i++)
-                            if (i < nv && g0 + i >= fixed_order) fb += (uint32_t)abs(rf[i]);
-                    } else {
-                        uint32_t sel = fixed_order == 0 ? fa0 : fixed_order == 1 ? fa1 : fixed_order == 2 ? fa2 : fixed_order == 3 ? fa3 : fa4;
-                        fb = sel >> wasted;  // all samples are multiples of 2^wasted, so the sums scale exactly
+                            if (i < nv && g0 + i >= lpc_order) ab += (uint32_t)abs(r[i]);
                     }
+                    tabs[5 * FRX_ENC_THREADS + tid] = ab;
                 }
-                tabs[tid] = fb;
+                compute_sync();  // SC
+                if (warp == 1 && lpc_try) analyse_partitions(sh, tabs + 5 * FRX_ENC_THREADS, 1, nsamp, lpc_order, po_max, kmax, 0);
+                compute_sync();  // SD
             }
-            __syncthreads();  // S8
-            // ---- K6: Rice partition analysis, warp 0 = fixed, warp 1 = lpc ----
-            int po_max = 0;
-            {
-                int tz = __ffs(nsamp) - 1;               // trailing zeros of the block size
-                po_max = min(a.max_po, max(0, tz - 4));  // partitions stay multiples of 16 samples
-                while (po_max > 0 && (nsamp >> po_max) <= FRX_MAX_LPC) po_max--;
-            }
-            bool lpc_valid = lpc_try;
-            if (WIDE && !lean && lpc_try) {
-                uint32_t b = 0;
-#pragma unroll
-                for (int w2 = 0; w2 < NWARPS; w2++) b |= sh.red32[w2][3];
-                if (b) lpc_valid = false;
-            }
-            if (warp == 0 && fixed_order >= 0) analyse_partitions(sh, tabs, 0, nsamp, fixed_order, po_max, kmax);
-            if (warp == 1 && lpc_valid) analyse_partitions(sh, tabs + FRX_ENC_THREADS, 1, nsamp, lpc_order, po_max, kmax);
-            __syncthreads();  // S9
 
             // ---- choose ----
             const uint64_t verb_bits = 8ull + (uint64_t)wasted + (uint64_t)nsamp * (uint64_t)sbps;
             int type = 1, order = 0, cand = 0;
             uint64_t best_bits = verb_bits;
             if (is_const) { type = 0; best_bits = 8ull + wasted + sbps; }
-            else if (!force_verbatim) {
+            else {
                 if (fixed_order >= 0) {
-                    uint64_t b = 8ull + wasted + (uint64_t)fixed_order * sbps + sh.cand_bits[0];
+                    const uint64_t b = 8ull + wasted + (uint64_t)fixed_order * sbps + sh.cand_bits[0];
                     if (b < best_bits) { best_bits = b; type = 2; order = fixed_order; cand = 0; }
                 }
-                if (lpc_valid) {
-                    uint64_t b = 8ull + wasted + 9ull + (uint64_t)lpc_order * (uint64_t)(sh.precision + sbps) + sh.cand_bits[1];
+                if (lpc_try) {
+                    const uint64_t b = 8ull + wasted + 9ull + (uint64_t)lpc_order * (uint64_t)(sh.precision + sbps) + sh.cand_bits[1];
                     if (b < best_bits) { best_bits = b; type = 3; order = lpc_order; cand = 1; }
                 }
             }
-
             // ---- K7a: winner's residuals (zig-zag folded), exact bit count per thread, block scan ----
-            const uint32_t sub_start = sh.bitpos;
+            const uint32_t sub_start = bitpos;
+            const uint32_t smask = sbps >= 32 ? 0xFFFFFFFFu : ((1u << sbps) - 1u);
             uint32_t u[FRX_SPT];
-            int po = 0;
+            int po = 0, psize = nsamp;
             uint32_t kk = 0;
-            int psize = nsamp;
             bool rice2 = false;
             uint32_t mybits = 0;
+            const int skip = (tid == 0) ? order : 0;
             if (type >= 2) {
                 po = sh.cand_po[cand];
                 psize = nsamp >> po;
                 kk = sh.kparam[cand][min(g0 / psize, (1 << po) - 1)];
                 rice2 = sh.cand_rice2[cand] != 0;
-                int32_t r[FRX_SPT];
-                if (type == 3) {
-                    if (lmode == 0) (void)lpc_residuals_dispatch<0, HISTN>(order, s, q, lshift, r);
-                    else if (WIDE) (void)lpc_residuals_dispatch<1, HISTN>(order, s, q, lshift, r);
-                } else {
+                if (type == 2) {
                     if (WIDE && !lean) (void)fixed_residuals<true, HISTN>(order, s, r);
                     else (void)fixed_residuals<false, HISTN>(order, s, r);
                 }
+                uint32_t qs = 0;
 #pragma unroll
                 for (int i = 0; i < FRX_SPT; i++) {
                     u[i] = zigzag(r[i]);
-                    if (i < nv && g0 + i >= order) mybits += (u[i] >> kk) + 1u + kk;
+                    qs += u[i] >> kk;
+                }
+                if (nv == FRX_SPT && tid != 0) mybits = qs + (uint32_t)FRX_SPT * (1u + kk);
+                else {
+#pragma unroll
+                    for (int i = 0; i < FRX_SPT; i++)
+                        if (i >= skip && i < nv) mybits += (u[i] >> kk) + 1u + kk;
                 }
                 if (tid < nthr && g0 % psize == 0) mybits += rice2 ? 5u : 4u;
                 if (tid == 0) {
                     mybits += 8u + (uint32_t)wasted + (uint32_t)order * (uint32_t)sbps + 6u;
                     if (type == 3) mybits += 9u + (uint32_t)order * (uint32_t)sh.precision;
-#pragma unroll
-                    for (int i = 0; i < HISTN; i++) sh.warm[i] = s[HISTN + i];
                 }
             } else if (type == 1) {
-                const uint32_t smask = sbps >= 32 ? 0xFFFFFFFFu : ((1u << sbps) - 1u);
-#pragma unroll
-                for (int i = 0; i < FRX_SPT; i++) u[i] = (uint32_t)s[HISTN + i] & smask;
                 mybits = (uint32_t)nv * (uint32_t)sbps;
                 if (tid == 0) mybits += 8u + (uint32_t)wasted;
             } else {
-                u[0] = (uint32_t)s[HISTN] & (sbps >= 32 ? 0xFFFFFFFFu : ((1u << sbps) - 1u));
                 if (tid == 0) mybits = 8u + (uint32_t)wasted + (uint32_t)sbps;
             }
             uint32_t incl = mybits;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
-                uint32_t n = __shfl_up_sync(FULLMASK, incl, o);
+                const uint32_t n = __shfl_up_sync(FULLMASK, incl, o);
                 if (lane >= o) incl += n;
             }
             if (lane == 31) sh.scan[warp] = incl;
-            __syncthreads();  // S10
+            compute_sync();  // SE
             uint32_t wbase = 0, total = 0;
 #pragma unroll
             for (int w2 = 0; w2 < NWARPS; w2++) {
-                uint32_t v = sh.scan[w2];
+                const uint32_t v = sh.scan[w2];
                 if (w2 < warp) wbase += v;
                 total += v;
             }
-            uint32_t start = sub_start + wbase + incl - mybits;
-            // Rice-coded size must beat verbatim, else redo the subframe as VERBATIM (keeps the frame inside its buffer)
-            if (type >= 2 && (uint64_t)total >= verb_bits) { force_verbatim = true; continue; }
-            if (tid == 0) sh.bitpos = sub_start + total;  // next read of bitpos is behind the next S2
-
+            if (type >= 2 && (uint64_t)total >= verb_bits) {
+                // the Rice-coded subframe would not beat VERBATIM: write it verbatim (keeps the frame inside its buffer)
+                type = 1;
+                mybits = (uint32_t)nv * (uint32_t)sbps;
+                if (tid == 0) mybits += 8u + (uint32_t)wasted;
+                incl = mybits;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t n = __shfl_up_sync(FULLMASK, incl, o);
+                    if (lane >= o) incl += n;
+                }
+                if (lane == 31) sh.scan2[warp] = incl;
+                compute_sync();
+                wbase = 0; total = 0;
+#pragma unroll
+                for (int w2 = 0; w2 < NWARPS; w2++) {
+                    const uint32_t v = sh.scan2[w2];
+                    if (w2 < warp) wbase += v;
+                    total += v;
+                }
+            }
+            const uint32_t start = sub_start + wbase + incl - mybits;
+            bitpos = sub_start + total;
+            if (ch == t.n_channels - 1 && tid == 0) {
+                // the frame's size is final: hand it to the control warp so the look-back overlaps packing and the CRC
+                sh.frame_bytes[slot] = ((bitpos + 7u) >> 3) + 2u;
+                mbar_arrive(&sh.sized[slot]);
+            }
             // ---- K7b: pack ----
             if (mybits) {
                 BitW bw;
                 bw.init(bits, start);
                 if (tid == 0) {
                     // subframe header: 0 | type(6) | wasted flag
-                    uint32_t tcode = type == 0 ? 0u : type == 1 ? 1u : type == 2 ? (8u | (uint32_t)order) : (32u | (uint32_t)(order - 1));
+                    const uint32_t tcode = type == 0 ? 0u : type == 1 ? 1u : type == 2 ? (8u | (uint32_t)order) : (32u | (uint32_t)(order - 1));
                     bw.put((tcode << 1) | (wasted ? 1u : 0u), 8);
                     if (wasted) { if (wasted > 1) bw.skip((uint32_t)wasted - 1u); bw.put(1u, 1); }
                 }
-                const uint32_t smask = sbps >= 32 ? 0xFFFFFFFFu : ((1u << sbps) - 1u);
                 if (type == 0) {
-                    if (tid == 0) bw.put(u[0], sbps);
+                    if (tid == 0) bw.put((uint32_t)s[HISTN] & smask, sbps);
                 } else if (type == 1) {
 #pragma unroll
                     for (int i = 0; i < FRX_SPT; i++)
-                        if (i < nv) bw.put(u[i], sbps);
+                        if (i < nv) bw.put((uint32_t)s[HISTN + i] & smask, sbps);
                 } else {
                     if (tid == 0) {
-                        for (int i = 0; i < order; i++) bw.put((uint32_t)sh.warm[i] & smask, sbps);
+                        for (int i = 0; i < order; i++) {
+                            // warm-up samples: a dynamic index into s[] would spill it, so select with compile-time indices
+                            int32_t wv = 0;
+#pragma unroll
+                            for (int k = 0; k < HISTN; k++) if (k == i) wv = s[HISTN + k];
+                            bw.put((uint32_t)wv & smask, sbps);
+                        }
                         if (type == 3) {
                             bw.put((uint32_t)(sh.precision - 1), 4);
                             bw.put((uint32_t)sh.shift & 31u, 5);
@@ -962,92 +1325,66 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS, 2) frx_encode_kernel(const En
                         bw.put(((rice2 ? 1u : 0u) << 4) | (uint32_t)po, 6);
                     }
                     if (g0 % psize == 0) bw.put(kk, rice2 ? 5 : 4);
-                    const uint32_t kmask = kk ? ((1u << kk) - 1u) : 0u;
-#pragma unroll
-                    for (int i = 0; i < FRX_SPT; i++) {
-                        if (i < nv && g0 + i >= order) {
-                            uint32_t uq = u[i] >> kk;
-                            uint32_t code = (1u << kk) | (u[i] & kmask);
-                            if (uq + 1u + kk <= 32u) bw.put(code, (int)(uq + 1u + kk));
-                            else { bw.skip(uq); bw.put(code, (int)(kk + 1u)); }
-                        }
-                    }
+                    pack_rice(bw, u, kk, skip, nv);
                 }
                 bw.finish();
             }
-            break;
-          }
         }  // channels
-        __syncthreads();  // Sa: every subframe is packed
+        compute_sync();  // Sa: every subframe is packed
 
-        // ---- frame footer: pad to byte, CRC-16 over the body (warps 6,7), byte offset by look-back (warp 0) ----
-        const uint32_t body_bytes = (sh.bitpos + 7u) >> 3;
+        // ---- frame footer: pad to byte, CRC-16 over the body (all compute threads, quads of words) ----
+        const uint32_t body_bytes = (bitpos + 7u) >> 3;
         const uint32_t nbytes = body_bytes + 2u;
-        if (warp >= NWARPS - 2) {
-            const int ct = tid - (FRX_ENC_THREADS - CRC_THREADS);   // 0..63
-            const uint32_t nw = body_bytes >> 2;                   // whole words
-            uint32_t per = (nw + CRC_THREADS - 1) / CRC_THREADS;
-            int lg = per <= 1 ? 0 : 32 - __clz((int)per - 1);      // Lw = 2^lg words per CRC thread
-            const uint32_t Lw = 1u << lg;
-            const int padw = (int)(CRC_THREADS * Lw) - (int)nw;    // virtual leading zero words
-            int w0 = ct * (int)Lw - padw, w1 = w0 + (int)Lw;
-            if (w0 < 0) w0 = 0;
+        {
+            const uint32_t nw = body_bytes >> 2;                       // whole words
+            const uint32_t nq = (nw + 3u) >> 2;                        // quads; the buffer is zero behind the frame
+            const uint32_t Lq = (nq + FRX_ENC_THREADS - 1) / FRX_ENC_THREADS;
+            const int padq = (int)(FRX_ENC_THREADS * Lq) - (int)nq;    // virtual leading zero quads
+            int q0 = tid * (int)Lq - padq;
+            const int q1 = q0 + (int)Lq;
+            if (q0 < 0) q0 = 0;
             uint32_t c = 0;
-            for (int wi = w0; wi < w1; wi++) {
-                uint32_t x = bits[wi] ^ (c << 16);
+            for (int qi = q0; qi < q1; qi++) {
+                uint4 wv = *reinterpret_cast<const uint4 *>(bits + 4 * qi);
+                if (qi == (int)nq - 1) {   // the word behind the last whole word holds the <= 3 tail bytes: not part of this pass
+                    const uint32_t k = nw - 4u * (uint32_t)qi;   // whole words in the last quad (1..4)
+                    if (k < 4u) wv.w = 0u;
+                    if (k < 3u) wv.z = 0u;
+                    if (k < 2u) wv.y = 0u;
+                }
+                uint32_t x = wv.x ^ (c << 16);
+                c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
+                x = wv.y ^ (c << 16);
+                c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
+                x = wv.z ^ (c << 16);
+                c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
+                x = wv.w ^ (c << 16);
                 c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
             }
-            if (c) c = frx_gf16_mulmod(c, (uint32_t)a.crc_xpow[lg * CRC_THREADS + (CRC_THREADS - 1 - ct)]);
+            if (c) c = frx_gf16_mulmod(c, (uint32_t)__ldg(&a.crc_xpow[(Lq - 1) * FRX_ENC_THREADS + (FRX_ENC_THREADS - 1 - tid)]));
             c = __reduce_xor_sync(FULLMASK, c);
-            if (lane == 0) sh.crc_part[warp - (NWARPS - 2)] = c;
-            if (ct == 0) sh.tailw = bits[nw];
+            if (lane == 0) sh.crc_part[warp] = c;
         }
-        // ---- K8: decoupled look-back for the byte offset (warp 0) ----
-        if (warp == 0) {
-            const uint64_t FLAG_A = 1ull << 62, FLAG_P = 2ull << 62, VMASK = (1ull << 62) - 1;
-            uint64_t exclusive = 0;
-            if (f == 0) {
-                if (lane == 0) frx_st_release_u64(&a.desc[0], FLAG_P | (uint64_t)nbytes);
-            } else {
-                if (lane == 0) frx_st_release_u64(&a.desc[f], FLAG_A | (uint64_t)nbytes);
-                long long pos = (long long)f - 1;
-                for (;;) {
-                    long long idx = pos - lane;
-                    uint64_t v = idx >= 0 ? frx_ld_acquire_u64(&a.desc[idx]) : FLAG_P;
-                    uint32_t flag = (uint32_t)(v >> 62);
-                    uint32_t notready = __ballot_sync(FULLMASK, flag == 0u);
-                    uint32_t isp = __ballot_sync(FULLMASK, flag == 2u);
-                    int firstp = isp ? (__ffs((int)isp) - 1) : 32;
-                    uint32_t need = firstp < 32 ? (firstp == 31 ? 0xFFFFFFFFu : ((2u << firstp) - 1u)) : 0xFFFFFFFFu;
-                    if (notready & need) { __nanosleep(40); continue; }
-                    uint64_t contrib = (lane <= firstp) ? (v & VMASK) : 0ull;
-                    exclusive += warp_sum_u64(contrib);
-                    if (firstp < 32) break;
-                    pos -= 32;
-                }
-                if (lane == 0) frx_st_release_u64(&a.desc[f], FLAG_P | (exclusive + (uint64_t)nbytes));
-            }
-            if (lane == 0) {
-                sh.out_offset = exclusive;
-                if (a.frame_size) a.frame_size[f] = nbytes;
-                if (a.frame_offset) a.frame_offset[f] = exclusive;
-                if (f == a.total_frames - 1 && a.total_bytes) *a.total_bytes = exclusive + nbytes;
-            }
-        }
-        __syncthreads();  // Sb
-        // ---- copy the frame to its final place ----
+        compute_sync();  // Sb
+        // ---- copy the frame to its final place (offset from the control warp's look-back) ----
+        mbar_wait(&sh.placed[slot], (fseq / FD_SLOTS) & 1u);
         {
-            const uint64_t off = sh.out_offset;
+            const uint64_t off = sh.out_offset[slot];
             if (off + nbytes > a.capacity) {
                 if (tid == 0) atomicExch(a.status, FRX_E_OVERFLOW);
             } else {
                 uint8_t *dst = a.bytes + off;
                 if (tid == FRX_ENC_THREADS - 1) {
-                    // finish the CRC over the <= 3 tail bytes and store it big-endian behind the body
-                    uint32_t c = sh.crc_part[0] ^ sh.crc_part[1];
-                    const uint32_t tw = sh.tailw;
+                    // undo the zero-word padding of the last quad, finish over the <= 3 tail bytes, store big-endian
+                    uint32_t c = 0;
+#pragma unroll
+                    for (int w2 = 0; w2 < NWARPS; w2++) c ^= sh.crc_part[w2];
+                    const uint32_t nw = body_bytes >> 2;
+                    const uint32_t z = ((nw + 3u) & ~3u) - nw;
+                    if (z && c) c = frx_gf16_mulmod(c, (uint32_t)a.crc_xinv[z]);
+                    const uint32_t tw = bits[nw];
                     for (uint32_t b = 0; b < (body_bytes & 3u); b++) {
-                        uint32_t byte = (tw >> (24 - 8 * b)) & 0xFFu;
+                        const uint32_t byte = (tw >> (24 - 8 * b)) & 0xFFu;
                         c = ((c << 8) ^ sh.crc_tab[0][((c >> 8) ^ byte) & 0xFFu]) & 0xFFFFu;
                     }
                     dst[body_bytes] = (uint8_t)(c >> 8);
@@ -1060,19 +1397,21 @@ __global__ void __launch_bounds__(FRX_ENC_THREADS, 2) frx_encode_kernel(const En
                 const uint32_t sh8 = head * 8u;
                 for (uint32_t j = tid; j < nwords; j += FRX_ENC_THREADS) {
                     // frame bytes [head+4j, head+4j+4): head < 4 so they straddle words j and j+1
-                    uint32_t w0 = bits[j], w1 = bits[j + 1];
-                    uint32_t v = head ? __funnelshift_l(w1, w0, sh8) : w0;
+                    const uint32_t w0 = bits[j], w1 = bits[j + 1];
+                    const uint32_t v = head ? __funnelshift_l(w1, w0, sh8) : w0;
                     dw[j] = frx_bswap32(v);
                 }
                 const uint32_t tail0 = head + (nwords << 2);
                 if (tid < (int)(body_bytes - tail0)) {
-                    uint32_t b = tail0 + (uint32_t)tid;
+                    const uint32_t b = tail0 + (uint32_t)tid;
                     dst[b] = (uint8_t)((bits[b >> 2] >> (24 - 8 * (b & 3))) & 0xFFu);
                 }
             }
         }
-        __syncthreads();  // Sz: all reads of the frame buffer done
+        compute_sync();  // Sz: all reads of the frame buffer done
         for (uint32_t j = tid; j <= (body_bytes >> 2); j += FRX_ENC_THREADS) bits[j] = 0u;
+        fseq++;
+        compute_sync();  // the next frame's header words go into a clean buffer
     }
 }
 
@@ -1106,7 +1445,7 @@ __global__ void frx_minmax_out_kernel(const FrxQuant *q, int dtype, double *mm) 
 // host launchers (called from frx_api.cu)
 // ------------------------------------------------------------------------------------------
 size_t frx_enc_smem_bytes(int frame_words) {
-    return ENC_SMALL_BYTES + ENC_UNION_BYTES + sizeof(uint32_t) * (size_t)frame_words;
+    return ENC_SMALL_BYTES + 2 * RAW_STRIDE + TABS_BYTES + sizeof(uint32_t) * (size_t)frame_words;
 }
 
 size_t frx_minmax_raw_size() { return sizeof(MinMaxRaw); }
@@ -1143,13 +1482,13 @@ static cudaError_t launch_encode_t(const EncArgs &a, int sm_count, cudaStream_t 
     e = cudaFuncSetAttribute(frx_encode_kernel<WIDE, HISTN>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e != cudaSuccess) return e;
     int occ = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, frx_encode_kernel<WIDE, HISTN>, FRX_ENC_THREADS, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, frx_encode_kernel<WIDE, HISTN>, FRX_ENC_CTA, smem);
     if (e != cudaSuccess) return e;
     if (occ < 1) return cudaErrorLaunchOutOfResources;
     long long grid = (long long)sm_count * occ;   // persistent: every CTA resident, tickets hand out the frames in order
     if (grid > (long long)a.total_frames) grid = a.total_frames;
     if (grid < 1) grid = 1;
-    frx_encode_kernel<WIDE, HISTN><<<(unsigned)grid, FRX_ENC_THREADS, smem, st>>>(a);
+    frx_encode_kernel<WIDE, HISTN><<<(unsigned)grid, FRX_ENC_CTA, smem, st>>>(a);
     return cudaGetLastError();
 }
 

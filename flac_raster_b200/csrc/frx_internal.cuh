@@ -2,6 +2,8 @@
 #pragma once
 #include "frx_common.cuh"
 
+#define FRX_CRC_MAXLQ 48   // CRC chunk tables cover frames up to 48 * 256 quads = 192 KB
+
 struct EncArgs {
     const void *raster;
     long long H, W, band_stride, row_stride;
@@ -9,7 +11,8 @@ struct EncArgs {
     const uint32_t *frame_prefix;
     const FrxQuant *quant;
     const float *window;
-    const uint16_t *crc_xpow;   // [11][64]: x^(32 * 2^lg * j) mod P, j = chunks that follow a CRC thread's chunk
+    const uint16_t *crc_xpow;   // [FRX_CRC_MAXLQ][256]: x^(128 * Lq * j) mod P, j = quad-chunks that follow a CRC thread's chunk of Lq quads
+    const uint16_t *crc_xinv;   // [4]: x^(-32 z) mod P, undoes z zero words appended to the last quad
     const uint16_t *crc_tab;    // [4][256] slicing-by-4 CRC-16 tables
     uint8_t *bytes;
     uint64_t capacity;
@@ -31,6 +34,7 @@ struct EncArgs {
     int qlp_precision;
     int frame_words;
     int dtype;
+    int tma_ok;                 // raster base and strides are 16-byte multiples: rows can be staged with TMA bulk copies
 };
 struct DecArgs {
     const uint8_t *bytes;
