@@ -275,7 +275,7 @@ int frx_encode_tiles(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *t
         c->window_len = L;
     }
     const uint64_t fb = frame_bytes_bound(prep.max_channels, prep.bps, p->blocksize);
-    const int frame_words = (int)((fb + 3) / 4) + 8;
+    const int frame_words = (((int)((fb + 3) / 4) + 8) + 3) & ~3;   // multiple of 4: the second frame buffer stays 16-byte aligned
     if (c->xpow_L != 2) {
         // CRC chunk combine tables (frx_encode.cu): x^(128 * Lq * j) mod P for Lq = 1..FRX_CRC_MAXLQ, j = 0..255; x^(-32 z), z = 0..3
         std::vector<uint16_t> xp(FRX_CRC_MAXLQ * 256 + 4);
@@ -328,7 +328,7 @@ int frx_encode_tiles(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *t
         const long long esz = frx_dtype_size(r.dtype);
         a.tma_ok = (((uintptr_t)r.data & 15u) == 0 && (r.band_stride * esz) % 16 == 0 && (r.row_stride * esz) % 16 == 0) ? 1 : 0;
     }
-    if (frx_enc_smem_bytes(frame_words) > 227 * 1024) return set_err(FRX_E_UNSUPPORTED, "frame buffer does not fit shared memory");
+    if (frx_enc_smem_bytes(frame_words, r.dtype) > 227 * 1024) return set_err(FRX_E_UNSUPPORTED, "frame buffer does not fit shared memory");
     CK(cudaEventRecord(c->ev[0], st));
     CK(frx_launch_encode(a, r.dtype, c->sm_count, st));
     CK(cudaEventRecord(c->ev[1], st));

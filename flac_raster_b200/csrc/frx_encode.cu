@@ -4,7 +4,7 @@
 //   K0  frx_minmax_kernel        per-stream min/max                      (converter.py:67-68, 152-153)
 //   K1..K8 frx_encode_kernel     one CTA per 4096-sample frame, persistent grid, ticket-ordered; 8 compute warps plus one
 //        control warp that takes tickets, stages the next raw samples with TMA bulk copies (mbarrier pipeline), builds the
-//        frame header and runs the look-back while the compute warps pack and checksum:
+//        frame header and runs the look-back while the compute warps search, pack and checksum:
 //        K1 tile cut + band->channel gather + PCM quantise            (converter.py:56-86, 185-194; cli.py:691-699)
 //        K2 fixed-order 0..4 trial            K3 windowed autocorrelation
 //        K4 Levinson-Durbin + order pick + coefficient quantisation    K5 residual
@@ -221,15 +221,38 @@ __device__ __forceinline__ uint32_t rice_param(uint32_t n, uint64_t s, uint32_t 
     return (uint32_t)k > kmax ? kmax : (uint32_t)k;
 }
 
+#ifdef FRX_DBG
+__device__ unsigned long long g_frx_dbg[16];
+#define DBG_ADD(i, v) atomicAdd(&g_frx_dbg[i], (unsigned long long)(v))
+#define DBG_CLK() clock64()
+#define DBG_PH(i) do { if (tid == 32 * DBG_PH_WARP) { const long long n_ = clock64(); atomicAdd(&g_frx_dbg[i], (unsigned long long)(n_ - dbg_ph)); dbg_ph = n_; } } while (0)
+#define DBG_PH_DECL long long dbg_ph = clock64()
+#ifndef DBG_PH_WARP
+#define DBG_PH_WARP 2
+#endif
+__device__ unsigned long long *g_frx_trace;   // 8 timestamps per frame
+__device__ __forceinline__ unsigned long long dbg_now() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define DBG_TRACE(f, k) do { if (g_frx_trace) g_frx_trace[(size_t)(f) * 8 + (k)] = dbg_now(); } while (0)
+#define DBG_TRACEV(f, k, v) do { if (g_frx_trace) g_frx_trace[(size_t)(f) * 8 + (k)] = (v); } while (0)
+#else
+#define DBG_ADD(i, v) do {} while (0)
+#define DBG_CLK() 0ll
+#define DBG_PH(i) do {} while (0)
+#define DBG_PH_DECL
+#define DBG_TRACE(f, k) do {} while (0)
+#define DBG_TRACEV(f, k, v) do {} while (0)
+#endif
 // ------------------------------------------------------------------------------------------
 // shared state of one encoder CTA
 // ------------------------------------------------------------------------------------------
 #define FD_SLOTS 4
 #define STOP_FRAME 0xFFFFFFFFu
-#define RAW_PAD 128                              // front pad: thread 0's history read stays inside the buffer
-#define RAW_STAGE_BYTES (FRX_MAX_BLOCK * 4)
-#define RAW_STRIDE (RAW_PAD + RAW_STAGE_BYTES)
 #define TABS_BYTES (6 * FRX_ENC_THREADS * 8)     // |e| sums per thread: fixed orders 0..4 + the LPC candidate
+// PCM of the current subframe in shared memory, padded so that a thread's 16-byte chunks at a 64-byte stride fall into
+// distinct bank groups: sample i lives at word PCM_IDX(i); 32 zero samples sit in front (history of the first thread).
+#define PCM_IDX(i) (((i) + 32) + 4 * (((i) + 32) >> 5))
+#define PCM_WORDS 4672
+#define PCM_BYTES (PCM_WORDS * 4)
 
 struct FrameDesc {                               // written by the control warp, read by the compute warps
     uint32_t f, fj, s0;
@@ -247,6 +270,7 @@ struct EncSmall {
     uint64_t sized[FD_SLOTS], placed[FD_SLOTS];  // frame size known -> look-back -> byte offset known
     FrameDesc fd[FD_SLOTS];
     uint32_t frame_bytes[FD_SLOTS];
+    uint32_t stage_stride;                       // bytes between the two raw stages (128 + 4096 * element size)
     uint64_t out_offset[FD_SLOTS];
     // per-subframe decisions
     int wasted, magbits, fixed_order, is_const, lean;
@@ -262,8 +286,9 @@ struct EncSmall {
     uint32_t wbad[NWARPS][2];
     float wac[NWARPS][FRX_MAX_LPC + 1];
     float autoc[FRX_MAX_LPC + 1];
+    float lpc_rows[FRX_MAX_LPC][FRX_MAX_LPC];    // predictor coefficients of every order (Levinson-Durbin by-product)
     uint32_t scan[NWARPS], scan2[NWARPS];
-    uint32_t crc_part[NWARPS];
+    uint32_t crc_part[2][NWARPS];                // per frame buffer
     uint16_t crc_tab[4][256];
 };
 #define ENC_SMALL_BYTES ((sizeof(EncSmall) + 127) & ~(size_t)127)
@@ -284,6 +309,13 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *b, uint32_t byte
 __device__ __forceinline__ bool mbar_try_wait(uint64_t *b, uint32_t parity) {
     uint32_t ok;
     asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
+    return ok != 0;
+}
+// non-blocking probe: try_wait may park the thread for a system-defined time, which a loop polling two barriers cannot afford
+__device__ __forceinline__ bool mbar_test(uint64_t *b, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                  : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
     return ok != 0;
 }
@@ -353,22 +385,15 @@ __device__ __noinline__ void analyse_partitions(EncSmall &sh, const uint64_t *ta
 }
 
 // ------------------------------------------------------------------------------------------
-// K1: raw staging buffer -> registers -> PCM.  Thread t owns samples [16t, 16t+16) and reads HISTN samples of
-// history in front of them, with the widest aligned shared-memory loads the byte offsets allow.
+// K1: raw staging buffer -> PCM in shared memory.  Thread t owns samples [16t, 16t+16).
 // ------------------------------------------------------------------------------------------
-template <int NWORDS, int ALIGNB>
-__device__ __forceinline__ void lds_words(const unsigned char *p, uint32_t *w) {
-    if (ALIGNB == 16) {
+template <int NWORDS>
+__device__ __forceinline__ void lds_words16(const unsigned char *p, uint32_t *w) {   // p is 16-byte aligned (or 8/4 for short rows)
+    if (NWORDS % 4 == 0) {
 #pragma unroll
         for (int k = 0; k < NWORDS / 4; k++) {
-            uint4 v = *reinterpret_cast<const uint4 *>(p + 16 * k);
+            const uint4 v = *reinterpret_cast<const uint4 *>(p + 16 * k);
             w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
-        }
-    } else if (ALIGNB == 8) {
-#pragma unroll
-        for (int k = 0; k < NWORDS / 2; k++) {
-            uint2 v = *reinterpret_cast<const uint2 *>(p + 8 * k);
-            w[2 * k] = v.x; w[2 * k + 1] = v.y;
         }
     } else {
 #pragma unroll
@@ -388,32 +413,67 @@ __device__ __forceinline__ typename FrxElem<DT>::T elem_of(const uint32_t *w, in
     }
 }
 
-template <int DT, int HISTN>
-__device__ __forceinline__ void load_samples(const unsigned char *stage, const FrxQuant &qz, int mode, int tid, int32_t *s) {
+// the thread's 16 raw elements -> 16 PCM samples (registers)
+template <int DT>
+__device__ __forceinline__ void quantize_own(const unsigned char *stage, const FrxQuant &qz, int mode, int tid, int32_t *x) {
     typedef typename FrxElem<DT>::T T;
     constexpr int ESZ = (int)sizeof(T);
-    constexpr int HB = HISTN * ESZ;                          // history bytes (multiple of 4)
-    constexpr int HALIGN = (HB % 16 == 0) ? 16 : ((HB % 8 == 0) ? 8 : 4);
-    constexpr int HW = HB / 4, OW = 16 * ESZ / 4;
-    uint32_t w[HW + OW];
-    const unsigned char *p = stage + (size_t)(16 * tid) * ESZ;
-    lds_words<HW, HALIGN>(p - HB, w);
-    lds_words<OW, (ESZ == 1 ? 16 : 16)>(p, w + HW);
+    constexpr int OW = FRX_SPT * ESZ / 4;
+    uint32_t w[OW];
+    lds_words16<OW>(stage + (size_t)(FRX_SPT * tid) * ESZ, w);
     if (mode == FRX_PCM_REFERENCE) {
 #pragma unroll
-        for (int i = 0; i < HISTN + FRX_SPT; i++) s[i] = frx_quant_ref<DT>(elem_of<DT>(w, i), qz);
+        for (int i = 0; i < FRX_SPT; i++) x[i] = frx_quant_ref<DT>(elem_of<DT>(w, i), qz);
     } else if (mode == FRX_PCM_LOSSLESS) {
 #pragma unroll
-        for (int i = 0; i < HISTN + FRX_SPT; i++) s[i] = frx_quant_lossless<DT>(elem_of<DT>(w, i));
+        for (int i = 0; i < FRX_SPT; i++) x[i] = frx_quant_lossless<DT>(elem_of<DT>(w, i));
     } else {
 #pragma unroll
-        for (int i = 0; i < HISTN + FRX_SPT; i++) s[i] = frx_quant_spatial<DT>(elem_of<DT>(w, i));
+        for (int i = 0; i < FRX_SPT; i++) x[i] = frx_quant_spatial<DT>(elem_of<DT>(w, i));
+    }
+}
+// K1 for one thread: quantise, zero what lies behind a short frame, store to the padded PCM buffer;
+// returns (OR of the samples, OR of their magnitudes) for the wasted-bits / magnitude decisions
+template <int DT, bool WIDE>
+__device__ __forceinline__ uint2 k1_quantize(const unsigned char *stage, const FrxQuant &qz, int mode, int tid, int nv, int32_t *pcm) {
+    int32_t x[FRX_SPT];
+    quantize_own<DT>(stage, qz, mode, tid, x);
+    uint32_t orv = 0, ora = 0;
+#pragma unroll
+    for (int i = 0; i < FRX_SPT; i++) {
+        if (i >= nv) x[i] = 0;
+        orv |= (uint32_t)x[i];
+        if (WIDE) ora |= (uint32_t)(x[i] ^ (x[i] >> 31));
+    }
+#pragma unroll
+    for (int k = 0; k < FRX_SPT / 4; k++)
+        *reinterpret_cast<int4 *>(pcm + PCM_IDX(FRX_SPT * tid + 4 * k)) = make_int4(x[4 * k], x[4 * k + 1], x[4 * k + 2], x[4 * k + 3]);
+    return make_uint2(orv, ora);
+}
+template <bool WIDE>
+__device__ __noinline__ uint2 k1_quantize_any(int dtype, const unsigned char *stage, const FrxQuant &qz, int mode, int tid, int nv, int32_t *pcm) {
+    switch (dtype) {   // the dtypes the benchmarks do not use share one out-of-line copy
+        case FRX_U8: return k1_quantize<FRX_U8, WIDE>(stage, qz, mode, tid, nv, pcm);
+        case FRX_I16: return k1_quantize<FRX_I16, WIDE>(stage, qz, mode, tid, nv, pcm);
+        case FRX_I32: return k1_quantize<FRX_I32, WIDE>(stage, qz, mode, tid, nv, pcm);
+        default: return k1_quantize<FRX_U32, WIDE>(stage, qz, mode, tid, nv, pcm);
+    }
+}
+
+// PCM shared memory -> registers: HISTN samples of history + the thread's 16 samples, arithmetic shift by `sh`
+template <int HISTN>
+__device__ __forceinline__ void read_pcm(const int32_t *pcm, int tid, int sh, int32_t *s) {
+    const int base = FRX_SPT * tid - HISTN;   // multiple of 4
+#pragma unroll
+    for (int k = 0; k < (HISTN + FRX_SPT) / 4; k++) {
+        const int4 v = *reinterpret_cast<const int4 *>(pcm + PCM_IDX(base + 4 * k));
+        s[4 * k] = v.x >> sh; s[4 * k + 1] = v.y >> sh; s[4 * k + 2] = v.z >> sh; s[4 * k + 3] = v.w >> sh;
     }
 }
 
 // generic gather (edge tiles whose rows are not 16-byte multiples): coalesced element loads into the raw stage
 template <int DT>
-__device__ __forceinline__ void gather_raw(const EncArgs &a, const frx_tile &t, int ch, uint32_t s0, int nsamp, unsigned char *stage, int tid) {
+__device__ __forceinline__ void gather_raw_t(const EncArgs &a, const frx_tile &t, int ch, uint32_t s0, int nsamp, unsigned char *stage, int tid) {
     typedef typename FrxElem<DT>::T T;
     const T *band = (const T *)a.raster + (long long)(t.first_band + ch) * a.band_stride + (long long)t.row_off * a.row_stride + t.col_off;
     T *dst = reinterpret_cast<T *>(stage);
@@ -423,7 +483,14 @@ __device__ __forceinline__ void gather_raw(const EncArgs &a, const frx_tile &t, 
     for (int i = tid; i < nsamp; i += FRX_ENC_THREADS) {
         dst[i] = __ldg(band + (long long)row * a.row_stride + col);
         col += FRX_ENC_THREADS;
-        if (col >= w) { uint32_t q = col / w; row += q; col -= q * w; }
+        if (col >= w) { const uint32_t q = col / w; row += q; col -= q * w; }
+    }
+}
+__device__ __noinline__ void gather_raw(const EncArgs &a, const frx_tile &t, int ch, uint32_t s0, int nsamp, unsigned char *stage, int tid) {
+    switch (frx_dtype_size(a.dtype)) {   // a pure move: only the element size matters
+        case 1: gather_raw_t<FRX_U8>(a, t, ch, s0, nsamp, stage, tid); break;
+        case 2: gather_raw_t<FRX_U16>(a, t, ch, s0, nsamp, stage, tid); break;
+        default: gather_raw_t<FRX_U32>(a, t, ch, s0, nsamp, stage, tid); break;
     }
 }
 
@@ -461,153 +528,207 @@ __device__ __forceinline__ int frame_header_bytes(uint8_t *hb, int nsamp, int sr
     return n;
 }
 
-// lane 0 of the control warp: everything the compute warps need to know about frame f
-__device__ __noinline__ void build_frame_desc(const EncArgs &a, FrameDesc &d, uint32_t f, int &ti) {
-    // tickets grow monotonically inside a CTA: walk forward from the cached tile, fall back to bisection for long jumps
-    int steps = 0;
-    while (f >= __ldg(&a.frame_prefix[ti + 1])) {
-        ti++;
-        if (++steps == 8) {
-            int lo = ti, hi = a.n_tiles;
+// control warp: everything the compute warps need to know about frame f.  The lanes probe 32 tile boundaries at once
+// and fetch the tile and its quantiser words side by side, so the whole descriptor costs two memory round trips.
+__device__ __noinline__ void build_frame_desc(const EncArgs &a, FrameDesc &d, uint32_t f, int &ti, int lane) {
+    {
+        const int cand = ti + 1 + lane;
+        const uint32_t pv = cand <= a.n_tiles ? __ldg(&a.frame_prefix[cand]) : 0xFFFFFFFFu;
+        const uint32_t m = __ballot_sync(FULLMASK, f < pv);
+        if (m) ti += __ffs((int)m) - 1;
+        else {   // long jump: bisection (frame_prefix[n_tiles] = total frames > f)
+            int lo = ti + 32, hi = a.n_tiles;
             while (hi - lo > 1) {
-                int mid = (lo + hi) >> 1;
+                const int mid = (lo + hi) >> 1;
                 if (__ldg(&a.frame_prefix[mid]) <= f) lo = mid; else hi = mid;
             }
             ti = lo;
-            break;
         }
     }
-    const frx_tile t = a.tiles[ti];
-    const uint32_t fj = f - __ldg(&a.frame_prefix[ti]);
-    const long long tile_n = (long long)t.h * t.w;
-    const uint32_t s0 = fj * (uint32_t)a.blocksize;
-    const int nsamp = (int)min((long long)a.blocksize, tile_n - (long long)s0);
-    d.f = f; d.fj = fj; d.s0 = s0; d.nsamp = nsamp; d.t = t; d.tile_idx = ti;
-    d.q = a.quant[ti];
-    const int epv = 16 / frx_dtype_size(a.dtype);            // elements per 16 bytes
-    d.tma = (a.tma_ok && (t.w % epv) == 0 && (t.col_off % epv) == 0) ? 1 : 0;
-    uint8_t hb[16];
-    const int n = frame_header_bytes(hb, nsamp, a.sr_code, a.sample_rate, t.n_channels, a.bps, fj);
+    constexpr int TW = (int)(sizeof(frx_tile) / 4), QW = (int)(sizeof(FrxQuant) / 4);
+    static_assert(TW + QW < 31, "descriptor words must fit one warp");
+    uint32_t wv = 0;
+    if (lane < TW) wv = __ldg(reinterpret_cast<const uint32_t *>(a.tiles + ti) + lane);
+    else if (lane < TW + QW) wv = __ldg(reinterpret_cast<const uint32_t *>(a.quant + ti) + (lane - TW));
+    else if (lane == 31) wv = __ldg(&a.frame_prefix[ti]);
+    if (lane < TW) reinterpret_cast<uint32_t *>(&d.t)[lane] = wv;
+    else if (lane < TW + QW) reinterpret_cast<uint32_t *>(&d.q)[lane - TW] = wv;
+    const uint32_t fj = f - __shfl_sync(FULLMASK, wv, 31);
+    __syncwarp();
+    if (lane == 0) {
+        const frx_tile t = d.t;
+        const long long tile_n = (long long)t.h * t.w;
+        const uint32_t s0 = fj * (uint32_t)a.blocksize;
+        const int nsamp = (int)min((long long)a.blocksize, tile_n - (long long)s0);
+        d.f = f; d.fj = fj; d.s0 = s0; d.nsamp = nsamp; d.tile_idx = ti;
+        const int epv = 16 / frx_dtype_size(a.dtype);            // elements per 16 bytes
+        d.tma = (a.tma_ok && (t.w % epv) == 0 && (t.col_off % epv) == 0) ? 1 : 0;
+        uint8_t hb[16];
+        const int n = frame_header_bytes(hb, nsamp, a.sr_code, a.sample_rate, t.n_channels, a.bps, fj);
 #pragma unroll
-    for (int wv = 0; wv < 4; wv++)
-        d.hdr[wv] = ((uint32_t)hb[4 * wv] << 24) | ((uint32_t)hb[4 * wv + 1] << 16) | ((uint32_t)hb[4 * wv + 2] << 8) | hb[4 * wv + 3];
-    d.hdr_bits = (uint32_t)n * 8u;
+        for (int k = 0; k < 4; k++)
+            d.hdr[k] = ((uint32_t)hb[4 * k] << 24) | ((uint32_t)hb[4 * k + 1] << 16) | ((uint32_t)hb[4 * k + 2] << 8) | hb[4 * k + 3];
+        d.hdr_bits = (uint32_t)n * 8u;
+    }
+    __syncwarp();
 }
 
-// K8: decoupled look-back over the frame sizes (whole control warp; 128 descriptors per round trip)
-__device__ __forceinline__ uint64_t lookback(const EncArgs &a, uint32_t f, uint32_t nbytes, int lane) {
-    const uint64_t FLAG_A = 1ull << 62, FLAG_P = 2ull << 62, VMASK = (1ull << 62) - 1;
-    uint64_t exclusive = 0;
-    if (f == 0) {
-        if (lane == 0) frx_st_release_u64(&a.desc[0], FLAG_P | (uint64_t)nbytes);
-        return 0;
+// K8: decoupled look-back over the frame sizes (whole control warp).  A descriptor word carries flag and value
+// together (A: the frame's size, P: the inclusive byte prefix), so relaxed device-scope accesses are enough.  The compute
+// warps publish A themselves as soon as the size is final; here 512 descriptors are examined per round trip (16
+// consecutive ones per lane, nearest first).  When the walk meets a frame that has not published yet, only that single
+// word is polled -- re-reading the window would hammer the L2 slice the publishers store to -- and the walk is resumable,
+// so the control warp keeps feeding the raw-sample pipeline while it waits.
+#define LB_PER_LANE 16
+struct LookBack {
+    long long pos;        // nearest descriptor not yet accounted for
+    uint64_t exclusive;   // bytes summed so far
+    bool blocked;         // desc[pos] had not been published at the last visit
+};
+// one step; true when the exclusive prefix is complete
+__device__ __noinline__ bool lookback_step(const EncArgs &a, LookBack &lb, int lane) {
+    const uint64_t FLAG_P = 2ull << 62, VMASK = (1ull << 62) - 1;
+    if (lb.pos < 0) return true;
+    if (lb.blocked) {
+        uint64_t w = 0;
+        if (lane == 0) w = frx_ld_relaxed_u64(&a.desc[lb.pos]);
+        w = __shfl_sync(FULLMASK, w, 0);
+        if ((w >> 62) == 0ull) return false;
+        lb.blocked = false;
     }
-    if (lane == 0) frx_st_release_u64(&a.desc[f], FLAG_A | (uint64_t)nbytes);
-    long long pos = (long long)f - 1;
-    for (;;) {
-        uint64_t v[4];
+    if (lane == 0) DBG_ADD(3, 1);
+    uint64_t v[LB_PER_LANE];
+    const long long base = lb.pos - (long long)lane * LB_PER_LANE;
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const long long idx = pos - 32 * k - lane;
-            v[k] = idx >= 0 ? frx_ld_acquire_u64(&a.desc[idx]) : FLAG_P;
-        }
-        bool done = false, retry = false;
+    for (int k = 0; k < LB_PER_LANE; k++) {
+        const long long idx = base - k;
+        v[k] = idx >= 0 ? frx_ld_relaxed_u64(&a.desc[idx]) : FLAG_P;
+    }
+    // per lane: walk its 16 entries nearest-first up to the first inclusive prefix (P) or the first one not ready
+    uint64_t sum = 0;
+    int state = 0;                     // 0: all 16 ready, no P   1: stopped at a P   2: stopped at a not-ready entry
+    int taken = 0;
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            if (done || retry) continue;
+    for (int k = 0; k < LB_PER_LANE; k++) {
+        if (state == 0) {
             const uint32_t flag = (uint32_t)(v[k] >> 62);
-            const uint32_t notready = __ballot_sync(FULLMASK, flag == 0u);
-            const uint32_t isp = __ballot_sync(FULLMASK, flag == 2u);
-            const int firstp = isp ? (__ffs((int)isp) - 1) : 32;
-            const uint32_t need = firstp >= 31 ? 0xFFFFFFFFu : ((2u << firstp) - 1u);
-            if (notready & need) { retry = true; continue; }   // restart from `pos` (already-summed windows were consumed)
-            const uint64_t contrib = (lane <= firstp) ? (v[k] & VMASK) : 0ull;
-            exclusive += warp_sum_u64(contrib);
-            if (firstp < 32) done = true; else pos -= 32;
+            if (flag == 0u) state = 2;
+            else { sum += v[k] & VMASK; taken++; if (flag == 2u) state = 1; }
         }
-        if (done) break;
-        if (retry) __nanosleep(20);
     }
-    if (lane == 0) frx_st_release_u64(&a.desc[f], FLAG_P | (exclusive + (uint64_t)nbytes));
-    return exclusive;
+    const uint32_t mP = __ballot_sync(FULLMASK, state == 1), mN = __ballot_sync(FULLMASK, state == 2);
+    const int firstP = mP ? (__ffs((int)mP) - 1) : 32, firstN = mN ? (__ffs((int)mN) - 1) : 32;
+    // lanes before the first stopper contribute everything; the stopper contributes what it took
+    const int stop = min(firstP, firstN);
+    lb.exclusive += warp_sum_u64((lane <= stop) ? sum : 0ull);
+    if (firstP < firstN) return true;  // reached an inclusive prefix
+    if (firstN < 32) {
+        const int tk = __shfl_sync(FULLMASK, taken, firstN);
+        lb.pos -= (long long)firstN * LB_PER_LANE + tk;      // the frame that has not published its size yet
+        lb.blocked = true;
+        if (lane == 0) DBG_ADD(4, 1);
+    } else lb.pos -= 32 * LB_PER_LANE;
+    return false;
 }
 
+// The control warp's event loop.  A CTA works on one frame and has at most the next one staged; the next ticket is
+// taken only when the current frame's size has been published, because a ticket that is reserved but not yet sized
+// holds up the look-back of every later frame (and convoys of such tickets serialise the whole grid).
 __device__ __noinline__ void control_warp(const EncArgs &a, EncSmall &sh, unsigned char *raw, int lane) {
     const int esz = frx_dtype_size(a.dtype);
-    uint32_t ticket_next = 0;
-    if (lane == 0) ticket_next = atomicAdd(a.ticket, 1u);
-    ticket_next = __shfl_sync(FULLMASK, ticket_next, 0);
     uint32_t unit_iss = 0, fseq_iss = 0, fseq_lb = 0;
     int ch_iss = 0, nch_cur = 0, ti = 0;
-    bool have_frame = false, stop_issued = false;
+    bool have_frame = false, want_frame = true, stop_issued = false, lb_active = false;
+    LookBack lb;
+    lb.pos = -1; lb.exclusive = 0; lb.blocked = false;
     for (;;) {
-        // ---- 1. frames whose size is known: look-back, publish the byte offset ----
-        if (fseq_lb < fseq_iss + (have_frame ? 1u : 0u)) {
+        bool progress = false;
+        // ---- 1. a frame's size became known: get the next frame going, then start this frame's look-back ----
+        if (!lb_active && fseq_lb < fseq_iss) {
             const int slot = (int)(fseq_lb & (FD_SLOTS - 1));
-            if (mbar_try_wait(&sh.sized[slot], (fseq_lb / FD_SLOTS) & 1u)) {
-                const uint32_t f = sh.fd[slot].f;
-                const uint32_t nbytes = sh.frame_bytes[slot];
-                const uint64_t off = lookback(a, f, nbytes, lane);
+            if (mbar_test(&sh.sized[slot], (fseq_lb / FD_SLOTS) & 1u)) {
+                if (!stop_issued) want_frame = true;
+                lb.pos = (long long)sh.fd[slot].f - 1;
+                lb.exclusive = 0; lb.blocked = false;
+                lb_active = true;
+                if (lane == 0) DBG_TRACE(sh.fd[slot].f, 2);
+                progress = true;
+            }
+        }
+        // ---- 2. next unit (frame, channel) into the raw stage ring ----
+        if (have_frame || want_frame) {
+            const int stage = (int)(unit_iss & 1u);
+            if (mbar_test(&sh.empty[stage], ((unit_iss >> 1) & 1u) ^ 1u)) {
+                progress = true;
+                if (!have_frame) {
+                    const int slot = (int)(fseq_iss & (FD_SLOTS - 1));
+                    uint32_t ticket = 0;
+                    if (lane == 0) ticket = atomicAdd(a.ticket, 1u);
+                    ticket = __shfl_sync(FULLMASK, ticket, 0);
+                    want_frame = false;
+                    if (ticket >= a.total_frames) {
+                        if (lane == 0) { sh.fd[slot].f = STOP_FRAME; mbar_arrive(&sh.full[stage]); }
+                        __syncwarp();
+                        stop_issued = true;
+                    } else {
+                        build_frame_desc(a, sh.fd[slot], ticket, ti, lane);
+                        if (lane == 0) { DBG_TRACE(ticket, 0); DBG_TRACEV(ticket, 6, blockIdx.x); }
+                        nch_cur = sh.fd[slot].t.n_channels;
+                        have_frame = true;
+                        ch_iss = 0;
+                    }
+                }
+                if (have_frame) {
+                    const FrameDesc &d = sh.fd[fseq_iss & (FD_SLOTS - 1)];
+                    unsigned char *dst = raw + (size_t)stage * sh.stage_stride;
+                    if (d.tma) {
+                        const long long w = d.t.w;
+                        const long long s0 = d.s0, s1 = s0 + d.nsamp;
+                        const long long row0 = s0 / w, row1 = (s1 - 1) / w;
+                        const unsigned char *band = (const unsigned char *)a.raster +
+                            ((long long)(d.t.first_band + ch_iss) * a.band_stride + (long long)d.t.row_off * a.row_stride + d.t.col_off) * esz;
+                        if (lane == 0) mbar_arrive_expect_tx(&sh.full[stage], (uint32_t)d.nsamp * (uint32_t)esz);
+                        __syncwarp();
+                        for (long long r = row0 + lane; r <= row1; r += 32) {
+                            const long long b0 = max(s0, r * w), b1 = min(s1, (r + 1) * w);
+                            bulk_g2s(dst + (b0 - s0) * esz, band + (r * a.row_stride + (b0 - r * w)) * esz, (uint32_t)((b1 - b0) * esz), &sh.full[stage]);
+                        }
+                    } else if (lane == 0) {
+                        mbar_arrive(&sh.full[stage]);
+                    }
+                    __syncwarp();
+                    unit_iss++;
+                    if (++ch_iss == nch_cur) { have_frame = false; fseq_iss++; }
+                }
+            }
+        }
+        // ---- 3. the look-back in flight ----
+        if (lb_active) {
+            if (lookback_step(a, lb, lane)) {
+                const int slot = (int)(fseq_lb & (FD_SLOTS - 1));
                 if (lane == 0) {
+                    const uint32_t f = sh.fd[slot].f;
+                    const uint32_t nbytes = sh.frame_bytes[slot];
+                    const uint64_t off = lb.exclusive;
+                    frx_st_relaxed_u64(&a.desc[f], (2ull << 62) | (off + (uint64_t)nbytes));
                     sh.out_offset[slot] = off;
                     if (a.frame_size) a.frame_size[f] = nbytes;
                     if (a.frame_offset) a.frame_offset[f] = off;
                     if (f == a.total_frames - 1 && a.total_bytes) *a.total_bytes = off + nbytes;
+                    DBG_TRACE(f, 3);
+                    DBG_ADD(6, 1);
                     mbar_arrive(&sh.placed[slot]);
                 }
                 __syncwarp();
+                lb_active = false;
                 fseq_lb++;
-                continue;
-            }
+                progress = true;
+            } else if (!lb.blocked) progress = true;
         }
-        if (stop_issued) {
-            if (fseq_lb == fseq_iss) break;
-            continue;
-        }
-        // ---- 2. next unit (frame, channel) into the raw stage ring ----
-        const int stage = (int)(unit_iss & 1u);
-        if (!mbar_try_wait(&sh.empty[stage], ((unit_iss >> 1) & 1u) ^ 1u)) continue;
-        if (!have_frame) {
-            const int slot = (int)(fseq_iss & (FD_SLOTS - 1));
-            if (ticket_next >= a.total_frames) {
-                if (lane == 0) { sh.fd[slot].f = STOP_FRAME; mbar_arrive(&sh.full[stage]); }
-                __syncwarp();
-                stop_issued = true;
-                continue;
-            }
-            if (lane == 0) build_frame_desc(a, sh.fd[slot], ticket_next, ti);
-            __syncwarp();
-            nch_cur = sh.fd[slot].t.n_channels;
-            if (lane == 0) ticket_next = atomicAdd(a.ticket, 1u);
-            ticket_next = __shfl_sync(FULLMASK, ticket_next, 0);
-            have_frame = true;
-            ch_iss = 0;
-        }
-        {
-            const FrameDesc &d = sh.fd[fseq_iss & (FD_SLOTS - 1)];
-            unsigned char *dst = raw + (size_t)stage * RAW_STRIDE + RAW_PAD;
-            if (d.tma) {
-                const long long w = d.t.w;
-                const long long s0 = d.s0, s1 = s0 + d.nsamp;
-                const long long row0 = s0 / w, row1 = (s1 - 1) / w;
-                const unsigned char *band = (const unsigned char *)a.raster +
-                    ((long long)(d.t.first_band + ch_iss) * a.band_stride + (long long)d.t.row_off * a.row_stride + d.t.col_off) * esz;
-                if (lane == 0) mbar_arrive_expect_tx(&sh.full[stage], (uint32_t)d.nsamp * (uint32_t)esz);
-                __syncwarp();
-                for (long long r = row0 + lane; r <= row1; r += 32) {
-                    const long long b0 = max(s0, r * w), b1 = min(s1, (r + 1) * w);
-                    bulk_g2s(dst + (b0 - s0) * esz, band + (r * a.row_stride + (b0 - r * w)) * esz, (uint32_t)((b1 - b0) * esz), &sh.full[stage]);
-                }
-            } else if (lane == 0) {
-                mbar_arrive(&sh.full[stage]);
-            }
-            __syncwarp();
-            unit_iss++;
-            if (++ch_iss == nch_cur) { have_frame = false; fseq_iss++; }
-        }
+        if (stop_issued && !lb_active && fseq_lb == fseq_iss) break;
+        if (!progress) __nanosleep(64);
     }
 }
-
 // residual of one sample, lean paths (no overflow possible by construction)
 template <int ORD>
 __device__ __forceinline__ int32_t lpc_res32(const int32_t *s, int i, const int32_t *q, int shift) {
@@ -721,24 +842,36 @@ __device__ __forceinline__ void fixed_trial32(const int32_t *s, uint32_t *fa) {
     }
     fa[0] = f0; fa[1] = f1; fa[2] = f2; fa[3] = f3; fa[4] = f4;
 }
-// the terms of thread 0 that lie in the warm-up region (sample index < order), computed exactly like the loop above does
-// with a zero history; subtracting them leaves sum |e_k| over samples k..n-1
+// masked form for thread 0 (warm-up samples do not count: sample g contributes to order k only when g >= k) and for
+// the partial thread of a short frame
 template <int HISTN>
-__device__ __forceinline__ void fixed_trial32_warmup(const int32_t *s, uint32_t *sub) {
-    const int32_t x0 = s[HISTN], x1 = s[HISTN + 1], x2 = s[HISTN + 2], x3 = s[HISTN + 3];
-    const int32_t a1 = x0, b1 = x1 - x0, c1 = x2 - x1, e1 = x3 - x2;      // d1[0..3]
-    const int32_t a2 = a1, b2 = b1 - a1, c2 = c1 - b1, e2 = e1 - c1;      // d2[0..3]
-    const int32_t a3 = a2, b3 = b2 - a2, c3 = c2 - b2;                    // d3[0..2]
-    const int32_t a4 = a3, b4 = b3 - a3, c4 = c3 - b3, e3 = e2 - c2, e4 = e3 - c3;  // d4[0..3]
-    sub[0] = 0;
-    sub[1] = (uint32_t)abs(a1);
-    sub[2] = (uint32_t)abs(a2) + (uint32_t)abs(b2);
-    sub[3] = (uint32_t)abs(a3) + (uint32_t)abs(b3) + (uint32_t)abs(c3);
-    sub[4] = (uint32_t)abs(a4) + (uint32_t)abs(b4) + (uint32_t)abs(c4) + (uint32_t)abs(e4);
+__device__ __forceinline__ void fixed_trial32_masked(const int32_t *s, int g0, int nv, uint32_t *fa) {
+    int32_t dm1 = s[HISTN - 1] - s[HISTN - 2], dm2 = s[HISTN - 2] - s[HISTN - 3], dm3 = s[HISTN - 3] - s[HISTN - 4];
+    int32_t d1p = dm1, d2p = dm1 - dm2, d3p = (dm1 - dm2) - (dm2 - dm3);
+#pragma unroll
+    for (int o = 0; o < 5; o++) fa[o] = 0;
+#pragma unroll
+    for (int i = 0; i < FRX_SPT; i++) {
+        const int32_t x = s[HISTN + i];
+        const int32_t d1 = x - s[HISTN + i - 1];
+        const int32_t d2 = d1 - d1p, d3 = d2 - d2p, d4 = d3 - d3p;
+        d1p = d1; d2p = d2; d3p = d3;
+        if (i < nv) {
+            const int g = g0 + i;
+            fa[0] += (uint32_t)abs(x);
+            if (g >= 1) fa[1] += (uint32_t)abs(d1);
+            if (g >= 2) fa[2] += (uint32_t)abs(d2);
+            if (g >= 3) fa[3] += (uint32_t)abs(d3);
+            if (g >= 4) fa[4] += (uint32_t)abs(d4);
+        }
+    }
 }
 
-// tukey(0.5) window value of sample g in a block of n samples (libFLAC's definition; short frames only)
-__device__ __forceinline__ float tukey_half(int g, int n) {
+// tukey(0.5) window value of sample g in a short frame of n samples (libFLAC's definition).  Out of line on purpose:
+// scalars in, scalar out, so the compiler cannot speculate the cosine into the full-frame path (which reads a table)
+// and no register array escapes into the call.
+__device__ __noinline__ float tukey_w(int g, int n) {
+    if (g < 0 || g >= n) return 0.f;
     const int Np = (int)(0.25f * (float)n) - 1;
     if (Np <= 0) return 1.0f;
     if (g <= Np) return 0.5f - 0.5f * cospif((float)g / (float)Np);
@@ -746,45 +879,54 @@ __device__ __forceinline__ float tukey_half(int g, int n) {
     return 1.0f;
 }
 
-// K4 on one thread, float32: Levinson-Durbin, expected-bits order pick, coefficient quantisation (libFLAC's scheme with
-// error feedback).  The decisions are ours; the bitstream stays exact because the residual is computed from the
-// quantised integers.
-template <bool WIDE>
-__device__ __noinline__ void lpc_design(EncSmall &sh, const float *autoc, int max_lpc, int nsamp, int wasted, int sbps, int qlp_precision,
-                                        int magbits, bool lean) {
+// K4 on one thread, float32, everything in registers (MAXO = largest order of the compression level):
+// Levinson-Durbin, expected-bits order pick, coefficient quantisation (libFLAC's scheme with error feedback).
+// The decisions are ours; the bitstream stays exact because the residual is computed from the quantised integers.
+template <bool WIDE, int MAXO>
+__device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, int wasted, int sbps, int qlp_precision, int magbits, bool lean) {
     sh.lpc_ok = 0;
-    const float a0 = autoc[0];
+    const float a0 = sh.autoc[0];
     if (!(a0 > 0.f)) return;
-    float lpc[FRX_MAX_LPC], coefs[FRX_MAX_LPC][FRX_MAX_LPC], errs[FRX_MAX_LPC];
-    float err = 1.0f;                                  // normalised: autoc / autoc[0]
     const float inv0 = 1.0f / a0;
+    float an[MAXO + 1], lpc[MAXO], errs[MAXO];
+#pragma unroll
+    for (int i = 0; i <= MAXO; i++) an[i] = sh.autoc[i] * inv0;   // normalised autocorrelation
+    float err = 1.0f;
     int mo = max_lpc;
-    for (int i = 0; i < mo; i++) {
-        float r = -autoc[i + 1] * inv0;
-        for (int j = 0; j < i; j++) r -= lpc[j] * (autoc[i - j] * inv0);
-        r /= err;
-        lpc[i] = r;
-        int j;
-        for (j = 0; j < (i >> 1); j++) {
-            const float tmp = lpc[j];
-            lpc[j] += r * lpc[i - 1 - j];
-            lpc[i - 1 - j] += r * tmp;
-        }
-        if (i & 1) lpc[j] += lpc[j] * r;
-        err *= (1.0f - r * r);
-        for (j = 0; j <= i; j++) coefs[i][j] = -lpc[j];
-        errs[i] = err;
-        if (!(err > 0.f)) { mo = i + 1; break; }
+#pragma unroll
+    for (int i = 0; i < MAXO; i++) {
+        if (i < mo) {
+            float r = -an[i + 1];
+#pragma unroll
+            for (int j = 0; j < i; j++) r -= lpc[j] * an[i - j];
+            r = __fdividef(r, err);
+            lpc[i] = r;
+#pragma unroll
+            for (int j = 0; j < (i >> 1); j++) {
+                const float tmp = lpc[j];
+                lpc[j] += r * lpc[i - 1 - j];
+                lpc[i - 1 - j] += r * tmp;
+            }
+            if (i & 1) lpc[i >> 1] += lpc[i >> 1] * r;
+            err *= (1.0f - r * r);
+#pragma unroll
+            for (int j = 0; j <= i; j++) sh.lpc_rows[i][j] = -lpc[j];
+            errs[i] = err;
+            if (!(err > 0.f)) mo = i + 1;
+        } else errs[i] = 0.f;
     }
     // expected bits per order; errs are relative to autoc[0] (taken before the wasted-bit shift)
     float best_bits = 3.0e38f;
     int best = 1;
     const float lscale = __log2f(a0) + __log2f(0.5f / (float)nsamp) - 2.0f * (float)wasted;
-    for (int o = 1; o <= mo; o++) {
-        const float e = errs[o - 1];
-        const float bpsr = e > 0.f ? fmaxf(0.f, 0.5f * (__log2f(e) + lscale)) : 0.f;
-        const float b = bpsr * (float)(nsamp - o) + (float)(o * (sbps + qlp_precision));
-        if (b < best_bits) { best_bits = b; best = o; }
+#pragma unroll
+    for (int o = 1; o <= MAXO; o++) {
+        if (o <= mo) {
+            const float e = errs[o - 1];
+            const float bpsr = e > 0.f ? fmaxf(0.f, 0.5f * (__log2f(e) + lscale)) : 0.f;
+            const float b = bpsr * (float)(nsamp - o) + (float)(o * (sbps + qlp_precision));
+            if (b < best_bits) { best_bits = b; best = o; }
+        }
     }
     const int order = best;
     int precision = qlp_precision;
@@ -793,8 +935,9 @@ __device__ __noinline__ void lpc_design(EncSmall &sh, const float *autoc, int ma
         if (lim < precision) precision = lim;
     }
     if (precision < 5) return;
+    const float *row = sh.lpc_rows[order - 1];
     float cmax = 0.f;
-    for (int j = 0; j < order; j++) cmax = fmaxf(cmax, fabsf(coefs[order - 1][j]));
+    for (int j = 0; j < order; j++) cmax = fmaxf(cmax, fabsf(row[j]));
     if (!(cmax > 0.f)) return;
     int e2;
     (void)frexpf(cmax, &e2);
@@ -806,7 +949,7 @@ __device__ __noinline__ void lpc_design(EncSmall &sh, const float *autoc, int ma
     long long sumabs = 0;
     const float scale = (float)(1 << shift);
     for (int j = 0; j < order; j++) {
-        error += coefs[order - 1][j] * scale;
+        error += row[j] * scale;
         int qq = __float2int_rn(error);
         if (qq > qmax) qq = qmax; else if (qq < qmin) qq = qmin;
         error -= (float)qq;
@@ -844,23 +987,186 @@ __device__ __forceinline__ void pack_rice(BitW &bw, const uint32_t *u, uint32_t 
     }
 }
 
+// Fat data (|s| > 2^23: lossless int32 / float bit patterns): 64-bit fixed trial and range-checked LPC residuals, the two
+// Rice searches, and the decisions -- a complete, slower replacement of the lean K2/K5/K6 stages.  All compute threads call it.
+template <int HISTN>
+__device__ __noinline__ void fat_search(EncSmall &sh, const int32_t *pcm, uint64_t *tabs, int tid, int nv, int nsamp, int wasted,
+                                        int po_max, uint32_t kmax) {
+    const int lane = tid & 31, warp = tid >> 5, g0 = tid * FRX_SPT;
+    int32_t s[HISTN + FRX_SPT];
+    read_pcm<HISTN>(pcm, tid, wasted, s);
+    const bool lpc_try = sh.lpc_ok != 0;
+    const int lpc_order = sh.lpc_order;
+    uint64_t acc[5] = { 0, 0, 0, 0, 0 };
+    uint32_t fbad = 0;
+#pragma unroll
+    for (int i = 0; i < FRX_SPT; i++) {
+        const int g = g0 + i;
+        if (i < nv) {
+            const int32_t *p = s + HISTN + i;
+            const long long A = p[0], B = p[-1], C = p[-2], D = p[-3], E = p[-4];
+            const long long e[5] = { A, A - B, A - 2 * B + C, A - 3 * B + 3 * C - D, A - 4 * B + 6 * C - 4 * D + E };
+#pragma unroll
+            for (int o = 0; o < 5; o++) {
+                if (g >= o) {
+                    const unsigned long long av = (unsigned long long)llabs(e[o]);
+                    acc[o] += av;
+                    if (av > 0x7FFFFFFFull) fbad |= 1u << o;
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 0; o < 5; o++) tabs[o * FRX_ENC_THREADS + tid] = acc[o];
+#pragma unroll
+    for (int o = 0; o < 5; o++) acc[o] = warp_sum_u64(acc[o]);
+    fbad = __reduce_or_sync(FULLMASK, fbad);
+    bool bad = false;
+    uint64_t ab = 0;
+    if (lpc_try) {
+        int32_t q[HISTN], r[FRX_SPT];
+#pragma unroll
+        for (int j = 0; j < HISTN; j++) q[j] = sh.qlp[j];
+        const uint32_t badm = lpc_residuals_dispatch<2, HISTN>(lpc_order, s, q, sh.shift, r);
+#pragma unroll
+        for (int i = 0; i < FRX_SPT; i++) {
+            if (i < nv && g0 + i >= lpc_order) {
+                if ((badm >> i) & 1u) bad = true;
+                ab += (uint32_t)abs(r[i]);
+            }
+        }
+    }
+    tabs[5 * FRX_ENC_THREADS + tid] = ab;
+    const unsigned anybad = __ballot_sync(FULLMASK, bad);
+    if (lane == 0) {
+#pragma unroll
+        for (int o = 0; o < 5; o++) sh.wfix[warp][o] = acc[o];
+        sh.wbad[warp][0] = fbad; sh.wbad[warp][1] = anybad ? 1u : 0u;
+    }
+    compute_sync();
+    if (warp == 0) {
+        uint32_t fb = 0;
+        for (int w2 = 0; w2 < NWARPS; w2++) fb |= sh.wbad[w2][0];
+        uint64_t bestv = ~0ull, f1 = 0;
+        int besto = -1;
+        for (int o = 0; o < 5; o++) {
+            uint64_t tot = 0;
+            for (int w2 = 0; w2 < NWARPS; w2++) tot += sh.wfix[w2][o];
+            if (o == 1) f1 = tot;
+            if (!((fb >> o) & 1u) && tot < bestv) { bestv = tot; besto = o; }
+        }
+        const int fo = (nsamp > 4) ? besto : -1;
+        if (lane == 0) { sh.is_const = (f1 == 0 && !(fb & 2u)) ? 1 : 0; sh.fixed_order = fo; }
+        if (fo >= 0) analyse_partitions(sh, tabs + fo * FRX_ENC_THREADS, 0, nsamp, fo, po_max, kmax, 0);
+    } else if (warp == 1) {
+        uint32_t b = 0;
+        for (int w2 = 0; w2 < NWARPS; w2++) b |= sh.wbad[w2][1];
+        const bool valid = lpc_try && !b;
+        if (lane == 0) sh.lpc_ok = valid ? 1 : 0;
+        if (valid) analyse_partitions(sh, tabs + 5 * FRX_ENC_THREADS, 1, nsamp, lpc_order, po_max, kmax, 0);
+    }
+    compute_sync();
+}
+
+// copy a finished frame from its shared-memory buffer to its final place and append the CRC-16
+__device__ __forceinline__ void copy_out_frame(const EncArgs &a, EncSmall &sh, const uint32_t *bits, const uint32_t *crc_part, uint64_t off,
+                                               uint32_t body_bytes, int tid) {
+    const uint32_t nbytes = body_bytes + 2u;
+    if (off + nbytes > a.capacity) {
+        if (tid == 0) atomicExch(a.status, FRX_E_OVERFLOW);
+        return;
+    }
+    uint8_t *dst = a.bytes + off;
+    if (tid == FRX_ENC_THREADS - 1) {
+        // undo the zero-word padding of the last quad, finish over the <= 3 tail bytes, store big-endian
+        uint32_t c = 0;
+#pragma unroll
+        for (int w2 = 0; w2 < NWARPS; w2++) c ^= crc_part[w2];
+        const uint32_t nw = body_bytes >> 2;
+        const uint32_t z = ((nw + 3u) & ~3u) - nw;
+        if (z && c) c = frx_gf16_mulmod(c, (uint32_t)a.crc_xinv[z]);
+        const uint32_t tw = bits[nw];
+        for (uint32_t b = 0; b < (body_bytes & 3u); b++) {
+            const uint32_t byte = (tw >> (24 - 8 * b)) & 0xFFu;
+            c = ((c << 8) ^ sh.crc_tab[0][((c >> 8) ^ byte) & 0xFFu]) & 0xFFFFu;
+        }
+        dst[body_bytes] = (uint8_t)(c >> 8);
+        dst[body_bytes + 1] = (uint8_t)c;
+    }
+    const uint32_t head = min(body_bytes, (uint32_t)((4u - (uint32_t)((uintptr_t)dst & 3u)) & 3u));
+    if (tid < (int)head) dst[tid] = (uint8_t)((bits[tid >> 2] >> (24 - 8 * (tid & 3))) & 0xFFu);
+    const uint32_t nwords = (body_bytes - head) >> 2;
+    uint32_t *dw = reinterpret_cast<uint32_t *>(dst + head);
+    const uint32_t sh8 = head * 8u;
+    for (uint32_t j = tid; j < nwords; j += FRX_ENC_THREADS) {
+        // frame bytes [head+4j, head+4j+4): head < 4 so they straddle words j and j+1
+        const uint32_t w0 = bits[j], w1 = bits[j + 1];
+        const uint32_t v = head ? __funnelshift_l(w1, w0, sh8) : w0;
+        dw[j] = frx_bswap32(v);
+    }
+    const uint32_t tail0 = head + (nwords << 2);
+    if (tid < (int)(body_bytes - tail0)) {
+        const uint32_t b = tail0 + (uint32_t)tid;
+        dst[b] = (uint8_t)((bits[b >> 2] >> (24 - 8 * (b & 3))) & 0xFFu);
+    }
+}
+
+// CRC-16 of the frame body's whole words: every compute thread takes a chunk of Lq quads, the chunk CRCs are shifted to
+// their place with x^(128 Lq j) mod P and xor-ed (per warp here, across warps by copy_out_frame)
+__device__ __forceinline__ void crc_frame(const EncArgs &a, EncSmall &sh, const uint32_t *bits, uint32_t *crc_part, uint32_t body_bytes,
+                                          int tid) {
+    const uint32_t nw = body_bytes >> 2;                       // whole words
+    const uint32_t nq = (nw + 3u) >> 2;                        // quads; the buffer is zero behind the frame
+    const uint32_t Lq = (nq + FRX_ENC_THREADS - 1) / FRX_ENC_THREADS;
+    const int padq = (int)(FRX_ENC_THREADS * Lq) - (int)nq;    // virtual leading zero quads
+    int q0 = tid * (int)Lq - padq;
+    const int q1 = q0 + (int)Lq;
+    if (q0 < 0) q0 = 0;
+    uint32_t c = 0;
+    for (int qi = q0; qi < q1; qi++) {
+        uint4 wv = *reinterpret_cast<const uint4 *>(bits + 4 * qi);
+        if (qi == (int)nq - 1) {   // the word behind the last whole word holds the <= 3 tail bytes: not part of this pass
+            const uint32_t k = nw - 4u * (uint32_t)qi;   // whole words in the last quad (1..4)
+            if (k < 4u) wv.w = 0u;
+            if (k < 3u) wv.z = 0u;
+            if (k < 2u) wv.y = 0u;
+        }
+        uint32_t x = wv.x ^ (c << 16);
+        c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
+        x = wv.y ^ (c << 16);
+        c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
+        x = wv.z ^ (c << 16);
+        c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
+        x = wv.w ^ (c << 16);
+        c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
+    }
+    if (c) c = frx_gf16_mulmod(c, (uint32_t)__ldg(&a.crc_xpow[(Lq - 1) * FRX_ENC_THREADS + (FRX_ENC_THREADS - 1 - tid)]));
+    c = __reduce_xor_sync(FULLMASK, c);
+    if ((tid & 31) == 0) crc_part[tid >> 5] = c;
+}
+
 // ------------------------------------------------------------------------------------------
 // The frame encoder.  WIDE: PCM wider than 16 bits (64-bit LPC accumulate, RICE2).  HISTN: history samples a thread
-// keeps = the largest LPC order of the compression level (4 when the level has no LPC stage).
-// 8 compute warps (one frame at a time, 16 samples per thread) + 1 control warp.
+// reads = the largest LPC order of the compression level (4 when the level has no LPC stage).
+// 8 compute warps (one frame at a time, 16 samples per thread) + 1 control warp.  The PCM of the current subframe
+// lives in padded shared memory and every stage re-reads it, so almost no register state crosses a barrier.
 // ------------------------------------------------------------------------------------------
 template <bool WIDE, int HISTN>
 __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     EncSmall &sh = *reinterpret_cast<EncSmall *>(smem_raw);
+    const uint32_t stage_stride = 128u + (uint32_t)FRX_MAX_BLOCK * (uint32_t)frx_dtype_size(a.dtype);
     unsigned char *raw = smem_raw + ENC_SMALL_BYTES;
-    uint64_t *tabs = reinterpret_cast<uint64_t *>(raw + 2 * RAW_STRIDE);
-    uint32_t *bits = reinterpret_cast<uint32_t *>(raw + 2 * RAW_STRIDE + TABS_BYTES);
+    int32_t *pcm = reinterpret_cast<int32_t *>(raw + 2 * stage_stride);
+    uint64_t *tabs = reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(pcm) + PCM_BYTES);
+    uint32_t *bits0 = reinterpret_cast<uint32_t *>(reinterpret_cast<unsigned char *>(tabs) + TABS_BYTES);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < a.frame_words; i += FRX_ENC_CTA) bits[i] = 0u;
+    for (int i = tid; i < 2 * a.frame_words; i += FRX_ENC_CTA) bits0[i] = 0u;
+    for (int i = tid; i < PCM_WORDS; i += FRX_ENC_CTA) pcm[i] = 0;
     for (int i = tid; i < 1024; i += FRX_ENC_CTA) (&sh.crc_tab[0][0])[i] = a.crc_tab[i];
     if (tid == 0) {
+        sh.stage_stride = stage_stride;
         for (int i = 0; i < 2; i++) { mbar_init(&sh.full[i], 1); mbar_init(&sh.empty[i], NWARPS); }
         for (int i = 0; i < FD_SLOTS; i++) { mbar_init(&sh.sized[i], 1); mbar_init(&sh.placed[i], 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -872,21 +1178,33 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
     const uint32_t kmax = a.bps > 16 ? 30u : 14u;  // RICE2 only for bps > 16 (libFLAC)
     const int g0 = tid * FRX_SPT;                  // first sample index of this thread
     uint32_t unit = 0, fseq = 0;
+    // copy-out runs one frame behind (double-buffered frame buffer), so the look-back never stalls the compute warps
+    bool pend = false;
+    uint32_t pend_body = 0;
 
+    const long long ck0 = DBG_CLK();
+    DBG_PH_DECL;
     for (;;) {
         // ---- next frame: its descriptor is valid once the first raw stage of the frame is full ----
         const int slot = (int)(fseq & (FD_SLOTS - 1));
+        const int buf = (int)(fseq & 1u);
+        uint32_t *bits = bits0 + (size_t)buf * a.frame_words;
+        const long long cw0 = DBG_CLK();
         mbar_wait(&sh.full[unit & 1u], (unit >> 1) & 1u);
+        if (tid == 0) DBG_ADD(0, DBG_CLK() - cw0);
         const FrameDesc &fd = sh.fd[slot];
         const uint32_t f = fd.f;
-        if (f == STOP_FRAME) break;
+        if (f == STOP_FRAME) { if (tid == 0) DBG_ADD(7, DBG_CLK() - ck0); break; }
+        if (tid == 0) DBG_TRACE(f, 4);
+        DBG_PH(15);
         const frx_tile t = fd.t;
         const uint32_t s0 = fd.s0;
         const int nsamp = fd.nsamp;
         const bool use_tma = fd.tma != 0;
         const int nthr = (nsamp + FRX_SPT - 1) / FRX_SPT;
         const int nv = min(FRX_SPT, max(0, nsamp - g0));  // valid samples of this thread
-        const bool full = (nsamp == a.blocksize) && (a.blocksize == FRX_MAX_BLOCK);
+        const bool full = (nsamp == FRX_MAX_BLOCK);
+        const bool plain = full && tid != 0;              // no per-sample masks needed for this thread
         uint32_t bitpos = fd.hdr_bits;
         if (tid < 4) bits[tid] = fd.hdr[tid];
         int po_max;
@@ -900,145 +1218,84 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
         // ================= per channel =================
         for (int ch = 0; ch < t.n_channels; ch++) {
             const int stage = (int)(unit & 1u);
-            unsigned char *stg = raw + (size_t)stage * RAW_STRIDE + RAW_PAD;
+            unsigned char *stg = raw + (size_t)stage * stage_stride;
             if (ch > 0) mbar_wait(&sh.full[stage], (unit >> 1) & 1u);
             if (!use_tma) {
-                switch (a.dtype) {
-                    case FRX_U8: gather_raw<FRX_U8>(a, t, ch, s0, nsamp, stg, tid); break;
-                    case FRX_I16: gather_raw<FRX_I16>(a, t, ch, s0, nsamp, stg, tid); break;
-                    case FRX_U16: gather_raw<FRX_U16>(a, t, ch, s0, nsamp, stg, tid); break;
-                    case FRX_I32: gather_raw<FRX_I32>(a, t, ch, s0, nsamp, stg, tid); break;
-                    case FRX_U32: gather_raw<FRX_U32>(a, t, ch, s0, nsamp, stg, tid); break;
-                    default: gather_raw<FRX_F32>(a, t, ch, s0, nsamp, stg, tid); break;
-                }
+                gather_raw(a, t, ch, s0, nsamp, stg, tid);
                 compute_sync();
             }
-            // ---- K1: registers = HISTN history + 16 samples, quantised to PCM ----
-            int32_t s[HISTN + FRX_SPT];
-            {
-                const FrxQuant qz = fd.q;
-                switch (a.dtype) {
-                    case FRX_U8: load_samples<FRX_U8, HISTN>(stg, qz, a.pcm_mode, tid, s); break;
-                    case FRX_I16: load_samples<FRX_I16, HISTN>(stg, qz, a.pcm_mode, tid, s); break;
-                    case FRX_U16: load_samples<FRX_U16, HISTN>(stg, qz, a.pcm_mode, tid, s); break;
-                    case FRX_I32: load_samples<FRX_I32, HISTN>(stg, qz, a.pcm_mode, tid, s); break;
-                    case FRX_U32: load_samples<FRX_U32, HISTN>(stg, qz, a.pcm_mode, tid, s); break;
-                    default: load_samples<FRX_F32, HISTN>(stg, qz, a.pcm_mode, tid, s); break;
-                }
-            }
-            // the raw stage may be refilled as soon as every warp has its samples in registers
-            if (!use_tma) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&sh.empty[stage]);
-            unit++;
-            if (tid == 0) {
-#pragma unroll
-                for (int i = 0; i < HISTN; i++) s[i] = 0;
-            }
-            if (!full) {
-#pragma unroll
-                for (int i = 0; i < HISTN + FRX_SPT; i++)
-                    if (g0 - HISTN + i >= nsamp) s[i] = 0;
-            }
-            // ---- wasted bits / magnitude ----
+            // ---- K1: the thread's 16 samples -> PCM -> shared memory ----
             uint32_t orv = 0, ora = 0;
-#pragma unroll
-            for (int i = 0; i < FRX_SPT; i++) {
-                orv |= (uint32_t)s[HISTN + i];
-                if (WIDE) ora |= (uint32_t)(s[HISTN + i] ^ (s[HISTN + i] >> 31));
+            {
+                uint2 oo;
+                if (a.dtype == FRX_F32) oo = k1_quantize<FRX_F32, WIDE>(stg, fd.q, a.pcm_mode, tid, nv, pcm);
+                else if (a.dtype == FRX_U16) oo = k1_quantize<FRX_U16, WIDE>(stg, fd.q, a.pcm_mode, tid, nv, pcm);
+                else oo = k1_quantize_any<WIDE>(a.dtype, stg, fd.q, a.pcm_mode, tid, nv, pcm);
+                orv = oo.x; ora = oo.y;
+                // the raw stage may be refilled as soon as every warp has read its samples
+                if (!use_tma) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sh.empty[stage]);
+                unit++;
             }
             orv = __reduce_or_sync(FULLMASK, orv);
             if (WIDE) ora = __reduce_or_sync(FULLMASK, ora);
-            // ---- K2 (lean): fixed-order trial in 32-bit, sum |e_k| over samples g >= k ----
-            uint32_t fa[5];
-            fixed_trial32<HISTN>(s, fa);
-            if (tid == 0) {
-                uint32_t sub[5];
-                fixed_trial32_warmup<HISTN>(s, sub);
-#pragma unroll
-                for (int o = 1; o < 5; o++) fa[o] -= sub[o];
-            }
-            if (!full && nv < FRX_SPT) {
-                // partial or empty thread of a short frame: redo with per-sample masks
-                int32_t dm1 = s[HISTN - 1] - s[HISTN - 2], dm2 = s[HISTN - 2] - s[HISTN - 3], dm3 = s[HISTN - 3] - s[HISTN - 4];
-                int32_t d1p = dm1, d2p = dm1 - dm2, d3p = (dm1 - dm2) - (dm2 - dm3);
-#pragma unroll
-                for (int o = 0; o < 5; o++) fa[o] = 0;
-#pragma unroll
-                for (int i = 0; i < FRX_SPT; i++) {
-                    const int32_t x = s[HISTN + i];
-                    const int32_t d1 = x - s[HISTN + i - 1];
-                    const int32_t d2 = d1 - d1p, d3 = d2 - d2p, d4 = d3 - d3p;
-                    d1p = d1; d2p = d2; d3p = d3;
-                    if (i < nv) {
-                        const int g = g0 + i;
-                        fa[0] += (uint32_t)abs(x);
-                        if (g >= 1) fa[1] += (uint32_t)abs(d1);
-                        if (g >= 2) fa[2] += (uint32_t)abs(d2);
-                        if (g >= 3) fa[3] += (uint32_t)abs(d3);
-                        if (g >= 4) fa[4] += (uint32_t)abs(d4);
-                    }
-                }
-            }
-#pragma unroll
-            for (int o = 0; o < 5; o++) tabs[o * FRX_ENC_THREADS + tid] = fa[o];
+            compute_sync();  // S0: PCM of the subframe is in shared memory
+            DBG_PH(9);
+            // ---- K2 (lean, 32-bit) fixed-order trial + K3 windowed autocorrelation partials ----
             {
-                uint64_t w5[5];
+                int32_t s[HISTN + FRX_SPT];
+                read_pcm<HISTN>(pcm, tid, 0, s);
+                uint32_t fa[5];
+                if (plain) fixed_trial32<HISTN>(s, fa);
+                else fixed_trial32_masked<HISTN>(s, g0, nv, fa);
 #pragma unroll
-                for (int o = 0; o < 5; o++) w5[o] = WIDE ? warp_sum_u32_wide(fa[o]) : (uint64_t)__reduce_add_sync(FULLMASK, fa[o]);
-                if (lane == 0) {
+                for (int o = 0; o < 5; o++) tabs[o * FRX_ENC_THREADS + tid] = fa[o];
+                {
+                    uint64_t w5[5];
 #pragma unroll
-                    for (int o = 0; o < 5; o++) sh.wfix[warp][o] = w5[o];
-                    sh.wor[warp][0] = orv; sh.wor[warp][1] = ora;
-                }
-            }
-            // ---- K3: windowed autocorrelation partials (float within the warp) ----
-            if (max_lpc > 0) {
-                float xw[HISTN + FRX_SPT];
-                if (full) {
-                    const float4 *w4 = reinterpret_cast<const float4 *>(a.window + g0);
+                    for (int o = 0; o < 5; o++) w5[o] = WIDE ? warp_sum_u32_wide(fa[o]) : (uint64_t)__reduce_add_sync(FULLMASK, fa[o]);
+                    if (lane == 0) {
 #pragma unroll
-                    for (int v = 0; v < FRX_SPT / 4; v++) {
-                        const float4 wv = __ldg(w4 + v);
-                        xw[HISTN + 4 * v] = (float)s[HISTN + 4 * v] * wv.x; xw[HISTN + 4 * v + 1] = (float)s[HISTN + 4 * v + 1] * wv.y;
-                        xw[HISTN + 4 * v + 2] = (float)s[HISTN + 4 * v + 2] * wv.z; xw[HISTN + 4 * v + 3] = (float)s[HISTN + 4 * v + 3] * wv.w;
+                        for (int o = 0; o < 5; o++) sh.wfix[warp][o] = w5[o];
+                        sh.wor[warp][0] = orv; sh.wor[warp][1] = ora;
                     }
-                    if (tid > 0) {
-                        const float4 *h4 = reinterpret_cast<const float4 *>(a.window + g0 - HISTN);
+                }
+                if (max_lpc > 0) {
+                    float xw[HISTN + FRX_SPT];
+                    if (full) {
+                        // window table: zero history of thread 0 comes from the zero samples in front of the PCM buffer
+                        const float4 *w4 = reinterpret_cast<const float4 *>(a.window + g0 - HISTN);
 #pragma unroll
-                        for (int v = 0; v < HISTN / 4; v++) {
-                            const float4 wv = __ldg(h4 + v);
+                        for (int v = 0; v < (HISTN + FRX_SPT) / 4; v++) {
+                            float4 wv = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (tid > 0 || v >= HISTN / 4) wv = __ldg(w4 + v);
                             xw[4 * v] = (float)s[4 * v] * wv.x; xw[4 * v + 1] = (float)s[4 * v + 1] * wv.y;
                             xw[4 * v + 2] = (float)s[4 * v + 2] * wv.z; xw[4 * v + 3] = (float)s[4 * v + 3] * wv.w;
                         }
                     } else {
 #pragma unroll
-                        for (int i = 0; i < HISTN; i++) xw[i] = 0.f;
+                        for (int i = 0; i < HISTN + FRX_SPT; i++) xw[i] = (float)s[i] * tukey_w(g0 - HISTN + i, nsamp);
                     }
-                } else {
+                    float ac[HISTN + 1];
 #pragma unroll
-                    for (int i = 0; i < HISTN + FRX_SPT; i++) {
-                        const int g = g0 - HISTN + i;
-                        xw[i] = (g >= 0 && g < nsamp) ? (float)s[i] * tukey_half(g, nsamp) : 0.f;
+                    for (int lag = 0; lag <= HISTN; lag++) ac[lag] = 0.f;
+#pragma unroll
+                    for (int i = 0; i < FRX_SPT; i++) {
+#pragma unroll
+                        for (int lag = 0; lag <= HISTN; lag++) ac[lag] = fmaf(xw[HISTN + i], xw[HISTN + i - lag], ac[lag]);
                     }
-                }
-                float ac[HISTN + 1];
 #pragma unroll
-                for (int lag = 0; lag <= HISTN; lag++) ac[lag] = 0.f;
+                    for (int lag = 0; lag <= HISTN; lag++) {
+                        float v = ac[lag];
 #pragma unroll
-                for (int i = 0; i < FRX_SPT; i++) {
-#pragma unroll
-                    for (int lag = 0; lag <= HISTN; lag++) ac[lag] = fmaf(xw[HISTN + i], xw[HISTN + i - lag], ac[lag]);
-                }
-#pragma unroll
-                for (int lag = 0; lag <= HISTN; lag++) {
-                    float v = ac[lag];
-#pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULLMASK, v, o);
-                    if (lane == 0) sh.wac[warp][lag] = v;
+                        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULLMASK, v, o);
+                        if (lane == 0) sh.wac[warp][lag] = v;
+                    }
                 }
             }
             compute_sync();  // SA: per-warp partials and tabs[0..4] are in shared memory
+            DBG_PH(10);
             // ---- warp 0: fixed-order decision + Rice search of the fixed candidate; warp 1: LPC design ----
             if (warp == 0) {
                 uint64_t tot = 0;
@@ -1072,115 +1329,40 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                 const bool lean = !WIDE || magbits <= 23;
                 float acs = 0.f;
                 if (lane <= max_lpc) { for (int w2 = 0; w2 < NWARPS; w2++) acs += sh.wac[w2][lane]; }
-                float *autoc = sh.autoc;
-                if (lane <= FRX_MAX_LPC) autoc[lane] = acs;
+                if (lane <= FRX_MAX_LPC) sh.autoc[lane] = acs;
                 __syncwarp();
                 if (lane == 0) {
                     sh.magbits = magbits; sh.lean = lean ? 1 : 0;
                     sh.lpc_ok = 0;
                     if (max_lpc > 0 && nsamp > 4)
-                        lpc_design<WIDE>(sh, autoc, max_lpc, nsamp, wasted, a.bps - wasted, a.qlp_precision, magbits, lean);
+                        lpc_design<WIDE, HISTN>(sh, max_lpc, nsamp, wasted, a.bps - wasted, a.qlp_precision, magbits, lean);
                 }
             }
             compute_sync();  // SB
+            DBG_PH(11);
             const int wasted = sh.wasted;
             const bool lean = sh.lean != 0;
             const int sbps = a.bps - wasted;
-            int fixed_order = sh.fixed_order;
-            bool is_const = sh.is_const != 0;
-            if (wasted) {
-#pragma unroll
-                for (int i = 0; i < HISTN + FRX_SPT; i++) s[i] >>= wasted;
-            }
-            bool lpc_try = sh.lpc_ok != 0;
             const int lpc_order = sh.lpc_order;
             const int lshift = sh.shift;
             int32_t r[FRX_SPT];
-            const int lmode = !WIDE ? 0 : (lean ? (sh.lpc_narrow ? 0 : 1) : 2);
-            int32_t q[HISTN];
-#pragma unroll
-            for (int j = 0; j < HISTN; j++) q[j] = sh.qlp[j];
             if (WIDE && !lean) {
-                // ---- fat data (|s| > 2^23: lossless int32 / float bit patterns): 64-bit fixed trial, range-checked LPC ----
-                uint64_t acc[5] = { 0, 0, 0, 0, 0 };
-                uint32_t fbad = 0;
-#pragma unroll
-                for (int i = 0; i < FRX_SPT; i++) {
-                    const int g = g0 + i;
-                    if (i < nv) {
-                        const int32_t *p = s + HISTN + i;
-                        const long long A = p[0], B = p[-1], C = p[-2], D = p[-3], E = p[-4];
-                        const long long e[5] = { A, A - B, A - 2 * B + C, A - 3 * B + 3 * C - D, A - 4 * B + 6 * C - 4 * D + E };
-#pragma unroll
-                        for (int o = 0; o < 5; o++) {
-                            if (g >= o) {
-                                const unsigned long long av = (unsigned long long)llabs(e[o]);
-                                acc[o] += av;
-                                if (av > 0x7FFFFFFFull) fbad |= 1u << o;
-                            }
-                        }
-                    }
-                }
-#pragma unroll
-                for (int o = 0; o < 5; o++) tabs[o * FRX_ENC_THREADS + tid] = acc[o];
-#pragma unroll
-                for (int o = 0; o < 5; o++) acc[o] = warp_sum_u64(acc[o]);
-                fbad = __reduce_or_sync(FULLMASK, fbad);
-                bool bad = false;
-                uint64_t ab = 0;
-                if (lpc_try) {
-                    const uint32_t badm = lpc_residuals_dispatch<2, HISTN>(lpc_order, s, q, lshift, r);
-#pragma unroll
-                    for (int i = 0; i < FRX_SPT; i++) {
-                        if (i < nv && g0 + i >= lpc_order) {
-                            if ((badm >> i) & 1u) bad = true;
-                            ab += (uint32_t)abs(r[i]);
-                        }
-                    }
-                }
-                tabs[5 * FRX_ENC_THREADS + tid] = ab;
-                const unsigned anybad = __ballot_sync(FULLMASK, bad);
-                if (lane == 0) {
-#pragma unroll
-                    for (int o = 0; o < 5; o++) sh.wfix[warp][o] = acc[o];
-                    sh.wbad[warp][0] = fbad; sh.wbad[warp][1] = anybad ? 1u : 0u;
-                }
-                compute_sync();
-                if (warp == 0) {
-                    uint32_t fb = 0;
-                    for (int w2 = 0; w2 < NWARPS; w2++) fb |= sh.wbad[w2][0];
-                    uint64_t bestv = ~0ull, f1 = 0;
-                    int besto = -1;
-                    for (int o = 0; o < 5; o++) {
-                        uint64_t tot = 0;
-                        for (int w2 = 0; w2 < NWARPS; w2++) tot += sh.wfix[w2][o];
-                        if (o == 1) f1 = tot;
-                        if (!((fb >> o) & 1u) && tot < bestv) { bestv = tot; besto = o; }
-                    }
-                    const int fo = (nsamp > 4) ? besto : -1;
-                    if (lane == 0) { sh.is_const = (f1 == 0 && !(fb & 2u)) ? 1 : 0; sh.fixed_order = fo; }
-                    if (fo >= 0) analyse_partitions(sh, tabs + fo * FRX_ENC_THREADS, 0, nsamp, fo, po_max, kmax, 0);
-                } else if (warp == 1) {
-                    uint32_t b = 0;
-                    for (int w2 = 0; w2 < NWARPS; w2++) b |= sh.wbad[w2][1];
-                    const bool valid = lpc_try && !b;
-                    if (lane == 0) sh.lpc_ok = valid ? 1 : 0;
-                    if (valid) analyse_partitions(sh, tabs + 5 * FRX_ENC_THREADS, 1, nsamp, lpc_order, po_max, kmax, 0);
-                }
-                compute_sync();
-                fixed_order = sh.fixed_order;
-                is_const = sh.is_const != 0;
-                lpc_try = sh.lpc_ok != 0;
+                fat_search<HISTN>(sh, pcm, tabs, tid, nv, nsamp, wasted, po_max, kmax);
             } else {
                 // ---- K5: LPC residuals (kept in registers) and their |r| sums ----
-                if (lpc_try) {
-                    if (lmode == 0) (void)lpc_residuals_dispatch<0, HISTN>(lpc_order, s, q, lshift, r);
-                    else if (WIDE) (void)lpc_residuals_dispatch<1, HISTN>(lpc_order, s, q, lshift, r);
-                    uint32_t ab = 0;
+                const bool lpc_try0 = sh.lpc_ok != 0;
+                if (lpc_try0) {
+                    int32_t s[HISTN + FRX_SPT], q[HISTN];
+                    read_pcm<HISTN>(pcm, tid, wasted, s);
 #pragma unroll
-                    for (int i = 0; i < FRX_SPT; i++) ab += (uint32_t)abs(r[i]);
-                    if (tid == 0 || (!full && nv < FRX_SPT)) {
-                        ab = 0;
+                    for (int j = 0; j < HISTN; j++) q[j] = sh.qlp[j];
+                    if (!WIDE || sh.lpc_narrow) (void)lpc_residuals_dispatch<0, HISTN>(lpc_order, s, q, lshift, r);
+                    else (void)lpc_residuals_dispatch<1, HISTN>(lpc_order, s, q, lshift, r);
+                    uint32_t ab = 0;
+                    if (plain) {
+#pragma unroll
+                        for (int i = 0; i < FRX_SPT; i++) ab += (uint32_t)abs(r[i]);
+                    } else {
 #pragma unroll
                         for (int i = 0; i < FRX_SPT; i++)
                             if (i < nv && g0 + i >= lpc_order) ab += (uint32_t)abs(r[i]);
@@ -1188,9 +1370,13 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                     tabs[5 * FRX_ENC_THREADS + tid] = ab;
                 }
                 compute_sync();  // SC
-                if (warp == 1 && lpc_try) analyse_partitions(sh, tabs + 5 * FRX_ENC_THREADS, 1, nsamp, lpc_order, po_max, kmax, 0);
+                if (warp == 1 && lpc_try0) analyse_partitions(sh, tabs + 5 * FRX_ENC_THREADS, 1, nsamp, lpc_order, po_max, kmax, 0);
                 compute_sync();  // SD
+                DBG_PH(12);
             }
+            const int fixed_order = sh.fixed_order;
+            const bool is_const = sh.is_const != 0;
+            const bool lpc_try = sh.lpc_ok != 0;
 
             // ---- choose ----
             const uint64_t verb_bits = 8ull + (uint64_t)wasted + (uint64_t)nsamp * (uint64_t)sbps;
@@ -1221,9 +1407,19 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                 psize = nsamp >> po;
                 kk = sh.kparam[cand][min(g0 / psize, (1 << po) - 1)];
                 rice2 = sh.cand_rice2[cand] != 0;
-                if (type == 2) {
-                    if (WIDE && !lean) (void)fixed_residuals<true, HISTN>(order, s, r);
-                    else (void)fixed_residuals<false, HISTN>(order, s, r);
+                if (type == 2 || (WIDE && !lean)) {
+                    // fixed winner (4 ops per sample) or a fat-path LPC winner: recompute from the PCM
+                    int32_t s[HISTN + FRX_SPT];
+                    read_pcm<HISTN>(pcm, tid, wasted, s);
+                    if (type == 2) {
+                        if (WIDE && !lean) (void)fixed_residuals<true, HISTN>(order, s, r);
+                        else (void)fixed_residuals<false, HISTN>(order, s, r);
+                    } else if (WIDE) {
+                        int32_t q[HISTN];
+#pragma unroll
+                        for (int j = 0; j < HISTN; j++) q[j] = sh.qlp[j];
+                        (void)lpc_residuals_dispatch<1, HISTN>(order, s, q, lshift, r);
+                    }
                 }
                 uint32_t qs = 0;
 #pragma unroll
@@ -1231,7 +1427,7 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                     u[i] = zigzag(r[i]);
                     qs += u[i] >> kk;
                 }
-                if (nv == FRX_SPT && tid != 0) mybits = qs + (uint32_t)FRX_SPT * (1u + kk);
+                if (plain) mybits = qs + (uint32_t)FRX_SPT * (1u + kk);
                 else {
 #pragma unroll
                     for (int i = 0; i < FRX_SPT; i++)
@@ -1256,6 +1452,7 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
             }
             if (lane == 31) sh.scan[warp] = incl;
             compute_sync();  // SE
+            DBG_PH(13);
             uint32_t wbase = 0, total = 0;
 #pragma unroll
             for (int w2 = 0; w2 < NWARPS; w2++) {
@@ -1288,7 +1485,10 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
             bitpos = sub_start + total;
             if (ch == t.n_channels - 1 && tid == 0) {
                 // the frame's size is final: hand it to the control warp so the look-back overlaps packing and the CRC
-                sh.frame_bytes[slot] = ((bitpos + 7u) >> 3) + 2u;
+                const uint32_t nb = ((bitpos + 7u) >> 3) + 2u;
+                if (f != 0) frx_st_relaxed_u64(&a.desc[f], (1ull << 62) | (uint64_t)nb);
+                DBG_TRACE(f, 1);   // flag A: size known, prefix not yet
+                sh.frame_bytes[slot] = nb;
                 mbar_arrive(&sh.sized[slot]);
             }
             // ---- K7b: pack ----
@@ -1302,20 +1502,12 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                     if (wasted) { if (wasted > 1) bw.skip((uint32_t)wasted - 1u); bw.put(1u, 1); }
                 }
                 if (type == 0) {
-                    if (tid == 0) bw.put((uint32_t)s[HISTN] & smask, sbps);
+                    if (tid == 0) bw.put((uint32_t)(pcm[PCM_IDX(0)] >> wasted) & smask, sbps);
                 } else if (type == 1) {
-#pragma unroll
-                    for (int i = 0; i < FRX_SPT; i++)
-                        if (i < nv) bw.put((uint32_t)s[HISTN + i] & smask, sbps);
+                    for (int i = 0; i < nv; i++) bw.put((uint32_t)(pcm[PCM_IDX(g0 + i)] >> wasted) & smask, sbps);
                 } else {
                     if (tid == 0) {
-                        for (int i = 0; i < order; i++) {
-                            // warm-up samples: a dynamic index into s[] would spill it, so select with compile-time indices
-                            int32_t wv = 0;
-#pragma unroll
-                            for (int k = 0; k < HISTN; k++) if (k == i) wv = s[HISTN + k];
-                            bw.put((uint32_t)wv & smask, sbps);
-                        }
+                        for (int i = 0; i < order; i++) bw.put((uint32_t)(pcm[PCM_IDX(i)] >> wasted) & smask, sbps);   // warm-up samples
                         if (type == 3) {
                             bw.put((uint32_t)(sh.precision - 1), 4);
                             bw.put((uint32_t)sh.shift & 31u, 5);
@@ -1329,89 +1521,38 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                 }
                 bw.finish();
             }
+            // the PCM buffer is rewritten by the next channel's K1: every reader of it (verbatim / warm-up packing) must be done
+            if (ch + 1 < t.n_channels) compute_sync();
         }  // channels
         compute_sync();  // Sa: every subframe is packed
+        DBG_PH(14);
 
-        // ---- frame footer: pad to byte, CRC-16 over the body (all compute threads, quads of words) ----
+        // ---- frame footer: CRC-16 of this frame; copy-out of the PREVIOUS frame (its byte offset has had a frame time to arrive) ----
         const uint32_t body_bytes = (bitpos + 7u) >> 3;
-        const uint32_t nbytes = body_bytes + 2u;
-        {
-            const uint32_t nw = body_bytes >> 2;                       // whole words
-            const uint32_t nq = (nw + 3u) >> 2;                        // quads; the buffer is zero behind the frame
-            const uint32_t Lq = (nq + FRX_ENC_THREADS - 1) / FRX_ENC_THREADS;
-            const int padq = (int)(FRX_ENC_THREADS * Lq) - (int)nq;    // virtual leading zero quads
-            int q0 = tid * (int)Lq - padq;
-            const int q1 = q0 + (int)Lq;
-            if (q0 < 0) q0 = 0;
-            uint32_t c = 0;
-            for (int qi = q0; qi < q1; qi++) {
-                uint4 wv = *reinterpret_cast<const uint4 *>(bits + 4 * qi);
-                if (qi == (int)nq - 1) {   // the word behind the last whole word holds the <= 3 tail bytes: not part of this pass
-                    const uint32_t k = nw - 4u * (uint32_t)qi;   // whole words in the last quad (1..4)
-                    if (k < 4u) wv.w = 0u;
-                    if (k < 3u) wv.z = 0u;
-                    if (k < 2u) wv.y = 0u;
-                }
-                uint32_t x = wv.x ^ (c << 16);
-                c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
-                x = wv.y ^ (c << 16);
-                c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
-                x = wv.z ^ (c << 16);
-                c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
-                x = wv.w ^ (c << 16);
-                c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
-            }
-            if (c) c = frx_gf16_mulmod(c, (uint32_t)__ldg(&a.crc_xpow[(Lq - 1) * FRX_ENC_THREADS + (FRX_ENC_THREADS - 1 - tid)]));
-            c = __reduce_xor_sync(FULLMASK, c);
-            if (lane == 0) sh.crc_part[warp] = c;
+        const long long cc0 = DBG_CLK();
+        crc_frame(a, sh, bits, sh.crc_part[buf], body_bytes, tid);
+        if (tid == 0) DBG_ADD(8, DBG_CLK() - cc0);
+        if (pend) {
+            const int pslot = (int)((fseq - 1u) & (FD_SLOTS - 1));
+            uint32_t *pbits = bits0 + (size_t)(buf ^ 1) * a.frame_words;
+            const long long cp0 = DBG_CLK();
+            mbar_wait(&sh.placed[pslot], ((fseq - 1u) / FD_SLOTS) & 1u);
+            if (tid == 0) { DBG_ADD(1, DBG_CLK() - cp0); DBG_TRACE(f, 7); }
+            copy_out_frame(a, sh, pbits, sh.crc_part[buf ^ 1], sh.out_offset[pslot], pend_body, tid);
+            compute_sync();  // all reads of the previous frame's buffer are done
+            for (uint32_t j = tid; j <= (pend_body >> 2); j += FRX_ENC_THREADS) pbits[j] = 0u;
         }
-        compute_sync();  // Sb
-        // ---- copy the frame to its final place (offset from the control warp's look-back) ----
-        mbar_wait(&sh.placed[slot], (fseq / FD_SLOTS) & 1u);
-        {
-            const uint64_t off = sh.out_offset[slot];
-            if (off + nbytes > a.capacity) {
-                if (tid == 0) atomicExch(a.status, FRX_E_OVERFLOW);
-            } else {
-                uint8_t *dst = a.bytes + off;
-                if (tid == FRX_ENC_THREADS - 1) {
-                    // undo the zero-word padding of the last quad, finish over the <= 3 tail bytes, store big-endian
-                    uint32_t c = 0;
-#pragma unroll
-                    for (int w2 = 0; w2 < NWARPS; w2++) c ^= sh.crc_part[w2];
-                    const uint32_t nw = body_bytes >> 2;
-                    const uint32_t z = ((nw + 3u) & ~3u) - nw;
-                    if (z && c) c = frx_gf16_mulmod(c, (uint32_t)a.crc_xinv[z]);
-                    const uint32_t tw = bits[nw];
-                    for (uint32_t b = 0; b < (body_bytes & 3u); b++) {
-                        const uint32_t byte = (tw >> (24 - 8 * b)) & 0xFFu;
-                        c = ((c << 8) ^ sh.crc_tab[0][((c >> 8) ^ byte) & 0xFFu]) & 0xFFFFu;
-                    }
-                    dst[body_bytes] = (uint8_t)(c >> 8);
-                    dst[body_bytes + 1] = (uint8_t)c;
-                }
-                const uint32_t head = min(body_bytes, (uint32_t)((4u - (uint32_t)((uintptr_t)dst & 3u)) & 3u));
-                if (tid < (int)head) dst[tid] = (uint8_t)((bits[tid >> 2] >> (24 - 8 * (tid & 3))) & 0xFFu);
-                const uint32_t nwords = (body_bytes - head) >> 2;
-                uint32_t *dw = reinterpret_cast<uint32_t *>(dst + head);
-                const uint32_t sh8 = head * 8u;
-                for (uint32_t j = tid; j < nwords; j += FRX_ENC_THREADS) {
-                    // frame bytes [head+4j, head+4j+4): head < 4 so they straddle words j and j+1
-                    const uint32_t w0 = bits[j], w1 = bits[j + 1];
-                    const uint32_t v = head ? __funnelshift_l(w1, w0, sh8) : w0;
-                    dw[j] = frx_bswap32(v);
-                }
-                const uint32_t tail0 = head + (nwords << 2);
-                if (tid < (int)(body_bytes - tail0)) {
-                    const uint32_t b = tail0 + (uint32_t)tid;
-                    dst[b] = (uint8_t)((bits[b >> 2] >> (24 - 8 * (b & 3))) & 0xFFu);
-                }
-            }
-        }
-        compute_sync();  // Sz: all reads of the frame buffer done
-        for (uint32_t j = tid; j <= (body_bytes >> 2); j += FRX_ENC_THREADS) bits[j] = 0u;
+        pend = true;
+        pend_body = body_bytes;
         fseq++;
-        compute_sync();  // the next frame's header words go into a clean buffer
+        compute_sync();  // crc_part / cleared buffer visible; the next frame's header words go into a clean buffer
+        DBG_PH(5);
+    }
+    if (pend) {   // flush the last frame
+        const int pslot = (int)((fseq - 1u) & (FD_SLOTS - 1));
+        const int pbuf = (int)((fseq - 1u) & 1u);
+        mbar_wait(&sh.placed[pslot], ((fseq - 1u) / FD_SLOTS) & 1u);
+        copy_out_frame(a, sh, bits0 + (size_t)pbuf * a.frame_words, sh.crc_part[pbuf], sh.out_offset[pslot], pend_body, tid);
     }
 }
 
@@ -1444,8 +1585,8 @@ __global__ void frx_minmax_out_kernel(const FrxQuant *q, int dtype, double *mm) 
 // ------------------------------------------------------------------------------------------
 // host launchers (called from frx_api.cu)
 // ------------------------------------------------------------------------------------------
-size_t frx_enc_smem_bytes(int frame_words) {
-    return ENC_SMALL_BYTES + 2 * RAW_STRIDE + TABS_BYTES + sizeof(uint32_t) * (size_t)frame_words;
+size_t frx_enc_smem_bytes(int frame_words, int dtype) {
+    return ENC_SMALL_BYTES + 2 * (128 + (size_t)FRX_MAX_BLOCK * frx_dtype_size(dtype)) + PCM_BYTES + TABS_BYTES + 2 * sizeof(uint32_t) * (size_t)frame_words;
 }
 
 size_t frx_minmax_raw_size() { return sizeof(MinMaxRaw); }
@@ -1476,7 +1617,7 @@ cudaError_t frx_launch_minmax(const frx_raster &r, const frx_tile *tiles_dev, co
 
 template <bool WIDE, int HISTN>
 static cudaError_t launch_encode_t(const EncArgs &a, int sm_count, cudaStream_t st) {
-    size_t smem = frx_enc_smem_bytes(a.frame_words);
+    size_t smem = frx_enc_smem_bytes(a.frame_words, a.dtype);
     cudaError_t e = cudaFuncSetAttribute(frx_encode_kernel<WIDE, HISTN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(frx_encode_kernel<WIDE, HISTN>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -1531,3 +1672,12 @@ cudaError_t frx_launch_quantize(const frx_raster &r, const frx_tile &t, const Fr
     if (minmax) frx_minmax_out_kernel<<<1, 32, 0, st>>>(q, r.dtype, minmax);
     return cudaGetLastError();
 }
+
+#ifdef FRX_DBG
+extern "C" void frx_debug_trace(unsigned long long *dev_ptr) { cudaMemcpyToSymbol(g_frx_trace, &dev_ptr, sizeof(dev_ptr)); }
+extern "C" void frx_debug_read(unsigned long long *out, int reset) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, g_frx_dbg, sizeof(unsigned long long) * 16);
+    if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(g_frx_dbg, z, sizeof(z)); }
+}
+#endif

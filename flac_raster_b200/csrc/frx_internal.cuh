@@ -52,7 +52,7 @@ struct DecArgs {
     int pcm_mode;
     int verify_crc;
 };
-size_t frx_enc_smem_bytes(int frame_words);
+size_t frx_enc_smem_bytes(int frame_words, int dtype);
 size_t frx_minmax_raw_size();
 cudaError_t frx_launch_minmax(const frx_raster &r, const frx_tile *tiles_dev, const uint32_t *unit_prefix_dev, int n_tiles,
                               uint32_t total_units, int unit_elems, void *mm_raw, FrxQuant *quant, cudaStream_t st);
