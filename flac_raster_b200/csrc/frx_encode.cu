@@ -180,6 +180,7 @@ struct BitW {
             idx += t >> 5; nb = (int)(t & 31u); acc = 0;
         } else nb = (int)t;
     }
+    __device__ __forceinline__ uint32_t bitpos() const { return idx * 32u + (uint32_t)nb; }
     __device__ __forceinline__ void finish() {
         if (nb > 0) {
             uint32_t w = (uint32_t)(acc >> 32);
@@ -726,7 +727,7 @@ __device__ __noinline__ void control_warp(const EncArgs &a, EncSmall &sh, unsign
             } else if (!lb.blocked) progress = true;
         }
         if (stop_issued && !lb_active && fseq_lb == fseq_iss) break;
-        if (!progress) __nanosleep(64);
+        if (!progress) __nanosleep(lb_active ? 100 : 400);
     }
 }
 // residual of one sample, lean paths (no overflow possible by construction)
@@ -973,16 +974,29 @@ __device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, in
     sh.lpc_ok = ok;
 }
 
-// K7b: Rice-code the thread's residuals.  `skip` leading samples are warm-up (thread 0 only), `nv` samples are valid.
-__device__ __forceinline__ void pack_rice(BitW &bw, const uint32_t *u, uint32_t kk, int skip, int nv) {
-    const uint32_t kmask = kk ? ((1u << kk) - 1u) : 0u;
+// OR an n-bit field (1..32 bits, v < 2^n) into the zeroed frame buffer at bit position p
+__device__ __forceinline__ void put_field(uint32_t *buf, uint32_t p, uint32_t v, uint32_t n) {
+    const uint64_t x = (uint64_t)v << (64u - (p & 31u) - n);
+    const uint32_t hi = (uint32_t)(x >> 32), lo = (uint32_t)x;
+    if (hi) atomicOr(&buf[p >> 5], hi);
+    if (lo) atomicOr(&buf[(p >> 5) + 1u], lo);
+}
+
+// K7b: Rice-code the thread's residuals straight into the (zeroed) frame buffer.  The unary zeros need no store at all;
+// every sample is one (k+1)-bit field -- stop bit plus low bits -- OR-ed at its bit position, straddling at most two
+// words.  `skip` leading samples are warm-up (thread 0 only), `nv` samples are valid, `plain` = neither applies.
+__device__ __forceinline__ void pack_rice(uint32_t *buf, uint32_t p, const uint32_t *u, uint32_t kk, int skip, int nv, bool plain) {
+    const uint32_t kmask = (1u << kk) - 1u;   // kk <= 30
+    const uint32_t len = kk + 1u;
 #pragma unroll
     for (int i = 0; i < FRX_SPT; i++) {
-        if (i >= skip && i < nv) {
-            const uint32_t uq = u[i] >> kk;
+        if (plain || (i >= skip && i < nv)) {
+            p += u[i] >> kk;
             const uint32_t code = (1u << kk) | (u[i] & kmask);
-            if (uq + 1u + kk <= 32u) bw.put(code, (int)(uq + 1u + kk));
-            else { bw.skip(uq); bw.put(code, (int)(kk + 1u)); }
+            const uint64_t v = (uint64_t)code << (64u - (p & 31u) - len);
+            atomicOr(&buf[p >> 5], (uint32_t)(v >> 32));
+            if ((uint32_t)v) atomicOr(&buf[(p >> 5) + 1u], (uint32_t)v);
+            p += len;
         }
     }
 }
@@ -1189,9 +1203,7 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
         const int slot = (int)(fseq & (FD_SLOTS - 1));
         const int buf = (int)(fseq & 1u);
         uint32_t *bits = bits0 + (size_t)buf * a.frame_words;
-        const long long cw0 = DBG_CLK();
         mbar_wait(&sh.full[unit & 1u], (unit >> 1) & 1u);
-        if (tid == 0) DBG_ADD(0, DBG_CLK() - cw0);
         const FrameDesc &fd = sh.fd[slot];
         const uint32_t f = fd.f;
         if (f == STOP_FRAME) { if (tid == 0) DBG_ADD(7, DBG_CLK() - ck0); break; }
@@ -1319,7 +1331,9 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                     sh.is_const = (f1 == 0) ? 1 : 0;   // sum |s[g]-s[g-1]| == 0  <=>  all samples equal
                     sh.fixed_order = fixed_order;
                 }
+                const long long ca0 = DBG_CLK();
                 if (fixed_order >= 0) analyse_partitions(sh, tabs + fixed_order * FRX_ENC_THREADS, 0, nsamp, fixed_order, po_max, kmax, wasted);
+                if (lane == 0) DBG_ADD(0, DBG_CLK() - ca0);
             } else if (warp == 1) {
                 uint32_t o32 = 0;
                 if (lane < 2) { for (int w2 = 0; w2 < NWARPS; w2++) o32 |= sh.wor[w2][lane]; }
@@ -1331,11 +1345,13 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                 if (lane <= max_lpc) { for (int w2 = 0; w2 < NWARPS; w2++) acs += sh.wac[w2][lane]; }
                 if (lane <= FRX_MAX_LPC) sh.autoc[lane] = acs;
                 __syncwarp();
+                const long long cl0 = DBG_CLK();
                 if (lane == 0) {
                     sh.magbits = magbits; sh.lean = lean ? 1 : 0;
                     sh.lpc_ok = 0;
                     if (max_lpc > 0 && nsamp > 4)
                         lpc_design<WIDE, HISTN>(sh, max_lpc, nsamp, wasted, a.bps - wasted, a.qlp_precision, magbits, lean);
+                    DBG_ADD(1, DBG_CLK() - cl0);
                 }
             }
             compute_sync();  // SB
@@ -1370,7 +1386,10 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                     tabs[5 * FRX_ENC_THREADS + tid] = ab;
                 }
                 compute_sync();  // SC
+                DBG_PH(8);
+                const long long cb0 = DBG_CLK();
                 if (warp == 1 && lpc_try0) analyse_partitions(sh, tabs + 5 * FRX_ENC_THREADS, 1, nsamp, lpc_order, po_max, kmax, 0);
+                if (tid == 32) DBG_ADD(2, DBG_CLK() - cb0);
                 compute_sync();  // SD
                 DBG_PH(12);
             }
@@ -1492,32 +1511,44 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                 mbar_arrive(&sh.sized[slot]);
             }
             // ---- K7b: pack ----
-            if (mybits) {
+            if (type >= 2) {
+                // every header field sits at a position known in closed form, so the lanes of warp 0 write them side by side
+                const uint32_t precision = (uint32_t)sh.precision;
+                const uint32_t p_warm = sub_start + 8u + (uint32_t)wasted;
+                const uint32_t p_lpc = p_warm + (uint32_t)order * (uint32_t)sbps;
+                const uint32_t p_rice = p_lpc + (type == 3 ? 9u + (uint32_t)order * precision : 0u);
+                if (tid == 0) {
+                    // subframe header: 0 | type(6) | wasted flag, then the wasted-bits count in unary
+                    const uint32_t tcode = type == 2 ? (8u | (uint32_t)order) : (32u | (uint32_t)(order - 1));
+                    put_field(bits, sub_start, (tcode << 1) | (wasted ? 1u : 0u), 8u);
+                    if (wasted) put_field(bits, sub_start + 8u + (uint32_t)wasted - 1u, 1u, 1u);
+                    if (type == 3) put_field(bits, p_lpc, ((precision - 1u) << 5) | ((uint32_t)sh.shift & 31u), 9u);
+                    put_field(bits, p_rice, ((rice2 ? 1u : 0u) << 4) | (uint32_t)po, 6u);
+                }
+                if (tid < order) {
+                    put_field(bits, p_warm + (uint32_t)tid * (uint32_t)sbps, (uint32_t)(pcm[PCM_IDX(tid)] >> wasted) & smask, (uint32_t)sbps);   // warm-up
+                    if (type == 3) put_field(bits, p_lpc + 9u + (uint32_t)tid * precision, (uint32_t)sh.qlp[tid] & ((1u << precision) - 1u), precision);
+                }
+                if (mybits) {
+                    uint32_t p = tid == 0 ? p_rice + 6u : start;
+                    if (g0 % psize == 0) {
+                        const uint32_t pb = rice2 ? 5u : 4u;
+                        if (kk) put_field(bits, p, kk, pb);
+                        p += pb;
+                    }
+                    pack_rice(bits, p, u, kk, skip, nv, plain);
+                }
+            } else if (mybits) {
                 BitW bw;
                 bw.init(bits, start);
                 if (tid == 0) {
-                    // subframe header: 0 | type(6) | wasted flag
-                    const uint32_t tcode = type == 0 ? 0u : type == 1 ? 1u : type == 2 ? (8u | (uint32_t)order) : (32u | (uint32_t)(order - 1));
-                    bw.put((tcode << 1) | (wasted ? 1u : 0u), 8);
+                    bw.put((type == 0 ? 0u : 2u) | (wasted ? 1u : 0u), 8);
                     if (wasted) { if (wasted > 1) bw.skip((uint32_t)wasted - 1u); bw.put(1u, 1); }
                 }
                 if (type == 0) {
                     if (tid == 0) bw.put((uint32_t)(pcm[PCM_IDX(0)] >> wasted) & smask, sbps);
-                } else if (type == 1) {
-                    for (int i = 0; i < nv; i++) bw.put((uint32_t)(pcm[PCM_IDX(g0 + i)] >> wasted) & smask, sbps);
                 } else {
-                    if (tid == 0) {
-                        for (int i = 0; i < order; i++) bw.put((uint32_t)(pcm[PCM_IDX(i)] >> wasted) & smask, sbps);   // warm-up samples
-                        if (type == 3) {
-                            bw.put((uint32_t)(sh.precision - 1), 4);
-                            bw.put((uint32_t)sh.shift & 31u, 5);
-                            const uint32_t pmask = (1u << sh.precision) - 1u;
-                            for (int j = 0; j < order; j++) bw.put((uint32_t)sh.qlp[j] & pmask, sh.precision);
-                        }
-                        bw.put(((rice2 ? 1u : 0u) << 4) | (uint32_t)po, 6);
-                    }
-                    if (g0 % psize == 0) bw.put(kk, rice2 ? 5 : 4);
-                    pack_rice(bw, u, kk, skip, nv);
+                    for (int i = 0; i < nv; i++) bw.put((uint32_t)(pcm[PCM_IDX(g0 + i)] >> wasted) & smask, sbps);
                 }
                 bw.finish();
             }
@@ -1531,13 +1562,13 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
         const uint32_t body_bytes = (bitpos + 7u) >> 3;
         const long long cc0 = DBG_CLK();
         crc_frame(a, sh, bits, sh.crc_part[buf], body_bytes, tid);
-        if (tid == 0) DBG_ADD(8, DBG_CLK() - cc0);
+
         if (pend) {
             const int pslot = (int)((fseq - 1u) & (FD_SLOTS - 1));
             uint32_t *pbits = bits0 + (size_t)(buf ^ 1) * a.frame_words;
             const long long cp0 = DBG_CLK();
             mbar_wait(&sh.placed[pslot], ((fseq - 1u) / FD_SLOTS) & 1u);
-            if (tid == 0) { DBG_ADD(1, DBG_CLK() - cp0); DBG_TRACE(f, 7); }
+            if (tid == 0) { DBG_TRACE(f, 7); }
             copy_out_frame(a, sh, pbits, sh.crc_part[buf ^ 1], sh.out_offset[pslot], pend_body, tid);
             compute_sync();  // all reads of the previous frame's buffer are done
             for (uint32_t j = tid; j <= (pend_body >> 2); j += FRX_ENC_THREADS) pbits[j] = 0u;

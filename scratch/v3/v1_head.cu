@@ -175,6 +175,7 @@ struct BitW {
             idx += t >> 5; nb = (int)(t & 31u); acc = 0;
         } else nb = (int)t;
     }
+    __device__ __forceinline__ uint32_t bitpos() const { return idx * 32u + (uint32_t)nb; }
     __device__ __forceinline__ void finish() {
         if (nb > 0) {
             uint32_t w = (uint32_t)(acc >> 32);

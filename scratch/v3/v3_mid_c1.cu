@@ -148,16 +148,29 @@ __device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, in
     sh.lpc_ok = ok;
 }
 
-// K7b: Rice-code the thread's residuals.  `skip` leading samples are warm-up (thread 0 only), `nv` samples are valid.
-__device__ __forceinline__ void pack_rice(BitW &bw, const uint32_t *u, uint32_t kk, int skip, int nv) {
-    const uint32_t kmask = kk ? ((1u << kk) - 1u) : 0u;
+// OR an n-bit field (1..32 bits, v < 2^n) into the zeroed frame buffer at bit position p
+__device__ __forceinline__ void put_field(uint32_t *buf, uint32_t p, uint32_t v, uint32_t n) {
+    const uint64_t x = (uint64_t)v << (64u - (p & 31u) - n);
+    const uint32_t hi = (uint32_t)(x >> 32), lo = (uint32_t)x;
+    if (hi) atomicOr(&buf[p >> 5], hi);
+    if (lo) atomicOr(&buf[(p >> 5) + 1u], lo);
+}
+
+// K7b: Rice-code the thread's residuals straight into the (zeroed) frame buffer.  The unary zeros need no store at all;
+// every sample is one (k+1)-bit field -- stop bit plus low bits -- OR-ed at its bit position, straddling at most two
+// words.  `skip` leading samples are warm-up (thread 0 only), `nv` samples are valid, `plain` = neither applies.
+__device__ __forceinline__ void pack_rice(uint32_t *buf, uint32_t p, const uint32_t *u, uint32_t kk, int skip, int nv, bool plain) {
+    const uint32_t kmask = (1u << kk) - 1u;   // kk <= 30
+    const uint32_t len = kk + 1u;
 #pragma unroll
     for (int i = 0; i < FRX_SPT; i++) {
-        if (i >= skip && i < nv) {
-            const uint32_t uq = u[i] >> kk;
+        if (plain || (i >= skip && i < nv)) {
+            p += u[i] >> kk;
             const uint32_t code = (1u << kk) | (u[i] & kmask);
-            if (uq + 1u + kk <= 32u) bw.put(code, (int)(uq + 1u + kk));
-            else { bw.skip(uq); bw.put(code, (int)(kk + 1u)); }
+            const uint64_t v = (uint64_t)code << (64u - (p & 31u) - len);
+            atomicOr(&buf[p >> 5], (uint32_t)(v >> 32));
+            if ((uint32_t)v) atomicOr(&buf[(p >> 5) + 1u], (uint32_t)v);
+            p += len;
         }
     }
 }

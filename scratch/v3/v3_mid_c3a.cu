@@ -42,9 +42,7 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
         const int slot = (int)(fseq & (FD_SLOTS - 1));
         const int buf = (int)(fseq & 1u);
         uint32_t *bits = bits0 + (size_t)buf * a.frame_words;
-        const long long cw0 = DBG_CLK();
         mbar_wait(&sh.full[unit & 1u], (unit >> 1) & 1u);
-        if (tid == 0) DBG_ADD(0, DBG_CLK() - cw0);
         const FrameDesc &fd = sh.fd[slot];
         const uint32_t f = fd.f;
         if (f == STOP_FRAME) { if (tid == 0) DBG_ADD(7, DBG_CLK() - ck0); break; }
@@ -172,7 +170,9 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                     sh.is_const = (f1 == 0) ? 1 : 0;   // sum |s[g]-s[g-1]| == 0  <=>  all samples equal
                     sh.fixed_order = fixed_order;
                 }
+                const long long ca0 = DBG_CLK();
                 if (fixed_order >= 0) analyse_partitions(sh, tabs + fixed_order * FRX_ENC_THREADS, 0, nsamp, fixed_order, po_max, kmax, wasted);
+                if (lane == 0) DBG_ADD(0, DBG_CLK() - ca0);
             } else if (warp == 1) {
                 uint32_t o32 = 0;
                 if (lane < 2) { for (int w2 = 0; w2 < NWARPS; w2++) o32 |= sh.wor[w2][lane]; }
@@ -184,11 +184,13 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                 if (lane <= max_lpc) { for (int w2 = 0; w2 < NWARPS; w2++) acs += sh.wac[w2][lane]; }
                 if (lane <= FRX_MAX_LPC) sh.autoc[lane] = acs;
                 __syncwarp();
+                const long long cl0 = DBG_CLK();
                 if (lane == 0) {
                     sh.magbits = magbits; sh.lean = lean ? 1 : 0;
                     sh.lpc_ok = 0;
                     if (max_lpc > 0 && nsamp > 4)
                         lpc_design<WIDE, HISTN>(sh, max_lpc, nsamp, wasted, a.bps - wasted, a.qlp_precision, magbits, lean);
+                    DBG_ADD(1, DBG_CLK() - cl0);
                 }
             }
             compute_sync();  // SB

@@ -28,7 +28,10 @@
                     tabs[5 * FRX_ENC_THREADS + tid] = ab;
                 }
                 compute_sync();  // SC
+                DBG_PH(8);
+                const long long cb0 = DBG_CLK();
                 if (warp == 1 && lpc_try0) analyse_partitions(sh, tabs + 5 * FRX_ENC_THREADS, 1, nsamp, lpc_order, po_max, kmax, 0);
+                if (tid == 32) DBG_ADD(2, DBG_CLK() - cb0);
                 compute_sync();  // SD
                 DBG_PH(12);
             }
@@ -150,32 +153,44 @@
                 mbar_arrive(&sh.sized[slot]);
             }
             // ---- K7b: pack ----
-            if (mybits) {
+            if (type >= 2) {
+                // every header field sits at a position known in closed form, so the lanes of warp 0 write them side by side
+                const uint32_t precision = (uint32_t)sh.precision;
+                const uint32_t p_warm = sub_start + 8u + (uint32_t)wasted;
+                const uint32_t p_lpc = p_warm + (uint32_t)order * (uint32_t)sbps;
+                const uint32_t p_rice = p_lpc + (type == 3 ? 9u + (uint32_t)order * precision : 0u);
+                if (tid == 0) {
+                    // subframe header: 0 | type(6) | wasted flag, then the wasted-bits count in unary
+                    const uint32_t tcode = type == 2 ? (8u | (uint32_t)order) : (32u | (uint32_t)(order - 1));
+                    put_field(bits, sub_start, (tcode << 1) | (wasted ? 1u : 0u), 8u);
+                    if (wasted) put_field(bits, sub_start + 8u + (uint32_t)wasted - 1u, 1u, 1u);
+                    if (type == 3) put_field(bits, p_lpc, ((precision - 1u) << 5) | ((uint32_t)sh.shift & 31u), 9u);
+                    put_field(bits, p_rice, ((rice2 ? 1u : 0u) << 4) | (uint32_t)po, 6u);
+                }
+                if (tid < order) {
+                    put_field(bits, p_warm + (uint32_t)tid * (uint32_t)sbps, (uint32_t)(pcm[PCM_IDX(tid)] >> wasted) & smask, (uint32_t)sbps);   // warm-up
+                    if (type == 3) put_field(bits, p_lpc + 9u + (uint32_t)tid * precision, (uint32_t)sh.qlp[tid] & ((1u << precision) - 1u), precision);
+                }
+                if (mybits) {
+                    uint32_t p = tid == 0 ? p_rice + 6u : start;
+                    if (g0 % psize == 0) {
+                        const uint32_t pb = rice2 ? 5u : 4u;
+                        if (kk) put_field(bits, p, kk, pb);
+                        p += pb;
+                    }
+                    pack_rice(bits, p, u, kk, skip, nv, plain);
+                }
+            } else if (mybits) {
                 BitW bw;
                 bw.init(bits, start);
                 if (tid == 0) {
-                    // subframe header: 0 | type(6) | wasted flag
-                    const uint32_t tcode = type == 0 ? 0u : type == 1 ? 1u : type == 2 ? (8u | (uint32_t)order) : (32u | (uint32_t)(order - 1));
-                    bw.put((tcode << 1) | (wasted ? 1u : 0u), 8);
+                    bw.put((type == 0 ? 0u : 2u) | (wasted ? 1u : 0u), 8);
                     if (wasted) { if (wasted > 1) bw.skip((uint32_t)wasted - 1u); bw.put(1u, 1); }
                 }
                 if (type == 0) {
                     if (tid == 0) bw.put((uint32_t)(pcm[PCM_IDX(0)] >> wasted) & smask, sbps);
-                } else if (type == 1) {
-                    for (int i = 0; i < nv; i++) bw.put((uint32_t)(pcm[PCM_IDX(g0 + i)] >> wasted) & smask, sbps);
                 } else {
-                    if (tid == 0) {
-                        for (int i = 0; i < order; i++) bw.put((uint32_t)(pcm[PCM_IDX(i)] >> wasted) & smask, sbps);   // warm-up samples
-                        if (type == 3) {
-                            bw.put((uint32_t)(sh.precision - 1), 4);
-                            bw.put((uint32_t)sh.shift & 31u, 5);
-                            const uint32_t pmask = (1u << sh.precision) - 1u;
-                            for (int j = 0; j < order; j++) bw.put((uint32_t)sh.qlp[j] & pmask, sh.precision);
-                        }
-                        bw.put(((rice2 ? 1u : 0u) << 4) | (uint32_t)po, 6);
-                    }
-                    if (g0 % psize == 0) bw.put(kk, rice2 ? 5 : 4);
-                    pack_rice(bw, u, kk, skip, nv);
+                    for (int i = 0; i < nv; i++) bw.put((uint32_t)(pcm[PCM_IDX(g0 + i)] >> wasted) & smask, sbps);
                 }
                 bw.finish();
             }
@@ -189,13 +204,13 @@
         const uint32_t body_bytes = (bitpos + 7u) >> 3;
         const long long cc0 = DBG_CLK();
         crc_frame(a, sh, bits, sh.crc_part[buf], body_bytes, tid);
-        if (tid == 0) DBG_ADD(8, DBG_CLK() - cc0);
+
         if (pend) {
             const int pslot = (int)((fseq - 1u) & (FD_SLOTS - 1));
             uint32_t *pbits = bits0 + (size_t)(buf ^ 1) * a.frame_words;
             const long long cp0 = DBG_CLK();
             mbar_wait(&sh.placed[pslot], ((fseq - 1u) / FD_SLOTS) & 1u);
-            if (tid == 0) { DBG_ADD(1, DBG_CLK() - cp0); DBG_TRACE(f, 7); }
+            if (tid == 0) { DBG_TRACE(f, 7); }
             copy_out_frame(a, sh, pbits, sh.crc_part[buf ^ 1], sh.out_offset[pslot], pend_body, tid);
             compute_sync();  // all reads of the previous frame's buffer are done
             for (uint32_t j = tid; j <= (pend_body >> 2); j += FRX_ENC_THREADS) pbits[j] = 0u;
