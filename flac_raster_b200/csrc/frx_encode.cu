@@ -278,9 +278,9 @@ struct EncSmall {
     int lpc_ok, lpc_order, shift, precision, lpc_narrow;
     int32_t qlp[FRX_MAX_LPC];
     int32_t warm[FRX_MAX_LPC];
-    uint32_t kparam[2][64];                      // candidate 0 = fixed, 1 = lpc
-    int cand_po[2], cand_rice2[2];
-    uint64_t cand_bits[2];
+    uint32_t kparam[2][128];                     // candidate 0 = fixed, 1 = lpc; level L's parameters start at (1 << L) - 1
+    uint64_t lvl_bits[2][8];                     // Rice search: estimated bits of partition order L (~0: not evaluated)
+    uint32_t lvl_big[2][8];                      // ... and whether it needs 5-bit parameters (RICE2)
     // reductions
     uint64_t wfix[NWARPS][5];
     uint32_t wor[NWARPS][2];
@@ -374,17 +374,71 @@ __device__ __noinline__ void analyse_partitions(EncSmall &sh, const uint64_t *ta
             sum += o;                                    // valid in lanes that are multiples of 2*step
         }
     }
-    // publish parameters of the best level
-    if (best_po == 6) { sh.kparam[cand][2 * lane] = kbest0; sh.kparam[cand][2 * lane + 1] = kbest1; }
+    // publish in the per-level format pick_level() reads: only the winning level carries a finite cost
+    uint32_t *kp = &sh.kparam[cand][(1 << best_po) - 1];
+    if (best_po == 6) { kp[2 * lane] = kbest0; kp[2 * lane + 1] = kbest1; }
     else {
         const int step = 1 << (F - best_po);
-        if ((lane & (step - 1)) == 0 && lane < (1 << F)) sh.kparam[cand][lane >> (F - best_po)] = kbest0;
+        if ((lane & (step - 1)) == 0 && lane < (1 << F)) kp[lane >> (F - best_po)] = kbest0;
     }
     uint32_t big = __ballot_sync(FULLMASK, kbest0 >= 15u || (best_po == 6 && kbest1 >= 15u));
-    if (lane == 0) { sh.cand_po[cand] = best_po; sh.cand_bits[cand] = best; sh.cand_rice2[cand] = big ? 1 : 0; }
+    if (lane < 8) { sh.lvl_bits[cand][lane] = (lane == best_po) ? best : ~0ull; sh.lvl_big[cand][lane] = big ? 1u : 0u; }
     __syncwarp();
 }
 
+// The same search for ONE partition order of a full 4096-sample frame (2^L partitions of 256 >> L threads each): the compute
+// warps run it side by side, warp L on level L.  The per-thread |r| sums must fit 32 bits (the lean paths guarantee it).
+__device__ __noinline__ void analyse_level(EncSmall &sh, const uint64_t *tabs, int cand, int L, int pred_order, uint32_t kmax, int rsh) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t nfull = (uint32_t)FRX_MAX_BLOCK >> L;
+    uint32_t *kp = &sh.kparam[cand][(1 << L) - 1];
+    uint64_t bits = 0;
+    uint32_t big = 0;
+    if (L <= 3) {
+        // a row of 32 threads never straddles a partition: reduce the eight rows (lane t keeps row t), then groups of rows
+        uint64_t mine = 0;
+#pragma unroll
+        for (int t = 0; t < 8; t++) {
+            const uint64_t s = warp_sum_u32_wide((uint32_t)(tabs[32 * t + lane] >> rsh));
+            if (lane == t) mine = s;
+        }
+        const int g = 8 >> L;
+        for (int o = 1; o < g; o <<= 1) mine += __shfl_xor_sync(FULLMASK, mine, o);
+        if (lane < 8 && (lane & (g - 1)) == 0) {
+            const int p = lane >> (3 - L);
+            const uint32_t n = nfull - (p == 0 ? (uint32_t)pred_order : 0u);
+            const uint32_t k = rice_param(n, mine, kmax);
+            bits = rice_estimate(k, n, mine);
+            kp[p] = k;
+            big = k >= 15u ? 1u : 0u;
+        }
+    } else {
+        const int T = FRX_ENC_THREADS >> L;            // threads per partition: 16, 8, 4
+        for (int p = lane; p < (1 << L); p += 32) {
+            uint64_t s = 0;
+            for (int i = 0; i < T; i++) s += tabs[p * T + i] >> rsh;
+            const uint32_t n = nfull - (p == 0 ? (uint32_t)pred_order : 0u);
+            const uint32_t k = rice_param(n, s, kmax);
+            bits += rice_estimate(k, n, s);
+            kp[p] = k;
+            big |= k >= 15u ? 1u : 0u;
+        }
+    }
+    bits = warp_sum_u64(bits) + 6;
+    const uint32_t anybig = __ballot_sync(FULLMASK, big != 0u);
+    if (lane == 0) { sh.lvl_bits[cand][L] = bits; sh.lvl_big[cand][L] = anybig ? 1u : 0u; }
+}
+
+// best partition order of a candidate: highest order first, a lower one only when strictly cheaper (libFLAC's loop)
+__device__ __forceinline__ void pick_level(const EncSmall &sh, int cand, int po_max, int &po, uint64_t &bits, bool &rice2) {
+    uint64_t best = ~0ull;
+    int bp = 0;
+    for (int L = po_max; L >= 0; L--) {
+        const uint64_t b = sh.lvl_bits[cand][L];
+        if (b < best) { best = b; bp = L; }
+    }
+    po = bp; bits = best; rice2 = sh.lvl_big[cand][bp] != 0u;
+}
 // ------------------------------------------------------------------------------------------
 // K1: raw staging buffer -> PCM in shared memory.  Thread t owns samples [16t, 16t+16).
 // ------------------------------------------------------------------------------------------
@@ -880,19 +934,21 @@ __device__ __noinline__ float tukey_w(int g, int n) {
     return 1.0f;
 }
 
-// K4 on one thread, float32, everything in registers (MAXO = largest order of the compression level):
-// Levinson-Durbin, expected-bits order pick, coefficient quantisation (libFLAC's scheme with error feedback).
+// K4 on one warp, float32 (MAXO = largest order of the compression level): every lane runs the Levinson-Durbin recursion
+// in registers; lane o-1 prices order o (expected bits), lane j owns coefficient j for the row store, the |max| and the
+// quantised value, so the serial part is the recursion and the error-feedback rounding only (libFLAC's scheme).
 // The decisions are ours; the bitstream stays exact because the residual is computed from the quantised integers.
 template <bool WIDE, int MAXO>
-__device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, int wasted, int sbps, int qlp_precision, int magbits, bool lean) {
-    sh.lpc_ok = 0;
+__device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, int wasted, int sbps, int qlp_precision, int magbits, bool lean,
+                                        int lane) {
+    if (lane == 0) sh.lpc_ok = 0;
     const float a0 = sh.autoc[0];
     if (!(a0 > 0.f)) return;
     const float inv0 = 1.0f / a0;
-    float an[MAXO + 1], lpc[MAXO], errs[MAXO];
+    float an[MAXO + 1], lpc[MAXO];
 #pragma unroll
     for (int i = 0; i <= MAXO; i++) an[i] = sh.autoc[i] * inv0;   // normalised autocorrelation
-    float err = 1.0f;
+    float err = 1.0f, myerr = 0.f;
     int mo = max_lpc;
 #pragma unroll
     for (int i = 0; i < MAXO; i++) {
@@ -910,36 +966,36 @@ __device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, in
             }
             if (i & 1) lpc[i >> 1] += lpc[i >> 1] * r;
             err *= (1.0f - r * r);
+            float mine = 0.f;                      // lane j stores predictor coefficient j of order i+1
 #pragma unroll
-            for (int j = 0; j <= i; j++) sh.lpc_rows[i][j] = -lpc[j];
-            errs[i] = err;
+            for (int j = 0; j <= i; j++) if (lane == j) mine = -lpc[j];
+            if (lane <= i) sh.lpc_rows[i][lane] = mine;
+            if (lane == i) myerr = err;
             if (!(err > 0.f)) mo = i + 1;
-        } else errs[i] = 0.f;
-    }
-    // expected bits per order; errs are relative to autoc[0] (taken before the wasted-bit shift)
-    float best_bits = 3.0e38f;
-    int best = 1;
-    const float lscale = __log2f(a0) + __log2f(0.5f / (float)nsamp) - 2.0f * (float)wasted;
-#pragma unroll
-    for (int o = 1; o <= MAXO; o++) {
-        if (o <= mo) {
-            const float e = errs[o - 1];
-            const float bpsr = e > 0.f ? fmaxf(0.f, 0.5f * (__log2f(e) + lscale)) : 0.f;
-            const float b = bpsr * (float)(nsamp - o) + (float)(o * (sbps + qlp_precision));
-            if (b < best_bits) { best_bits = b; best = o; }
         }
     }
-    const int order = best;
+    __syncwarp();
+    // expected bits per order; errs are relative to autoc[0] (taken before the wasted-bit shift)
+    const float lscale = __log2f(a0) + __log2f(0.5f / (float)nsamp) - 2.0f * (float)wasted;
+    uint32_t key = 0xFFFFFFFFu;
+    if (lane < mo) {
+        const int o = lane + 1;
+        const float bpsr = myerr > 0.f ? fmaxf(0.f, 0.5f * (__log2f(myerr) + lscale)) : 0.f;
+        const float b = bpsr * (float)(nsamp - o) + (float)(o * (sbps + qlp_precision));
+        key = __float_as_uint(b);                  // b >= 0: the bit pattern orders like the value
+        if (!(b >= 0.f)) key = 0xFFFFFFFEu;
+    }
+    const uint32_t kmin = __reduce_min_sync(FULLMASK, key);
+    const int order = __ffs((int)__ballot_sync(FULLMASK, key == kmin));   // lowest order among ties
     int precision = qlp_precision;
     if (!WIDE) {
         const int lim = 32 - sbps - (31 - __clz(order));
         if (lim < precision) precision = lim;
     }
     if (precision < 5) return;
-    const float *row = sh.lpc_rows[order - 1];
-    float cmax = 0.f;
-    for (int j = 0; j < order; j++) cmax = fmaxf(cmax, fabsf(row[j]));
-    if (!(cmax > 0.f)) return;
+    const float rv = lane < order ? sh.lpc_rows[order - 1][lane] : 0.f;
+    const float cmax = __uint_as_float(__reduce_max_sync(FULLMASK, __float_as_uint(fabsf(rv))));
+    if (!(cmax > 0.f) || !(cmax < 3.0e38f)) return;
     int e2;
     (void)frexpf(cmax, &e2);
     int shift = (precision - 1) - (e2 - 1) - 1;
@@ -949,16 +1005,20 @@ __device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, in
     float error = 0.f;
     long long sumabs = 0;
     const float scale = (float)(1 << shift);
-    for (int j = 0; j < order; j++) {
-        error += row[j] * scale;
-        int qq = __float2int_rn(error);
-        if (qq > qmax) qq = qmax; else if (qq < qmin) qq = qmin;
-        error -= (float)qq;
-        sh.qlp[j] = qq;
-        sumabs += qq < 0 ? -qq : qq;
+    int myq = 0;
+#pragma unroll
+    for (int j = 0; j < MAXO; j++) {
+        const float c = __shfl_sync(FULLMASK, rv, j);
+        if (j < order) {
+            error += c * scale;
+            int qq = __float2int_rn(error);
+            if (qq > qmax) qq = qmax; else if (qq < qmin) qq = qmin;
+            error -= (float)qq;
+            if (lane == j) myq = qq;
+            sumabs += qq < 0 ? -qq : qq;
+        }
     }
-    for (int j = order; j < FRX_MAX_LPC; j++) sh.qlp[j] = 0;
-    sh.lpc_order = order; sh.shift = shift; sh.precision = precision;
+    if (lane < FRX_MAX_LPC) sh.qlp[lane] = myq;
     int ok = 1, narrow = 1;
     if (WIDE) {
         // |prediction sum| <= sumabs * 2^mag; the residual bound decides which arithmetic is safe
@@ -970,8 +1030,8 @@ __device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, in
             if (Bnd >= (1ll << 27)) ok = 0;   // keeps 32-bit residual sums exact; such wild predictors never win anyway
         }
     }
-    sh.lpc_narrow = narrow;
-    sh.lpc_ok = ok;
+    if (lane == 0) { sh.lpc_order = order; sh.shift = shift; sh.precision = precision; sh.lpc_narrow = narrow; sh.lpc_ok = ok; }
+    __syncwarp();
 }
 
 // OR an n-bit field (1..32 bits, v < 2^n) into the zeroed frame buffer at bit position p
@@ -1308,50 +1368,45 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
             }
             compute_sync();  // SA: per-warp partials and tabs[0..4] are in shared memory
             DBG_PH(10);
-            // ---- warp 0: fixed-order decision + Rice search of the fixed candidate; warp 1: LPC design ----
-            if (warp == 0) {
+            // ---- every warp: fixed-order decision (cheap, redundant).  Warps 0..6: Rice search of the fixed candidate, one
+            //      partition order each; warp 7: LPC design ----
+            {
                 uint64_t tot = 0;
                 uint32_t o32 = 0;
                 if (lane < 5) { for (int w2 = 0; w2 < NWARPS; w2++) tot += sh.wfix[w2][lane]; }
                 else if (lane < 7) { for (int w2 = 0; w2 < NWARPS; w2++) o32 |= sh.wor[w2][lane - 5]; }
-                const uint32_t all_or = __shfl_sync(FULLMASK, o32, 5);
-                const int wasted = all_or ? (__ffs((int)all_or) - 1) : 0;
-                const uint64_t f1 = __shfl_sync(FULLMASK, tot, 1);
-                uint64_t bestv = (lane < 5) ? tot : ~0ull;   // best fixed order among lanes 0..4 (lowest order wins ties)
-                int besto = lane;
-                for (int o = 1; o < 8; o <<= 1) {
-                    const uint64_t ov = __shfl_xor_sync(FULLMASK, bestv, o);
-                    const int oo = __shfl_xor_sync(FULLMASK, besto, o);
-                    if (ov < bestv || (ov == bestv && oo < besto)) { bestv = ov; besto = oo; }
-                }
-                besto = __shfl_sync(FULLMASK, besto, 0);
-                const int fixed_order = (nsamp > 4) ? besto : -1;
-                if (lane == 0) {
-                    sh.wasted = wasted;
-                    sh.is_const = (f1 == 0) ? 1 : 0;   // sum |s[g]-s[g-1]| == 0  <=>  all samples equal
-                    sh.fixed_order = fixed_order;
-                }
-                const long long ca0 = DBG_CLK();
-                if (fixed_order >= 0) analyse_partitions(sh, tabs + fixed_order * FRX_ENC_THREADS, 0, nsamp, fixed_order, po_max, kmax, wasted);
-                if (lane == 0) DBG_ADD(0, DBG_CLK() - ca0);
-            } else if (warp == 1) {
-                uint32_t o32 = 0;
-                if (lane < 2) { for (int w2 = 0; w2 < NWARPS; w2++) o32 |= sh.wor[w2][lane]; }
-                const uint32_t all_or = __shfl_sync(FULLMASK, o32, 0), all_abs = __shfl_sync(FULLMASK, o32, 1);
+                const uint32_t all_or = __shfl_sync(FULLMASK, o32, 5), all_abs = __shfl_sync(FULLMASK, o32, 6);
                 const int wasted = all_or ? (__ffs((int)all_or) - 1) : 0;
                 const int magbits = WIDE ? 32 - __clz((int)all_abs) : 15;  // bits of the largest magnitude
                 const bool lean = !WIDE || magbits <= 23;
-                float acs = 0.f;
-                if (lane <= max_lpc) { for (int w2 = 0; w2 < NWARPS; w2++) acs += sh.wac[w2][lane]; }
-                if (lane <= FRX_MAX_LPC) sh.autoc[lane] = acs;
-                __syncwarp();
-                const long long cl0 = DBG_CLK();
-                if (lane == 0) {
-                    sh.magbits = magbits; sh.lean = lean ? 1 : 0;
-                    sh.lpc_ok = 0;
+                if (warp == NWARPS - 1) {
+                    float acs = 0.f;
+                    if (lane <= max_lpc) { for (int w2 = 0; w2 < NWARPS; w2++) acs += sh.wac[w2][lane]; }
+                    if (lane <= FRX_MAX_LPC) sh.autoc[lane] = acs;
+                    if (lane == 0) { sh.magbits = magbits; sh.lean = lean ? 1 : 0; sh.lpc_ok = 0; }
+                    __syncwarp();
                     if (max_lpc > 0 && nsamp > 4)
-                        lpc_design<WIDE, HISTN>(sh, max_lpc, nsamp, wasted, a.bps - wasted, a.qlp_precision, magbits, lean);
-                    DBG_ADD(1, DBG_CLK() - cl0);
+                        lpc_design<WIDE, HISTN>(sh, max_lpc, nsamp, wasted, a.bps - wasted, a.qlp_precision, magbits, lean, lane);
+                } else {
+                    const uint64_t f1 = __shfl_sync(FULLMASK, tot, 1);
+                    uint64_t bestv = (lane < 5) ? tot : ~0ull;   // best fixed order among lanes 0..4 (lowest order wins ties)
+                    int besto = lane;
+                    for (int o = 1; o < 8; o <<= 1) {
+                        const uint64_t ov = __shfl_xor_sync(FULLMASK, bestv, o);
+                        const int oo = __shfl_xor_sync(FULLMASK, besto, o);
+                        if (ov < bestv || (ov == bestv && oo < besto)) { bestv = ov; besto = oo; }
+                    }
+                    besto = __shfl_sync(FULLMASK, besto, 0);
+                    const int fixed_order = (nsamp > 4) ? besto : -1;
+                    if (warp == 0 && lane == 0) {
+                        sh.wasted = wasted;
+                        sh.is_const = (f1 == 0) ? 1 : 0;   // sum |s[g]-s[g-1]| == 0  <=>  all samples equal
+                        sh.fixed_order = fixed_order;
+                    }
+                    if (fixed_order >= 0 && lean) {          // fat data: fat_search redoes the fixed candidate in 64 bits
+                        if (full) { if (warp <= po_max) analyse_level(sh, tabs + fixed_order * FRX_ENC_THREADS, 0, warp, fixed_order, kmax, wasted); }
+                        else if (warp == 0) analyse_partitions(sh, tabs + fixed_order * FRX_ENC_THREADS, 0, nsamp, fixed_order, po_max, kmax, wasted);
+                    }
                 }
             }
             compute_sync();  // SB
@@ -1387,9 +1442,10 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                 }
                 compute_sync();  // SC
                 DBG_PH(8);
-                const long long cb0 = DBG_CLK();
-                if (warp == 1 && lpc_try0) analyse_partitions(sh, tabs + 5 * FRX_ENC_THREADS, 1, nsamp, lpc_order, po_max, kmax, 0);
-                if (tid == 32) DBG_ADD(2, DBG_CLK() - cb0);
+                if (lpc_try0) {
+                    if (full) { if (warp <= po_max) analyse_level(sh, tabs + 5 * FRX_ENC_THREADS, 1, warp, lpc_order, kmax, 0); }
+                    else if (warp == 1) analyse_partitions(sh, tabs + 5 * FRX_ENC_THREADS, 1, nsamp, lpc_order, po_max, kmax, 0);
+                }
                 compute_sync();  // SD
                 DBG_PH(12);
             }
@@ -1399,33 +1455,35 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
 
             // ---- choose ----
             const uint64_t verb_bits = 8ull + (uint64_t)wasted + (uint64_t)nsamp * (uint64_t)sbps;
-            int type = 1, order = 0, cand = 0;
+            int type = 1, order = 0, cand = 0, po = 0;
+            bool rice2 = false;
             uint64_t best_bits = verb_bits;
             if (is_const) { type = 0; best_bits = 8ull + wasted + sbps; }
             else {
                 if (fixed_order >= 0) {
-                    const uint64_t b = 8ull + wasted + (uint64_t)fixed_order * sbps + sh.cand_bits[0];
-                    if (b < best_bits) { best_bits = b; type = 2; order = fixed_order; cand = 0; }
+                    int lp; uint64_t lb; bool l2;
+                    pick_level(sh, 0, po_max, lp, lb, l2);
+                    const uint64_t b = 8ull + wasted + (uint64_t)fixed_order * sbps + lb;
+                    if (b < best_bits) { best_bits = b; type = 2; order = fixed_order; cand = 0; po = lp; rice2 = l2; }
                 }
                 if (lpc_try) {
-                    const uint64_t b = 8ull + wasted + 9ull + (uint64_t)lpc_order * (uint64_t)(sh.precision + sbps) + sh.cand_bits[1];
-                    if (b < best_bits) { best_bits = b; type = 3; order = lpc_order; cand = 1; }
+                    int lp; uint64_t lb; bool l2;
+                    pick_level(sh, 1, po_max, lp, lb, l2);
+                    const uint64_t b = 8ull + wasted + 9ull + (uint64_t)lpc_order * (uint64_t)(sh.precision + sbps) + lb;
+                    if (b < best_bits) { best_bits = b; type = 3; order = lpc_order; cand = 1; po = lp; rice2 = l2; }
                 }
             }
             // ---- K7a: winner's residuals (zig-zag folded), exact bit count per thread, block scan ----
             const uint32_t sub_start = bitpos;
             const uint32_t smask = sbps >= 32 ? 0xFFFFFFFFu : ((1u << sbps) - 1u);
             uint32_t u[FRX_SPT];
-            int po = 0, psize = nsamp;
+            int psize = nsamp;
             uint32_t kk = 0;
-            bool rice2 = false;
             uint32_t mybits = 0;
             const int skip = (tid == 0) ? order : 0;
             if (type >= 2) {
-                po = sh.cand_po[cand];
                 psize = nsamp >> po;
-                kk = sh.kparam[cand][min(g0 / psize, (1 << po) - 1)];
-                rice2 = sh.cand_rice2[cand] != 0;
+                kk = sh.kparam[cand][(1 << po) - 1 + min(g0 / psize, (1 << po) - 1)];
                 if (type == 2 || (WIDE && !lean)) {
                     // fixed winner (4 ops per sample) or a fat-path LPC winner: recompute from the PCM
                     int32_t s[HISTN + FRX_SPT];

@@ -42,14 +42,68 @@ __device__ __noinline__ void analyse_partitions(EncSmall &sh, const uint64_t *ta
             sum += o;                                    // valid in lanes that are multiples of 2*step
         }
     }
-    // publish parameters of the best level
-    if (best_po == 6) { sh.kparam[cand][2 * lane] = kbest0; sh.kparam[cand][2 * lane + 1] = kbest1; }
+    // publish in the per-level format pick_level() reads: only the winning level carries a finite cost
+    uint32_t *kp = &sh.kparam[cand][(1 << best_po) - 1];
+    if (best_po == 6) { kp[2 * lane] = kbest0; kp[2 * lane + 1] = kbest1; }
     else {
         const int step = 1 << (F - best_po);
-        if ((lane & (step - 1)) == 0 && lane < (1 << F)) sh.kparam[cand][lane >> (F - best_po)] = kbest0;
+        if ((lane & (step - 1)) == 0 && lane < (1 << F)) kp[lane >> (F - best_po)] = kbest0;
     }
     uint32_t big = __ballot_sync(FULLMASK, kbest0 >= 15u || (best_po == 6 && kbest1 >= 15u));
-    if (lane == 0) { sh.cand_po[cand] = best_po; sh.cand_bits[cand] = best; sh.cand_rice2[cand] = big ? 1 : 0; }
+    if (lane < 8) { sh.lvl_bits[cand][lane] = (lane == best_po) ? best : ~0ull; sh.lvl_big[cand][lane] = big ? 1u : 0u; }
     __syncwarp();
 }
 
+// The same search for ONE partition order of a full 4096-sample frame (2^L partitions of 256 >> L threads each): the compute
+// warps run it side by side, warp L on level L.  The per-thread |r| sums must fit 32 bits (the lean paths guarantee it).
+__device__ __noinline__ void analyse_level(EncSmall &sh, const uint64_t *tabs, int cand, int L, int pred_order, uint32_t kmax, int rsh) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t nfull = (uint32_t)FRX_MAX_BLOCK >> L;
+    uint32_t *kp = &sh.kparam[cand][(1 << L) - 1];
+    uint64_t bits = 0;
+    uint32_t big = 0;
+    if (L <= 3) {
+        // a row of 32 threads never straddles a partition: reduce the eight rows (lane t keeps row t), then groups of rows
+        uint64_t mine = 0;
+#pragma unroll
+        for (int t = 0; t < 8; t++) {
+            const uint64_t s = warp_sum_u32_wide((uint32_t)(tabs[32 * t + lane] >> rsh));
+            if (lane == t) mine = s;
+        }
+        const int g = 8 >> L;
+        for (int o = 1; o < g; o <<= 1) mine += __shfl_xor_sync(FULLMASK, mine, o);
+        if (lane < 8 && (lane & (g - 1)) == 0) {
+            const int p = lane >> (3 - L);
+            const uint32_t n = nfull - (p == 0 ? (uint32_t)pred_order : 0u);
+            const uint32_t k = rice_param(n, mine, kmax);
+            bits = rice_estimate(k, n, mine);
+            kp[p] = k;
+            big = k >= 15u ? 1u : 0u;
+        }
+    } else {
+        const int T = FRX_ENC_THREADS >> L;            // threads per partition: 16, 8, 4
+        for (int p = lane; p < (1 << L); p += 32) {
+            uint64_t s = 0;
+            for (int i = 0; i < T; i++) s += tabs[p * T + i] >> rsh;
+            const uint32_t n = nfull - (p == 0 ? (uint32_t)pred_order : 0u);
+            const uint32_t k = rice_param(n, s, kmax);
+            bits += rice_estimate(k, n, s);
+            kp[p] = k;
+            big |= k >= 15u ? 1u : 0u;
+        }
+    }
+    bits = warp_sum_u64(bits) + 6;
+    const uint32_t anybig = __ballot_sync(FULLMASK, big != 0u);
+    if (lane == 0) { sh.lvl_bits[cand][L] = bits; sh.lvl_big[cand][L] = anybig ? 1u : 0u; }
+}
+
+// best partition order of a candidate: highest order first, a lower one only when strictly cheaper (libFLAC's loop)
+__device__ __forceinline__ void pick_level(const EncSmall &sh, int cand, int po_max, int &po, uint64_t &bits, bool &rice2) {
+    uint64_t best = ~0ull;
+    int bp = 0;
+    for (int L = po_max; L >= 0; L--) {
+        const uint64_t b = sh.lvl_bits[cand][L];
+        if (b < best) { best = b; bp = L; }
+    }
+    po = bp; bits = best; rice2 = sh.lvl_big[cand][bp] != 0u;
+}

@@ -54,9 +54,9 @@ struct EncSmall {
     int lpc_ok, lpc_order, shift, precision, lpc_narrow;
     int32_t qlp[FRX_MAX_LPC];
     int32_t warm[FRX_MAX_LPC];
-    uint32_t kparam[2][64];                      // candidate 0 = fixed, 1 = lpc
-    int cand_po[2], cand_rice2[2];
-    uint64_t cand_bits[2];
+    uint32_t kparam[2][128];                     // candidate 0 = fixed, 1 = lpc; level L's parameters start at (1 << L) - 1
+    uint64_t lvl_bits[2][8];                     // Rice search: estimated bits of partition order L (~0: not evaluated)
+    uint32_t lvl_big[2][8];                      // ... and whether it needs 5-bit parameters (RICE2)
     // reductions
     uint64_t wfix[NWARPS][5];
     uint32_t wor[NWARPS][2];

@@ -54,19 +54,21 @@ __device__ __noinline__ float tukey_w(int g, int n) {
     return 1.0f;
 }
 
-// K4 on one thread, float32, everything in registers (MAXO = largest order of the compression level):
-// Levinson-Durbin, expected-bits order pick, coefficient quantisation (libFLAC's scheme with error feedback).
+// K4 on one warp, float32 (MAXO = largest order of the compression level): every lane runs the Levinson-Durbin recursion
+// in registers; lane o-1 prices order o (expected bits), lane j owns coefficient j for the row store, the |max| and the
+// quantised value, so the serial part is the recursion and the error-feedback rounding only (libFLAC's scheme).
 // The decisions are ours; the bitstream stays exact because the residual is computed from the quantised integers.
 template <bool WIDE, int MAXO>
-__device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, int wasted, int sbps, int qlp_precision, int magbits, bool lean) {
-    sh.lpc_ok = 0;
+__device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, int wasted, int sbps, int qlp_precision, int magbits, bool lean,
+                                        int lane) {
+    if (lane == 0) sh.lpc_ok = 0;
     const float a0 = sh.autoc[0];
     if (!(a0 > 0.f)) return;
     const float inv0 = 1.0f / a0;
-    float an[MAXO + 1], lpc[MAXO], errs[MAXO];
+    float an[MAXO + 1], lpc[MAXO];
 #pragma unroll
     for (int i = 0; i <= MAXO; i++) an[i] = sh.autoc[i] * inv0;   // normalised autocorrelation
-    float err = 1.0f;
+    float err = 1.0f, myerr = 0.f;
     int mo = max_lpc;
 #pragma unroll
     for (int i = 0; i < MAXO; i++) {
@@ -84,36 +86,36 @@ __device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, in
             }
             if (i & 1) lpc[i >> 1] += lpc[i >> 1] * r;
             err *= (1.0f - r * r);
+            float mine = 0.f;                      // lane j stores predictor coefficient j of order i+1
 #pragma unroll
-            for (int j = 0; j <= i; j++) sh.lpc_rows[i][j] = -lpc[j];
-            errs[i] = err;
+            for (int j = 0; j <= i; j++) if (lane == j) mine = -lpc[j];
+            if (lane <= i) sh.lpc_rows[i][lane] = mine;
+            if (lane == i) myerr = err;
             if (!(err > 0.f)) mo = i + 1;
-        } else errs[i] = 0.f;
-    }
-    // expected bits per order; errs are relative to autoc[0] (taken before the wasted-bit shift)
-    float best_bits = 3.0e38f;
-    int best = 1;
-    const float lscale = __log2f(a0) + __log2f(0.5f / (float)nsamp) - 2.0f * (float)wasted;
-#pragma unroll
-    for (int o = 1; o <= MAXO; o++) {
-        if (o <= mo) {
-            const float e = errs[o - 1];
-            const float bpsr = e > 0.f ? fmaxf(0.f, 0.5f * (__log2f(e) + lscale)) : 0.f;
-            const float b = bpsr * (float)(nsamp - o) + (float)(o * (sbps + qlp_precision));
-            if (b < best_bits) { best_bits = b; best = o; }
         }
     }
-    const int order = best;
+    __syncwarp();
+    // expected bits per order; errs are relative to autoc[0] (taken before the wasted-bit shift)
+    const float lscale = __log2f(a0) + __log2f(0.5f / (float)nsamp) - 2.0f * (float)wasted;
+    uint32_t key = 0xFFFFFFFFu;
+    if (lane < mo) {
+        const int o = lane + 1;
+        const float bpsr = myerr > 0.f ? fmaxf(0.f, 0.5f * (__log2f(myerr) + lscale)) : 0.f;
+        const float b = bpsr * (float)(nsamp - o) + (float)(o * (sbps + qlp_precision));
+        key = __float_as_uint(b);                  // b >= 0: the bit pattern orders like the value
+        if (!(b >= 0.f)) key = 0xFFFFFFFEu;
+    }
+    const uint32_t kmin = __reduce_min_sync(FULLMASK, key);
+    const int order = __ffs((int)__ballot_sync(FULLMASK, key == kmin));   // lowest order among ties
     int precision = qlp_precision;
     if (!WIDE) {
         const int lim = 32 - sbps - (31 - __clz(order));
         if (lim < precision) precision = lim;
     }
     if (precision < 5) return;
-    const float *row = sh.lpc_rows[order - 1];
-    float cmax = 0.f;
-    for (int j = 0; j < order; j++) cmax = fmaxf(cmax, fabsf(row[j]));
-    if (!(cmax > 0.f)) return;
+    const float rv = lane < order ? sh.lpc_rows[order - 1][lane] : 0.f;
+    const float cmax = __uint_as_float(__reduce_max_sync(FULLMASK, __float_as_uint(fabsf(rv))));
+    if (!(cmax > 0.f) || !(cmax < 3.0e38f)) return;
     int e2;
     (void)frexpf(cmax, &e2);
     int shift = (precision - 1) - (e2 - 1) - 1;
@@ -123,16 +125,20 @@ __device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, in
     float error = 0.f;
     long long sumabs = 0;
     const float scale = (float)(1 << shift);
-    for (int j = 0; j < order; j++) {
-        error += row[j] * scale;
-        int qq = __float2int_rn(error);
-        if (qq > qmax) qq = qmax; else if (qq < qmin) qq = qmin;
-        error -= (float)qq;
-        sh.qlp[j] = qq;
-        sumabs += qq < 0 ? -qq : qq;
+    int myq = 0;
+#pragma unroll
+    for (int j = 0; j < MAXO; j++) {
+        const float c = __shfl_sync(FULLMASK, rv, j);
+        if (j < order) {
+            error += c * scale;
+            int qq = __float2int_rn(error);
+            if (qq > qmax) qq = qmax; else if (qq < qmin) qq = qmin;
+            error -= (float)qq;
+            if (lane == j) myq = qq;
+            sumabs += qq < 0 ? -qq : qq;
+        }
     }
-    for (int j = order; j < FRX_MAX_LPC; j++) sh.qlp[j] = 0;
-    sh.lpc_order = order; sh.shift = shift; sh.precision = precision;
+    if (lane < FRX_MAX_LPC) sh.qlp[lane] = myq;
     int ok = 1, narrow = 1;
     if (WIDE) {
         // |prediction sum| <= sumabs * 2^mag; the residual bound decides which arithmetic is safe
@@ -144,8 +150,8 @@ __device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, in
             if (Bnd >= (1ll << 27)) ok = 0;   // keeps 32-bit residual sums exact; such wild predictors never win anyway
         }
     }
-    sh.lpc_narrow = narrow;
-    sh.lpc_ok = ok;
+    if (lane == 0) { sh.lpc_order = order; sh.shift = shift; sh.precision = precision; sh.lpc_narrow = narrow; sh.lpc_ok = ok; }
+    __syncwarp();
 }
 
 // OR an n-bit field (1..32 bits, v < 2^n) into the zeroed frame buffer at bit position p

@@ -147,50 +147,45 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
             }
             compute_sync();  // SA: per-warp partials and tabs[0..4] are in shared memory
             DBG_PH(10);
-            // ---- warp 0: fixed-order decision + Rice search of the fixed candidate; warp 1: LPC design ----
-            if (warp == 0) {
+            // ---- every warp: fixed-order decision (cheap, redundant).  Warps 0..6: Rice search of the fixed candidate, one
+            //      partition order each; warp 7: LPC design ----
+            {
                 uint64_t tot = 0;
                 uint32_t o32 = 0;
                 if (lane < 5) { for (int w2 = 0; w2 < NWARPS; w2++) tot += sh.wfix[w2][lane]; }
                 else if (lane < 7) { for (int w2 = 0; w2 < NWARPS; w2++) o32 |= sh.wor[w2][lane - 5]; }
-                const uint32_t all_or = __shfl_sync(FULLMASK, o32, 5);
-                const int wasted = all_or ? (__ffs((int)all_or) - 1) : 0;
-                const uint64_t f1 = __shfl_sync(FULLMASK, tot, 1);
-                uint64_t bestv = (lane < 5) ? tot : ~0ull;   // best fixed order among lanes 0..4 (lowest order wins ties)
-                int besto = lane;
-                for (int o = 1; o < 8; o <<= 1) {
-                    const uint64_t ov = __shfl_xor_sync(FULLMASK, bestv, o);
-                    const int oo = __shfl_xor_sync(FULLMASK, besto, o);
-                    if (ov < bestv || (ov == bestv && oo < besto)) { bestv = ov; besto = oo; }
-                }
-                besto = __shfl_sync(FULLMASK, besto, 0);
-                const int fixed_order = (nsamp > 4) ? besto : -1;
-                if (lane == 0) {
-                    sh.wasted = wasted;
-                    sh.is_const = (f1 == 0) ? 1 : 0;   // sum |s[g]-s[g-1]| == 0  <=>  all samples equal
-                    sh.fixed_order = fixed_order;
-                }
-                const long long ca0 = DBG_CLK();
-                if (fixed_order >= 0) analyse_partitions(sh, tabs + fixed_order * FRX_ENC_THREADS, 0, nsamp, fixed_order, po_max, kmax, wasted);
-                if (lane == 0) DBG_ADD(0, DBG_CLK() - ca0);
-            } else if (warp == 1) {
-                uint32_t o32 = 0;
-                if (lane < 2) { for (int w2 = 0; w2 < NWARPS; w2++) o32 |= sh.wor[w2][lane]; }
-                const uint32_t all_or = __shfl_sync(FULLMASK, o32, 0), all_abs = __shfl_sync(FULLMASK, o32, 1);
+                const uint32_t all_or = __shfl_sync(FULLMASK, o32, 5), all_abs = __shfl_sync(FULLMASK, o32, 6);
                 const int wasted = all_or ? (__ffs((int)all_or) - 1) : 0;
                 const int magbits = WIDE ? 32 - __clz((int)all_abs) : 15;  // bits of the largest magnitude
                 const bool lean = !WIDE || magbits <= 23;
-                float acs = 0.f;
-                if (lane <= max_lpc) { for (int w2 = 0; w2 < NWARPS; w2++) acs += sh.wac[w2][lane]; }
-                if (lane <= FRX_MAX_LPC) sh.autoc[lane] = acs;
-                __syncwarp();
-                const long long cl0 = DBG_CLK();
-                if (lane == 0) {
-                    sh.magbits = magbits; sh.lean = lean ? 1 : 0;
-                    sh.lpc_ok = 0;
+                if (warp == NWARPS - 1) {
+                    float acs = 0.f;
+                    if (lane <= max_lpc) { for (int w2 = 0; w2 < NWARPS; w2++) acs += sh.wac[w2][lane]; }
+                    if (lane <= FRX_MAX_LPC) sh.autoc[lane] = acs;
+                    if (lane == 0) { sh.magbits = magbits; sh.lean = lean ? 1 : 0; sh.lpc_ok = 0; }
+                    __syncwarp();
                     if (max_lpc > 0 && nsamp > 4)
-                        lpc_design<WIDE, HISTN>(sh, max_lpc, nsamp, wasted, a.bps - wasted, a.qlp_precision, magbits, lean);
-                    DBG_ADD(1, DBG_CLK() - cl0);
+                        lpc_design<WIDE, HISTN>(sh, max_lpc, nsamp, wasted, a.bps - wasted, a.qlp_precision, magbits, lean, lane);
+                } else {
+                    const uint64_t f1 = __shfl_sync(FULLMASK, tot, 1);
+                    uint64_t bestv = (lane < 5) ? tot : ~0ull;   // best fixed order among lanes 0..4 (lowest order wins ties)
+                    int besto = lane;
+                    for (int o = 1; o < 8; o <<= 1) {
+                        const uint64_t ov = __shfl_xor_sync(FULLMASK, bestv, o);
+                        const int oo = __shfl_xor_sync(FULLMASK, besto, o);
+                        if (ov < bestv || (ov == bestv && oo < besto)) { bestv = ov; besto = oo; }
+                    }
+                    besto = __shfl_sync(FULLMASK, besto, 0);
+                    const int fixed_order = (nsamp > 4) ? besto : -1;
+                    if (warp == 0 && lane == 0) {
+                        sh.wasted = wasted;
+                        sh.is_const = (f1 == 0) ? 1 : 0;   // sum |s[g]-s[g-1]| == 0  <=>  all samples equal
+                        sh.fixed_order = fixed_order;
+                    }
+                    if (fixed_order >= 0 && lean) {          // fat data: fat_search redoes the fixed candidate in 64 bits
+                        if (full) { if (warp <= po_max) analyse_level(sh, tabs + fixed_order * FRX_ENC_THREADS, 0, warp, fixed_order, kmax, wasted); }
+                        else if (warp == 0) analyse_partitions(sh, tabs + fixed_order * FRX_ENC_THREADS, 0, nsamp, fixed_order, po_max, kmax, wasted);
+                    }
                 }
             }
             compute_sync();  // SB

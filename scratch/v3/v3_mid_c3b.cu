@@ -29,9 +29,10 @@
                 }
                 compute_sync();  // SC
                 DBG_PH(8);
-                const long long cb0 = DBG_CLK();
-                if (warp == 1 && lpc_try0) analyse_partitions(sh, tabs + 5 * FRX_ENC_THREADS, 1, nsamp, lpc_order, po_max, kmax, 0);
-                if (tid == 32) DBG_ADD(2, DBG_CLK() - cb0);
+                if (lpc_try0) {
+                    if (full) { if (warp <= po_max) analyse_level(sh, tabs + 5 * FRX_ENC_THREADS, 1, warp, lpc_order, kmax, 0); }
+                    else if (warp == 1) analyse_partitions(sh, tabs + 5 * FRX_ENC_THREADS, 1, nsamp, lpc_order, po_max, kmax, 0);
+                }
                 compute_sync();  // SD
                 DBG_PH(12);
             }
@@ -41,33 +42,35 @@
 
             // ---- choose ----
             const uint64_t verb_bits = 8ull + (uint64_t)wasted + (uint64_t)nsamp * (uint64_t)sbps;
-            int type = 1, order = 0, cand = 0;
+            int type = 1, order = 0, cand = 0, po = 0;
+            bool rice2 = false;
             uint64_t best_bits = verb_bits;
             if (is_const) { type = 0; best_bits = 8ull + wasted + sbps; }
             else {
                 if (fixed_order >= 0) {
-                    const uint64_t b = 8ull + wasted + (uint64_t)fixed_order * sbps + sh.cand_bits[0];
-                    if (b < best_bits) { best_bits = b; type = 2; order = fixed_order; cand = 0; }
+                    int lp; uint64_t lb; bool l2;
+                    pick_level(sh, 0, po_max, lp, lb, l2);
+                    const uint64_t b = 8ull + wasted + (uint64_t)fixed_order * sbps + lb;
+                    if (b < best_bits) { best_bits = b; type = 2; order = fixed_order; cand = 0; po = lp; rice2 = l2; }
                 }
                 if (lpc_try) {
-                    const uint64_t b = 8ull + wasted + 9ull + (uint64_t)lpc_order * (uint64_t)(sh.precision + sbps) + sh.cand_bits[1];
-                    if (b < best_bits) { best_bits = b; type = 3; order = lpc_order; cand = 1; }
+                    int lp; uint64_t lb; bool l2;
+                    pick_level(sh, 1, po_max, lp, lb, l2);
+                    const uint64_t b = 8ull + wasted + 9ull + (uint64_t)lpc_order * (uint64_t)(sh.precision + sbps) + lb;
+                    if (b < best_bits) { best_bits = b; type = 3; order = lpc_order; cand = 1; po = lp; rice2 = l2; }
                 }
             }
             // ---- K7a: winner's residuals (zig-zag folded), exact bit count per thread, block scan ----
             const uint32_t sub_start = bitpos;
             const uint32_t smask = sbps >= 32 ? 0xFFFFFFFFu : ((1u << sbps) - 1u);
             uint32_t u[FRX_SPT];
-            int po = 0, psize = nsamp;
+            int psize = nsamp;
             uint32_t kk = 0;
-            bool rice2 = false;
             uint32_t mybits = 0;
             const int skip = (tid == 0) ? order : 0;
             if (type >= 2) {
-                po = sh.cand_po[cand];
                 psize = nsamp >> po;
-                kk = sh.kparam[cand][min(g0 / psize, (1 << po) - 1)];
-                rice2 = sh.cand_rice2[cand] != 0;
+                kk = sh.kparam[cand][(1 << po) - 1 + min(g0 / psize, (1 << po) - 1)];
                 if (type == 2 || (WIDE && !lean)) {
                     // fixed winner (4 ops per sample) or a fat-path LPC winner: recompute from the PCM
                     int32_t s[HISTN + FRX_SPT];
