@@ -262,16 +262,16 @@ struct FrameDesc {                               // written by the control warp,
     uint32_t hdr[4];
     uint32_t hdr_bits;
     int32_t tma;                                 // 1: raw samples staged by TMA bulk copies; 0: compute warps gather them
-    int32_t tile_idx, pad;
+    int32_t tile_idx;
+    int16_t po_max, max_lpc;                     // largest Rice partition order / LPC order this frame can use
     FrxQuant q;
 };
 
 struct EncSmall {
-    uint64_t full[2], empty[2];                  // raw stage pipeline (mbarriers)
+    uint64_t full[1], empty[1];                  // raw stage hand-over (mbarriers): one stage, refilled as soon as K1 has read it
     uint64_t sized[FD_SLOTS], placed[FD_SLOTS];  // frame size known -> look-back -> byte offset known
     FrameDesc fd[FD_SLOTS];
     uint32_t frame_bytes[FD_SLOTS];
-    uint32_t stage_stride;                       // bytes between the two raw stages (128 + 4096 * element size)
     uint64_t out_offset[FD_SLOTS];
     // per-subframe decisions
     int wasted, magbits, fixed_order, is_const, lean;
@@ -292,6 +292,8 @@ struct EncSmall {
     uint32_t crc_part[2][NWARPS];                // per frame buffer
     uint16_t crc_tab[4][256];
 };
+#define RES_BYTES (FRX_MAX_BLOCK * 4)             // the candidate's residuals, sample-major: res[i * 256 + tid]
+#define RES_IDX(i, tid) ((i) * FRX_ENC_THREADS + (tid))
 #define ENC_SMALL_BYTES ((sizeof(EncSmall) + 127) & ~(size_t)127)
 
 // ------------------------------------------------------------------------------------------
@@ -616,6 +618,13 @@ __device__ __noinline__ void build_frame_desc(const EncArgs &a, FrameDesc &d, ui
         const uint32_t s0 = fj * (uint32_t)a.blocksize;
         const int nsamp = (int)min((long long)a.blocksize, tile_n - (long long)s0);
         d.f = f; d.fj = fj; d.s0 = s0; d.nsamp = nsamp; d.tile_idx = ti;
+        {
+            const int tz = __ffs(nsamp) - 1;               // trailing zeros of the block size
+            int po_max = min(a.max_po, max(0, tz - 4));    // partitions stay multiples of 16 samples
+            while (po_max > 0 && (nsamp >> po_max) <= FRX_MAX_LPC) po_max--;
+            d.po_max = (int16_t)po_max;
+            d.max_lpc = (int16_t)min(a.max_lpc_order, nsamp - 1);
+        }
         const int epv = 16 / frx_dtype_size(a.dtype);            // elements per 16 bytes
         d.tma = (a.tma_ok && (t.w % epv) == 0 && (t.col_off % epv) == 0) ? 1 : 0;
         uint8_t hb[16];
@@ -712,8 +721,8 @@ __device__ __noinline__ void control_warp(const EncArgs &a, EncSmall &sh, unsign
         }
         // ---- 2. next unit (frame, channel) into the raw stage ring ----
         if (have_frame || want_frame) {
-            const int stage = (int)(unit_iss & 1u);
-            if (mbar_test(&sh.empty[stage], ((unit_iss >> 1) & 1u) ^ 1u)) {
+            const int stage = 0;
+            if (mbar_test(&sh.empty[stage], (unit_iss & 1u) ^ 1u)) {
                 progress = true;
                 if (!have_frame) {
                     const int slot = (int)(fseq_iss & (FD_SLOTS - 1));
@@ -735,7 +744,7 @@ __device__ __noinline__ void control_warp(const EncArgs &a, EncSmall &sh, unsign
                 }
                 if (have_frame) {
                     const FrameDesc &d = sh.fd[fseq_iss & (FD_SLOTS - 1)];
-                    unsigned char *dst = raw + (size_t)stage * sh.stage_stride;
+                    unsigned char *dst = raw;
                     if (d.tma) {
                         const long long w = d.t.w;
                         const long long s0 = d.s0, s1 = s0 + d.nsamp;
@@ -781,7 +790,7 @@ __device__ __noinline__ void control_warp(const EncArgs &a, EncSmall &sh, unsign
             } else if (!lb.blocked) progress = true;
         }
         if (stop_issued && !lb_active && fseq_lb == fseq_iss) break;
-        if (!progress) __nanosleep(lb_active ? 100 : 400);
+        if (!progress) __nanosleep(400);
     }
 }
 // residual of one sample, lean paths (no overflow possible by construction)
@@ -815,6 +824,20 @@ __device__ __forceinline__ uint32_t lpc_residuals(const int32_t *s, const int32_
         }
     }
     return bad;
+}
+// Lean K5: residuals of the thread's 16 samples with all HISTN taps (coefficients beyond the order are zero), parked in the
+// shared residual buffer as they are produced; returns the thread's sum of |r| over the samples that will be coded.
+template <int MODE, int HISTN>
+__device__ __forceinline__ uint32_t lpc_residuals_park(const int32_t *s, const int32_t *q, int shift, int32_t *res, int tid, bool plain, int nv,
+                                                       int first_coded) {
+    uint32_t ab = 0;
+#pragma unroll
+    for (int i = 0; i < FRX_SPT; i++) {
+        const int32_t rr = MODE == 0 ? lpc_res32<HISTN>(s, HISTN + i, q, shift) : (int32_t)lpc_res64<HISTN>(s, HISTN + i, q, shift);
+        res[RES_IDX(i, tid)] = rr;
+        if (plain || (i < nv && i >= first_coded)) ab += (uint32_t)abs(rr);
+    }
+    return ab;
 }
 template <int MODE, int HISTN>
 __device__ __forceinline__ uint32_t lpc_residuals_dispatch(int order, const int32_t *s, const int32_t *q, int shift, int32_t *r) {
@@ -1044,15 +1067,16 @@ __device__ __forceinline__ void put_field(uint32_t *buf, uint32_t p, uint32_t v,
 
 // K7b: Rice-code the thread's residuals straight into the (zeroed) frame buffer.  The unary zeros need no store at all;
 // every sample is one (k+1)-bit field -- stop bit plus low bits -- OR-ed at its bit position, straddling at most two
-// words.  `skip` leading samples are warm-up (thread 0 only), `nv` samples are valid, `plain` = neither applies.
-__device__ __forceinline__ void pack_rice(uint32_t *buf, uint32_t p, const uint32_t *u, uint32_t kk, int skip, int nv, bool plain) {
+// words.  The residuals come from the shared residual buffer (sample-major, conflict-free).  `skip` leading samples are warm-up (thread 0 only), `nv` samples are valid, `plain` = neither applies.
+__device__ __forceinline__ void pack_rice(uint32_t *buf, uint32_t p, const int32_t *res, int tid, uint32_t kk, int skip, int nv, bool plain) {
     const uint32_t kmask = (1u << kk) - 1u;   // kk <= 30
     const uint32_t len = kk + 1u;
 #pragma unroll
     for (int i = 0; i < FRX_SPT; i++) {
         if (plain || (i >= skip && i < nv)) {
-            p += u[i] >> kk;
-            const uint32_t code = (1u << kk) | (u[i] & kmask);
+            const uint32_t u = zigzag(res[RES_IDX(i, tid)]);
+            p += u >> kk;
+            const uint32_t code = (1u << kk) | (u & kmask);
             const uint64_t v = (uint64_t)code << (64u - (p & 31u) - len);
             atomicOr(&buf[p >> 5], (uint32_t)(v >> 32));
             if ((uint32_t)v) atomicOr(&buf[(p >> 5) + 1u], (uint32_t)v);
@@ -1231,8 +1255,9 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
     EncSmall &sh = *reinterpret_cast<EncSmall *>(smem_raw);
     const uint32_t stage_stride = 128u + (uint32_t)FRX_MAX_BLOCK * (uint32_t)frx_dtype_size(a.dtype);
     unsigned char *raw = smem_raw + ENC_SMALL_BYTES;
-    int32_t *pcm = reinterpret_cast<int32_t *>(raw + 2 * stage_stride);
-    uint64_t *tabs = reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(pcm) + PCM_BYTES);
+    int32_t *pcm = reinterpret_cast<int32_t *>(raw + stage_stride);
+    int32_t *res = reinterpret_cast<int32_t *>(reinterpret_cast<unsigned char *>(pcm) + PCM_BYTES);
+    uint64_t *tabs = reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(res) + RES_BYTES);
     uint32_t *bits0 = reinterpret_cast<uint32_t *>(reinterpret_cast<unsigned char *>(tabs) + TABS_BYTES);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -1240,8 +1265,7 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
     for (int i = tid; i < PCM_WORDS; i += FRX_ENC_CTA) pcm[i] = 0;
     for (int i = tid; i < 1024; i += FRX_ENC_CTA) (&sh.crc_tab[0][0])[i] = a.crc_tab[i];
     if (tid == 0) {
-        sh.stage_stride = stage_stride;
-        for (int i = 0; i < 2; i++) { mbar_init(&sh.full[i], 1); mbar_init(&sh.empty[i], NWARPS); }
+        mbar_init(&sh.full[0], 1); mbar_init(&sh.empty[0], NWARPS);
         for (int i = 0; i < FD_SLOTS; i++) { mbar_init(&sh.sized[i], 1); mbar_init(&sh.placed[i], 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -1263,37 +1287,30 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
         const int slot = (int)(fseq & (FD_SLOTS - 1));
         const int buf = (int)(fseq & 1u);
         uint32_t *bits = bits0 + (size_t)buf * a.frame_words;
-        mbar_wait(&sh.full[unit & 1u], (unit >> 1) & 1u);
+        mbar_wait(&sh.full[0], unit & 1u);
         const FrameDesc &fd = sh.fd[slot];
         const uint32_t f = fd.f;
         if (f == STOP_FRAME) { if (tid == 0) DBG_ADD(7, DBG_CLK() - ck0); break; }
         if (tid == 0) DBG_TRACE(f, 4);
         DBG_PH(15);
-        const frx_tile t = fd.t;
+        const int n_channels = fd.t.n_channels;
         const uint32_t s0 = fd.s0;
         const int nsamp = fd.nsamp;
         const bool use_tma = fd.tma != 0;
-        const int nthr = (nsamp + FRX_SPT - 1) / FRX_SPT;
         const int nv = min(FRX_SPT, max(0, nsamp - g0));  // valid samples of this thread
         const bool full = (nsamp == FRX_MAX_BLOCK);
         const bool plain = full && tid != 0;              // no per-sample masks needed for this thread
         uint32_t bitpos = fd.hdr_bits;
         if (tid < 4) bits[tid] = fd.hdr[tid];
-        int po_max;
-        {
-            const int tz = __ffs(nsamp) - 1;               // trailing zeros of the block size
-            po_max = min(a.max_po, max(0, tz - 4));        // partitions stay multiples of 16 samples
-            while (po_max > 0 && (nsamp >> po_max) <= FRX_MAX_LPC) po_max--;
-        }
-        const int max_lpc = min(min(a.max_lpc_order, HISTN), nsamp - 1);
+        const int po_max = fd.po_max;
+        const int max_lpc = min((int)fd.max_lpc, HISTN);
 
         // ================= per channel =================
-        for (int ch = 0; ch < t.n_channels; ch++) {
-            const int stage = (int)(unit & 1u);
-            unsigned char *stg = raw + (size_t)stage * stage_stride;
-            if (ch > 0) mbar_wait(&sh.full[stage], (unit >> 1) & 1u);
+        for (int ch = 0; ch < n_channels; ch++) {
+            unsigned char *stg = raw;
+            if (ch > 0) mbar_wait(&sh.full[0], unit & 1u);
             if (!use_tma) {
-                gather_raw(a, t, ch, s0, nsamp, stg, tid);
+                gather_raw(a, fd.t, ch, s0, nsamp, stg, tid);
                 compute_sync();
             }
             // ---- K1: the thread's 16 samples -> PCM -> shared memory ----
@@ -1307,7 +1324,7 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                 // the raw stage may be refilled as soon as every warp has read its samples
                 if (!use_tma) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&sh.empty[stage]);
+                if (lane == 0) mbar_arrive(&sh.empty[0]);
                 unit++;
             }
             orv = __reduce_or_sync(FULLMASK, orv);
@@ -1416,7 +1433,6 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
             const int sbps = a.bps - wasted;
             const int lpc_order = sh.lpc_order;
             const int lshift = sh.shift;
-            int32_t r[FRX_SPT];
             if (WIDE && !lean) {
                 fat_search<HISTN>(sh, pcm, tabs, tid, nv, nsamp, wasted, po_max, kmax);
             } else {
@@ -1427,17 +1443,9 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                     read_pcm<HISTN>(pcm, tid, wasted, s);
 #pragma unroll
                     for (int j = 0; j < HISTN; j++) q[j] = sh.qlp[j];
-                    if (!WIDE || sh.lpc_narrow) (void)lpc_residuals_dispatch<0, HISTN>(lpc_order, s, q, lshift, r);
-                    else (void)lpc_residuals_dispatch<1, HISTN>(lpc_order, s, q, lshift, r);
-                    uint32_t ab = 0;
-                    if (plain) {
-#pragma unroll
-                        for (int i = 0; i < FRX_SPT; i++) ab += (uint32_t)abs(r[i]);
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < FRX_SPT; i++)
-                            if (i < nv && g0 + i >= lpc_order) ab += (uint32_t)abs(r[i]);
-                    }
+                    uint32_t ab;
+                    if (!WIDE || sh.lpc_narrow) ab = lpc_residuals_park<0, HISTN>(s, q, lshift, res, tid, plain, nv, lpc_order - g0);
+                    else ab = lpc_residuals_park<1, HISTN>(s, q, lshift, res, tid, plain, nv, lpc_order - g0);
                     tabs[5 * FRX_ENC_THREADS + tid] = ab;
                 }
                 compute_sync();  // SC
@@ -1476,7 +1484,6 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
             // ---- K7a: winner's residuals (zig-zag folded), exact bit count per thread, block scan ----
             const uint32_t sub_start = bitpos;
             const uint32_t smask = sbps >= 32 ? 0xFFFFFFFFu : ((1u << sbps) - 1u);
-            uint32_t u[FRX_SPT];
             int psize = nsamp;
             uint32_t kk = 0;
             uint32_t mybits = 0;
@@ -1484,8 +1491,9 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
             if (type >= 2) {
                 psize = nsamp >> po;
                 kk = sh.kparam[cand][(1 << po) - 1 + min(g0 / psize, (1 << po) - 1)];
+                int32_t r[FRX_SPT];
                 if (type == 2 || (WIDE && !lean)) {
-                    // fixed winner (4 ops per sample) or a fat-path LPC winner: recompute from the PCM
+                    // fixed winner (4 ops per sample) or a fat-path LPC winner: recompute from the PCM, park in the residual buffer
                     int32_t s[HISTN + FRX_SPT];
                     read_pcm<HISTN>(pcm, tid, wasted, s);
                     if (type == 2) {
@@ -1497,20 +1505,24 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                         for (int j = 0; j < HISTN; j++) q[j] = sh.qlp[j];
                         (void)lpc_residuals_dispatch<1, HISTN>(order, s, q, lshift, r);
                     }
-                }
-                uint32_t qs = 0;
 #pragma unroll
-                for (int i = 0; i < FRX_SPT; i++) {
-                    u[i] = zigzag(r[i]);
-                    qs += u[i] >> kk;
+                    for (int i = 0; i < FRX_SPT; i++) res[RES_IDX(i, tid)] = r[i];
+                } else {
+                    // lean LPC winner: K5 left its residuals in the buffer
+#pragma unroll
+                    for (int i = 0; i < FRX_SPT; i++) r[i] = res[RES_IDX(i, tid)];
                 }
-                if (plain) mybits = qs + (uint32_t)FRX_SPT * (1u + kk);
-                else {
+                if (plain) {
+                    uint32_t qs = 0;
+#pragma unroll
+                    for (int i = 0; i < FRX_SPT; i++) qs += zigzag(r[i]) >> kk;
+                    mybits = qs + (uint32_t)FRX_SPT * (1u + kk);
+                } else {
 #pragma unroll
                     for (int i = 0; i < FRX_SPT; i++)
-                        if (i >= skip && i < nv) mybits += (u[i] >> kk) + 1u + kk;
+                        if (i >= skip && i < nv) mybits += (zigzag(r[i]) >> kk) + 1u + kk;
                 }
-                if (tid < nthr && g0 % psize == 0) mybits += rice2 ? 5u : 4u;
+                if (nv > 0 && g0 % psize == 0) mybits += rice2 ? 5u : 4u;
                 if (tid == 0) {
                     mybits += 8u + (uint32_t)wasted + (uint32_t)order * (uint32_t)sbps + 6u;
                     if (type == 3) mybits += 9u + (uint32_t)order * (uint32_t)sh.precision;
@@ -1560,7 +1572,7 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
             }
             const uint32_t start = sub_start + wbase + incl - mybits;
             bitpos = sub_start + total;
-            if (ch == t.n_channels - 1 && tid == 0) {
+            if (ch == n_channels - 1 && tid == 0) {
                 // the frame's size is final: hand it to the control warp so the look-back overlaps packing and the CRC
                 const uint32_t nb = ((bitpos + 7u) >> 3) + 2u;
                 if (f != 0) frx_st_relaxed_u64(&a.desc[f], (1ull << 62) | (uint64_t)nb);
@@ -1594,7 +1606,7 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                         if (kk) put_field(bits, p, kk, pb);
                         p += pb;
                     }
-                    pack_rice(bits, p, u, kk, skip, nv, plain);
+                    pack_rice(bits, p, res, tid, kk, skip, nv, plain);
                 }
             } else if (mybits) {
                 BitW bw;
@@ -1611,7 +1623,7 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                 bw.finish();
             }
             // the PCM buffer is rewritten by the next channel's K1: every reader of it (verbatim / warm-up packing) must be done
-            if (ch + 1 < t.n_channels) compute_sync();
+            if (ch + 1 < n_channels) compute_sync();
         }  // channels
         compute_sync();  // Sa: every subframe is packed
         DBG_PH(14);
@@ -1675,7 +1687,7 @@ __global__ void frx_minmax_out_kernel(const FrxQuant *q, int dtype, double *mm) 
 // host launchers (called from frx_api.cu)
 // ------------------------------------------------------------------------------------------
 size_t frx_enc_smem_bytes(int frame_words, int dtype) {
-    return ENC_SMALL_BYTES + 2 * (128 + (size_t)FRX_MAX_BLOCK * frx_dtype_size(dtype)) + PCM_BYTES + TABS_BYTES + 2 * sizeof(uint32_t) * (size_t)frame_words;
+    return ENC_SMALL_BYTES + (128 + (size_t)FRX_MAX_BLOCK * frx_dtype_size(dtype)) + PCM_BYTES + RES_BYTES + TABS_BYTES + 2 * sizeof(uint32_t) * (size_t)frame_words;
 }
 
 size_t frx_minmax_raw_size() { return sizeof(MinMaxRaw); }

@@ -16,7 +16,7 @@ tail = R('v1_tail.cu')
 tail = tail.replace('''size_t frx_enc_smem_bytes(int frame_words) {
     return ENC_SMALL_BYTES + ENC_UNION_BYTES + sizeof(uint32_t) * (size_t)frame_words;
 }''', '''size_t frx_enc_smem_bytes(int frame_words, int dtype) {
-    return ENC_SMALL_BYTES + 2 * (128 + (size_t)FRX_MAX_BLOCK * frx_dtype_size(dtype)) + PCM_BYTES + TABS_BYTES + 2 * sizeof(uint32_t) * (size_t)frame_words;
+    return ENC_SMALL_BYTES + (128 + (size_t)FRX_MAX_BLOCK * frx_dtype_size(dtype)) + PCM_BYTES + RES_BYTES + TABS_BYTES + 2 * sizeof(uint32_t) * (size_t)frame_words;
 }''')
 tail = tail.replace("size_t smem = frx_enc_smem_bytes(a.frame_words);", "size_t smem = frx_enc_smem_bytes(a.frame_words, a.dtype);")
 tail = tail.replace("cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, frx_encode_kernel<WIDE, HISTN>, FRX_ENC_THREADS, smem);", "cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, frx_encode_kernel<WIDE, HISTN>, FRX_ENC_CTA, smem);")

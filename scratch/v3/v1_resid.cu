@@ -30,6 +30,20 @@ __device__ __forceinline__ uint32_t lpc_residuals(const int32_t *s, const int32_
     }
     return bad;
 }
+// Lean K5: residuals of the thread's 16 samples with all HISTN taps (coefficients beyond the order are zero), parked in the
+// shared residual buffer as they are produced; returns the thread's sum of |r| over the samples that will be coded.
+template <int MODE, int HISTN>
+__device__ __forceinline__ uint32_t lpc_residuals_park(const int32_t *s, const int32_t *q, int shift, int32_t *res, int tid, bool plain, int nv,
+                                                       int first_coded) {
+    uint32_t ab = 0;
+#pragma unroll
+    for (int i = 0; i < FRX_SPT; i++) {
+        const int32_t rr = MODE == 0 ? lpc_res32<HISTN>(s, HISTN + i, q, shift) : (int32_t)lpc_res64<HISTN>(s, HISTN + i, q, shift);
+        res[RES_IDX(i, tid)] = rr;
+        if (plain || (i < nv && i >= first_coded)) ab += (uint32_t)abs(rr);
+    }
+    return ab;
+}
 template <int MODE, int HISTN>
 __device__ __forceinline__ uint32_t lpc_residuals_dispatch(int order, const int32_t *s, const int32_t *q, int shift, int32_t *r) {
     switch (order) {

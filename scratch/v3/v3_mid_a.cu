@@ -38,16 +38,16 @@ struct FrameDesc {                               // written by the control warp,
     uint32_t hdr[4];
     uint32_t hdr_bits;
     int32_t tma;                                 // 1: raw samples staged by TMA bulk copies; 0: compute warps gather them
-    int32_t tile_idx, pad;
+    int32_t tile_idx;
+    int16_t po_max, max_lpc;                     // largest Rice partition order / LPC order this frame can use
     FrxQuant q;
 };
 
 struct EncSmall {
-    uint64_t full[2], empty[2];                  // raw stage pipeline (mbarriers)
+    uint64_t full[1], empty[1];                  // raw stage hand-over (mbarriers): one stage, refilled as soon as K1 has read it
     uint64_t sized[FD_SLOTS], placed[FD_SLOTS];  // frame size known -> look-back -> byte offset known
     FrameDesc fd[FD_SLOTS];
     uint32_t frame_bytes[FD_SLOTS];
-    uint32_t stage_stride;                       // bytes between the two raw stages (128 + 4096 * element size)
     uint64_t out_offset[FD_SLOTS];
     // per-subframe decisions
     int wasted, magbits, fixed_order, is_const, lean;
@@ -68,6 +68,8 @@ struct EncSmall {
     uint32_t crc_part[2][NWARPS];                // per frame buffer
     uint16_t crc_tab[4][256];
 };
+#define RES_BYTES (FRX_MAX_BLOCK * 4)             // the candidate's residuals, sample-major: res[i * 256 + tid]
+#define RES_IDX(i, tid) ((i) * FRX_ENC_THREADS + (tid))
 #define ENC_SMALL_BYTES ((sizeof(EncSmall) + 127) & ~(size_t)127)
 
 // ------------------------------------------------------------------------------------------

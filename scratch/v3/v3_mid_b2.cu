@@ -65,6 +65,13 @@ __device__ __noinline__ void build_frame_desc(const EncArgs &a, FrameDesc &d, ui
         const uint32_t s0 = fj * (uint32_t)a.blocksize;
         const int nsamp = (int)min((long long)a.blocksize, tile_n - (long long)s0);
         d.f = f; d.fj = fj; d.s0 = s0; d.nsamp = nsamp; d.tile_idx = ti;
+        {
+            const int tz = __ffs(nsamp) - 1;               // trailing zeros of the block size
+            int po_max = min(a.max_po, max(0, tz - 4));    // partitions stay multiples of 16 samples
+            while (po_max > 0 && (nsamp >> po_max) <= FRX_MAX_LPC) po_max--;
+            d.po_max = (int16_t)po_max;
+            d.max_lpc = (int16_t)min(a.max_lpc_order, nsamp - 1);
+        }
         const int epv = 16 / frx_dtype_size(a.dtype);            // elements per 16 bytes
         d.tma = (a.tma_ok && (t.w % epv) == 0 && (t.col_off % epv) == 0) ? 1 : 0;
         uint8_t hb[16];
@@ -161,8 +168,8 @@ __device__ __noinline__ void control_warp(const EncArgs &a, EncSmall &sh, unsign
         }
         // ---- 2. next unit (frame, channel) into the raw stage ring ----
         if (have_frame || want_frame) {
-            const int stage = (int)(unit_iss & 1u);
-            if (mbar_test(&sh.empty[stage], ((unit_iss >> 1) & 1u) ^ 1u)) {
+            const int stage = 0;
+            if (mbar_test(&sh.empty[stage], (unit_iss & 1u) ^ 1u)) {
                 progress = true;
                 if (!have_frame) {
                     const int slot = (int)(fseq_iss & (FD_SLOTS - 1));
@@ -184,7 +191,7 @@ __device__ __noinline__ void control_warp(const EncArgs &a, EncSmall &sh, unsign
                 }
                 if (have_frame) {
                     const FrameDesc &d = sh.fd[fseq_iss & (FD_SLOTS - 1)];
-                    unsigned char *dst = raw + (size_t)stage * sh.stage_stride;
+                    unsigned char *dst = raw;
                     if (d.tma) {
                         const long long w = d.t.w;
                         const long long s0 = d.s0, s1 = s0 + d.nsamp;
@@ -230,6 +237,6 @@ __device__ __noinline__ void control_warp(const EncArgs &a, EncSmall &sh, unsign
             } else if (!lb.blocked) progress = true;
         }
         if (stop_issued && !lb_active && fseq_lb == fseq_iss) break;
-        if (!progress) __nanosleep(lb_active ? 100 : 400);
+        if (!progress) __nanosleep(400);
     }
 }

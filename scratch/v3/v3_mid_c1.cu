@@ -164,15 +164,16 @@ __device__ __forceinline__ void put_field(uint32_t *buf, uint32_t p, uint32_t v,
 
 // K7b: Rice-code the thread's residuals straight into the (zeroed) frame buffer.  The unary zeros need no store at all;
 // every sample is one (k+1)-bit field -- stop bit plus low bits -- OR-ed at its bit position, straddling at most two
-// words.  `skip` leading samples are warm-up (thread 0 only), `nv` samples are valid, `plain` = neither applies.
-__device__ __forceinline__ void pack_rice(uint32_t *buf, uint32_t p, const uint32_t *u, uint32_t kk, int skip, int nv, bool plain) {
+// words.  The residuals come from the shared residual buffer (sample-major, conflict-free).  `skip` leading samples are warm-up (thread 0 only), `nv` samples are valid, `plain` = neither applies.
+__device__ __forceinline__ void pack_rice(uint32_t *buf, uint32_t p, const int32_t *res, int tid, uint32_t kk, int skip, int nv, bool plain) {
     const uint32_t kmask = (1u << kk) - 1u;   // kk <= 30
     const uint32_t len = kk + 1u;
 #pragma unroll
     for (int i = 0; i < FRX_SPT; i++) {
         if (plain || (i >= skip && i < nv)) {
-            p += u[i] >> kk;
-            const uint32_t code = (1u << kk) | (u[i] & kmask);
+            const uint32_t u = zigzag(res[RES_IDX(i, tid)]);
+            p += u >> kk;
+            const uint32_t code = (1u << kk) | (u & kmask);
             const uint64_t v = (uint64_t)code << (64u - (p & 31u) - len);
             atomicOr(&buf[p >> 5], (uint32_t)(v >> 32));
             if ((uint32_t)v) atomicOr(&buf[(p >> 5) + 1u], (uint32_t)v);

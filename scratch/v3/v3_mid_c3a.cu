@@ -10,8 +10,9 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
     EncSmall &sh = *reinterpret_cast<EncSmall *>(smem_raw);
     const uint32_t stage_stride = 128u + (uint32_t)FRX_MAX_BLOCK * (uint32_t)frx_dtype_size(a.dtype);
     unsigned char *raw = smem_raw + ENC_SMALL_BYTES;
-    int32_t *pcm = reinterpret_cast<int32_t *>(raw + 2 * stage_stride);
-    uint64_t *tabs = reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(pcm) + PCM_BYTES);
+    int32_t *pcm = reinterpret_cast<int32_t *>(raw + stage_stride);
+    int32_t *res = reinterpret_cast<int32_t *>(reinterpret_cast<unsigned char *>(pcm) + PCM_BYTES);
+    uint64_t *tabs = reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(res) + RES_BYTES);
     uint32_t *bits0 = reinterpret_cast<uint32_t *>(reinterpret_cast<unsigned char *>(tabs) + TABS_BYTES);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -19,8 +20,7 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
     for (int i = tid; i < PCM_WORDS; i += FRX_ENC_CTA) pcm[i] = 0;
     for (int i = tid; i < 1024; i += FRX_ENC_CTA) (&sh.crc_tab[0][0])[i] = a.crc_tab[i];
     if (tid == 0) {
-        sh.stage_stride = stage_stride;
-        for (int i = 0; i < 2; i++) { mbar_init(&sh.full[i], 1); mbar_init(&sh.empty[i], NWARPS); }
+        mbar_init(&sh.full[0], 1); mbar_init(&sh.empty[0], NWARPS);
         for (int i = 0; i < FD_SLOTS; i++) { mbar_init(&sh.sized[i], 1); mbar_init(&sh.placed[i], 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -42,37 +42,30 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
         const int slot = (int)(fseq & (FD_SLOTS - 1));
         const int buf = (int)(fseq & 1u);
         uint32_t *bits = bits0 + (size_t)buf * a.frame_words;
-        mbar_wait(&sh.full[unit & 1u], (unit >> 1) & 1u);
+        mbar_wait(&sh.full[0], unit & 1u);
         const FrameDesc &fd = sh.fd[slot];
         const uint32_t f = fd.f;
         if (f == STOP_FRAME) { if (tid == 0) DBG_ADD(7, DBG_CLK() - ck0); break; }
         if (tid == 0) DBG_TRACE(f, 4);
         DBG_PH(15);
-        const frx_tile t = fd.t;
+        const int n_channels = fd.t.n_channels;
         const uint32_t s0 = fd.s0;
         const int nsamp = fd.nsamp;
         const bool use_tma = fd.tma != 0;
-        const int nthr = (nsamp + FRX_SPT - 1) / FRX_SPT;
         const int nv = min(FRX_SPT, max(0, nsamp - g0));  // valid samples of this thread
         const bool full = (nsamp == FRX_MAX_BLOCK);
         const bool plain = full && tid != 0;              // no per-sample masks needed for this thread
         uint32_t bitpos = fd.hdr_bits;
         if (tid < 4) bits[tid] = fd.hdr[tid];
-        int po_max;
-        {
-            const int tz = __ffs(nsamp) - 1;               // trailing zeros of the block size
-            po_max = min(a.max_po, max(0, tz - 4));        // partitions stay multiples of 16 samples
-            while (po_max > 0 && (nsamp >> po_max) <= FRX_MAX_LPC) po_max--;
-        }
-        const int max_lpc = min(min(a.max_lpc_order, HISTN), nsamp - 1);
+        const int po_max = fd.po_max;
+        const int max_lpc = min((int)fd.max_lpc, HISTN);
 
         // ================= per channel =================
-        for (int ch = 0; ch < t.n_channels; ch++) {
-            const int stage = (int)(unit & 1u);
-            unsigned char *stg = raw + (size_t)stage * stage_stride;
-            if (ch > 0) mbar_wait(&sh.full[stage], (unit >> 1) & 1u);
+        for (int ch = 0; ch < n_channels; ch++) {
+            unsigned char *stg = raw;
+            if (ch > 0) mbar_wait(&sh.full[0], unit & 1u);
             if (!use_tma) {
-                gather_raw(a, t, ch, s0, nsamp, stg, tid);
+                gather_raw(a, fd.t, ch, s0, nsamp, stg, tid);
                 compute_sync();
             }
             // ---- K1: the thread's 16 samples -> PCM -> shared memory ----
@@ -86,7 +79,7 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                 // the raw stage may be refilled as soon as every warp has read its samples
                 if (!use_tma) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&sh.empty[stage]);
+                if (lane == 0) mbar_arrive(&sh.empty[0]);
                 unit++;
             }
             orv = __reduce_or_sync(FULLMASK, orv);

@@ -3,7 +3,6 @@
             const int sbps = a.bps - wasted;
             const int lpc_order = sh.lpc_order;
             const int lshift = sh.shift;
-            int32_t r[FRX_SPT];
             if (WIDE && !lean) {
                 fat_search<HISTN>(sh, pcm, tabs, tid, nv, nsamp, wasted, po_max, kmax);
             } else {
@@ -14,17 +13,9 @@
                     read_pcm<HISTN>(pcm, tid, wasted, s);
 #pragma unroll
                     for (int j = 0; j < HISTN; j++) q[j] = sh.qlp[j];
-                    if (!WIDE || sh.lpc_narrow) (void)lpc_residuals_dispatch<0, HISTN>(lpc_order, s, q, lshift, r);
-                    else (void)lpc_residuals_dispatch<1, HISTN>(lpc_order, s, q, lshift, r);
-                    uint32_t ab = 0;
-                    if (plain) {
-#pragma unroll
-                        for (int i = 0; i < FRX_SPT; i++) ab += (uint32_t)abs(r[i]);
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < FRX_SPT; i++)
-                            if (i < nv && g0 + i >= lpc_order) ab += (uint32_t)abs(r[i]);
-                    }
+                    uint32_t ab;
+                    if (!WIDE || sh.lpc_narrow) ab = lpc_residuals_park<0, HISTN>(s, q, lshift, res, tid, plain, nv, lpc_order - g0);
+                    else ab = lpc_residuals_park<1, HISTN>(s, q, lshift, res, tid, plain, nv, lpc_order - g0);
                     tabs[5 * FRX_ENC_THREADS + tid] = ab;
                 }
                 compute_sync();  // SC
@@ -63,7 +54,6 @@
             // ---- K7a: winner's residuals (zig-zag folded), exact bit count per thread, block scan ----
             const uint32_t sub_start = bitpos;
             const uint32_t smask = sbps >= 32 ? 0xFFFFFFFFu : ((1u << sbps) - 1u);
-            uint32_t u[FRX_SPT];
             int psize = nsamp;
             uint32_t kk = 0;
             uint32_t mybits = 0;
@@ -71,8 +61,9 @@
             if (type >= 2) {
                 psize = nsamp >> po;
                 kk = sh.kparam[cand][(1 << po) - 1 + min(g0 / psize, (1 << po) - 1)];
+                int32_t r[FRX_SPT];
                 if (type == 2 || (WIDE && !lean)) {
-                    // fixed winner (4 ops per sample) or a fat-path LPC winner: recompute from the PCM
+                    // fixed winner (4 ops per sample) or a fat-path LPC winner: recompute from the PCM, park in the residual buffer
                     int32_t s[HISTN + FRX_SPT];
                     read_pcm<HISTN>(pcm, tid, wasted, s);
                     if (type == 2) {
@@ -84,20 +75,24 @@
                         for (int j = 0; j < HISTN; j++) q[j] = sh.qlp[j];
                         (void)lpc_residuals_dispatch<1, HISTN>(order, s, q, lshift, r);
                     }
-                }
-                uint32_t qs = 0;
 #pragma unroll
-                for (int i = 0; i < FRX_SPT; i++) {
-                    u[i] = zigzag(r[i]);
-                    qs += u[i] >> kk;
+                    for (int i = 0; i < FRX_SPT; i++) res[RES_IDX(i, tid)] = r[i];
+                } else {
+                    // lean LPC winner: K5 left its residuals in the buffer
+#pragma unroll
+                    for (int i = 0; i < FRX_SPT; i++) r[i] = res[RES_IDX(i, tid)];
                 }
-                if (plain) mybits = qs + (uint32_t)FRX_SPT * (1u + kk);
-                else {
+                if (plain) {
+                    uint32_t qs = 0;
+#pragma unroll
+                    for (int i = 0; i < FRX_SPT; i++) qs += zigzag(r[i]) >> kk;
+                    mybits = qs + (uint32_t)FRX_SPT * (1u + kk);
+                } else {
 #pragma unroll
                     for (int i = 0; i < FRX_SPT; i++)
-                        if (i >= skip && i < nv) mybits += (u[i] >> kk) + 1u + kk;
+                        if (i >= skip && i < nv) mybits += (zigzag(r[i]) >> kk) + 1u + kk;
                 }
-                if (tid < nthr && g0 % psize == 0) mybits += rice2 ? 5u : 4u;
+                if (nv > 0 && g0 % psize == 0) mybits += rice2 ? 5u : 4u;
                 if (tid == 0) {
                     mybits += 8u + (uint32_t)wasted + (uint32_t)order * (uint32_t)sbps + 6u;
                     if (type == 3) mybits += 9u + (uint32_t)order * (uint32_t)sh.precision;
@@ -147,7 +142,7 @@
             }
             const uint32_t start = sub_start + wbase + incl - mybits;
             bitpos = sub_start + total;
-            if (ch == t.n_channels - 1 && tid == 0) {
+            if (ch == n_channels - 1 && tid == 0) {
                 // the frame's size is final: hand it to the control warp so the look-back overlaps packing and the CRC
                 const uint32_t nb = ((bitpos + 7u) >> 3) + 2u;
                 if (f != 0) frx_st_relaxed_u64(&a.desc[f], (1ull << 62) | (uint64_t)nb);
@@ -181,7 +176,7 @@
                         if (kk) put_field(bits, p, kk, pb);
                         p += pb;
                     }
-                    pack_rice(bits, p, u, kk, skip, nv, plain);
+                    pack_rice(bits, p, res, tid, kk, skip, nv, plain);
                 }
             } else if (mybits) {
                 BitW bw;
@@ -198,7 +193,7 @@
                 bw.finish();
             }
             // the PCM buffer is rewritten by the next channel's K1: every reader of it (verbatim / warm-up packing) must be done
-            if (ch + 1 < t.n_channels) compute_sync();
+            if (ch + 1 < n_channels) compute_sync();
         }  // channels
         compute_sync();  // Sa: every subframe is packed
         DBG_PH(14);
