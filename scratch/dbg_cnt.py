@@ -5,7 +5,7 @@ from flac_raster_b200.codec import Codec, tile_grid
 import flac_raster_b200.codec as C
 lib = ctypes.CDLL('/root/repo/flac_raster_b200/libfrx.so')
 codec = Codec(0)
-names = ['analyse fixed (w0)', 'lpc_design (w1 lane0)', 'analyse lpc (w1)', 'lb_rounds', 'lb_notready', 'PH footer(crc+copy)', 'frames', 'compute_total', 'PH lpcres ->SC', 'PH K1 ->S0', 'PH trial+autoc ->SA', 'PH decide/design ->SB', 'PH analyse ->SD', 'PH choose/scan ->SE', 'PH pack ->Sa', 'PH waitfull']
+names = ['analyse L6 (w6)', 'lpc_design (w7)', 'analyse L0 (w0)', 'lb_rounds', 'lb_notready', 'PH footer(crc+copy)', 'frames', 'compute_total', 'PH lpcres ->SC', 'PH K1 ->S0', 'PH trial+autoc ->SA', 'PH decide/design ->SB', 'PH analyse ->SD', 'PH choose/scan ->SE', 'PH pack ->Sa', 'PH waitfull']
 for H in (8192,):
     r = synth.dem_f32(H, H, seed=1)
     tiles = tile_grid(H, H, 1024, 0, 1)

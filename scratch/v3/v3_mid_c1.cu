@@ -86,10 +86,10 @@ __device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, in
             }
             if (i & 1) lpc[i >> 1] += lpc[i >> 1] * r;
             err *= (1.0f - r * r);
-            float mine = 0.f;                      // lane j stores predictor coefficient j of order i+1
+            if (lane == 0) {                       // (a per-lane select of lpc[j] would turn lpc[] into a local-memory array)
 #pragma unroll
-            for (int j = 0; j <= i; j++) if (lane == j) mine = -lpc[j];
-            if (lane <= i) sh.lpc_rows[i][lane] = mine;
+                for (int j = 0; j <= i; j++) sh.lpc_rows[i][j] = -lpc[j];
+            }
             if (lane == i) myerr = err;
             if (!(err > 0.f)) mo = i + 1;
         }

@@ -157,8 +157,10 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                     if (lane <= FRX_MAX_LPC) sh.autoc[lane] = acs;
                     if (lane == 0) { sh.magbits = magbits; sh.lean = lean ? 1 : 0; sh.lpc_ok = 0; }
                     __syncwarp();
+                    const long long cl0 = DBG_CLK();
                     if (max_lpc > 0 && nsamp > 4)
                         lpc_design<WIDE, HISTN>(sh, max_lpc, nsamp, wasted, a.bps - wasted, a.qlp_precision, magbits, lean, lane);
+                    if (lane == 0) DBG_ADD(1, DBG_CLK() - cl0);
                 } else {
                     const uint64_t f1 = __shfl_sync(FULLMASK, tot, 1);
                     uint64_t bestv = (lane < 5) ? tot : ~0ull;   // best fixed order among lanes 0..4 (lowest order wins ties)
@@ -176,8 +178,12 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
                         sh.fixed_order = fixed_order;
                     }
                     if (fixed_order >= 0 && lean) {          // fat data: fat_search redoes the fixed candidate in 64 bits
-                        if (full) { if (warp <= po_max) analyse_level(sh, tabs + fixed_order * FRX_ENC_THREADS, 0, warp, fixed_order, kmax, wasted); }
-                        else if (warp == 0) analyse_partitions(sh, tabs + fixed_order * FRX_ENC_THREADS, 0, nsamp, fixed_order, po_max, kmax, wasted);
+                        const long long ca0 = DBG_CLK();
+                        if (full) {
+                            if (warp <= po_max) analyse_level(sh, tabs + fixed_order * FRX_ENC_THREADS, 0, warp, fixed_order, kmax, wasted);
+                            if (lane == 0 && warp == 6) DBG_ADD(0, DBG_CLK() - ca0);
+                            if (lane == 0 && warp == 0) DBG_ADD(2, DBG_CLK() - ca0);
+                        } else if (warp == 0) analyse_partitions(sh, tabs + fixed_order * FRX_ENC_THREADS, 0, nsamp, fixed_order, po_max, kmax, wasted);
                     }
                 }
             }
