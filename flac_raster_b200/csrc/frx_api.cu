@@ -2,6 +2,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <vector>
@@ -41,6 +42,11 @@ struct frx_ctx {
     cudaEvent_t ev[4] = { nullptr, nullptr, nullptr, nullptr };
     bool enc_timed = false, dec_timed = false;
     int verify_crc = 1;
+    // *_host pipeline: copy-in / compute / copy-out streams, one event per tile group, pinned per-group totals
+    cudaStream_t hs[3] = { nullptr, nullptr, nullptr };
+    std::vector<cudaEvent_t> hev;
+    void *pin_small = nullptr;
+    size_t pin_small_cap = 0;
 };
 
 static int ensure(Buf &b, size_t bytes) {
@@ -103,6 +109,9 @@ void frx_ctx_destroy(frx_ctx *c) {
                    &c->h_raster, &c->h_bytes, &c->h_small, &c->h_out };
     for (Buf *b : all) if (b->p) cudaFree(b->p);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    for (int i = 0; i < 3; i++) if (c->hs[i]) cudaStreamDestroy(c->hs[i]);
+    for (cudaEvent_t e : c->hev) cudaEventDestroy(e);
+    if (c->pin_small) cudaFreeHost(c->pin_small);
     delete c;
 }
 
@@ -439,6 +448,14 @@ int frx_dequantize(frx_ctx *c, const int32_t *pcm_dev, int32_t h, int32_t w, int
 }
 
 // ---- host-buffer entry points: stage, run, fetch ---------------------------------------------
+// Host buffers in, host buffers out.  The tiles are cut into groups of consecutive tiles (a group = the tiles that
+// share a band of raster rows, at least FRX_HOST_GROUP_BYTES of samples -- the environment variable of that name overrides it); while group k is encoded, the rows of the
+// groups behind it are still arriving over PCIe and the bytes of group k-1 are already leaving, each on its own stream.
+// Every group is one frx_encode_tiles() call into its own slice of the device output (slices sized by the worst-case
+// bound), so the result is byte-identical to a single call: the group streams are simply concatenated on the host side
+// and the per-group offsets rebased.
+#define FRX_HOST_GROUP_BYTES (32ull << 20)
+#define FRX_HOST_ROW_BLOCK_BYTES (8ull << 20)
 int frx_encode_tiles_host(frx_ctx *c, const frx_raster *raster_host, const frx_tile *tiles, int32_t n_tiles,
                           const frx_encode_params *p, const frx_encode_out *out) {
     if (!c) return set_err(FRX_E_INVALID, "ctx is NULL");
@@ -451,7 +468,9 @@ int frx_encode_tiles_host(frx_ctx *c, const frx_raster *raster_host, const frx_t
     uint64_t total_frames = 0, max_bytes = 0;
     rc = frx_encode_bound(tiles, n_tiles, r.dtype, p, &total_frames, &max_bytes); if (rc) return rc;
     const size_t esz = (size_t)frx_dtype_size(r.dtype);
-    // H2D: the band range the tiles touch, row range likewise (dense copy of the covering box)
+    for (int i = 0; i < 3; i++) if (!c->hs[i]) CK(cudaStreamCreateWithFlags(&c->hs[i], cudaStreamNonBlocking));
+    cudaStream_t s_in = c->hs[0], s_cmp = c->hs[1], s_out = c->hs[2];
+    // the band range and the row range the tiles touch: the device copy is the dense covering box
     long long r0 = r.height, r1 = 0, b0 = r.bands, b1 = 0;
     for (int i = 0; i < n_tiles; i++) {
         if (tiles[i].row_off < r0) r0 = tiles[i].row_off;
@@ -462,49 +481,136 @@ int frx_encode_tiles_host(frx_ctx *c, const frx_raster *raster_host, const frx_t
     const long long rows = r1 - r0, nb = b1 - b0;
     const size_t plane = (size_t)rows * (size_t)r.width;
     ENSURE(c->h_raster, plane * (size_t)nb * esz);
-    cudaStream_t st = 0;
-    for (long long b = 0; b < nb; b++) {
-        const char *src = (const char *)r.data + ((size_t)(b0 + b) * (size_t)r.band_stride + (size_t)r0 * (size_t)r.row_stride) * esz;
-        CK(cudaMemcpy2DAsync((char *)c->h_raster.p + (size_t)b * plane * esz, (size_t)r.width * esz, src, (size_t)r.row_stride * esz,
-                             (size_t)r.width * esz, (size_t)rows, cudaMemcpyHostToDevice, st));
+    // ---- tile groups ----
+    struct Group { int t0, t1; long long gr0, gr1; uint64_t frames, bound, byte_base, frame_base; };
+    std::vector<Group> groups;
+    {
+        uint64_t group_bytes = FRX_HOST_GROUP_BYTES;
+        if (const char *e = getenv("FRX_HOST_GROUP_BYTES")) { const long long v = atoll(e); if (v > 0) group_bytes = (uint64_t)v; }
+        int t0 = 0;
+        while (t0 < n_tiles) {
+            Group g;
+            g.t0 = t0; g.gr0 = tiles[t0].row_off; g.gr1 = tiles[t0].row_off + tiles[t0].h;
+            uint64_t bytes = 0;
+            int t = t0;
+            while (t < n_tiles) {
+                const bool same_rows = tiles[t].row_off >= g.gr0 && tiles[t].row_off + tiles[t].h <= g.gr1;
+                if (!same_rows && bytes >= group_bytes) break;
+                if (tiles[t].row_off < g.gr0) g.gr0 = tiles[t].row_off;
+                if (tiles[t].row_off + tiles[t].h > g.gr1) g.gr1 = tiles[t].row_off + tiles[t].h;
+                bytes += (uint64_t)tiles[t].h * tiles[t].w * tiles[t].n_channels * esz;
+                t++;
+            }
+            g.t1 = t;
+            groups.push_back(g);
+            t0 = t;
+        }
+        uint64_t bb = 0, fb = 0;
+        for (Group &g : groups) {
+            rc = frx_encode_bound(tiles + g.t0, g.t1 - g.t0, r.dtype, p, &g.frames, &g.bound); if (rc) return rc;
+            g.byte_base = bb; g.frame_base = fb;
+            bb += (g.bound + 15) & ~15ull;      // 16-byte aligned slices
+            fb += g.frames;
+        }
+        max_bytes = bb;
     }
-    std::vector<frx_tile> lt(tiles, tiles + n_tiles);
-    for (auto &t : lt) { t.row_off -= (int32_t)r0; t.first_band -= (int32_t)b0; }
-    frx_raster rd = r;
-    rd.data = c->h_raster.p; rd.bands = (int32_t)nb; rd.height = rows; rd.row_stride = r.width; rd.band_stride = (long long)plane;
-    // device outputs
-    uint64_t cap = out->capacity < max_bytes ? out->capacity : max_bytes;
-    ENSURE(c->h_bytes, cap + 16);
+    const int ng = (int)groups.size();
+    while ((int)c->hev.size() < ng) { cudaEvent_t e; CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); c->hev.push_back(e); }
+    if (c->pin_small_cap < (size_t)ng * 16) {
+        if (c->pin_small) cudaFreeHost(c->pin_small);
+        c->pin_small = nullptr; c->pin_small_cap = 0;
+        CK(cudaHostAlloc(&c->pin_small, (size_t)ng * 16 + 64, cudaHostAllocDefault));
+        c->pin_small_cap = (size_t)ng * 16 + 64;
+    }
+    struct Tot { uint64_t total; int32_t status, pad; };
+    Tot *tot = (Tot *)c->pin_small;
+    // ---- device outputs ----
+    ENSURE(c->h_bytes, max_bytes + 16);
     size_t small = sizeof(uint64_t) * 2 * (size_t)n_tiles + sizeof(double) * 2 * (size_t)n_tiles + sizeof(uint32_t) * (size_t)total_frames +
-                   sizeof(uint64_t) * (size_t)total_frames + 64;
+                   sizeof(uint64_t) * (size_t)total_frames + 16 * (size_t)ng + 64;
     ENSURE(c->h_small, small);
     char *sp = (char *)c->h_small.p;
-    frx_encode_out od;
-    memset(&od, 0, sizeof(od));
-    od.bytes = (uint8_t *)c->h_bytes.p; od.capacity = cap;
-    od.total_bytes = (uint64_t *)sp; sp += 16;
-    od.status = (int32_t *)sp; sp += 16;
-    od.tile_offset = (uint64_t *)sp; sp += sizeof(uint64_t) * n_tiles;
-    od.tile_size = (uint64_t *)sp; sp += sizeof(uint64_t) * n_tiles;
-    od.tile_minmax = (double *)sp; sp += sizeof(double) * 2 * n_tiles;
-    od.frame_offset = (uint64_t *)sp; sp += sizeof(uint64_t) * total_frames;
-    od.frame_size = (uint32_t *)sp;
-    rc = frx_encode_tiles(c, &rd, lt.data(), n_tiles, p, &od, st); if (rc) return rc;
-    uint64_t total = 0;
-    int32_t status = 0;
-    CK(cudaMemcpyAsync(&total, od.total_bytes, sizeof(total), cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(&status, od.status, sizeof(status), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    if (out->total_bytes) *out->total_bytes = total;
-    if (out->status) *out->status = status;
-    if (status) return set_err(status, "output capacity %llu too small (need %llu)", (unsigned long long)out->capacity, (unsigned long long)total);
-    CK(cudaMemcpyAsync(out->bytes, od.bytes, total, cudaMemcpyDeviceToHost, st));
-    if (out->tile_offset) CK(cudaMemcpyAsync(out->tile_offset, od.tile_offset, sizeof(uint64_t) * n_tiles, cudaMemcpyDeviceToHost, st));
-    if (out->tile_size) CK(cudaMemcpyAsync(out->tile_size, od.tile_size, sizeof(uint64_t) * n_tiles, cudaMemcpyDeviceToHost, st));
-    if (out->tile_minmax) CK(cudaMemcpyAsync(out->tile_minmax, od.tile_minmax, sizeof(double) * 2 * n_tiles, cudaMemcpyDeviceToHost, st));
-    if (out->frame_offset) CK(cudaMemcpyAsync(out->frame_offset, od.frame_offset, sizeof(uint64_t) * total_frames, cudaMemcpyDeviceToHost, st));
-    if (out->frame_size) CK(cudaMemcpyAsync(out->frame_size, od.frame_size, sizeof(uint32_t) * total_frames, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
+    Tot *tot_dev = (Tot *)sp; sp += 16 * (size_t)ng;
+    uint64_t *d_tile_offset = (uint64_t *)sp; sp += sizeof(uint64_t) * n_tiles;
+    uint64_t *d_tile_size = (uint64_t *)sp; sp += sizeof(uint64_t) * n_tiles;
+    double *d_tile_minmax = (double *)sp; sp += sizeof(double) * 2 * n_tiles;
+    uint64_t *d_frame_offset = (uint64_t *)sp; sp += sizeof(uint64_t) * total_frames;
+    uint32_t *d_frame_size = (uint32_t *)sp;
+    // ---- copy-in: row blocks in the order the groups need them, all queued up front on their own stream ----
+    {
+        long long rb = (long long)(FRX_HOST_ROW_BLOCK_BYTES / ((size_t)r.width * esz * (size_t)nb));
+        if (rb < 1) rb = 1;
+        const long long nblk = (rows + rb - 1) / rb;
+        std::vector<char> have((size_t)nblk, 0);
+        for (int k = 0; k < ng; k++) {
+            const long long k0 = (groups[k].gr0 - r0) / rb, k1 = (groups[k].gr1 - r0 + rb - 1) / rb;
+            for (long long blk = k0; blk < k1; blk++) {
+                if (have[(size_t)blk]) continue;
+                have[(size_t)blk] = 1;
+                const long long y0 = blk * rb, y1 = (y0 + rb < rows) ? y0 + rb : rows;
+                for (long long b = 0; b < nb; b++) {
+                    const char *src = (const char *)r.data + ((size_t)(b0 + b) * (size_t)r.band_stride + (size_t)(r0 + y0) * (size_t)r.row_stride) * esz;
+                    char *dst = (char *)c->h_raster.p + ((size_t)b * plane + (size_t)y0 * (size_t)r.width) * esz;
+                    CK(cudaMemcpy2DAsync(dst, (size_t)r.width * esz, src, (size_t)r.row_stride * esz, (size_t)r.width * esz, (size_t)(y1 - y0),
+                                         cudaMemcpyHostToDevice, s_in));
+                }
+            }
+            CK(cudaEventRecord(c->hev[k], s_in));
+        }
+    }
+    frx_raster rd = r;
+    rd.data = c->h_raster.p; rd.bands = (int32_t)nb; rd.height = rows; rd.row_stride = r.width; rd.band_stride = (long long)plane;
+    // ---- encode group k while group k-1 goes home ----
+    std::vector<frx_tile> lt;
+    std::vector<uint64_t> host_base((size_t)ng, 0);
+    uint64_t host_off = 0;
+    int failed = 0;
+    auto copy_out_group = [&](int k) -> int {
+        // the group's encode and its totals copy have completed (the caller synchronised the compute stream)
+        const Group &g = groups[k];
+        host_base[k] = host_off;
+        if (tot[k].status) { failed = tot[k].status; host_off += tot[k].total; return FRX_OK; }
+        if (host_off + tot[k].total > out->capacity) { failed = FRX_E_OVERFLOW; host_off += tot[k].total; return FRX_OK; }
+        CK(cudaMemcpyAsync(out->bytes + host_off, (const uint8_t *)c->h_bytes.p + g.byte_base, tot[k].total, cudaMemcpyDeviceToHost, s_out));
+        host_off += tot[k].total;
+        return FRX_OK;
+    };
+    for (int k = 0; k < ng; k++) {
+        const Group &g = groups[k];
+        lt.assign(tiles + g.t0, tiles + g.t1);
+        for (auto &t : lt) { t.row_off -= (int32_t)r0; t.first_band -= (int32_t)b0; }
+        frx_encode_out od;
+        memset(&od, 0, sizeof(od));
+        od.bytes = (uint8_t *)c->h_bytes.p + g.byte_base; od.capacity = g.bound;
+        od.total_bytes = &tot_dev[k].total; od.status = &tot_dev[k].status;
+        od.tile_offset = d_tile_offset + g.t0; od.tile_size = d_tile_size + g.t0; od.tile_minmax = d_tile_minmax + 2 * (size_t)g.t0;
+        od.frame_offset = d_frame_offset + g.frame_base; od.frame_size = d_frame_size + g.frame_base;
+        CK(cudaStreamWaitEvent(s_cmp, c->hev[k], 0));
+        // (frx_encode_tiles synchronises its stream once while staging the tile tables: group k-1 is finished after it)
+        rc = frx_encode_tiles(c, &rd, lt.data(), g.t1 - g.t0, p, &od, s_cmp); if (rc) return rc;
+        CK(cudaMemcpyAsync(&tot[k], &tot_dev[k], sizeof(Tot), cudaMemcpyDeviceToHost, s_cmp));
+        if (k > 0) { rc = copy_out_group(k - 1); if (rc) return rc; }
+    }
+    CK(cudaStreamSynchronize(s_cmp));
+    rc = copy_out_group(ng - 1); if (rc) return rc;
+    if (out->total_bytes) *out->total_bytes = host_off;
+    if (out->status) *out->status = failed;
+    if (failed) {
+        cudaStreamSynchronize(s_out);
+        return set_err(failed, "output capacity %llu too small (need %llu)", (unsigned long long)out->capacity, (unsigned long long)host_off);
+    }
+    if (out->tile_offset) CK(cudaMemcpyAsync(out->tile_offset, d_tile_offset, sizeof(uint64_t) * n_tiles, cudaMemcpyDeviceToHost, s_out));
+    if (out->tile_size) CK(cudaMemcpyAsync(out->tile_size, d_tile_size, sizeof(uint64_t) * n_tiles, cudaMemcpyDeviceToHost, s_out));
+    if (out->tile_minmax) CK(cudaMemcpyAsync(out->tile_minmax, d_tile_minmax, sizeof(double) * 2 * n_tiles, cudaMemcpyDeviceToHost, s_out));
+    if (out->frame_offset) CK(cudaMemcpyAsync(out->frame_offset, d_frame_offset, sizeof(uint64_t) * total_frames, cudaMemcpyDeviceToHost, s_out));
+    if (out->frame_size) CK(cudaMemcpyAsync(out->frame_size, d_frame_size, sizeof(uint32_t) * total_frames, cudaMemcpyDeviceToHost, s_out));
+    CK(cudaStreamSynchronize(s_out));
+    // offsets inside a group start at 0: rebase them onto the concatenated stream
+    for (int k = 1; k < ng; k++) {
+        const Group &g = groups[k];
+        if (out->tile_offset) for (int t = g.t0; t < g.t1; t++) out->tile_offset[t] += host_base[k];
+        if (out->frame_offset) for (uint64_t f = g.frame_base; f < g.frame_base + g.frames; f++) out->frame_offset[f] += host_base[k];
+    }
     return FRX_OK;
 }
 

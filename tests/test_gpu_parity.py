@@ -211,6 +211,34 @@ def test_host_entry_points_roundtrip(codec, golden):
         assert np.array_equal(out[e["out_offset"]: e["out_offset"] + nch * h * w].reshape(nch, h, w), want.reshape(nch, h, w))
 
 
+def test_host_pipeline_groups_equal_single_call(codec, monkeypatch):
+    """frx_encode_tiles_host cuts the tiles into groups that overlap copy-in, encode and copy-out; however the groups fall,
+    the stream and every index array must equal the one-call device path."""
+    import torch
+    from flac_raster_b200 import synth
+    r = synth.dem_f32(1100, 900, seed=5).cpu().numpy()
+    tiles = tiles_for(r, 256, "all")
+    dev = codec.encode_tiles(torch.from_numpy(r).cuda(), tiles)
+    total = int(dev.total_bytes.cpu()[0])
+    want = dev.bytes[:total].cpu().numpy()
+    for group_bytes in ("1", "300000", "1000000000"):
+        monkeypatch.setenv("FRX_HOST_GROUP_BYTES", group_bytes)
+        res = codec.encode_tiles_host(r, tiles)
+        assert int(res.total_bytes[0]) == total
+        assert np.array_equal(res.bytes[:total], want)
+        assert np.array_equal(res.tile_offset, dev.tile_offset.cpu().numpy())
+        assert np.array_equal(res.tile_size, dev.tile_size.cpu().numpy())
+        assert np.array_equal(res.frame_offset, dev.frame_offset.cpu().numpy())
+        assert np.array_equal(res.frame_size, dev.frame_size.cpu().numpy())
+        assert np.array_equal(res.tile_minmax, dev.tile_minmax.cpu().numpy())
+    # a capacity that is too small is reported, not overrun
+    from flac_raster_b200._lib import FrxError
+    small = codec.encode_tiles_host(r, tiles)
+    small.bytes = np.empty(total // 2, dtype=np.uint8)
+    with pytest.raises(FrxError):
+        codec.encode_tiles_host(r, tiles, out=small)
+
+
 def test_more_than_8_channels_is_rejected(codec):
     import torch
     from flac_raster_b200._lib import FrxUnsupported
