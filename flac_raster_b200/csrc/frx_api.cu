@@ -34,7 +34,7 @@ struct frx_ctx {
     int sm_count = 148;
     uint64_t launches = 0;
     Buf tiles, prefix, unit_prefix, mmraw, quant, desc, misc, window, xpow, crctab, fsize, foff;
-    Buf dtiles, dprefix, fpos, scan_prefix, scan_tiles;
+    Buf dtiles, dprefix, fpos, flen, scan_prefix, scan_tiles;
     Buf h_raster, h_bytes, h_small, h_out;  // device staging for the *_host entry points
     int window_len = -1;
     int xpow_L = -1;
@@ -72,6 +72,28 @@ static int ensure_crctab(frx_ctx *c) {
     return FRX_OK;
 }
 
+// CRC chunk combine tables (frx_encode.cu, frx_crc_check_kernel): x^(128 * Lq * j) mod P for Lq = 1..FRX_CRC_MAXLQ, j = 0..255;
+// x^(-32 z), z = 0..3
+static int ensure_xpow(frx_ctx *c) {
+    if (c->xpow_L != 2) {
+        std::vector<uint16_t> xp(FRX_CRC_MAXLQ * 256 + 4);
+        for (int lq = 1; lq <= FRX_CRC_MAXLQ; lq++) {
+            uint32_t base = 2, e = 128u * lq, acc = 1;
+            while (e) { if (e & 1u) acc = frx_gf16_mulmod(acc, base); base = frx_gf16_mulmod(base, base); e >>= 1; }
+            uint32_t cur = 1;
+            for (int j = 0; j < 256; j++) { xp[(lq - 1) * 256 + j] = (uint16_t)cur; cur = frx_gf16_mulmod(cur, acc); }
+        }
+        uint32_t inv32 = 0xC002u;                       // x^-1: x * (x^15 + x^14 + x) = P + 1
+        for (int i = 0; i < 5; i++) inv32 = frx_gf16_mulmod(inv32, inv32);   // x^-32
+        uint32_t cur = 1;
+        for (int z = 0; z < 4; z++) { xp[FRX_CRC_MAXLQ * 256 + z] = (uint16_t)cur; cur = frx_gf16_mulmod(cur, inv32); }
+        ENSURE(c->xpow, sizeof(uint16_t) * xp.size());
+        CK(cudaMemcpy(c->xpow.p, xp.data(), sizeof(uint16_t) * xp.size(), cudaMemcpyHostToDevice));
+        c->xpow_L = 2;
+    }
+    return FRX_OK;
+}
+
 extern "C" {
 
 int frx_version(void) { return FRX_VERSION_MAJOR * 100 + FRX_VERSION_MINOR; }
@@ -105,7 +127,7 @@ void frx_ctx_destroy(frx_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     Buf *all[] = { &c->tiles, &c->prefix, &c->unit_prefix, &c->mmraw, &c->quant, &c->desc, &c->misc, &c->window, &c->xpow,
-                   &c->crctab, &c->fsize, &c->foff, &c->dtiles, &c->dprefix, &c->fpos, &c->scan_prefix, &c->scan_tiles,
+                   &c->crctab, &c->fsize, &c->foff, &c->dtiles, &c->dprefix, &c->fpos, &c->flen, &c->scan_prefix, &c->scan_tiles,
                    &c->h_raster, &c->h_bytes, &c->h_small, &c->h_out };
     for (Buf *b : all) if (b->p) cudaFree(b->p);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
@@ -285,23 +307,7 @@ int frx_encode_tiles(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *t
     }
     const uint64_t fb = frame_bytes_bound(prep.max_channels, prep.bps, p->blocksize);
     const int frame_words = (((int)((fb + 3) / 4) + 8) + 3) & ~3;   // multiple of 4: the second frame buffer stays 16-byte aligned
-    if (c->xpow_L != 2) {
-        // CRC chunk combine tables (frx_encode.cu): x^(128 * Lq * j) mod P for Lq = 1..FRX_CRC_MAXLQ, j = 0..255; x^(-32 z), z = 0..3
-        std::vector<uint16_t> xp(FRX_CRC_MAXLQ * 256 + 4);
-        for (int lq = 1; lq <= FRX_CRC_MAXLQ; lq++) {
-            uint32_t base = 2, e = 128u * lq, acc = 1;
-            while (e) { if (e & 1u) acc = frx_gf16_mulmod(acc, base); base = frx_gf16_mulmod(base, base); e >>= 1; }
-            uint32_t cur = 1;
-            for (int j = 0; j < 256; j++) { xp[(lq - 1) * 256 + j] = (uint16_t)cur; cur = frx_gf16_mulmod(cur, acc); }
-        }
-        uint32_t inv32 = 0xC002u;                       // x^-1: x * (x^15 + x^14 + x) = P + 1
-        for (int i = 0; i < 5; i++) inv32 = frx_gf16_mulmod(inv32, inv32);   // x^-32
-        uint32_t cur = 1;
-        for (int z = 0; z < 4; z++) { xp[FRX_CRC_MAXLQ * 256 + z] = (uint16_t)cur; cur = frx_gf16_mulmod(cur, inv32); }
-        ENSURE(c->xpow, sizeof(uint16_t) * xp.size());
-        CK(cudaMemcpy(c->xpow.p, xp.data(), sizeof(uint16_t) * xp.size(), cudaMemcpyHostToDevice));
-        c->xpow_L = 2;
-    }
+    { int rc2 = ensure_xpow(c); if (rc2) return rc2; }
     if (frame_words > FRX_CRC_MAXLQ * 256 * 4) return set_err(FRX_E_UNSUPPORTED, "frame too large for the CRC chunk tables");
     {
         int rc2 = ensure_crctab(c);
@@ -398,9 +404,11 @@ static int decode_core(frx_ctx *c, const uint8_t *bytes_dev, uint64_t n_bytes, c
     ENSURE(c->dtiles, sizeof(frx_dtile) * n_tiles);
     ENSURE(c->dprefix, sizeof(uint32_t) * (n_tiles + 1));
     ENSURE(c->fpos, sizeof(uint64_t) * (size_t)(nf + 1));
+    ENSURE(c->flen, sizeof(uint32_t) * (size_t)(nf + 1));
     ENSURE(c->scan_prefix, sizeof(uint32_t) * sprefix.size());
     ENSURE(c->scan_tiles, sizeof(int32_t) * (stiles.size() + 1));
     { int rc2 = ensure_crctab(c); if (rc2) return rc2; }
+    { int rc2 = ensure_xpow(c); if (rc2) return rc2; }
     CK(cudaMemcpyAsync(c->dtiles.p, tiles, sizeof(frx_dtile) * n_tiles, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(c->dprefix.p, dprefix.data(), sizeof(uint32_t) * (n_tiles + 1), cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(c->scan_prefix.p, sprefix.data(), sizeof(uint32_t) * sprefix.size(), cudaMemcpyHostToDevice, st));
@@ -410,7 +418,7 @@ static int decode_core(frx_ctx *c, const uint8_t *bytes_dev, uint64_t n_bytes, c
     DecArgs a;
     memset(&a, 0, sizeof(a));
     a.bytes = bytes_dev; a.n_bytes = n_bytes; a.tiles = (const frx_dtile *)c->dtiles.p; a.dprefix = (const uint32_t *)c->dprefix.p;
-    a.frame_pos = (uint64_t *)c->fpos.p; a.frame_size = frame_size_dev; a.crc_tab = (const uint16_t *)c->crctab.p;
+    a.frame_pos = (uint64_t *)c->fpos.p; a.frame_len = (uint32_t *)c->flen.p; a.frame_size = frame_size_dev; a.crc_tab = (const uint16_t *)c->crctab.p;
     a.out = out_dev; a.tile_status = tile_status_dev; a.total_frames = (uint32_t)nf; a.n_tiles = n_tiles; a.blocksize = blocksize;
     a.pcm_mode = pcm_mode; a.verify_crc = c->verify_crc;
     CK(frx_launch_frame_pos(a, st));
@@ -421,6 +429,7 @@ static int decode_core(frx_ctx *c, const uint8_t *bytes_dev, uint64_t n_bytes, c
     }
     CK(cudaEventRecord(c->ev[2], st));
     CK(frx_launch_decode(a, out_dtype, st));
+    if (c->verify_crc) { CK(frx_launch_crc_check(a, (const uint16_t *)c->xpow.p, c->sm_count, st)); c->launches += 1; }
     CK(cudaEventRecord(c->ev[3], st));
     c->dec_timed = true;
     c->launches += 1;

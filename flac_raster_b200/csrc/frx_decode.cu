@@ -4,12 +4,13 @@
 //   K9a frx_frame_pos_kernel     frame byte positions from a frame-size table (our own files)
 //   K9b frx_frame_discover_kernel sync-code scan + header/CRC-8 validation (reference-produced files carry
 //                                no seek table and STREAMINFO frame sizes are 0)
-//   K10-K12 frx_decode_kernel    one thread per frame: header parse, Rice/Rice2/escape unpack, FIXED/LPC
-//                                restore, wasted-bit shift, CRC-16 check, PCM -> raster dtype
-//                                (pyflac.FileDecoder.process + converter.py:88-110, 265-273)
+//   K10-K12 frx_decode_kernel    one lane per frame, 32 frames of a warp in lockstep: header parse, Rice/Rice2/escape
+//                                unpack, FIXED/LPC restore, wasted-bit shift, PCM -> raster dtype, stores transposed
+//                                through shared memory into full lines (pyflac.FileDecoder.process +
+//                                converter.py:88-110, 265-273)
+//   K10c frx_crc_check_kernel    CRC-16 of every frame, one warp per frame, coalesced
 // Rice decoding and the LPC recurrence are serial inside a subframe; the parallelism is across frames
-// (config 5: 10^4 queries x 256 frames), so one thread owns one frame and lanes never diverge on data
-// except at escape partitions.
+// (config 5: 10^4 queries x 256 frames).
 #include "frx_internal.cuh"
 
 
@@ -115,99 +116,113 @@ __global__ void frx_frame_discover_kernel(DecArgs a, const uint32_t *unit_prefix
 }
 
 // ------------------------------------------------------------------------------------------
-// bit reader: 64-bit window refilled with aligned, bounds-clamped 32-bit words
+// bit reader.  A lane walks its own frame, but a warp runs its 32 lanes in lockstep: if every lane fetched from global
+// memory whenever its own window ran dry, the warp would stall on 32 unrelated misses per few samples.  So each lane
+// owns a ring of DEC_RING words in shared memory (column `lane` of ring[word][lane], conflict-free), topped up for all
+// lanes at once at every chunk boundary with aligned 16-byte loads; the 64-bit window is fed from the ring.
 // ------------------------------------------------------------------------------------------
+#define DEC_RING 32
+__device__ __noinline__ uint4 dec_load16_clamped(const uint8_t *np, const uint8_t *lo, const uint8_t *hi) {
+    uint32_t w[4];
+    for (int k = 0; k < 4; k++) {
+        w[k] = 0;
+        for (int i = 0; i < 4; i++) {
+            const uint8_t *p = np + 4 * k + i;
+            const uint32_t b = (p >= lo && p < hi) ? (uint32_t)__ldg(p) : 0u;
+            w[k] |= b << (8 * i);
+        }
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
 struct BitR {
     const uint8_t *lo, *hi;     // valid byte range of the buffer
-    const uint8_t *wp;          // next 4-byte aligned word to load
-    uint64_t acc;  // left aligned
-    int cnt;       // valid bits in acc
-    uint64_t consumed;  // bits consumed since init
-    __device__ __forceinline__ uint32_t load_word() {
-        uint32_t w;
-        if (wp >= lo && wp + 4 <= hi) w = frx_bswap32(__ldg((const uint32_t *)wp));
-        else {
-            w = 0;
+    const uint8_t *np;          // next 16-byte aligned block to fetch
+    uint32_t *ring;             // &ring[0][lane]; word i of the stream sits at ring[(i % DEC_RING) * 32]
+    uint32_t rd, wr;            // words consumed / fetched
+    uint64_t acc;               // left aligned
+    int cnt;                    // valid bits in acc
+    uint32_t consumed;          // bits consumed since init
+    __device__ __forceinline__ uint4 load16() const {
+        if (np >= lo && np + 16 <= hi) return __ldg(reinterpret_cast<const uint4 *>(np));
+        return dec_load16_clamped(np, lo, hi);
+    }
+    __device__ __forceinline__ void push16(const uint4 v) {
+        ring[((wr + 0u) % DEC_RING) * 32] = frx_bswap32(v.x);
+        ring[((wr + 1u) % DEC_RING) * 32] = frx_bswap32(v.y);
+        ring[((wr + 2u) % DEC_RING) * 32] = frx_bswap32(v.z);
+        ring[((wr + 3u) % DEC_RING) * 32] = frx_bswap32(v.w);
+        wr += 4; np += 16;
+    }
+    // chunk boundary: every lane fills its ring (uniform trip count so the loads of a round issue together)
+    __device__ __forceinline__ void topup(bool want) {
+        for (;;) {
+            const uint32_t free_blocks = want ? (DEC_RING - (wr - rd)) >> 2 : 0u;
+            if (!__any_sync(0xFFFFFFFFu, free_blocks != 0u)) break;
+            uint4 v[4];
 #pragma unroll
-            for (int i = 0; i < 4; i++) {
-                const uint8_t *q = wp + i;
-                uint32_t b = (q >= lo && q < hi) ? (uint32_t)__ldg(q) : 0u;
-                w |= b << (24 - 8 * i);
-            }
+            for (int k = 0; k < 4; k++) if ((uint32_t)k < free_blocks) { const uint8_t *p = np; np += 16 * k; v[k] = load16(); np = p; }
+#pragma unroll
+            for (int k = 0; k < 4; k++) if ((uint32_t)k < free_blocks) push16(v[k]);
+            if (!__any_sync(0xFFFFFFFFu, free_blocks > 4u)) break;
         }
-        wp += 4;
+    }
+    __device__ __forceinline__ uint32_t pop() {
+        if (rd == wr) push16(load16());      // ring ran dry inside a chunk (more than ~4 bytes per sample): fetch on demand
+        const uint32_t w = ring[(rd % DEC_RING) * 32];
+        rd++;
         return w;
     }
-    __device__ __forceinline__ void init(const uint8_t *base, uint64_t n_bytes, uint64_t pos) {
+    __device__ __forceinline__ void init(const uint8_t *base, uint64_t n_bytes, uint64_t pos, uint32_t *ring_col, bool live) {
         lo = base; hi = base + n_bytes;
-        uintptr_t addr = (uintptr_t)(base + pos);
-        int lead = (int)(addr & 3u);
-        wp = (const uint8_t *)(addr - lead);
-        consumed = 0;
-        uint32_t w = load_word();
-        acc = (uint64_t)w << (32 + 8 * lead);
-        cnt = 32 - 8 * lead;
-        refill();
+        const uintptr_t addr = (uintptr_t)(base + pos);
+        const int lead = (int)(addr & 15u);
+        np = (const uint8_t *)(addr - lead);
+        ring = ring_col; rd = 0; wr = 0; consumed = 0; acc = 0; cnt = 0;
+        topup(live);
+        if (live) {
+            rd = (uint32_t)(lead >> 2);
+            const int lb = 8 * (lead & 3);
+            acc = (uint64_t)pop() << (32 + lb);
+            cnt = 32 - lb;
+            refill();
+        }
     }
     __device__ __forceinline__ void refill() {
         if (cnt <= 32) {
-            uint32_t w = load_word();
-            acc |= (uint64_t)w << (32 - cnt);
+            acc |= (uint64_t)pop() << (32 - cnt);
             cnt += 32;
         }
     }
     // n in 0..32
     __device__ __forceinline__ uint32_t get(int n) {
         refill();
-        uint32_t v = n ? (uint32_t)(acc >> (64 - n)) : 0u;
-        acc = n >= 64 ? 0 : (acc << n);
-        cnt -= n; consumed += (uint64_t)n;
+        const uint32_t v = n ? (uint32_t)(acc >> (64 - n)) : 0u;
+        acc <<= n;
+        cnt -= n; consumed += (uint32_t)n;
         return v;
     }
     __device__ __forceinline__ int32_t sget(int n) {  // signed, n in 1..32
-        uint32_t v = get(n);
+        const uint32_t v = get(n);
         return n >= 32 ? (int32_t)v : ((int32_t)(v << (32 - n)) >> (32 - n));
     }
     __device__ __forceinline__ uint32_t unary() {
-        uint32_t q = 0;
+        uint32_t z = 0;
         for (;;) {
             refill();
             if (acc == 0) {
-                q += (uint32_t)cnt; consumed += (uint64_t)cnt; cnt = 0;
-                if (wp > hi + 8) return q;  // ran off the buffer: malformed
+                z += (uint32_t)cnt; consumed += (uint32_t)cnt; cnt = 0;
+                if (np > hi + 256) return z;  // ran off the buffer: malformed
                 continue;
             }
-            int lz = __clzll((long long)acc);
-            q += (uint32_t)lz;
+            const int lz = __clzll((long long)acc);
+            z += (uint32_t)lz;
             acc = lz == 63 ? 0ull : (acc << (lz + 1));  // a set bit exists within cnt bits, so lz < cnt
-            cnt -= lz + 1; consumed += (uint64_t)lz + 1u;
-            return q;
+            cnt -= lz + 1; consumed += (uint32_t)lz + 1u;
+            return z;
         }
     }
 };
 
-// ------------------------------------------------------------------------------------------
-// raster output cursor: walks the tile row-major, one element per put()
-// ------------------------------------------------------------------------------------------
-template <int DT>
-struct OutW {
-    typedef typename FrxElem<DT>::T T;
-    T *base;           // element pointer to (band c,row 0,col 0) of the tile
-    long long row_stride;
-    int w, row, col;
-    __device__ __forceinline__ void init(T *b, long long rs, int width, long long px) {
-        base = b; row_stride = rs; w = width;
-        row = (int)(px / width); col = (int)(px - (long long)row * width);
-    }
-    __device__ __forceinline__ void put(T v) {
-        base[(long long)row * row_stride + col] = v;
-        if (++col == w) { col = 0; row++; }
-    }
-};
-
-// ------------------------------------------------------------------------------------------
-// residual + predictor restore for one subframe, ORD-tap ring held in registers
-// ------------------------------------------------------------------------------------------
 struct RiceState {
     uint32_t k;        // current parameter
     uint32_t left;     // samples left in the current partition
@@ -226,204 +241,369 @@ __device__ __forceinline__ int32_t rice_next(BitR &br, RiceState &rs) {
     }
     rs.left--;
     if (rs.rawbits >= 0) return rs.rawbits ? br.sget(rs.rawbits) : 0;
-    uint32_t q = br.unary();
-    uint32_t u = (q << rs.k) | br.get((int)rs.k);
+    const uint32_t z = br.unary();
+    const uint32_t u = (z << rs.k) | br.get((int)rs.k);
     return (int32_t)(u >> 1) ^ -(int32_t)(u & 1u);
-}
-
-template <int DT, int ORD, bool WIDE>
-__device__ __forceinline__ void restore_subframe(BitR &br, RiceState &rs, OutW<DT> &ow, const int32_t *coef, int order, int shift,
-                                                 const int32_t *warm, int nsamp, int wasted, int bps, const FrxDequant &dq, int mode) {
-    int32_t h[ORD];
-#pragma unroll
-    for (int i = 0; i < ORD; i++) h[i] = i < order ? warm[i] : 0;
-    for (int i = 0; i < order; i++) ow.put(frx_dequant<DT>((int32_t)((uint32_t)warm[i] << wasted), bps, dq, mode));
-    for (int n0 = 0; n0 < nsamp; n0 += ORD) {
-#pragma unroll
-        for (int m = 0; m < ORD; m++) {
-            int n = n0 + m;
-            if (n >= order && n < nsamp) {
-                int32_t r = rice_next(br, rs);
-                int32_t v;
-                if (WIDE) {
-                    long long acc = 0;
-#pragma unroll
-                    for (int j = 0; j < ORD; j++) acc += (long long)coef[j] * (long long)h[(m - 1 - j + 2 * ORD) % ORD];
-                    v = (int32_t)((long long)r + (acc >> shift));
-                } else {
-                    int32_t acc = 0;
-#pragma unroll
-                    for (int j = 0; j < ORD; j++) acc += coef[j] * h[(m - 1 - j + 2 * ORD) % ORD];
-                    v = r + (acc >> shift);
-                }
-                h[m] = v;
-                ow.put(frx_dequant<DT>((int32_t)((uint32_t)v << wasted), bps, dq, mode));
-            }
-        }
-    }
-}
-
-// generic order (13..32): history ring in local memory
-template <int DT>
-__device__ void restore_subframe_generic(BitR &br, RiceState &rs, OutW<DT> &ow, const int32_t *coef, int order, int shift,
-                                         const int32_t *warm, int nsamp, int wasted, int bps, const FrxDequant &dq, int mode) {
-    int32_t h[32];
-    for (int i = 0; i < 32; i++) h[i] = i < order ? warm[i] : 0;
-    for (int i = 0; i < order; i++) ow.put(frx_dequant<DT>((int32_t)((uint32_t)warm[i] << wasted), bps, dq, mode));
-    for (int n = order; n < nsamp; n++) {
-        int32_t r = rice_next(br, rs);
-        long long acc = 0;
-        for (int j = 0; j < order; j++) acc += (long long)coef[j] * (long long)h[(n - 1 - j) & 31];
-        int32_t v = (int32_t)((long long)r + (acc >> shift));
-        h[n & 31] = v;
-        ow.put(frx_dequant<DT>((int32_t)((uint32_t)v << wasted), bps, dq, mode));
-    }
 }
 
 __device__ __forceinline__ int ilog2_u32(uint32_t v) { return 31 - __clz((int)v); }
 
+// ------------------------------------------------------------------------------------------
+// K10-K12.  One lane owns one frame (Rice decoding and the predictor recurrence are serial inside a subframe; the
+// parallelism is across frames), but a warp walks its 32 frames in lockstep, 32 samples at a time: the restored samples
+// go through a shared-memory transpose so that every global store is one full line of one frame's raster row, instead of
+// 32 lanes scattering single elements 16 KB apart.
+// ------------------------------------------------------------------------------------------
+#define DEC_WARPS 4
+#define DEC_MAXORD 16
+struct DecWarpSmem {
+    uint32_t ring[DEC_RING][32];     // input rings, one column per lane
+    uint32_t stage[32][33];          // [frame lane][sample in chunk], padded
+    unsigned long long ptr[32];      // byte address of the first sample of the lane's chunk
+    long long rstride[32];           // row stride of the lane's tile, elements
+    uint32_t room[32];               // elements left in the raster row at the chunk start
+    uint32_t cnt[32];                // valid samples of the lane in this chunk
+    uint32_t wid[32];                // tile width
+};
+
+struct SubF {
+    int type;          // 0 constant, 1 verbatim, 2 predictive, 3 nothing to do
+    int order, shift, wasted, sbps;
+    int32_t cval;
+    RiceState rs;
+};
+
+// generic order (17..32): history ring in local memory, scattered stores (libFLAC never emits these below -l 17)
 template <int DT>
-__global__ void __launch_bounds__(128) frx_decode_kernel(const DecArgs a) {
+__device__ __noinline__ void restore_subframe_generic(BitR &br, RiceState &rs, typename FrxElem<DT>::T *base, long long row_stride, int w,
+                                                      long long px, const int32_t *coef, int order, int shift, const int32_t *warm, int nsamp,
+                                                      int wasted, int bps, const FrxDequant &dq, int mode) {
     typedef typename FrxElem<DT>::T T;
+    int row = (int)(px / w), col = (int)(px - (long long)row * w);
+    int32_t h[32];
+    for (int i = 0; i < 32; i++) h[i] = i < order ? warm[i] : 0;
+    for (int n = 0; n < nsamp; n++) {
+        int32_t v;
+        if (n < order) v = warm[n];
+        else {
+            const int32_t r = rice_next(br, rs);
+            long long acc = 0;
+            for (int j = 0; j < order; j++) acc += (long long)coef[j] * (long long)h[(n - 1 - j) & 31];
+            v = (int32_t)((long long)r + (acc >> shift));
+            h[n & 31] = v;
+        }
+        base[(long long)row * row_stride + col] = frx_dequant<DT>((int32_t)((uint32_t)v << wasted), bps, dq, mode);
+        if (++col == w) { col = 0; row++; }
+    }
+}
+
+template <int DT>
+__device__ __forceinline__ uint32_t dec_pack(typename FrxElem<DT>::T v) {
+    typedef typename FrxElem<DT>::T T;
+    if (sizeof(T) == 4) { uint32_t u; memcpy(&u, &v, 4); return u; }
+    if (sizeof(T) == 2) { uint16_t u; memcpy(&u, &v, 2); return u; }
+    uint8_t u; memcpy(&u, &v, 1); return u;
+}
+template <int DT>
+__device__ __forceinline__ void dec_store(unsigned long long addr, uint32_t bits) {
+    typedef typename FrxElem<DT>::T T;
+    if (sizeof(T) == 4) *reinterpret_cast<uint32_t *>(addr) = bits;
+    else if (sizeof(T) == 2) *reinterpret_cast<uint16_t *>(addr) = (uint16_t)bits;
+    else *reinterpret_cast<uint8_t *>(addr) = (uint8_t)bits;
+}
+
+// the warp writes the 32x32 staged samples: iteration j stores frame j's chunk, lane = sample
+template <int DT>
+__device__ __forceinline__ void flush_chunk(DecWarpSmem &ws, int lane) {
+    typedef typename FrxElem<DT>::T T;
+    __syncwarp();
+#pragma unroll 4
+    for (int j = 0; j < 32; j++) {
+        const uint32_t cnt = ws.cnt[j];
+        if ((uint32_t)lane < cnt) {
+            const uint32_t room = ws.room[j];
+            unsigned long long addr = ws.ptr[j];
+            if ((uint32_t)lane < room) addr += (unsigned long long)lane * sizeof(T);
+            else {
+                // the chunk runs over the end of the raster row (tile widths that are not multiples of 32)
+                const uint32_t w = ws.wid[j];
+                const uint32_t k = (uint32_t)lane - room;
+                const uint32_t down = 1u + k / w, colx = k - (k / w) * w;
+                addr = addr - (unsigned long long)(w - room) * sizeof(T) + ((unsigned long long)((long long)down * ws.rstride[j]) + colx) * sizeof(T);
+            }
+            dec_store<DT>(addr, ws.stage[j][lane]);
+        }
+    }
+    __syncwarp();
+}
+
+// lockstep restore of one channel for the 32 frames of a warp; ORD = history length (multiple of 4 dividing 32),
+// WIDE = 64-bit accumulate.  Uniform control flow: lanes whose subframe is not predictive ride along predicated.
+template <int DT, int ORD, bool WIDE>
+__device__ __forceinline__ void run_chunks(BitR &br, SubF &sf, int32_t *coef, int32_t *h, DecWarpSmem &ws, int lane, int my_n, int nmax,
+                                           unsigned long long base_addr, long long row_stride, int w, int row, int col, int bps,
+                                           const FrxDequant &dq, int mode) {
+    typedef typename FrxElem<DT>::T T;
+    for (int n0 = 0; n0 < nmax; n0 += 32) {
+        br.topup(n0 < my_n);
+        // where this lane's chunk lands
+        ws.ptr[lane] = base_addr + (unsigned long long)((long long)row * row_stride + col) * sizeof(T);
+        ws.rstride[lane] = row_stride;
+        ws.room[lane] = (uint32_t)(w - col);
+        ws.wid[lane] = (uint32_t)w;
+        ws.cnt[lane] = (uint32_t)min(32, max(0, my_n - n0));
+        for (int mb = 0; mb < 32; mb += ORD) {
+#pragma unroll
+            for (int mi = 0; mi < ORD; mi++) {
+                const int n = n0 + mb + mi;
+                int32_t v = sf.cval;
+                if (n < my_n) {
+                    if (sf.type == 2) {
+                        if (n >= sf.order) {
+                            const int32_t r = rice_next(br, sf.rs);
+                            if (WIDE) {
+                                long long acc = 0;
+#pragma unroll
+                                for (int j = 0; j < ORD; j++) acc += (long long)coef[j] * (long long)h[(mi - 1 - j + 2 * ORD) % ORD];
+                                v = (int32_t)((long long)r + (acc >> sf.shift));
+                            } else {
+                                int32_t acc = 0;
+#pragma unroll
+                                for (int j = 0; j < ORD; j++) acc += coef[j] * h[(mi - 1 - j + 2 * ORD) % ORD];
+                                v = r + (acc >> sf.shift);
+                            }
+                            h[mi] = v;
+                        } else v = h[mi];   // warm-up sample (n < order <= ORD, so n == mi)
+                    } else if (sf.type == 1) v = br.sget(sf.sbps);
+                }
+                ws.stage[lane][mb + mi] = dec_pack<DT>(frx_dequant<DT>((int32_t)((uint32_t)v << sf.wasted), bps, dq, mode));
+            }
+        }
+        flush_chunk<DT>(ws, lane);
+        col += 32;
+        while (col >= w) { col -= w; row++; }
+    }
+}
+
+template <int DT>
+__global__ void __launch_bounds__(32 * DEC_WARPS, 4) frx_decode_kernel(const DecArgs a) {
+    typedef typename FrxElem<DT>::T T;
+    __shared__ DecWarpSmem wsm[DEC_WARPS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    DecWarpSmem &ws = wsm[warp];
+    const uint32_t f = (blockIdx.x * DEC_WARPS + warp) * 32u + (uint32_t)lane;
+    bool bad = false, live = f < a.total_frames;
+    int status = FRX_E_BITSTREAM;
+    int ti = 0;
+    frx_dtile t;
+    memset(&t, 0, sizeof(t));
+    uint32_t fj = 0;
+    uint64_t pos = 0, end = 0;
+    long long s0 = 0;
+    int nsamp = 0, channels = 0, bps = 0;
+    FrxDequant dq;
+    dq.range_f = 0.f; dq.dmin_f = 0.f;
+    BitR br;
+    if (live) {
+        ti = dec_find_tile(a.dprefix, a.n_tiles, f);
+        t = a.tiles[ti];
+        fj = f - a.dprefix[ti];
+        pos = a.frame_pos[f];
+        if (pos == FRX_NOPOS || pos < t.byte_offset || pos >= t.byte_offset + t.byte_size) bad = true;
+        end = t.byte_offset + t.byte_size;
+        if (!bad && fj + 1 < t.n_frames) {
+            const uint64_t nx = a.frame_pos[f + 1];
+            if (nx != FRX_NOPOS && nx > pos && nx <= end) end = nx;
+        }
+        dq.range_f = (float)(t.dmax - t.dmin);
+        dq.dmin_f = (float)t.dmin;
+    }
+    br.init(a.bytes, a.n_bytes, pos, &ws.ring[0][lane], live && !bad);   // warp-wide: fills the input rings
+    if (live && !bad) {
+        const long long tile_n = (long long)t.h * t.w;
+        s0 = (long long)fj * a.blocksize;
+        const int expect = (int)min((long long)a.blocksize, tile_n - s0);
+        // ---- K10: frame header ----
+        const uint32_t sync = br.get(16);
+        if (sync != 0xFFF8u) bad = true;
+        const uint32_t bs_code = br.get(4), sr_code = br.get(4), ch_code = br.get(4), sz_code = br.get(3);
+        br.get(1);
+        {
+            const uint32_t x = br.get(8);
+            const int extra = !(x & 0x80u) ? 0 : (x & 0xE0u) == 0xC0u ? 1 : (x & 0xF0u) == 0xE0u ? 2 : (x & 0xF8u) == 0xF0u ? 3 : (x & 0xFCu) == 0xF8u ? 4 : 5;
+            for (int e = 0; e < extra; e++) br.get(8);
+        }
+        if (bs_code == 1) nsamp = 192;
+        else if (bs_code >= 2 && bs_code <= 5) nsamp = 576 << (bs_code - 2);
+        else if (bs_code == 6) nsamp = (int)br.get(8) + 1;
+        else if (bs_code == 7) nsamp = (int)br.get(16) + 1;
+        else if (bs_code >= 8) nsamp = 256 << (bs_code - 8);
+        else { nsamp = 0; bad = true; }
+        if (sr_code == 12u) br.get(8); else if (sr_code == 13u || sr_code == 14u) br.get(16);
+        br.get(8);  // CRC-8 (validated by discovery for foreign files; the CRC-16 pass covers the header too)
+        bps = sz_code ? frx_size_code_bps(sz_code) : t.bps;
+        channels = ch_code < 8u ? (int)ch_code + 1 : 2;
+        if (nsamp != expect || bps != t.bps || channels != t.channels || ch_code >= 8u) bad = true;
+        if (ch_code >= 8u && ch_code <= 10u) status = FRX_E_UNSUPPORTED;   // stereo decorrelation: see frx_api (unsupported)
+    }
+    int my_n = (live && !bad) ? nsamp : 0;
+    const int my_ch = (live && !bad) ? channels : 0;
+    const int nmax = __reduce_max_sync(0xFFFFFFFFu, my_n), chmax = __reduce_max_sync(0xFFFFFFFFu, my_ch);
+    const int w = my_n ? t.w : (1 << 30);
+    const int row0 = my_n ? (int)(s0 / t.w) : 0, col0 = my_n ? (int)(s0 - (long long)row0 * t.w) : 0;
+
+    for (int c = 0; c < chmax; c++) {
+        SubF sf;
+        sf.type = 3; sf.order = 0; sf.shift = 0; sf.wasted = 0; sf.sbps = bps; sf.cval = 0;
+        sf.rs.k = 0; sf.rs.left = 0; sf.rs.pbits = 4; sf.rs.esc = 15u; sf.rs.rawbits = -1; sf.rs.psize = 1;
+        int32_t coef[DEC_MAXORD], h[DEC_MAXORD];
+#pragma unroll
+        for (int j = 0; j < DEC_MAXORD; j++) { coef[j] = 0; h[j] = 0; }
+        bool wide = false;
+        const unsigned long long base_addr = (unsigned long long)((T *)a.out + t.out_offset + (long long)c * t.out_band_stride);
+        if (c < my_ch && !bad) {
+            // ---- K11 front: subframe header, warm-up samples, predictor ----
+            const uint32_t hdr = br.get(8);
+            const uint32_t type = (hdr >> 1) & 0x3Fu;
+            if (hdr & 0x80u) bad = true;
+            if (hdr & 1u) sf.wasted = (int)br.unary() + 1;
+            sf.sbps = bps - sf.wasted;
+            if (sf.sbps <= 0) bad = true;
+            if (bad) {}
+            else if (type == 0) { sf.type = 0; sf.cval = br.sget(sf.sbps); }
+            else if (type == 1) sf.type = 1;
+            else {
+                bool lpc = false;
+                int order = 0, prec = 3;
+                if (type >= 8 && type <= 12) order = (int)type - 8;
+                else if (type >= 32) { order = (int)(type & 31u) + 1; lpc = true; }
+                else bad = true;
+                if (order > nsamp) bad = true;
+                if (!bad && order > DEC_MAXORD) {
+                    // rare long predictors: this lane restores its whole subframe on its own, then idles through the lockstep part
+                    int32_t coefl[32], warml[32];
+                    for (int i = 0; i < order; i++) warml[i] = br.sget(sf.sbps);
+                    prec = (int)br.get(4) + 1;
+                    const int shift = br.sget(5);
+                    if (prec == 16 || shift < 0) bad = true;
+                    for (int j = 0; j < order; j++) coefl[j] = br.sget(prec);
+                    const uint32_t method = br.get(2), po = br.get(4);
+                    if (method > 1u || (po > 0 && ((uint32_t)nsamp >> po) << po != (uint32_t)nsamp) || ((uint32_t)nsamp >> po) < (uint32_t)order) bad = true;
+                    if (!bad) {
+                        RiceState rs;
+                        rs.pbits = method ? 5 : 4; rs.esc = method ? 31u : 15u; rs.psize = (uint32_t)nsamp >> po; rs.rawbits = -1;
+                        rs.k = br.get(rs.pbits);
+                        rs.left = rs.psize - (uint32_t)order;
+                        if (rs.k == rs.esc) rs.rawbits = (int)br.get(5);
+                        BitR brl = br;     // only the copy's address escapes into the out-of-line routine: br itself stays in registers
+                        restore_subframe_generic<DT>(brl, rs, (T *)base_addr, t.out_row_stride, t.w, s0, coefl, order, shift, warml, nsamp, sf.wasted,
+                                                     bps, dq, a.pcm_mode);
+                        br = brl;
+                    }
+                } else if (!bad) {
+#pragma unroll
+                    for (int i = 0; i < DEC_MAXORD; i++) if (i < order) h[i] = br.sget(sf.sbps);
+                    if (lpc) {
+                        prec = (int)br.get(4) + 1;
+                        sf.shift = br.sget(5);
+                        if (prec == 16 || sf.shift < 0) bad = true;
+#pragma unroll
+                        for (int j = 0; j < DEC_MAXORD; j++) if (j < order) coef[j] = br.sget(prec);
+                    } else {
+                        if (order == 1) { coef[0] = 1; }
+                        else if (order == 2) { coef[0] = 2; coef[1] = -1; }
+                        else if (order == 3) { coef[0] = 3; coef[1] = -3; coef[2] = 1; }
+                        else if (order == 4) { coef[0] = 4; coef[1] = -6; coef[2] = 4; coef[3] = -1; }
+                    }
+                    const uint32_t method = br.get(2), po = br.get(4);
+                    if (method > 1u || (po > 0 && ((uint32_t)nsamp >> po) << po != (uint32_t)nsamp) || ((uint32_t)nsamp >> po) < (uint32_t)order) bad = true;
+                    if (!bad) {
+                        sf.type = 2; sf.order = order;
+                        sf.rs.pbits = method ? 5 : 4; sf.rs.esc = method ? 31u : 15u; sf.rs.psize = (uint32_t)nsamp >> po;
+                        // the first partition is short by `order`: prime it here
+                        sf.rs.k = br.get(sf.rs.pbits);
+                        sf.rs.left = sf.rs.psize - (uint32_t)order;
+                        sf.rs.rawbits = -1;
+                        if (sf.rs.k == sf.rs.esc) sf.rs.rawbits = (int)br.get(5);
+                        wide = order > 0 && (sf.sbps + prec + ilog2_u32((uint32_t)order) > 32);
+                    }
+                }
+            }
+        }
+        const int lane_n = (sf.type != 3 && !bad) ? my_n : 0;
+        const int omax = __reduce_max_sync(0xFFFFFFFFu, (uint32_t)(sf.type == 2 && lane_n ? sf.order : 0));
+        const bool anywide = __any_sync(0xFFFFFFFFu, wide && lane_n);
+        // ---- K11 back + K12: lockstep restore, dequantise, coalesced stores ----
+        if (omax <= 4) {
+            if (anywide) run_chunks<DT, 4, true>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
+            else run_chunks<DT, 4, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
+        } else if (omax <= 8) {
+            if (anywide) run_chunks<DT, 8, true>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
+            else run_chunks<DT, 8, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
+        } else {
+            if (anywide) run_chunks<DT, 16, true>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
+            else run_chunks<DT, 16, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
+        }
+        if (bad) my_n = 0;
+    }
+    if (!live) return;
+    // ---- footer: byte align; the frame must end where the next one starts (CRC-16: frx_crc_check_kernel) ----
+    const uint64_t fsize = (uint64_t)((br.consumed + 7u) >> 3) + 2u;
+    if (!bad && pos + fsize > end) bad = true;
+    if (!bad && fj + 1 < t.n_frames && a.frame_pos[f + 1] != FRX_NOPOS && pos + fsize != a.frame_pos[f + 1]) bad = true;
+    if (a.frame_len) a.frame_len[f] = bad ? 0u : (uint32_t)fsize;
+    if (bad) atomicExch(&a.tile_status[ti], status);
+}
+
+// ---- CRC-16 of every decoded frame: one warp per frame, coalesced reads.  Lane l takes a contiguous run of Lq 16-byte
+// quads (the run of lane 0 may be short: virtual leading zeros do not change a CRC); the 32 chunk CRCs are moved to
+// their place with x^(128 Lq j) mod P -- the encoder's table -- and xor-ed.  A frame including its stored CRC gives 0.
+__global__ void __launch_bounds__(128) frx_crc_check_kernel(const DecArgs a, const uint16_t *xpow) {
     __shared__ uint16_t crc_tab[4][256];
     for (int i = threadIdx.x; i < 1024; i += blockDim.x) (&crc_tab[0][0])[i] = a.crc_tab[i];
     __syncthreads();
-    uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f >= a.total_frames) return;
-    const int ti = dec_find_tile(a.dprefix, a.n_tiles, f);
-    const frx_dtile t = a.tiles[ti];
-    const uint32_t fj = f - a.dprefix[ti];
-    const uint64_t pos = a.frame_pos[f];
-    if (pos == FRX_NOPOS || pos < t.byte_offset || pos >= t.byte_offset + t.byte_size) { atomicExch(&a.tile_status[ti], FRX_E_BITSTREAM); return; }
-    uint64_t end = t.byte_offset + t.byte_size;
-    if (fj + 1 < t.n_frames) {
-        uint64_t nx = a.frame_pos[f + 1];
-        if (nx != FRX_NOPOS && nx > pos && nx <= end) end = nx;
-    }
-    const long long tile_n = (long long)t.h * t.w;
-    const long long s0 = (long long)fj * a.blocksize;
-    const int expect = (int)min((long long)a.blocksize, tile_n - s0);
-    FrxDequant dq;
-    dq.range_f = (float)(t.dmax - t.dmin);
-    dq.dmin_f = (float)t.dmin;
-
-    BitR br;
-    br.init(a.bytes, a.n_bytes, pos);
-    bool bad = false;
-    // ---- header ----
-    uint32_t sync = br.get(16);
-    if (sync != 0xFFF8u) bad = true;
-    uint32_t bs_code = br.get(4), sr_code = br.get(4), ch_code = br.get(4), sz_code = br.get(3);
-    br.get(1);
-    {
-        uint32_t x = br.get(8);
-        int extra = !(x & 0x80u) ? 0 : (x & 0xE0u) == 0xC0u ? 1 : (x & 0xF0u) == 0xE0u ? 2 : (x & 0xF8u) == 0xF0u ? 3 : (x & 0xFCu) == 0xF8u ? 4 : 5;
-        for (int e = 0; e < extra; e++) br.get(8);
-    }
-    int nsamp;
-    if (bs_code == 1) nsamp = 192;
-    else if (bs_code >= 2 && bs_code <= 5) nsamp = 576 << (bs_code - 2);
-    else if (bs_code == 6) nsamp = (int)br.get(8) + 1;
-    else if (bs_code == 7) nsamp = (int)br.get(16) + 1;
-    else if (bs_code >= 8) nsamp = 256 << (bs_code - 8);
-    else { nsamp = 0; bad = true; }
-    if (sr_code == 12u) br.get(8); else if (sr_code == 13u || sr_code == 14u) br.get(16);
-    br.get(8);  // CRC-8 (validated by discovery for foreign files; CRC-16 below covers the header too)
-    int bps = sz_code ? frx_size_code_bps(sz_code) : t.bps;
-    int channels = ch_code < 8u ? (int)ch_code + 1 : 2;
-    if (nsamp != expect || bps != t.bps || channels != t.channels || ch_code >= 8u) bad = true;  // stereo decorrelation: see frx_api (unsupported)
-    if (bad) { atomicExch(&a.tile_status[ti], ch_code >= 8u && ch_code <= 10u ? FRX_E_UNSUPPORTED : FRX_E_BITSTREAM); return; }
-
-    T *obase = (T *)a.out + t.out_offset;
-    for (int c = 0; c < channels && !bad; c++) {
-        OutW<DT> ow;
-        ow.init(obase + (long long)c * t.out_band_stride, t.out_row_stride, t.w, s0);
-        uint32_t hdr = br.get(8);
-        if (hdr & 0x80u) { bad = true; break; }
-        uint32_t type = (hdr >> 1) & 0x3Fu;
-        int wasted = 0;
-        if (hdr & 1u) wasted = (int)br.unary() + 1;
-        int sbps = bps - wasted;
-        if (sbps <= 0) { bad = true; break; }
-        if (type == 0) {
-            int32_t v = br.sget(sbps);
-            T o = frx_dequant<DT>((int32_t)((uint32_t)v << wasted), bps, dq, a.pcm_mode);
-            for (int i = 0; i < nsamp; i++) ow.put(o);
-        } else if (type == 1) {
-            for (int i = 0; i < nsamp; i++) {
-                int32_t v = br.sget(sbps);
-                ow.put(frx_dequant<DT>((int32_t)((uint32_t)v << wasted), bps, dq, a.pcm_mode));
+    const int lane = threadIdx.x & 31;
+    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t f = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; f < a.total_frames; f += nwarps) {
+        const uint32_t fsize = a.frame_len[f];
+        if (fsize == 0) continue;                       // the decoder already flagged it
+        const uint8_t *p = a.bytes + a.frame_pos[f];
+        uint32_t crc = 0;                               // running CRC over the passes (frames above 32 * 48 quads)
+        uint32_t done = 0;
+        while (done < fsize) {
+            const uint32_t pass = min(fsize - done, 32u * 16u * (uint32_t)FRX_CRC_MAXLQ);
+            const uint32_t Lq = (pass + 511u) / 512u, C = Lq * 16u;
+            // lane l covers pass bytes [pass - (32 - l) C, pass - (31 - l) C), clipped at 0
+            const long long b1 = (long long)pass - (long long)(31 - lane) * C;
+            long long b0 = b1 - C;
+            if (b0 < 0) b0 = 0;
+            uint32_t c = 0;
+            if (b1 > 0) {
+                const uint8_t *q = p + done + b0;
+                long long n = b1 - b0;
+                while (n > 0 && ((uintptr_t)q & 3u)) { c = ((c << 8) ^ crc_tab[0][((c >> 8) ^ *q) & 0xFFu]) & 0xFFFFu; q++; n--; }
+                for (; n >= 4; n -= 4, q += 4) {
+                    const uint32_t x = frx_bswap32(__ldg(reinterpret_cast<const uint32_t *>(q))) ^ (c << 16);
+                    c = (uint32_t)crc_tab[3][x >> 24] ^ crc_tab[2][(x >> 16) & 0xFFu] ^ crc_tab[1][(x >> 8) & 0xFFu] ^ crc_tab[0][x & 0xFFu];
+                }
+                for (; n > 0; n--, q++) c = ((c << 8) ^ crc_tab[0][((c >> 8) ^ *q) & 0xFFu]) & 0xFFFFu;
             }
-        } else {
-            int order, shift = 0, prec = 0;
-            int32_t coef[32];
-            int32_t warm[32];
-            bool lpc = false;
-            if (type >= 8 && type <= 12) order = (int)type - 8;
-            else if (type >= 32) { order = (int)(type & 31u) + 1; lpc = true; }
-            else { bad = true; break; }
-            if (order > nsamp) { bad = true; break; }
-            for (int i = 0; i < order; i++) warm[i] = br.sget(sbps);
-            for (int j = 0; j < 32; j++) coef[j] = 0;
-            if (lpc) {
-                prec = (int)br.get(4) + 1;
-                shift = br.sget(5);
-                if (prec == 16 || shift < 0) { bad = true; break; }
-                for (int j = 0; j < order; j++) coef[j] = br.sget(prec);
-            } else {
-                if (order == 1) { coef[0] = 1; }
-                else if (order == 2) { coef[0] = 2; coef[1] = -1; }
-                else if (order == 3) { coef[0] = 3; coef[1] = -3; coef[2] = 1; }
-                else if (order == 4) { coef[0] = 4; coef[1] = -6; coef[2] = 4; coef[3] = -1; }
-                prec = 3;
-            }
-            // residual header
-            uint32_t method = br.get(2);
-            uint32_t po = br.get(4);
-            if (method > 1u || ((uint32_t)nsamp >> po) << po != (uint32_t)nsamp && po > 0) { bad = true; break; }
-            if (((uint32_t)nsamp >> po) < (uint32_t)order) { bad = true; break; }
-            RiceState rs;
-            rs.pbits = method ? 5 : 4; rs.esc = method ? 31u : 15u; rs.psize = (uint32_t)nsamp >> po;
-            rs.left = 0; rs.k = 0; rs.rawbits = -1;
-            // the first partition is short by `order`: prime it here
-            rs.k = br.get(rs.pbits);
-            rs.left = rs.psize - (uint32_t)order;
-            if (rs.k == rs.esc) rs.rawbits = (int)br.get(5);
-            const bool wide = order > 0 && (sbps + prec + ilog2_u32((uint32_t)order) > 32);
-            if (order <= 4) {
-                if (wide) restore_subframe<DT, 4, true>(br, rs, ow, coef, order, shift, warm, nsamp, wasted, bps, dq, a.pcm_mode);
-                else restore_subframe<DT, 4, false>(br, rs, ow, coef, order, shift, warm, nsamp, wasted, bps, dq, a.pcm_mode);
-            } else if (order <= 8) {
-                if (wide) restore_subframe<DT, 8, true>(br, rs, ow, coef, order, shift, warm, nsamp, wasted, bps, dq, a.pcm_mode);
-                else restore_subframe<DT, 8, false>(br, rs, ow, coef, order, shift, warm, nsamp, wasted, bps, dq, a.pcm_mode);
-            } else if (order <= 12) {
-                if (wide) restore_subframe<DT, 12, true>(br, rs, ow, coef, order, shift, warm, nsamp, wasted, bps, dq, a.pcm_mode);
-                else restore_subframe<DT, 12, false>(br, rs, ow, coef, order, shift, warm, nsamp, wasted, bps, dq, a.pcm_mode);
-            } else {
-                restore_subframe_generic<DT>(br, rs, ow, coef, order, shift, warm, nsamp, wasted, bps, dq, a.pcm_mode);
-            }
+            if (c && lane != 31) c = frx_gf16_mulmod(c, (uint32_t)__ldg(&xpow[(Lq - 1) * 256 + (31 - lane)]));
+            c = __reduce_xor_sync(0xFFFFFFFFu, c);
+            // crc <- crc * x^(8 pass) + c ; x^(8 pass) = x^(128 Lq 32) when the pass is full, and a full pass is the only one followed by another
+            if (done) {
+                // previous passes were full: shift the running CRC by this pass's length, 8 bits at a time is too slow -> square-and-multiply
+                uint32_t e = pass * 8u, base = 2u, acc = 1u;
+                while (e) { if (e & 1u) acc = frx_gf16_mulmod(acc, base); base = frx_gf16_mulmod(base, base); e >>= 1; }
+                crc = frx_gf16_mulmod(crc, acc) ^ c;
+            } else crc = c;
+            done += pass;
+        }
+        if (crc != 0 && lane == 0) {
+            const int ti = dec_find_tile(a.dprefix, a.n_tiles, f);
+            atomicExch(&a.tile_status[ti], FRX_E_BITSTREAM);
         }
     }
-    // ---- footer: byte align + CRC-16 ----
-    uint64_t body_bytes = (br.consumed + 7u) >> 3;
-    uint64_t fsize = body_bytes + 2u;
-    if (!bad && pos + fsize > end) bad = true;
-    if (!bad && fj + 1 < t.n_frames && a.frame_pos[f + 1] != FRX_NOPOS && pos + fsize != a.frame_pos[f + 1]) bad = true;
-    if (!bad && a.verify_crc) {
-        // CRC over the whole frame including the stored CRC must be 0
-        const uint8_t *p = a.bytes + pos;
-        uint32_t c = 0;
-        uint64_t i = 0;
-        while (i < fsize && ((uintptr_t)(p + i) & 3u)) { c = ((c << 8) ^ crc_tab[0][((c >> 8) ^ p[i]) & 0xFFu]) & 0xFFFFu; i++; }
-        for (; i + 4 <= fsize; i += 4) {
-            uint32_t w = frx_bswap32(__ldg((const uint32_t *)(p + i)));
-            uint32_t x = w ^ (c << 16);
-            c = (uint32_t)crc_tab[3][x >> 24] ^ crc_tab[2][(x >> 16) & 0xFFu] ^ crc_tab[1][(x >> 8) & 0xFFu] ^ crc_tab[0][x & 0xFFu];
-        }
-        for (; i < fsize; i++) c = ((c << 8) ^ crc_tab[0][((c >> 8) ^ p[i]) & 0xFFu]) & 0xFFFFu;
-        if (c != 0) bad = true;
-    }
-    if (bad) atomicExch(&a.tile_status[ti], FRX_E_BITSTREAM);
 }
 
 // K12 alone
@@ -467,16 +647,23 @@ cudaError_t frx_launch_discover(const DecArgs &a, const uint32_t *unit_prefix, c
     return cudaGetLastError();
 }
 
+cudaError_t frx_launch_crc_check(const DecArgs &a, const uint16_t *xpow, int sm_count, cudaStream_t st) {
+    if (!a.total_frames) return cudaSuccess;
+    unsigned want = (a.total_frames + 3u) / 4u, cap = (unsigned)sm_count * 16u;
+    frx_crc_check_kernel<<<want < cap ? want : cap, 128, 0, st>>>(a, xpow);
+    return cudaGetLastError();
+}
+
 cudaError_t frx_launch_decode(const DecArgs &a, int out_dtype, cudaStream_t st) {
     unsigned grid = (a.total_frames + 127u) / 128u;
     if (!grid) return cudaSuccess;
     switch (out_dtype) {
-        case FRX_U8: frx_decode_kernel<FRX_U8><<<grid, 128, 0, st>>>(a); break;
-        case FRX_I16: frx_decode_kernel<FRX_I16><<<grid, 128, 0, st>>>(a); break;
-        case FRX_U16: frx_decode_kernel<FRX_U16><<<grid, 128, 0, st>>>(a); break;
-        case FRX_I32: frx_decode_kernel<FRX_I32><<<grid, 128, 0, st>>>(a); break;
-        case FRX_U32: frx_decode_kernel<FRX_U32><<<grid, 128, 0, st>>>(a); break;
-        case FRX_F32: frx_decode_kernel<FRX_F32><<<grid, 128, 0, st>>>(a); break;
+        case FRX_U8: frx_decode_kernel<FRX_U8><<<grid, 32 * DEC_WARPS, 0, st>>>(a); break;
+        case FRX_I16: frx_decode_kernel<FRX_I16><<<grid, 32 * DEC_WARPS, 0, st>>>(a); break;
+        case FRX_U16: frx_decode_kernel<FRX_U16><<<grid, 32 * DEC_WARPS, 0, st>>>(a); break;
+        case FRX_I32: frx_decode_kernel<FRX_I32><<<grid, 32 * DEC_WARPS, 0, st>>>(a); break;
+        case FRX_U32: frx_decode_kernel<FRX_U32><<<grid, 32 * DEC_WARPS, 0, st>>>(a); break;
+        case FRX_F32: frx_decode_kernel<FRX_F32><<<grid, 32 * DEC_WARPS, 0, st>>>(a); break;
         default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();

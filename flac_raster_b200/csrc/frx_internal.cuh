@@ -43,6 +43,7 @@ struct DecArgs {
     const uint32_t *dprefix;
     uint64_t *frame_pos;
     const uint32_t *frame_size;
+    uint32_t *frame_len;            // decoded size of every frame (0: rejected), input of the CRC pass
     const uint16_t *crc_tab;
     void *out;
     int32_t *tile_status;
@@ -53,6 +54,7 @@ struct DecArgs {
     int verify_crc;
 };
 size_t frx_enc_smem_bytes(int frame_words, int dtype);
+cudaError_t frx_launch_crc_check(const DecArgs &a, const uint16_t *xpow, int sm_count, cudaStream_t st);
 size_t frx_minmax_raw_size();
 cudaError_t frx_launch_minmax(const frx_raster &r, const frx_tile *tiles_dev, const uint32_t *unit_prefix_dev, int n_tiles,
                               uint32_t total_units, int unit_elems, void *mm_raw, FrxQuant *quant, cudaStream_t st);
