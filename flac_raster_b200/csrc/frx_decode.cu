@@ -141,7 +141,7 @@ struct BitR {
     uint32_t rd, wr;            // words consumed / fetched
     uint64_t acc;               // left aligned
     int cnt;                    // valid bits in acc
-    uint32_t consumed;          // bits consumed since init
+    uint32_t start_bits;        // stream position of the frame's first bit, in bits from ring word 0
     __device__ __forceinline__ uint4 load16() const {
         if (np >= lo && np + 16 <= hi) return __ldg(reinterpret_cast<const uint4 *>(np));
         return dec_load16_clamped(np, lo, hi);
@@ -177,7 +177,7 @@ struct BitR {
         const uintptr_t addr = (uintptr_t)(base + pos);
         const int lead = (int)(addr & 15u);
         np = (const uint8_t *)(addr - lead);
-        ring = ring_col; rd = 0; wr = 0; consumed = 0; acc = 0; cnt = 0;
+        ring = ring_col; rd = 0; wr = 0; start_bits = (uint32_t)lead * 8u; acc = 0; cnt = 0;
         topup(live);
         if (live) {
             rd = (uint32_t)(lead >> 2);
@@ -187,6 +187,8 @@ struct BitR {
             refill();
         }
     }
+    // bits consumed since init: everything popped, minus what still sits in the window
+    __device__ __forceinline__ uint32_t consumed() const { return rd * 32u - (uint32_t)cnt - start_bits; }
     __device__ __forceinline__ void refill() {
         if (cnt <= 32) {
             acc |= (uint64_t)pop() << (32 - cnt);
@@ -198,7 +200,7 @@ struct BitR {
         refill();
         const uint32_t v = n ? (uint32_t)(acc >> (64 - n)) : 0u;
         acc <<= n;
-        cnt -= n; consumed += (uint32_t)n;
+        cnt -= n;
         return v;
     }
     __device__ __forceinline__ int32_t sget(int n) {  // signed, n in 1..32
@@ -210,14 +212,14 @@ struct BitR {
         for (;;) {
             refill();
             if (acc == 0) {
-                z += (uint32_t)cnt; consumed += (uint32_t)cnt; cnt = 0;
+                z += (uint32_t)cnt; cnt = 0;
                 if (np > hi + 256) return z;  // ran off the buffer: malformed
                 continue;
             }
             const int lz = __clzll((long long)acc);
             z += (uint32_t)lz;
             acc = lz == 63 ? 0ull : (acc << (lz + 1));  // a set bit exists within cnt bits, so lz < cnt
-            cnt -= lz + 1; consumed += (uint32_t)lz + 1u;
+            cnt -= lz + 1;
             return z;
         }
     }
@@ -254,7 +256,7 @@ __device__ __forceinline__ int ilog2_u32(uint32_t v) { return 31 - __clz((int)v)
 // go through a shared-memory transpose so that every global store is one full line of one frame's raster row, instead of
 // 32 lanes scattering single elements 16 KB apart.
 // ------------------------------------------------------------------------------------------
-#define DEC_WARPS 4
+#define DEC_WARPS 1     // one warp per CTA: a frame takes milliseconds on its lane, so the grid must fit one wave; small CTAs pack the SMs evenly
 #define DEC_MAXORD 16
 struct DecWarpSmem {
     uint32_t ring[DEC_RING][32];     // input rings, one column per lane
@@ -352,31 +354,56 @@ __device__ __forceinline__ void run_chunks(BitR &br, SubF &sf, int32_t *coef, in
         ws.room[lane] = (uint32_t)(w - col);
         ws.wid[lane] = (uint32_t)w;
         ws.cnt[lane] = (uint32_t)min(32, max(0, my_n - n0));
+        // a chunk past the warm-up in which every lane restores 32 predicted samples needs no per-sample predicates
+        const bool steady = __all_sync(0xFFFFFFFFu, sf.type == 2 && n0 >= 32 && n0 + 32 <= my_n);
+        if (steady) {
+            for (int mb = 0; mb < 32; mb += ORD) {
+#pragma unroll
+                for (int mi = 0; mi < ORD; mi++) {
+                    const int32_t r = rice_next(br, sf.rs);
+                    int32_t v;
+                    if (WIDE) {
+                        long long acc = 0;
+#pragma unroll
+                        for (int j = 0; j < ORD; j++) acc += (long long)coef[j] * (long long)h[(mi - 1 - j + 2 * ORD) % ORD];
+                        v = (int32_t)((long long)r + (acc >> sf.shift));
+                    } else {
+                        int32_t acc = 0;
+#pragma unroll
+                        for (int j = 0; j < ORD; j++) acc += coef[j] * h[(mi - 1 - j + 2 * ORD) % ORD];
+                        v = r + (acc >> sf.shift);
+                    }
+                    h[mi] = v;
+                    ws.stage[lane][mb + mi] = dec_pack<DT>(frx_dequant<DT>((int32_t)((uint32_t)v << sf.wasted), bps, dq, mode));
+                }
+            }
+        } else {
         for (int mb = 0; mb < 32; mb += ORD) {
 #pragma unroll
-            for (int mi = 0; mi < ORD; mi++) {
-                const int n = n0 + mb + mi;
-                int32_t v = sf.cval;
-                if (n < my_n) {
-                    if (sf.type == 2) {
-                        if (n >= sf.order) {
-                            const int32_t r = rice_next(br, sf.rs);
-                            if (WIDE) {
-                                long long acc = 0;
+                for (int mi = 0; mi < ORD; mi++) {
+                    const int n = n0 + mb + mi;
+                    int32_t v = sf.cval;
+                    if (n < my_n) {
+                        if (sf.type == 2) {
+                            if (n >= sf.order) {
+                                const int32_t r = rice_next(br, sf.rs);
+                                if (WIDE) {
+                                    long long acc = 0;
 #pragma unroll
-                                for (int j = 0; j < ORD; j++) acc += (long long)coef[j] * (long long)h[(mi - 1 - j + 2 * ORD) % ORD];
-                                v = (int32_t)((long long)r + (acc >> sf.shift));
-                            } else {
-                                int32_t acc = 0;
+                                    for (int j = 0; j < ORD; j++) acc += (long long)coef[j] * (long long)h[(mi - 1 - j + 2 * ORD) % ORD];
+                                    v = (int32_t)((long long)r + (acc >> sf.shift));
+                                } else {
+                                    int32_t acc = 0;
 #pragma unroll
-                                for (int j = 0; j < ORD; j++) acc += coef[j] * h[(mi - 1 - j + 2 * ORD) % ORD];
-                                v = r + (acc >> sf.shift);
-                            }
-                            h[mi] = v;
-                        } else v = h[mi];   // warm-up sample (n < order <= ORD, so n == mi)
-                    } else if (sf.type == 1) v = br.sget(sf.sbps);
+                                    for (int j = 0; j < ORD; j++) acc += coef[j] * h[(mi - 1 - j + 2 * ORD) % ORD];
+                                    v = r + (acc >> sf.shift);
+                                }
+                                h[mi] = v;
+                            } else v = h[mi];   // warm-up sample (n < order <= ORD, so n == mi)
+                        } else if (sf.type == 1) v = br.sget(sf.sbps);
+                    }
+                    ws.stage[lane][mb + mi] = dec_pack<DT>(frx_dequant<DT>((int32_t)((uint32_t)v << sf.wasted), bps, dq, mode));
                 }
-                ws.stage[lane][mb + mi] = dec_pack<DT>(frx_dequant<DT>((int32_t)((uint32_t)v << sf.wasted), bps, dq, mode));
             }
         }
         flush_chunk<DT>(ws, lane);
@@ -386,7 +413,7 @@ __device__ __forceinline__ void run_chunks(BitR &br, SubF &sf, int32_t *coef, in
 }
 
 template <int DT>
-__global__ void __launch_bounds__(32 * DEC_WARPS, 4) frx_decode_kernel(const DecArgs a) {
+__global__ void __launch_bounds__(32 * DEC_WARPS, 20) frx_decode_kernel(const DecArgs a) {
     typedef typename FrxElem<DT>::T T;
     __shared__ DecWarpSmem wsm[DEC_WARPS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -548,7 +575,7 @@ __global__ void __launch_bounds__(32 * DEC_WARPS, 4) frx_decode_kernel(const Dec
     }
     if (!live) return;
     // ---- footer: byte align; the frame must end where the next one starts (CRC-16: frx_crc_check_kernel) ----
-    const uint64_t fsize = (uint64_t)((br.consumed + 7u) >> 3) + 2u;
+    const uint64_t fsize = (uint64_t)((br.consumed() + 7u) >> 3) + 2u;
     if (!bad && pos + fsize > end) bad = true;
     if (!bad && fj + 1 < t.n_frames && a.frame_pos[f + 1] != FRX_NOPOS && pos + fsize != a.frame_pos[f + 1]) bad = true;
     if (a.frame_len) a.frame_len[f] = bad ? 0u : (uint32_t)fsize;
@@ -655,7 +682,7 @@ cudaError_t frx_launch_crc_check(const DecArgs &a, const uint16_t *xpow, int sm_
 }
 
 cudaError_t frx_launch_decode(const DecArgs &a, int out_dtype, cudaStream_t st) {
-    unsigned grid = (a.total_frames + 127u) / 128u;
+    unsigned grid = (a.total_frames + 32u * DEC_WARPS - 1u) / (32u * DEC_WARPS);
     if (!grid) return cudaSuccess;
     switch (out_dtype) {
         case FRX_U8: frx_decode_kernel<FRX_U8><<<grid, 32 * DEC_WARPS, 0, st>>>(a); break;

@@ -24,7 +24,7 @@ struct BitR {
     uint32_t rd, wr;            // words consumed / fetched
     uint64_t acc;               // left aligned
     int cnt;                    // valid bits in acc
-    uint32_t consumed;          // bits consumed since init
+    uint32_t start_bits;        // stream position of the frame's first bit, in bits from ring word 0
     __device__ __forceinline__ uint4 load16() const {
         if (np >= lo && np + 16 <= hi) return __ldg(reinterpret_cast<const uint4 *>(np));
         return dec_load16_clamped(np, lo, hi);
@@ -60,7 +60,7 @@ struct BitR {
         const uintptr_t addr = (uintptr_t)(base + pos);
         const int lead = (int)(addr & 15u);
         np = (const uint8_t *)(addr - lead);
-        ring = ring_col; rd = 0; wr = 0; consumed = 0; acc = 0; cnt = 0;
+        ring = ring_col; rd = 0; wr = 0; start_bits = (uint32_t)lead * 8u; acc = 0; cnt = 0;
         topup(live);
         if (live) {
             rd = (uint32_t)(lead >> 2);
@@ -70,6 +70,8 @@ struct BitR {
             refill();
         }
     }
+    // bits consumed since init: everything popped, minus what still sits in the window
+    __device__ __forceinline__ uint32_t consumed() const { return rd * 32u - (uint32_t)cnt - start_bits; }
     __device__ __forceinline__ void refill() {
         if (cnt <= 32) {
             acc |= (uint64_t)pop() << (32 - cnt);
@@ -81,7 +83,7 @@ struct BitR {
         refill();
         const uint32_t v = n ? (uint32_t)(acc >> (64 - n)) : 0u;
         acc <<= n;
-        cnt -= n; consumed += (uint32_t)n;
+        cnt -= n;
         return v;
     }
     __device__ __forceinline__ int32_t sget(int n) {  // signed, n in 1..32
@@ -93,14 +95,14 @@ struct BitR {
         for (;;) {
             refill();
             if (acc == 0) {
-                z += (uint32_t)cnt; consumed += (uint32_t)cnt; cnt = 0;
+                z += (uint32_t)cnt; cnt = 0;
                 if (np > hi + 256) return z;  // ran off the buffer: malformed
                 continue;
             }
             const int lz = __clzll((long long)acc);
             z += (uint32_t)lz;
             acc = lz == 63 ? 0ull : (acc << (lz + 1));  // a set bit exists within cnt bits, so lz < cnt
-            cnt -= lz + 1; consumed += (uint32_t)lz + 1u;
+            cnt -= lz + 1;
             return z;
         }
     }

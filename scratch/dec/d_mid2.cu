@@ -4,7 +4,7 @@
 // go through a shared-memory transpose so that every global store is one full line of one frame's raster row, instead of
 // 32 lanes scattering single elements 16 KB apart.
 // ------------------------------------------------------------------------------------------
-#define DEC_WARPS 4
+#define DEC_WARPS 1     // one warp per CTA: a frame takes milliseconds on its lane, so the grid must fit one wave; small CTAs pack the SMs evenly
 #define DEC_MAXORD 16
 struct DecWarpSmem {
     uint32_t ring[DEC_RING][32];     // input rings, one column per lane
@@ -102,31 +102,56 @@ __device__ __forceinline__ void run_chunks(BitR &br, SubF &sf, int32_t *coef, in
         ws.room[lane] = (uint32_t)(w - col);
         ws.wid[lane] = (uint32_t)w;
         ws.cnt[lane] = (uint32_t)min(32, max(0, my_n - n0));
+        // a chunk past the warm-up in which every lane restores 32 predicted samples needs no per-sample predicates
+        const bool steady = __all_sync(0xFFFFFFFFu, sf.type == 2 && n0 >= 32 && n0 + 32 <= my_n);
+        if (steady) {
+            for (int mb = 0; mb < 32; mb += ORD) {
+#pragma unroll
+                for (int mi = 0; mi < ORD; mi++) {
+                    const int32_t r = rice_next(br, sf.rs);
+                    int32_t v;
+                    if (WIDE) {
+                        long long acc = 0;
+#pragma unroll
+                        for (int j = 0; j < ORD; j++) acc += (long long)coef[j] * (long long)h[(mi - 1 - j + 2 * ORD) % ORD];
+                        v = (int32_t)((long long)r + (acc >> sf.shift));
+                    } else {
+                        int32_t acc = 0;
+#pragma unroll
+                        for (int j = 0; j < ORD; j++) acc += coef[j] * h[(mi - 1 - j + 2 * ORD) % ORD];
+                        v = r + (acc >> sf.shift);
+                    }
+                    h[mi] = v;
+                    ws.stage[lane][mb + mi] = dec_pack<DT>(frx_dequant<DT>((int32_t)((uint32_t)v << sf.wasted), bps, dq, mode));
+                }
+            }
+        } else {
         for (int mb = 0; mb < 32; mb += ORD) {
 #pragma unroll
-            for (int mi = 0; mi < ORD; mi++) {
-                const int n = n0 + mb + mi;
-                int32_t v = sf.cval;
-                if (n < my_n) {
-                    if (sf.type == 2) {
-                        if (n >= sf.order) {
-                            const int32_t r = rice_next(br, sf.rs);
-                            if (WIDE) {
-                                long long acc = 0;
+                for (int mi = 0; mi < ORD; mi++) {
+                    const int n = n0 + mb + mi;
+                    int32_t v = sf.cval;
+                    if (n < my_n) {
+                        if (sf.type == 2) {
+                            if (n >= sf.order) {
+                                const int32_t r = rice_next(br, sf.rs);
+                                if (WIDE) {
+                                    long long acc = 0;
 #pragma unroll
-                                for (int j = 0; j < ORD; j++) acc += (long long)coef[j] * (long long)h[(mi - 1 - j + 2 * ORD) % ORD];
-                                v = (int32_t)((long long)r + (acc >> sf.shift));
-                            } else {
-                                int32_t acc = 0;
+                                    for (int j = 0; j < ORD; j++) acc += (long long)coef[j] * (long long)h[(mi - 1 - j + 2 * ORD) % ORD];
+                                    v = (int32_t)((long long)r + (acc >> sf.shift));
+                                } else {
+                                    int32_t acc = 0;
 #pragma unroll
-                                for (int j = 0; j < ORD; j++) acc += coef[j] * h[(mi - 1 - j + 2 * ORD) % ORD];
-                                v = r + (acc >> sf.shift);
-                            }
-                            h[mi] = v;
-                        } else v = h[mi];   // warm-up sample (n < order <= ORD, so n == mi)
-                    } else if (sf.type == 1) v = br.sget(sf.sbps);
+                                    for (int j = 0; j < ORD; j++) acc += coef[j] * h[(mi - 1 - j + 2 * ORD) % ORD];
+                                    v = r + (acc >> sf.shift);
+                                }
+                                h[mi] = v;
+                            } else v = h[mi];   // warm-up sample (n < order <= ORD, so n == mi)
+                        } else if (sf.type == 1) v = br.sget(sf.sbps);
+                    }
+                    ws.stage[lane][mb + mi] = dec_pack<DT>(frx_dequant<DT>((int32_t)((uint32_t)v << sf.wasted), bps, dq, mode));
                 }
-                ws.stage[lane][mb + mi] = dec_pack<DT>(frx_dequant<DT>((int32_t)((uint32_t)v << sf.wasted), bps, dq, mode));
             }
         }
         flush_chunk<DT>(ws, lane);

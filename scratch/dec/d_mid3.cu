@@ -1,5 +1,5 @@
 template <int DT>
-__global__ void __launch_bounds__(32 * DEC_WARPS, 4) frx_decode_kernel(const DecArgs a) {
+__global__ void __launch_bounds__(32 * DEC_WARPS, 20) frx_decode_kernel(const DecArgs a) {
     typedef typename FrxElem<DT>::T T;
     __shared__ DecWarpSmem wsm[DEC_WARPS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(32 * DEC_WARPS, 4) frx_decode_kernel(const Dec
     }
     if (!live) return;
     // ---- footer: byte align; the frame must end where the next one starts (CRC-16: frx_crc_check_kernel) ----
-    const uint64_t fsize = (uint64_t)((br.consumed + 7u) >> 3) + 2u;
+    const uint64_t fsize = (uint64_t)((br.consumed() + 7u) >> 3) + 2u;
     if (!bad && pos + fsize > end) bad = true;
     if (!bad && fj + 1 < t.n_frames && a.frame_pos[f + 1] != FRX_NOPOS && pos + fsize != a.frame_pos[f + 1]) bad = true;
     if (a.frame_len) a.frame_len[f] = bad ? 0u : (uint32_t)fsize;
