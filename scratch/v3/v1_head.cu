@@ -62,20 +62,47 @@ __global__ void __launch_bounds__(256) frx_minmax_kernel(const void *raster, lon
     long long imin = LLONG_MAX, imax = LLONG_MIN;
     float fmin = CUDART_INF_F, fmax = -CUDART_INF_F;
     int nan = 0;
-    for (long long vr = vrow0; vr < vrow1; vr++) {
-        int c = (int)(vr / t.h);
-        int r = (int)(vr - (long long)c * t.h);
-        const T *row = base + (long long)(t.first_band + c) * band_stride + (long long)(t.row_off + r) * row_stride + t.col_off;
-        for (int x = threadIdx.x; x < t.w; x += blockDim.x) {
-            T v = row[x];
-            if (DT == FRX_F32) {
-                float f = (float)v;
-                if (f != f) nan = 1;
-                fmin = fminf(fmin, f); fmax = fmaxf(fmax, f);
-            } else {
-                long long iv = (long long)v;
-                imin = min(imin, iv); imax = max(imax, iv);
+    // 16-byte loads when the tile rows allow it (every thread keeps several in flight), element loads otherwise
+    constexpr int VEC = 16 / (int)sizeof(T);
+    const bool vec_ok = (((uintptr_t)base & 15u) == 0) && (band_stride % VEC) == 0 && (row_stride % VEC) == 0 && (t.col_off % VEC) == 0 && (t.w % VEC) == 0;
+    auto take = [&](T v) {
+        if (DT == FRX_F32) {
+            const float f = (float)v;
+            if (f != f) nan = 1;
+            fmin = fminf(fmin, f); fmax = fmaxf(fmax, f);
+        } else {
+            const long long iv = (long long)v;
+            imin = min(imin, iv); imax = max(imax, iv);
+        }
+    };
+    auto row_ptr = [&](long long vr) {
+        const int c = (int)(vr / t.h);
+        const int r = (int)(vr - (long long)c * t.h);
+        return base + (long long)(t.first_band + c) * band_stride + (long long)(t.row_off + r) * row_stride + t.col_off;
+    };
+    if (vec_ok) {
+        const int n4 = t.w / VEC;
+        for (long long vr = vrow0; vr < vrow1; vr += 4) {     // four rows at a time: four independent loads per thread
+            const uint4 *rp[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) rp[k] = reinterpret_cast<const uint4 *>(row_ptr(min(vr + k, vrow1 - 1)));
+            for (int x = threadIdx.x; x < n4; x += blockDim.x) {
+                uint4 q[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) q[k] = __ldg(rp[k] + x);
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    T e[VEC];
+                    memcpy(e, &q[k], 16);
+#pragma unroll
+                    for (int j = 0; j < VEC; j++) take(e[j]);
+                }
             }
+        }
+    } else {
+        for (long long vr = vrow0; vr < vrow1; vr++) {
+            const T *row = row_ptr(vr);
+            for (int x = threadIdx.x; x < t.w; x += blockDim.x) take(row[x]);
         }
     }
     // warp reduce
