@@ -43,6 +43,16 @@ SMALL = {"c2": (4096, 4096), "c3": (4096, 4096)}
 FALLBACK_HBM_GBS = 6650.0
 
 
+def ncu_traffic(workload: str, kernel: str):
+    """dram bytes (read + write) per launch of `kernel` from the committed ncu --set full capture of this workload
+    (profiles/r1_traffic.json); None when no capture exists for it."""
+    try:
+        t = json.loads((ROOT / "profiles" / "r1_traffic.json").read_text())[workload][kernel]
+        return int(t["dram_read_bytes"]) + int(t["dram_write_bytes"])
+    except Exception:
+        return None
+
+
 class ClockSampler(threading.Thread):
     """Samples SM clock + throttle reasons of one GPU through NVML while the timed region runs."""
 
@@ -318,7 +328,8 @@ def main_ours(args):
     decode = {"metric": "decode_tiles_per_s", "value": round(world * len(tiles) / (dec_ms * 1e-3), 1), "unit": "tiles/s",
               "ms_per_step": round(dec_ms, 3), "tiles_per_step": len(tiles), "mpixel_per_s": round(world * H * W / dec_ms / 1e3, 1),
               "roofline": {"bound": "hbm", "achieved": round(alg_bytes / (dec_k_ms * 1e-3) / 1e9, 2), "peak": peak, "unit": "GB/s",
-                           "frac": round(alg_bytes / (dec_k_ms * 1e-3) / 1e9 / peak, 4), "traffic": None,
+                           "frac": round(alg_bytes / (dec_k_ms * 1e-3) / 1e9 / peak, 4),
+                           "traffic": None if args.small else ncu_traffic(args.workload, "frx_decode_kernel"),
                            "kernel": "frx_decode_kernel", "kernel_ms": round(dec_k_ms, 4)}}
 
     # ---- e2e: host buffers through the C-ABI host entry point, pinned memory, H2D + D2H timed ----
@@ -387,7 +398,7 @@ def main_ours(args):
                        "l2": f"inputs larger than L2 ({raster_bytes / 1e6:.0f} MB raster per step vs 126 MB), no flush needed",
                        "per_rank": "each rank encodes its own raster of this shape (seed + rank); no collective"},
             "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                         "traffic": None, "kernel": "frx_encode_kernel", "kernel_ms": round(k_ms, 4), "algorithmic_bytes": alg_bytes,
+                         "traffic": None if args.small else ncu_traffic(args.workload, "frx_encode_kernel"), "kernel": "frx_encode_kernel", "kernel_ms": round(k_ms, 4), "algorithmic_bytes": alg_bytes,
                          "peak_source": peak_src},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "decode": decode,
         }
