@@ -458,15 +458,19 @@ __device__ __noinline__ void analyse_level(EncSmall &sh, const uint64_t *tabs, i
     if (lane == 0) { sh.lvl_bits[cand][L] = bits; sh.lvl_big[cand][L] = anybig ? 1u : 0u; }
 }
 
-// best partition order of a candidate: highest order first, a lower one only when strictly cheaper (libFLAC's loop)
+// best partition order of a candidate: highest order first, a lower one only when strictly cheaper (libFLAC's loop).
+// Called by whole warps: lane L looks at order L, one redux picks the minimum, the highest lane holding it wins.
 __device__ __forceinline__ void pick_level(const EncSmall &sh, int cand, int po_max, int &po, uint64_t &bits, bool &rice2) {
-    uint64_t best = ~0ull;
-    int bp = 0;
-    for (int L = po_max; L >= 0; L--) {
-        const uint64_t b = sh.lvl_bits[cand][L];
-        if (b < best) { best = b; bp = L; }
+    const int lane = threadIdx.x & 31;
+    uint32_t key = 0xFFFFFFFFu, big = 0;
+    if (lane <= po_max) {
+        const uint64_t b = sh.lvl_bits[cand][lane];
+        key = b < 0xFFFFFFFEull ? (uint32_t)b : 0xFFFFFFFEu;
+        big = sh.lvl_big[cand][lane];
     }
-    po = bp; bits = best; rice2 = sh.lvl_big[cand][bp] != 0u;
+    const uint32_t m = __reduce_min_sync(FULLMASK, key);
+    const int bp = 31 - __clz((int)(__ballot_sync(FULLMASK, key == m) & 0xFFu));
+    po = bp; bits = m; rice2 = __shfl_sync(FULLMASK, big, bp) != 0u;
 }
 // ------------------------------------------------------------------------------------------
 // K1: raw staging buffer -> PCM in shared memory.  Thread t owns samples [16t, 16t+16).
@@ -817,7 +821,7 @@ __device__ __noinline__ void control_warp(const EncArgs &a, EncSmall &sh, unsign
             } else if (!lb.blocked) progress = true;
         }
         if (stop_issued && !lb_active && fseq_lb == fseq_iss) break;
-        if (!progress) __nanosleep(400);
+        if (!progress) __nanosleep(200);
     }
 }
 // residual of one sample, lean paths (no overflow possible by construction)
@@ -1238,8 +1242,14 @@ __device__ __forceinline__ void copy_out_frame(const EncArgs &a, EncSmall &sh, c
 
 // CRC-16 of the frame body's whole words: every compute thread takes a chunk of Lq quads, the chunk CRCs are shifted to
 // their place with x^(128 Lq j) mod P and xor-ed (per warp here, across warps by copy_out_frame)
+// shift factor of this thread's chunk; loaded ahead of the barrier in front of crc_frame so its latency is hidden
+__device__ __forceinline__ uint32_t crc_shift_factor(const EncArgs &a, uint32_t body_bytes, int tid) {
+    const uint32_t nq = ((body_bytes >> 2) + 3u) >> 2;
+    const uint32_t Lq = (nq + FRX_ENC_THREADS - 1) / FRX_ENC_THREADS;
+    return (uint32_t)__ldg(&a.crc_xpow[(max(Lq, 1u) - 1) * FRX_ENC_THREADS + (FRX_ENC_THREADS - 1 - tid)]);
+}
 __device__ __forceinline__ void crc_frame(const EncArgs &a, EncSmall &sh, const uint32_t *bits, uint32_t *crc_part, uint32_t body_bytes,
-                                          int tid) {
+                                          int tid, uint32_t shift_factor) {
     const uint32_t nw = body_bytes >> 2;                       // whole words
     const uint32_t nq = (nw + 3u) >> 2;                        // quads; the buffer is zero behind the frame
     const uint32_t Lq = (nq + FRX_ENC_THREADS - 1) / FRX_ENC_THREADS;
@@ -1265,7 +1275,7 @@ __device__ __forceinline__ void crc_frame(const EncArgs &a, EncSmall &sh, const 
         x = wv.w ^ (c << 16);
         c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
     }
-    if (c) c = frx_gf16_mulmod(c, (uint32_t)__ldg(&a.crc_xpow[(Lq - 1) * FRX_ENC_THREADS + (FRX_ENC_THREADS - 1 - tid)]));
+    if (c) c = frx_gf16_mulmod(c, shift_factor);
     c = __reduce_xor_sync(FULLMASK, c);
     if ((tid & 31) == 0) crc_part[tid >> 5] = c;
 }
@@ -1658,13 +1668,14 @@ __global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArg
             // the PCM buffer is rewritten by the next channel's K1: every reader of it (verbatim / warm-up packing) must be done
             if (ch + 1 < n_channels) compute_sync();
         }  // channels
+        const uint32_t crc_xp = crc_shift_factor(a, (bitpos + 7u) >> 3, tid);
         compute_sync();  // Sa: every subframe is packed
         DBG_PH(14);
 
         // ---- frame footer: CRC-16 of this frame; copy-out of the PREVIOUS frame (its byte offset has had a frame time to arrive) ----
         const uint32_t body_bytes = (bitpos + 7u) >> 3;
         const long long cc0 = DBG_CLK();
-        crc_frame(a, sh, bits, sh.crc_part[buf], body_bytes, tid);
+        crc_frame(a, sh, bits, sh.crc_part[buf], body_bytes, tid, crc_xp);
 
         if (pend) {
             const int pslot = (int)((fseq - 1u) & (FD_SLOTS - 1));

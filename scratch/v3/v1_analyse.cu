@@ -97,13 +97,17 @@ __device__ __noinline__ void analyse_level(EncSmall &sh, const uint64_t *tabs, i
     if (lane == 0) { sh.lvl_bits[cand][L] = bits; sh.lvl_big[cand][L] = anybig ? 1u : 0u; }
 }
 
-// best partition order of a candidate: highest order first, a lower one only when strictly cheaper (libFLAC's loop)
+// best partition order of a candidate: highest order first, a lower one only when strictly cheaper (libFLAC's loop).
+// Called by whole warps: lane L looks at order L, one redux picks the minimum, the highest lane holding it wins.
 __device__ __forceinline__ void pick_level(const EncSmall &sh, int cand, int po_max, int &po, uint64_t &bits, bool &rice2) {
-    uint64_t best = ~0ull;
-    int bp = 0;
-    for (int L = po_max; L >= 0; L--) {
-        const uint64_t b = sh.lvl_bits[cand][L];
-        if (b < best) { best = b; bp = L; }
+    const int lane = threadIdx.x & 31;
+    uint32_t key = 0xFFFFFFFFu, big = 0;
+    if (lane <= po_max) {
+        const uint64_t b = sh.lvl_bits[cand][lane];
+        key = b < 0xFFFFFFFEull ? (uint32_t)b : 0xFFFFFFFEu;
+        big = sh.lvl_big[cand][lane];
     }
-    po = bp; bits = best; rice2 = sh.lvl_big[cand][bp] != 0u;
+    const uint32_t m = __reduce_min_sync(FULLMASK, key);
+    const int bp = 31 - __clz((int)(__ballot_sync(FULLMASK, key == m) & 0xFFu));
+    po = bp; bits = m; rice2 = __shfl_sync(FULLMASK, big, bp) != 0u;
 }

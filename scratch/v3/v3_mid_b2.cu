@@ -237,6 +237,6 @@ __device__ __noinline__ void control_warp(const EncArgs &a, EncSmall &sh, unsign
             } else if (!lb.blocked) progress = true;
         }
         if (stop_issued && !lb_active && fseq_lb == fseq_iss) break;
-        if (!progress) __nanosleep(400);
+        if (!progress) __nanosleep(200);
     }
 }

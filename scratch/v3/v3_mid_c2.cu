@@ -43,8 +43,14 @@ __device__ __forceinline__ void copy_out_frame(const EncArgs &a, EncSmall &sh, c
 
 // CRC-16 of the frame body's whole words: every compute thread takes a chunk of Lq quads, the chunk CRCs are shifted to
 // their place with x^(128 Lq j) mod P and xor-ed (per warp here, across warps by copy_out_frame)
+// shift factor of this thread's chunk; loaded ahead of the barrier in front of crc_frame so its latency is hidden
+__device__ __forceinline__ uint32_t crc_shift_factor(const EncArgs &a, uint32_t body_bytes, int tid) {
+    const uint32_t nq = ((body_bytes >> 2) + 3u) >> 2;
+    const uint32_t Lq = (nq + FRX_ENC_THREADS - 1) / FRX_ENC_THREADS;
+    return (uint32_t)__ldg(&a.crc_xpow[(max(Lq, 1u) - 1) * FRX_ENC_THREADS + (FRX_ENC_THREADS - 1 - tid)]);
+}
 __device__ __forceinline__ void crc_frame(const EncArgs &a, EncSmall &sh, const uint32_t *bits, uint32_t *crc_part, uint32_t body_bytes,
-                                          int tid) {
+                                          int tid, uint32_t shift_factor) {
     const uint32_t nw = body_bytes >> 2;                       // whole words
     const uint32_t nq = (nw + 3u) >> 2;                        // quads; the buffer is zero behind the frame
     const uint32_t Lq = (nq + FRX_ENC_THREADS - 1) / FRX_ENC_THREADS;
@@ -70,7 +76,7 @@ __device__ __forceinline__ void crc_frame(const EncArgs &a, EncSmall &sh, const 
         x = wv.w ^ (c << 16);
         c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
     }
-    if (c) c = frx_gf16_mulmod(c, (uint32_t)__ldg(&a.crc_xpow[(Lq - 1) * FRX_ENC_THREADS + (FRX_ENC_THREADS - 1 - tid)]));
+    if (c) c = frx_gf16_mulmod(c, shift_factor);
     c = __reduce_xor_sync(FULLMASK, c);
     if ((tid & 31) == 0) crc_part[tid >> 5] = c;
 }

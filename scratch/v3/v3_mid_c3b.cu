@@ -195,13 +195,14 @@
             // the PCM buffer is rewritten by the next channel's K1: every reader of it (verbatim / warm-up packing) must be done
             if (ch + 1 < n_channels) compute_sync();
         }  // channels
+        const uint32_t crc_xp = crc_shift_factor(a, (bitpos + 7u) >> 3, tid);
         compute_sync();  // Sa: every subframe is packed
         DBG_PH(14);
 
         // ---- frame footer: CRC-16 of this frame; copy-out of the PREVIOUS frame (its byte offset has had a frame time to arrive) ----
         const uint32_t body_bytes = (bitpos + 7u) >> 3;
         const long long cc0 = DBG_CLK();
-        crc_frame(a, sh, bits, sh.crc_part[buf], body_bytes, tid);
+        crc_frame(a, sh, bits, sh.crc_part[buf], body_bytes, tid, crc_xp);
 
         if (pend) {
             const int pslot = (int)((fseq - 1u) & (FD_SLOTS - 1));
