@@ -34,7 +34,7 @@ struct frx_ctx {
     int sm_count = 148;
     uint64_t launches = 0;
     Buf tiles, prefix, unit_prefix, mmraw, quant, desc, misc, window, xpow, crctab, fsize, foff;
-    Buf dtiles, dprefix, fpos, flen, scan_prefix, scan_tiles;
+    Buf dtiles, dprefix, fpos, flen, stereo, scan_prefix, scan_tiles;
     Buf h_raster, h_bytes, h_small, h_out;  // device staging for the *_host entry points
     int window_len = -1;
     int xpow_L = -1;
@@ -127,7 +127,7 @@ void frx_ctx_destroy(frx_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     Buf *all[] = { &c->tiles, &c->prefix, &c->unit_prefix, &c->mmraw, &c->quant, &c->desc, &c->misc, &c->window, &c->xpow,
-                   &c->crctab, &c->fsize, &c->foff, &c->dtiles, &c->dprefix, &c->fpos, &c->flen, &c->scan_prefix, &c->scan_tiles,
+                   &c->crctab, &c->fsize, &c->foff, &c->dtiles, &c->dprefix, &c->fpos, &c->flen, &c->stereo, &c->scan_prefix, &c->scan_tiles,
                    &c->h_raster, &c->h_bytes, &c->h_small, &c->h_out };
     for (Buf *b : all) if (b->p) cudaFree(b->p);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
@@ -405,6 +405,9 @@ static int decode_core(frx_ctx *c, const uint8_t *bytes_dev, uint64_t n_bytes, c
     ENSURE(c->dprefix, sizeof(uint32_t) * (n_tiles + 1));
     ENSURE(c->fpos, sizeof(uint64_t) * (size_t)(nf + 1));
     ENSURE(c->flen, sizeof(uint32_t) * (size_t)(nf + 1));
+    bool two_ch = false;
+    for (int i = 0; i < n_tiles; i++) two_ch = two_ch || tiles[i].channels == 2;
+    if (two_ch) ENSURE(c->stereo, sizeof(int32_t) * (size_t)nf * (size_t)blocksize);   // scratch rows for stereo decorrelation
     ENSURE(c->scan_prefix, sizeof(uint32_t) * sprefix.size());
     ENSURE(c->scan_tiles, sizeof(int32_t) * (stiles.size() + 1));
     { int rc2 = ensure_crctab(c); if (rc2) return rc2; }
@@ -418,7 +421,7 @@ static int decode_core(frx_ctx *c, const uint8_t *bytes_dev, uint64_t n_bytes, c
     DecArgs a;
     memset(&a, 0, sizeof(a));
     a.bytes = bytes_dev; a.n_bytes = n_bytes; a.tiles = (const frx_dtile *)c->dtiles.p; a.dprefix = (const uint32_t *)c->dprefix.p;
-    a.frame_pos = (uint64_t *)c->fpos.p; a.frame_len = (uint32_t *)c->flen.p; a.frame_size = frame_size_dev; a.crc_tab = (const uint16_t *)c->crctab.p;
+    a.frame_pos = (uint64_t *)c->fpos.p; a.frame_len = (uint32_t *)c->flen.p; a.stereo_scratch = two_ch ? (int32_t *)c->stereo.p : nullptr; a.frame_size = frame_size_dev; a.crc_tab = (const uint16_t *)c->crctab.p;
     a.out = out_dev; a.tile_status = tile_status_dev; a.total_frames = (uint32_t)nf; a.n_tiles = n_tiles; a.blocksize = blocksize;
     a.pcm_mode = pcm_mode; a.verify_crc = c->verify_crc;
     CK(frx_launch_frame_pos(a, st));

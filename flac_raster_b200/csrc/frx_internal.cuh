@@ -43,6 +43,7 @@ struct DecArgs {
     const uint32_t *dprefix;
     uint64_t *frame_pos;
     const uint32_t *frame_size;
+    int32_t *stereo_scratch;        // one blocksize row of int32 per frame, only when two-channel tiles are decoded (else NULL)
     uint32_t *frame_len;            // decoded size of every frame (0: rejected), input of the CRC pass
     const uint16_t *crc_tab;
     void *out;

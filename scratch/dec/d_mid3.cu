@@ -14,6 +14,7 @@ __global__ void __launch_bounds__(32 * DEC_WARPS, 20) frx_decode_kernel(const De
     uint64_t pos = 0, end = 0;
     long long s0 = 0;
     int nsamp = 0, channels = 0, bps = 0;
+    uint32_t stereo = 0;
     FrxDequant dq;
     dq.range_f = 0.f; dq.dmin_f = 0.f;
     BitR br;
@@ -56,12 +57,16 @@ __global__ void __launch_bounds__(32 * DEC_WARPS, 20) frx_decode_kernel(const De
         br.get(8);  // CRC-8 (validated by discovery for foreign files; the CRC-16 pass covers the header too)
         bps = sz_code ? frx_size_code_bps(sz_code) : t.bps;
         channels = ch_code < 8u ? (int)ch_code + 1 : 2;
-        if (nsamp != expect || bps != t.bps || channels != t.channels || ch_code >= 8u) bad = true;
-        if (ch_code >= 8u && ch_code <= 10u) status = FRX_E_UNSUPPORTED;   // stereo decorrelation: see frx_api (unsupported)
+        if (nsamp != expect || bps != t.bps || channels != t.channels || ch_code > 10u) bad = true;
+        if (ch_code >= 8u && !bad) {
+            stereo = ch_code - 7u;                       // 1 left/side, 2 side/right, 3 mid/side
+            if (!a.stereo_scratch || bps >= 32) { bad = true; status = FRX_E_UNSUPPORTED; }
+        }
     }
     int my_n = (live && !bad) ? nsamp : 0;
     const int my_ch = (live && !bad) ? channels : 0;
     const int nmax = __reduce_max_sync(0xFFFFFFFFu, my_n), chmax = __reduce_max_sync(0xFFFFFFFFu, my_ch);
+    const bool any_stereo = __any_sync(0xFFFFFFFFu, stereo != 0u && my_n > 0);
     const int w = my_n ? t.w : (1 << 30);
     const int row0 = my_n ? (int)(s0 / t.w) : 0, col0 = my_n ? (int)(s0 - (long long)row0 * t.w) : 0;
 
@@ -80,7 +85,8 @@ __global__ void __launch_bounds__(32 * DEC_WARPS, 20) frx_decode_kernel(const De
             const uint32_t type = (hdr >> 1) & 0x3Fu;
             if (hdr & 0x80u) bad = true;
             if (hdr & 1u) sf.wasted = (int)br.unary() + 1;
-            sf.sbps = bps - sf.wasted;
+            const int side = ((stereo == 1u && c == 1) || (stereo == 2u && c == 0) || (stereo == 3u && c == 1)) ? 1 : 0;
+            sf.sbps = bps + side - sf.wasted;
             if (sf.sbps <= 0) bad = true;
             if (bad) {}
             else if (type == 0) { sf.type = 0; sf.cval = br.sget(sf.sbps); }
@@ -92,6 +98,7 @@ __global__ void __launch_bounds__(32 * DEC_WARPS, 20) frx_decode_kernel(const De
                 else if (type >= 32) { order = (int)(type & 31u) + 1; lpc = true; }
                 else bad = true;
                 if (order > nsamp) bad = true;
+                if (!bad && order > DEC_MAXORD && stereo) { bad = true; status = FRX_E_UNSUPPORTED; }
                 if (!bad && order > DEC_MAXORD) {
                     // rare long predictors: this lane restores its whole subframe on its own, then idles through the lockstep part
                     int32_t coefl[32], warml[32];
@@ -147,15 +154,21 @@ __global__ void __launch_bounds__(32 * DEC_WARPS, 20) frx_decode_kernel(const De
         const int omax = __reduce_max_sync(0xFFFFFFFFu, (uint32_t)(sf.type == 2 && lane_n ? sf.order : 0));
         const bool anywide = __any_sync(0xFFFFFFFFu, wide && lane_n);
         // ---- K11 back + K12: lockstep restore, dequantise, coalesced stores ----
-        if (omax <= 4) {
-            if (anywide) run_chunks<DT, 4, true>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
-            else run_chunks<DT, 4, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
+        if (any_stereo) {
+            // warps holding decorrelated stereo frames take one general instantiation (16 taps, 64-bit accumulate)
+            const uint32_t st_mode = stereo ? (c == 0 ? 1u : 1u + stereo) : 0u;
+            const unsigned long long scratch_addr = (unsigned long long)(a.stereo_scratch + (size_t)(live ? f : 0u) * (size_t)a.blocksize);
+            run_chunks<DT, 16, true, true>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode,
+                                           st_mode, scratch_addr, (long long)t.out_band_stride * (long long)sizeof(T));
+        } else if (omax <= 4) {
+            if (anywide) run_chunks<DT, 4, true, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
+            else run_chunks<DT, 4, false, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
         } else if (omax <= 8) {
-            if (anywide) run_chunks<DT, 8, true>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
-            else run_chunks<DT, 8, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
+            if (anywide) run_chunks<DT, 8, true, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
+            else run_chunks<DT, 8, false, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
         } else {
-            if (anywide) run_chunks<DT, 16, true>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
-            else run_chunks<DT, 16, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
+            if (anywide) run_chunks<DT, 16, true, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
+            else run_chunks<DT, 16, false, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
         }
         if (bad) my_n = 0;
     }

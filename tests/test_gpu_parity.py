@@ -187,6 +187,46 @@ def test_decode_reference_fixture_dem_spatial(codec):
     assert int(out.abs().max().item()) == 0
 
 
+def test_decode_stereo_decorrelation(codec):
+    """Two-channel streams as libFLAC writes them at level 5: left/side, side/right and mid/side frames (RFC 9639 4.2).
+    The oracle's encoder restates libFLAC's mid-side search; its decoder is the reference for the PCM.  Both the
+    frame-table path and sync discovery are covered, with tile widths that make chunks straddle raster rows."""
+    import torch
+    import oracle
+    from flac_raster_b200 import flacmeta
+    from flac_raster_b200.codec import make_dtiles
+    rng = np.random.default_rng(11)
+    h, w = 96, 200
+    n = h * w
+    base = np.cumsum(rng.integers(-40, 41, n)).astype(np.int64)
+    cases = {
+        "correlated": np.stack([base + rng.integers(-3, 4, n), base + rng.integers(-3, 4, n)], axis=1),
+        "left_quiet": np.stack([rng.integers(-5, 6, n), base], axis=1),
+        "right_quiet": np.stack([base, rng.integers(-5, 6, n)], axis=1),
+    }
+    seen = set()
+    for name, pcm in cases.items():
+        pcm = np.clip(pcm, -30000, 30000).astype(np.int16)
+        data, fsizes = oracle.encode_stream(pcm, 16, level=5)
+        ref, _si, frames = oracle.decode_stream(data)[:3]
+        seen.update(int(f["chan_assign"]) for f in frames)
+        assert np.array_equal(ref.reshape(-1, 2), pcm)
+        hdr = flacmeta.parse_header(data)
+        nfr = (n + 4095) // 4096
+        buf = torch.from_numpy(np.frombuffer(data, dtype=np.uint8).copy()).cuda()
+        for table in (True, False):
+            e = dict(byte_offset=hdr.first_frame_offset, byte_size=len(data) - hdr.first_frame_offset, out_offset=0, out_band_stride=n,
+                     out_row_stride=w, h=h, w=w, channels=2, bps=16, dmin=0.0, dmax=0.0, first_frame=0 if table else None, n_frames=nfr)
+            out = torch.zeros(2 * n, dtype=torch.int16, device="cuda")
+            fs = torch.from_numpy(fsizes.astype(np.int32)).cuda() if table else None
+            status = codec.decode_tiles(buf, make_dtiles([e]), out, out_dtype="int16", pcm_mode="lossless", frame_size=fs)
+            torch.cuda.synchronize()
+            assert int(status[0].item()) == 0, (name, table)
+            got = out.cpu().numpy().reshape(2, n)
+            assert np.array_equal(got[0], pcm[:, 0]) and np.array_equal(got[1], pcm[:, 1]), (name, table)
+    assert seen & {8, 9, 10}, f"the oracle encoder never chose a decorrelated assignment: {seen}"
+
+
 def test_host_entry_points_roundtrip(codec, golden):
     from flac_raster_b200.codec import make_dtiles
     r = golden["in_dem"]
