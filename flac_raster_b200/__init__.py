@@ -7,7 +7,8 @@ the reference's entry points: ``RasterFLACConverter`` (converter.py), ``SpatialF
 format (streaming.py), the CLI commands (cli.py) and a pyFLAC-shaped shim (pyflac_shim.py).
 """
 __version__ = "0.1.0"
-__all__ = ["RasterFLACConverter", "SpatialFLACEncoder", "SpatialFLACStreamer", "SpatialIndex", "SpatialFrame"]
+__all__ = ["RasterFLACConverter", "SpatialFLACEncoder", "SpatialFLACStreamer", "SpatialIndex", "SpatialFrame",
+           "compare_tiffs", "display_comparison_table"]
 
 
 def __getattr__(name):  # lazy: importing the package must not need numpy/torch/libfrx
@@ -17,4 +18,7 @@ def __getattr__(name):  # lazy: importing the package must not need numpy/torch/
     if name in ("SpatialFLACEncoder", "SpatialFLACStreamer", "SpatialIndex", "SpatialFrame"):
         from . import spatial_encoder
         return getattr(spatial_encoder, name)
+    if name in ("compare_tiffs", "display_comparison_table"):
+        from . import compare
+        return getattr(compare, name)
     raise AttributeError(name)

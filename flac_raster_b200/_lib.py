@@ -52,6 +52,11 @@ class EncodeOut(C.Structure):
                 ("frame_offset", C.c_void_p), ("total_bytes", C.c_void_p), ("status", C.c_void_p)]
 
 
+class TiffChunk(C.Structure):
+    _fields_ = [("src_offset", C.c_uint64), ("row0", C.c_int32), ("col0", C.c_int32), ("rows", C.c_int32),
+                ("cols", C.c_int32), ("pitch", C.c_int32), ("band", C.c_int32)]
+
+
 class DTile(C.Structure):
     _fields_ = [("byte_offset", C.c_uint64), ("byte_size", C.c_uint64), ("out_offset", C.c_uint64),
                 ("out_band_stride", C.c_int64), ("out_row_stride", C.c_int64),
@@ -62,7 +67,7 @@ class DTile(C.Structure):
 EXPORTS = ["frx_version", "frx_last_error", "frx_device_count", "frx_ctx_create", "frx_ctx_destroy",
            "frx_encode_bound", "frx_pcm_bps", "frx_encode_tiles", "frx_decode_tiles", "frx_quantize",
            "frx_dequantize", "frx_encode_tiles_host", "frx_decode_tiles_host", "frx_launch_count",
-           "frx_last_kernel_ms"]
+           "frx_last_kernel_ms", "frx_tiff_unpack"]
 
 _lib = None
 
@@ -115,6 +120,9 @@ def lib():
         L.frx_decode_tiles_host.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(DTile), C.c_int32,
                                             C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_uint64,
                                             C.c_void_p]
+        L.frx_tiff_unpack.restype = C.c_int
+        L.frx_tiff_unpack.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(TiffChunk), C.c_int32, C.c_int32,
+                                      C.c_int32, C.POINTER(Raster), C.c_void_p]
         L.frx_launch_count.restype = C.c_uint64
         L.frx_launch_count.argtypes = [C.c_void_p]
         L.frx_last_kernel_ms.restype = C.c_int

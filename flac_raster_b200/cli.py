@@ -1,5 +1,6 @@
-"""``flac-raster`` command line: the four commands on the hot path, same flags as the reference
-(convert cli.py:32-93, query :293-406, create-streaming :620-804, extract-streaming :875-1039).
+"""``flac-raster`` command line, same commands and flags as the reference: the four on the hot path
+(convert cli.py:32-93, query :293-406, create-streaming :620-804, extract-streaming :875-1039) and the
+inspection commands around it (info :96-244, compare :247-290, extract-tile :409-617, spatial-info :807-874).
 Additive flags (``--device/--gpus``, ``--bands``, ``--pcm-mode``) default to the reference's behaviour.
 Errors follow the reference: message on the console, exit code 1.
 """
@@ -145,6 +146,218 @@ def query(
     except Exception as e:  # noqa: BLE001
         logger.exception("Query failed")
         _fail(f"Error during query: {e}")
+
+
+def _suffix_of(path_or_url: str):
+    if path_or_url.startswith(("http://", "https://")):
+        from urllib.parse import urlparse
+        return Path(urlparse(path_or_url).path).suffix.lower(), True
+    return Path(path_or_url).suffix.lower(), False
+
+
+@app.command()
+def info(file_path: str = typer.Argument(..., help="FLAC or TIFF file to inspect (local path or HTTP URL)")):
+    """Display information about a FLAC or TIFF file"""
+    suffix, is_url = _suffix_of(file_path)
+    if not is_url and not Path(file_path).exists():
+        _fail(f"Error: File does not exist: {file_path}")
+    mb = lambda n: f"{n / 1024 / 1024:.2f} MB"
+    if suffix in (".tif", ".tiff"):
+        if is_url:
+            _fail("Error: URL-based TIFF inspection not supported yet")
+        from . import rio
+        with rio.open(file_path) as src:
+            console.print("[cyan]TIFF Information:[/cyan]")
+            for label, value in (("Dimensions", f"{src.width} x {src.height}"), ("Bands", src.count), ("Data type", src.dtypes[0]),
+                                 ("CRS", src.crs), ("Bounds", src.bounds), ("File size", mb(Path(file_path).stat().st_size))):
+                console.print(f"  {label}: {value}")
+        return
+    if suffix != ".flac":
+        _fail(f"Error: Unsupported file format: {suffix}")
+    console.print("[cyan]FLAC Information:[/cyan]")
+    if is_url:   # cli.py:141-165: size from a HEAD request, index through ranged reads only
+        try:
+            import requests
+            from .spatial_encoder import SpatialFLACStreamer
+            console.print(f"  Remote file size: {mb(int(requests.head(file_path).headers.get('content-length', 0)))}")
+            console.print("  [cyan]Loading metadata (lazy loading)...[/cyan]")
+            idx = SpatialFLACStreamer(file_path).spatial_index
+            console.print(f"  Spatial tiles: {len(idx.frames)}")
+            console.print(f"  Total indexed data: {idx.total_bytes:,} bytes")
+            console.print("\n[green]Spatial FLAC Metadata:[/green]")
+            console.print("  Spatial format: Yes")
+            console.print(f"  Total frames/tiles: {len(idx.frames)}")
+            console.print(f"  CRS: {idx.crs}")
+            console.print(f"  Transform: {idx.transform}")
+        except Exception as e:  # noqa: BLE001
+            console.print(f"  [red]Error reading remote FLAC file: {e}[/red]")
+        return
+    size = mb(Path(file_path).stat().st_size)
+    try:   # cli.py:170-180 decodes the whole file to report its shape; here that is one batched GPU decode
+        from .pyflac_shim import FileDecoder
+        audio, rate = FileDecoder(str(file_path)).process()
+        console.print(f"  Sample rate: {rate} Hz")
+        console.print(f"  Channels: {audio.shape[1] if audio.ndim > 1 else 1}")
+        console.print(f"  Audio shape: {audio.shape}")
+        console.print(f"  Data type: {audio.dtype}")
+    except Exception as e:  # noqa: BLE001
+        console.print(f"  [red]Error reading FLAC file: {e}[/red]")
+    console.print(f"  File size: {size}")
+    shown = False
+    try:
+        from . import flacmeta
+        with open(file_path, "rb") as f:
+            hd = flacmeta.parse_header(f.read(1 << 24))
+        if "GEOSPATIAL_CRS" in hd:
+            g = lambda k: hd.get("GEOSPATIAL_" + k, "N/A")
+            console.print("\n[green]Embedded Geospatial Metadata:[/green]")
+            console.print(f"  Original dimensions: {g('WIDTH')} x {g('HEIGHT')}")
+            console.print(f"  Original bands: {g('COUNT')}")
+            console.print(f"  Original dtype: {g('DTYPE')}")
+            console.print(f"  CRS: {g('CRS')}")
+            console.print(f"  Data range: [{g('DATA_MIN')}, {g('DATA_MAX')}]")
+            console.print(f"  Spatial tiling: {'Yes' if str(hd.get('GEOSPATIAL_SPATIAL_TILING', 'false')).lower() == 'true' else 'No'}")
+            raw = hd.get("GEOSPATIAL_BOUNDS")
+            if raw:
+                b = json.loads(raw)
+                b = [b[k] for k in ("left", "bottom", "right", "top")] if isinstance(b, dict) else b
+                console.print(f"  Bounds: ({b[0]:.6f}, {b[1]:.6f}, {b[2]:.6f}, {b[3]:.6f})")
+            shown = True
+    except Exception:  # noqa: BLE001 - fall through to the sidecar like the reference
+        shown = False
+    if not shown:
+        side = Path(file_path).with_suffix(".json")
+        if side.exists():
+            md = json.loads(side.read_text())
+            console.print(f"\n[yellow]Raster Metadata (from {side.name}):[/yellow]")
+            console.print(f"  Original dimensions: {md['width']} x {md['height']}")
+            console.print(f"  Original bands: {md['count']}")
+            console.print(f"  Original dtype: {md['dtype']}")
+            console.print(f"  CRS: {md.get('crs', 'None')}")
+            if md.get("bounds"):
+                b = md["bounds"]
+                console.print(f"  Bounds: ({b['left']}, {b['bottom']}, {b['right']}, {b['top']})")
+            shown = True
+    if not shown:
+        console.print("\n[yellow]No embedded or sidecar metadata found[/yellow]")
+
+
+@app.command()
+def compare(
+    file1: Path = typer.Argument(..., help="First TIFF file"),
+    file2: Path = typer.Argument(..., help="Second TIFF file"),
+    show_bands: bool = typer.Option(True, "--show-bands/--no-bands", help="Show per-band statistics"),
+    export_json: Optional[Path] = typer.Option(None, "--export", "-e", help="Export comparison results to JSON"),
+):
+    """Compare two TIFF files and display statistics"""
+    for f in (file1, file2):
+        if not f.exists():
+            _fail(f"Error: File does not exist: {f}")
+    for f in (file1, file2):
+        if f.suffix.lower() not in (".tif", ".tiff"):
+            _fail(f"Error: {f} is not a TIFF file")
+    try:
+        from .compare import compare_tiffs, display_comparison_table
+        results = compare_tiffs(file1, file2, show_bands)
+        display_comparison_table(results)
+        if export_json:
+            export_json.write_text(json.dumps(results, indent=2))
+            console.print(f"\n[green]SUCCESS: Comparison results exported to: {export_json}[/green]")
+    except Exception as e:  # noqa: BLE001 - cli.py:287-290
+        logger.exception("Comparison failed")
+        _fail(f"Error during comparison: {e}")
+
+
+@app.command("extract-tile")
+def extract_tile(
+    flac_file: str = typer.Argument(..., help="Spatial FLAC file (local path or HTTP URL)"),
+    bbox: str = typer.Option(..., "--bbox", "-b", help="Bounding box as 'xmin,ymin,xmax,ymax'"),
+    output: Path = typer.Option(..., "--output", "-o", help="Output TIFF file path"),
+    device: int = typer.Option(0, "--device", help="CUDA device index"),
+):
+    """Extract a specific tile from spatial FLAC as TIFF file"""
+    is_url = flac_file.startswith(("http://", "https://"))
+    if not is_url and not Path(flac_file).exists():
+        _fail(f"Error: FLAC file does not exist: {flac_file}")
+    box = tuple(_parse_bbox(bbox))
+    try:
+        from . import rio
+        from .spatial_encoder import SpatialFLACStreamer
+        console.print(f"[cyan]Loading spatial index from: {flac_file}[/cyan]")
+        streamer = SpatialFLACStreamer(flac_file if is_url else Path(flac_file))
+        console.print(f"[cyan]Finding tiles for bbox: {bbox}[/cyan]")
+        ranges = streamer.get_byte_ranges_for_bbox(box)
+        if not ranges:
+            _fail(f"Error: No tiles found for bbox {bbox}")
+        console.print(f"[green]Found {len(ranges)} tile(s) for extraction[/green]")
+        # cli.py:474-480, 547-553: the tile written is the FIRST frame whose bbox contains the query box
+        inside = [fr for fr in streamer.spatial_index.frames
+                  if box[0] >= fr.bbox[0] and box[1] >= fr.bbox[1] and box[2] <= fr.bbox[2] and box[3] <= fr.bbox[3]]
+        if not inside:
+            _fail("Error: Could not find exact frame for bbox")
+        target = inside[0]
+        console.print(f"[green]Using frame {target.frame_id} with bbox {target.bbox}[/green]")
+        # the reference decodes the whole file (or trusts stale offsets, SURVEY 0.3); here only this tile's byte range is
+        # fetched and decoded, in one batched GPU call (SpatialFLACStreamer.decode_frames)
+        (_, block), = streamer.decode_frames([target], device)
+        tile = block[0]                                   # band 1, like src.read(1, window=...) (cli.py:571)
+        w = target.window
+        tt = streamer.spatial_index.transform
+        tt = rio.Affine(*list(tt)[:6]) * rio.Affine.translation(w.col_off, w.row_off)
+        console.print(f"[cyan]Writing TIFF to: {output}[/cyan]")
+        with rio.open(output, "w", driver="GTiff", height=tile.shape[0], width=tile.shape[1], count=1, dtype=tile.dtype,
+                      crs=streamer.spatial_index.crs, transform=tt) as dst:
+            dst.write(tile, 1)
+        console.print(f"[green]SUCCESS: Tile extracted to: {output}[/green]")
+        with rio.open(output) as src:
+            console.print("[cyan]Verification:[/cyan]")
+            console.print(f"  Dimensions: {src.width} x {src.height}")
+            console.print(f"  CRS: {src.crs}")
+            console.print(f"  Bounds: {src.bounds}")
+            console.print(f"  Data type: {src.dtypes[0]}")
+            data = src.read(1)
+            console.print(f"  Data range: [{data.min()}, {data.max()}]")
+    except typer.Exit:
+        raise
+    except Exception as e:  # noqa: BLE001 - cli.py:614-617
+        logger.exception("Tile extraction failed")
+        _fail(f"Error during tile extraction: {e}")
+
+
+@app.command("spatial-info")
+def spatial_info(flac_file: str = typer.Argument(..., help="Spatial FLAC file to analyze (local path or HTTP URL)")):
+    """Show spatial index information for FLAC file"""
+    is_url = flac_file.startswith(("http://", "https://"))
+    if not is_url and not Path(flac_file).exists():
+        _fail(f"Error: FLAC file does not exist: {flac_file}")
+    try:
+        from .spatial_encoder import SpatialFLACStreamer
+        idx = SpatialFLACStreamer(flac_file if is_url else Path(flac_file)).spatial_index
+        console.print(f"[green]Spatial FLAC File: {flac_file if is_url else Path(flac_file).name}[/green]")
+        console.print(f"CRS: {idx.crs}")
+        console.print(f"Transform: {idx.transform}")
+        console.print(f"Total frames/tiles: {len(idx.frames)}")
+        table = Table(title="Spatial Frames")
+        for name, style in (("Frame ID", "cyan"), ("Bbox (xmin, ymin, xmax, ymax)", "green"),
+                            ("Window (col, row, width, height)", "yellow"), ("Byte Range", "blue"), ("Size", "magenta")):
+            table.add_column(name, style=style)
+        shown = idx.frames[:10]                            # cli.py:846: the first ten frames, and their bytes only
+        for fr in shown:
+            w = fr.window
+            table.add_row(str(fr.frame_id), "(" + ", ".join(f"{v:.6f}" for v in fr.bbox) + ")",
+                          f"({w.col_off}, {w.row_off}, {w.width}, {w.height})",
+                          f"{fr.byte_offset}-{fr.byte_offset + fr.byte_size - 1}", f"{fr.byte_size:,} bytes")
+        console.print(table)
+        if len(idx.frames) > 10:
+            console.print(f"[yellow]... and {len(idx.frames) - 10} more frames[/yellow]")
+        console.print(f"[bold]Total indexed data: {sum(fr.byte_size for fr in shown):,} bytes[/bold]")
+    except FileNotFoundError as e:
+        _fail(f"Error: Spatial index not found. File may not have spatial tiling enabled: {e}")
+    except typer.Exit:
+        raise
+    except Exception as e:  # noqa: BLE001 - cli.py:871-874
+        logger.exception("Spatial info failed")
+        _fail(f"Error reading spatial info: {e}")
 
 
 @app.command("create-streaming")

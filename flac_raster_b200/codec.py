@@ -31,6 +31,11 @@ def _tdtype(name: str):
             "uint32": torch.uint32, "float32": torch.float32}[name]
 
 
+def np_dtype_of(raster) -> np.dtype:
+    """numpy dtype of a numpy array or a torch tensor"""
+    return raster.dtype if isinstance(raster, np.ndarray) else np.dtype(dtype_name(raster))
+
+
 def dtype_name(t) -> str:
     name = _TORCH_NAMES.get(str(t.dtype)) if not isinstance(t, np.ndarray) else str(t.dtype)
     if name not in L.DTYPE_CODE:
@@ -115,6 +120,54 @@ class Codec:
         e, d = C.c_float(), C.c_float()
         L.check(self._lib.frx_last_kernel_ms(self._h, C.byref(e), C.byref(d)))
         return e.value, d.value
+
+    # ---- raster ingestion ----------------------------------------------------
+    def tiff_unpack(self, file_dev, chunks, dtype: str, bands: int, height: int, width: int, samples_per_pixel: int,
+                    swap_bytes: bool = False, out=None, stream=None):
+        """file_dev: CUDA uint8 tensor holding (a span of) an uncompressed TIFF as it lies on disk.
+        chunks: [(src_offset, row0, col0, rows, cols, pitch, band)] (see include/frx.h frx_tiff_chunk).
+        Returns the band-planar CUDA tensor (bands, height, width) that rasterio's read() would return."""
+        torch = _torch()
+        assert file_dev.is_cuda and file_dev.dtype == torch.uint8 and file_dev.is_contiguous()
+        if out is None:
+            out = torch.empty((bands, height, width), dtype=_tdtype(dtype), device=file_dev.device)
+        assert out.is_cuda and out.is_contiguous() and tuple(out.shape) == (bands, height, width)
+        arr = (L.TiffChunk * max(1, len(chunks)))()
+        for i, ch in enumerate(chunks):
+            (arr[i].src_offset, arr[i].row0, arr[i].col0, arr[i].rows, arr[i].cols, arr[i].pitch, arr[i].band) = (int(x) for x in ch)
+        r = self._raster_desc(out.data_ptr(), dtype, bands, height, width)
+        L.check(self._lib.frx_tiff_unpack(self._h, C.c_void_p(file_dev.data_ptr()), file_dev.numel(), arr, len(chunks),
+                                          int(samples_per_pixel), 1 if swap_bytes else 0, C.byref(r), self._stream(stream)))
+        return out
+
+    def read_tiff(self, src, row0: int = 0, row1: int | None = None):
+        """Rows [row0, row1) of an open raster as a band-planar CUDA tensor.  With the built-in GeoTIFF reader the file
+        bytes go to the device as they are and frx_tiff_unpack rearranges them there; any other dataset object
+        (rasterio) is read on the host and uploaded."""
+        if hasattr(src, "read_device") and src.dtypes[0] in L.DTYPE_CODE:
+            return src.read_device(self, row0, row1)
+        from .rio import Window
+        from .synth import from_numpy
+        row1 = src.height if row1 is None else row1
+        return from_numpy(src.read(window=Window(0, row0, src.width, row1 - row0)), device=f"cuda:{self.device}")
+
+    def encode_tiles_any(self, raster, tiles, level: int = 5, blocksize: int = 4096, sample_rate: int = 44100,
+                         pcm_mode: str = "reference") -> EncodeResult:
+        """encode_tiles_host for a numpy raster; for a CUDA tensor (read_tiff) the device entry point, results copied
+        back as numpy arrays of the same layout."""
+        if isinstance(raster, np.ndarray):
+            return self.encode_tiles_host(raster, tiles, level=level, blocksize=blocksize, sample_rate=sample_rate, pcm_mode=pcm_mode)
+        torch = _torch()
+        res = self.encode_tiles(raster, tiles, level=level, blocksize=blocksize, sample_rate=sample_rate, pcm_mode=pcm_mode)
+        torch.cuda.synchronize(raster.device)
+        if int(res.status.item()) != 0:
+            raise L.FrxError(int(res.status.item()), "encode output buffer too small")
+        total = int(res.total_bytes.item())
+        return EncodeResult(bytes=res.bytes[:total].cpu().numpy(), tile_offset=res.tile_offset.cpu().numpy(),
+                            tile_size=res.tile_size.cpu().numpy(), tile_minmax=res.tile_minmax.cpu().numpy(),
+                            frame_size=res.frame_size.cpu().numpy(), frame_offset=res.frame_offset.cpu().numpy(),
+                            total_bytes=np.array([total], dtype=np.int64), status=np.zeros(1, dtype=np.int32),
+                            frames_per_tile=res.frames_per_tile, bps=res.bps, blocksize=res.blocksize)
 
     # ---- device path -----------------------------------------------------------------------
     def encode_tiles(self, raster, tiles, level: int = 5, blocksize: int = 4096, sample_rate: int = 44100,

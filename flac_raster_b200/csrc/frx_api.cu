@@ -34,7 +34,7 @@ struct frx_ctx {
     int sm_count = 148;
     uint64_t launches = 0;
     Buf tiles, prefix, unit_prefix, mmraw, quant, desc, misc, window, xpow, crctab, fsize, foff;
-    Buf dtiles, dprefix, fpos, flen, stereo, scan_prefix, scan_tiles;
+    Buf dtiles, dprefix, fpos, flen, stereo, scan_prefix, scan_tiles, ing_chunks, ing_prefix;
     Buf h_raster, h_bytes, h_small, h_out;  // device staging for the *_host entry points
     int window_len = -1;
     int xpow_L = -1;
@@ -127,7 +127,7 @@ void frx_ctx_destroy(frx_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     Buf *all[] = { &c->tiles, &c->prefix, &c->unit_prefix, &c->mmraw, &c->quant, &c->desc, &c->misc, &c->window, &c->xpow,
-                   &c->crctab, &c->fsize, &c->foff, &c->dtiles, &c->dprefix, &c->fpos, &c->flen, &c->stereo, &c->scan_prefix, &c->scan_tiles,
+                   &c->crctab, &c->fsize, &c->foff, &c->dtiles, &c->dprefix, &c->fpos, &c->flen, &c->stereo, &c->scan_prefix, &c->scan_tiles, &c->ing_chunks, &c->ing_prefix,
                    &c->h_raster, &c->h_bytes, &c->h_small, &c->h_out };
     for (Buf *b : all) if (b->p) cudaFree(b->p);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
@@ -351,6 +351,49 @@ int frx_encode_tiles(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *t
     CK(frx_launch_tile_index((const uint32_t *)c->prefix.p, frame_size, frame_offset, (const FrxQuant *)c->quant.p, r.dtype, n_tiles,
                              out->tile_offset, out->tile_size, out->tile_minmax, st));
     c->launches += 2;
+    return FRX_OK;
+}
+
+int frx_tiff_unpack(frx_ctx *c, const uint8_t *file_dev, uint64_t n_bytes, const frx_tiff_chunk *chunks, int32_t n_chunks,
+                    int32_t samples_per_pixel, int32_t swap_bytes, const frx_raster *dst_dev, void *stream) {
+    if (!c) return set_err(FRX_E_INVALID, "ctx is NULL");
+    if (!file_dev) return set_err(FRX_E_INVALID, "file_dev is NULL");
+    int rc = check_raster(dst_dev); if (rc) return rc;
+    if (n_chunks < 0 || (n_chunks > 0 && !chunks)) return set_err(FRX_E_INVALID, "bad chunk list");
+    if (samples_per_pixel < 1 || samples_per_pixel > 256) return set_err(FRX_E_INVALID, "samples_per_pixel %d out of range", samples_per_pixel);
+    frx_raster r = normalise_raster(dst_dev);
+    const int esz = frx_dtype_size(r.dtype);
+    const int seg_px = frx_ingest_seg_pixels(esz, samples_per_pixel);
+    std::vector<uint32_t> prefix((size_t)n_chunks + 1);
+    uint64_t nu = 0;
+    for (int i = 0; i < n_chunks; i++) {
+        const frx_tiff_chunk &k = chunks[i];
+        prefix[i] = (uint32_t)nu;
+        if (k.rows < 0 || k.cols < 0 || k.row0 < 0 || k.col0 < 0 || k.pitch < k.cols || (int64_t)k.row0 + k.rows > r.height ||
+            (int64_t)k.col0 + k.cols > r.width || k.band >= r.bands || (k.band < 0 && samples_per_pixel > r.bands))
+            return set_err(FRX_E_INVALID, "chunk %d lies outside the raster", i);
+        if (k.rows == 0 || k.cols == 0) continue;
+        const uint64_t nb = k.band < 0 ? (uint64_t)samples_per_pixel : 1u;
+        const uint64_t span = ((uint64_t)(k.rows - 1) * (uint64_t)k.pitch + (uint64_t)k.cols) * nb * (uint64_t)esz;
+        if (k.src_offset > n_bytes || span > n_bytes - k.src_offset) return set_err(FRX_E_INVALID, "chunk %d reads past the file image", i);
+        nu += (uint64_t)k.rows * (((uint64_t)k.cols + seg_px - 1) / seg_px);
+        if (nu > 0x7FFFFFF0ull) return set_err(FRX_E_UNSUPPORTED, "too many row segments in one call");
+    }
+    prefix[n_chunks] = (uint32_t)nu;
+    if (!nu) return FRX_OK;
+    CK(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    ENSURE(c->ing_chunks, sizeof(frx_tiff_chunk) * (size_t)n_chunks);
+    ENSURE(c->ing_prefix, sizeof(uint32_t) * ((size_t)n_chunks + 1));
+    CK(cudaMemcpyAsync(c->ing_chunks.p, chunks, sizeof(frx_tiff_chunk) * (size_t)n_chunks, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(c->ing_prefix.p, prefix.data(), sizeof(uint32_t) * ((size_t)n_chunks + 1), cudaMemcpyHostToDevice, st));
+    CK(cudaStreamSynchronize(st));   // `prefix` dies at return
+    CK(cudaEventRecord(c->ev[0], st));
+    CK(frx_launch_tiff_unpack(file_dev, (const frx_tiff_chunk *)c->ing_chunks.p, (const uint32_t *)c->ing_prefix.p, n_chunks, (uint32_t)nu,
+                              samples_per_pixel, swap_bytes ? 1 : 0, r, st));
+    CK(cudaEventRecord(c->ev[1], st));
+    c->enc_timed = true;   // frx_last_kernel_ms reports this kernel until the next encode call
+    c->launches += 1;
     return FRX_OK;
 }
 

@@ -1782,6 +1782,10 @@ cudaError_t frx_launch_encode(const EncArgs &a, int dtype, int sm_count, cudaStr
     (void)dtype;
     const bool wide = a.bps > 16;
     const int hist = a.max_lpc_order <= 4 ? 4 : (a.max_lpc_order <= 8 ? 8 : 12);
+#ifdef FRX_DEV_L5   // development builds (scratch/dev/build.sh): only the level-5 instantiations, 20 s instead of 5 min
+    if (hist != 8) return cudaErrorInvalidValue;
+    return wide ? launch_encode_t<true, 8>(a, sm_count, st) : launch_encode_t<false, 8>(a, sm_count, st);
+#else
     if (wide) {
         if (hist == 4) return launch_encode_t<true, 4>(a, sm_count, st);
         if (hist == 8) return launch_encode_t<true, 8>(a, sm_count, st);
@@ -1790,6 +1794,7 @@ cudaError_t frx_launch_encode(const EncArgs &a, int dtype, int sm_count, cudaStr
     if (hist == 4) return launch_encode_t<false, 4>(a, sm_count, st);
     if (hist == 8) return launch_encode_t<false, 8>(a, sm_count, st);
     return launch_encode_t<false, 12>(a, sm_count, st);
+#endif
 }
 
 cudaError_t frx_launch_tile_index(const uint32_t *frame_prefix, const uint32_t *frame_size, const uint64_t *frame_offset,

@@ -72,4 +72,6 @@ cudaError_t frx_launch_discover(const DecArgs &a, const uint32_t *unit_prefix, c
 cudaError_t frx_launch_decode(const DecArgs &a, int out_dtype, cudaStream_t st);
 cudaError_t frx_launch_dequantize(const int32_t *pcm, int h, int w, int channels, int bps, int out_dtype, int mode, double dmin,
                                   double dmax, void *out, cudaStream_t st);
-
+int frx_ingest_seg_pixels(int esz, int spp);
+cudaError_t frx_launch_tiff_unpack(const uint8_t *src, const frx_tiff_chunk *chunks_dev, const uint32_t *unit_prefix_dev, int n_chunks,
+                                   uint32_t total_units, int spp, int swap, const frx_raster &dst, cudaStream_t st);

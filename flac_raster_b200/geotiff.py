@@ -280,6 +280,61 @@ class DatasetReader:
                             out[c, a - r0: b - r0, i * tw: i * tw + cw] = blk[a - j * th: b - j * th, :cw]
         return out
 
+    # ---- device ingestion (include/frx.h frx_tiff_unpack) ---------------------------------
+    def chunk_table(self, row0: int = 0, row1: int | None = None):
+        """Strips/tiles intersecting rows [row0, row1) as frx_tiff_chunk tuples
+        (file_offset, dst_row0, dst_col0, rows, cols, pitch, band), destination rows relative to `row0`.
+        The same geometry _read_rows() walks on the host."""
+        H, W, C = self.height, self.width, self.count
+        row1 = H if row1 is None else row1
+        esz = self._dtype.itemsize
+        out = []
+        if not self._tiled:
+            rps = self._rps
+            spp = (H + rps - 1) // rps
+            for s in range(row0 // rps, (row1 - 1) // rps + 1):
+                sr0 = s * rps
+                a, b = max(row0, sr0), min(row1, sr0 + min(rps, H - sr0))
+                if self._planar == 1:
+                    out.append((self._offsets[s] + (a - sr0) * W * C * esz, a - row0, 0, b - a, W, W, -1))
+                else:
+                    for c in range(C):
+                        out.append((self._offsets[c * spp + s] + (a - sr0) * W * esz, a - row0, 0, b - a, W, W, c))
+        else:
+            tw, th = self._tw, self._th
+            tx, ty = (W + tw - 1) // tw, (H + th - 1) // th
+            for j in range(row0 // th, (row1 - 1) // th + 1):
+                a, b = max(row0, j * th), min(row1, min((j + 1) * th, H))
+                for i in range(tx):
+                    cw = min(tw, W - i * tw)
+                    if self._planar == 1:
+                        out.append((self._offsets[j * tx + i] + (a - j * th) * tw * C * esz, a - row0, i * tw, b - a, cw, tw, -1))
+                    else:
+                        for c in range(C):
+                            out.append((self._offsets[c * tx * ty + j * tx + i] + (a - j * th) * tw * esz, a - row0, i * tw,
+                                        b - a, cw, tw, c))
+        return out
+
+    def read_device(self, codec, row0: int = 0, row1: int | None = None):
+        """read() without the host-side rearrangement: the byte span of the file that holds the chunks goes to the
+        device as it is (pinned staging buffer, one H2D copy) and frx_tiff_unpack lays it out as (count, rows, width)."""
+        import torch
+        row1 = self.height if row1 is None else row1
+        chunks = self.chunk_table(row0, row1)
+        esz = self._dtype.itemsize
+        lo = min(c[0] for c in chunks)
+        hi = max(c[0] + ((c[3] - 1) * c[5] + c[4]) * (self.count if c[6] < 0 else 1) * esz for c in chunks)
+        lo_al = lo & ~255                       # keeps the file's own alignment phase on the device
+        host = torch.empty(hi - lo_al, dtype=torch.uint8, pin_memory=True)
+        self._f.seek(lo_al)
+        got = self._f.readinto(memoryview(host.numpy()))
+        if got != hi - lo_al:
+            raise ValueError(f"{self.name}: truncated TIFF (wanted {hi - lo_al} bytes at {lo_al}, got {got})")
+        dev = host.to(f"cuda:{codec.device}", non_blocking=True)
+        rel = [(c[0] - lo_al,) + tuple(c[1:]) for c in chunks]
+        swap = (self._bo == ">") != (__import__("sys").byteorder == "big")
+        return codec.tiff_unpack(dev, rel, self.dtypes[0], self.count, row1 - row0, self.width, self.count, swap_bytes=swap)
+
     def read(self, indexes=None, window=None):
         if window is None:
             r0, r1, c0, c1 = 0, self.height, 0, self.width

@@ -20,7 +20,7 @@ from typing import Dict, Iterable, List, Optional, Sequence, Tuple
 import numpy as np
 
 from . import flacmeta, rio
-from .codec import make_dtiles, pcm_bps
+from .codec import make_dtiles, np_dtype_of, pcm_bps
 from .converter import (BLOCKSIZE, decode_stream, get_codec, metadata_comments, metadata_from_comments, raster_metadata,
                         sample_rate_for, stream_header)
 from .geotiff import BoundingBox
@@ -77,12 +77,12 @@ def encode_streaming_tiles(raster: np.ndarray, tiles, crs, transform, nodata=Non
     # the per-tile tiff_to_flac call sees a (nch, th, tw) array: sample rate keyed on nch*th (always 44100 for th<=1024)
     rates = {sample_rate_for(nch, t[2]) for t in tiles}
     blobs: List[Optional[bytes]] = [None] * len(tiles)
-    dtype = raster.dtype
+    dtype = np_dtype_of(raster)
     for sr in sorted(rates):
         sel = [i for i, t in enumerate(tiles) if sample_rate_for(nch, t[2]) == sr]
         units = [(tiles[i][0] - row_base, tiles[i][1], tiles[i][2], tiles[i][3], 0, nch) for i in sel]
-        res = get_codec(device).encode_tiles_host(raster, units, level=STREAMING_LEVEL, blocksize=BLOCKSIZE, sample_rate=sr,
-                                                  pcm_mode=pcm_mode)
+        res = get_codec(device).encode_tiles_any(raster, units, level=STREAMING_LEVEL, blocksize=BLOCKSIZE, sample_rate=sr,
+                                                 pcm_mode=pcm_mode)
         data = res.bytes[:int(res.total_bytes[0])]
         fpos = 0
         for k, i in enumerate(sel):
@@ -126,14 +126,20 @@ def create_streaming(input_file, output_file, tile_size: int = 1024, bands: str 
     """create-streaming (cli.py:620-804).  `devices`: GPUs of this process; tile ranges are sharded over them
     (one libfrx context each) and merged on the host."""
     with rio.open(input_file) as src:
-        raster = src.read()
         crs, transform, nodata = src.crs, src.transform, getattr(src, "nodata", None)
         width, height = src.width, src.height
-    tiles = calculate_tiles(height, width, tile_size)
-    shards = []
-    for k, dev in enumerate(devices):
-        lo, hi = shard_range(len(tiles), len(devices), k)
-        shards.append(encode_streaming_tiles(raster, tiles[lo:hi], crs, transform, nodata, bands, pcm_mode, dev))
+        tiles = calculate_tiles(height, width, tile_size)
+        shards = []
+        for k, dev in enumerate(devices):
+            lo, hi = shard_range(len(tiles), len(devices), k)
+            if lo == hi:
+                shards.append(([], []))
+                continue
+            # each device ingests only the raster rows its tile range touches (file bytes -> device -> frx_tiff_unpack)
+            r0 = min(t[0] for t in tiles[lo:hi])
+            r1 = max(t[0] + t[2] for t in tiles[lo:hi])
+            raster = get_codec(dev).read_tiff(src, r0, r1)
+            shards.append(encode_streaming_tiles(raster, tiles[lo:hi], crs, transform, nodata, bands, pcm_mode, dev, row_base=r0))
     chunks, offsets, sizes = merge_shards(shards)
     index = build_index(crs, transform, width, height, tile_size, tiles, offsets, sizes)
     write_streaming_file(output_file, index, chunks)

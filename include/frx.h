@@ -157,6 +157,30 @@ int frx_decode_tiles_host(frx_ctx *ctx, const uint8_t *bytes_host, uint64_t n_by
                           int32_t n_tiles, const uint32_t *frame_size_host, int32_t blocksize, int32_t out_dtype,
                           int32_t pcm_mode, void *out_host, uint64_t out_elems, int32_t *tile_status_host);
 
+/* ---- raster ingestion -------------------------------------------------- */
+/* One strip or tile of an uncompressed TIFF: where its bytes sit in the staged file image and
+ * which rectangle of the raster they fill.  Chunk rows hold `pitch` pixels (the tile width; the
+ * image width for strips), of which the first `cols` are stored; `rows`/`cols` are already
+ * clipped to the image (TIFF pads edge tiles).  band < 0: pixel-interleaved chunk holding every
+ * band (PlanarConfiguration 1); band >= 0: one band's chunk (PlanarConfiguration 2).           */
+typedef struct frx_tiff_chunk {
+    uint64_t src_offset;      /* byte offset of the chunk inside `file_dev` */
+    int32_t row0, col0, rows, cols;
+    int32_t pitch;
+    int32_t band;
+} frx_tiff_chunk;
+
+/* File bytes (device) -> band-planar raster (device): de-interleave, un-tile, clip, byte-swap.
+ * replaces: rasterio's read() into a (bands,h,w) ndarray followed by the H2D copy of that array
+ * (converter.py:137-141, spatial_encoder.py:154-183, cli.py:699) -- the file image is copied to
+ * the device once, as it lies on disk, and this kernel does the rearrangement there.
+ * `dst_dev` describes the destination raster (dtype, bands, geometry; `data` is written).
+ * samples_per_pixel: bands stored per pixel in interleaved chunks.  swap_bytes: file byte order
+ * differs from the device's (big-endian "MM" files).                                            */
+int frx_tiff_unpack(frx_ctx *ctx, const uint8_t *file_dev, uint64_t n_bytes, const frx_tiff_chunk *chunks_host,
+                    int32_t n_chunks, int32_t samples_per_pixel, int32_t swap_bytes, const frx_raster *dst_dev,
+                    void *stream);
+
 /* ---- instrumentation ---------------------------------------------------------------------- */
 /* Kernel launches issued by this context since creation (bench.py reports it). */
 uint64_t frx_launch_count(const frx_ctx *ctx);

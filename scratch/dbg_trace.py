@@ -1,11 +1,14 @@
 import sys, ctypes, torch, numpy as np
 sys.path.insert(0, '/root/repo')
+from pathlib import Path
+from flac_raster_b200 import _lib
+_lib.LIB_PATH = Path('/root/repo/scratch/dev/libfrx_%s.so' % sys.argv[2])
+lib = ctypes.CDLL(str(_lib.LIB_PATH))
 from flac_raster_b200 import synth
 from flac_raster_b200.codec import Codec, tile_grid
-lib = ctypes.CDLL('/root/repo/flac_raster_b200/libfrx.so')
 lib.frx_debug_trace.argtypes = [ctypes.c_void_p]
 codec = Codec(0)
-H = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
+H = int(sys.argv[1])
 r = synth.dem_f32(H, H, seed=1)
 tiles = tile_grid(H, H, 1024, 0, 1)
 res = codec.encode_tiles(r, tiles)
@@ -33,10 +36,10 @@ print('   mean %.1f p50 %.1f p99 %.1f max %.1f' % (lag.mean(), np.percentile(lag
 # blocking distance
 m = blk > 0
 d = (np.arange(nf)[m] - blk[m])
-print('blocked look-backs', m.sum(), 'distance mean %.1f p50 %.1f p99 %.1f max %d' % (d.mean(), np.percentile(d, 50), np.percentile(d, 99), d.max()))
+if m.sum(): print('blocked look-backs', m.sum(), 'distance mean %.1f p50 %.1f p99 %.1f max %d' % (d.mean(), np.percentile(d, 50), np.percentile(d, 99), d.max()))
 # the frames that were waited on: reserve->A of those vs all
 bl = np.unique(blk[m])
-print('blockers', len(bl), 'their reserve->A mean %.1f vs all %.1f' % (((A - res_t)[bl] / 1e3).mean(), ((A - res_t) / 1e3).mean()))
+if m.sum(): print('blockers', len(bl), 'their reserve->A mean %.1f vs all %.1f' % (((A - res_t)[bl] / 1e3).mean(), ((A - res_t) / 1e3).mean()))
 # per-CTA frame counts
 c = np.bincount(cta.astype(int), minlength=296)
 print('frames per CTA min %d max %d' % (c.min(), c.max()))

@@ -36,6 +36,22 @@ def _lossless_inv(pcm, dtype):
 class OracleCodec:
     device = 0
 
+    def read_tiff(self, src, row0=0, row1=None):
+        """Codec.read_tiff through the numpy restatement of frx_tiff_unpack (oracle/tiff_unpack.py)."""
+        from oracle import tiff_unpack
+        row1 = src.height if row1 is None else row1
+        if not hasattr(src, "chunk_table"):
+            from flac_raster_b200.rio import Window
+            return src.read(window=Window(0, row0, src.width, row1 - row0))
+        chunks = src.chunk_table(row0, row1)
+        with open(src.name, "rb") as f:
+            data = f.read()
+        return tiff_unpack.unpack(data, chunks, src.dtypes[0], src.count, row1 - row0, src.width, src.count,
+                                  swap_bytes=(src._bo == ">"))
+
+    def encode_tiles_any(self, raster, tiles, **kw):
+        return self.encode_tiles_host(raster, tiles, **kw)
+
     def encode_tiles_host(self, raster, tiles, level=5, blocksize=4096, sample_rate=44100, pcm_mode="reference", out=None):
         chunks, fsizes, mm, toff, tsz, fpt = [], [], [], [], [], []
         pos = 0

@@ -45,3 +45,68 @@ def check_encode_against_oracle(raster_np, tiles, res_bytes, tile_offset, tile_s
     if check_size:
         assert ours_total <= size_margin * oracle_total + 16, (ours_total, oracle_total)
     return ours_total, oracle_total
+
+
+def write_tiff_variant(path, arr, tile=None, rows_per_strip=None, planar=1, big_endian=False, pad=0):
+    """Test-only TIFF writer for the layouts the ingestion kernel must handle: `arr` (C,H,W); strips (rows_per_strip) or
+    tiles (tile=(tw,th), multiples of 16, edge tiles zero-padded); PlanarConfiguration 1 or 2; either byte order;
+    `pad` stray bytes in front of every chunk (odd values make the chunks unaligned)."""
+    import struct
+    arr = np.asarray(arr)
+    C, H, W = arr.shape
+    bo = ">" if big_endian else "<"
+    dt = arr.dtype.newbyteorder(bo)
+    chunks = []
+    if tile:
+        tw, th = tile
+        tx, ty = (W + tw - 1) // tw, (H + th - 1) // th
+        padded = np.zeros((C, ty * th, tx * tw), dtype=arr.dtype)
+        padded[:, :H, :W] = arr
+        planes = [None] if planar == 1 else list(range(C))
+        for c in planes:
+            for j in range(ty):
+                for i in range(tx):
+                    blk = padded[:, j * th:(j + 1) * th, i * tw:(i + 1) * tw]
+                    chunks.append(blk.transpose(1, 2, 0).astype(dt).tobytes() if c is None else blk[c].astype(dt).tobytes())
+    else:
+        rps = rows_per_strip or H
+        planes = [None] if planar == 1 else list(range(C))
+        for c in planes:
+            for r0 in range(0, H, rps):
+                blk = arr[:, r0:r0 + rps, :]
+                chunks.append(blk.transpose(1, 2, 0).astype(dt).tobytes() if c is None else blk[c].astype(dt).tobytes())
+    body = bytearray(b"\0" * 8)
+    offsets, counts = [], []
+    for ch in chunks:
+        body += b"\xAA" * pad
+        offsets.append(len(body))
+        counts.append(len(ch))
+        body += ch
+    if len(body) & 1:
+        body += b"\0"
+    sf = {"u": 1, "i": 2, "f": 3}[arr.dtype.kind]
+    entries = [(256, 4, [W]), (257, 4, [H]), (258, 3, [arr.dtype.itemsize * 8] * C), (259, 3, [1]), (262, 3, [1]),
+               (277, 3, [C]), (284, 3, [planar]), (339, 3, [sf] * C)]
+    if tile:
+        entries += [(322, 4, [tile[0]]), (323, 4, [tile[1]]), (324, 4, offsets), (325, 4, counts)]
+    else:
+        entries += [(273, 4, offsets), (278, 4, [rows_per_strip or H]), (279, 4, counts)]
+    entries.sort()
+    extra = bytearray()
+    ifd_off = len(body)
+    extra_base = ifd_off + 2 + 12 * len(entries) + 4
+    ifd = struct.pack(bo + "H", len(entries))
+    for tag, typ, vals in entries:
+        fmt = {3: "H", 4: "I"}[typ]
+        raw = struct.pack(bo + fmt * len(vals), *vals)
+        if len(raw) <= 4:
+            ifd += struct.pack(bo + "HHI", tag, typ, len(vals)) + raw.ljust(4, b"\0")
+        else:
+            ifd += struct.pack(bo + "HHII", tag, typ, len(vals), extra_base + len(extra))
+            extra += raw
+            if len(extra) & 1:
+                extra += b"\0"
+    ifd += struct.pack(bo + "I", 0)
+    body[0:8] = (b"MM" if big_endian else b"II") + struct.pack(bo + "HI", 42, ifd_off)
+    with open(path, "wb") as f:
+        f.write(bytes(body) + ifd + bytes(extra))

@@ -310,3 +310,28 @@ def cli_commands(tmp):
     assert r.exit_code == 0 and (tmp / "d.bin").read_bytes() == (tmp / "sp.flac").read_bytes()
     assert run(app, ["query", str(tmp / "sp.flac"), "--bbox", "1,2,3"]).exit_code == 1
     assert run(app, ["query", str(tmp / "rgb.flac"), "--bbox", "0,0,1,1"]).exit_code == 1   # no spatial index
+    # inspection commands around the path (cli.py:96-290, 409-617, 807-874)
+    r = run(app, ["info", str(tmp / "rgb.tif")])
+    assert r.exit_code == 0 and "Dimensions: 256 x 256" in r.output and "Bands: 3" in r.output, r.output
+    r = run(app, ["info", str(tmp / "rgb.flac")])
+    assert r.exit_code == 0 and "Channels: 3" in r.output and "(65536, 3)" in r.output and "Original dtype: uint8" in r.output, r.output
+    assert run(app, ["info", str(tmp / "nope.flac")]).exit_code == 1
+    assert run(app, ["info", str(tmp / "x.txt")]).exit_code == 1
+    r = run(app, ["compare", str(tmp / "rgb.tif"), str(tmp / "back.tif"), "-e", str(tmp / "cmp.json")])
+    assert r.exit_code == 0, r.output
+    cj = json.loads((tmp / "cmp.json").read_text())
+    assert cj["shape_match"] and cj["arrays_equal"] and cj["max_difference"] == 0.0 and len(cj["bands"]) == 3
+    assert run(app, ["compare", str(tmp / "rgb.tif"), str(tmp / "rgb.flac")]).exit_code == 1       # not a TIFF, cli.py:267-273
+    r = run(app, ["spatial-info", str(tmp / "sp.flac")])
+    assert r.exit_code == 0 and "Total frames/tiles: 4" in r.output, r.output
+    assert run(app, ["spatial-info", str(tmp / "rgb.flac")]).exit_code == 1                          # no spatial index
+    from flac_raster_b200.spatial_encoder import SpatialFLACStreamer
+    fr = SpatialFLACStreamer(tmp / "sp.flac").spatial_index.frames[1]
+    x0, y0, x1, y1 = fr.bbox
+    inner = f"{x0 + (x1 - x0) * 0.25},{y0 + (y1 - y0) * 0.25},{x0 + (x1 - x0) * 0.5},{y0 + (y1 - y0) * 0.5}"
+    r = run(app, ["extract-tile", str(tmp / "sp.flac"), "--bbox", inner, "-o", str(tmp / "tile1.tif")])
+    assert r.exit_code == 0 and "Using frame 1" in r.output, r.output
+    w = fr.window
+    want = read_tif(GOLDEN / "sample_rgb.tif")[0][0, w.row_off:w.row_off + w.height, w.col_off:w.col_off + w.width]
+    assert np.array_equal(read_tif(tmp / "tile1.tif")[0][0], want)            # --spatial defaults to the lossless mapping
+    assert run(app, ["extract-tile", str(tmp / "sp.flac"), "--bbox", "1000,1000,1001,1001", "-o", str(tmp / "t.tif")]).exit_code == 1
