@@ -19,7 +19,7 @@ import numpy as np
 
 from . import _lib as L
 from . import flacmeta, rio
-from .codec import Codec, make_dtiles, pcm_bps
+from .codec import Codec, make_dtiles, np_dtype_of, pcm_bps
 
 BLOCKSIZE = 4096  # converter.py:205
 ENCODER_TAG = "FLAC-Raster v0.1.0"  # converter.py:330 (kept so reference readers see the same key set)
@@ -123,17 +123,19 @@ def stream_header(channels: int, bps: int, sample_rate: int, total_samples: int,
     return flacmeta.build_header(si, comments, padding=padding, applications=apps)
 
 
-def encode_array(data: np.ndarray, compression_level: int = 5, sample_rate: Optional[int] = None,
+def encode_array(data, compression_level: int = 5, sample_rate: Optional[int] = None,
                  pcm_mode: str = "reference", device: int = 0):
-    """(bands,h,w) host array -> (frame bytes, frame_sizes, data_min, data_max, bps): the hot-path part of
+    """(bands,h,w) host array or CUDA tensor (Codec.read_tiff) -> (frame bytes, frame_sizes, data_min, data_max, bps): the hot-path part of
     tiff_to_flac (converter.py:152-153, 180-216) as ONE libfrx call (whole raster = one stream)."""
     if data.ndim == 2:
         data = data[None]
     bands, h, w = data.shape
     codec = get_codec(device)
     sr = sample_rate or sample_rate_for(bands, h)
-    res = codec.encode_tiles_host(np.ascontiguousarray(data), [(0, 0, h, w, 0, bands)], level=compression_level,
-                                  blocksize=BLOCKSIZE, sample_rate=sr, pcm_mode=pcm_mode)
+    if isinstance(data, np.ndarray):
+        data = np.ascontiguousarray(data)
+    res = codec.encode_tiles_any(data, [(0, 0, h, w, 0, bands)], level=compression_level, blocksize=BLOCKSIZE, sample_rate=sr,
+                                 pcm_mode=pcm_mode)
     total = int(res.total_bytes[0])
     return (res.bytes[:total], res.frame_size.astype(np.int64), float(res.tile_minmax[0, 0]), float(res.tile_minmax[0, 1]),
             res.bps)
@@ -194,13 +196,14 @@ class RasterFLACConverter:
             return SpatialFLACEncoder(tile_size=tile_size, device=self.device).encode_spatial_flac(
                 tiff_path, flac_path, compression_level)
         with rio.open(tiff_path) as src:
-            data = src.read()
+            data = get_codec(self.device).read_tiff(src)      # file bytes -> device -> frx_tiff_unpack (no host rearrangement)
             meta = dict(src.meta)
             bounds, crs, transform = src.bounds, src.crs, src.transform
         count, h, w = data.shape
-        sample_rate, label = self._calculate_audio_params(data, data.dtype)
-        self.logger.info(f"Raster {w}x{h}, {count} band(s), {data.dtype}; sample rate {sample_rate} Hz, label {label}-bit, "
-                         f"effective {pcm_bps(data.dtype.name, self.pcm_mode)}-bit")
+        dtype = np_dtype_of(data)
+        sample_rate, label = self._calculate_audio_params(data, dtype)
+        self.logger.info(f"Raster {w}x{h}, {count} band(s), {dtype}; sample rate {sample_rate} Hz, label {label}-bit, "
+                         f"effective {pcm_bps(dtype.name, self.pcm_mode)}-bit")
         frames, frame_sizes, dmin, dmax, bps = encode_array(data, compression_level, sample_rate, self.pcm_mode, self.device)
         md = raster_metadata(meta["width"], meta["height"], meta["count"], meta["dtype"], crs, transform, bounds, dmin, dmax,
                              meta.get("nodata"), meta.get("driver", "GTiff"))

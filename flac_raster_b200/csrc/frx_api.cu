@@ -360,10 +360,9 @@ int frx_tiff_unpack(frx_ctx *c, const uint8_t *file_dev, uint64_t n_bytes, const
     if (!file_dev) return set_err(FRX_E_INVALID, "file_dev is NULL");
     int rc = check_raster(dst_dev); if (rc) return rc;
     if (n_chunks < 0 || (n_chunks > 0 && !chunks)) return set_err(FRX_E_INVALID, "bad chunk list");
-    if (samples_per_pixel < 1 || samples_per_pixel > 256) return set_err(FRX_E_INVALID, "samples_per_pixel %d out of range", samples_per_pixel);
+    if (samples_per_pixel < 1 || samples_per_pixel > 64) return set_err(FRX_E_INVALID, "samples_per_pixel %d out of range", samples_per_pixel);
     frx_raster r = normalise_raster(dst_dev);
     const int esz = frx_dtype_size(r.dtype);
-    const int seg_px = frx_ingest_seg_pixels(esz, samples_per_pixel);
     std::vector<uint32_t> prefix((size_t)n_chunks + 1);
     uint64_t nu = 0;
     for (int i = 0; i < n_chunks; i++) {
@@ -376,7 +375,7 @@ int frx_tiff_unpack(frx_ctx *c, const uint8_t *file_dev, uint64_t n_bytes, const
         const uint64_t nb = k.band < 0 ? (uint64_t)samples_per_pixel : 1u;
         const uint64_t span = ((uint64_t)(k.rows - 1) * (uint64_t)k.pitch + (uint64_t)k.cols) * nb * (uint64_t)esz;
         if (k.src_offset > n_bytes || span > n_bytes - k.src_offset) return set_err(FRX_E_INVALID, "chunk %d reads past the file image", i);
-        nu += (uint64_t)k.rows * (((uint64_t)k.cols + seg_px - 1) / seg_px);
+        { int rpu, spx; nu += frx_ingest_plan(esz, (int)nb, k.rows, k.cols, k.pitch, &rpu, &spx); }
         if (nu > 0x7FFFFFF0ull) return set_err(FRX_E_UNSUPPORTED, "too many row segments in one call");
     }
     prefix[n_chunks] = (uint32_t)nu;

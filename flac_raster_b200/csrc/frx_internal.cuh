@@ -72,6 +72,21 @@ cudaError_t frx_launch_discover(const DecArgs &a, const uint32_t *unit_prefix, c
 cudaError_t frx_launch_decode(const DecArgs &a, int out_dtype, cudaStream_t st);
 cudaError_t frx_launch_dequantize(const int32_t *pcm, int h, int w, int channels, int bps, int out_dtype, int mode, double dmin,
                                   double dmax, void *out, cudaStream_t st);
-int frx_ingest_seg_pixels(int esz, int spp);
+// frx_tiff_unpack work split, shared by the host (unit counts) and the kernel: a chunk whose rows are short is cut into runs of
+// whole rows (one contiguous source block per unit), a chunk with long rows into row segments of seg_px pixels.
+#define FRX_ING_SEG_BYTES 16384
+__host__ __device__ inline unsigned long long frx_ingest_plan(int esz, int nb, int rows, int cols, int pitch, int *rows_per_unit, int *seg_px) {
+    const long long row_bytes = (long long)pitch * nb * esz;
+    if (row_bytes * 2 <= FRX_ING_SEG_BYTES) {
+        *rows_per_unit = (int)(FRX_ING_SEG_BYTES / row_bytes);
+        *seg_px = pitch;
+        return ((unsigned long long)rows + *rows_per_unit - 1) / *rows_per_unit;
+    }
+    int px = (FRX_ING_SEG_BYTES / (esz * nb)) & ~15;      // multiples of 16 pixels keep segment starts 16-byte aligned
+    if (px < 16) px = 16;
+    *rows_per_unit = 1;
+    *seg_px = px;
+    return (unsigned long long)rows * (((unsigned long long)cols + px - 1) / px);
+}
 cudaError_t frx_launch_tiff_unpack(const uint8_t *src, const frx_tiff_chunk *chunks_dev, const uint32_t *unit_prefix_dev, int n_chunks,
                                    uint32_t total_units, int spp, int swap, const frx_raster &dst, cudaStream_t st);

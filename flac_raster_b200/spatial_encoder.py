@@ -23,7 +23,7 @@ from typing import Dict, List, Optional, Tuple
 import numpy as np
 
 from . import flacmeta, rio
-from .codec import make_dtiles, pcm_bps
+from .codec import make_dtiles, np_dtype_of, pcm_bps
 from .converter import BLOCKSIZE, ENCODER_TAG, get_codec, stream_header
 from .rio import CRS, Affine, Window
 
@@ -128,8 +128,10 @@ class SpatialFLACEncoder:
             from ._lib import E_UNSUPPORTED, FrxUnsupported
             raise FrxUnsupported(E_UNSUPPORTED, f"{count} channels: FLAC allows at most {MAX_CHANNELS} per stream")
         units = [(r, c, h, w, b0, nb) for (r, c, h, w) in tiles for (b0, nb) in groups]
-        res = get_codec(self.device).encode_tiles_host(np.ascontiguousarray(raster), units, level=compression_level,
-                                                       blocksize=BLOCKSIZE, sample_rate=44100, pcm_mode=self.pcm_mode)
+        if isinstance(raster, np.ndarray):
+            raster = np.ascontiguousarray(raster)
+        res = get_codec(self.device).encode_tiles_any(raster, units, level=compression_level, blocksize=BLOCKSIZE,
+                                                      sample_rate=44100, pcm_mode=self.pcm_mode)
         return tiles, groups, res
 
     def encode_spatial_flac(self, tiff_path: Path, flac_path: Path, compression_level: int = 5,
@@ -138,7 +140,7 @@ class SpatialFLACEncoder:
         tiff_path, flac_path = Path(tiff_path), Path(flac_path)
         self.logger.info(f"Starting spatial FLAC encoding: {tiff_path} -> {flac_path}")
         with rio.open(tiff_path) as src:
-            raster = src.read()
+            raster = get_codec(self.device).read_tiff(src)    # file bytes -> device -> frx_tiff_unpack
             transform, crs = src.transform, src.crs
         count, height, width = raster.shape
         tiles, groups, res = self.encode_array(raster, compression_level)
@@ -182,7 +184,7 @@ class SpatialFLACEncoder:
         for _ in range(8):
             frames = build(reserve)
             index = SpatialIndex(frames, crs, transform)
-            comments = self._comments(index, crs, transform, height, width, count, raster.dtype, dmin, dmax, len(tiles))
+            comments = self._comments(index, crs, transform, height, width, count, np_dtype_of(raster), dmin, dmax, len(tiles))
             h0 = stream_header(groups[0][1], bps, 44100, u0[2] * u0[3], fs0, comments)
             need = len(h0) - base_len
             if reserve >= need and (reserve == need or reserve - need >= 4):
