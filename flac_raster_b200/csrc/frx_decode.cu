@@ -121,7 +121,7 @@ __global__ void frx_frame_discover_kernel(DecArgs a, const uint32_t *unit_prefix
 // owns a ring of DEC_RING words in shared memory (column `lane` of ring[word][lane], conflict-free), topped up for all
 // lanes at once at every chunk boundary with aligned 16-byte loads; the 64-bit window is fed from the ring.
 // ------------------------------------------------------------------------------------------
-#define DEC_RING 32
+#define DEC_RING 24          // words per lane (3 KB per warp): with 32 the CTA's shared memory capped the SM at 20 warps
 __device__ __noinline__ uint4 dec_load16_clamped(const uint8_t *np, const uint8_t *lo, const uint8_t *hi) {
     uint32_t w[4];
     for (int k = 0; k < 4; k++) {
@@ -256,7 +256,7 @@ __device__ __forceinline__ int ilog2_u32(uint32_t v) { return 31 - __clz((int)v)
 // go through a shared-memory transpose so that every global store is one full line of one frame's raster row, instead of
 // 32 lanes scattering single elements 16 KB apart.
 // ------------------------------------------------------------------------------------------
-#define DEC_WARPS 1     // one warp per CTA: a frame takes milliseconds on its lane, so the grid must fit one wave; small CTAs pack the SMs evenly
+#define DEC_WARPS 1     // one warp per CTA: a frame takes milliseconds on its lane, so the grid must fit one wave (22 CTAs per SM: C2's 3 052 warps need 20.6); small CTAs pack the SMs evenly
 #define DEC_MAXORD 16
 struct DecWarpSmem {
     uint32_t ring[DEC_RING][32];     // input rings, one column per lane
@@ -466,7 +466,7 @@ __device__ __forceinline__ void run_chunks(BitR &br, SubF &sf, int32_t *coef, in
 }
 
 template <int DT>
-__global__ void __launch_bounds__(32 * DEC_WARPS, 20) frx_decode_kernel(const DecArgs a) {
+__global__ void __launch_bounds__(32 * DEC_WARPS, 22) frx_decode_kernel(const DecArgs a) {
     typedef typename FrxElem<DT>::T T;
     __shared__ DecWarpSmem wsm[DEC_WARPS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -747,19 +747,35 @@ cudaError_t frx_launch_crc_check(const DecArgs &a, const uint16_t *xpow, int sm_
     return cudaGetLastError();
 }
 
+// A frame takes milliseconds on its lane, so every frame should start in the first wave: the kernel is built for 22
+// one-warp CTAs per SM (80 registers, 9 KB of shared memory each) and asks for the largest shared-memory carve-out,
+// without which the driver keeps part of the 227 KB as L1 and fewer CTAs fit.
+template <int DT>
+static cudaError_t launch_decode_t(const DecArgs &a, unsigned grid, cudaStream_t st) {
+    static bool configured[64] = { false };   // per device: function attributes belong to the device's context
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || !configured[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(frx_decode_kernel<DT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        if (e != cudaSuccess) return e;
+        if (dev >= 0 && dev < 64) configured[dev] = true;
+    }
+    frx_decode_kernel<DT><<<grid, 32 * DEC_WARPS, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
 cudaError_t frx_launch_decode(const DecArgs &a, int out_dtype, cudaStream_t st) {
     unsigned grid = (a.total_frames + 32u * DEC_WARPS - 1u) / (32u * DEC_WARPS);
     if (!grid) return cudaSuccess;
     switch (out_dtype) {
-        case FRX_U8: frx_decode_kernel<FRX_U8><<<grid, 32 * DEC_WARPS, 0, st>>>(a); break;
-        case FRX_I16: frx_decode_kernel<FRX_I16><<<grid, 32 * DEC_WARPS, 0, st>>>(a); break;
-        case FRX_U16: frx_decode_kernel<FRX_U16><<<grid, 32 * DEC_WARPS, 0, st>>>(a); break;
-        case FRX_I32: frx_decode_kernel<FRX_I32><<<grid, 32 * DEC_WARPS, 0, st>>>(a); break;
-        case FRX_U32: frx_decode_kernel<FRX_U32><<<grid, 32 * DEC_WARPS, 0, st>>>(a); break;
-        case FRX_F32: frx_decode_kernel<FRX_F32><<<grid, 32 * DEC_WARPS, 0, st>>>(a); break;
+        case FRX_U8: return launch_decode_t<FRX_U8>(a, grid, st);
+        case FRX_I16: return launch_decode_t<FRX_I16>(a, grid, st);
+        case FRX_U16: return launch_decode_t<FRX_U16>(a, grid, st);
+        case FRX_I32: return launch_decode_t<FRX_I32>(a, grid, st);
+        case FRX_U32: return launch_decode_t<FRX_U32>(a, grid, st);
+        case FRX_F32: return launch_decode_t<FRX_F32>(a, grid, st);
         default: return cudaErrorInvalidValue;
     }
-    return cudaGetLastError();
 }
 
 cudaError_t frx_launch_dequantize(const int32_t *pcm, int h, int w, int channels, int bps, int out_dtype, int mode, double dmin,
