@@ -473,7 +473,7 @@ static int decode_core(frx_ctx *c, const uint8_t *bytes_dev, uint64_t n_bytes, c
         c->launches += 1;
     }
     CK(cudaEventRecord(c->ev[2], st));
-    CK(frx_launch_decode(a, out_dtype, st));
+    CK(frx_launch_decode(a, out_dtype, c->sm_count, st));
     if (c->verify_crc) { CK(frx_launch_crc_check(a, (const uint16_t *)c->xpow.p, c->sm_count, st)); c->launches += 1; }
     CK(cudaEventRecord(c->ev[3], st));
     c->dec_timed = true;

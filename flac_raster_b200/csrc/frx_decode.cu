@@ -13,24 +13,11 @@
 // (config 5: 10^4 queries x 256 frames).
 #include "frx_internal.cuh"
 
+#define FRX_DEC_CTAS 20
+#define FRX_DEC_RINGW 32
+#define FRX_DEC_NS dec_w20
+#include "frx_decode_frame.cuh"
 
-#define FRX_NOPOS 0xFFFFFFFFFFFFFFFFull
-
-__device__ __forceinline__ int frx_size_code_bps(uint32_t c) {
-    switch (c) { case 1: return 8; case 2: return 12; case 4: return 16; case 5: return 20; case 6: return 24; case 7: return 32; case 0: return 0; }
-    return -1;
-}
-
-__device__ __forceinline__ int dec_find_tile(const uint32_t *prefix, int n, uint32_t f) {
-    int lo = 0, hi = n;
-    while (hi - lo > 1) {
-        int mid = (lo + hi) >> 1;
-        if (prefix[mid] <= f) lo = mid; else hi = mid;
-    }
-    return lo;
-}
-
-// ---- K9a: one warp per tile, chunked shuffle scan over the tile's frame sizes ----
 __global__ void frx_frame_pos_kernel(DecArgs a) {
     int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= a.n_tiles) return;
@@ -115,538 +102,6 @@ __global__ void frx_frame_discover_kernel(DecArgs a, const uint32_t *unit_prefix
     }
 }
 
-// ------------------------------------------------------------------------------------------
-// bit reader.  A lane walks its own frame, but a warp runs its 32 lanes in lockstep: if every lane fetched from global
-// memory whenever its own window ran dry, the warp would stall on 32 unrelated misses per few samples.  So each lane
-// owns a ring of DEC_RING words in shared memory (column `lane` of ring[word][lane], conflict-free), topped up for all
-// lanes at once at every chunk boundary with aligned 16-byte loads; the 64-bit window is fed from the ring.
-// ------------------------------------------------------------------------------------------
-#define DEC_RING 24          // words per lane (3 KB per warp): with 32 the CTA's shared memory capped the SM at 20 warps
-__device__ __noinline__ uint4 dec_load16_clamped(const uint8_t *np, const uint8_t *lo, const uint8_t *hi) {
-    uint32_t w[4];
-    for (int k = 0; k < 4; k++) {
-        w[k] = 0;
-        for (int i = 0; i < 4; i++) {
-            const uint8_t *p = np + 4 * k + i;
-            const uint32_t b = (p >= lo && p < hi) ? (uint32_t)__ldg(p) : 0u;
-            w[k] |= b << (8 * i);
-        }
-    }
-    return make_uint4(w[0], w[1], w[2], w[3]);
-}
-struct BitR {
-    const uint8_t *lo, *hi;     // valid byte range of the buffer
-    const uint8_t *np;          // next 16-byte aligned block to fetch
-    uint32_t *ring;             // &ring[0][lane]; word i of the stream sits at ring[(i % DEC_RING) * 32]
-    uint32_t rd, wr;            // words consumed / fetched
-    uint64_t acc;               // left aligned
-    int cnt;                    // valid bits in acc
-    uint32_t start_bits;        // stream position of the frame's first bit, in bits from ring word 0
-    __device__ __forceinline__ uint4 load16() const {
-        if (np >= lo && np + 16 <= hi) return __ldg(reinterpret_cast<const uint4 *>(np));
-        return dec_load16_clamped(np, lo, hi);
-    }
-    __device__ __forceinline__ void push16(const uint4 v) {
-        ring[((wr + 0u) % DEC_RING) * 32] = frx_bswap32(v.x);
-        ring[((wr + 1u) % DEC_RING) * 32] = frx_bswap32(v.y);
-        ring[((wr + 2u) % DEC_RING) * 32] = frx_bswap32(v.z);
-        ring[((wr + 3u) % DEC_RING) * 32] = frx_bswap32(v.w);
-        wr += 4; np += 16;
-    }
-    // chunk boundary: every lane fills its ring (uniform trip count so the loads of a round issue together)
-    __device__ __forceinline__ void topup(bool want) {
-        for (;;) {
-            const uint32_t free_blocks = want ? (DEC_RING - (wr - rd)) >> 2 : 0u;
-            if (!__any_sync(0xFFFFFFFFu, free_blocks != 0u)) break;
-            uint4 v[4];
-#pragma unroll
-            for (int k = 0; k < 4; k++) if ((uint32_t)k < free_blocks) { const uint8_t *p = np; np += 16 * k; v[k] = load16(); np = p; }
-#pragma unroll
-            for (int k = 0; k < 4; k++) if ((uint32_t)k < free_blocks) push16(v[k]);
-            if (!__any_sync(0xFFFFFFFFu, free_blocks > 4u)) break;
-        }
-    }
-    __device__ __forceinline__ uint32_t pop() {
-        if (rd == wr) push16(load16());      // ring ran dry inside a chunk (more than ~4 bytes per sample): fetch on demand
-        const uint32_t w = ring[(rd % DEC_RING) * 32];
-        rd++;
-        return w;
-    }
-    __device__ __forceinline__ void init(const uint8_t *base, uint64_t n_bytes, uint64_t pos, uint32_t *ring_col, bool live) {
-        lo = base; hi = base + n_bytes;
-        const uintptr_t addr = (uintptr_t)(base + pos);
-        const int lead = (int)(addr & 15u);
-        np = (const uint8_t *)(addr - lead);
-        ring = ring_col; rd = 0; wr = 0; start_bits = (uint32_t)lead * 8u; acc = 0; cnt = 0;
-        topup(live);
-        if (live) {
-            rd = (uint32_t)(lead >> 2);
-            const int lb = 8 * (lead & 3);
-            acc = (uint64_t)pop() << (32 + lb);
-            cnt = 32 - lb;
-            refill();
-        }
-    }
-    // bits consumed since init: everything popped, minus what still sits in the window
-    __device__ __forceinline__ uint32_t consumed() const { return rd * 32u - (uint32_t)cnt - start_bits; }
-    __device__ __forceinline__ void refill() {
-        if (cnt <= 32) {
-            acc |= (uint64_t)pop() << (32 - cnt);
-            cnt += 32;
-        }
-    }
-    // n in 0..32
-    __device__ __forceinline__ uint32_t get(int n) {
-        refill();
-        const uint32_t v = n ? (uint32_t)(acc >> (64 - n)) : 0u;
-        acc <<= n;
-        cnt -= n;
-        return v;
-    }
-    __device__ __forceinline__ int32_t sget(int n) {  // signed, n in 1..32
-        const uint32_t v = get(n);
-        return n >= 32 ? (int32_t)v : ((int32_t)(v << (32 - n)) >> (32 - n));
-    }
-    __device__ __forceinline__ uint32_t unary() {
-        uint32_t z = 0;
-        for (;;) {
-            refill();
-            if (acc == 0) {
-                z += (uint32_t)cnt; cnt = 0;
-                if (np > hi + 256) return z;  // ran off the buffer: malformed
-                continue;
-            }
-            const int lz = __clzll((long long)acc);
-            z += (uint32_t)lz;
-            acc = lz == 63 ? 0ull : (acc << (lz + 1));  // a set bit exists within cnt bits, so lz < cnt
-            cnt -= lz + 1;
-            return z;
-        }
-    }
-};
-
-struct RiceState {
-    uint32_t k;        // current parameter
-    uint32_t left;     // samples left in the current partition
-    int pbits;         // 4 or 5
-    uint32_t esc;      // 15 or 31
-    int rawbits;       // >= 0: escape partition with this many raw bits
-    uint32_t psize;    // samples per partition
-};
-
-__device__ __forceinline__ int32_t rice_next(BitR &br, RiceState &rs) {
-    if (rs.left == 0) {
-        rs.k = br.get(rs.pbits);
-        rs.left = rs.psize;
-        rs.rawbits = -1;
-        if (rs.k == rs.esc) rs.rawbits = (int)br.get(5);
-    }
-    rs.left--;
-    if (rs.rawbits >= 0) return rs.rawbits ? br.sget(rs.rawbits) : 0;
-    const uint32_t z = br.unary();
-    const uint32_t u = (z << rs.k) | br.get((int)rs.k);
-    return (int32_t)(u >> 1) ^ -(int32_t)(u & 1u);
-}
-
-__device__ __forceinline__ int ilog2_u32(uint32_t v) { return 31 - __clz((int)v); }
-
-// ------------------------------------------------------------------------------------------
-// K10-K12.  One lane owns one frame (Rice decoding and the predictor recurrence are serial inside a subframe; the
-// parallelism is across frames), but a warp walks its 32 frames in lockstep, 32 samples at a time: the restored samples
-// go through a shared-memory transpose so that every global store is one full line of one frame's raster row, instead of
-// 32 lanes scattering single elements 16 KB apart.
-// ------------------------------------------------------------------------------------------
-#define DEC_WARPS 1     // one warp per CTA: a frame takes milliseconds on its lane, so the grid must fit one wave (22 CTAs per SM: C2's 3 052 warps need 20.6); small CTAs pack the SMs evenly
-#define DEC_MAXORD 16
-struct DecWarpSmem {
-    uint32_t ring[DEC_RING][32];     // input rings, one column per lane
-    uint32_t stage[32][33];          // [frame lane][sample in chunk], padded
-    unsigned long long ptr[32];      // byte address of the first sample of the lane's chunk
-    long long rstride[32];           // row stride of the lane's tile, elements
-    uint32_t room[32];               // elements left in the raster row at the chunk start
-    uint32_t cnt[32];                // valid samples of the lane in this chunk
-    uint32_t wid[32];                // tile width
-    // stereo decorrelation only (frames with channel assignment 8..10)
-    uint32_t mode[32];               // 0 plain, 1 first channel -> raw PCM into the scratch row, 2/3/4 second channel of L/S, S/R, M/S
-    unsigned long long ptr2[32];     // byte address of the chunk in the frame's scratch row
-    long long bstride[32];           // bytes between the two band planes of the output
-    float dq_range[32], dq_min[32];
-    int32_t bpsv[32];
-};
-
-struct SubF {
-    int type;          // 0 constant, 1 verbatim, 2 predictive, 3 nothing to do
-    int order, shift, wasted, sbps;
-    int32_t cval;
-    RiceState rs;
-};
-
-// generic order (17..32): history ring in local memory, scattered stores (libFLAC never emits these below -l 17)
-template <int DT>
-__device__ __noinline__ void restore_subframe_generic(BitR &br, RiceState &rs, typename FrxElem<DT>::T *base, long long row_stride, int w,
-                                                      long long px, const int32_t *coef, int order, int shift, const int32_t *warm, int nsamp,
-                                                      int wasted, int bps, const FrxDequant &dq, int mode) {
-    typedef typename FrxElem<DT>::T T;
-    int row = (int)(px / w), col = (int)(px - (long long)row * w);
-    int32_t h[32];
-    for (int i = 0; i < 32; i++) h[i] = i < order ? warm[i] : 0;
-    for (int n = 0; n < nsamp; n++) {
-        int32_t v;
-        if (n < order) v = warm[n];
-        else {
-            const int32_t r = rice_next(br, rs);
-            long long acc = 0;
-            for (int j = 0; j < order; j++) acc += (long long)coef[j] * (long long)h[(n - 1 - j) & 31];
-            v = (int32_t)((long long)r + (acc >> shift));
-            h[n & 31] = v;
-        }
-        base[(long long)row * row_stride + col] = frx_dequant<DT>((int32_t)((uint32_t)v << wasted), bps, dq, mode);
-        if (++col == w) { col = 0; row++; }
-    }
-}
-
-template <int DT>
-__device__ __forceinline__ uint32_t dec_pack(typename FrxElem<DT>::T v) {
-    typedef typename FrxElem<DT>::T T;
-    if (sizeof(T) == 4) { uint32_t u; memcpy(&u, &v, 4); return u; }
-    if (sizeof(T) == 2) { uint16_t u; memcpy(&u, &v, 2); return u; }
-    uint8_t u; memcpy(&u, &v, 1); return u;
-}
-template <int DT>
-__device__ __forceinline__ void dec_store(unsigned long long addr, uint32_t bits) {
-    typedef typename FrxElem<DT>::T T;
-    if (sizeof(T) == 4) *reinterpret_cast<uint32_t *>(addr) = bits;
-    else if (sizeof(T) == 2) *reinterpret_cast<uint16_t *>(addr) = (uint16_t)bits;
-    else *reinterpret_cast<uint8_t *>(addr) = (uint8_t)bits;
-}
-
-// the warp writes the 32x32 staged samples: iteration j stores frame j's chunk, lane = sample
-template <int DT>
-__device__ __forceinline__ void flush_chunk(DecWarpSmem &ws, int lane) {
-    typedef typename FrxElem<DT>::T T;
-    __syncwarp();
-#pragma unroll 4
-    for (int j = 0; j < 32; j++) {
-        const uint32_t cnt = ws.cnt[j];
-        if ((uint32_t)lane < cnt) {
-            const uint32_t room = ws.room[j];
-            unsigned long long addr = ws.ptr[j];
-            if ((uint32_t)lane < room) addr += (unsigned long long)lane * sizeof(T);
-            else {
-                // the chunk runs over the end of the raster row (tile widths that are not multiples of 32)
-                const uint32_t w = ws.wid[j];
-                const uint32_t k = (uint32_t)lane - room;
-                const uint32_t down = 1u + k / w, colx = k - (k / w) * w;
-                addr = addr - (unsigned long long)(w - room) * sizeof(T) + ((unsigned long long)((long long)down * ws.rstride[j]) + colx) * sizeof(T);
-            }
-            dec_store<DT>(addr, ws.stage[j][lane]);
-        }
-    }
-    __syncwarp();
-}
-
-// write-out for warps that hold frames with stereo decorrelation (libFLAC tries left/side, side/right and mid/side for
-// exactly two channels; RFC 9639 section 4.2): the first channel's PCM is parked in a scratch row, the second channel's
-// chunk is combined with it here, lane = sample, so both band planes are still written as full lines.
-template <int DT>
-__device__ __forceinline__ void flush_chunk_stereo(DecWarpSmem &ws, int lane, int pcm_mode) {
-    typedef typename FrxElem<DT>::T T;
-    __syncwarp();
-    for (int j = 0; j < 32; j++) {
-        const uint32_t cnt = ws.cnt[j];
-        if ((uint32_t)lane >= cnt) continue;
-        const uint32_t mode = ws.mode[j];
-        const uint32_t bits = ws.stage[j][lane];
-        if (mode == 1u) { *reinterpret_cast<uint32_t *>(ws.ptr2[j] + 4ull * (unsigned)lane) = bits; continue; }
-        const uint32_t room = ws.room[j];
-        unsigned long long addr = ws.ptr[j];
-        if ((uint32_t)lane < room) addr += (unsigned long long)lane * sizeof(T);
-        else {
-            const uint32_t w = ws.wid[j];
-            const uint32_t k = (uint32_t)lane - room;
-            const uint32_t down = 1u + k / w, colx = k - (k / w) * w;
-            addr = addr - (unsigned long long)(w - room) * sizeof(T) + ((unsigned long long)((long long)down * ws.rstride[j]) + colx) * sizeof(T);
-        }
-        if (mode == 0u) { dec_store<DT>(addr, bits); continue; }
-        const int32_t s1 = (int32_t)bits;
-        const int32_t s0 = *reinterpret_cast<const int32_t *>(ws.ptr2[j] + 4ull * (unsigned)lane);
-        int32_t L, R;
-        if (mode == 2u) { L = s0; R = s0 - s1; }                 // left, side
-        else if (mode == 3u) { R = s1; L = s0 + s1; }            // side, right
-        else { const int32_t mid = (int32_t)(((uint32_t)s0 << 1) | ((uint32_t)s1 & 1u)); L = (mid + s1) >> 1; R = (mid - s1) >> 1; }
-        FrxDequant dq;
-        dq.range_f = ws.dq_range[j]; dq.dmin_f = ws.dq_min[j];
-        const int bps = ws.bpsv[j];
-        dec_store<DT>(addr - (unsigned long long)ws.bstride[j], dec_pack<DT>(frx_dequant<DT>(L, bps, dq, pcm_mode)));
-        dec_store<DT>(addr, dec_pack<DT>(frx_dequant<DT>(R, bps, dq, pcm_mode)));
-    }
-    __syncwarp();
-}
-
-// lockstep restore of one channel for the 32 frames of a warp; ORD = history length (multiple of 4 dividing 32),
-// WIDE = 64-bit accumulate.  Uniform control flow: lanes whose subframe is not predictive ride along predicated.
-template <int DT, int ORD, bool WIDE, bool ST>
-__device__ __forceinline__ void run_chunks(BitR &br, SubF &sf, int32_t *coef, int32_t *h, DecWarpSmem &ws, int lane, int my_n, int nmax,
-                                           unsigned long long base_addr, long long row_stride, int w, int row, int col, int bps,
-                                           const FrxDequant &dq, int mode, uint32_t st_mode = 0u, unsigned long long scratch_addr = 0ull,
-                                           long long band_stride_bytes = 0) {
-    typedef typename FrxElem<DT>::T T;
-    for (int n0 = 0; n0 < nmax; n0 += 32) {
-        br.topup(n0 < my_n);
-        // where this lane's chunk lands
-        ws.ptr[lane] = base_addr + (unsigned long long)((long long)row * row_stride + col) * sizeof(T);
-        ws.rstride[lane] = row_stride;
-        ws.room[lane] = (uint32_t)(w - col);
-        ws.wid[lane] = (uint32_t)w;
-        ws.cnt[lane] = (uint32_t)min(32, max(0, my_n - n0));
-        if (ST) {
-            ws.mode[lane] = st_mode; ws.ptr2[lane] = scratch_addr + 4ull * (unsigned)n0; ws.bstride[lane] = band_stride_bytes;
-            ws.dq_range[lane] = dq.range_f; ws.dq_min[lane] = dq.dmin_f; ws.bpsv[lane] = bps;
-        }
-        // a chunk past the warm-up in which every lane restores 32 predicted samples needs no per-sample predicates
-        const bool steady = !ST && __all_sync(0xFFFFFFFFu, sf.type == 2 && n0 >= 32 && n0 + 32 <= my_n);
-        if (steady) {
-            for (int mb = 0; mb < 32; mb += ORD) {
-#pragma unroll
-                for (int mi = 0; mi < ORD; mi++) {
-                    const int32_t r = rice_next(br, sf.rs);
-                    int32_t v;
-                    if (WIDE) {
-                        long long acc = 0;
-#pragma unroll
-                        for (int j = 0; j < ORD; j++) acc += (long long)coef[j] * (long long)h[(mi - 1 - j + 2 * ORD) % ORD];
-                        v = (int32_t)((long long)r + (acc >> sf.shift));
-                    } else {
-                        int32_t acc = 0;
-#pragma unroll
-                        for (int j = 0; j < ORD; j++) acc += coef[j] * h[(mi - 1 - j + 2 * ORD) % ORD];
-                        v = r + (acc >> sf.shift);
-                    }
-                    h[mi] = v;
-                    ws.stage[lane][mb + mi] = dec_pack<DT>(frx_dequant<DT>((int32_t)((uint32_t)v << sf.wasted), bps, dq, mode));
-                }
-            }
-        } else {
-        for (int mb = 0; mb < 32; mb += ORD) {
-#pragma unroll
-                for (int mi = 0; mi < ORD; mi++) {
-                    const int n = n0 + mb + mi;
-                    int32_t v = sf.cval;
-                    if (n < my_n) {
-                        if (sf.type == 2) {
-                            if (n >= sf.order) {
-                                const int32_t r = rice_next(br, sf.rs);
-                                if (WIDE) {
-                                    long long acc = 0;
-#pragma unroll
-                                    for (int j = 0; j < ORD; j++) acc += (long long)coef[j] * (long long)h[(mi - 1 - j + 2 * ORD) % ORD];
-                                    v = (int32_t)((long long)r + (acc >> sf.shift));
-                                } else {
-                                    int32_t acc = 0;
-#pragma unroll
-                                    for (int j = 0; j < ORD; j++) acc += coef[j] * h[(mi - 1 - j + 2 * ORD) % ORD];
-                                    v = r + (acc >> sf.shift);
-                                }
-                                h[mi] = v;
-                            } else v = h[mi];   // warm-up sample (n < order <= ORD, so n == mi)
-                        } else if (sf.type == 1) v = br.sget(sf.sbps);
-                    }
-                    {
-                        const uint32_t rawv = (uint32_t)v << sf.wasted;
-                        const uint32_t outv = dec_pack<DT>(frx_dequant<DT>((int32_t)rawv, bps, dq, mode));
-                        ws.stage[lane][mb + mi] = (ST && st_mode) ? rawv : outv;
-                    }
-                }
-            }
-        }
-        if (ST) flush_chunk_stereo<DT>(ws, lane, mode); else flush_chunk<DT>(ws, lane);
-        col += 32;
-        while (col >= w) { col -= w; row++; }
-    }
-}
-
-template <int DT>
-__global__ void __launch_bounds__(32 * DEC_WARPS, 22) frx_decode_kernel(const DecArgs a) {
-    typedef typename FrxElem<DT>::T T;
-    __shared__ DecWarpSmem wsm[DEC_WARPS];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    DecWarpSmem &ws = wsm[warp];
-    const uint32_t f = (blockIdx.x * DEC_WARPS + warp) * 32u + (uint32_t)lane;
-    bool bad = false, live = f < a.total_frames;
-    int status = FRX_E_BITSTREAM;
-    int ti = 0;
-    frx_dtile t;
-    memset(&t, 0, sizeof(t));
-    uint32_t fj = 0;
-    uint64_t pos = 0, end = 0;
-    long long s0 = 0;
-    int nsamp = 0, channels = 0, bps = 0;
-    uint32_t stereo = 0;
-    FrxDequant dq;
-    dq.range_f = 0.f; dq.dmin_f = 0.f;
-    BitR br;
-    if (live) {
-        ti = dec_find_tile(a.dprefix, a.n_tiles, f);
-        t = a.tiles[ti];
-        fj = f - a.dprefix[ti];
-        pos = a.frame_pos[f];
-        if (pos == FRX_NOPOS || pos < t.byte_offset || pos >= t.byte_offset + t.byte_size) bad = true;
-        end = t.byte_offset + t.byte_size;
-        if (!bad && fj + 1 < t.n_frames) {
-            const uint64_t nx = a.frame_pos[f + 1];
-            if (nx != FRX_NOPOS && nx > pos && nx <= end) end = nx;
-        }
-        dq.range_f = (float)(t.dmax - t.dmin);
-        dq.dmin_f = (float)t.dmin;
-    }
-    br.init(a.bytes, a.n_bytes, pos, &ws.ring[0][lane], live && !bad);   // warp-wide: fills the input rings
-    if (live && !bad) {
-        const long long tile_n = (long long)t.h * t.w;
-        s0 = (long long)fj * a.blocksize;
-        const int expect = (int)min((long long)a.blocksize, tile_n - s0);
-        // ---- K10: frame header ----
-        const uint32_t sync = br.get(16);
-        if (sync != 0xFFF8u) bad = true;
-        const uint32_t bs_code = br.get(4), sr_code = br.get(4), ch_code = br.get(4), sz_code = br.get(3);
-        br.get(1);
-        {
-            const uint32_t x = br.get(8);
-            const int extra = !(x & 0x80u) ? 0 : (x & 0xE0u) == 0xC0u ? 1 : (x & 0xF0u) == 0xE0u ? 2 : (x & 0xF8u) == 0xF0u ? 3 : (x & 0xFCu) == 0xF8u ? 4 : 5;
-            for (int e = 0; e < extra; e++) br.get(8);
-        }
-        if (bs_code == 1) nsamp = 192;
-        else if (bs_code >= 2 && bs_code <= 5) nsamp = 576 << (bs_code - 2);
-        else if (bs_code == 6) nsamp = (int)br.get(8) + 1;
-        else if (bs_code == 7) nsamp = (int)br.get(16) + 1;
-        else if (bs_code >= 8) nsamp = 256 << (bs_code - 8);
-        else { nsamp = 0; bad = true; }
-        if (sr_code == 12u) br.get(8); else if (sr_code == 13u || sr_code == 14u) br.get(16);
-        br.get(8);  // CRC-8 (validated by discovery for foreign files; the CRC-16 pass covers the header too)
-        bps = sz_code ? frx_size_code_bps(sz_code) : t.bps;
-        channels = ch_code < 8u ? (int)ch_code + 1 : 2;
-        if (nsamp != expect || bps != t.bps || channels != t.channels || ch_code > 10u) bad = true;
-        if (ch_code >= 8u && !bad) {
-            stereo = ch_code - 7u;                       // 1 left/side, 2 side/right, 3 mid/side
-            if (!a.stereo_scratch || bps >= 32) { bad = true; status = FRX_E_UNSUPPORTED; }
-        }
-    }
-    int my_n = (live && !bad) ? nsamp : 0;
-    const int my_ch = (live && !bad) ? channels : 0;
-    const int nmax = __reduce_max_sync(0xFFFFFFFFu, my_n), chmax = __reduce_max_sync(0xFFFFFFFFu, my_ch);
-    const bool any_stereo = __any_sync(0xFFFFFFFFu, stereo != 0u && my_n > 0);
-    const int w = my_n ? t.w : (1 << 30);
-    const int row0 = my_n ? (int)(s0 / t.w) : 0, col0 = my_n ? (int)(s0 - (long long)row0 * t.w) : 0;
-
-    for (int c = 0; c < chmax; c++) {
-        SubF sf;
-        sf.type = 3; sf.order = 0; sf.shift = 0; sf.wasted = 0; sf.sbps = bps; sf.cval = 0;
-        sf.rs.k = 0; sf.rs.left = 0; sf.rs.pbits = 4; sf.rs.esc = 15u; sf.rs.rawbits = -1; sf.rs.psize = 1;
-        int32_t coef[DEC_MAXORD], h[DEC_MAXORD];
-#pragma unroll
-        for (int j = 0; j < DEC_MAXORD; j++) { coef[j] = 0; h[j] = 0; }
-        bool wide = false;
-        const unsigned long long base_addr = (unsigned long long)((T *)a.out + t.out_offset + (long long)c * t.out_band_stride);
-        if (c < my_ch && !bad) {
-            // ---- K11 front: subframe header, warm-up samples, predictor ----
-            const uint32_t hdr = br.get(8);
-            const uint32_t type = (hdr >> 1) & 0x3Fu;
-            if (hdr & 0x80u) bad = true;
-            if (hdr & 1u) sf.wasted = (int)br.unary() + 1;
-            const int side = ((stereo == 1u && c == 1) || (stereo == 2u && c == 0) || (stereo == 3u && c == 1)) ? 1 : 0;
-            sf.sbps = bps + side - sf.wasted;
-            if (sf.sbps <= 0) bad = true;
-            if (bad) {}
-            else if (type == 0) { sf.type = 0; sf.cval = br.sget(sf.sbps); }
-            else if (type == 1) sf.type = 1;
-            else {
-                bool lpc = false;
-                int order = 0, prec = 3;
-                if (type >= 8 && type <= 12) order = (int)type - 8;
-                else if (type >= 32) { order = (int)(type & 31u) + 1; lpc = true; }
-                else bad = true;
-                if (order > nsamp) bad = true;
-                if (!bad && order > DEC_MAXORD && stereo) { bad = true; status = FRX_E_UNSUPPORTED; }
-                if (!bad && order > DEC_MAXORD) {
-                    // rare long predictors: this lane restores its whole subframe on its own, then idles through the lockstep part
-                    int32_t coefl[32], warml[32];
-                    for (int i = 0; i < order; i++) warml[i] = br.sget(sf.sbps);
-                    prec = (int)br.get(4) + 1;
-                    const int shift = br.sget(5);
-                    if (prec == 16 || shift < 0) bad = true;
-                    for (int j = 0; j < order; j++) coefl[j] = br.sget(prec);
-                    const uint32_t method = br.get(2), po = br.get(4);
-                    if (method > 1u || (po > 0 && ((uint32_t)nsamp >> po) << po != (uint32_t)nsamp) || ((uint32_t)nsamp >> po) < (uint32_t)order) bad = true;
-                    if (!bad) {
-                        RiceState rs;
-                        rs.pbits = method ? 5 : 4; rs.esc = method ? 31u : 15u; rs.psize = (uint32_t)nsamp >> po; rs.rawbits = -1;
-                        rs.k = br.get(rs.pbits);
-                        rs.left = rs.psize - (uint32_t)order;
-                        if (rs.k == rs.esc) rs.rawbits = (int)br.get(5);
-                        BitR brl = br;     // only the copy's address escapes into the out-of-line routine: br itself stays in registers
-                        restore_subframe_generic<DT>(brl, rs, (T *)base_addr, t.out_row_stride, t.w, s0, coefl, order, shift, warml, nsamp, sf.wasted,
-                                                     bps, dq, a.pcm_mode);
-                        br = brl;
-                    }
-                } else if (!bad) {
-#pragma unroll
-                    for (int i = 0; i < DEC_MAXORD; i++) if (i < order) h[i] = br.sget(sf.sbps);
-                    if (lpc) {
-                        prec = (int)br.get(4) + 1;
-                        sf.shift = br.sget(5);
-                        if (prec == 16 || sf.shift < 0) bad = true;
-#pragma unroll
-                        for (int j = 0; j < DEC_MAXORD; j++) if (j < order) coef[j] = br.sget(prec);
-                    } else {
-                        if (order == 1) { coef[0] = 1; }
-                        else if (order == 2) { coef[0] = 2; coef[1] = -1; }
-                        else if (order == 3) { coef[0] = 3; coef[1] = -3; coef[2] = 1; }
-                        else if (order == 4) { coef[0] = 4; coef[1] = -6; coef[2] = 4; coef[3] = -1; }
-                    }
-                    const uint32_t method = br.get(2), po = br.get(4);
-                    if (method > 1u || (po > 0 && ((uint32_t)nsamp >> po) << po != (uint32_t)nsamp) || ((uint32_t)nsamp >> po) < (uint32_t)order) bad = true;
-                    if (!bad) {
-                        sf.type = 2; sf.order = order;
-                        sf.rs.pbits = method ? 5 : 4; sf.rs.esc = method ? 31u : 15u; sf.rs.psize = (uint32_t)nsamp >> po;
-                        // the first partition is short by `order`: prime it here
-                        sf.rs.k = br.get(sf.rs.pbits);
-                        sf.rs.left = sf.rs.psize - (uint32_t)order;
-                        sf.rs.rawbits = -1;
-                        if (sf.rs.k == sf.rs.esc) sf.rs.rawbits = (int)br.get(5);
-                        wide = order > 0 && (sf.sbps + prec + ilog2_u32((uint32_t)order) > 32);
-                    }
-                }
-            }
-        }
-        const int lane_n = (sf.type != 3 && !bad) ? my_n : 0;
-        const int omax = __reduce_max_sync(0xFFFFFFFFu, (uint32_t)(sf.type == 2 && lane_n ? sf.order : 0));
-        const bool anywide = __any_sync(0xFFFFFFFFu, wide && lane_n);
-        // ---- K11 back + K12: lockstep restore, dequantise, coalesced stores ----
-        if (any_stereo) {
-            // warps holding decorrelated stereo frames take one general instantiation (16 taps, 64-bit accumulate)
-            const uint32_t st_mode = stereo ? (c == 0 ? 1u : 1u + stereo) : 0u;
-            const unsigned long long scratch_addr = (unsigned long long)(a.stereo_scratch + (size_t)(live ? f : 0u) * (size_t)a.blocksize);
-            run_chunks<DT, 16, true, true>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode,
-                                           st_mode, scratch_addr, (long long)t.out_band_stride * (long long)sizeof(T));
-        } else if (omax <= 4) {
-            if (anywide) run_chunks<DT, 4, true, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
-            else run_chunks<DT, 4, false, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
-        } else if (omax <= 8) {
-            if (anywide) run_chunks<DT, 8, true, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
-            else run_chunks<DT, 8, false, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
-        } else {
-            if (anywide) run_chunks<DT, 16, true, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
-            else run_chunks<DT, 16, false, false>(br, sf, coef, h, ws, lane, lane_n, nmax, base_addr, t.out_row_stride, w, row0, col0, bps, dq, a.pcm_mode);
-        }
-        if (bad) my_n = 0;
-    }
-    if (!live) return;
-    // ---- footer: byte align; the frame must end where the next one starts (CRC-16: frx_crc_check_kernel) ----
-    const uint64_t fsize = (uint64_t)((br.consumed() + 7u) >> 3) + 2u;
-    if (!bad && pos + fsize > end) bad = true;
-    if (!bad && fj + 1 < t.n_frames && a.frame_pos[f + 1] != FRX_NOPOS && pos + fsize != a.frame_pos[f + 1]) bad = true;
-    if (a.frame_len) a.frame_len[f] = bad ? 0u : (uint32_t)fsize;
-    if (bad) atomicExch(&a.tile_status[ti], status);
-}
 
 // ---- CRC-16 of every decoded frame: one warp per frame, coalesced reads.  Lane l takes a contiguous run of Lq 16-byte
 // quads (the run of lane 0 may be short: virtual leading zeros do not change a CRC); the 32 chunk CRCs are moved to
@@ -747,35 +202,13 @@ cudaError_t frx_launch_crc_check(const DecArgs &a, const uint16_t *xpow, int sm_
     return cudaGetLastError();
 }
 
-// A frame takes milliseconds on its lane, so every frame should start in the first wave: the kernel is built for 22
-// one-warp CTAs per SM (80 registers, 9 KB of shared memory each) and asks for the largest shared-memory carve-out,
-// without which the driver keeps part of the 227 KB as L1 and fewer CTAs fit.
-template <int DT>
-static cudaError_t launch_decode_t(const DecArgs &a, unsigned grid, cudaStream_t st) {
-    static bool configured[64] = { false };   // per device: function attributes belong to the device's context
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev < 0 || dev >= 64 || !configured[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(frx_decode_kernel<DT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        if (e != cudaSuccess) return e;
-        if (dev >= 0 && dev < 64) configured[dev] = true;
-    }
-    frx_decode_kernel<DT><<<grid, 32 * DEC_WARPS, 0, st>>>(a);
-    return cudaGetLastError();
-}
+cudaError_t frx_launch_decode_w22(const DecArgs &a, int out_dtype, cudaStream_t st);   // frx_decode_w22.cu
 
-cudaError_t frx_launch_decode(const DecArgs &a, int out_dtype, cudaStream_t st) {
-    unsigned grid = (a.total_frames + 32u * DEC_WARPS - 1u) / (32u * DEC_WARPS);
-    if (!grid) return cudaSuccess;
-    switch (out_dtype) {
-        case FRX_U8: return launch_decode_t<FRX_U8>(a, grid, st);
-        case FRX_I16: return launch_decode_t<FRX_I16>(a, grid, st);
-        case FRX_U16: return launch_decode_t<FRX_U16>(a, grid, st);
-        case FRX_I32: return launch_decode_t<FRX_I32>(a, grid, st);
-        case FRX_U32: return launch_decode_t<FRX_U32>(a, grid, st);
-        case FRX_F32: return launch_decode_t<FRX_F32>(a, grid, st);
-        default: return cudaErrorInvalidValue;
-    }
+// Which copy: the 22-per-SM one exactly when it turns two waves into one; otherwise the 96-register copy (C3: 63 vs 68 ms).
+cudaError_t frx_launch_decode(const DecArgs &a, int out_dtype, int sm_count, cudaStream_t st) {
+    const uint32_t warps = (a.total_frames + 31u) / 32u;
+    if (warps > 20u * (uint32_t)sm_count && warps <= 22u * (uint32_t)sm_count) return frx_launch_decode_w22(a, out_dtype, st);
+    return dec_w20::launch(a, out_dtype, st);
 }
 
 cudaError_t frx_launch_dequantize(const int32_t *pcm, int h, int w, int channels, int bps, int out_dtype, int mode, double dmin,

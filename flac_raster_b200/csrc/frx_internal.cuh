@@ -69,7 +69,7 @@ void frx_make_crc16_tables(uint16_t *tab);
 cudaError_t frx_launch_frame_pos(const DecArgs &a, cudaStream_t st);
 cudaError_t frx_launch_discover(const DecArgs &a, const uint32_t *unit_prefix, const int32_t *unit_tiles, int n_scan_tiles,
                                 uint32_t total_units, cudaStream_t st);
-cudaError_t frx_launch_decode(const DecArgs &a, int out_dtype, cudaStream_t st);
+cudaError_t frx_launch_decode(const DecArgs &a, int out_dtype, int sm_count, cudaStream_t st);
 cudaError_t frx_launch_dequantize(const int32_t *pcm, int h, int w, int channels, int bps, int out_dtype, int mode, double dmin,
                                   double dmax, void *out, cudaStream_t st);
 // frx_tiff_unpack work split, shared by the host (unit counts) and the kernel: a chunk whose rows are short is cut into runs of
