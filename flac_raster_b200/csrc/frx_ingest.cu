@@ -86,10 +86,16 @@ __global__ void __launch_bounds__(ING_THREADS) frx_tiff_unpack_kernel(const uint
     typedef typename IngElem<ESZ>::T T;
     __shared__ __align__(16) uint8_t stage[FRX_ING_SEG_BYTES + 48];
     const uint32_t u = blockIdx.x;
-    int lo = 0, hi = n_chunks;
-    while (hi - lo > 1) {
-        const int mid = (lo + hi) >> 1;
-        if (unit_prefix[mid] <= u) lo = mid; else hi = mid;
+    // chunk of this unit: chunks of one file nearly always hold the same number of units, so the proportional guess is
+    // right (two independent loads); the bisection -- log2(n_chunks) dependent L2 round trips per CTA -- is the fallback
+    int lo = (int)(((unsigned long long)u * (unsigned long long)n_chunks) / gridDim.x);
+    if (!(__ldg(&unit_prefix[lo]) <= u && u < __ldg(&unit_prefix[lo + 1]))) {
+        int hi = n_chunks;
+        lo = 0;
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (__ldg(&unit_prefix[mid]) <= u) lo = mid; else hi = mid;
+        }
     }
     const frx_tiff_chunk ch = chunks[lo];
     const uint32_t lu = u - unit_prefix[lo];
