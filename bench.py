@@ -188,15 +188,19 @@ def main_reference(args):
         return 0
     import oracle
     wl = workload(args)
-    threads = oracle.num_threads()
+    # every host core this process may run on, set explicitly: torchrun exports OMP_NUM_THREADS=1 to its workers
+    try:
+        threads = len(os.sched_getaffinity(0))
+    except AttributeError:
+        threads = os.cpu_count() or oracle.num_threads()
     n_tiles = min(len(tiles_for(wl)), max(threads, 8) * (1 if not args.small else 1))
     n_tiles = min(n_tiles, wl["W"] // wl["tile"] if wl["W"] >= wl["tile"] else 1) or 1
     strip, tiles = cpu_sample_tiles(wl, n_tiles, host_strip_generator(wl, wl["seed"]))
     for _ in range(max(1, min(args.warmup, 1))):
-        run_cpu(wl, strip, tiles)
+        run_cpu(wl, strip, tiles, threads)
     vals, dts = [], []
     for _ in range(args.steps):
-        v, dt, nbytes = run_cpu(wl, strip, tiles)
+        v, dt, nbytes = run_cpu(wl, strip, tiles, threads)
         vals.append(v)
         dts.append(dt)
     total_px = sum(t[2] * t[3] for t in tiles) * args.steps
@@ -235,7 +239,23 @@ def main_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL prints its version banner on stdout when the communicator comes up: keep stdout for the JSON line only
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            try:
+                import ctypes
+                ctypes.CDLL(None).fflush(None)   # the banner sits in C stdio's buffer when stdout is a pipe
+            except Exception:
+                pass
+            os.dup2(saved, 1)
+            os.close(saved)
 
     def barrier():
         if world > 1:

@@ -325,7 +325,10 @@ class DatasetReader:
         lo = min(c[0] for c in chunks)
         hi = max(c[0] + ((c[3] - 1) * c[5] + c[4]) * (self.count if c[6] < 0 else 1) * esz for c in chunks)
         lo_al = lo & ~255                       # keeps the file's own alignment phase on the device
-        host = torch.empty(hi - lo_al, dtype=torch.uint8, pin_memory=True)
+        try:
+            host = torch.empty(hi - lo_al, dtype=torch.uint8, pin_memory=True)
+        except RuntimeError:                    # not enough lockable memory for the whole span: a pageable copy still works
+            host = torch.empty(hi - lo_al, dtype=torch.uint8)
         self._f.seek(lo_al)
         got = self._f.readinto(memoryview(host.numpy()))
         if got != hi - lo_al:
