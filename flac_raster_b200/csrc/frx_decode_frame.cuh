@@ -135,6 +135,20 @@ __device__ __forceinline__ int32_t rice_next(BitR &br, RiceState &rs) {
     }
     rs.left--;
     if (rs.rawbits >= 0) return rs.rawbits ? br.sget(rs.rawbits) : 0;
+    // common case: the whole code (zeros, stop bit, k low bits) already sits in the 64-bit window -- one refill, no loop
+    br.refill();
+    const int k = (int)rs.k;
+    if (br.acc != 0ull) {
+        const int lz = __clzll((long long)br.acc);
+        if (lz + k < br.cnt) {
+            const uint64_t t = (br.acc << lz) << 1;                   // zeros and the stop bit dropped (two shifts: lz may be 63)
+            const uint32_t low = k ? (uint32_t)(t >> (64 - k)) : 0u;
+            br.acc = t << k;
+            br.cnt -= lz + 1 + k;
+            const uint32_t u = ((uint32_t)lz << k) | low;
+            return (int32_t)(u >> 1) ^ -(int32_t)(u & 1u);
+        }
+    }
     const uint32_t z = br.unary();
     const uint32_t u = (z << rs.k) | br.get((int)rs.k);
     return (int32_t)(u >> 1) ^ -(int32_t)(u & 1u);
