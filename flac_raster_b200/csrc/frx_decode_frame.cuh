@@ -57,6 +57,9 @@ struct BitR {
             for (int k = 0; k < 4; k++) if ((uint32_t)k < free_blocks) push16(v[k]);
             if (!__any_sync(0xFFFFFFFFu, free_blocks > 4u)) break;
         }
+        // the line after next goes to L2 now: a lane walks its frame sequentially and comes back a chunk (tens of
+        // microseconds) later, so its next top-up finds the bytes on chip instead of waiting on DRAM
+        if (want && np + 384 <= hi) asm volatile("prefetch.global.L2 [%0];" ::"l"(np + 256));
     }
     __device__ __forceinline__ uint32_t pop() {
         if (rd == wr) push16(load16());      // ring ran dry inside a chunk (more than ~4 bytes per sample): fetch on demand
@@ -231,6 +234,14 @@ template <int DT>
 __device__ __forceinline__ void flush_chunk(DecWarpSmem &ws, int lane) {
     typedef typename FrxElem<DT>::T T;
     __syncwarp();
+    // every frame of the warp has a full chunk that stays inside its raster row (tile widths that are multiples of 32,
+    // away from the frame ends): one pointer per frame, no per-frame geometry
+    if (__all_sync(0xFFFFFFFFu, ws.cnt[lane] == 32u && ws.room[lane] >= 32u)) {
+#pragma unroll 8
+        for (int j = 0; j < 32; j++) dec_store<DT>(ws.ptr[j] + (unsigned long long)lane * sizeof(T), ws.stage[j][lane]);
+        __syncwarp();
+        return;
+    }
 #pragma unroll 4
     for (int j = 0; j < 32; j++) {
         const uint32_t cnt = ws.cnt[j];
