@@ -57,9 +57,23 @@ struct BitR {
             for (int k = 0; k < 4; k++) if ((uint32_t)k < free_blocks) push16(v[k]);
             if (!__any_sync(0xFFFFFFFFu, free_blocks > 4u)) break;
         }
-        // the line after next goes to L2 now: a lane walks its frame sequentially and comes back a chunk (tens of
-        // microseconds) later, so its next top-up finds the bytes on chip instead of waiting on DRAM
-        if (want && np + 384 <= hi) asm volatile("prefetch.global.L2 [%0];" ::"l"(np + 256));
+    }
+    // The same in two halves around the write-out of a chunk: the loads are issued before it and land in the ring after
+    // it, so their latency is covered by the stores instead of being waited for at the next chunk boundary.  At most four
+    // blocks per lane (what a chunk usually consumes); topup() at the boundary picks up any remainder.
+    __device__ __forceinline__ uint32_t topup_issue(bool want, uint4 (&v)[4]) {
+        uint32_t nb = want ? (DEC_RING - (wr - rd)) >> 2 : 0u;
+        nb = nb > 4u ? 4u : nb;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            v[k] = make_uint4(0u, 0u, 0u, 0u);
+            if ((uint32_t)k < nb) { const uint8_t *p = np; np += 16 * k; v[k] = load16(); np = p; }
+        }
+        return nb;
+    }
+    __device__ __forceinline__ void topup_commit(const uint4 (&v)[4], uint32_t nb) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) if ((uint32_t)k < nb) push16(v[k]);
     }
     __device__ __forceinline__ uint32_t pop() {
         if (rd == wr) push16(load16());      // ring ran dry inside a chunk (more than ~4 bytes per sample): fetch on demand
@@ -376,7 +390,10 @@ __device__ __forceinline__ void run_chunks(BitR &br, SubF &sf, int32_t *coef, in
                 }
             }
         }
+        uint4 pv[4];
+        const uint32_t pn = br.topup_issue(n0 + 32 < my_n, pv);    // the next chunk's bytes travel during the write-out
         if (ST) flush_chunk_stereo<DT>(ws, lane, mode); else flush_chunk<DT>(ws, lane);
+        br.topup_commit(pv, pn);
         col += 32;
         while (col >= w) { col -= w; row++; }
     }
