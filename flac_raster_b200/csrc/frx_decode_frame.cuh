@@ -155,13 +155,16 @@ __device__ __forceinline__ int32_t rice_next(BitR &br, RiceState &rs) {
     // common case: the whole code (zeros, stop bit, k low bits) already sits in the 64-bit window -- one refill, no loop
     br.refill();
     const int k = (int)rs.k;
-    if (br.acc != 0ull) {
-        const int lz = __clzll((long long)br.acc);
-        if (lz + k < br.cnt) {
-            const uint64_t t = (br.acc << lz) << 1;                   // zeros and the stop bit dropped (two shifts: lz may be 63)
-            const uint32_t low = k ? (uint32_t)(t >> (64 - k)) : 0u;
-            br.acc = t << k;
-            br.cnt -= lz + 1 + k;
+    // (after refill() the upper 32 bits of the window are all valid, so 32-bit arithmetic on them suffices)
+    const uint32_t hi = (uint32_t)(br.acc >> 32);
+    if (hi != 0u) {
+        const int lz = __clz((int)hi);
+        if (lz + k < 32) {
+            const uint32_t t = (hi << lz) << 1;                       // zeros and the stop bit dropped (two shifts: lz may be 31)
+            const uint32_t low = k ? (t >> (32 - k)) : 0u;
+            const int used = lz + 1 + k;                              // <= 32
+            br.acc = (br.acc << (used - 1)) << 1;
+            br.cnt -= used;
             const uint32_t u = ((uint32_t)lz << k) | low;
             return (int32_t)(u >> 1) ^ -(int32_t)(u & 1u);
         }
