@@ -4,6 +4,9 @@
 //   ~3 ms on its lane whatever else runs, so a few warps left over for a second wave cost a whole frame time.
 // The including translation unit defines FRX_DEC_CTAS, FRX_DEC_RINGW and FRX_DEC_NS (namespace of this copy).
 #include "frx_decode_common.cuh"
+#ifndef FRX_DEC_EARLY_ISSUE
+#define FRX_DEC_EARLY_ISSUE 1
+#endif
 
 namespace FRX_DEC_NS {
 
@@ -393,10 +396,14 @@ __device__ __forceinline__ void run_chunks(BitR &br, SubF &sf, int32_t *coef, in
                 }
             }
         }
+#if FRX_DEC_EARLY_ISSUE
         uint4 pv[4];
         const uint32_t pn = br.topup_issue(n0 + 32 < my_n, pv);    // the next chunk's bytes travel during the write-out
         if (ST) flush_chunk_stereo<DT>(ws, lane, mode); else flush_chunk<DT>(ws, lane);
         br.topup_commit(pv, pn);
+#else
+        if (ST) flush_chunk_stereo<DT>(ws, lane, mode); else flush_chunk<DT>(ws, lane);
+#endif
         col += 32;
         while (col >= w) { col -= w; row++; }
     }
