@@ -18,7 +18,7 @@
  *     coefficient quantisation with error feedback, fixed-order 0-4 trial, Rice
  *     partition-order search by partition sums) and is PINNED against the
  *     libFLAC-1.4.3-produced fixtures test_data/sample_rgb.flac and
- *     test_data/sample_dem.flac by tests/test_oracle.py.
+ *     test_data/sample_dem.flac by tests/test_oracle_golden.py.
  *   - ofl_ref_encode_tiles() / ofl_ref_decode_tiles(): the reference's tile loop
  *     (cli.py:691-763 create-streaming body; cli.py:1016-1023 + converter.py:234-282
  *     extract-streaming body) restated end to end in C with an OpenMP loop over
@@ -899,6 +899,15 @@ static void process_subframe(enc_ws_t *ws, const preset_t *ps, const int64_t *si
     }
 }
 
+/* Test-only switches (tests/test_gpu_decode_cases.py): streams a FLAC decoder must accept although libFLAC's presets
+ * never write them -- LPC orders up to 32 (non-subset) and escaped (raw binary) Rice partitions (RFC 9639 9.2.7.1).
+ * Both default to off, which leaves ofl_encode() the libFLAC restatement pinned by the golden fixtures. */
+static int g_test_max_lpc_order = 0, g_test_escape_mod = 0;
+void ofl_set_test_options(int max_lpc_order, int escape_mod) {
+    g_test_max_lpc_order = max_lpc_order < 0 ? 0 : (max_lpc_order > OFL_MAX_LPC_ORDER ? OFL_MAX_LPC_ORDER : max_lpc_order);
+    g_test_escape_mod = escape_mod < 0 ? 0 : escape_mod;
+}
+
 static void write_subframe(bw_t *w, const subframe_t *sf, const int64_t *sig, uint32_t blocksize) {
     int bps = sf->bps;
     uint32_t typecode = sf->type == 0 ? 0u : sf->type == 1 ? 1u : sf->type == 2 ? (8u | (uint32_t)sf->order) : (32u | (uint32_t)(sf->order - 1));
@@ -925,6 +934,26 @@ static void write_subframe(bw_t *w, const subframe_t *sf, const int64_t *sig, ui
         uint32_t n = blocksize >> sf->part_order;
         if (p == 0) n -= (uint32_t)sf->order;
         uint32_t k = sf->rice_param[p];
+        if (g_test_escape_mod > 0 && (p % (uint32_t)g_test_escape_mod) == 0) {
+            /* escape code: parameter all ones, 5-bit raw width, residuals as two's-complement fields */
+            int nb = 0;
+            for (uint32_t j = 0; j < n; j++) {
+                int64_t r = sf->residual[ri + j];
+                int need = 1;
+                while (need < 32 && (r < -((int64_t)1 << (need - 1)) || r > ((int64_t)1 << (need - 1)) - 1)) need++;
+                if (need > nb) nb = need;
+            }
+            if (n == 0) nb = 0;
+            int all_zero = 1;
+            for (uint32_t j = 0; j < n; j++) if (sf->residual[ri + j]) { all_zero = 0; break; }
+            if (all_zero) nb = 0;
+            if (nb <= 31) {
+                bw_bits(w, rice2 ? 31 : 15, rice2 ? 5 : 4);
+                bw_bits(w, (uint64_t)nb, 5);
+                for (uint32_t j = 0; j < n; j++) { int32_t r = sf->residual[ri++]; if (nb) bw_bits64(w, (uint64_t)(int64_t)r, nb); }
+                continue;
+            }
+        }
         bw_bits(w, k, rice2 ? 5 : 4);
         for (uint32_t j = 0; j < n; j++) {
             int32_t r = sf->residual[ri++];
@@ -1092,7 +1121,9 @@ int ofl_encode(const int32_t *pcm, size_t n, int channels, int bps, int sample_r
     if (bps < 4 || bps > 32) return -3;
     if (blocksize < 16 || blocksize > 65535) return -4;
     if (level < 0) level = 0; if (level > 8) level = 8;
-    const preset_t *ps = &presets[level];
+    preset_t pst = presets[level];
+    if (g_test_max_lpc_order > 0) pst.max_lpc_order = g_test_max_lpc_order;
+    const preset_t *ps = &pst;
     bw_t w = { out, out_cap, 0, 0, 0, 0 };
     if (write_header) write_stream_header(&w, channels, bps, (uint32_t)sample_rate, (uint32_t)blocksize);
     enc_ws_t *ws = ws_new(blocksize);

@@ -15,15 +15,44 @@ def tiles_for(raster, tile, bands="all"):
     return out
 
 
+def lossless_pcm(block):
+    """pcm_mode=lossless (SURVEY decision D1): identity mapping into a signed PCM of the effective width.
+    -> (int32 PCM (h*w, bands), bps, dmin, dmax, sample_rate) like quant.reference_pcm."""
+    bands = block.shape[0]
+    a = block.transpose(1, 2, 0).reshape(-1, bands)
+    dt = block.dtype
+    if dt == np.uint16:
+        pcm, bps = a.astype(np.int32) - 32768, 16
+    elif dt == np.uint8 or dt == np.int16:
+        pcm, bps = a.astype(np.int32), 16
+    elif dt == np.int32:
+        pcm, bps = a.astype(np.int32), 32
+    elif dt == np.uint32:
+        pcm, bps = (a ^ np.uint32(0x80000000)).view(np.int32), 32
+    else:
+        b = np.ascontiguousarray(a).view(np.int32).astype(np.int64)
+        pcm, bps = np.where(b >= 0, b, 0x80000000 - (b & 0xFFFFFFFF)).astype(np.int64).astype(np.int32), 32
+    return pcm, bps, float(np.min(block)), float(np.max(block)), 44100
+
+
+def spatial_pcm(block):
+    """pcm_mode=reference_spatial: spatial_encoder.py:229-248 + pyFLAC truncation (oracle/quant.py)."""
+    pcm, bps = quant.spatial_reference_pcm(block)
+    return pcm, bps, float(np.min(block)), float(np.max(block)), 44100
+
+
 def check_encode_against_oracle(raster_np, tiles, res_bytes, tile_offset, tile_size, tile_minmax, frame_size,
-                                blocksize=4096, level=5, size_margin=1.02, check_size=True, sample_rate=44100):
+                                blocksize=4096, level=5, size_margin=1.02, check_size=True, sample_rate=44100,
+                                pcm_fn=None):
     """P1 (PCM == reference quantiser), P2 (independent decoder accepts the stream and returns the PCM),
-    size gate vs the libFLAC-level restatement.  Returns (ours_total, oracle_total)."""
+    size gate vs the libFLAC-level restatement.  Returns (ours_total, oracle_total).
+    pcm_fn: block -> (pcm, bps, dmin, dmax, sr); default = the reference quantiser (pcm_mode=reference)."""
+    pcm_fn = pcm_fn or quant.reference_pcm
     ours_total = oracle_total = 0
     fpos = 0
     for i, (r0, c0, h, w, b0, nch) in enumerate(tiles):
         block = raster_np[b0:b0 + nch, r0:r0 + h, c0:c0 + w]
-        pcm_ref, bps, dmin, dmax, _sr = quant.reference_pcm(block)
+        pcm_ref, bps, dmin, dmax, _sr = pcm_fn(block)
         off, size = int(tile_offset[i]), int(tile_size[i])
         data = bytes(res_bytes[off:off + size])
         pcm, frames, rc = oracle.decode_frames(data, nch, bps, sample_rate, max_samples=h * w + 16)
