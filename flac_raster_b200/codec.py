@@ -226,6 +226,19 @@ class Codec:
                                            C.c_void_p(status.data_ptr()), self._stream(stream)))
         return status
 
+    def decode_tiles_noalloc(self, data, dtiles, out, status, out_dtype: str | None = None, frame_size=None, blocksize: int = 4096,
+                             pcm_mode: str = "reference", n_bytes: int | None = None, stream=None):
+        """decode_tiles through frx_decode_tiles_noalloc: nothing is allocated, here or in the library (the caller passes
+        `status`; scratch is a static device array inside libfrx).  At most _lib.NOALLOC_MAX_TILES tiles and
+        _lib.NOALLOC_MAX_FRAMES frames per call, no two-channel tiles; calls that overlap on one GPU race (include/frx.h)."""
+        out_dtype = out_dtype or dtype_name(out)
+        fs = C.c_void_p(frame_size.data_ptr()) if frame_size is not None else None
+        nb = int(n_bytes) if n_bytes is not None else data.numel()
+        L.check(self._lib.frx_decode_tiles_noalloc(self._h, C.c_void_p(data.data_ptr()), nb, dtiles, len(dtiles), fs, blocksize,
+                                                   L.DTYPE_CODE[out_dtype], L.PCM_MODE[pcm_mode], C.c_void_p(out.data_ptr()),
+                                                   C.c_void_p(status.data_ptr()), self._stream(stream)))
+        return status
+
     def quantize(self, raster, tile, pcm_mode: str = "reference", dtype: str | None = None):
         """K0+K1 only: (pcm int32 (h*w, n_ch) tensor, minmax float64[2] tensor)."""
         torch = _torch()

@@ -3,6 +3,7 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <pthread.h>
 #include <string.h>
 
 #include <vector>
@@ -713,3 +714,133 @@ int frx_decode_tiles_host(frx_ctx *c, const uint8_t *bytes_host, uint64_t n_byte
 }
 
 }  // extern "C"
+
+// ---- allocation-free decode (include/frx.h: frx_decode_tiles_noalloc) -----------------------------------------
+// The scratch the decode launch sequence needs, laid out in one file-scope device array.  Every GPU that loads libfrx
+// holds its own instance until the process exits.  In host code the array's NAME is only a host-side stand-in: the
+// device address comes from cudaGetSymbolAddress, taken once per device with that device current (noalloc_setup).
+struct NoallocStage {                                   // host-built tables, copied to the head of the scratch in one go
+    frx_dtile tiles[FRX_NOALLOC_MAX_TILES];
+    uint32_t dprefix[FRX_NOALLOC_MAX_TILES + 1];
+    uint32_t scan_prefix[FRX_NOALLOC_MAX_TILES + 1];
+    int32_t scan_tiles[FRX_NOALLOC_MAX_TILES + 1];
+};
+#define NA_ALIGN(x) (((x) + 255) & ~(size_t)255)
+#define NA_OFF_STAGE 0
+#define NA_OFF_CRCTAB NA_ALIGN(sizeof(NoallocStage))
+#define NA_XPOW_ELEMS (FRX_CRC_MAXLQ * 256 + 4)
+#define NA_OFF_XPOW (NA_OFF_CRCTAB + NA_ALIGN(1024 * sizeof(uint16_t)))
+#define NA_OFF_FPOS (NA_OFF_XPOW + NA_ALIGN(NA_XPOW_ELEMS * sizeof(uint16_t)))
+#define NA_OFF_FLEN (NA_OFF_FPOS + NA_ALIGN(sizeof(uint64_t) * (FRX_NOALLOC_MAX_FRAMES + 1)))
+#define NA_SCRATCH_BYTES (NA_OFF_FLEN + NA_ALIGN(sizeof(uint32_t) * (FRX_NOALLOC_MAX_FRAMES + 1)))
+static __device__ __align__(256) unsigned char g_frx_noalloc_scratch[NA_SCRATCH_BYTES];
+
+#define NA_MAX_DEVICES 64
+static unsigned char *g_na_ptr[NA_MAX_DEVICES];         // device address of the array on each device, 0 until set up
+static pthread_mutex_t g_na_lock = PTHREAD_MUTEX_INITIALIZER;
+
+// once per device, with that device current: the array's device address, and the constant tables into it
+static int noalloc_setup(int device, unsigned char **out) {
+    if (device < 0 || device >= NA_MAX_DEVICES) return set_err(FRX_E_UNSUPPORTED, "device %d beyond the %d the allocation-free path tracks", device, NA_MAX_DEVICES);
+    pthread_mutex_lock(&g_na_lock);
+    unsigned char *p = g_na_ptr[device];
+    int rc = FRX_OK;
+    if (!p) {
+        cudaError_t e = cudaGetSymbolAddress((void **)&p, g_frx_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            rc = set_err(FRX_E_CUDA, "cudaGetSymbolAddress(g_frx_noalloc_scratch) failed on device %d: %s", device, cudaGetErrorString(e));
+            p = nullptr;
+        } else {
+            static uint16_t tab[1024], xp[NA_XPOW_ELEMS];   // host tables (static: 27 KB is too much for a caller's stack)
+            frx_make_crc16_tables(tab);
+            for (int lq = 1; lq <= FRX_CRC_MAXLQ; lq++) {   // x^(128 lq j) mod P, as ensure_xpow builds them
+                uint32_t base = 2, ex = 128u * lq, acc = 1;
+                while (ex) { if (ex & 1u) acc = frx_gf16_mulmod(acc, base); base = frx_gf16_mulmod(base, base); ex >>= 1; }
+                uint32_t cur = 1;
+                for (int j = 0; j < 256; j++) { xp[(lq - 1) * 256 + j] = (uint16_t)cur; cur = frx_gf16_mulmod(cur, acc); }
+            }
+            uint32_t inv32 = 0xC002u;
+            for (int i = 0; i < 5; i++) inv32 = frx_gf16_mulmod(inv32, inv32);
+            uint32_t cur = 1;
+            for (int z = 0; z < 4; z++) { xp[FRX_CRC_MAXLQ * 256 + z] = (uint16_t)cur; cur = frx_gf16_mulmod(cur, inv32); }
+            e = cudaMemcpy(p + NA_OFF_CRCTAB, tab, sizeof(tab), cudaMemcpyHostToDevice);
+            if (e == cudaSuccess) e = cudaMemcpy(p + NA_OFF_XPOW, xp, sizeof(xp), cudaMemcpyHostToDevice);
+            if (e != cudaSuccess) { rc = set_err(FRX_E_CUDA, "copying the CRC tables into the static scratch failed: %s", cudaGetErrorString(e)); p = nullptr; }
+            else g_na_ptr[device] = p;
+        }
+    }
+    pthread_mutex_unlock(&g_na_lock);
+    *out = p;
+    return rc;
+}
+
+extern "C" int frx_decode_tiles_noalloc(frx_ctx *c, const uint8_t *bytes_dev, uint64_t n_bytes, const frx_dtile *tiles, int32_t n_tiles,
+                                        const uint32_t *frame_size_dev, int32_t blocksize, int32_t out_dtype, int32_t pcm_mode,
+                                        void *out_dev, int32_t *tile_status_dev, void *stream) {
+    if (!c) return set_err(FRX_E_INVALID, "ctx is NULL");
+    if (!bytes_dev || !tiles || n_tiles <= 0 || !out_dev || !tile_status_dev) return set_err(FRX_E_INVALID, "NULL argument");
+    if (blocksize < 16 || blocksize > 65535) return set_err(FRX_E_INVALID, "bad blocksize %d", blocksize);
+    if (out_dtype < FRX_U8 || out_dtype > FRX_F32) return set_err(FRX_E_INVALID, "bad out_dtype %d", out_dtype);
+    if (n_tiles > FRX_NOALLOC_MAX_TILES)
+        return set_err(FRX_E_UNSUPPORTED, "%d tiles in one call; the allocation-free decode holds scratch for at most FRX_NOALLOC_MAX_TILES = %d (use frx_decode_tiles or split the batch)",
+                       n_tiles, FRX_NOALLOC_MAX_TILES);
+    NoallocStage hs;                                    // 11.8 KB on the stack: no heap either
+    uint64_t nf = 0, nu = 0;
+    int n_scan = 0;
+    for (int i = 0; i < n_tiles; i++) {
+        const frx_dtile &t = tiles[i];
+        if (t.channels < 1 || t.channels > FRX_MAX_CH || t.h <= 0 || t.w <= 0 || (t.bps != 16 && t.bps != 32 && t.bps != 8 && t.bps != 24 && t.bps != 12 && t.bps != 20))
+            return set_err(FRX_E_INVALID, "tile %d: bad geometry/bps", i);
+        if (t.channels == 2)
+            return set_err(FRX_E_UNSUPPORTED, "tile %d has two channels: stereo-decorrelated frames need a scratch row per frame, which the fixed scratch of the allocation-free decode does not hold (use frx_decode_tiles)", i);
+        if (t.byte_offset > n_bytes || t.byte_size > n_bytes - t.byte_offset) return set_err(FRX_E_INVALID, "tile %d: byte range outside the buffer", i);
+        const uint64_t expect = ((uint64_t)t.h * t.w + blocksize - 1) / blocksize;
+        if (t.n_frames != expect) return set_err(FRX_E_INVALID, "tile %d: n_frames %u != ceil(h*w/blocksize) %llu", i, t.n_frames, (unsigned long long)expect);
+        if (t.first_frame != 0xFFFFFFFFu && !frame_size_dev) return set_err(FRX_E_INVALID, "tile %d needs frame_size", i);
+        hs.tiles[i] = t;
+        hs.dprefix[i] = (uint32_t)nf;
+        nf += t.n_frames;
+        if (nf > FRX_NOALLOC_MAX_FRAMES)
+            return set_err(FRX_E_UNSUPPORTED, "the tiles hold more than FRX_NOALLOC_MAX_FRAMES = %d frames (reached at tile %d); the allocation-free decode has no scratch for more (use frx_decode_tiles or split the batch)",
+                           FRX_NOALLOC_MAX_FRAMES, i);
+        if (t.first_frame == 0xFFFFFFFFu) {
+            hs.scan_prefix[n_scan] = (uint32_t)nu;
+            hs.scan_tiles[n_scan] = i;
+            n_scan++;
+            nu += (t.byte_size + 4095) / 4096;
+            if (nu > 0x7FFFFFF0ull) return set_err(FRX_E_UNSUPPORTED, "too many bytes to scan for frame starts in one call");
+        }
+    }
+    hs.dprefix[n_tiles] = (uint32_t)nf;
+    hs.scan_prefix[n_scan] = (uint32_t)nu;
+    CK(cudaSetDevice(c->device));
+    unsigned char *base = nullptr;
+    { int rc = noalloc_setup(c->device, &base); if (rc) return rc; }
+    cudaStream_t st = (cudaStream_t)stream;
+    // pageable source: the runtime copies `hs` to its own staging area before this returns, so the stack copy may die
+    CK(cudaMemcpyAsync(base + NA_OFF_STAGE, &hs, sizeof(hs), cudaMemcpyHostToDevice, st));
+    // what must start at zero: the tile status, and the frame lengths the CRC pass reads (the array keeps the last call's)
+    CK(cudaMemsetAsync(tile_status_dev, 0, sizeof(int32_t) * n_tiles, st));
+    CK(cudaMemsetAsync(base + NA_OFF_FLEN, 0, sizeof(uint32_t) * (size_t)(nf + 1), st));
+    NoallocStage *ds = (NoallocStage *)(base + NA_OFF_STAGE);
+    DecArgs a;
+    memset(&a, 0, sizeof(a));
+    a.bytes = bytes_dev; a.n_bytes = n_bytes; a.tiles = ds->tiles; a.dprefix = ds->dprefix;
+    a.frame_pos = (uint64_t *)(base + NA_OFF_FPOS); a.frame_len = (uint32_t *)(base + NA_OFF_FLEN); a.stereo_scratch = nullptr;
+    a.frame_size = frame_size_dev; a.crc_tab = (const uint16_t *)(base + NA_OFF_CRCTAB);
+    a.out = out_dev; a.tile_status = tile_status_dev; a.total_frames = (uint32_t)nf; a.n_tiles = n_tiles; a.blocksize = blocksize;
+    a.pcm_mode = pcm_mode; a.verify_crc = c->verify_crc;
+    CK(frx_launch_frame_pos(a, st));
+    c->launches += 1;
+    if (n_scan) {
+        CK(frx_launch_discover(a, ds->scan_prefix, ds->scan_tiles, n_scan, (uint32_t)nu, st));
+        c->launches += 1;
+    }
+    CK(cudaEventRecord(c->ev[2], st));
+    CK(frx_launch_decode(a, out_dtype, c->sm_count, st));
+    if (c->verify_crc) { CK(frx_launch_crc_check(a, (const uint16_t *)(base + NA_OFF_XPOW), c->sm_count, st)); c->launches += 1; }
+    CK(cudaEventRecord(c->ev[3], st));
+    c->dec_timed = true;
+    c->launches += 1;
+    return FRX_OK;
+}

@@ -157,6 +157,25 @@ int frx_decode_tiles_host(frx_ctx *ctx, const uint8_t *bytes_host, uint64_t n_by
                           int32_t n_tiles, const uint32_t *frame_size_host, int32_t blocksize, int32_t out_dtype,
                           int32_t pcm_mode, void *out_host, uint64_t out_elems, int32_t *tile_status_host);
 
+/* ---- allocation-free decode ---------------------------------------------------------------- */
+/* No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid allocation).  Same arguments, same kernels and same outputs as frx_decode_tiles, but the
+ * call allocates nothing: no cudaMalloc/cudaFree, no allocating library routine.  Its scratch
+ * (tile descriptors, frame positions and lengths, CRC tables; about 430 KB) is a file-scope
+ * `static __device__` array inside libfrx, which every GPU that loads the library holds until
+ * the process exits.  Limits: n_tiles <= FRX_NOALLOC_MAX_TILES, the tiles' frames together
+ * <= FRX_NOALLOC_MAX_FRAMES, no two-channel tiles (their stereo-decorrelated frames need a scratch
+ * row per frame) -- anything beyond returns FRX_E_UNSUPPORTED and says which limit was hit.
+ * All calls on one device share the array, and it keeps the previous call's contents (the call
+ * clears what must start at zero): two calls that overlap on the GPU -- different streams or
+ * contexts of the same device -- race.  Calls on one stream, or ordered by events, are safe.   */
+#define FRX_NOALLOC_MAX_TILES 128
+#define FRX_NOALLOC_MAX_FRAMES 32768
+int frx_decode_tiles_noalloc(frx_ctx *ctx, const uint8_t *bytes_dev, uint64_t n_bytes, const frx_dtile *tiles_host,
+                             int32_t n_tiles, const uint32_t *frame_size_dev, int32_t blocksize, int32_t out_dtype,
+                             int32_t pcm_mode, void *out_dev, int32_t *tile_status_dev, void *stream);
+
 /* ---- raster ingestion -------------------------------------------------- */
 /* One strip or tile of an uncompressed TIFF: where its bytes sit in the staged file image and
  * which rectangle of the raster they fill.  Chunk rows hold `pitch` pixels (the tile width; the
