@@ -1,0 +1,214 @@
+
+// ==========================================================================================
+// K7: bit packing.  Every lane appends a run of fields to the stream in lane order; a field is `zer` zero bits followed by
+// the low `len` bits of `val` (len <= 32).  Lanes accumulate their bits in registers and store whole words; the words two
+// lanes share are merged with a segmented OR-scan, so shared memory sees plain stores only.
+// ==========================================================================================
+struct Emitter {
+    uint32_t P;        // bit position of the end of the stream inside the warp buffer
+    uint32_t carry;    // bits of the incomplete last word (top-aligned)
+};
+struct LaneBits {
+    uint32_t hi, lo, firstw;
+    int nb;
+    uint32_t *wp;
+    bool flushed;
+    __device__ __forceinline__ void init(uint32_t *out, uint32_t bitpos) {
+        wp = out + (bitpos >> 5); nb = (int)(bitpos & 31u); hi = 0; lo = 0; firstw = 0; flushed = false;
+    }
+    __device__ __forceinline__ void flush() {
+        if (!flushed) { firstw = hi; flushed = true; } else *wp = hi;
+        wp++; hi = lo; lo = 0; nb -= 32;
+    }
+    __device__ __forceinline__ void put(uint32_t c, int n) {   // n in 1..32, c < 2^n
+        const uint32_t ct = c << (32 - n);
+        hi |= ct >> nb;
+        lo = __funnelshift_r(0u, ct, (uint32_t)nb);            // ct << (32 - nb), 0 when nb == 0
+        nb += n;
+        if (nb >= 32) flush();
+    }
+    __device__ __forceinline__ void zeros(uint32_t q) {
+        nb += (int)q;
+        while (nb >= 32) flush();
+    }
+};
+template <int NF>
+__device__ __forceinline__ void emit_fields(uint32_t *out, Emitter &em, const uint32_t (&val)[NF], const uint32_t (&len)[NF], const uint32_t (&zer)[NF], int lane) {
+    uint32_t T = 0;
+#pragma unroll
+    for (int i = 0; i < NF; i++) T += len[i] + zer[i];
+    uint32_t incl = T;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(FULLMASK, incl, o);
+        if (lane >= o) incl += n;
+    }
+    const uint32_t total = __shfl_sync(FULLMASK, incl, 31);
+    const uint32_t start = em.P + incl - T;
+    LaneBits lb;
+    lb.init(out, start);
+#pragma unroll
+    for (int i = 0; i < NF; i++) {
+        const uint32_t n = len[i] + zer[i];
+        if (n) {
+            if (n <= 32u) lb.put(val[i], (int)n);
+            else { lb.zeros(zer[i]); if (len[i]) lb.put(val[i], (int)len[i]); }
+        }
+    }
+    // the incomplete last word of every lane flows to the lanes behind it until one of them completes the word
+    uint32_t v = lb.hi;
+    uint32_t fl = lb.flushed ? 1u : 0u;
+    if (lane == 0 && !lb.flushed) v |= em.carry;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t pv = __shfl_up_sync(FULLMASK, v, o);
+        const uint32_t pf = __shfl_up_sync(FULLMASK, fl, o);
+        if (lane >= o && !fl) { v |= pv; fl = pf; }
+    }
+    uint32_t cin = __shfl_up_sync(FULLMASK, v, 1);
+    if (lane == 0) cin = em.carry;
+    if (lb.flushed) out[start >> 5] = lb.firstw | cin;
+    em.carry = __shfl_sync(FULLMASK, v, 31);
+    em.P += total;
+    __syncwarp();
+}
+
+// subframe header: 0 | type(6) | wasted flag, wasted-bits count in unary, warm-up samples, LPC precision / shift /
+// coefficients, Rice method + partition order -- one field per lane, in stream order
+__device__ __noinline__ void pack_subframe_header(WarpSh &ws, uint32_t *out, Emitter &em, const SubDec &d, const uint32_t *pcm, int lane) {
+    const int type = d.type, order = d.order, wasted = d.wasted, sbps = d.sbps;
+    uint32_t val[2] = { 0, 0 }, len[2] = { 0, 0 }, zer[2] = { 0, 0 };
+    const uint32_t smask = sbps >= 32 ? 0xFFFFFFFFu : ((1u << sbps) - 1u);
+    if (lane == 0) {
+        const uint32_t tcode = type == 0 ? 0u : (type == 1 ? 1u : (type == 2 ? (8u | (uint32_t)order) : (32u | (uint32_t)(order - 1))));
+        val[0] = (tcode << 1) | (wasted ? 1u : 0u); len[0] = 8;
+        if (wasted) { val[1] = 1u; len[1] = 1; zer[1] = (uint32_t)wasted - 1u; }
+    }
+    if (type == 0) {
+        if (lane == 1) { val[0] = pcm[PIDX(0)] & smask; len[0] = (uint32_t)sbps; }
+    } else if (type >= 2) {
+        if (lane >= 1 && lane <= order) { val[0] = (uint32_t)ws.warm[lane - 1] & smask; len[0] = (uint32_t)sbps; }
+        int nxt = order + 1;
+        if (type == 3) {
+            const uint32_t precision = d.precision;
+            if (lane == nxt) { val[0] = ((precision - 1u) << 5) | ((uint32_t)d.shift & 31u); len[0] = 9; }
+            if (lane > nxt && lane <= nxt + order) { val[0] = (uint32_t)(int32_t)d.qlp[lane - nxt - 1] & ((1u << precision) - 1u); len[0] = precision; }
+            nxt += order + 1;
+        }
+        if (lane == nxt) { val[0] = ((d.rice2 ? 1u : 0u) << 4) | (uint32_t)d.po; len[0] = 6; }
+    }
+    emit_fields<2>(out, em, val, len, zer, lane);
+}
+
+// Rice-coded residual section, chunk by chunk: 128 residuals into registers, then their bits into the words behind them
+__device__ __noinline__ void pack_rice(uint32_t *out, Emitter &em, const SubDec &d, uint32_t *pcm, int nsamp, int lane) {
+    const int order = d.order, po = d.po;
+    const int psize = nsamp >> po;
+    const uint32_t pb = d.rice2 ? 5u : 4u;
+    const bool pow2 = (psize & (psize - 1)) == 0;
+    const int psh = 31 - __clz(psize);
+    const int nchunks = (nsamp + BLK - 1) / BLK;
+    for (int c = 0; c < nchunks; c++) {
+        const int g = BLK * c + 4 * lane;
+        const uint4 v = *reinterpret_cast<const uint4 *>(pcm + PIDX(g));
+        __syncwarp();
+        const uint32_t u[4] = { v.x, v.y, v.z, v.w };
+        uint32_t val[5], len[5], zer[5];
+        const int pi = g < nsamp ? (pow2 ? (g >> psh) : (g / psize)) : 0;
+        const uint32_t k = g < nsamp ? d.k[pi] : 0u;
+        const bool pstart = g < nsamp && g == pi * psize;
+        val[0] = k; len[0] = pstart ? pb : 0u; zer[0] = 0;
+        const uint32_t kmask = (1u << k) - 1u;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const bool coded = (g + i) < nsamp && (g + i) >= order;
+            val[1 + i] = (1u << k) | (u[i] & kmask);
+            len[1 + i] = coded ? k + 1u : 0u;
+            zer[1 + i] = coded ? (u[i] >> k) : 0u;
+        }
+        emit_fields<5>(out, em, val, len, zer, lane);
+    }
+}
+// VERBATIM body: the samples as sbps-bit fields
+__device__ __noinline__ void pack_verbatim(uint32_t *out, Emitter &em, const SubDec &d, uint32_t *pcm, int nsamp, int lane) {
+    const uint32_t sbps = d.sbps;
+    const int nchunks = (nsamp + BLK - 1) / BLK;
+    for (int c = 0; c < nchunks; c++) {
+        const int g = BLK * c + 4 * lane;
+        const uint4 v = *reinterpret_cast<const uint4 *>(pcm + PIDX(g));
+        __syncwarp();
+        const uint32_t u[4] = { v.x, v.y, v.z, v.w };
+        const uint32_t smask = sbps >= 32u ? 0xFFFFFFFFu : ((1u << sbps) - 1u);   // sbps <= 32: a side channel is only tried for 16-bit PCM
+        uint32_t val[4], len[4], zer[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) { val[i] = u[i] & smask; len[i] = (g + i) < nsamp ? sbps : 0u; zer[i] = 0; }
+        emit_fields<4>(out, em, val, len, zer, lane);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// CRC-16 of `nw` whole words of the warp buffer (big-endian words): every lane takes a run of Lq 16-byte quads through the
+// 4x256 table, the runs are combined with x^(128 Lq j) mod P.  Warp-uniform result.
+// ------------------------------------------------------------------------------------------
+__device__ __noinline__ uint32_t crc_words(const EncArgs &a, const uint16_t (*tab)[256], const uint32_t *bits, uint32_t nw, int lane) {
+    if (nw == 0) return 0;
+    const uint32_t nq = (nw + 3u) >> 2;
+    const uint32_t Lq = (nq + 31u) / 32u;
+    const uint32_t shift_factor = (uint32_t)__ldg(&a.crc_xpow[(Lq - 1) * 256 + (31 - lane)]);
+    const int padq = (int)(32u * Lq) - (int)nq;                // virtual leading zero quads
+    int q0 = lane * (int)Lq - padq;
+    const int q1 = q0 + (int)Lq;
+    if (q0 < 0) q0 = 0;
+    uint32_t c = 0;
+    for (int qi = q0; qi < q1; qi++) {
+        uint4 wv = *reinterpret_cast<const uint4 *>(bits + 4 * qi);
+        if (qi == (int)nq - 1) {
+            const uint32_t k = nw - 4u * (uint32_t)qi;         // whole words in the last quad (1..4)
+            if (k < 4u) wv.w = 0u;
+            if (k < 3u) wv.z = 0u;
+            if (k < 2u) wv.y = 0u;
+        }
+        uint32_t x = wv.x ^ (c << 16);
+        c = (uint32_t)tab[3][x >> 24] ^ tab[2][(x >> 16) & 0xFFu] ^ tab[1][(x >> 8) & 0xFFu] ^ tab[0][x & 0xFFu];
+        x = wv.y ^ (c << 16);
+        c = (uint32_t)tab[3][x >> 24] ^ tab[2][(x >> 16) & 0xFFu] ^ tab[1][(x >> 8) & 0xFFu] ^ tab[0][x & 0xFFu];
+        x = wv.z ^ (c << 16);
+        c = (uint32_t)tab[3][x >> 24] ^ tab[2][(x >> 16) & 0xFFu] ^ tab[1][(x >> 8) & 0xFFu] ^ tab[0][x & 0xFFu];
+        x = wv.w ^ (c << 16);
+        c = (uint32_t)tab[3][x >> 24] ^ tab[2][(x >> 16) & 0xFFu] ^ tab[1][(x >> 8) & 0xFFu] ^ tab[0][x & 0xFFu];
+    }
+    if (c) c = frx_gf16_mulmod(c, shift_factor);
+    c = __reduce_xor_sync(FULLMASK, c);
+    const uint32_t z = 4u * nq - nw;                           // zero words appended to the last quad
+    if (z && c) c = frx_gf16_mulmod(c, (uint32_t)__ldg(&a.crc_xinv[z]));
+    return c;
+}
+// x^(32 n) mod P
+__device__ __noinline__ uint32_t gf16_xpow32(uint32_t n) {
+    uint32_t r = 1, b = frx_gf16_mulmod(0x8005u, 0x8005u);     // x^16 = 0x8005 (mod P), squared
+    while (n) {
+        if (n & 1u) r = frx_gf16_mulmod(r, b);
+        b = frx_gf16_mulmod(b, b);
+        n >>= 1;
+    }
+    return r;
+}
+// words [0, nw) of the warp buffer -> dst (any byte alignment), big-endian byte order
+__device__ __forceinline__ void copy_words_out(uint8_t *dst, const uint32_t *bits, uint32_t nw, int lane) {
+    const uint32_t nbytes = nw * 4u;
+    const uint32_t head = min(nbytes, (uint32_t)((4u - (uint32_t)((uintptr_t)dst & 3u)) & 3u));
+    if (lane < (int)head) dst[lane] = (uint8_t)((bits[lane >> 2] >> (24 - 8 * (lane & 3))) & 0xFFu);
+    const uint32_t nwords = (nbytes - head) >> 2;
+    uint32_t *dw = reinterpret_cast<uint32_t *>(dst + head);
+    const uint32_t sh8 = head * 8u;
+    for (uint32_t j = lane; j < nwords; j += 32) {
+        const uint32_t w0 = bits[j], w1 = bits[j + 1];
+        const uint32_t v = head ? __funnelshift_l(w1, w0, sh8) : w0;
+        dw[j] = frx_bswap32(v);
+    }
+    const uint32_t tail0 = head + (nwords << 2);
+    if (lane < (int)(nbytes - tail0)) {
+        const uint32_t b = tail0 + (uint32_t)lane;
+        dst[b] = (uint8_t)((bits[b >> 2] >> (24 - 8 * (b & 3))) & 0xFFu);
+    }
+}
