@@ -1,0 +1,43 @@
+"""Assemble csrc/frx_encode.cu from the round-1 file's K0 head and launcher tail (git show) and the v2 parts."""
+import subprocess, sys
+from pathlib import Path
+root = Path(__file__).resolve().parents[2]
+r1 = subprocess.run(["git", "show", "ed1290f:flac_raster_b200/csrc/frx_encode.cu"], capture_output=True, text=True, cwd=root, check=True).stdout.split("\n")
+def find(s):
+    for i, l in enumerate(r1):
+        if s in l:
+            return i
+    raise KeyError(s)
+head = "\n".join(r1[:find("// bit writer into the zero-initialised shared frame buffer") - 1])
+tail = "\n".join(r1[find("// K0+K1 alone (frx_quantize): interleaved int32 PCM of one tile") - 1:])
+head = (Path(__file__).parent / "header.txt").read_text() + head[head.index("#include <math_constants.h>"):]
+head = head.replace("#define HIST FRX_MAX_LPC\n#define NWARPS (FRX_ENC_THREADS / 32)   // compute warps\n", "")
+old = tail[tail.index("size_t frx_enc_smem_bytes"):tail.index("size_t frx_minmax_raw_size()")]
+tail = tail.replace(old, """size_t frx_enc_smem_bytes(int frame_words, int dtype) {
+    (void)frame_words; (void)dtype;
+    return 2048 + (size_t)ENC_WARPS * WARP_BYTES;
+}
+
+""")
+old = tail[tail.index("template <bool WIDE, int HISTN>\nstatic cudaError_t launch_encode_t"):tail.index("cudaError_t frx_launch_encode(")]
+tail = tail.replace(old, """template <bool WIDE, int HISTN>
+static cudaError_t launch_encode_t(const EncArgs &a, int sm_count, cudaStream_t st) {
+    const size_t smem = frx_enc_smem_bytes(0, 0);
+    cudaError_t e = cudaFuncSetAttribute(frx_encode_kernel<WIDE, HISTN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(frx_encode_kernel<WIDE, HISTN>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e != cudaSuccess) return e;
+    // persistent: one CTA of twelve frame warps per SM, tickets hand out the frames in order
+    long long grid = sm_count;
+    const long long need = ((long long)a.total_frames + ENC_WARPS - 1) / ENC_WARPS;
+    if (grid > need) grid = need;
+    if (grid < 1) grid = 1;
+    frx_encode_kernel<WIDE, HISTN><<<(unsigned)grid, ENC_CTA, smem, st>>>(a);
+    return cudaGetLastError();
+}
+
+""")
+tail = tail[:tail.index('#ifdef FRX_DBG\nextern "C" void frx_debug_trace')]
+mid = "".join((Path(__file__).parent / f"mid_{i}.cu").read_text() for i in range(1, 9))
+(root / "flac_raster_b200" / "csrc" / "frx_encode.cu").write_text(head + mid + "\n" + tail)
+print("assembled")
