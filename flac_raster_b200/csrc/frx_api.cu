@@ -34,10 +34,9 @@ struct frx_ctx {
     int device = 0;
     int sm_count = 148;
     uint64_t launches = 0;
-    Buf tiles, prefix, unit_prefix, mmraw, quant, desc, misc, window, xpow, crctab, fsize, foff;
+    Buf tiles, prefix, unit_prefix, mmraw, quant, desc, misc, xpow, crctab, fsize, foff;
     Buf dtiles, dprefix, fpos, flen, stereo, scan_prefix, scan_tiles, ing_chunks, ing_prefix;
     Buf h_raster, h_bytes, h_small, h_out;  // device staging for the *_host entry points
-    int window_len = -1;
     int xpow_L = -1;
     bool crctab_ready = false;
     cudaEvent_t ev[4] = { nullptr, nullptr, nullptr, nullptr };
@@ -127,7 +126,7 @@ int frx_ctx_create(int device, frx_ctx **out) {
 void frx_ctx_destroy(frx_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    Buf *all[] = { &c->tiles, &c->prefix, &c->unit_prefix, &c->mmraw, &c->quant, &c->desc, &c->misc, &c->window, &c->xpow,
+    Buf *all[] = { &c->tiles, &c->prefix, &c->unit_prefix, &c->mmraw, &c->quant, &c->desc, &c->misc, &c->xpow,
                    &c->crctab, &c->fsize, &c->foff, &c->dtiles, &c->dprefix, &c->fpos, &c->flen, &c->stereo, &c->scan_prefix, &c->scan_tiles, &c->ing_chunks, &c->ing_prefix,
                    &c->h_raster, &c->h_bytes, &c->h_small, &c->h_out };
     for (Buf *b : all) if (b->p) cudaFree(b->p);
@@ -174,10 +173,6 @@ static int check_tiles(const frx_tile *tiles, int n, int bands, long long H, lon
             return set_err(FRX_E_INVALID, "tile %d: window/bands outside the raster", i);
     }
     return FRX_OK;
-}
-
-static uint64_t frame_bytes_bound(int channels, int bps, int blocksize) {
-    return 16ull + (uint64_t)channels * (2ull + ((uint64_t)blocksize * bps + 7) / 8 + 1) + 2ull;
 }
 
 int frx_encode_bound(const frx_tile *tiles, int32_t n_tiles, int32_t dtype, const frx_encode_params *p, uint64_t *total_frames,
@@ -293,23 +288,8 @@ int frx_encode_tiles(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *t
     EncPrep prep;
     rc = encode_prepare(c, r, tiles, n_tiles, p, prep, st); if (rc) return rc;
 
-    // window (tukey 0.5, libFLAC's definition) and CRC shift table
-    if (c->window_len != p->blocksize) {
-        std::vector<float> w(p->blocksize, 1.0f);
-        int L = p->blocksize, Np = (int)(0.5f / 2.0f * L) - 1;
-        if (Np > 0)
-            for (int n = 0; n <= Np; n++) {
-                w[n] = (float)(0.5f - 0.5f * cosf((float)(M_PI * n / Np)));
-                w[L - Np - 1 + n] = (float)(0.5f - 0.5f * cosf((float)(M_PI * (n + Np) / Np)));
-            }
-        ENSURE(c->window, sizeof(float) * L);
-        CK(cudaMemcpy(c->window.p, w.data(), sizeof(float) * L, cudaMemcpyHostToDevice));
-        c->window_len = L;
-    }
-    const uint64_t fb = frame_bytes_bound(prep.max_channels, prep.bps, p->blocksize);
-    const int frame_words = (((int)((fb + 3) / 4) + 8) + 3) & ~3;   // multiple of 4: the second frame buffer stays 16-byte aligned
+    const int frame_words = 0;   // (round 1 sized per-CTA frame buffers with this; a frame warp now packs in place)
     { int rc2 = ensure_xpow(c); if (rc2) return rc2; }
-    if (frame_words > FRX_CRC_MAXLQ * 256 * 4) return set_err(FRX_E_UNSUPPORTED, "frame too large for the CRC chunk tables");
     {
         int rc2 = ensure_crctab(c);
         if (rc2) return rc2;
@@ -330,7 +310,7 @@ int frx_encode_tiles(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *t
     memset(&a, 0, sizeof(a));
     a.raster = r.data; a.H = r.height; a.W = r.width; a.band_stride = r.band_stride; a.row_stride = r.row_stride;
     a.tiles = (const frx_tile *)c->tiles.p; a.frame_prefix = (const uint32_t *)c->prefix.p; a.quant = (const FrxQuant *)c->quant.p;
-    a.window = (const float *)c->window.p; a.crc_xpow = (const uint16_t *)c->xpow.p; a.crc_xinv = a.crc_xpow + FRX_CRC_MAXLQ * 256;
+    a.crc_xpow = (const uint16_t *)c->xpow.p; a.crc_xinv = a.crc_xpow + FRX_CRC_MAXLQ * 256;
     a.bytes = out->bytes; a.capacity = out->capacity; a.frame_size = frame_size; a.frame_offset = frame_offset;
     a.desc = (uint64_t *)c->desc.p; a.ticket = (uint32_t *)c->misc.p;
     a.status = out->status ? out->status : (int32_t *)((char *)c->misc.p + 16);
@@ -344,7 +324,10 @@ int frx_encode_tiles(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *t
         const long long esz = frx_dtype_size(r.dtype);
         a.tma_ok = (((uintptr_t)r.data & 15u) == 0 && (r.band_stride * esz) % 16 == 0 && (r.row_stride * esz) % 16 == 0) ? 1 : 0;
     }
-    if (frx_enc_smem_bytes(frame_words, r.dtype) > 227 * 1024) return set_err(FRX_E_UNSUPPORTED, "frame buffer does not fit shared memory");
+    {
+        static const int lvl_ms[9] = { 0, 1, 1, 0, 1, 1, 1, 1, 1 };   // libFLAC presets with mid-side coding (dump:6926-6934)
+        a.stereo = (lvl_ms[p->compression_level] && prep.bps <= 16) ? 1 : 0;
+    }
     CK(cudaEventRecord(c->ev[0], st));
     CK(frx_launch_encode(a, r.dtype, c->sm_count, st));
     CK(cudaEventRecord(c->ev[1], st));

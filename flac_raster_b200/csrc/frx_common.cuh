@@ -7,10 +7,7 @@
 
 #define FRX_MAX_CH 8
 #define FRX_MAX_LPC 12          // libFLAC levels 0..8 never exceed order 12 (dump:6926-6934)
-#define FRX_ENC_THREADS 256     // compute threads of an encoder CTA: one CTA per frame, 16 samples per thread at blocksize 4096
-#define FRX_ENC_CTA 288         // + one control warp (tickets, TMA prefetch, frame header, look-back)
-#define FRX_SPT 16              // samples per thread
-#define FRX_MAX_BLOCK 4096      // FRX_ENC_THREADS * FRX_SPT
+#define FRX_MAX_BLOCK 4096      // largest frame: one warp per frame, 128 samples per lane
 
 struct FrxCtxDev;  // opaque
 

@@ -2,26 +2,24 @@
 //
 // Kernels (SURVEY.md section 8a ids):
 //   K0  frx_minmax_kernel        per-stream min/max                      (converter.py:67-68, 152-153)
-//   K1..K8 frx_encode_kernel     one CTA per 4096-sample frame, persistent grid, ticket-ordered; 8 compute warps plus one
-//        control warp that takes tickets, stages the next raw samples with TMA bulk copies (mbarrier pipeline), builds the
-//        frame header and runs the look-back while the compute warps search, pack and checksum:
-//        K1 tile cut + band->channel gather + PCM quantise            (converter.py:56-86, 185-194; cli.py:691-699)
+//   K1..K8 frx_encode_kernel     one WARP per 4096-sample frame, twelve independent warps per SM, persistent grid,
+//        ticket-ordered:
+//        K1 tile cut + band->channel gather (TMA bulk copies) + PCM quantise   (converter.py:56-86, 185-194; cli.py:691-699)
 //        K2 fixed-order 0..4 trial            K3 windowed autocorrelation
-//        K4 Levinson-Durbin + order pick + coefficient quantisation    K5 residual
-//        K6 Rice partition sums, parameter + partition-order choice    K7 bit packing + CRC-8/16
+//        K4 Levinson-Durbin + order pick + coefficient quantisation    K5 residual (in place)
+//        K6 Rice partition sums, parameter + partition-order choice    K7 bit packing (in place) + CRC-8/16
 //        K8 decoupled look-back over frame sizes -> final byte offset, frame copied straight to its place
 //   frx_tile_index_kernel        per-tile offset/size/minmax from the per-frame table
 //
 // What libFLAC does per frame (process_subframe_; restated in oracle/flac_oracle.c) is kept in spirit:
 // candidates are CONSTANT, VERBATIM, the best FIXED order by sum|e|, and the LPC order picked from the
 // Levinson error curve; each candidate is costed with the partition-sum Rice estimate and the cheapest
-// wins.  The search is our own (the bitstream, not the decisions, is the contract).
+// wins; two-channel streams also try mid and side (left/side, side/right, mid/side).  The search is our own
+// (the bitstream, not the decisions, is the contract).
 #include <math_constants.h>
 
 #include "frx_internal.cuh"
 
-#define HIST FRX_MAX_LPC
-#define NWARPS (FRX_ENC_THREADS / 32)   // compute warps
 
 
 // ------------------------------------------------------------------------------------------
@@ -173,68 +171,38 @@ __global__ void frx_tile_index_kernel(const uint32_t *frame_prefix, const uint32
     }
 }
 
-// ------------------------------------------------------------------------------------------
-// bit writer into the zero-initialised shared frame buffer (big-endian 32-bit words).  A thread's first and
-// last words may be shared with its neighbours (atomicOr); the words in between are its own (plain stores).
-// ------------------------------------------------------------------------------------------
-struct BitW {
-    uint32_t *buf;
-    uint32_t idx;
-    uint64_t acc;
-    int nb;
-    bool first;
-    __device__ __forceinline__ void init(uint32_t *b, uint32_t bitpos) {
-        buf = b; idx = bitpos >> 5; nb = (int)(bitpos & 31u); acc = 0; first = true;
-    }
-    __device__ __forceinline__ void flushword() {
-        uint32_t w = (uint32_t)(acc >> 32);
-        if (first) { if (w) atomicOr(&buf[idx], w); first = false; }
-        else buf[idx] = w;
-        idx++; acc <<= 32; nb -= 32;
-    }
-    // n in 1..32, v < 2^n
-    __device__ __forceinline__ void put(uint32_t v, int n) {
-        acc |= (uint64_t)v << (64 - nb - n);
-        nb += n;
-        if (nb >= 32) flushword();
-    }
-    __device__ __forceinline__ void skip(uint32_t q) {  // q zero bits
-        uint32_t t = (uint32_t)nb + q;
-        if (t >= 32u) {
-            uint32_t w = (uint32_t)(acc >> 32);
-            if (first) { if (w) atomicOr(&buf[idx], w); first = false; }
-            else if (w) buf[idx] = w;
-            idx += t >> 5; nb = (int)(t & 31u); acc = 0;
-        } else nb = (int)t;
-    }
-    __device__ __forceinline__ uint32_t bitpos() const { return idx * 32u + (uint32_t)nb; }
-    __device__ __forceinline__ void finish() {
-        if (nb > 0) {
-            uint32_t w = (uint32_t)(acc >> 32);
-            if (w) atomicOr(&buf[idx], w);
-        }
-    }
-};
-
-// ------------------------------------------------------------------------------------------
-// warp helpers
-// ------------------------------------------------------------------------------------------
+// ==========================================================================================
+// Frame encoder, round 2: ONE WARP PER FRAME, twelve independent warps per SM.
+//
+// A warp owns a 4096-sample frame from ticket to copy-out; nothing in the frame loop is a block-wide barrier.  A lane
+// owns a contiguous block of 128 samples, so every search stage is a register sliding window over shared memory that is
+// read with 16-byte loads, the level-5 Rice partitions ARE the lanes, and all reductions are shuffles.  Per warp the
+// shared memory is one 16.9 KB buffer that holds, in turn and in place: the raw samples as TMA delivered them, the
+// PCM, the zig-zag residuals of the winning predictor, and finally the packed frame (the packer reads a chunk of 128
+// residuals into registers before it writes the bits of that chunk, and the bits never overtake the reader: checked per
+// subframe from the exact bit counts, VERBATIM otherwise).  Frame sizes go through the decoupled look-back as soon as the
+// exact bit count is known, so the byte offset arrives while the frame is being packed and checksummed.
+// ==========================================================================================
 #define FULLMASK 0xFFFFFFFFu
+#define ENC_WARPS 12
+#define ENC_CTA (ENC_WARPS * 32)
+#define SLACK_W 64                                   // words in front of the PCM area: the packed stream runs ahead by its headers
+#define BLK 128                                      // samples per lane block of a full frame = samples per pack chunk
+#define BLK_W (BLK + 4)                              // words per block: 4 words of padding keep 16-byte lane-strided loads conflict-free
+#define PIDX(g) ((g) + 4 * ((g) >> 7))               // word of sample g inside the PCM area
+#define PCM_W (FRX_MAX_BLOCK + 4 * (FRX_MAX_BLOCK / BLK))
+#define WBUF_W (SLACK_W + PCM_W + 12)
+
 __device__ __forceinline__ uint64_t warp_sum_u64(uint64_t v) {
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULLMASK, v, o);
     return v;
 }
-__device__ __forceinline__ double warp_sum_f64(double v) {
+__device__ __forceinline__ float warp_sum_f32(float v) {
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULLMASK, v, o);
     return v;
 }
-// sum of 32 u32 values as u64 with two redux.sync (low / high halves cannot overflow)
-__device__ __forceinline__ uint64_t warp_sum_u32_wide(uint32_t v) {
-    uint32_t lo = __reduce_add_sync(FULLMASK, v & 0xFFFFu);
-    uint32_t hi = __reduce_add_sync(FULLMASK, v >> 16);
-    return (uint64_t)lo + ((uint64_t)hi << 16);
-}
 __device__ __forceinline__ uint32_t zigzag(int32_t r) { return ((uint32_t)r << 1) ^ (uint32_t)(r >> 31); }
+__device__ __forceinline__ uint32_t unzig_abs(uint32_t u) { return (u >> 1) + (u & 1u); }   // |r| of a zig-zag folded residual
 
 // libFLAC-style Rice cost estimate from the partition sum (oracle/flac_oracle.c rice_bits_estimate)
 __device__ __forceinline__ uint64_t rice_estimate(uint32_t k, uint32_t n, uint64_t s) {
@@ -249,89 +217,12 @@ __device__ __forceinline__ uint32_t rice_param(uint32_t n, uint64_t s, uint32_t 
     return (uint32_t)k > kmax ? kmax : (uint32_t)k;
 }
 
-#ifdef FRX_DBG
-__device__ unsigned long long g_frx_dbg[16];
-#define DBG_ADD(i, v) atomicAdd(&g_frx_dbg[i], (unsigned long long)(v))
-#define DBG_CLK() clock64()
-#define DBG_PH(i) do { if (tid == 32 * DBG_PH_WARP) { const long long n_ = clock64(); atomicAdd(&g_frx_dbg[i], (unsigned long long)(n_ - dbg_ph)); dbg_ph = n_; } } while (0)
-#define DBG_PH_DECL long long dbg_ph = clock64()
-#ifndef DBG_PH_WARP
-#define DBG_PH_WARP 2
-#endif
-__device__ unsigned long long *g_frx_trace;   // 8 timestamps per frame
-__device__ __forceinline__ unsigned long long dbg_now() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
-#define DBG_TRACE(f, k) do { if (g_frx_trace) g_frx_trace[(size_t)(f) * 8 + (k)] = dbg_now(); } while (0)
-#define DBG_TRACEV(f, k, v) do { if (g_frx_trace) g_frx_trace[(size_t)(f) * 8 + (k)] = (v); } while (0)
-#else
-#define DBG_ADD(i, v) do {} while (0)
-#define DBG_CLK() 0ll
-#define DBG_PH(i) do {} while (0)
-#define DBG_PH_DECL
-#define DBG_TRACE(f, k) do {} while (0)
-#define DBG_TRACEV(f, k, v) do {} while (0)
-#endif
 // ------------------------------------------------------------------------------------------
-// shared state of one encoder CTA
-// ------------------------------------------------------------------------------------------
-#define FD_SLOTS 4
-#define STOP_FRAME 0xFFFFFFFFu
-#define TABS_BYTES (6 * FRX_ENC_THREADS * 8)     // |e| sums per thread: fixed orders 0..4 + the LPC candidate
-// PCM of the current subframe in shared memory, padded so that a thread's 16-byte chunks at a 64-byte stride fall into
-// distinct bank groups: sample i lives at word PCM_IDX(i); 32 zero samples sit in front (history of the first thread).
-#define PCM_IDX(i) (((i) + 32) + 4 * (((i) + 32) >> 5))
-#define PCM_WORDS 4672
-#define PCM_BYTES (PCM_WORDS * 4)
-
-struct FrameDesc {                               // written by the control warp, read by the compute warps
-    uint32_t f, fj, s0;
-    int32_t nsamp;
-    frx_tile t;
-    uint32_t hdr[4];
-    uint32_t hdr_bits;
-    int32_t tma;                                 // 1: raw samples staged by TMA bulk copies; 0: compute warps gather them
-    int32_t tile_idx;
-    int16_t po_max, max_lpc;                     // largest Rice partition order / LPC order this frame can use
-    FrxQuant q;
-};
-
-struct EncSmall {
-    uint64_t full[1], empty[1];                  // raw stage hand-over (mbarriers): one stage, refilled as soon as K1 has read it
-    uint64_t sized[FD_SLOTS], placed[FD_SLOTS];  // frame size known -> look-back -> byte offset known
-    FrameDesc fd[FD_SLOTS];
-    uint32_t frame_bytes[FD_SLOTS];
-    uint64_t out_offset[FD_SLOTS];
-    // per-subframe decisions
-    int wasted, magbits, fixed_order, is_const, lean;
-    int lpc_ok, lpc_order, shift, precision, lpc_narrow;
-    int32_t qlp[FRX_MAX_LPC];
-    int32_t warm[FRX_MAX_LPC];
-    uint32_t kparam[2][128];                     // candidate 0 = fixed, 1 = lpc; level L's parameters start at (1 << L) - 1
-    uint64_t lvl_bits[2][8];                     // Rice search: estimated bits of partition order L (~0: not evaluated)
-    uint32_t lvl_big[2][8];                      // ... and whether it needs 5-bit parameters (RICE2)
-    // reductions
-    uint64_t wfix[NWARPS][5];
-    uint32_t wor[NWARPS][2];
-    uint32_t wbad[NWARPS][2];
-    float wac[NWARPS][FRX_MAX_LPC + 1];
-    float autoc[FRX_MAX_LPC + 1];
-    float lpc_rows[FRX_MAX_LPC][FRX_MAX_LPC];    // predictor coefficients of every order (Levinson-Durbin by-product)
-    uint32_t scan[NWARPS], scan2[NWARPS];
-    uint32_t crc_part[2][NWARPS];                // per frame buffer
-    uint16_t crc_tab[4][256];
-};
-#define RES_BYTES (FRX_MAX_BLOCK * 4)             // the candidate's residuals, sample-major: res[i * 256 + tid]
-#define RES_IDX(i, tid) ((i) * FRX_ENC_THREADS + (tid))
-#define ENC_SMALL_BYTES ((sizeof(EncSmall) + 127) & ~(size_t)127)
-
-// ------------------------------------------------------------------------------------------
-// mbarrier / TMA (bulk async copy) / named barrier primitives
+// mbarrier / TMA (bulk async copy) primitives
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t *b, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t *b) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
 }
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *b, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
@@ -339,13 +230,6 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *b, uint32_t byte
 __device__ __forceinline__ bool mbar_try_wait(uint64_t *b, uint32_t parity) {
     uint32_t ok;
     asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                 : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
-    return ok != 0;
-}
-// non-blocking probe: try_wait may park the thread for a system-defined time, which a loop polling two barriers cannot afford
-__device__ __forceinline__ bool mbar_test(uint64_t *b, uint32_t parity) {
-    uint32_t ok;
-    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                  : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
     return ok != 0;
 }
@@ -357,235 +241,45 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void compute_sync() { asm volatile("bar.sync 1, %0;" ::"n"(FRX_ENC_THREADS) : "memory"); }
-
-// One warp analyses one candidate: partition sums from the per-thread |r| sums, Rice parameter per partition,
-// estimated bits per partition order, best order.  Lane p owns finest-level partition p (2p, 2p+1 when po_max == 6);
-// coarser levels are built with shuffles, so partition q of level L lives in lane q << (F - L).
-__device__ __noinline__ void analyse_partitions(EncSmall &sh, const uint64_t *tabs, int cand, int nsamp, int pred_order, int po_max, uint32_t kmax, int rsh) {
-    const int lane = threadIdx.x & 31;
-    const int F = po_max > 5 ? 5 : po_max;               // finest level held one-per-lane
-    const int nthr = (nsamp + FRX_SPT - 1) / FRX_SPT;
-    uint64_t sum = 0, sumB = 0;                          // sumB: second half when po_max == 6
-    uint64_t best = ~0ull;
-    int best_po = 0;
-    uint32_t kbest0 = 0, kbest1 = 0;
-    if (po_max == 6) {
-        const int tpp = (nsamp >> 6) / FRX_SPT;          // threads per level-6 partition
-        for (int t = 0; t < tpp; t++) { sum += tabs[(2 * lane) * tpp + t] >> rsh; sumB += tabs[(2 * lane + 1) * tpp + t] >> rsh; }
-        uint32_t n0 = (uint32_t)(nsamp >> 6) - (lane == 0 ? (uint32_t)pred_order : 0u), n1 = (uint32_t)(nsamp >> 6);
-        uint32_t k0 = rice_param(n0, sum, kmax), k1 = rice_param(n1, sumB, kmax);
-        uint64_t b = rice_estimate(k0, n0, sum) + rice_estimate(k1, n1, sumB);
-        b = warp_sum_u64(b) + 6;
-        best = b; best_po = 6; kbest0 = k0; kbest1 = k1;
-        sum += sumB;
-    } else if (F == 0) {
-        for (int t = lane; t < nthr; t += 32) sum += tabs[t] >> rsh;
-        sum = warp_sum_u64(sum);
-    } else {
-        const int tpp = (nsamp >> F) / FRX_SPT;          // threads per finest partition (>= 1)
-        if (lane < (1 << F))
-            for (int t = 0; t < tpp; t++) sum += tabs[lane * tpp + t] >> rsh;
-    }
-    // levels F .. 0
-    for (int L = F; L >= 0; L--) {
-        const int step = 1 << (F - L);                   // lanes that are multiples of step hold level-L partitions
-        const bool mine = (lane & (step - 1)) == 0 && lane < (1 << F);
-        const int p = lane >> (F - L);
-        uint32_t n = (uint32_t)(nsamp >> L) - (p == 0 ? (uint32_t)pred_order : 0u);
-        uint32_t k = 0;
-        uint64_t b = 0;
-        if (mine) { k = rice_param(n, sum, kmax); b = rice_estimate(k, n, sum); }
-        b = warp_sum_u64(b) + 6;
-        if (b < best) { best = b; best_po = L; kbest0 = k; }
-        if (L > 0) {
-            uint64_t o = __shfl_down_sync(FULLMASK, sum, step);
-            sum += o;                                    // valid in lanes that are multiples of 2*step
-        }
-    }
-    // publish in the per-level format pick_level() reads: only the winning level carries a finite cost
-    uint32_t *kp = &sh.kparam[cand][(1 << best_po) - 1];
-    if (best_po == 6) { kp[2 * lane] = kbest0; kp[2 * lane + 1] = kbest1; }
-    else {
-        const int step = 1 << (F - best_po);
-        if ((lane & (step - 1)) == 0 && lane < (1 << F)) kp[lane >> (F - best_po)] = kbest0;
-    }
-    uint32_t big = __ballot_sync(FULLMASK, kbest0 >= 15u || (best_po == 6 && kbest1 >= 15u));
-    if (lane < 8) { sh.lvl_bits[cand][lane] = (lane == best_po) ? best : ~0ull; sh.lvl_big[cand][lane] = big ? 1u : 0u; }
-    __syncwarp();
-}
-
-// The same search for ONE partition order of a full 4096-sample frame (2^L partitions of 256 >> L threads each): the compute
-// warps run it side by side, warp L on level L.  The per-thread |r| sums must fit 32 bits (the lean paths guarantee it).
-__device__ __noinline__ void analyse_level(EncSmall &sh, const uint64_t *tabs, int cand, int L, int pred_order, uint32_t kmax, int rsh) {
-    const int lane = threadIdx.x & 31;
-    const uint32_t nfull = (uint32_t)FRX_MAX_BLOCK >> L;
-    uint32_t *kp = &sh.kparam[cand][(1 << L) - 1];
-    uint64_t bits = 0;
-    uint32_t big = 0;
-    if (L <= 3) {
-        // a row of 32 threads never straddles a partition: reduce the eight rows (lane t keeps row t), then groups of rows
-        uint64_t mine = 0;
-#pragma unroll
-        for (int t = 0; t < 8; t++) {
-            const uint64_t s = warp_sum_u32_wide((uint32_t)(tabs[32 * t + lane] >> rsh));
-            if (lane == t) mine = s;
-        }
-        const int g = 8 >> L;
-        for (int o = 1; o < g; o <<= 1) mine += __shfl_xor_sync(FULLMASK, mine, o);
-        if (lane < 8 && (lane & (g - 1)) == 0) {
-            const int p = lane >> (3 - L);
-            const uint32_t n = nfull - (p == 0 ? (uint32_t)pred_order : 0u);
-            const uint32_t k = rice_param(n, mine, kmax);
-            bits = rice_estimate(k, n, mine);
-            kp[p] = k;
-            big = k >= 15u ? 1u : 0u;
-        }
-    } else {
-        const int T = FRX_ENC_THREADS >> L;            // threads per partition: 16, 8, 4
-        for (int p = lane; p < (1 << L); p += 32) {
-            uint64_t s = 0;
-            for (int i = 0; i < T; i++) s += tabs[p * T + i] >> rsh;
-            const uint32_t n = nfull - (p == 0 ? (uint32_t)pred_order : 0u);
-            const uint32_t k = rice_param(n, s, kmax);
-            bits += rice_estimate(k, n, s);
-            kp[p] = k;
-            big |= k >= 15u ? 1u : 0u;
-        }
-    }
-    bits = warp_sum_u64(bits) + 6;
-    const uint32_t anybig = __ballot_sync(FULLMASK, big != 0u);
-    if (lane == 0) { sh.lvl_bits[cand][L] = bits; sh.lvl_big[cand][L] = anybig ? 1u : 0u; }
-}
-
-// best partition order of a candidate: highest order first, a lower one only when strictly cheaper (libFLAC's loop).
-// Called by whole warps: lane L looks at order L, one redux picks the minimum, the highest lane holding it wins.
-__device__ __forceinline__ void pick_level(const EncSmall &sh, int cand, int po_max, int &po, uint64_t &bits, bool &rice2) {
-    const int lane = threadIdx.x & 31;
-    uint32_t key = 0xFFFFFFFFu, big = 0;
-    if (lane <= po_max) {
-        const uint64_t b = sh.lvl_bits[cand][lane];
-        key = b < 0xFFFFFFFEull ? (uint32_t)b : 0xFFFFFFFEu;
-        big = sh.lvl_big[cand][lane];
-    }
-    const uint32_t m = __reduce_min_sync(FULLMASK, key);
-    const int bp = 31 - __clz((int)(__ballot_sync(FULLMASK, key == m) & 0xFFu));
-    po = bp; bits = m; rice2 = __shfl_sync(FULLMASK, big, bp) != 0u;
-}
-// ------------------------------------------------------------------------------------------
-// K1: raw staging buffer -> PCM in shared memory.  Thread t owns samples [16t, 16t+16).
-// ------------------------------------------------------------------------------------------
-template <int NWORDS>
-__device__ __forceinline__ void lds_words16(const unsigned char *p, uint32_t *w) {   // p is 16-byte aligned (or 8/4 for short rows)
-    if (NWORDS % 4 == 0) {
-#pragma unroll
-        for (int k = 0; k < NWORDS / 4; k++) {
-            const uint4 v = *reinterpret_cast<const uint4 *>(p + 16 * k);
-            w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
-        }
-    } else {
-#pragma unroll
-        for (int k = 0; k < NWORDS; k++) w[k] = *reinterpret_cast<const uint32_t *>(p + 4 * k);
-    }
-}
-template <int DT>
-__device__ __forceinline__ typename FrxElem<DT>::T elem_of(const uint32_t *w, int i) {
-    typedef typename FrxElem<DT>::T T;
-    if (sizeof(T) == 4) {
-        if (DT == FRX_F32) return (T)__uint_as_float(w[i]);
-        return (T)w[i];
-    } else if (sizeof(T) == 2) {
-        return (T)((w[i >> 1] >> ((i & 1) * 16)) & 0xFFFFu);
-    } else {
-        return (T)((w[i >> 2] >> ((i & 3) * 8)) & 0xFFu);
-    }
-}
-
-// the thread's 16 raw elements -> 16 PCM samples (registers)
-template <int DT>
-__device__ __forceinline__ void quantize_own(const unsigned char *stage, const FrxQuant &qz, int mode, int tid, int32_t *x) {
-    typedef typename FrxElem<DT>::T T;
-    constexpr int ESZ = (int)sizeof(T);
-    constexpr int OW = FRX_SPT * ESZ / 4;
-    uint32_t w[OW];
-    lds_words16<OW>(stage + (size_t)(FRX_SPT * tid) * ESZ, w);
-    if (mode == FRX_PCM_REFERENCE) {
-#pragma unroll
-        for (int i = 0; i < FRX_SPT; i++) x[i] = frx_quant_ref<DT>(elem_of<DT>(w, i), qz);
-    } else if (mode == FRX_PCM_LOSSLESS) {
-#pragma unroll
-        for (int i = 0; i < FRX_SPT; i++) x[i] = frx_quant_lossless<DT>(elem_of<DT>(w, i));
-    } else {
-#pragma unroll
-        for (int i = 0; i < FRX_SPT; i++) x[i] = frx_quant_spatial<DT>(elem_of<DT>(w, i));
-    }
-}
-// K1 for one thread: quantise, zero what lies behind a short frame, store to the padded PCM buffer;
-// returns (OR of the samples, OR of their magnitudes) for the wasted-bits / magnitude decisions
-template <int DT, bool WIDE>
-__device__ __forceinline__ uint2 k1_quantize(const unsigned char *stage, const FrxQuant &qz, int mode, int tid, int nv, int32_t *pcm) {
-    int32_t x[FRX_SPT];
-    quantize_own<DT>(stage, qz, mode, tid, x);
-    uint32_t orv = 0, ora = 0;
-#pragma unroll
-    for (int i = 0; i < FRX_SPT; i++) {
-        if (i >= nv) x[i] = 0;
-        orv |= (uint32_t)x[i];
-        if (WIDE) ora |= (uint32_t)(x[i] ^ (x[i] >> 31));
-    }
-#pragma unroll
-    for (int k = 0; k < FRX_SPT / 4; k++)
-        *reinterpret_cast<int4 *>(pcm + PCM_IDX(FRX_SPT * tid + 4 * k)) = make_int4(x[4 * k], x[4 * k + 1], x[4 * k + 2], x[4 * k + 3]);
-    return make_uint2(orv, ora);
-}
-template <bool WIDE>
-__device__ __noinline__ uint2 k1_quantize_any(int dtype, const unsigned char *stage, const FrxQuant &qz, int mode, int tid, int nv, int32_t *pcm) {
-    switch (dtype) {   // the dtypes the benchmarks do not use share one out-of-line copy
-        case FRX_U8: return k1_quantize<FRX_U8, WIDE>(stage, qz, mode, tid, nv, pcm);
-        case FRX_I16: return k1_quantize<FRX_I16, WIDE>(stage, qz, mode, tid, nv, pcm);
-        case FRX_I32: return k1_quantize<FRX_I32, WIDE>(stage, qz, mode, tid, nv, pcm);
-        default: return k1_quantize<FRX_U32, WIDE>(stage, qz, mode, tid, nv, pcm);
-    }
-}
-
-// PCM shared memory -> registers: HISTN samples of history + the thread's 16 samples, arithmetic shift by `sh`
-template <int HISTN>
-__device__ __forceinline__ void read_pcm(const int32_t *pcm, int tid, int sh, int32_t *s) {
-    const int base = FRX_SPT * tid - HISTN;   // multiple of 4
-#pragma unroll
-    for (int k = 0; k < (HISTN + FRX_SPT) / 4; k++) {
-        const int4 v = *reinterpret_cast<const int4 *>(pcm + PCM_IDX(base + 4 * k));
-        s[4 * k] = v.x >> sh; s[4 * k + 1] = v.y >> sh; s[4 * k + 2] = v.z >> sh; s[4 * k + 3] = v.w >> sh;
-    }
-}
-
-// generic gather (edge tiles whose rows are not 16-byte multiples): coalesced element loads into the raw stage
-template <int DT>
-__device__ __forceinline__ void gather_raw_t(const EncArgs &a, const frx_tile &t, int ch, uint32_t s0, int nsamp, unsigned char *stage, int tid) {
-    typedef typename FrxElem<DT>::T T;
-    const T *band = (const T *)a.raster + (long long)(t.first_band + ch) * a.band_stride + (long long)t.row_off * a.row_stride + t.col_off;
-    T *dst = reinterpret_cast<T *>(stage);
-    const uint32_t w = (uint32_t)t.w;
-    uint32_t sidx = s0 + (uint32_t)tid;
-    uint32_t row = sidx / w, col = sidx - row * w;
-    for (int i = tid; i < nsamp; i += FRX_ENC_THREADS) {
-        dst[i] = __ldg(band + (long long)row * a.row_stride + col);
-        col += FRX_ENC_THREADS;
-        if (col >= w) { const uint32_t q = col / w; row += q; col -= q * w; }
-    }
-}
-__device__ __noinline__ void gather_raw(const EncArgs &a, const frx_tile &t, int ch, uint32_t s0, int nsamp, unsigned char *stage, int tid) {
-    switch (frx_dtype_size(a.dtype)) {   // a pure move: only the element size matters
-        case 1: gather_raw_t<FRX_U8>(a, t, ch, s0, nsamp, stage, tid); break;
-        case 2: gather_raw_t<FRX_U16>(a, t, ch, s0, nsamp, stage, tid); break;
-        default: gather_raw_t<FRX_U32>(a, t, ch, s0, nsamp, stage, tid); break;
-    }
-}
 
 // ------------------------------------------------------------------------------------------
-// control warp pieces
+// per-warp shared state
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ int frame_header_bytes(uint8_t *hb, int nsamp, int sr_code, int sample_rate, int channels, int bps, uint32_t fj) {
+struct FrameDesc {
+    uint32_t f, fj;
+    long long s0;                                // first sample of the frame inside its tile (row-major), 64-bit: tiles may hold >= 2^32 samples
+    int32_t nsamp;
+    frx_tile t;
+    uint32_t hdr[4];
+    uint32_t hdr_bits;
+    int32_t tma;                                 // 1: rows are 16-byte multiples, raw samples staged by TMA bulk copies
+    int32_t tile_idx;
+    int16_t po_max, max_lpc;                     // largest Rice partition order / LPC order this frame can use
+    FrxQuant q;
+};
+struct SubDec {                                  // decision record of one subframe
+    uint8_t type, order, wasted, po, rice2, precision, sbps, vch;   // type: 0 CONSTANT 1 VERBATIM 2 FIXED 3 LPC; vch: virtual channel
+    uint8_t fast, narrow, pad0, pad1;            // fast: full frame of lean data (blocked 32-bit passes); narrow: 32-bit LPC accumulate
+    int32_t shift;
+    uint32_t bits;                               // exact size of the subframe
+    int16_t qlp[FRX_MAX_LPC];
+    uint8_t k[64];
+};
+struct WarpSh {
+    uint64_t mbar;
+    FrameDesc fd;
+    int32_t qlp[FRX_MAX_LPC];
+    int32_t warm[FRX_MAX_LPC];
+    uint8_t kparam[2][64];                       // candidate 0 = fixed, 1 = lpc; parameters of the candidate's best partition order
+    SubDec dec[FRX_MAX_CH];
+};
+#define WARP_SH_BYTES ((sizeof(WarpSh) + 127) & ~(size_t)127)
+#define WARP_BYTES (WARP_SH_BYTES + ((WBUF_W * 4 + 127) & ~(size_t)127))
+
+// ------------------------------------------------------------------------------------------
+// frame header, frame descriptor
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ int frame_header_bytes(uint8_t *hb, int nsamp, int sr_code, int sample_rate, int chan_code, int bps, uint32_t fj) {
     int n = 0, bs_code, bs_extra = 0;
     switch (nsamp) {
         case 192: bs_code = 1; break; case 576: bs_code = 2; break; case 1152: bs_code = 3; break;
@@ -598,7 +292,7 @@ __device__ __forceinline__ int frame_header_bytes(uint8_t *hb, int nsamp, int sr
     const int sz_code = bps == 16 ? 4 : (bps == 32 ? 7 : (bps == 8 ? 1 : (bps == 24 ? 6 : 0)));
     hb[n++] = 0xFF; hb[n++] = 0xF8;
     hb[n++] = (uint8_t)((bs_code << 4) | sr_code);
-    hb[n++] = (uint8_t)(((channels - 1) << 4) | (sz_code << 1));
+    hb[n++] = (uint8_t)((chan_code << 4) | (sz_code << 1));
     const uint32_t v = fj;
     if (v < 0x80u) hb[n++] = (uint8_t)v;
     else if (v < 0x800u) { hb[n++] = (uint8_t)(0xC0 | (v >> 6)); hb[n++] = (uint8_t)(0x80 | (v & 0x3F)); }
@@ -615,9 +309,18 @@ __device__ __forceinline__ int frame_header_bytes(uint8_t *hb, int nsamp, int sr
     for (int i = n; i < 16; i++) hb[i] = 0;
     return n;
 }
+// header words of the frame for a channel-assignment code (0..7 independent, 8 left/side, 9 side/right, 10 mid/side)
+__device__ __noinline__ void make_frame_header(const EncArgs &a, FrameDesc &d, int chan_code) {
+    uint8_t hb[16];
+    const int n = frame_header_bytes(hb, d.nsamp, a.sr_code, a.sample_rate, chan_code, a.bps, d.fj);
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+        d.hdr[k] = ((uint32_t)hb[4 * k] << 24) | ((uint32_t)hb[4 * k + 1] << 16) | ((uint32_t)hb[4 * k + 2] << 8) | hb[4 * k + 3];
+    d.hdr_bits = (uint32_t)n * 8u;
+}
 
-// control warp: everything the compute warps need to know about frame f.  The lanes probe 32 tile boundaries at once
-// and fetch the tile and its quantiser words side by side, so the whole descriptor costs two memory round trips.
+// Everything the warp needs to know about frame f.  The lanes probe 32 tile boundaries at once and fetch the tile and its
+// quantiser words side by side, so the whole descriptor costs two memory round trips.
 __device__ __noinline__ void build_frame_desc(const EncArgs &a, FrameDesc &d, uint32_t f, int &ti, int lane) {
     {
         const int cand = ti + 1 + lane;
@@ -646,41 +349,34 @@ __device__ __noinline__ void build_frame_desc(const EncArgs &a, FrameDesc &d, ui
     if (lane == 0) {
         const frx_tile t = d.t;
         const long long tile_n = (long long)t.h * t.w;
-        const uint32_t s0 = fj * (uint32_t)a.blocksize;
-        const int nsamp = (int)min((long long)a.blocksize, tile_n - (long long)s0);
+        const long long s0 = (long long)fj * (long long)a.blocksize;
+        const int nsamp = (int)min((long long)a.blocksize, tile_n - s0);
         d.f = f; d.fj = fj; d.s0 = s0; d.nsamp = nsamp; d.tile_idx = ti;
         {
             const int tz = __ffs(nsamp) - 1;               // trailing zeros of the block size
             int po_max = min(a.max_po, max(0, tz - 4));    // partitions stay multiples of 16 samples
             while (po_max > 0 && (nsamp >> po_max) <= FRX_MAX_LPC) po_max--;
+            if (nsamp != FRX_MAX_BLOCK && po_max > 5) po_max = 5;   // short frames: the partition bins hold 32 sums
             d.po_max = (int16_t)po_max;
             d.max_lpc = (int16_t)min(a.max_lpc_order, nsamp - 1);
         }
         const int epv = 16 / frx_dtype_size(a.dtype);            // elements per 16 bytes
-        d.tma = (a.tma_ok && (t.w % epv) == 0 && (t.col_off % epv) == 0) ? 1 : 0;
-        uint8_t hb[16];
-        const int n = frame_header_bytes(hb, nsamp, a.sr_code, a.sample_rate, t.n_channels, a.bps, fj);
-#pragma unroll
-        for (int k = 0; k < 4; k++)
-            d.hdr[k] = ((uint32_t)hb[4 * k] << 24) | ((uint32_t)hb[4 * k + 1] << 16) | ((uint32_t)hb[4 * k + 2] << 8) | hb[4 * k + 3];
-        d.hdr_bits = (uint32_t)n * 8u;
+        d.tma = (a.tma_ok && (t.w % epv) == 0 && (t.col_off % epv) == 0 && (a.blocksize % epv) == 0) ? 1 : 0;
+        make_frame_header(a, d, t.n_channels - 1);
     }
     __syncwarp();
 }
 
-// K8: decoupled look-back over the frame sizes (whole control warp).  A descriptor word carries flag and value
-// together (A: the frame's size, P: the inclusive byte prefix), so relaxed device-scope accesses are enough.  The compute
-// warps publish A themselves as soon as the size is final; here 512 descriptors are examined per round trip (16
-// consecutive ones per lane, nearest first).  When the walk meets a frame that has not published yet, only that single
-// word is polled -- re-reading the window would hammer the L2 slice the publishers store to -- and the walk is resumable,
-// so the control warp keeps feeding the raw-sample pipeline while it waits.
+// K8: decoupled look-back over the frame sizes (whole warp).  A descriptor word carries flag and value together (A: the
+// frame's size, P: the inclusive byte prefix), so relaxed device-scope accesses are enough.  512 descriptors are examined
+// per round trip (16 consecutive ones per lane, nearest first).  When the walk meets a frame that has not published yet,
+// only that single word is polled.
 #define LB_PER_LANE 16
 struct LookBack {
     long long pos;        // nearest descriptor not yet accounted for
     uint64_t exclusive;   // bytes summed so far
     bool blocked;         // desc[pos] had not been published at the last visit
 };
-// one step; true when the exclusive prefix is complete
 __device__ __noinline__ bool lookback_step(const EncArgs &a, LookBack &lb, int lane) {
     const uint64_t FLAG_P = 2ull << 62, VMASK = (1ull << 62) - 1;
     if (lb.pos < 0) return true;
@@ -691,7 +387,6 @@ __device__ __noinline__ bool lookback_step(const EncArgs &a, LookBack &lb, int l
         if ((w >> 62) == 0ull) return false;
         lb.blocked = false;
     }
-    if (lane == 0) DBG_ADD(3, 1);
     uint64_t v[LB_PER_LANE];
     const long long base = lb.pos - (long long)lane * LB_PER_LANE;
 #pragma unroll
@@ -699,7 +394,6 @@ __device__ __noinline__ bool lookback_step(const EncArgs &a, LookBack &lb, int l
         const long long idx = base - k;
         v[k] = idx >= 0 ? frx_ld_relaxed_u64(&a.desc[idx]) : FLAG_P;
     }
-    // per lane: walk its 16 entries nearest-first up to the first inclusive prefix (P) or the first one not ready
     uint64_t sum = 0;
     int state = 0;                     // 0: all 16 ready, no P   1: stopped at a P   2: stopped at a not-ready entry
     int taken = 0;
@@ -713,7 +407,6 @@ __device__ __noinline__ bool lookback_step(const EncArgs &a, LookBack &lb, int l
     }
     const uint32_t mP = __ballot_sync(FULLMASK, state == 1), mN = __ballot_sync(FULLMASK, state == 2);
     const int firstP = mP ? (__ffs((int)mP) - 1) : 32, firstN = mN ? (__ffs((int)mN) - 1) : 32;
-    // lanes before the first stopper contribute everything; the stopper contributes what it took
     const int stop = min(firstP, firstN);
     lb.exclusive += warp_sum_u64((lane <= stop) ? sum : 0ull);
     if (firstP < firstN) return true;  // reached an inclusive prefix
@@ -721,292 +414,200 @@ __device__ __noinline__ bool lookback_step(const EncArgs &a, LookBack &lb, int l
         const int tk = __shfl_sync(FULLMASK, taken, firstN);
         lb.pos -= (long long)firstN * LB_PER_LANE + tk;      // the frame that has not published its size yet
         lb.blocked = true;
-        if (lane == 0) DBG_ADD(4, 1);
     } else lb.pos -= 32 * LB_PER_LANE;
     return false;
 }
 
-// The control warp's event loop.  A CTA works on one frame and has at most the next one staged; the next ticket is
-// taken only when the current frame's size has been published, because a ticket that is reserved but not yet sized
-// holds up the look-back of every later frame (and convoys of such tickets serialise the whole grid).
-__device__ __noinline__ void control_warp(const EncArgs &a, EncSmall &sh, unsigned char *raw, int lane) {
-    const int esz = frx_dtype_size(a.dtype);
-    uint32_t unit_iss = 0, fseq_iss = 0, fseq_lb = 0;
-    int ch_iss = 0, nch_cur = 0, ti = 0;
-    bool have_frame = false, want_frame = true, stop_issued = false, lb_active = false;
-    LookBack lb;
-    lb.pos = -1; lb.exclusive = 0; lb.blocked = false;
-    for (;;) {
-        bool progress = false;
-        // ---- 1. a frame's size became known: get the next frame going, then start this frame's look-back ----
-        if (!lb_active && fseq_lb < fseq_iss) {
-            const int slot = (int)(fseq_lb & (FD_SLOTS - 1));
-            if (mbar_test(&sh.sized[slot], (fseq_lb / FD_SLOTS) & 1u)) {
-                if (!stop_issued) want_frame = true;
-                lb.pos = (long long)sh.fd[slot].f - 1;
-                lb.exclusive = 0; lb.blocked = false;
-                lb_active = true;
-                if (lane == 0) DBG_TRACE(sh.fd[slot].f, 2);
-                progress = true;
-            }
-        }
-        // ---- 2. next unit (frame, channel) into the raw stage ring ----
-        if (have_frame || want_frame) {
-            const int stage = 0;
-            if (mbar_test(&sh.empty[stage], (unit_iss & 1u) ^ 1u)) {
-                progress = true;
-                if (!have_frame) {
-                    const int slot = (int)(fseq_iss & (FD_SLOTS - 1));
-                    uint32_t ticket = 0;
-                    if (lane == 0) ticket = atomicAdd(a.ticket, 1u);
-                    ticket = __shfl_sync(FULLMASK, ticket, 0);
-                    want_frame = false;
-                    if (ticket >= a.total_frames) {
-                        if (lane == 0) { sh.fd[slot].f = STOP_FRAME; mbar_arrive(&sh.full[stage]); }
-                        __syncwarp();
-                        stop_issued = true;
-                    } else {
-                        build_frame_desc(a, sh.fd[slot], ticket, ti, lane);
-                        if (lane == 0) { DBG_TRACE(ticket, 0); DBG_TRACEV(ticket, 6, blockIdx.x); }
-                        nch_cur = sh.fd[slot].t.n_channels;
-                        have_frame = true;
-                        ch_iss = 0;
-                    }
-                }
-                if (have_frame) {
-                    const FrameDesc &d = sh.fd[fseq_iss & (FD_SLOTS - 1)];
-                    unsigned char *dst = raw;
-                    if (d.tma) {
-                        const long long w = d.t.w;
-                        const long long s0 = d.s0, s1 = s0 + d.nsamp;
-                        const long long row0 = s0 / w, row1 = (s1 - 1) / w;
-                        const unsigned char *band = (const unsigned char *)a.raster +
-                            ((long long)(d.t.first_band + ch_iss) * a.band_stride + (long long)d.t.row_off * a.row_stride + d.t.col_off) * esz;
-                        if (lane == 0) mbar_arrive_expect_tx(&sh.full[stage], (uint32_t)d.nsamp * (uint32_t)esz);
-                        __syncwarp();
-                        for (long long r = row0 + lane; r <= row1; r += 32) {
-                            const long long b0 = max(s0, r * w), b1 = min(s1, (r + 1) * w);
-                            bulk_g2s(dst + (b0 - s0) * esz, band + (r * a.row_stride + (b0 - r * w)) * esz, (uint32_t)((b1 - b0) * esz), &sh.full[stage]);
-                        }
-                    } else if (lane == 0) {
-                        mbar_arrive(&sh.full[stage]);
-                    }
-                    __syncwarp();
-                    unit_iss++;
-                    if (++ch_iss == nch_cur) { have_frame = false; fseq_iss++; }
-                }
-            }
-        }
-        // ---- 3. the look-back in flight ----
-        if (lb_active) {
-            if (lookback_step(a, lb, lane)) {
-                const int slot = (int)(fseq_lb & (FD_SLOTS - 1));
-                if (lane == 0) {
-                    const uint32_t f = sh.fd[slot].f;
-                    const uint32_t nbytes = sh.frame_bytes[slot];
-                    const uint64_t off = lb.exclusive;
-                    frx_st_relaxed_u64(&a.desc[f], (2ull << 62) | (off + (uint64_t)nbytes));
-                    sh.out_offset[slot] = off;
-                    if (a.frame_size) a.frame_size[f] = nbytes;
-                    if (a.frame_offset) a.frame_offset[f] = off;
-                    if (f == a.total_frames - 1 && a.total_bytes) *a.total_bytes = off + nbytes;
-                    DBG_TRACE(f, 3);
-                    DBG_ADD(6, 1);
-                    mbar_arrive(&sh.placed[slot]);
-                }
-                __syncwarp();
-                lb_active = false;
-                fseq_lb++;
-                progress = true;
-            } else if (!lb.blocked) progress = true;
-        }
-        if (stop_issued && !lb_active && fseq_lb == fseq_iss) break;
-        if (!progress) __nanosleep(200);
-    }
-}
-// residual of one sample, lean paths (no overflow possible by construction)
-template <int ORD>
-__device__ __forceinline__ int32_t lpc_res32(const int32_t *s, int i, const int32_t *q, int shift) {
-    int32_t acc = 0;
-#pragma unroll
-    for (int j = 0; j < ORD; j++) acc += q[j] * s[i - 1 - j];
-    return s[i] - (acc >> shift);
-}
-template <int ORD>
-__device__ __forceinline__ long long lpc_res64(const int32_t *s, int i, const int32_t *q, int shift) {
-    long long acc = 0;
-#pragma unroll
-    for (int j = 0; j < ORD; j++) acc += (long long)q[j] * (long long)s[i - 1 - j];
-    return (long long)s[i] - (acc >> shift);
+// ------------------------------------------------------------------------------------------
+// K1: raw samples -> PCM in the warp buffer.  Virtual channel vch: 0..7 = band first_band + vch; for two-channel stereo
+// trials 8 = mid ((L+R)>>1), 9 = side (L-R).
+// ------------------------------------------------------------------------------------------
+template <int DT>
+__device__ __forceinline__ int32_t quant_one(typename FrxElem<DT>::T v, const FrxQuant &qz, int mode) {
+    if (mode == FRX_PCM_REFERENCE) return frx_quant_ref<DT>(v, qz);
+    if (mode == FRX_PCM_LOSSLESS) return frx_quant_lossless<DT>(v);
+    return frx_quant_spatial<DT>(v);
 }
 
-// All 16 residuals of this thread for LPC order ORD.  MODE 0: 32-bit accumulate, 1: 64-bit accumulate (result
-// known to fit), 2: 64-bit with range check (fat data).  Returns a bitmask of samples whose residual does not fit.
-template <int ORD, int MODE, int HISTN>
-__device__ __forceinline__ uint32_t lpc_residuals(const int32_t *s, const int32_t *q, int shift, int32_t *r) {
-    uint32_t bad = 0;
+// in-place expansion of one block: raw elements sit end-aligned in the block's first 512 bytes + 16, PCM words grow from
+// its start (a 16-byte read is always ahead of the words written so far)
+template <int DT>
+__device__ __forceinline__ void quantize_block(uint32_t *blk, const FrxQuant &qz, int mode, int nvalid, uint32_t &orv, uint32_t &ora) {
+    typedef typename FrxElem<DT>::T T;
+    constexpr int ESZ = (int)sizeof(T);
+    constexpr int EPV = 16 / ESZ;                           // elements per 16-byte load
+    const unsigned char *raw = reinterpret_cast<const unsigned char *>(blk) + (BLK_W * 4 - 16 - BLK * ESZ);
+#pragma unroll 2
+    for (int t = 0; t < BLK / EPV; t++) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(raw + 16 * t);
+        T e[EPV];
+        memcpy(e, &v, 16);
+        int32_t x[EPV];
 #pragma unroll
-    for (int i = 0; i < FRX_SPT; i++) {
-        if (MODE == 0) r[i] = lpc_res32<ORD>(s, HISTN + i, q, shift);
-        else {
-            long long rr = lpc_res64<ORD>(s, HISTN + i, q, shift);
-            if (MODE == 2 && (rr <= (long long)INT32_MIN || rr > (long long)INT32_MAX)) bad |= 1u << i;
-            r[i] = (int32_t)rr;
+        for (int i = 0; i < EPV; i++) {
+            x[i] = quant_one<DT>(e[i], qz, mode);
+            if (t * EPV + i >= nvalid) x[i] = 0;
+            orv |= (uint32_t)x[i];
+            ora |= (uint32_t)(x[i] ^ (x[i] >> 31));
         }
-    }
-    return bad;
-}
-// Lean K5: residuals of the thread's 16 samples with all HISTN taps (coefficients beyond the order are zero), parked in the
-// shared residual buffer as they are produced; returns the thread's sum of |r| over the samples that will be coded.
-template <int MODE, int HISTN>
-__device__ __forceinline__ uint32_t lpc_residuals_park(const int32_t *s, const int32_t *q, int shift, int32_t *res, int tid, bool plain, int nv,
-                                                       int first_coded) {
-    uint32_t ab = 0;
 #pragma unroll
-    for (int i = 0; i < FRX_SPT; i++) {
-        const int32_t rr = MODE == 0 ? lpc_res32<HISTN>(s, HISTN + i, q, shift) : (int32_t)lpc_res64<HISTN>(s, HISTN + i, q, shift);
-        res[RES_IDX(i, tid)] = rr;
-        if (plain || (i < nv && i >= first_coded)) ab += (uint32_t)abs(rr);
+        for (int i = 0; i < EPV / 4; i++)
+            *reinterpret_cast<uint4 *>(blk + t * EPV + 4 * i) = make_uint4((uint32_t)x[4 * i], (uint32_t)x[4 * i + 1], (uint32_t)x[4 * i + 2], (uint32_t)x[4 * i + 3]);   // same type as the read: ordered
     }
-    return ab;
 }
-template <int MODE, int HISTN>
-__device__ __forceinline__ uint32_t lpc_residuals_dispatch(int order, const int32_t *s, const int32_t *q, int shift, int32_t *r) {
-    switch (order) {
-        case 1: return lpc_residuals<1, MODE, HISTN>(s, q, shift, r);
-        case 2: return lpc_residuals<2, MODE, HISTN>(s, q, shift, r);
-        case 3: return lpc_residuals<3, MODE, HISTN>(s, q, shift, r);
-        case 4: return lpc_residuals<4, MODE, HISTN>(s, q, shift, r);
-        default: break;
+__device__ __noinline__ void quantize_block_any(int dtype, uint32_t *blk, const FrxQuant &qz, int mode, int nvalid, uint32_t &orv, uint32_t &ora) {
+    switch (dtype) {   // the dtypes the benchmarks do not use share one out-of-line copy
+        case FRX_U8: quantize_block<FRX_U8>(blk, qz, mode, nvalid, orv, ora); break;
+        case FRX_I16: quantize_block<FRX_I16>(blk, qz, mode, nvalid, orv, ora); break;
+        case FRX_I32: quantize_block<FRX_I32>(blk, qz, mode, nvalid, orv, ora); break;
+        default: quantize_block<FRX_U32>(blk, qz, mode, nvalid, orv, ora); break;
     }
-    if (HISTN >= 8) {
-        switch (order) {
-            case 5: return lpc_residuals<5, MODE, HISTN>(s, q, shift, r);
-            case 6: return lpc_residuals<6, MODE, HISTN>(s, q, shift, r);
-            case 7: return lpc_residuals<7, MODE, HISTN>(s, q, shift, r);
-            case 8: return lpc_residuals<8, MODE, HISTN>(s, q, shift, r);
-            default: break;
-        }
-    }
-    if (HISTN >= 12) {
-        switch (order) {
-            case 9: return lpc_residuals<9, MODE, HISTN>(s, q, shift, r);
-            case 10: return lpc_residuals<10, MODE, HISTN>(s, q, shift, r);
-            case 11: return lpc_residuals<11, MODE, HISTN>(s, q, shift, r);
-            default: return lpc_residuals<12, MODE, HISTN>(s, q, shift, r);
-        }
-    }
-    return 0;
 }
 
-// fixed-order residuals; WIDE64: 64-bit with range check
-template <bool WIDE64, int HISTN>
-__device__ __forceinline__ uint32_t fixed_residuals(int order, const int32_t *s, int32_t *r) {
-    uint32_t bad = 0;
-#pragma unroll
-    for (int i = 0; i < FRX_SPT; i++) {
-        const int32_t *p = s + HISTN + i;
-        if (WIDE64) {
-            long long A = p[0], B = p[-1], C = p[-2], D = p[-3], E = p[-4], rr;
-            switch (order) {
-                case 0: rr = A; break;
-                case 1: rr = A - B; break;
-                case 2: rr = A - 2 * B + C; break;
-                case 3: rr = A - 3 * B + 3 * C - D; break;
-                default: rr = A - 4 * B + 6 * C - 4 * D + E; break;
-            }
-            if (rr <= (long long)INT32_MIN || rr > (long long)INT32_MAX) bad |= 1u << i;
-            r[i] = (int32_t)rr;
-        } else {
-            int32_t A = p[0], B = p[-1], C = p[-2], D = p[-3], E = p[-4], rr;
-            switch (order) {
-                case 0: rr = A; break;
-                case 1: rr = A - B; break;
-                case 2: rr = A - 2 * B + C; break;
-                case 3: rr = A - 3 * B + 3 * C - D; break;
-                default: rr = A - 4 * B + 6 * C - 4 * D + E; break;
-            }
-            r[i] = rr;
-        }
+template <int DT>
+__device__ __forceinline__ int32_t gather_one(const EncArgs &a, const FrameDesc &d, int band, long long t) {
+    typedef typename FrxElem<DT>::T T;
+    const long long row = t / d.t.w, col = t - row * d.t.w;
+    const T *p = (const T *)a.raster + (long long)band * a.band_stride + ((long long)d.t.row_off + row) * a.row_stride + d.t.col_off + col;
+    return quant_one<DT>(__ldg(p), d.q, a.pcm_mode);
+}
+__device__ __noinline__ int32_t gather_any(const EncArgs &a, const FrameDesc &d, int band, long long t) {
+    switch (a.dtype) {
+        case FRX_U8: return gather_one<FRX_U8>(a, d, band, t);
+        case FRX_I16: return gather_one<FRX_I16>(a, d, band, t);
+        case FRX_U16: return gather_one<FRX_U16>(a, d, band, t);
+        case FRX_I32: return gather_one<FRX_I32>(a, d, band, t);
+        case FRX_U32: return gather_one<FRX_U32>(a, d, band, t);
+        default: return gather_one<FRX_F32>(a, d, band, t);
     }
-    return bad;
+}
+
+// Stage virtual channel `vch` of the frame as PCM in buf[SLACK_W + PIDX(g)].  Returns (OR of the samples, OR of their
+// magnitudes), warp-uniform.  The samples behind a short frame are zero up to the next block boundary + one block.
+__device__ __noinline__ uint2 load_channel(const EncArgs &a, WarpSh &ws, uint32_t *buf, int vch, uint32_t &phase, int lane) {
+    const FrameDesc &d = ws.fd;
+    const int nsamp = d.nsamp;
+    uint32_t *pcm = buf + SLACK_W;
+    uint32_t orv = 0, ora = 0;
+    const int nblk = (nsamp + BLK - 1) / BLK;
+    if (d.tma && vch < 8) {
+        const int esz = frx_dtype_size(a.dtype);
+        const long long w = d.t.w;
+        const unsigned char *band = (const unsigned char *)a.raster +
+            ((long long)(d.t.first_band + vch) * a.band_stride + (long long)d.t.row_off * a.row_stride + d.t.col_off) * esz;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // earlier generic accesses to the buffer before the async writes
+        __syncwarp();
+        if (lane == 0) mbar_arrive_expect_tx(&ws.mbar, (uint32_t)nsamp * (uint32_t)esz);
+        __syncwarp();
+        if (lane < nblk) {
+            const long long g0 = (long long)lane * BLK, g1 = min((long long)nsamp, g0 + BLK);
+            long long t0 = d.s0 + g0;
+            const long long t1 = d.s0 + g1;
+            long long row = t0 / w;
+            unsigned char *dst0 = reinterpret_cast<unsigned char *>(pcm + lane * BLK_W) + (BLK_W * 4 - 16 - BLK * esz);
+            while (t0 < t1) {
+                const long long rend = min(t1, (row + 1) * w);
+                bulk_g2s(dst0 + (t0 - d.s0 - g0) * esz, band + (row * a.row_stride + (t0 - row * w)) * esz, (uint32_t)((rend - t0) * esz), &ws.mbar);
+                t0 = rend; row++;
+            }
+        }
+        mbar_wait(&ws.mbar, phase);
+        phase ^= 1u;
+        if (lane < nblk) {
+            const int nvalid = min(BLK, nsamp - lane * BLK);
+            uint32_t *blk = pcm + lane * BLK_W;
+            if (a.dtype == FRX_F32) quantize_block<FRX_F32>(blk, d.q, a.pcm_mode, nvalid, orv, ora);
+            else if (a.dtype == FRX_U16) quantize_block<FRX_U16>(blk, d.q, a.pcm_mode, nvalid, orv, ora);
+            else quantize_block_any(a.dtype, blk, d.q, a.pcm_mode, nvalid, orv, ora);
+        } else if (lane == nblk) {
+            uint32_t *blk = pcm + lane * BLK_W;
+            for (int i = 0; i < BLK; i += 4) *reinterpret_cast<int4 *>(blk + i) = make_int4(0, 0, 0, 0);
+        }
+    } else {
+        const int b0 = d.t.first_band;
+        for (int g = lane; g < nsamp; g += 32) {
+            int32_t x;
+            if (vch < 8) x = gather_any(a, d, b0 + vch, d.s0 + g);
+            else {
+                const int32_t l = gather_any(a, d, b0, d.s0 + g), r = gather_any(a, d, b0 + 1, d.s0 + g);
+                x = vch == 8 ? ((l + r) >> 1) : (l - r);
+            }
+            pcm[PIDX(g)] = (uint32_t)x;
+            orv |= (uint32_t)x;
+            ora |= (uint32_t)(x ^ (x >> 31));
+        }
+        const int gend = min(FRX_MAX_BLOCK, nblk * BLK + BLK);
+        for (int g = nsamp + lane; g < gend; g += 32) pcm[PIDX(g)] = 0u;
+    }
+    orv = __reduce_or_sync(FULLMASK, orv);
+    ora = __reduce_or_sync(FULLMASK, ora);
+    __syncwarp();
+    return make_uint2(orv, ora);
 }
 
 // ------------------------------------------------------------------------------------------
-// per-thread pieces of the subframe search
+// Rice search of one candidate from its partition sums.  F = the level whose partitions the lanes hold one each (5 for
+// full frames): lane p holds the sum of level-F partition p in sumA + sumB; for po_max == 6 sumA / sumB are the two
+// level-6 partitions 2p, 2p+1.  Coarser levels are built with shuffles; levels above po_max are not evaluated.  Writes the
+// best order's parameters to kparam[] and returns (estimated bits incl. the 6-bit method/order field, best order, RICE2).
 // ------------------------------------------------------------------------------------------
-// K2 fixed-order trial, 32-bit: sum |e_k| over the thread's 16 samples for k = 0..4 (history in s[HISTN-4..HISTN-1])
-template <int HISTN>
-__device__ __forceinline__ void fixed_trial32(const int32_t *s, uint32_t *fa) {
-    int32_t dm1 = s[HISTN - 1] - s[HISTN - 2], dm2 = s[HISTN - 2] - s[HISTN - 3], dm3 = s[HISTN - 3] - s[HISTN - 4];
-    int32_t d1p = dm1, d2p = dm1 - dm2, d3p = (dm1 - dm2) - (dm2 - dm3);
-    uint32_t f0 = 0, f1 = 0, f2 = 0, f3 = 0, f4 = 0;
-#pragma unroll
-    for (int i = 0; i < FRX_SPT; i++) {
-        const int32_t x = s[HISTN + i];
-        const int32_t d1 = x - s[HISTN + i - 1];
-        const int32_t d2 = d1 - d1p, d3 = d2 - d2p, d4 = d3 - d3p;
-        d1p = d1; d2p = d2; d3p = d3;
-        f0 += (uint32_t)abs(x); f1 += (uint32_t)abs(d1); f2 += (uint32_t)abs(d2); f3 += (uint32_t)abs(d3); f4 += (uint32_t)abs(d4);
+struct RiceChoice { uint64_t bits; int po; bool rice2; };
+__device__ __noinline__ RiceChoice analyse_partitions(uint8_t *kparam, uint64_t sumA, uint64_t sumB, int nsamp, int pred_order, int po_max,
+                                                      int F, uint32_t kmax) {
+    const int lane = threadIdx.x & 31;
+    uint64_t sum = sumA + sumB;
+    uint64_t best = ~0ull;
+    int best_po = 0;
+    uint32_t kbest0 = 0, kbest1 = 0;
+    if (po_max == 6) {
+        const uint32_t n0 = (uint32_t)(nsamp >> 6) - (lane == 0 ? (uint32_t)pred_order : 0u), n1 = (uint32_t)(nsamp >> 6);
+        const uint32_t k0 = rice_param(n0, sumA, kmax), k1 = rice_param(n1, sumB, kmax);
+        uint64_t b = rice_estimate(k0, n0, sumA) + rice_estimate(k1, n1, sumB);
+        b = warp_sum_u64(b) + 6;
+        best = b; best_po = 6; kbest0 = k0; kbest1 = k1;
     }
-    fa[0] = f0; fa[1] = f1; fa[2] = f2; fa[3] = f3; fa[4] = f4;
-}
-// masked form for thread 0 (warm-up samples do not count: sample g contributes to order k only when g >= k) and for
-// the partial thread of a short frame
-template <int HISTN>
-__device__ __forceinline__ void fixed_trial32_masked(const int32_t *s, int g0, int nv, uint32_t *fa) {
-    int32_t dm1 = s[HISTN - 1] - s[HISTN - 2], dm2 = s[HISTN - 2] - s[HISTN - 3], dm3 = s[HISTN - 3] - s[HISTN - 4];
-    int32_t d1p = dm1, d2p = dm1 - dm2, d3p = (dm1 - dm2) - (dm2 - dm3);
-#pragma unroll
-    for (int o = 0; o < 5; o++) fa[o] = 0;
-#pragma unroll
-    for (int i = 0; i < FRX_SPT; i++) {
-        const int32_t x = s[HISTN + i];
-        const int32_t d1 = x - s[HISTN + i - 1];
-        const int32_t d2 = d1 - d1p, d3 = d2 - d2p, d4 = d3 - d3p;
-        d1p = d1; d2p = d2; d3p = d3;
-        if (i < nv) {
-            const int g = g0 + i;
-            fa[0] += (uint32_t)abs(x);
-            if (g >= 1) fa[1] += (uint32_t)abs(d1);
-            if (g >= 2) fa[2] += (uint32_t)abs(d2);
-            if (g >= 3) fa[3] += (uint32_t)abs(d3);
-            if (g >= 4) fa[4] += (uint32_t)abs(d4);
+    for (int L = F; L >= 0; L--) {
+        const int step = 1 << (F - L);                   // lanes that are multiples of step hold level-L partitions
+        const bool mine = (lane & (step - 1)) == 0 && lane < (1 << F);
+        const int p = lane >> (F - L);
+        const uint32_t n = (uint32_t)(nsamp >> L) - (p == 0 ? (uint32_t)pred_order : 0u);
+        uint32_t k = 0;
+        uint64_t b = 0;
+        if (L <= po_max) {
+            if (mine) { k = rice_param(n, sum, kmax); b = rice_estimate(k, n, sum); }
+            b = warp_sum_u64(b) + 6;
+            if (b < best) { best = b; best_po = L; kbest0 = k; }
+        }
+        if (L > 0) {
+            const uint64_t o = __shfl_down_sync(FULLMASK, sum, step);
+            sum += o;                                    // valid in lanes that are multiples of 2*step
         }
     }
+    if (best_po == 6) { kparam[2 * lane] = (uint8_t)kbest0; kparam[2 * lane + 1] = (uint8_t)kbest1; }
+    else {
+        const int step = 1 << (F - best_po);
+        if ((lane & (step - 1)) == 0 && lane < (1 << F)) kparam[lane >> (F - best_po)] = (uint8_t)kbest0;
+    }
+    const uint32_t big = __ballot_sync(FULLMASK, kbest0 >= 15u || (best_po == 6 && kbest1 >= 15u));
+    __syncwarp();
+    RiceChoice rc;
+    rc.bits = best; rc.po = best_po; rc.rice2 = big != 0u;
+    return rc;
 }
 
-// tukey(0.5) window value of sample g in a short frame of n samples (libFLAC's definition).  Out of line on purpose:
-// scalars in, scalar out, so the compiler cannot speculate the cosine into the full-frame path (which reads a table)
-// and no register array escapes into the call.
-__device__ __noinline__ float tukey_w(int g, int n) {
-    if (g < 0 || g >= n) return 0.f;
-    const int Np = (int)(0.25f * (float)n) - 1;
-    if (Np <= 0) return 1.0f;
-    if (g <= Np) return 0.5f - 0.5f * cospif((float)g / (float)Np);
-    if (g >= n - Np - 1) return 0.5f - 0.5f * cospif((float)(g - (n - Np - 1) + Np) / (float)Np);
-    return 1.0f;
-}
-
-// K4 on one warp, float32 (MAXO = largest order of the compression level): every lane runs the Levinson-Durbin recursion
-// in registers; lane o-1 prices order o (expected bits), lane j owns coefficient j for the row store, the |max| and the
-// quantised value, so the serial part is the recursion and the error-feedback rounding only (libFLAC's scheme).
-// The decisions are ours; the bitstream stays exact because the residual is computed from the quantised integers.
-template <bool WIDE, int MAXO>
-__device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, int wasted, int sbps, int qlp_precision, int magbits, bool lean,
-                                        int lane) {
-    if (lane == 0) sh.lpc_ok = 0;
-    const float a0 = sh.autoc[0];
-    if (!(a0 > 0.f)) return;
-    const float inv0 = 1.0f / a0;
-    float an[MAXO + 1], lpc[MAXO];
-#pragma unroll
-    for (int i = 0; i <= MAXO; i++) an[i] = sh.autoc[i] * inv0;   // normalised autocorrelation
-    float err = 1.0f, myerr = 0.f;
-    int mo = max_lpc;
+// ------------------------------------------------------------------------------------------
+// K4: LPC design on one warp from the (warp-uniform) autocorrelation.  Every lane runs the Levinson-Durbin recursion in
+// registers; lane o-1 prices order o; the recursion is repeated up to the chosen order to get its coefficients, lane j owns
+// coefficient j for the |max| and the quantised value (libFLAC's error-feedback rounding).  The decisions are ours; the
+// bitstream stays exact because the residual is computed from the quantised integers.
+// ------------------------------------------------------------------------------------------
+struct LpcChoice { int ok, order, shift, precision, narrow; };
+template <int MAXO>
+__device__ __forceinline__ void levinson(const float *an, int upto, float *lpc, float &myerr, int &mo, int lane) {
+    float err = 1.0f;
 #pragma unroll
     for (int i = 0; i < MAXO; i++) {
-        if (i < mo) {
+        if (i < upto && i < mo) {
             float r = -an[i + 1];
 #pragma unroll
             for (int j = 0; j < i; j++) r -= lpc[j] * an[i - j];
@@ -1020,17 +621,28 @@ __device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, in
             }
             if (i & 1) lpc[i >> 1] += lpc[i >> 1] * r;
             err *= (1.0f - r * r);
-            if (lane == 0) {                       // (a per-lane select of lpc[j] would turn lpc[] into a local-memory array)
-#pragma unroll
-                for (int j = 0; j <= i; j++) sh.lpc_rows[i][j] = -lpc[j];
-            }
             if (lane == i) myerr = err;
             if (!(err > 0.f)) mo = i + 1;
         }
     }
-    __syncwarp();
-    // expected bits per order; errs are relative to autoc[0] (taken before the wasted-bit shift)
-    const float lscale = __log2f(a0) + __log2f(0.5f / (float)nsamp) - 2.0f * (float)wasted;
+}
+template <bool WIDE, int MAXO>
+__device__ __noinline__ LpcChoice lpc_design(WarpSh &ws, const float *autoc, int max_lpc, int nsamp, int sbps, int qlp_precision, int magbits, int lane) {
+    LpcChoice out;
+    out.ok = 0; out.order = 0; out.shift = 0; out.precision = 0; out.narrow = 1;
+    const float a0 = autoc[0];
+    if (!(a0 > 0.f)) return out;
+    const float inv0 = 1.0f / a0;
+    float an[MAXO + 1], lpc[MAXO];
+#pragma unroll
+    for (int i = 0; i <= MAXO; i++) an[i] = autoc[i] * inv0;   // normalised autocorrelation
+#pragma unroll
+    for (int i = 0; i < MAXO; i++) lpc[i] = 0.f;
+    float myerr = 0.f;
+    int mo = max_lpc;
+    levinson<MAXO>(an, MAXO, lpc, myerr, mo, lane);
+    // expected bits per order; errs are relative to autoc[0]
+    const float lscale = __log2f(a0) + __log2f(0.5f / (float)nsamp);
     uint32_t key = 0xFFFFFFFFu;
     if (lane < mo) {
         const int o = lane + 1;
@@ -1041,20 +653,29 @@ __device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, in
     }
     const uint32_t kmin = __reduce_min_sync(FULLMASK, key);
     const int order = __ffs((int)__ballot_sync(FULLMASK, key == kmin));   // lowest order among ties
+    if (order < 1 || kmin == 0xFFFFFFFFu) return out;
     int precision = qlp_precision;
     if (!WIDE) {
         const int lim = 32 - sbps - (31 - __clz(order));
         if (lim < precision) precision = lim;
     }
-    if (precision < 5) return;
-    const float rv = lane < order ? sh.lpc_rows[order - 1][lane] : 0.f;
+    if (precision < 5) return out;
+    if (order < MAXO) {                            // coefficients of the chosen order: repeat the recursion up to it
+#pragma unroll
+        for (int i = 0; i < MAXO; i++) lpc[i] = 0.f;
+        float e2 = 0.f; int mo2 = max_lpc;
+        levinson<MAXO>(an, order, lpc, e2, mo2, lane);
+    }
+    float rv = 0.f;
+#pragma unroll
+    for (int j = 0; j < MAXO; j++) if (lane == j && j < order) rv = -lpc[j];
     const float cmax = __uint_as_float(__reduce_max_sync(FULLMASK, __float_as_uint(fabsf(rv))));
-    if (!(cmax > 0.f) || !(cmax < 3.0e38f)) return;
+    if (!(cmax > 0.f) || !(cmax < 3.0e38f)) return out;
     int e2;
     (void)frexpf(cmax, &e2);
     int shift = (precision - 1) - (e2 - 1) - 1;
     if (shift > 15) shift = 15;
-    if (shift < 0) return;
+    if (shift < 0) return out;
     const int qmax = (1 << (precision - 1)) - 1, qmin = -(1 << (precision - 1));
     float error = 0.f;
     long long sumabs = 0;
@@ -1072,632 +693,985 @@ __device__ __noinline__ void lpc_design(EncSmall &sh, int max_lpc, int nsamp, in
             sumabs += qq < 0 ? -qq : qq;
         }
     }
-    if (lane < FRX_MAX_LPC) sh.qlp[lane] = myq;
+    if (lane < FRX_MAX_LPC) ws.qlp[lane] = myq;
     int ok = 1, narrow = 1;
     if (WIDE) {
         // |prediction sum| <= sumabs * 2^mag; the residual bound decides which arithmetic is safe
-        const int mag = magbits - wasted;
-        const long long M = 1ll << (mag < 0 ? 0 : mag);
+        const long long M = 1ll << (magbits < 0 ? 0 : magbits);
         narrow = (sumabs * M < (1ll << 31)) ? 1 : 0;
-        if (lean) {
-            const long long Bnd = M + ((sumabs * M) >> shift) + 1;
-            if (Bnd >= (1ll << 27)) ok = 0;   // keeps 32-bit residual sums exact; such wild predictors never win anyway
+        const long long Bnd = M + ((sumabs * M) >> shift) + 1;
+        if (Bnd >= (1ll << 31)) ok = 0;            // such wild predictors never win anyway
+    }
+    __syncwarp();
+    out.ok = ok; out.order = order; out.shift = shift; out.precision = precision; out.narrow = narrow;
+    return out;
+}
+
+// tukey(0.5) window value of sample g in a frame of n samples (libFLAC's definition), for the generic path
+__device__ __noinline__ float tukey_w(int g, int n) {
+    if (g < 0 || g >= n) return 0.f;
+    const int Np = (int)(0.25f * (float)n) - 1;
+    if (Np <= 0) return 1.0f;
+    if (g <= Np) return 0.5f - 0.5f * cospif((float)g / (float)Np);
+    if (g >= n - Np - 1) return 0.5f - 0.5f * cospif((float)(g - (n - Np - 1) + Np) / (float)Np);
+    return 1.0f;
+}
+
+// ==========================================================================================
+// FAST PATH: full 4096-sample frames of lean data (|sample| <= 2^23).  Lane L owns samples [128 L, 128 L + 128).
+// Sliding windows live in registers: in phase P of a rotation, slot (4 P + j) % W holds logical element j
+// (0..H-1 = history, oldest first; H..H+3 = the four new samples).  NP = W / 4 steps bring the window back to phase 0.
+// ==========================================================================================
+template <int P, int NP, class S>
+struct RunPh {
+    static __device__ __forceinline__ void go(S &s, uint32_t *base, int it) {
+        s.template step<P>(base + 4 * (it + P));
+        if constexpr (P + 1 < NP) RunPh<P + 1, NP, S>::go(s, base, it);
+    }
+};
+// the lane's block in two halves of 16 steps (the level-6 Rice partitions); fold() after every rotation
+template <int H, class S>
+__device__ __forceinline__ void walk_block(S &s, uint32_t *blk) {
+    constexpr int NP = (H + 4) / 4, STEPS_H = (BLK / 2) / 4, MAINH = (STEPS_H / NP) * NP, REMH = STEPS_H - MAINH;
+#pragma unroll 1
+    for (int half = 0; half < 2; half++) {
+        uint32_t *hb = blk + (BLK / 2) * half;
+#pragma unroll 1
+        for (int it = 0; it < MAINH; it += NP) { RunPh<0, NP, S>::go(s, hb, it); s.fold(half); }
+        if constexpr (REMH > 0) { RunPh<0, REMH, S>::go(s, hb, MAINH); s.fold(half); s.template realign<REMH>(); }
+    }
+}
+template <int H>
+__device__ __forceinline__ void load_history(const uint32_t *blk, int lane, int32_t (&hs)[H]) {
+    if (lane > 0) {
+#pragma unroll
+        for (int k = 0; k < H / 4; k++) {
+            const uint4 v = *reinterpret_cast<const uint4 *>(blk - BLK_W + BLK - H + 4 * k);
+            hs[4 * k] = (int32_t)v.x; hs[4 * k + 1] = (int32_t)v.y; hs[4 * k + 2] = (int32_t)v.z; hs[4 * k + 3] = (int32_t)v.w;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < H; k++) hs[k] = 0;
+    }
+}
+
+// ---- K2 + K3: |e_k| sums of the fixed predictors per 64-sample half, windowed autocorrelation partials ----
+template <int H>
+struct P1 {
+    static constexpr int W = H + 4;
+    float xw[W];
+    float ac[H + 1];
+    float c0, c1, twoc, wa, wb;   // window recurrence: c_{n+1} = twoc c_n - c_{n-1}, w = wa - wb c;  c1 = cos(phase of the next sample)
+    int32_t prev, d1p, d2p, d3p;
+    uint32_t f[5];                // sums of the running rotation (<= 16 samples, |e4| < 2^27)
+    uint64_t fs[5][2];
+    template <int P>
+    __device__ __forceinline__ void step(uint32_t *p) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(p);
+        const int32_t x[4] = { (int32_t)v.x, (int32_t)v.y, (int32_t)v.z, (int32_t)v.w };
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int32_t d1 = x[i] - prev;
+            const int32_t d2 = d1 - d1p, d3 = d2 - d2p, d4 = d3 - d3p;
+            prev = x[i]; d1p = d1; d2p = d2; d3p = d3;
+            f[0] += (uint32_t)abs(x[i]); f[1] += (uint32_t)abs(d1); f[2] += (uint32_t)abs(d2);
+            f[3] += (uint32_t)abs(d3); f[4] += (uint32_t)abs(d4);
+            const float cn = fmaf(twoc, c1, -c0);
+            const float wv = fmaf(-wb, c1, wa);
+            c0 = c1; c1 = cn;
+            const float xv = (float)x[i] * wv;
+            xw[(4 * P + H + i) % W] = xv;
+#pragma unroll
+            for (int lag = 0; lag <= H; lag++) ac[lag] = fmaf(xv, xw[(4 * P + H + i - lag) % W], ac[lag]);
         }
     }
-    if (lane == 0) { sh.lpc_order = order; sh.shift = shift; sh.precision = precision; sh.lpc_narrow = narrow; sh.lpc_ok = ok; }
+    __device__ __forceinline__ void fold(int half) {
+#pragma unroll
+        for (int o = 0; o < 5; o++) { fs[o][half] += f[o]; f[o] = 0; }
+    }
+    template <int R>
+    __device__ __forceinline__ void realign() {
+        float t[W];
+#pragma unroll
+        for (int k = 0; k < W; k++) t[k] = xw[(4 * R + k) % W];
+#pragma unroll
+        for (int k = 0; k < W; k++) xw[k] = t[k];
+    }
+};
+template <int H>
+__device__ __forceinline__ void pass1_full(uint32_t *pcm, int lane, uint64_t (&fs)[5][2], float (&ac)[H + 1]) {
+    uint32_t *blk = pcm + lane * BLK_W;
+    P1<H> st;
+    int32_t hs[H];
+    load_history<H>(blk, lane, hs);
+    // window: rising taper on lanes 0..7 (g <= 1023), falling on lanes 24..31 (g >= 3072), flat between (Np = 1023)
+    {
+        const int g0 = lane * BLK - H;
+        const float inv = 1.0f / 1023.0f;
+        const int ph = lane < 8 ? g0 : g0 - 2049;
+        st.c0 = cospif((float)(ph - 1) * inv);
+        st.c1 = cospif((float)ph * inv);
+        st.twoc = 2.0f * cospif(inv);
+        const bool taper = lane < 8 || lane >= 24;
+        st.wa = taper ? 0.5f : 1.0f;
+        st.wb = taper ? 0.5f : 0.0f;
+    }
+#pragma unroll
+    for (int k = 0; k < H; k++) {
+        const float cn = fmaf(st.twoc, st.c1, -st.c0);
+        const float wv = fmaf(-st.wb, st.c1, st.wa);
+        st.c0 = st.c1; st.c1 = cn;
+        st.xw[k] = (float)hs[k] * wv;
+    }
+#pragma unroll
+    for (int k = 0; k <= H; k++) st.ac[k] = 0.f;
+    st.prev = hs[H - 1];
+    st.d1p = hs[H - 1] - hs[H - 2];
+    {
+        const int32_t dm2 = hs[H - 2] - hs[H - 3], dm3 = hs[H - 3] - hs[H - 4];
+        st.d2p = st.d1p - dm2;
+        st.d3p = st.d2p - (dm2 - dm3);
+    }
+#pragma unroll
+    for (int o = 0; o < 5; o++) { st.f[o] = 0; st.fs[o][0] = 0; st.fs[o][1] = 0; }
+    walk_block<H>(st, blk);
+#pragma unroll
+    for (int o = 0; o < 5; o++) { fs[o][0] = st.fs[o][0]; fs[o][1] = st.fs[o][1]; }
+#pragma unroll
+    for (int k = 0; k <= H; k++) ac[k] = st.ac[k];
+}
+
+// ---- K5: LPC residuals of the lane's block with all H taps (coefficients beyond the order are zero), zig-zag folded and
+//      stored in place of the samples; |r| sums per half.  MODE 0: 32-bit accumulate, 1: 64-bit accumulate ----
+template <int H, int MODE, bool WIDE>
+struct P2 {
+    static constexpr int W = H + 4;
+    int32_t s[W];
+    int32_t q[H];
+    int shift;
+    uint32_t acc32;
+    uint64_t acc64;
+    uint64_t tot[2];
+    template <int P>
+    __device__ __forceinline__ void step(uint32_t *p) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(p);
+        s[(4 * P + H) % W] = (int32_t)v.x; s[(4 * P + H + 1) % W] = (int32_t)v.y; s[(4 * P + H + 2) % W] = (int32_t)v.z; s[(4 * P + H + 3) % W] = (int32_t)v.w;
+        uint32_t u[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            int32_t r;
+            if (MODE == 0) {
+                int32_t a = 0;
+#pragma unroll
+                for (int j = 0; j < H; j++) a += q[j] * s[(4 * P + H + i - 1 - j) % W];
+                r = s[(4 * P + H + i) % W] - (a >> shift);
+            } else {
+                long long a = 0;
+#pragma unroll
+                for (int j = 0; j < H; j++) a += (long long)q[j] * (long long)s[(4 * P + H + i - 1 - j) % W];
+                r = (int32_t)((long long)s[(4 * P + H + i) % W] - (a >> shift));
+            }
+            u[i] = zigzag(r);
+            if (WIDE) acc64 += (uint32_t)abs(r); else acc32 += (uint32_t)abs(r);
+        }
+        *reinterpret_cast<uint4 *>(p) = make_uint4(u[0], u[1], u[2], u[3]);
+    }
+    __device__ __forceinline__ void fold(int half) {
+        if (WIDE) { tot[half] += acc64; acc64 = 0; } else { tot[half] += acc32; acc32 = 0; }
+    }
+    template <int R>
+    __device__ __forceinline__ void realign() {
+        int32_t t[W];
+#pragma unroll
+        for (int k = 0; k < W; k++) t[k] = s[(4 * R + k) % W];
+#pragma unroll
+        for (int k = 0; k < W; k++) s[k] = t[k];
+    }
+};
+template <int H, int MODE, bool WIDE>
+__device__ __forceinline__ void lpc_inplace_full(WarpSh &ws, uint32_t *pcm, int shift, int lane, uint64_t &sumA, uint64_t &sumB) {
+    uint32_t *blk = pcm + lane * BLK_W;
+    P2<H, MODE, WIDE> st;
+    int32_t hs[H];
+    load_history<H>(blk, lane, hs);
+    __syncwarp();                      // every lane holds its history before any lane overwrites samples
+#pragma unroll
+    for (int k = 0; k < H; k++) st.s[k] = hs[k];
+#pragma unroll
+    for (int j = 0; j < H; j++) st.q[j] = j < FRX_MAX_LPC ? ws.qlp[j] : 0;
+    st.shift = shift; st.acc32 = 0; st.acc64 = 0; st.tot[0] = 0; st.tot[1] = 0;
+    walk_block<H>(st, blk);
+    sumA = st.tot[0]; sumB = st.tot[1];
+    __syncwarp();
+}
+template <int H, bool WIDE>
+__device__ __noinline__ void lpc_inplace_full_any(WarpSh &ws, uint32_t *pcm, int shift, int narrow, int lane, uint64_t &sumA, uint64_t &sumB) {
+    if (!WIDE || narrow) lpc_inplace_full<H, 0, WIDE>(ws, pcm, shift, lane, sumA, sumB);
+    else lpc_inplace_full<H, 1, WIDE>(ws, pcm, shift, lane, sumA, sumB);
+}
+
+// fixed predictor of order `order` (0..4), residuals zig-zag folded in place (32-bit arithmetic: lean data)
+__device__ __noinline__ void fixed_inplace_full(uint32_t *pcm, int order, int lane) {
+    uint32_t *blk = pcm + lane * BLK_W;
+    int32_t hs[4];
+    load_history<4>(blk, lane, hs);
+    __syncwarp();
+    int32_t prev = hs[3], d1p = hs[3] - hs[2];
+    const int32_t dm2 = hs[2] - hs[1], dm3 = hs[1] - hs[0];
+    int32_t d2p = d1p - dm2, d3p = d2p - (dm2 - dm3);
+#pragma unroll 2
+    for (int it = 0; it < BLK / 4; it++) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(blk + 4 * it);
+        const int32_t x[4] = { (int32_t)v.x, (int32_t)v.y, (int32_t)v.z, (int32_t)v.w };
+        uint32_t u[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int32_t d1 = x[i] - prev;
+            const int32_t d2 = d1 - d1p, d3 = d2 - d2p, d4 = d3 - d3p;
+            prev = x[i]; d1p = d1; d2p = d2; d3p = d3;
+            const int32_t r = order == 0 ? x[i] : (order == 1 ? d1 : (order == 2 ? d2 : (order == 3 ? d3 : d4)));
+            u[i] = zigzag(r);
+        }
+        *reinterpret_cast<uint4 *>(blk + 4 * it) = make_uint4(u[0], u[1], u[2], u[3]);
+    }
     __syncwarp();
 }
 
-// OR an n-bit field (1..32 bits, v < 2^n) into the zeroed frame buffer at bit position p
-__device__ __forceinline__ void put_field(uint32_t *buf, uint32_t p, uint32_t v, uint32_t n) {
-    const uint64_t x = (uint64_t)v << (64u - (p & 31u) - n);
-    const uint32_t hi = (uint32_t)(x >> 32), lo = (uint32_t)x;
-    if (hi) atomicOr(&buf[p >> 5], hi);
-    if (lo) atomicOr(&buf[(p >> 5) + 1u], lo);
-}
-
-// K7b: Rice-code the thread's residuals straight into the (zeroed) frame buffer.  The unary zeros need no store at all;
-// every sample is one (k+1)-bit field -- stop bit plus low bits -- OR-ed at its bit position, straddling at most two
-// words.  The residuals come from the shared residual buffer (sample-major, conflict-free).  `skip` leading samples are warm-up (thread 0 only), `nv` samples are valid, `plain` = neither applies.
-__device__ __forceinline__ void pack_rice(uint32_t *buf, uint32_t p, const int32_t *res, int tid, uint32_t kk, int skip, int nv, bool plain) {
-    const uint32_t kmask = (1u << kk) - 1u;   // kk <= 30
-    const uint32_t len = kk + 1u;
-#pragma unroll
-    for (int i = 0; i < FRX_SPT; i++) {
-        if (plain || (i >= skip && i < nv)) {
-            const uint32_t u = zigzag(res[RES_IDX(i, tid)]);
-            p += u >> kk;
-            const uint32_t code = (1u << kk) | (u & kmask);
-            const uint64_t v = (uint64_t)code << (64u - (p & 31u) - len);
-            atomicOr(&buf[p >> 5], (uint32_t)(v >> 32));
-            if ((uint32_t)v) atomicOr(&buf[(p >> 5) + 1u], (uint32_t)v);
-            p += len;
-        }
+// exact Rice bits of the lane's block: k0 / k1 = parameters of its two halves
+__device__ __forceinline__ uint32_t count_full(const uint32_t *pcm, int lane, uint32_t k0, uint32_t k1) {
+    const uint32_t *blk = pcm + lane * BLK_W;
+    uint32_t c0 = 0, c1 = 0;
+#pragma unroll 4
+    for (int it = 0; it < BLK / 8; it++) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(blk + 4 * it);
+        const uint4 w = *reinterpret_cast<const uint4 *>(blk + BLK / 2 + 4 * it);
+        c0 += (v.x >> k0) + (v.y >> k0) + (v.z >> k0) + (v.w >> k0);
+        c1 += (w.x >> k1) + (w.y >> k1) + (w.z >> k1) + (w.w >> k1);
     }
+    return c0 + c1 + (BLK / 2) * (k0 + 1u) + (BLK / 2) * (k1 + 1u);
 }
 
-// Fat data (|s| > 2^23: lossless int32 / float bit patterns): 64-bit fixed trial and range-checked LPC residuals, the two
-// Rice searches, and the decisions -- a complete, slower replacement of the lean K2/K5/K6 stages.  All compute threads call it.
-template <int HISTN>
-__device__ __noinline__ void fat_search(EncSmall &sh, const int32_t *pcm, uint64_t *tabs, int tid, int nv, int nsamp, int wasted,
-                                        int po_max, uint32_t kmax) {
-    const int lane = tid & 31, warp = tid >> 5, g0 = tid * FRX_SPT;
-    int32_t s[HISTN + FRX_SPT];
-    read_pcm<HISTN>(pcm, tid, wasted, s);
-    const bool lpc_try = sh.lpc_ok != 0;
-    const int lpc_order = sh.lpc_order;
-    uint64_t acc[5] = { 0, 0, 0, 0, 0 };
-    uint32_t fbad = 0;
+// ==========================================================================================
+// GENERIC PATH: short frames and fat data (|sample| > 2^23): 64-bit arithmetic with range checks, samples striped over
+// the lanes (g = 32 i + lane), in-place passes walk the frame from its end so that history is still intact.
+// ==========================================================================================
+__device__ __forceinline__ long long pcm_at(const uint32_t *pcm, int g) { return g >= 0 ? (long long)(int32_t)pcm[PIDX(g)] : 0ll; }
+
+__device__ __forceinline__ long long fixed_resid64(const uint32_t *pcm, int g, int order) {
+    const long long A = pcm_at(pcm, g);
+    if (order == 0) return A;
+    const long long B = pcm_at(pcm, g - 1);
+    if (order == 1) return A - B;
+    const long long C = pcm_at(pcm, g - 2);
+    if (order == 2) return A - 2 * B + C;
+    const long long D = pcm_at(pcm, g - 3);
+    if (order == 3) return A - 3 * B + 3 * C - D;
+    return A - 4 * B + 6 * C - 4 * D + pcm_at(pcm, g - 4);
+}
+
+template <int MAXO>
+__device__ __noinline__ void pass1_generic(const uint32_t *pcm, int nsamp, int max_lpc, int lane, uint64_t (&tot)[5], uint32_t &badmask,
+                                           float (&ac)[MAXO + 1]) {
 #pragma unroll
-    for (int i = 0; i < FRX_SPT; i++) {
-        const int g = g0 + i;
-        if (i < nv) {
-            const int32_t *p = s + HISTN + i;
-            const long long A = p[0], B = p[-1], C = p[-2], D = p[-3], E = p[-4];
-            const long long e[5] = { A, A - B, A - 2 * B + C, A - 3 * B + 3 * C - D, A - 4 * B + 6 * C - 4 * D + E };
+    for (int o = 0; o < 5; o++) tot[o] = 0;
+#pragma unroll
+    for (int k = 0; k <= MAXO; k++) ac[k] = 0.f;
+    uint32_t bad = 0;
+    float xw_prev = 0.f;
+    const int niter = (nsamp + 31) >> 5;
+    for (int it = 0; it < niter; it++) {
+        const int g = 32 * it + lane;
+        const bool valid = g < nsamp;
+        const long long A = valid ? pcm_at(pcm, g) : 0, B = pcm_at(pcm, g - 1), C = pcm_at(pcm, g - 2), D = pcm_at(pcm, g - 3), E = pcm_at(pcm, g - 4);
+        const long long e[5] = { A, A - B, A - 2 * B + C, A - 3 * B + 3 * C - D, A - 4 * B + 6 * C - 4 * D + E };
+        if (valid) {
 #pragma unroll
             for (int o = 0; o < 5; o++) {
                 if (g >= o) {
                     const unsigned long long av = (unsigned long long)llabs(e[o]);
-                    acc[o] += av;
-                    if (av > 0x7FFFFFFFull) fbad |= 1u << o;
+                    tot[o] += av;
+                    if (av > 0x7FFFFFFFull) bad |= 1u << o;
                 }
             }
         }
-    }
+        if (max_lpc > 0) {
+            const float xw = valid ? (float)(int32_t)A * tukey_w(g, nsamp) : 0.f;
 #pragma unroll
-    for (int o = 0; o < 5; o++) tabs[o * FRX_ENC_THREADS + tid] = acc[o];
-#pragma unroll
-    for (int o = 0; o < 5; o++) acc[o] = warp_sum_u64(acc[o]);
-    fbad = __reduce_or_sync(FULLMASK, fbad);
-    bool bad = false;
-    uint64_t ab = 0;
-    if (lpc_try) {
-        int32_t q[HISTN], r[FRX_SPT];
-#pragma unroll
-        for (int j = 0; j < HISTN; j++) q[j] = sh.qlp[j];
-        const uint32_t badm = lpc_residuals_dispatch<2, HISTN>(lpc_order, s, q, sh.shift, r);
-#pragma unroll
-        for (int i = 0; i < FRX_SPT; i++) {
-            if (i < nv && g0 + i >= lpc_order) {
-                if ((badm >> i) & 1u) bad = true;
-                ab += (uint32_t)abs(r[i]);
+            for (int lag = 0; lag <= MAXO; lag++) {
+                const float same = __shfl_up_sync(FULLMASK, xw, lag);                        // lane - lag of this row
+                const float prev = __shfl_sync(FULLMASK, xw_prev, (32 + lane - lag) & 31);   // tail of the previous row
+                const float partner = lag == 0 ? xw : (lane >= lag ? same : prev);
+                if (lag <= max_lpc) ac[lag] = fmaf(xw, partner, ac[lag]);
             }
+            xw_prev = xw;
         }
     }
-    tabs[5 * FRX_ENC_THREADS + tid] = ab;
-    const unsigned anybad = __ballot_sync(FULLMASK, bad);
-    if (lane == 0) {
 #pragma unroll
-        for (int o = 0; o < 5; o++) sh.wfix[warp][o] = acc[o];
-        sh.wbad[warp][0] = fbad; sh.wbad[warp][1] = anybad ? 1u : 0u;
-    }
-    compute_sync();
-    if (warp == 0) {
-        uint32_t fb = 0;
-        for (int w2 = 0; w2 < NWARPS; w2++) fb |= sh.wbad[w2][0];
-        uint64_t bestv = ~0ull, f1 = 0;
-        int besto = -1;
-        for (int o = 0; o < 5; o++) {
-            uint64_t tot = 0;
-            for (int w2 = 0; w2 < NWARPS; w2++) tot += sh.wfix[w2][o];
-            if (o == 1) f1 = tot;
-            if (!((fb >> o) & 1u) && tot < bestv) { bestv = tot; besto = o; }
-        }
-        const int fo = (nsamp > 4) ? besto : -1;
-        if (lane == 0) { sh.is_const = (f1 == 0 && !(fb & 2u)) ? 1 : 0; sh.fixed_order = fo; }
-        if (fo >= 0) analyse_partitions(sh, tabs + fo * FRX_ENC_THREADS, 0, nsamp, fo, po_max, kmax, 0);
-    } else if (warp == 1) {
-        uint32_t b = 0;
-        for (int w2 = 0; w2 < NWARPS; w2++) b |= sh.wbad[w2][1];
-        const bool valid = lpc_try && !b;
-        if (lane == 0) sh.lpc_ok = valid ? 1 : 0;
-        if (valid) analyse_partitions(sh, tabs + 5 * FRX_ENC_THREADS, 1, nsamp, lpc_order, po_max, kmax, 0);
-    }
-    compute_sync();
+    for (int o = 0; o < 5; o++) tot[o] = warp_sum_u64(tot[o]);
+#pragma unroll
+    for (int k = 0; k <= MAXO; k++) ac[k] = warp_sum_f32(ac[k]);
+    badmask = __reduce_or_sync(FULLMASK, bad);
 }
 
-// copy a finished frame from its shared-memory buffer to its final place and append the CRC-16
-__device__ __forceinline__ void copy_out_frame(const EncArgs &a, EncSmall &sh, const uint32_t *bits, const uint32_t *crc_part, uint64_t off,
-                                               uint32_t body_bytes, int tid) {
-    const uint32_t nbytes = body_bytes + 2u;
-    if (off + nbytes > a.capacity) {
-        if (tid == 0) atomicExch(a.status, FRX_E_OVERFLOW);
-        return;
+// |r| sums of the fixed predictor into the partition bins, nothing stored (the PCM stays intact for the LPC trial)
+__device__ __noinline__ void fixed_sums_generic(const uint32_t *pcm, unsigned long long *bins, int nsamp, int order, int psf, int lane) {
+    const int niter = (nsamp + 31) >> 5;
+    for (int it = 0; it < niter; it++) {
+        const int g = 32 * it + lane;
+        if (g < nsamp && g >= order) atomicAdd(&bins[g / psf], (unsigned long long)llabs(fixed_resid64(pcm, g, order)));
     }
-    uint8_t *dst = a.bytes + off;
-    if (tid == FRX_ENC_THREADS - 1) {
-        // undo the zero-word padding of the last quad, finish over the <= 3 tail bytes, store big-endian
+    __syncwarp();
+}
+
+// residuals of the predictor (fixed: order 0..4, lpc == false; LPC: coefficients ws.qlp, shift) folded in place, warm-up
+// samples zeroed; |r| sums added to the 64-bit bins of the finest partition level (psf = samples per finest partition).
+// Returns false when a residual does not fit (INT32_MIN, INT32_MAX]: the buffer is then garbage and must be reloaded.
+__device__ __noinline__ bool resid_inplace_generic(WarpSh &ws, uint32_t *pcm, unsigned long long *bins, int nsamp, bool lpc, int order, int shift,
+                                                   int psf, int lane) {
+    bool bad = false;
+    const int niter = (nsamp + 31) >> 5;
+    for (int it = niter - 1; it >= 0; it--) {
+        const int g = 32 * it + lane;
+        const bool valid = g < nsamp;
+        long long r = 0;
+        if (valid && g >= order) {
+            if (lpc) {
+                long long acc = 0;
+                for (int j = 0; j < order; j++) acc += (long long)ws.qlp[j] * pcm_at(pcm, g - 1 - j);
+                r = pcm_at(pcm, g) - (acc >> shift);
+            } else r = fixed_resid64(pcm, g, order);
+            if (r <= (long long)INT32_MIN || r > (long long)INT32_MAX) bad = true;
+        }
+        __syncwarp();
+        if (valid) {
+            pcm[PIDX(g)] = g >= order ? zigzag((int32_t)r) : 0u;
+            if (bins && g >= order) atomicAdd(&bins[g / psf], (unsigned long long)llabs(r));
+        }
+        __syncwarp();
+    }
+    return !__any_sync(FULLMASK, bad);
+}
+
+// exact Rice bits of the whole subframe body (codes + parameters) and the in-place check: the bits of chunk c (128 samples)
+// must end before the first word of chunk c + 1.  kk = the chosen order's parameters, psize = samples per partition.
+__device__ __noinline__ uint32_t count_generic(const uint32_t *pcm, const uint8_t *kk, int nsamp, int order, int psize, uint32_t pb, uint32_t headbits,
+                                               bool &inplace_ok, int lane) {
+    uint32_t cnt = 0, run = headbits;
+    bool ok = true;
+    const int niter = (nsamp + 31) >> 5;
+    for (int it = 0; it < niter; it++) {
+        const int g = 32 * it + lane;
         uint32_t c = 0;
-#pragma unroll
-        for (int w2 = 0; w2 < NWARPS; w2++) c ^= crc_part[w2];
-        const uint32_t nw = body_bytes >> 2;
-        const uint32_t z = ((nw + 3u) & ~3u) - nw;
-        if (z && c) c = frx_gf16_mulmod(c, (uint32_t)a.crc_xinv[z]);
-        const uint32_t tw = bits[nw];
-        for (uint32_t b = 0; b < (body_bytes & 3u); b++) {
-            const uint32_t byte = (tw >> (24 - 8 * b)) & 0xFFu;
-            c = ((c << 8) ^ sh.crc_tab[0][((c >> 8) ^ byte) & 0xFFu]) & 0xFFFFu;
+        if (g < nsamp) {
+            const int pi = g / psize;
+            const uint32_t k = kk[pi];
+            if (g >= order) c = (pcm[PIDX(g)] >> k) + k + 1u;
+            if (g == pi * psize) c += pb;
         }
-        dst[body_bytes] = (uint8_t)(c >> 8);
-        dst[body_bytes + 1] = (uint8_t)c;
+        cnt += c;
+        if ((it & 3) == 3 || it == niter - 1) {
+            run += __reduce_add_sync(FULLMASK, cnt);
+            cnt = 0;
+            const uint32_t chunk = (uint32_t)it >> 2;
+            if (run > 32u * (SLACK_W + BLK_W * (chunk + 1u))) ok = false;
+        }
     }
-    const uint32_t head = min(body_bytes, (uint32_t)((4u - (uint32_t)((uintptr_t)dst & 3u)) & 3u));
-    if (tid < (int)head) dst[tid] = (uint8_t)((bits[tid >> 2] >> (24 - 8 * (tid & 3))) & 0xFFu);
-    const uint32_t nwords = (body_bytes - head) >> 2;
-    uint32_t *dw = reinterpret_cast<uint32_t *>(dst + head);
-    const uint32_t sh8 = head * 8u;
-    for (uint32_t j = tid; j < nwords; j += FRX_ENC_THREADS) {
-        // frame bytes [head+4j, head+4j+4): head < 4 so they straddle words j and j+1
-        const uint32_t w0 = bits[j], w1 = bits[j + 1];
-        const uint32_t v = head ? __funnelshift_l(w1, w0, sh8) : w0;
-        dw[j] = frx_bswap32(v);
+    inplace_ok = ok;
+    return run - headbits;
+}
+
+// ==========================================================================================
+// K7: bit packing.  Every lane appends a run of fields to the stream in lane order; a field is `zer` zero bits followed by
+// the low `len` bits of `val` (len <= 32).  Lanes accumulate their bits in registers and store whole words; the words two
+// lanes share are merged with a segmented OR-scan, so shared memory sees plain stores only.
+// ==========================================================================================
+struct Emitter {
+    uint32_t P;        // bit position of the end of the stream inside the warp buffer
+    uint32_t carry;    // bits of the incomplete last word (top-aligned)
+};
+struct LaneBits {
+    uint32_t hi, lo, firstw;
+    int nb;
+    uint32_t *wp;
+    bool flushed;
+    __device__ __forceinline__ void init(uint32_t *out, uint32_t bitpos) {
+        wp = out + (bitpos >> 5); nb = (int)(bitpos & 31u); hi = 0; lo = 0; firstw = 0; flushed = false;
     }
-    const uint32_t tail0 = head + (nwords << 2);
-    if (tid < (int)(body_bytes - tail0)) {
-        const uint32_t b = tail0 + (uint32_t)tid;
-        dst[b] = (uint8_t)((bits[b >> 2] >> (24 - 8 * (b & 3))) & 0xFFu);
+    __device__ __forceinline__ void flush() {
+        if (!flushed) { firstw = hi; flushed = true; } else *wp = hi;
+        wp++; hi = lo; lo = 0; nb -= 32;
+    }
+    __device__ __forceinline__ void put(uint32_t c, int n) {   // n in 1..32, c < 2^n
+        const uint32_t ct = c << (32 - n);
+        hi |= ct >> nb;
+        lo = __funnelshift_r(0u, ct, (uint32_t)nb);            // ct << (32 - nb), 0 when nb == 0
+        nb += n;
+        if (nb >= 32) flush();
+    }
+    __device__ __forceinline__ void zeros(uint32_t q) {
+        nb += (int)q;
+        while (nb >= 32) flush();
+    }
+};
+template <int NF>
+__device__ __forceinline__ void emit_fields(uint32_t *out, Emitter &em, const uint32_t (&val)[NF], const uint32_t (&len)[NF], const uint32_t (&zer)[NF], int lane) {
+    uint32_t T = 0;
+#pragma unroll
+    for (int i = 0; i < NF; i++) T += len[i] + zer[i];
+    uint32_t incl = T;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(FULLMASK, incl, o);
+        if (lane >= o) incl += n;
+    }
+    const uint32_t total = __shfl_sync(FULLMASK, incl, 31);
+    const uint32_t start = em.P + incl - T;
+    LaneBits lb;
+    lb.init(out, start);
+#pragma unroll
+    for (int i = 0; i < NF; i++) {
+        const uint32_t n = len[i] + zer[i];
+        if (n) {
+            if (n <= 32u) lb.put(val[i], (int)n);
+            else { lb.zeros(zer[i]); if (len[i]) lb.put(val[i], (int)len[i]); }
+        }
+    }
+    // the incomplete last word of every lane flows to the lanes behind it until one of them completes the word
+    uint32_t v = lb.hi;
+    uint32_t fl = lb.flushed ? 1u : 0u;
+    if (lane == 0 && !lb.flushed) v |= em.carry;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t pv = __shfl_up_sync(FULLMASK, v, o);
+        const uint32_t pf = __shfl_up_sync(FULLMASK, fl, o);
+        if (lane >= o && !fl) { v |= pv; fl = pf; }
+    }
+    uint32_t cin = __shfl_up_sync(FULLMASK, v, 1);
+    if (lane == 0) cin = em.carry;
+    if (lb.flushed) out[start >> 5] = lb.firstw | cin;
+    em.carry = __shfl_sync(FULLMASK, v, 31);
+    em.P += total;
+    __syncwarp();
+}
+
+// subframe header: 0 | type(6) | wasted flag, wasted-bits count in unary, warm-up samples, LPC precision / shift /
+// coefficients, Rice method + partition order -- one field per lane, in stream order
+__device__ __noinline__ void pack_subframe_header(WarpSh &ws, uint32_t *out, Emitter &em, const SubDec &d, const uint32_t *pcm, int lane) {
+    const int type = d.type, order = d.order, wasted = d.wasted, sbps = d.sbps;
+    uint32_t val[2] = { 0, 0 }, len[2] = { 0, 0 }, zer[2] = { 0, 0 };
+    const uint32_t smask = sbps >= 32 ? 0xFFFFFFFFu : ((1u << sbps) - 1u);
+    if (lane == 0) {
+        const uint32_t tcode = type == 0 ? 0u : (type == 1 ? 1u : (type == 2 ? (8u | (uint32_t)order) : (32u | (uint32_t)(order - 1))));
+        val[0] = (tcode << 1) | (wasted ? 1u : 0u); len[0] = 8;
+        if (wasted) { val[1] = 1u; len[1] = 1; zer[1] = (uint32_t)wasted - 1u; }
+    }
+    if (type == 0) {
+        if (lane == 1) { val[0] = pcm[PIDX(0)] & smask; len[0] = (uint32_t)sbps; }
+    } else if (type >= 2) {
+        if (lane >= 1 && lane <= order) { val[0] = (uint32_t)ws.warm[lane - 1] & smask; len[0] = (uint32_t)sbps; }
+        int nxt = order + 1;
+        if (type == 3) {
+            const uint32_t precision = d.precision;
+            if (lane == nxt) { val[0] = ((precision - 1u) << 5) | ((uint32_t)d.shift & 31u); len[0] = 9; }
+            if (lane > nxt && lane <= nxt + order) { val[0] = (uint32_t)(int32_t)d.qlp[lane - nxt - 1] & ((1u << precision) - 1u); len[0] = precision; }
+            nxt += order + 1;
+        }
+        if (lane == nxt) { val[0] = ((d.rice2 ? 1u : 0u) << 4) | (uint32_t)d.po; len[0] = 6; }
+    }
+    emit_fields<2>(out, em, val, len, zer, lane);
+}
+
+// Rice-coded residual section, chunk by chunk: 128 residuals into registers, then their bits into the words behind them
+__device__ __noinline__ void pack_rice(uint32_t *out, Emitter &em, const SubDec &d, uint32_t *pcm, int nsamp, int lane) {
+    const int order = d.order, po = d.po;
+    const int psize = nsamp >> po;
+    const uint32_t pb = d.rice2 ? 5u : 4u;
+    const bool pow2 = (psize & (psize - 1)) == 0;
+    const int psh = 31 - __clz(psize);
+    const int nchunks = (nsamp + BLK - 1) / BLK;
+    for (int c = 0; c < nchunks; c++) {
+        const int g = BLK * c + 4 * lane;
+        const uint4 v = *reinterpret_cast<const uint4 *>(pcm + PIDX(g));
+        __syncwarp();
+        const uint32_t u[4] = { v.x, v.y, v.z, v.w };
+        uint32_t val[5], len[5], zer[5];
+        const int pi = g < nsamp ? (pow2 ? (g >> psh) : (g / psize)) : 0;
+        const uint32_t k = g < nsamp ? d.k[pi] : 0u;
+        const bool pstart = g < nsamp && g == pi * psize;
+        val[0] = k; len[0] = pstart ? pb : 0u; zer[0] = 0;
+        const uint32_t kmask = (1u << k) - 1u;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const bool coded = (g + i) < nsamp && (g + i) >= order;
+            val[1 + i] = (1u << k) | (u[i] & kmask);
+            len[1 + i] = coded ? k + 1u : 0u;
+            zer[1 + i] = coded ? (u[i] >> k) : 0u;
+        }
+        emit_fields<5>(out, em, val, len, zer, lane);
+    }
+}
+// VERBATIM body: the samples as sbps-bit fields
+__device__ __noinline__ void pack_verbatim(uint32_t *out, Emitter &em, const SubDec &d, uint32_t *pcm, int nsamp, int lane) {
+    const uint32_t sbps = d.sbps;
+    const int nchunks = (nsamp + BLK - 1) / BLK;
+    for (int c = 0; c < nchunks; c++) {
+        const int g = BLK * c + 4 * lane;
+        const uint4 v = *reinterpret_cast<const uint4 *>(pcm + PIDX(g));
+        __syncwarp();
+        const uint32_t u[4] = { v.x, v.y, v.z, v.w };
+        const uint32_t smask = sbps >= 32u ? 0xFFFFFFFFu : ((1u << sbps) - 1u);   // sbps <= 32: a side channel is only tried for 16-bit PCM
+        uint32_t val[4], len[4], zer[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) { val[i] = u[i] & smask; len[i] = (g + i) < nsamp ? sbps : 0u; zer[i] = 0; }
+        emit_fields<4>(out, em, val, len, zer, lane);
     }
 }
 
-// CRC-16 of the frame body's whole words: every compute thread takes a chunk of Lq quads, the chunk CRCs are shifted to
-// their place with x^(128 Lq j) mod P and xor-ed (per warp here, across warps by copy_out_frame)
-// shift factor of this thread's chunk; loaded ahead of the barrier in front of crc_frame so its latency is hidden
-__device__ __forceinline__ uint32_t crc_shift_factor(const EncArgs &a, uint32_t body_bytes, int tid) {
-    const uint32_t nq = ((body_bytes >> 2) + 3u) >> 2;
-    const uint32_t Lq = (nq + FRX_ENC_THREADS - 1) / FRX_ENC_THREADS;
-    return (uint32_t)__ldg(&a.crc_xpow[(max(Lq, 1u) - 1) * FRX_ENC_THREADS + (FRX_ENC_THREADS - 1 - tid)]);
-}
-__device__ __forceinline__ void crc_frame(const EncArgs &a, EncSmall &sh, const uint32_t *bits, uint32_t *crc_part, uint32_t body_bytes,
-                                          int tid, uint32_t shift_factor) {
-    const uint32_t nw = body_bytes >> 2;                       // whole words
-    const uint32_t nq = (nw + 3u) >> 2;                        // quads; the buffer is zero behind the frame
-    const uint32_t Lq = (nq + FRX_ENC_THREADS - 1) / FRX_ENC_THREADS;
-    const int padq = (int)(FRX_ENC_THREADS * Lq) - (int)nq;    // virtual leading zero quads
-    int q0 = tid * (int)Lq - padq;
+// ------------------------------------------------------------------------------------------
+// CRC-16 of `nw` whole words of the warp buffer (big-endian words): every lane takes a run of Lq 16-byte quads through the
+// 4x256 table, the runs are combined with x^(128 Lq j) mod P.  Warp-uniform result.
+// ------------------------------------------------------------------------------------------
+__device__ __noinline__ uint32_t crc_words(const EncArgs &a, const uint16_t (*tab)[256], const uint32_t *bits, uint32_t nw, int lane) {
+    if (nw == 0) return 0;
+    const uint32_t nq = (nw + 3u) >> 2;
+    const uint32_t Lq = (nq + 31u) / 32u;
+    const uint32_t shift_factor = (uint32_t)__ldg(&a.crc_xpow[(Lq - 1) * 256 + (31 - lane)]);
+    const int padq = (int)(32u * Lq) - (int)nq;                // virtual leading zero quads
+    int q0 = lane * (int)Lq - padq;
     const int q1 = q0 + (int)Lq;
     if (q0 < 0) q0 = 0;
     uint32_t c = 0;
     for (int qi = q0; qi < q1; qi++) {
         uint4 wv = *reinterpret_cast<const uint4 *>(bits + 4 * qi);
-        if (qi == (int)nq - 1) {   // the word behind the last whole word holds the <= 3 tail bytes: not part of this pass
-            const uint32_t k = nw - 4u * (uint32_t)qi;   // whole words in the last quad (1..4)
+        if (qi == (int)nq - 1) {
+            const uint32_t k = nw - 4u * (uint32_t)qi;         // whole words in the last quad (1..4)
             if (k < 4u) wv.w = 0u;
             if (k < 3u) wv.z = 0u;
             if (k < 2u) wv.y = 0u;
         }
         uint32_t x = wv.x ^ (c << 16);
-        c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
+        c = (uint32_t)tab[3][x >> 24] ^ tab[2][(x >> 16) & 0xFFu] ^ tab[1][(x >> 8) & 0xFFu] ^ tab[0][x & 0xFFu];
         x = wv.y ^ (c << 16);
-        c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
+        c = (uint32_t)tab[3][x >> 24] ^ tab[2][(x >> 16) & 0xFFu] ^ tab[1][(x >> 8) & 0xFFu] ^ tab[0][x & 0xFFu];
         x = wv.z ^ (c << 16);
-        c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
+        c = (uint32_t)tab[3][x >> 24] ^ tab[2][(x >> 16) & 0xFFu] ^ tab[1][(x >> 8) & 0xFFu] ^ tab[0][x & 0xFFu];
         x = wv.w ^ (c << 16);
-        c = (uint32_t)sh.crc_tab[3][x >> 24] ^ sh.crc_tab[2][(x >> 16) & 0xFFu] ^ sh.crc_tab[1][(x >> 8) & 0xFFu] ^ sh.crc_tab[0][x & 0xFFu];
+        c = (uint32_t)tab[3][x >> 24] ^ tab[2][(x >> 16) & 0xFFu] ^ tab[1][(x >> 8) & 0xFFu] ^ tab[0][x & 0xFFu];
     }
     if (c) c = frx_gf16_mulmod(c, shift_factor);
     c = __reduce_xor_sync(FULLMASK, c);
-    if ((tid & 31) == 0) crc_part[tid >> 5] = c;
+    const uint32_t z = 4u * nq - nw;                           // zero words appended to the last quad
+    if (z && c) c = frx_gf16_mulmod(c, (uint32_t)__ldg(&a.crc_xinv[z]));
+    return c;
+}
+// x^(32 n) mod P
+__device__ __noinline__ uint32_t gf16_xpow32(uint32_t n) {
+    uint32_t r = 1, b = frx_gf16_mulmod(0x8005u, 0x8005u);     // x^16 = 0x8005 (mod P), squared
+    while (n) {
+        if (n & 1u) r = frx_gf16_mulmod(r, b);
+        b = frx_gf16_mulmod(b, b);
+        n >>= 1;
+    }
+    return r;
+}
+// words [0, nw) of the warp buffer -> dst (any byte alignment), big-endian byte order
+__device__ __forceinline__ void copy_words_out(uint8_t *dst, const uint32_t *bits, uint32_t nw, int lane) {
+    const uint32_t nbytes = nw * 4u;
+    const uint32_t head = min(nbytes, (uint32_t)((4u - (uint32_t)((uintptr_t)dst & 3u)) & 3u));
+    if (lane < (int)head) dst[lane] = (uint8_t)((bits[lane >> 2] >> (24 - 8 * (lane & 3))) & 0xFFu);
+    const uint32_t nwords = (nbytes - head) >> 2;
+    uint32_t *dw = reinterpret_cast<uint32_t *>(dst + head);
+    const uint32_t sh8 = head * 8u;
+    for (uint32_t j = lane; j < nwords; j += 32) {
+        const uint32_t w0 = bits[j], w1 = bits[j + 1];
+        const uint32_t v = head ? __funnelshift_l(w1, w0, sh8) : w0;
+        dw[j] = frx_bswap32(v);
+    }
+    const uint32_t tail0 = head + (nwords << 2);
+    if (lane < (int)(nbytes - tail0)) {
+        const uint32_t b = tail0 + (uint32_t)lane;
+        dst[b] = (uint8_t)((bits[b >> 2] >> (24 - 8 * (b & 3))) & 0xFFu);
+    }
 }
 
-// ------------------------------------------------------------------------------------------
-// The frame encoder.  WIDE: PCM wider than 16 bits (64-bit LPC accumulate, RICE2).  HISTN: history samples a thread
-// reads = the largest LPC order of the compression level (4 when the level has no LPC stage).
-// 8 compute warps (one frame at a time, 16 samples per thread) + 1 control warp.  The PCM of the current subframe
-// lives in padded shared memory and every stage re-reads it, so almost no register state crosses a barrier.
-// ------------------------------------------------------------------------------------------
-template <bool WIDE, int HISTN>
-__global__ void __launch_bounds__(FRX_ENC_CTA, 2) frx_encode_kernel(const EncArgs a) {
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    EncSmall &sh = *reinterpret_cast<EncSmall *>(smem_raw);
-    const uint32_t stage_stride = 128u + (uint32_t)FRX_MAX_BLOCK * (uint32_t)frx_dtype_size(a.dtype);
-    unsigned char *raw = smem_raw + ENC_SMALL_BYTES;
-    int32_t *pcm = reinterpret_cast<int32_t *>(raw + stage_stride);
-    int32_t *res = reinterpret_cast<int32_t *>(reinterpret_cast<unsigned char *>(pcm) + PCM_BYTES);
-    uint64_t *tabs = reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(res) + RES_BYTES);
-    uint32_t *bits0 = reinterpret_cast<uint32_t *>(reinterpret_cast<unsigned char *>(tabs) + TABS_BYTES);
+// ==========================================================================================
+// per-subframe search: CONSTANT / VERBATIM / best FIXED order / LPC, each Rice-coded candidate costed from its partition
+// sums, the winner's residuals left in the buffer, its exact size counted
+// ==========================================================================================
+#define BUF_PCM 0
+#define BUF_RES 1
+#define BUF_JUNK 2
+struct BufState { int kind, vch, type, order; };
 
+__device__ __forceinline__ void shift_wasted(uint32_t *pcm, int nsamp, int wasted, int lane) {
+    const int gend = min(FRX_MAX_BLOCK, ((nsamp + BLK - 1) / BLK) * BLK);
+    for (int g = lane; g < gend; g += 32) pcm[PIDX(g)] = (uint32_t)((int32_t)pcm[PIDX(g)] >> wasted);
+    __syncwarp();
+}
+__device__ __forceinline__ void save_warmup(WarpSh &ws, const uint32_t *pcm, int order, int lane) {
+    if (lane < order) ws.warm[lane] = (int32_t)pcm[PIDX(lane)];
+    __syncwarp();
+}
+
+// residuals of the recorded decision into the buffer (the buffer holds the PCM of d.vch, wasted bits already shifted out)
+template <bool WIDE, int H>
+__device__ __forceinline__ bool residuals_inplace(WarpSh &ws, uint32_t *buf, const SubDec &d, int nsamp, unsigned long long *bins, int psf, int lane,
+                                                  uint64_t &sumA, uint64_t &sumB) {
+    uint32_t *pcm = buf + SLACK_W;
+    const int type = d.type, order = d.order, shift = d.shift, narrow = d.narrow;
+    const bool fast = d.fast != 0;
+    save_warmup(ws, pcm, order, lane);
+    bool ok = true;
+    sumA = 0; sumB = 0;
+    if (fast) {
+        if (type == 3) lpc_inplace_full_any<H, WIDE>(ws, pcm, shift, narrow, lane, sumA, sumB);
+        else fixed_inplace_full(pcm, order, lane);
+        // warm-up samples are not coded: take their |r| out of the first half's sum and zero them
+        uint32_t wv = 0;
+        if (lane < order) { wv = unzig_abs(pcm[lane]); pcm[lane] = 0u; }
+        const uint64_t wsum = warp_sum_u64(wv);
+        if (lane == 0 && type == 3) sumA -= wsum;
+        __syncwarp();
+    } else {
+        ok = resid_inplace_generic(ws, pcm, bins, nsamp, type == 3, order, shift, psf, lane);
+    }
+    return ok;
+}
+
+template <bool WIDE, int H>
+__device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint32_t *buf, int vch, int ci, uint32_t startbits, uint32_t &phase,
+                                             BufState &bs, int lane) {
+    SubDec &d = ws.dec[ci];
+    const FrameDesc &fd = ws.fd;
+    uint32_t *pcm = buf + SLACK_W;
+    const int nsamp = fd.nsamp;
+    const bool full = nsamp == FRX_MAX_BLOCK;
+    const uint2 st = load_channel(a, ws, buf, vch, phase, lane);
+    const uint32_t orv = st.x, ora = st.y;
+    const int wasted = orv ? (__ffs((int)orv) - 1) : 0;
+    if (wasted) shift_wasted(pcm, nsamp, wasted, lane);
+    const int magbits = 32 - __clz((int)(ora >> wasted));          // |sample| <= 2^magbits
+    const int sbps = a.bps + (vch == 9 ? 1 : 0) - wasted;
+    const bool fast = full && magbits <= 23;
+    const uint32_t kmax = a.bps > 16 ? 30u : 14u;                    // RICE2 only for bps > 16 (libFLAC)
+    const int po_max = fd.po_max;
+    const int max_lpc = min((int)fd.max_lpc, H);
+    const uint64_t verb_bits = 8ull + (uint64_t)wasted + (uint64_t)nsamp * (uint64_t)sbps;
+    bs.kind = BUF_PCM; bs.vch = vch; bs.type = 1; bs.order = 0;
+    if (lane == 0) {
+        d.type = 1; d.order = 0; d.wasted = (uint8_t)wasted; d.po = 0; d.rice2 = 0; d.precision = 0; d.sbps = (uint8_t)sbps; d.vch = (uint8_t)vch;
+        d.fast = fast ? 1 : 0; d.narrow = 1; d.shift = 0; d.bits = (uint32_t)verb_bits;
+    }
+    __syncwarp();
+
+    // ---- K2 + K3 ----
+    uint64_t tot[5];
+    uint64_t fsl[5][2];
+    uint32_t badmask = 0;
+    float autoc[H + 1];
+    if (fast) {
+        float acl[H + 1];
+        pass1_full<H>(pcm, lane, fsl, acl);
+        if (lane == 0) {   // warm-up rule: sample g counts for order k only when g >= k
+            int32_t prev = 0, d1p = 0, d2p = 0, d3p = 0;
+#pragma unroll
+            for (int g = 0; g < 4; g++) {
+                const int32_t x = (int32_t)pcm[g];
+                const int32_t d1 = x - prev, d2 = d1 - d1p, d3 = d2 - d2p, d4 = d3 - d3p;
+                prev = x; d1p = d1; d2p = d2; d3p = d3;
+                if (g < 1) fsl[1][0] -= (uint32_t)abs(d1);
+                if (g < 2) fsl[2][0] -= (uint32_t)abs(d2);
+                if (g < 3) fsl[3][0] -= (uint32_t)abs(d3);
+                fsl[4][0] -= (uint32_t)abs(d4);
+            }
+        }
+#pragma unroll
+        for (int o = 0; o < 5; o++) tot[o] = warp_sum_u64(fsl[o][0] + fsl[o][1]);
+#pragma unroll
+        for (int k = 0; k <= H; k++) autoc[k] = warp_sum_f32(acl[k]);
+    } else {
+#pragma unroll
+        for (int o = 0; o < 5; o++) { fsl[o][0] = 0; fsl[o][1] = 0; }
+        pass1_generic<H>(pcm, nsamp, max_lpc, lane, tot, badmask, autoc);
+    }
+    if (tot[1] == 0 && !(badmask & 2u)) {     // sum |s[g] - s[g-1]| == 0  <=>  all samples equal
+        if (lane == 0) { d.type = 0; d.bits = 8u + (uint32_t)wasted + (uint32_t)sbps; }
+        __syncwarp();
+        return;
+    }
+    int fixed_order = -1;
+    if (nsamp > 4) {
+        uint64_t bestv = ~0ull;
+#pragma unroll
+        for (int o = 0; o < 5; o++)
+            if (!((badmask >> o) & 1u) && tot[o] < bestv) { bestv = tot[o]; fixed_order = o; }
+    }
+    // ---- K4 ----
+    LpcChoice lc;
+    lc.ok = 0; lc.order = 0; lc.shift = 0; lc.precision = 0; lc.narrow = 1;
+    if (max_lpc > 0 && nsamp > 4) lc = lpc_design<WIDE, H>(ws, autoc, max_lpc, nsamp, sbps, a.qlp_precision, magbits, lane);
+
+    unsigned long long *bins = reinterpret_cast<unsigned long long *>(buf);   // generic path: 32 sums in the slack words
+    const int Fg = po_max > 5 ? 5 : po_max;
+    const int psf = nsamp >> Fg;
+    uint64_t best_bits = verb_bits;
+    int type = 1, order = 0, po = 0, cand = 0;
+    bool rice2 = false;
+    // ---- fixed candidate: cost from its partition sums ----
+    if (fixed_order >= 0) {
+        RiceChoice rf;
+        if (fast) {
+            uint64_t sA = 0, sB = 0;
+#pragma unroll
+            for (int o = 0; o < 5; o++) if (o == fixed_order) { sA = fsl[o][0]; sB = fsl[o][1]; }
+            rf = analyse_partitions(ws.kparam[0], sA, sB, nsamp, fixed_order, po_max, 5, kmax);
+        } else {
+            bins[lane] = 0ull;
+            __syncwarp();
+            fixed_sums_generic(pcm, bins, nsamp, fixed_order, psf, lane);
+            const uint64_t sA = lane < (1 << Fg) ? bins[lane] : 0ull;
+            __syncwarp();
+            rf = analyse_partitions(ws.kparam[0], sA, 0ull, nsamp, fixed_order, Fg, Fg, kmax);
+        }
+        const uint64_t b = 8ull + wasted + (uint64_t)fixed_order * sbps + rf.bits;
+        if (b < best_bits) { best_bits = b; type = 2; order = fixed_order; po = rf.po; rice2 = rf.rice2; cand = 0; }
+    }
+    // ---- LPC candidate: residuals in place (the usual winner), cost from their partition sums ----
+    if (lc.ok) {
+        if (lane == 0) { d.type = 3; d.order = (uint8_t)lc.order; d.shift = lc.shift; d.narrow = (uint8_t)lc.narrow; d.precision = (uint8_t)lc.precision; }
+        __syncwarp();
+        uint64_t sA = 0, sB = 0;
+        if (!fast) { bins[lane] = 0ull; __syncwarp(); }
+        const bool ok = residuals_inplace<WIDE, H>(ws, buf, d, nsamp, bins, psf, lane, sA, sB);
+        bs.kind = ok ? BUF_RES : BUF_JUNK; bs.type = 3; bs.order = lc.order;
+        if (ok) {
+            RiceChoice rl;
+            if (fast) rl = analyse_partitions(ws.kparam[1], sA, sB, nsamp, lc.order, po_max, 5, kmax);
+            else {
+                sA = lane < (1 << Fg) ? bins[lane] : 0ull;
+                __syncwarp();
+                rl = analyse_partitions(ws.kparam[1], sA, 0ull, nsamp, lc.order, Fg, Fg, kmax);
+            }
+            const uint64_t b = 8ull + wasted + 9ull + (uint64_t)lc.order * (uint64_t)(lc.precision + sbps) + rl.bits;
+            if (b < best_bits) { best_bits = b; type = 3; order = lc.order; po = rl.po; rice2 = rl.rice2; cand = 1; }
+        }
+    }
+    if (type == 1) {
+        if (lane == 0) { d.type = 1; d.order = 0; }
+        __syncwarp();
+        return;
+    }
+    // ---- record the winner; make the buffer hold its residuals ----
+    if (lane == 0) {
+        d.type = (uint8_t)type; d.order = (uint8_t)order; d.po = (uint8_t)po; d.rice2 = rice2 ? 1 : 0;
+        if (type == 2) { d.precision = 0; d.shift = 0; }
+    }
+    if (lane < FRX_MAX_LPC) d.qlp[lane] = type == 3 ? (int16_t)ws.qlp[lane] : (int16_t)0;
+    d.k[lane] = ws.kparam[cand][lane]; d.k[lane + 32] = ws.kparam[cand][lane + 32];
+    __syncwarp();
+    if (type == 2) {
+        if (bs.kind != BUF_PCM) {
+            (void)load_channel(a, ws, buf, vch, phase, lane);
+            if (wasted) shift_wasted(pcm, nsamp, wasted, lane);
+        }
+        uint64_t x0, x1;
+        (void)residuals_inplace<WIDE, H>(ws, buf, d, nsamp, nullptr, psf, lane, x0, x1);
+        bs.kind = BUF_RES; bs.type = 2; bs.order = order;
+    }
+    // ---- exact size ----
+    const uint32_t pb = rice2 ? 5u : 4u;
+    const uint32_t hb = 8u + (uint32_t)wasted + (uint32_t)order * (uint32_t)sbps + (type == 3 ? 9u + (uint32_t)order * (uint32_t)lc.precision : 0u) + 6u;
+    uint32_t total;
+    bool inplace_ok;
+    if (fast) {
+        const int psh = 12 - po;                                   // log2(samples per partition)
+        const int g0 = lane * BLK;
+        const uint32_t k0 = d.k[g0 >> psh], k1 = d.k[(g0 + BLK / 2) >> psh];
+        uint32_t c = count_full(pcm, lane, k0, k1);
+        if (lane == 0) c -= (uint32_t)order * (k0 + 1u);           // warm-up samples carry no code (their slots hold 0)
+        if ((g0 & ((1 << psh) - 1)) == 0) c += pb;
+        if (po == 6) c += pb;
+        if (lane == 0) c += hb;
+        uint32_t incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t n = __shfl_up_sync(FULLMASK, incl, o);
+            if (lane >= o) incl += n;
+        }
+        total = __shfl_sync(FULLMASK, incl, 31);
+        inplace_ok = __all_sync(FULLMASK, startbits + incl <= 32u * (SLACK_W + BLK_W * ((uint32_t)lane + 1u)));
+    } else {
+        total = hb + count_generic(pcm, d.k, nsamp, order, nsamp >> po, pb, startbits + hb, inplace_ok, lane);
+    }
+    if ((uint64_t)total >= verb_bits || !inplace_ok) {
+        // the Rice-coded subframe would not beat VERBATIM (or cannot be packed in place): write it verbatim
+        if (lane == 0) { d.type = 1; d.order = 0; d.bits = (uint32_t)verb_bits; }
+    } else if (lane == 0) d.bits = total;
+    __syncwarp();
+}
+
+// make the buffer hold what packing subframe d needs: its PCM (CONSTANT / VERBATIM) or its residuals
+template <bool WIDE, int H>
+__device__ __noinline__ void materialise(const EncArgs &a, WarpSh &ws, uint32_t *buf, const SubDec &d, uint32_t &phase, BufState &bs, int lane) {
+    const bool want_res = d.type >= 2;
+    if (bs.vch == d.vch) {
+        if (want_res && bs.kind == BUF_RES && bs.type == d.type && bs.order == d.order) return;
+        if (!want_res && bs.kind == BUF_PCM) return;
+    }
+    uint32_t *pcm = buf + SLACK_W;
+    (void)load_channel(a, ws, buf, d.vch, phase, lane);
+    if (d.wasted) shift_wasted(pcm, ws.fd.nsamp, d.wasted, lane);
+    bs.kind = BUF_PCM; bs.vch = d.vch;
+    if (want_res) {
+        if (lane < FRX_MAX_LPC) ws.qlp[lane] = d.qlp[lane];
+        __syncwarp();
+        uint64_t x0, x1;
+        (void)residuals_inplace<WIDE, H>(ws, buf, d, ws.fd.nsamp, nullptr, 1, lane, x0, x1);
+        bs.kind = BUF_RES; bs.type = d.type; bs.order = d.order;
+    }
+}
+
+// ==========================================================================================
+// The frame encoder.  WIDE: PCM wider than 16 bits (RICE2 parameters, 64-bit LPC accumulate when needed).  H: history
+// samples of the register windows = the largest LPC order of the compression level (4 when the level has no LPC stage).
+// ==========================================================================================
+template <bool WIDE, int H>
+__global__ void __launch_bounds__(ENC_CTA, 1) frx_encode_kernel(const EncArgs a) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    uint16_t (*crc_tab)[256] = reinterpret_cast<uint16_t (*)[256]>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < 2 * a.frame_words; i += FRX_ENC_CTA) bits0[i] = 0u;
-    for (int i = tid; i < PCM_WORDS; i += FRX_ENC_CTA) pcm[i] = 0;
-    for (int i = tid; i < 1024; i += FRX_ENC_CTA) (&sh.crc_tab[0][0])[i] = a.crc_tab[i];
-    if (tid == 0) {
-        mbar_init(&sh.full[0], 1); mbar_init(&sh.empty[0], NWARPS);
-        for (int i = 0; i < FD_SLOTS; i++) { mbar_init(&sh.sized[i], 1); mbar_init(&sh.placed[i], 1); }
+    unsigned char *wbase = smem_raw + 2048 + (size_t)warp * WARP_BYTES;
+    WarpSh &ws = *reinterpret_cast<WarpSh *>(wbase);
+    uint32_t *buf = reinterpret_cast<uint32_t *>(wbase + WARP_SH_BYTES);
+    uint32_t *pcm = buf + SLACK_W;
+    for (int i = tid; i < 1024; i += ENC_CTA) (&crc_tab[0][0])[i] = a.crc_tab[i];
+    if (lane == 0) {
+        mbar_init(&ws.mbar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
     __syncthreads();
-    if (warp == NWARPS) { control_warp(a, sh, raw, lane); return; }
+    uint32_t phase = 0;
+    int ti = 0;
+    const bool stereo = a.stereo != 0;
 
-    const uint32_t kmax = a.bps > 16 ? 30u : 14u;  // RICE2 only for bps > 16 (libFLAC)
-    const int g0 = tid * FRX_SPT;                  // first sample index of this thread
-    uint32_t unit = 0, fseq = 0;
-    // copy-out runs one frame behind (double-buffered frame buffer), so the look-back never stalls the compute warps
-    bool pend = false;
-    uint32_t pend_body = 0;
-
-    const long long ck0 = DBG_CLK();
-    DBG_PH_DECL;
     for (;;) {
-        // ---- next frame: its descriptor is valid once the first raw stage of the frame is full ----
-        const int slot = (int)(fseq & (FD_SLOTS - 1));
-        const int buf = (int)(fseq & 1u);
-        uint32_t *bits = bits0 + (size_t)buf * a.frame_words;
-        mbar_wait(&sh.full[0], unit & 1u);
-        const FrameDesc &fd = sh.fd[slot];
-        const uint32_t f = fd.f;
-        if (f == STOP_FRAME) { if (tid == 0) DBG_ADD(7, DBG_CLK() - ck0); break; }
-        if (tid == 0) DBG_TRACE(f, 4);
-        DBG_PH(15);
-        const int n_channels = fd.t.n_channels;
-        const uint32_t s0 = fd.s0;
-        const int nsamp = fd.nsamp;
-        const bool use_tma = fd.tma != 0;
-        const int nv = min(FRX_SPT, max(0, nsamp - g0));  // valid samples of this thread
-        const bool full = (nsamp == FRX_MAX_BLOCK);
-        const bool plain = full && tid != 0;              // no per-sample masks needed for this thread
-        uint32_t bitpos = fd.hdr_bits;
-        if (tid < 4) bits[tid] = fd.hdr[tid];
-        const int po_max = fd.po_max;
-        const int max_lpc = min((int)fd.max_lpc, HISTN);
+        uint32_t f = 0;
+        if (lane == 0) f = atomicAdd(a.ticket, 1u);
+        f = __shfl_sync(FULLMASK, f, 0);
+        if (f >= a.total_frames) break;
+        build_frame_desc(a, ws.fd, f, ti, lane);
+        const int nsamp = ws.fd.nsamp;
+        const int n_ch = ws.fd.t.n_channels;
+        BufState bs;
+        bs.kind = BUF_JUNK; bs.vch = -1; bs.type = 0; bs.order = 0;
 
-        // ================= per channel =================
-        for (int ch = 0; ch < n_channels; ch++) {
-            unsigned char *stg = raw;
-            if (ch > 0) mbar_wait(&sh.full[0], unit & 1u);
-            if (!use_tma) {
-                gather_raw(a, fd.t, ch, s0, nsamp, stg, tid);
-                compute_sync();
-            }
-            // ---- K1: the thread's 16 samples -> PCM -> shared memory ----
-            uint32_t orv = 0, ora = 0;
-            {
-                uint2 oo;
-                if (a.dtype == FRX_F32) oo = k1_quantize<FRX_F32, WIDE>(stg, fd.q, a.pcm_mode, tid, nv, pcm);
-                else if (a.dtype == FRX_U16) oo = k1_quantize<FRX_U16, WIDE>(stg, fd.q, a.pcm_mode, tid, nv, pcm);
-                else oo = k1_quantize_any<WIDE>(a.dtype, stg, fd.q, a.pcm_mode, tid, nv, pcm);
-                orv = oo.x; ora = oo.y;
-                // the raw stage may be refilled as soon as every warp has read its samples
-                if (!use_tma) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&sh.empty[0]);
-                unit++;
-            }
-            orv = __reduce_or_sync(FULLMASK, orv);
-            if (WIDE) ora = __reduce_or_sync(FULLMASK, ora);
-            compute_sync();  // S0: PCM of the subframe is in shared memory
-            DBG_PH(9);
-            // ---- K2 (lean, 32-bit) fixed-order trial + K3 windowed autocorrelation partials ----
-            {
-                int32_t s[HISTN + FRX_SPT];
-                read_pcm<HISTN>(pcm, tid, 0, s);
-                uint32_t fa[5];
-                if (plain) fixed_trial32<HISTN>(s, fa);
-                else fixed_trial32_masked<HISTN>(s, g0, nv, fa);
-#pragma unroll
-                for (int o = 0; o < 5; o++) tabs[o * FRX_ENC_THREADS + tid] = fa[o];
-                {
-                    uint64_t w5[5];
-#pragma unroll
-                    for (int o = 0; o < 5; o++) w5[o] = WIDE ? warp_sum_u32_wide(fa[o]) : (uint64_t)__reduce_add_sync(FULLMASK, fa[o]);
-                    if (lane == 0) {
-#pragma unroll
-                        for (int o = 0; o < 5; o++) sh.wfix[warp][o] = w5[o];
-                        sh.wor[warp][0] = orv; sh.wor[warp][1] = ora;
-                    }
-                }
-                if (max_lpc > 0) {
-                    float xw[HISTN + FRX_SPT];
-                    if (full) {
-                        // window table: zero history of thread 0 comes from the zero samples in front of the PCM buffer
-                        const float4 *w4 = reinterpret_cast<const float4 *>(a.window + g0 - HISTN);
-#pragma unroll
-                        for (int v = 0; v < (HISTN + FRX_SPT) / 4; v++) {
-                            float4 wv = make_float4(0.f, 0.f, 0.f, 0.f);
-                            if (tid > 0 || v >= HISTN / 4) wv = __ldg(w4 + v);
-                            xw[4 * v] = (float)s[4 * v] * wv.x; xw[4 * v + 1] = (float)s[4 * v + 1] * wv.y;
-                            xw[4 * v + 2] = (float)s[4 * v + 2] * wv.z; xw[4 * v + 3] = (float)s[4 * v + 3] * wv.w;
-                        }
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < HISTN + FRX_SPT; i++) xw[i] = (float)s[i] * tukey_w(g0 - HISTN + i, nsamp);
-                    }
-                    float ac[HISTN + 1];
-#pragma unroll
-                    for (int lag = 0; lag <= HISTN; lag++) ac[lag] = 0.f;
-#pragma unroll
-                    for (int i = 0; i < FRX_SPT; i++) {
-#pragma unroll
-                        for (int lag = 0; lag <= HISTN; lag++) ac[lag] = fmaf(xw[HISTN + i], xw[HISTN + i - lag], ac[lag]);
-                    }
-#pragma unroll
-                    for (int lag = 0; lag <= HISTN; lag++) {
-                        float v = ac[lag];
-#pragma unroll
-                        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULLMASK, v, o);
-                        if (lane == 0) sh.wac[warp][lag] = v;
-                    }
-                }
-            }
-            compute_sync();  // SA: per-warp partials and tabs[0..4] are in shared memory
-            DBG_PH(10);
-            // ---- every warp: fixed-order decision (cheap, redundant).  Warps 0..6: Rice search of the fixed candidate, one
-            //      partition order each; warp 7: LPC design ----
-            {
-                uint64_t tot = 0;
-                uint32_t o32 = 0;
-                if (lane < 5) { for (int w2 = 0; w2 < NWARPS; w2++) tot += sh.wfix[w2][lane]; }
-                else if (lane < 7) { for (int w2 = 0; w2 < NWARPS; w2++) o32 |= sh.wor[w2][lane - 5]; }
-                const uint32_t all_or = __shfl_sync(FULLMASK, o32, 5), all_abs = __shfl_sync(FULLMASK, o32, 6);
-                const int wasted = all_or ? (__ffs((int)all_or) - 1) : 0;
-                const int magbits = WIDE ? 32 - __clz((int)all_abs) : 15;  // bits of the largest magnitude
-                const bool lean = !WIDE || magbits <= 23;
-                if (warp == NWARPS - 1) {
-                    float acs = 0.f;
-                    if (lane <= max_lpc) { for (int w2 = 0; w2 < NWARPS; w2++) acs += sh.wac[w2][lane]; }
-                    if (lane <= FRX_MAX_LPC) sh.autoc[lane] = acs;
-                    if (lane == 0) { sh.magbits = magbits; sh.lean = lean ? 1 : 0; sh.lpc_ok = 0; }
-                    __syncwarp();
-                    const long long cl0 = DBG_CLK();
-                    if (max_lpc > 0 && nsamp > 4)
-                        lpc_design<WIDE, HISTN>(sh, max_lpc, nsamp, wasted, a.bps - wasted, a.qlp_precision, magbits, lean, lane);
-                    if (lane == 0) DBG_ADD(1, DBG_CLK() - cl0);
-                } else {
-                    const uint64_t f1 = __shfl_sync(FULLMASK, tot, 1);
-                    uint64_t bestv = (lane < 5) ? tot : ~0ull;   // best fixed order among lanes 0..4 (lowest order wins ties)
-                    int besto = lane;
-                    for (int o = 1; o < 8; o <<= 1) {
-                        const uint64_t ov = __shfl_xor_sync(FULLMASK, bestv, o);
-                        const int oo = __shfl_xor_sync(FULLMASK, besto, o);
-                        if (ov < bestv || (ov == bestv && oo < besto)) { bestv = ov; besto = oo; }
-                    }
-                    besto = __shfl_sync(FULLMASK, besto, 0);
-                    const int fixed_order = (nsamp > 4) ? besto : -1;
-                    if (warp == 0 && lane == 0) {
-                        sh.wasted = wasted;
-                        sh.is_const = (f1 == 0) ? 1 : 0;   // sum |s[g]-s[g-1]| == 0  <=>  all samples equal
-                        sh.fixed_order = fixed_order;
-                    }
-                    if (fixed_order >= 0 && lean) {          // fat data: fat_search redoes the fixed candidate in 64 bits
-                        const long long ca0 = DBG_CLK();
-                        if (full) {
-                            if (warp <= po_max) analyse_level(sh, tabs + fixed_order * FRX_ENC_THREADS, 0, warp, fixed_order, kmax, wasted);
-                            if (lane == 0 && warp == 6) DBG_ADD(0, DBG_CLK() - ca0);
-                            if (lane == 0 && warp == 0) DBG_ADD(2, DBG_CLK() - ca0);
-                        } else if (warp == 0) analyse_partitions(sh, tabs + fixed_order * FRX_ENC_THREADS, 0, nsamp, fixed_order, po_max, kmax, wasted);
-                    }
-                }
-            }
-            compute_sync();  // SB
-            DBG_PH(11);
-            const int wasted = sh.wasted;
-            const bool lean = sh.lean != 0;
-            const int sbps = a.bps - wasted;
-            const int lpc_order = sh.lpc_order;
-            const int lshift = sh.shift;
-            if (WIDE && !lean) {
-                fat_search<HISTN>(sh, pcm, tabs, tid, nv, nsamp, wasted, po_max, kmax);
-            } else {
-                // ---- K5: LPC residuals (kept in registers) and their |r| sums ----
-                const bool lpc_try0 = sh.lpc_ok != 0;
-                if (lpc_try0) {
-                    int32_t s[HISTN + FRX_SPT], q[HISTN];
-                    read_pcm<HISTN>(pcm, tid, wasted, s);
-#pragma unroll
-                    for (int j = 0; j < HISTN; j++) q[j] = sh.qlp[j];
-                    uint32_t ab;
-                    if (!WIDE || sh.lpc_narrow) ab = lpc_residuals_park<0, HISTN>(s, q, lshift, res, tid, plain, nv, lpc_order - g0);
-                    else ab = lpc_residuals_park<1, HISTN>(s, q, lshift, res, tid, plain, nv, lpc_order - g0);
-                    tabs[5 * FRX_ENC_THREADS + tid] = ab;
-                }
-                compute_sync();  // SC
-                DBG_PH(8);
-                if (lpc_try0) {
-                    if (full) { if (warp <= po_max) analyse_level(sh, tabs + 5 * FRX_ENC_THREADS, 1, warp, lpc_order, kmax, 0); }
-                    else if (warp == 1) analyse_partitions(sh, tabs + 5 * FRX_ENC_THREADS, 1, nsamp, lpc_order, po_max, kmax, 0);
-                }
-                compute_sync();  // SD
-                DBG_PH(12);
-            }
-            const int fixed_order = sh.fixed_order;
-            const bool is_const = sh.is_const != 0;
-            const bool lpc_try = sh.lpc_ok != 0;
-
-            // ---- choose ----
-            const uint64_t verb_bits = 8ull + (uint64_t)wasted + (uint64_t)nsamp * (uint64_t)sbps;
-            int type = 1, order = 0, cand = 0, po = 0;
-            bool rice2 = false;
-            uint64_t best_bits = verb_bits;
-            if (is_const) { type = 0; best_bits = 8ull + wasted + sbps; }
-            else {
-                if (fixed_order >= 0) {
-                    int lp; uint64_t lb; bool l2;
-                    pick_level(sh, 0, po_max, lp, lb, l2);
-                    const uint64_t b = 8ull + wasted + (uint64_t)fixed_order * sbps + lb;
-                    if (b < best_bits) { best_bits = b; type = 2; order = fixed_order; cand = 0; po = lp; rice2 = l2; }
-                }
-                if (lpc_try) {
-                    int lp; uint64_t lb; bool l2;
-                    pick_level(sh, 1, po_max, lp, lb, l2);
-                    const uint64_t b = 8ull + wasted + 9ull + (uint64_t)lpc_order * (uint64_t)(sh.precision + sbps) + lb;
-                    if (b < best_bits) { best_bits = b; type = 3; order = lpc_order; cand = 1; po = lp; rice2 = l2; }
-                }
-            }
-            // ---- K7a: winner's residuals (zig-zag folded), exact bit count per thread, block scan ----
-            const uint32_t sub_start = bitpos;
-            const uint32_t smask = sbps >= 32 ? 0xFFFFFFFFu : ((1u << sbps) - 1u);
-            int psize = nsamp;
-            uint32_t kk = 0;
-            uint32_t mybits = 0;
-            const int skip = (tid == 0) ? order : 0;
-            if (type >= 2) {
-                psize = nsamp >> po;
-                kk = sh.kparam[cand][(1 << po) - 1 + min(g0 / psize, (1 << po) - 1)];
-                int32_t r[FRX_SPT];
-                if (type == 2 || (WIDE && !lean)) {
-                    // fixed winner (4 ops per sample) or a fat-path LPC winner: recompute from the PCM, park in the residual buffer
-                    int32_t s[HISTN + FRX_SPT];
-                    read_pcm<HISTN>(pcm, tid, wasted, s);
-                    if (type == 2) {
-                        if (WIDE && !lean) (void)fixed_residuals<true, HISTN>(order, s, r);
-                        else (void)fixed_residuals<false, HISTN>(order, s, r);
-                    } else if (WIDE) {
-                        int32_t q[HISTN];
-#pragma unroll
-                        for (int j = 0; j < HISTN; j++) q[j] = sh.qlp[j];
-                        (void)lpc_residuals_dispatch<1, HISTN>(order, s, q, lshift, r);
-                    }
-#pragma unroll
-                    for (int i = 0; i < FRX_SPT; i++) res[RES_IDX(i, tid)] = r[i];
-                } else {
-                    // lean LPC winner: K5 left its residuals in the buffer
-#pragma unroll
-                    for (int i = 0; i < FRX_SPT; i++) r[i] = res[RES_IDX(i, tid)];
-                }
-                if (plain) {
-                    uint32_t qs = 0;
-#pragma unroll
-                    for (int i = 0; i < FRX_SPT; i++) qs += zigzag(r[i]) >> kk;
-                    mybits = qs + (uint32_t)FRX_SPT * (1u + kk);
-                } else {
-#pragma unroll
-                    for (int i = 0; i < FRX_SPT; i++)
-                        if (i >= skip && i < nv) mybits += (zigzag(r[i]) >> kk) + 1u + kk;
-                }
-                if (nv > 0 && g0 % psize == 0) mybits += rice2 ? 5u : 4u;
-                if (tid == 0) {
-                    mybits += 8u + (uint32_t)wasted + (uint32_t)order * (uint32_t)sbps + 6u;
-                    if (type == 3) mybits += 9u + (uint32_t)order * (uint32_t)sh.precision;
-                }
-            } else if (type == 1) {
-                mybits = (uint32_t)nv * (uint32_t)sbps;
-                if (tid == 0) mybits += 8u + (uint32_t)wasted;
-            } else {
-                if (tid == 0) mybits = 8u + (uint32_t)wasted + (uint32_t)sbps;
-            }
-            uint32_t incl = mybits;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t n = __shfl_up_sync(FULLMASK, incl, o);
-                if (lane >= o) incl += n;
-            }
-            if (lane == 31) sh.scan[warp] = incl;
-            compute_sync();  // SE
-            DBG_PH(13);
-            uint32_t wbase = 0, total = 0;
-#pragma unroll
-            for (int w2 = 0; w2 < NWARPS; w2++) {
-                const uint32_t v = sh.scan[w2];
-                if (w2 < warp) wbase += v;
-                total += v;
-            }
-            if (type >= 2 && (uint64_t)total >= verb_bits) {
-                // the Rice-coded subframe would not beat VERBATIM: write it verbatim (keeps the frame inside its buffer)
-                type = 1;
-                mybits = (uint32_t)nv * (uint32_t)sbps;
-                if (tid == 0) mybits += 8u + (uint32_t)wasted;
-                incl = mybits;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const uint32_t n = __shfl_up_sync(FULLMASK, incl, o);
-                    if (lane >= o) incl += n;
-                }
-                if (lane == 31) sh.scan2[warp] = incl;
-                compute_sync();
-                wbase = 0; total = 0;
-#pragma unroll
-                for (int w2 = 0; w2 < NWARPS; w2++) {
-                    const uint32_t v = sh.scan2[w2];
-                    if (w2 < warp) wbase += v;
-                    total += v;
-                }
-            }
-            const uint32_t start = sub_start + wbase + incl - mybits;
-            bitpos = sub_start + total;
-            if (ch == n_channels - 1 && tid == 0) {
-                // the frame's size is final: hand it to the control warp so the look-back overlaps packing and the CRC
-                const uint32_t nb = ((bitpos + 7u) >> 3) + 2u;
-                if (f != 0) frx_st_relaxed_u64(&a.desc[f], (1ull << 62) | (uint64_t)nb);
-                DBG_TRACE(f, 1);   // flag A: size known, prefix not yet
-                sh.frame_bytes[slot] = nb;
-                mbar_arrive(&sh.sized[slot]);
-            }
-            // ---- K7b: pack ----
-            if (type >= 2) {
-                // every header field sits at a position known in closed form, so the lanes of warp 0 write them side by side
-                const uint32_t precision = (uint32_t)sh.precision;
-                const uint32_t p_warm = sub_start + 8u + (uint32_t)wasted;
-                const uint32_t p_lpc = p_warm + (uint32_t)order * (uint32_t)sbps;
-                const uint32_t p_rice = p_lpc + (type == 3 ? 9u + (uint32_t)order * precision : 0u);
-                if (tid == 0) {
-                    // subframe header: 0 | type(6) | wasted flag, then the wasted-bits count in unary
-                    const uint32_t tcode = type == 2 ? (8u | (uint32_t)order) : (32u | (uint32_t)(order - 1));
-                    put_field(bits, sub_start, (tcode << 1) | (wasted ? 1u : 0u), 8u);
-                    if (wasted) put_field(bits, sub_start + 8u + (uint32_t)wasted - 1u, 1u, 1u);
-                    if (type == 3) put_field(bits, p_lpc, ((precision - 1u) << 5) | ((uint32_t)sh.shift & 31u), 9u);
-                    put_field(bits, p_rice, ((rice2 ? 1u : 0u) << 4) | (uint32_t)po, 6u);
-                }
-                if (tid < order) {
-                    put_field(bits, p_warm + (uint32_t)tid * (uint32_t)sbps, (uint32_t)(pcm[PCM_IDX(tid)] >> wasted) & smask, (uint32_t)sbps);   // warm-up
-                    if (type == 3) put_field(bits, p_lpc + 9u + (uint32_t)tid * precision, (uint32_t)sh.qlp[tid] & ((1u << precision) - 1u), precision);
-                }
-                if (mybits) {
-                    uint32_t p = tid == 0 ? p_rice + 6u : start;
-                    if (g0 % psize == 0) {
-                        const uint32_t pb = rice2 ? 5u : 4u;
-                        if (kk) put_field(bits, p, kk, pb);
-                        p += pb;
-                    }
-                    pack_rice(bits, p, res, tid, kk, skip, nv, plain);
-                }
-            } else if (mybits) {
-                BitW bw;
-                bw.init(bits, start);
-                if (tid == 0) {
-                    bw.put((type == 0 ? 0u : 2u) | (wasted ? 1u : 0u), 8);
-                    if (wasted) { if (wasted > 1) bw.skip((uint32_t)wasted - 1u); bw.put(1u, 1); }
-                }
-                if (type == 0) {
-                    if (tid == 0) bw.put((uint32_t)(pcm[PCM_IDX(0)] >> wasted) & smask, sbps);
-                } else {
-                    for (int i = 0; i < nv; i++) bw.put((uint32_t)(pcm[PCM_IDX(g0 + i)] >> wasted) & smask, sbps);
-                }
-                bw.finish();
-            }
-            // the PCM buffer is rewritten by the next channel's K1: every reader of it (verbatim / warm-up packing) must be done
-            if (ch + 1 < n_channels) compute_sync();
-        }  // channels
-        const uint32_t crc_xp = crc_shift_factor(a, (bitpos + 7u) >> 3, tid);
-        compute_sync();  // Sa: every subframe is packed
-        DBG_PH(14);
-
-        // ---- frame footer: CRC-16 of this frame; copy-out of the PREVIOUS frame (its byte offset has had a frame time to arrive) ----
-        const uint32_t body_bytes = (bitpos + 7u) >> 3;
-        const long long cc0 = DBG_CLK();
-        crc_frame(a, sh, bits, sh.crc_part[buf], body_bytes, tid, crc_xp);
-
-        if (pend) {
-            const int pslot = (int)((fseq - 1u) & (FD_SLOTS - 1));
-            uint32_t *pbits = bits0 + (size_t)(buf ^ 1) * a.frame_words;
-            const long long cp0 = DBG_CLK();
-            mbar_wait(&sh.placed[pslot], ((fseq - 1u) / FD_SLOTS) & 1u);
-            if (tid == 0) { DBG_TRACE(f, 7); }
-            copy_out_frame(a, sh, pbits, sh.crc_part[buf ^ 1], sh.out_offset[pslot], pend_body, tid);
-            compute_sync();  // all reads of the previous frame's buffer are done
-            for (uint32_t j = tid; j <= (pend_body >> 2); j += FRX_ENC_THREADS) pbits[j] = 0u;
+        // ---- sweep 1: search every subframe, exact sizes ----
+        const int nsub = n_ch;
+        int sub0 = 0, sub1 = 1;     // decision records of the first two subframes (the stereo choice permutes them)
+        if (n_ch == 2 && stereo) {
+            // left, right, mid, side; the cheapest of L/R, L/S, S/R, M/S (libFLAC's exhaustive stereo decision)
+            analyse_channel<WIDE, H>(a, ws, buf, 0, 0, ws.fd.hdr_bits, phase, bs, lane);
+            analyse_channel<WIDE, H>(a, ws, buf, 1, 1, ws.fd.hdr_bits, phase, bs, lane);
+            analyse_channel<WIDE, H>(a, ws, buf, 8, 2, ws.fd.hdr_bits, phase, bs, lane);
+            analyse_channel<WIDE, H>(a, ws, buf, 9, 3, ws.fd.hdr_bits, phase, bs, lane);
+            const uint32_t bL = ws.dec[0].bits, bR = ws.dec[1].bits, bM = ws.dec[2].bits, bS = ws.dec[3].bits;
+            uint32_t best = bL + bR; int ca = 1; sub0 = 0; sub1 = 1;
+            if (bL + bS < best) { best = bL + bS; ca = 8; sub0 = 0; sub1 = 3; }
+            if (bR + bS < best) { best = bR + bS; ca = 9; sub0 = 3; sub1 = 1; }
+            if (bM + bS < best) { best = bM + bS; ca = 10; sub0 = 2; sub1 = 3; }
+            if (lane == 0) make_frame_header(a, ws.fd, ca);
+            __syncwarp();
+        } else {
+            for (int c = 0; c < n_ch; c++)
+                analyse_channel<WIDE, H>(a, ws, buf, c, c, c == 0 ? ws.fd.hdr_bits : 32u, phase, bs, lane);
         }
-        pend = true;
-        pend_body = body_bytes;
-        fseq++;
-        compute_sync();  // crc_part / cleared buffer visible; the next frame's header words go into a clean buffer
-        DBG_PH(5);
-    }
-    if (pend) {   // flush the last frame
-        const int pslot = (int)((fseq - 1u) & (FD_SLOTS - 1));
-        const int pbuf = (int)((fseq - 1u) & 1u);
-        mbar_wait(&sh.placed[pslot], ((fseq - 1u) / FD_SLOTS) & 1u);
-        copy_out_frame(a, sh, bits0 + (size_t)pbuf * a.frame_words, sh.crc_part[pbuf], sh.out_offset[pslot], pend_body, tid);
+        uint32_t frame_bits = ws.fd.hdr_bits;
+        for (int c = 0; c < nsub; c++) frame_bits += ws.dec[c == 0 ? sub0 : (c == 1 ? sub1 : c)].bits;
+        const uint32_t body_bytes = (frame_bits + 7u) >> 3;
+        const uint32_t nbytes = body_bytes + 2u;
+        if (lane == 0) {
+            // the frame's size is final: publish it, the look-back of the frames behind this one can proceed
+            if (f != 0) frx_st_relaxed_u64(&a.desc[f], (1ull << 62) | (uint64_t)nbytes);
+            if (a.frame_size) a.frame_size[f] = nbytes;
+        }
+
+        // ---- sweep 2: pack ----
+        Emitter em;
+        em.P = 0; em.carry = 0;
+        {
+            uint32_t val[1], len[1], zer[1] = { 0 };
+            const uint32_t hbits = ws.fd.hdr_bits;
+            val[0] = lane < 4 ? ws.fd.hdr[lane] : 0u;
+            len[0] = (uint32_t)max(0, min(32, (int)hbits - 32 * lane));
+            if (len[0] < 32u && len[0] > 0u) val[0] >>= (32u - len[0]);
+            emit_fields<1>(buf, em, val, len, zer, lane);
+        }
+        bool have_off = false, overflow = false;
+        uint64_t off = 0;
+        uint32_t done = 0;          // bytes of the frame already copied out (multi-channel frames go out subframe by subframe)
+        uint32_t crc_run = 0;
+        auto get_offset = [&]() {
+            LookBack lb;
+            lb.pos = (long long)f - 1; lb.exclusive = 0; lb.blocked = false;
+            while (!lookback_step(a, lb, lane)) { if (lb.blocked) __nanosleep(100); }
+            off = lb.exclusive;
+            if (lane == 0) {
+                frx_st_relaxed_u64(&a.desc[f], (2ull << 62) | (off + (uint64_t)nbytes));
+                if (a.frame_offset) a.frame_offset[f] = off;
+                if (f == a.total_frames - 1 && a.total_bytes) *a.total_bytes = off + nbytes;
+            }
+            have_off = true;
+            if (off + nbytes > a.capacity) {
+                overflow = true;
+                if (lane == 0) atomicExch(a.status, FRX_E_OVERFLOW);
+            }
+        };
+        for (int c = 0; c < nsub; c++) {
+            const SubDec &d = ws.dec[c == 0 ? sub0 : (c == 1 ? sub1 : c)];
+            materialise<WIDE, H>(a, ws, buf, d, phase, bs, lane);
+            pack_subframe_header(ws, buf, em, d, pcm, lane);
+            if (d.type >= 2) pack_rice(buf, em, d, pcm, nsamp, lane);
+            else if (d.type == 1) pack_verbatim(buf, em, d, pcm, nsamp, lane);
+            bs.kind = BUF_JUNK;                     // the packed bits now lie over the samples
+            if (c + 1 < nsub) {
+                // the next subframe needs the whole buffer: send the complete words of the stream on their way
+                if (!have_off) get_offset();
+                const uint32_t nw = em.P >> 5;
+                __syncwarp();
+                const uint32_t cs = crc_words(a, crc_tab, buf, nw, lane);
+                crc_run = (done ? frx_gf16_mulmod(crc_run, gf16_xpow32(nw)) : 0u) ^ cs;
+                if (!overflow) copy_words_out(a.bytes + off + done, buf, nw, lane);
+                done += nw * 4u;
+                em.P &= 31u;
+                __syncwarp();
+            }
+        }
+        // ---- frame footer: zero padding to a byte boundary, CRC-16 ----
+        {
+            const uint32_t p0 = em.P;
+            em.P = (em.P + 7u) & ~7u;
+            if ((p0 & 31u) && !(em.P & 31u)) {       // the padding completes the last word: it is still in the carry
+                if (lane == 0) buf[p0 >> 5] = em.carry;
+                em.carry = 0;
+            }
+        }
+        const uint32_t nw = em.P >> 5, tb = (em.P & 31u) >> 3;
+        __syncwarp();
+        uint32_t crc = crc_words(a, crc_tab, buf, nw, lane);
+        if (done) crc ^= frx_gf16_mulmod(crc_run, gf16_xpow32(nw));
+        for (uint32_t b = 0; b < tb; b++) {
+            const uint32_t byte = (em.carry >> (24 - 8 * b)) & 0xFFu;
+            crc = ((crc << 8) ^ crc_tab[0][((crc >> 8) ^ byte) & 0xFFu]) & 0xFFFFu;
+        }
+        if (!have_off) get_offset();
+        if (!overflow) {
+            uint8_t *dst = a.bytes + off + done;
+            copy_words_out(dst, buf, nw, lane);
+            if (lane < (int)tb) dst[nw * 4u + lane] = (uint8_t)((em.carry >> (24 - 8 * lane)) & 0xFFu);
+            if (lane == 4) dst[nw * 4u + tb] = (uint8_t)(crc >> 8);
+            if (lane == 5) dst[nw * 4u + tb + 1u] = (uint8_t)crc;
+        }
+        __syncwarp();
     }
 }
 
@@ -1731,7 +1705,8 @@ __global__ void frx_minmax_out_kernel(const FrxQuant *q, int dtype, double *mm) 
 // host launchers (called from frx_api.cu)
 // ------------------------------------------------------------------------------------------
 size_t frx_enc_smem_bytes(int frame_words, int dtype) {
-    return ENC_SMALL_BYTES + (128 + (size_t)FRX_MAX_BLOCK * frx_dtype_size(dtype)) + PCM_BYTES + RES_BYTES + TABS_BYTES + 2 * sizeof(uint32_t) * (size_t)frame_words;
+    (void)frame_words; (void)dtype;
+    return 2048 + (size_t)ENC_WARPS * WARP_BYTES;
 }
 
 size_t frx_minmax_raw_size() { return sizeof(MinMaxRaw); }
@@ -1762,19 +1737,17 @@ cudaError_t frx_launch_minmax(const frx_raster &r, const frx_tile *tiles_dev, co
 
 template <bool WIDE, int HISTN>
 static cudaError_t launch_encode_t(const EncArgs &a, int sm_count, cudaStream_t st) {
-    size_t smem = frx_enc_smem_bytes(a.frame_words, a.dtype);
+    const size_t smem = frx_enc_smem_bytes(0, 0);
     cudaError_t e = cudaFuncSetAttribute(frx_encode_kernel<WIDE, HISTN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(frx_encode_kernel<WIDE, HISTN>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e != cudaSuccess) return e;
-    int occ = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, frx_encode_kernel<WIDE, HISTN>, FRX_ENC_CTA, smem);
-    if (e != cudaSuccess) return e;
-    if (occ < 1) return cudaErrorLaunchOutOfResources;
-    long long grid = (long long)sm_count * occ;   // persistent: every CTA resident, tickets hand out the frames in order
-    if (grid > (long long)a.total_frames) grid = a.total_frames;
+    // persistent: one CTA of twelve frame warps per SM, tickets hand out the frames in order
+    long long grid = sm_count;
+    const long long need = ((long long)a.total_frames + ENC_WARPS - 1) / ENC_WARPS;
+    if (grid > need) grid = need;
     if (grid < 1) grid = 1;
-    frx_encode_kernel<WIDE, HISTN><<<(unsigned)grid, FRX_ENC_CTA, smem, st>>>(a);
+    frx_encode_kernel<WIDE, HISTN><<<(unsigned)grid, ENC_CTA, smem, st>>>(a);
     return cudaGetLastError();
 }
 
@@ -1823,11 +1796,3 @@ cudaError_t frx_launch_quantize(const frx_raster &r, const frx_tile &t, const Fr
     return cudaGetLastError();
 }
 
-#ifdef FRX_DBG
-extern "C" void frx_debug_trace(unsigned long long *dev_ptr) { cudaMemcpyToSymbol(g_frx_trace, &dev_ptr, sizeof(dev_ptr)); }
-extern "C" void frx_debug_read(unsigned long long *out, int reset) {
-    cudaDeviceSynchronize();
-    cudaMemcpyFromSymbol(out, g_frx_dbg, sizeof(unsigned long long) * 16);
-    if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(g_frx_dbg, z, sizeof(z)); }
-}
-#endif

@@ -10,7 +10,6 @@ struct EncArgs {
     const frx_tile *tiles;
     const uint32_t *frame_prefix;
     const FrxQuant *quant;
-    const float *window;
     const uint16_t *crc_xpow;   // [FRX_CRC_MAXLQ][256]: x^(128 * Lq * j) mod P, j = quad-chunks that follow a CRC thread's chunk of Lq quads
     const uint16_t *crc_xinv;   // [4]: x^(-32 z) mod P, undoes z zero words appended to the last quad
     const uint16_t *crc_tab;    // [4][256] slicing-by-4 CRC-16 tables
@@ -35,6 +34,7 @@ struct EncArgs {
     int frame_words;
     int dtype;
     int tma_ok;                 // raster base and strides are 16-byte multiples: rows can be staged with TMA bulk copies
+    int stereo;                 // two-channel streams try mid/side decorrelation (libFLAC levels 1, 2, 4..8; 16-bit PCM only)
 };
 struct DecArgs {
     const uint8_t *bytes;

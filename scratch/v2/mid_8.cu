@@ -115,7 +115,14 @@ __global__ void __launch_bounds__(ENC_CTA, 1) frx_encode_kernel(const EncArgs a)
             }
         }
         // ---- frame footer: zero padding to a byte boundary, CRC-16 ----
-        em.P = (em.P + 7u) & ~7u;
+        {
+            const uint32_t p0 = em.P;
+            em.P = (em.P + 7u) & ~7u;
+            if ((p0 & 31u) && !(em.P & 31u)) {       // the padding completes the last word: it is still in the carry
+                if (lane == 0) buf[p0 >> 5] = em.carry;
+                em.carry = 0;
+            }
+        }
         const uint32_t nw = em.P >> 5, tb = (em.P & 31u) >> 3;
         __syncwarp();
         uint32_t crc = crc_words(a, crc_tab, buf, nw, lane);
