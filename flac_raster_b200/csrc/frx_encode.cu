@@ -271,6 +271,9 @@ struct WarpSh {
     int32_t qlp[FRX_MAX_LPC];
     int32_t warm[FRX_MAX_LPC];
     uint8_t kparam[2][64];                       // candidate 0 = fixed, 1 = lpc; parameters of the candidate's best partition order
+    uint64_t g_tot[5];                           // generic path: results of pass1_generic
+    float g_ac[FRX_MAX_LPC + 1];
+    uint32_t g_bad;
     SubDec dec[FRX_MAX_CH];
 };
 #define WARP_SH_BYTES ((sizeof(WarpSh) + 127) & ~(size_t)127)
@@ -627,7 +630,7 @@ __device__ __forceinline__ void levinson(const float *an, int upto, float *lpc, 
     }
 }
 template <bool WIDE, int MAXO>
-__device__ __noinline__ LpcChoice lpc_design(WarpSh &ws, const float *autoc, int max_lpc, int nsamp, int sbps, int qlp_precision, int magbits, int lane) {
+__device__ __forceinline__ LpcChoice lpc_design(WarpSh &ws, const float *autoc, int max_lpc, int nsamp, int sbps, int qlp_precision, int magbits, int lane) {
     LpcChoice out;
     out.ok = 0; out.order = 0; out.shift = 0; out.precision = 0; out.narrow = 1;
     const float a0 = autoc[0];
@@ -737,8 +740,9 @@ __device__ __forceinline__ void walk_block(S &s, uint32_t *blk) {
     for (int half = 0; half < 2; half++) {
         uint32_t *hb = blk + (BLK / 2) * half;
 #pragma unroll 1
-        for (int it = 0; it < MAINH; it += NP) { RunPh<0, NP, S>::go(s, hb, it); s.fold(half); }
-        if constexpr (REMH > 0) { RunPh<0, REMH, S>::go(s, hb, MAINH); s.fold(half); s.template realign<REMH>(); }
+        for (int it = 0; it < MAINH; it += NP) { RunPh<0, NP, S>::go(s, hb, it); s.fold(); }
+        if constexpr (REMH > 0) { RunPh<0, REMH, S>::go(s, hb, MAINH); s.fold(); s.template realign<REMH>(); }
+        if (half == 0) s.end_first_half();
     }
 }
 template <int H>
@@ -764,7 +768,7 @@ struct P1 {
     float c0, c1, twoc, wa, wb;   // window recurrence: c_{n+1} = twoc c_n - c_{n-1}, w = wa - wb c;  c1 = cos(phase of the next sample)
     int32_t prev, d1p, d2p, d3p;
     uint32_t f[5];                // sums of the running rotation (<= 16 samples, |e4| < 2^27)
-    uint64_t fs[5][2];
+    uint64_t cur[5], first[5];    // sums of the running half / of the first half (no dynamically indexed arrays: registers)
     template <int P>
     __device__ __forceinline__ void step(uint32_t *p) {
         const uint4 v = *reinterpret_cast<const uint4 *>(p);
@@ -785,9 +789,13 @@ struct P1 {
             for (int lag = 0; lag <= H; lag++) ac[lag] = fmaf(xv, xw[(4 * P + H + i - lag) % W], ac[lag]);
         }
     }
-    __device__ __forceinline__ void fold(int half) {
+    __device__ __forceinline__ void fold() {
 #pragma unroll
-        for (int o = 0; o < 5; o++) { fs[o][half] += f[o]; f[o] = 0; }
+        for (int o = 0; o < 5; o++) { cur[o] += f[o]; f[o] = 0; }
+    }
+    __device__ __forceinline__ void end_first_half() {
+#pragma unroll
+        for (int o = 0; o < 5; o++) { first[o] = cur[o]; cur[o] = 0; }
     }
     template <int R>
     __device__ __forceinline__ void realign() {
@@ -833,10 +841,10 @@ __device__ __forceinline__ void pass1_full(uint32_t *pcm, int lane, uint64_t (&f
         st.d3p = st.d2p - (dm2 - dm3);
     }
 #pragma unroll
-    for (int o = 0; o < 5; o++) { st.f[o] = 0; st.fs[o][0] = 0; st.fs[o][1] = 0; }
+    for (int o = 0; o < 5; o++) { st.f[o] = 0; st.cur[o] = 0; st.first[o] = 0; }
     walk_block<H>(st, blk);
 #pragma unroll
-    for (int o = 0; o < 5; o++) { fs[o][0] = st.fs[o][0]; fs[o][1] = st.fs[o][1]; }
+    for (int o = 0; o < 5; o++) { fs[o][0] = st.first[o]; fs[o][1] = st.cur[o]; }
 #pragma unroll
     for (int k = 0; k <= H; k++) ac[k] = st.ac[k];
 }
@@ -851,7 +859,7 @@ struct P2 {
     int shift;
     uint32_t acc32;
     uint64_t acc64;
-    uint64_t tot[2];
+    uint64_t cur, first;
     template <int P>
     __device__ __forceinline__ void step(uint32_t *p) {
         const uint4 v = *reinterpret_cast<const uint4 *>(p);
@@ -876,9 +884,10 @@ struct P2 {
         }
         *reinterpret_cast<uint4 *>(p) = make_uint4(u[0], u[1], u[2], u[3]);
     }
-    __device__ __forceinline__ void fold(int half) {
-        if (WIDE) { tot[half] += acc64; acc64 = 0; } else { tot[half] += acc32; acc32 = 0; }
+    __device__ __forceinline__ void fold() {
+        if (WIDE) { cur += acc64; acc64 = 0; } else { cur += acc32; acc32 = 0; }
     }
+    __device__ __forceinline__ void end_first_half() { first = cur; cur = 0; }
     template <int R>
     __device__ __forceinline__ void realign() {
         int32_t t[W];
@@ -899,9 +908,9 @@ __device__ __forceinline__ void lpc_inplace_full(WarpSh &ws, uint32_t *pcm, int 
     for (int k = 0; k < H; k++) st.s[k] = hs[k];
 #pragma unroll
     for (int j = 0; j < H; j++) st.q[j] = j < FRX_MAX_LPC ? ws.qlp[j] : 0;
-    st.shift = shift; st.acc32 = 0; st.acc64 = 0; st.tot[0] = 0; st.tot[1] = 0;
+    st.shift = shift; st.acc32 = 0; st.acc64 = 0; st.cur = 0; st.first = 0;
     walk_block<H>(st, blk);
-    sumA = st.tot[0]; sumB = st.tot[1];
+    sumA = st.first; sumB = st.cur;
     __syncwarp();
 }
 template <int H, bool WIDE>
@@ -969,9 +978,12 @@ __device__ __forceinline__ long long fixed_resid64(const uint32_t *pcm, int g, i
     return A - 4 * B + 6 * C - 4 * D + pcm_at(pcm, g - 4);
 }
 
+// results go through shared memory (ws.g_*): reference parameters of an out-of-line function would pin the caller's arrays to local memory
 template <int MAXO>
-__device__ __noinline__ void pass1_generic(const uint32_t *pcm, int nsamp, int max_lpc, int lane, uint64_t (&tot)[5], uint32_t &badmask,
-                                           float (&ac)[MAXO + 1]) {
+__device__ __noinline__ void pass1_generic(WarpSh &ws, const uint32_t *pcm, int nsamp, int max_lpc, int lane) {
+    uint64_t tot[5];
+    float ac[MAXO + 1];
+    uint32_t badmask;
 #pragma unroll
     for (int o = 0; o < 5; o++) tot[o] = 0;
 #pragma unroll
@@ -1011,6 +1023,14 @@ __device__ __noinline__ void pass1_generic(const uint32_t *pcm, int nsamp, int m
 #pragma unroll
     for (int k = 0; k <= MAXO; k++) ac[k] = warp_sum_f32(ac[k]);
     badmask = __reduce_or_sync(FULLMASK, bad);
+    if (lane == 0) {
+#pragma unroll
+        for (int o = 0; o < 5; o++) ws.g_tot[o] = tot[o];
+#pragma unroll
+        for (int k = 0; k <= MAXO; k++) ws.g_ac[k] = ac[k];
+        ws.g_bad = badmask;
+    }
+    __syncwarp();
 }
 
 // |r| sums of the fixed predictor into the partition bins, nothing stored (the PCM stays intact for the LPC trial)
@@ -1156,7 +1176,7 @@ __device__ __forceinline__ void emit_fields(uint32_t *out, Emitter &em, const ui
 
 // subframe header: 0 | type(6) | wasted flag, wasted-bits count in unary, warm-up samples, LPC precision / shift /
 // coefficients, Rice method + partition order -- one field per lane, in stream order
-__device__ __noinline__ void pack_subframe_header(WarpSh &ws, uint32_t *out, Emitter &em, const SubDec &d, const uint32_t *pcm, int lane) {
+__device__ __noinline__ Emitter pack_subframe_header(WarpSh &ws, uint32_t *out, Emitter em, const SubDec &d, const uint32_t *pcm, int lane) {
     const int type = d.type, order = d.order, wasted = d.wasted, sbps = d.sbps;
     uint32_t val[2] = { 0, 0 }, len[2] = { 0, 0 }, zer[2] = { 0, 0 };
     const uint32_t smask = sbps >= 32 ? 0xFFFFFFFFu : ((1u << sbps) - 1u);
@@ -1179,10 +1199,11 @@ __device__ __noinline__ void pack_subframe_header(WarpSh &ws, uint32_t *out, Emi
         if (lane == nxt) { val[0] = ((d.rice2 ? 1u : 0u) << 4) | (uint32_t)d.po; len[0] = 6; }
     }
     emit_fields<2>(out, em, val, len, zer, lane);
+    return em;
 }
 
 // Rice-coded residual section, chunk by chunk: 128 residuals into registers, then their bits into the words behind them
-__device__ __noinline__ void pack_rice(uint32_t *out, Emitter &em, const SubDec &d, uint32_t *pcm, int nsamp, int lane) {
+__device__ __noinline__ Emitter pack_rice(uint32_t *out, Emitter em, const SubDec &d, uint32_t *pcm, int nsamp, int lane) {
     const int order = d.order, po = d.po;
     const int psize = nsamp >> po;
     const uint32_t pb = d.rice2 ? 5u : 4u;
@@ -1209,9 +1230,10 @@ __device__ __noinline__ void pack_rice(uint32_t *out, Emitter &em, const SubDec 
         }
         emit_fields<5>(out, em, val, len, zer, lane);
     }
+    return em;
 }
 // VERBATIM body: the samples as sbps-bit fields
-__device__ __noinline__ void pack_verbatim(uint32_t *out, Emitter &em, const SubDec &d, uint32_t *pcm, int nsamp, int lane) {
+__device__ __noinline__ Emitter pack_verbatim(uint32_t *out, Emitter em, const SubDec &d, uint32_t *pcm, int nsamp, int lane) {
     const uint32_t sbps = d.sbps;
     const int nchunks = (nsamp + BLK - 1) / BLK;
     for (int c = 0; c < nchunks; c++) {
@@ -1225,6 +1247,7 @@ __device__ __noinline__ void pack_verbatim(uint32_t *out, Emitter &em, const Sub
         for (int i = 0; i < 4; i++) { val[i] = u[i] & smask; len[i] = (g + i) < nsamp ? sbps : 0u; zer[i] = 0; }
         emit_fields<4>(out, em, val, len, zer, lane);
     }
+    return em;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1392,7 +1415,12 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
     } else {
 #pragma unroll
         for (int o = 0; o < 5; o++) { fsl[o][0] = 0; fsl[o][1] = 0; }
-        pass1_generic<H>(pcm, nsamp, max_lpc, lane, tot, badmask, autoc);
+        pass1_generic<H>(ws, pcm, nsamp, max_lpc, lane);
+#pragma unroll
+        for (int o = 0; o < 5; o++) tot[o] = ws.g_tot[o];
+#pragma unroll
+        for (int k = 0; k <= H; k++) autoc[k] = ws.g_ac[k];
+        badmask = ws.g_bad;
     }
     if (tot[1] == 0 && !(badmask & 2u)) {     // sum |s[g] - s[g-1]| == 0  <=>  all samples equal
         if (lane == 0) { d.type = 0; d.bits = 8u + (uint32_t)wasted + (uint32_t)sbps; }
@@ -1629,9 +1657,9 @@ __global__ void __launch_bounds__(ENC_CTA, 1) frx_encode_kernel(const EncArgs a)
         for (int c = 0; c < nsub; c++) {
             const SubDec &d = ws.dec[c == 0 ? sub0 : (c == 1 ? sub1 : c)];
             materialise<WIDE, H>(a, ws, buf, d, phase, bs, lane);
-            pack_subframe_header(ws, buf, em, d, pcm, lane);
-            if (d.type >= 2) pack_rice(buf, em, d, pcm, nsamp, lane);
-            else if (d.type == 1) pack_verbatim(buf, em, d, pcm, nsamp, lane);
+            em = pack_subframe_header(ws, buf, em, d, pcm, lane);
+            if (d.type >= 2) em = pack_rice(buf, em, d, pcm, nsamp, lane);
+            else if (d.type == 1) em = pack_verbatim(buf, em, d, pcm, nsamp, lane);
             bs.kind = BUF_JUNK;                     // the packed bits now lie over the samples
             if (c + 1 < nsub) {
                 // the next subframe needs the whole buffer: send the complete words of the stream on their way

@@ -99,6 +99,9 @@ struct WarpSh {
     int32_t qlp[FRX_MAX_LPC];
     int32_t warm[FRX_MAX_LPC];
     uint8_t kparam[2][64];                       // candidate 0 = fixed, 1 = lpc; parameters of the candidate's best partition order
+    uint64_t g_tot[5];                           // generic path: results of pass1_generic
+    float g_ac[FRX_MAX_LPC + 1];
+    uint32_t g_bad;
     SubDec dec[FRX_MAX_CH];
 };
 #define WARP_SH_BYTES ((sizeof(WarpSh) + 127) & ~(size_t)127)

@@ -31,7 +31,7 @@ __device__ __forceinline__ void levinson(const float *an, int upto, float *lpc, 
     }
 }
 template <bool WIDE, int MAXO>
-__device__ __noinline__ LpcChoice lpc_design(WarpSh &ws, const float *autoc, int max_lpc, int nsamp, int sbps, int qlp_precision, int magbits, int lane) {
+__device__ __forceinline__ LpcChoice lpc_design(WarpSh &ws, const float *autoc, int max_lpc, int nsamp, int sbps, int qlp_precision, int magbits, int lane) {
     LpcChoice out;
     out.ok = 0; out.order = 0; out.shift = 0; out.precision = 0; out.narrow = 1;
     const float a0 = autoc[0];
@@ -141,8 +141,9 @@ __device__ __forceinline__ void walk_block(S &s, uint32_t *blk) {
     for (int half = 0; half < 2; half++) {
         uint32_t *hb = blk + (BLK / 2) * half;
 #pragma unroll 1
-        for (int it = 0; it < MAINH; it += NP) { RunPh<0, NP, S>::go(s, hb, it); s.fold(half); }
-        if constexpr (REMH > 0) { RunPh<0, REMH, S>::go(s, hb, MAINH); s.fold(half); s.template realign<REMH>(); }
+        for (int it = 0; it < MAINH; it += NP) { RunPh<0, NP, S>::go(s, hb, it); s.fold(); }
+        if constexpr (REMH > 0) { RunPh<0, REMH, S>::go(s, hb, MAINH); s.fold(); s.template realign<REMH>(); }
+        if (half == 0) s.end_first_half();
     }
 }
 template <int H>
@@ -168,7 +169,7 @@ struct P1 {
     float c0, c1, twoc, wa, wb;   // window recurrence: c_{n+1} = twoc c_n - c_{n-1}, w = wa - wb c;  c1 = cos(phase of the next sample)
     int32_t prev, d1p, d2p, d3p;
     uint32_t f[5];                // sums of the running rotation (<= 16 samples, |e4| < 2^27)
-    uint64_t fs[5][2];
+    uint64_t cur[5], first[5];    // sums of the running half / of the first half (no dynamically indexed arrays: registers)
     template <int P>
     __device__ __forceinline__ void step(uint32_t *p) {
         const uint4 v = *reinterpret_cast<const uint4 *>(p);
@@ -189,9 +190,13 @@ struct P1 {
             for (int lag = 0; lag <= H; lag++) ac[lag] = fmaf(xv, xw[(4 * P + H + i - lag) % W], ac[lag]);
         }
     }
-    __device__ __forceinline__ void fold(int half) {
+    __device__ __forceinline__ void fold() {
 #pragma unroll
-        for (int o = 0; o < 5; o++) { fs[o][half] += f[o]; f[o] = 0; }
+        for (int o = 0; o < 5; o++) { cur[o] += f[o]; f[o] = 0; }
+    }
+    __device__ __forceinline__ void end_first_half() {
+#pragma unroll
+        for (int o = 0; o < 5; o++) { first[o] = cur[o]; cur[o] = 0; }
     }
     template <int R>
     __device__ __forceinline__ void realign() {
@@ -237,10 +242,10 @@ __device__ __forceinline__ void pass1_full(uint32_t *pcm, int lane, uint64_t (&f
         st.d3p = st.d2p - (dm2 - dm3);
     }
 #pragma unroll
-    for (int o = 0; o < 5; o++) { st.f[o] = 0; st.fs[o][0] = 0; st.fs[o][1] = 0; }
+    for (int o = 0; o < 5; o++) { st.f[o] = 0; st.cur[o] = 0; st.first[o] = 0; }
     walk_block<H>(st, blk);
 #pragma unroll
-    for (int o = 0; o < 5; o++) { fs[o][0] = st.fs[o][0]; fs[o][1] = st.fs[o][1]; }
+    for (int o = 0; o < 5; o++) { fs[o][0] = st.first[o]; fs[o][1] = st.cur[o]; }
 #pragma unroll
     for (int k = 0; k <= H; k++) ac[k] = st.ac[k];
 }

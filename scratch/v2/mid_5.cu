@@ -9,7 +9,7 @@ struct P2 {
     int shift;
     uint32_t acc32;
     uint64_t acc64;
-    uint64_t tot[2];
+    uint64_t cur, first;
     template <int P>
     __device__ __forceinline__ void step(uint32_t *p) {
         const uint4 v = *reinterpret_cast<const uint4 *>(p);
@@ -34,9 +34,10 @@ struct P2 {
         }
         *reinterpret_cast<uint4 *>(p) = make_uint4(u[0], u[1], u[2], u[3]);
     }
-    __device__ __forceinline__ void fold(int half) {
-        if (WIDE) { tot[half] += acc64; acc64 = 0; } else { tot[half] += acc32; acc32 = 0; }
+    __device__ __forceinline__ void fold() {
+        if (WIDE) { cur += acc64; acc64 = 0; } else { cur += acc32; acc32 = 0; }
     }
+    __device__ __forceinline__ void end_first_half() { first = cur; cur = 0; }
     template <int R>
     __device__ __forceinline__ void realign() {
         int32_t t[W];
@@ -57,9 +58,9 @@ __device__ __forceinline__ void lpc_inplace_full(WarpSh &ws, uint32_t *pcm, int 
     for (int k = 0; k < H; k++) st.s[k] = hs[k];
 #pragma unroll
     for (int j = 0; j < H; j++) st.q[j] = j < FRX_MAX_LPC ? ws.qlp[j] : 0;
-    st.shift = shift; st.acc32 = 0; st.acc64 = 0; st.tot[0] = 0; st.tot[1] = 0;
+    st.shift = shift; st.acc32 = 0; st.acc64 = 0; st.cur = 0; st.first = 0;
     walk_block<H>(st, blk);
-    sumA = st.tot[0]; sumB = st.tot[1];
+    sumA = st.first; sumB = st.cur;
     __syncwarp();
 }
 template <int H, bool WIDE>
@@ -127,9 +128,12 @@ __device__ __forceinline__ long long fixed_resid64(const uint32_t *pcm, int g, i
     return A - 4 * B + 6 * C - 4 * D + pcm_at(pcm, g - 4);
 }
 
+// results go through shared memory (ws.g_*): reference parameters of an out-of-line function would pin the caller's arrays to local memory
 template <int MAXO>
-__device__ __noinline__ void pass1_generic(const uint32_t *pcm, int nsamp, int max_lpc, int lane, uint64_t (&tot)[5], uint32_t &badmask,
-                                           float (&ac)[MAXO + 1]) {
+__device__ __noinline__ void pass1_generic(WarpSh &ws, const uint32_t *pcm, int nsamp, int max_lpc, int lane) {
+    uint64_t tot[5];
+    float ac[MAXO + 1];
+    uint32_t badmask;
 #pragma unroll
     for (int o = 0; o < 5; o++) tot[o] = 0;
 #pragma unroll
@@ -169,6 +173,14 @@ __device__ __noinline__ void pass1_generic(const uint32_t *pcm, int nsamp, int m
 #pragma unroll
     for (int k = 0; k <= MAXO; k++) ac[k] = warp_sum_f32(ac[k]);
     badmask = __reduce_or_sync(FULLMASK, bad);
+    if (lane == 0) {
+#pragma unroll
+        for (int o = 0; o < 5; o++) ws.g_tot[o] = tot[o];
+#pragma unroll
+        for (int k = 0; k <= MAXO; k++) ws.g_ac[k] = ac[k];
+        ws.g_bad = badmask;
+    }
+    __syncwarp();
 }
 
 // |r| sums of the fixed predictor into the partition bins, nothing stored (the PCM stays intact for the LPC trial)

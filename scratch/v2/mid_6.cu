@@ -75,7 +75,7 @@ __device__ __forceinline__ void emit_fields(uint32_t *out, Emitter &em, const ui
 
 // subframe header: 0 | type(6) | wasted flag, wasted-bits count in unary, warm-up samples, LPC precision / shift /
 // coefficients, Rice method + partition order -- one field per lane, in stream order
-__device__ __noinline__ void pack_subframe_header(WarpSh &ws, uint32_t *out, Emitter &em, const SubDec &d, const uint32_t *pcm, int lane) {
+__device__ __noinline__ Emitter pack_subframe_header(WarpSh &ws, uint32_t *out, Emitter em, const SubDec &d, const uint32_t *pcm, int lane) {
     const int type = d.type, order = d.order, wasted = d.wasted, sbps = d.sbps;
     uint32_t val[2] = { 0, 0 }, len[2] = { 0, 0 }, zer[2] = { 0, 0 };
     const uint32_t smask = sbps >= 32 ? 0xFFFFFFFFu : ((1u << sbps) - 1u);
@@ -98,10 +98,11 @@ __device__ __noinline__ void pack_subframe_header(WarpSh &ws, uint32_t *out, Emi
         if (lane == nxt) { val[0] = ((d.rice2 ? 1u : 0u) << 4) | (uint32_t)d.po; len[0] = 6; }
     }
     emit_fields<2>(out, em, val, len, zer, lane);
+    return em;
 }
 
 // Rice-coded residual section, chunk by chunk: 128 residuals into registers, then their bits into the words behind them
-__device__ __noinline__ void pack_rice(uint32_t *out, Emitter &em, const SubDec &d, uint32_t *pcm, int nsamp, int lane) {
+__device__ __noinline__ Emitter pack_rice(uint32_t *out, Emitter em, const SubDec &d, uint32_t *pcm, int nsamp, int lane) {
     const int order = d.order, po = d.po;
     const int psize = nsamp >> po;
     const uint32_t pb = d.rice2 ? 5u : 4u;
@@ -128,9 +129,10 @@ __device__ __noinline__ void pack_rice(uint32_t *out, Emitter &em, const SubDec 
         }
         emit_fields<5>(out, em, val, len, zer, lane);
     }
+    return em;
 }
 // VERBATIM body: the samples as sbps-bit fields
-__device__ __noinline__ void pack_verbatim(uint32_t *out, Emitter &em, const SubDec &d, uint32_t *pcm, int nsamp, int lane) {
+__device__ __noinline__ Emitter pack_verbatim(uint32_t *out, Emitter em, const SubDec &d, uint32_t *pcm, int nsamp, int lane) {
     const uint32_t sbps = d.sbps;
     const int nchunks = (nsamp + BLK - 1) / BLK;
     for (int c = 0; c < nchunks; c++) {
@@ -144,6 +146,7 @@ __device__ __noinline__ void pack_verbatim(uint32_t *out, Emitter &em, const Sub
         for (int i = 0; i < 4; i++) { val[i] = u[i] & smask; len[i] = (g + i) < nsamp ? sbps : 0u; zer[i] = 0; }
         emit_fields<4>(out, em, val, len, zer, lane);
     }
+    return em;
 }
 
 // ------------------------------------------------------------------------------------------

@@ -97,7 +97,12 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
     } else {
 #pragma unroll
         for (int o = 0; o < 5; o++) { fsl[o][0] = 0; fsl[o][1] = 0; }
-        pass1_generic<H>(pcm, nsamp, max_lpc, lane, tot, badmask, autoc);
+        pass1_generic<H>(ws, pcm, nsamp, max_lpc, lane);
+#pragma unroll
+        for (int o = 0; o < 5; o++) tot[o] = ws.g_tot[o];
+#pragma unroll
+        for (int k = 0; k <= H; k++) autoc[k] = ws.g_ac[k];
+        badmask = ws.g_bad;
     }
     if (tot[1] == 0 && !(badmask & 2u)) {     // sum |s[g] - s[g-1]| == 0  <=>  all samples equal
         if (lane == 0) { d.type = 0; d.bits = 8u + (uint32_t)wasted + (uint32_t)sbps; }
