@@ -259,7 +259,8 @@ struct FrameDesc {
 };
 struct SubDec {                                  // decision record of one subframe
     uint8_t type, order, wasted, po, rice2, precision, sbps, vch;   // type: 0 CONSTANT 1 VERBATIM 2 FIXED 3 LPC; vch: virtual channel
-    uint8_t fast, narrow, pad0, pad1;            // fast: full frame of lean data (blocked 32-bit passes); narrow: 32-bit LPC accumulate
+    uint8_t fast, narrow, runs, pad1;            // fast: full frame of lean data (blocked 32-bit passes); narrow: 32-bit LPC accumulate;
+                                                 // runs: every lane may pack its own block as one run (pack_runs)
     int32_t shift;
     uint32_t bits;                               // exact size of the subframe
     int16_t qlp[FRX_MAX_LPC];
@@ -946,18 +947,31 @@ __device__ __noinline__ void fixed_inplace_full(uint32_t *pcm, int order, int la
     __syncwarp();
 }
 
-// exact Rice bits of the lane's block: k0 / k1 = parameters of its two halves
-__device__ __forceinline__ uint32_t count_full(const uint32_t *pcm, int lane, uint32_t k0, uint32_t k1) {
+// Exact Rice bits of the lane's block in stream order (k0 / k1 = parameters of its two halves, pb0 / pb1 = parameter bits in
+// front of them) and the lane-local condition of pack_runs: a lane that writes its run over its own block, starting four
+// words in front of it, never overtakes its reads when the bits through every group of four samples stay within
+// 128 t + 224.
+__device__ __forceinline__ uint32_t count_block(const uint32_t *pcm, int lane, uint32_t k0, uint32_t k1, uint32_t pb0, uint32_t pb1, bool &ok) {
     const uint32_t *blk = pcm + lane * BLK_W;
-    uint32_t c0 = 0, c1 = 0;
+    uint32_t c = pb0, lim = 224u, bad = 0;
+    const uint32_t s0 = 4u * (k0 + 1u), s1 = 4u * (k1 + 1u);
 #pragma unroll 4
     for (int it = 0; it < BLK / 8; it++) {
         const uint4 v = *reinterpret_cast<const uint4 *>(blk + 4 * it);
-        const uint4 w = *reinterpret_cast<const uint4 *>(blk + BLK / 2 + 4 * it);
-        c0 += (v.x >> k0) + (v.y >> k0) + (v.z >> k0) + (v.w >> k0);
-        c1 += (w.x >> k1) + (w.y >> k1) + (w.z >> k1) + (w.w >> k1);
+        c += s0 + ((v.x >> k0) + (v.y >> k0)) + ((v.z >> k0) + (v.w >> k0));
+        bad |= (c > lim) ? 1u : 0u;
+        lim += 128u;
     }
-    return c0 + c1 + (BLK / 2) * (k0 + 1u) + (BLK / 2) * (k1 + 1u);
+    c += pb1;
+#pragma unroll 4
+    for (int it = BLK / 8; it < BLK / 4; it++) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(blk + 4 * it);
+        c += s1 + ((v.x >> k1) + (v.y >> k1)) + ((v.z >> k1) + (v.w >> k1));
+        bad |= (c > lim) ? 1u : 0u;
+        lim += 128u;
+    }
+    ok = bad == 0u;
+    return c;
 }
 
 // ==========================================================================================
@@ -1202,7 +1216,15 @@ __device__ __noinline__ Emitter pack_subframe_header(WarpSh &ws, uint32_t *out, 
     return em;
 }
 
-// Rice-coded residual section, chunk by chunk: 128 residuals into registers, then their bits into the words behind them
+// Rice-coded residual section, chunk by chunk: 128 residuals into registers, then their bits into the words behind them.
+// Fast path (whole warp): the lane's four codes (and a partition parameter in front of them) are shift-appended into one
+// 128-bit string, the string is moved so that its END sits on the word grid of the stream, and the words come out right to
+// left: X0 = the incomplete last word (handed to the lanes behind), X1..Xn = the words this lane completes.  A chunk in which
+// some code is longer than 32 bits, or a lane's bits do not fit the string, takes emit_fields.
+__device__ __forceinline__ void append128(uint32_t &w3, uint32_t &w2, uint32_t &w1, uint32_t &w0, uint32_t v, uint32_t n) {   // n <= 32
+    w3 = __funnelshift_lc(w2, w3, n); w2 = __funnelshift_lc(w1, w2, n); w1 = __funnelshift_lc(w0, w1, n);
+    w0 = __funnelshift_lc(0u, w0, n) | v;
+}
 __device__ __noinline__ Emitter pack_rice(uint32_t *out, Emitter em, const SubDec &d, uint32_t *pcm, int nsamp, int lane) {
     const int order = d.order, po = d.po;
     const int psize = nsamp >> po;
@@ -1215,23 +1237,166 @@ __device__ __noinline__ Emitter pack_rice(uint32_t *out, Emitter em, const SubDe
         const uint4 v = *reinterpret_cast<const uint4 *>(pcm + PIDX(g));
         __syncwarp();
         const uint32_t u[4] = { v.x, v.y, v.z, v.w };
-        uint32_t val[5], len[5], zer[5];
-        const int pi = g < nsamp ? (pow2 ? (g >> psh) : (g / psize)) : 0;
-        const uint32_t k = g < nsamp ? d.k[pi] : 0u;
-        const bool pstart = g < nsamp && g == pi * psize;
-        val[0] = k; len[0] = pstart ? pb : 0u; zer[0] = 0;
-        const uint32_t kmask = (1u << k) - 1u;
+        const bool allcoded = (c > 0 || order == 0) && BLK * (c + 1) <= nsamp;      // warp-uniform
+        int pi;
+        if (pow2) pi = g >> psh;
+        else pi = g < nsamp ? g / psize : 0;
+        const bool inside = allcoded || g < nsamp;
+        const uint32_t k = inside ? d.k[pi] : 0u;
+        const bool pstart = inside && g == pi * psize;
+        const uint32_t kmask = (1u << k) - 1u, kbit = 1u << k, k1 = k + 1u;
+        uint32_t q[4], cv[4], cl[4];
+        if (allcoded) {
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const bool coded = (g + i) < nsamp && (g + i) >= order;
-            val[1 + i] = (1u << k) | (u[i] & kmask);
-            len[1 + i] = coded ? k + 1u : 0u;
-            zer[1 + i] = coded ? (u[i] >> k) : 0u;
+            for (int i = 0; i < 4; i++) { q[i] = u[i] >> k; cv[i] = (u[i] & kmask) | kbit; cl[i] = q[i] + k1; }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const bool coded = (g + i) < nsamp && (g + i) >= order;
+                q[i] = u[i] >> k;
+                cv[i] = coded ? ((u[i] & kmask) | kbit) : 0u;
+                cl[i] = coded ? q[i] + k1 : 0u;                   // code length: zeros, stop bit, k low bits
+            }
         }
-        emit_fields<5>(out, em, val, len, zer, lane);
+        const uint32_t p0 = pstart ? pb : 0u;
+        const uint32_t T = p0 + (cl[0] + cl[1]) + (cl[2] + cl[3]);
+        uint32_t incl = T;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t n = __shfl_up_sync(FULLMASK, incl, o);
+            if (lane >= o) incl += n;
+        }
+        const uint32_t start = em.P + incl - T, sh = start & 31u;
+        const bool fits = ((cl[0] | cl[1] | cl[2] | cl[3]) <= 32u) && (sh + T <= 128u);   // (the OR bounds the largest length from above)
+        if (__all_sync(FULLMASK, fits)) {
+            const uint32_t total = __shfl_sync(FULLMASK, incl, 31);
+            uint32_t w3 = 0, w2 = 0, w1 = 0, w0 = pstart ? k : 0u;
+            append128(w3, w2, w1, w0, cv[0], cl[0]);
+            append128(w3, w2, w1, w0, cv[1], cl[1]);
+            append128(w3, w2, w1, w0, cv[2], cl[2]);
+            append128(w3, w2, w1, w0, cv[3], cl[3]);
+            const uint32_t endb = sh + T;                          // bits from the lane's first word boundary to the end of its string
+            const uint32_t a = 32u - (endb & 31u);                 // 1..32: move the end of the string onto the word grid
+            const uint32_t X4 = __funnelshift_lc(w3, 0u, a), X3 = __funnelshift_lc(w2, w3, a), X2 = __funnelshift_lc(w1, w2, a),
+                           X1 = __funnelshift_lc(w0, w1, a), X0 = __funnelshift_lc(0u, w0, a);
+            const uint32_t nfull = endb >> 5;                      // words this lane completes (0..4): X_nfull (first) .. X1 (last)
+            uint32_t vv = X0, fl = nfull ? 1u : 0u;
+            if (lane == 0 && !fl) vv |= em.carry;
+            if (!__all_sync(FULLMASK, fl)) {                      // some lane completes no word: its bits flow on (segmented OR scan)
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t pv = __shfl_up_sync(FULLMASK, vv, o);
+                    const uint32_t pf = __shfl_up_sync(FULLMASK, fl, o);
+                    if (lane >= o && !fl) { vv |= pv; fl = pf; }
+                }
+            }
+            uint32_t cin = __shfl_up_sync(FULLMASK, vv, 1);
+            if (lane == 0) cin = em.carry;
+            uint32_t *wp = out + (start >> 5) + nfull;             // one past the last word this lane completes
+            const uint32_t first = nfull == 1u ? X1 : (nfull == 2u ? X2 : (nfull == 3u ? X3 : X4));
+            if (nfull >= 2u) wp[-1] = X1;
+            if (nfull >= 3u) wp[-2] = X2;
+            if (nfull >= 4u) wp[-3] = X3;
+            if (nfull >= 1u) out[start >> 5] = first | cin;
+            em.carry = __shfl_sync(FULLMASK, vv, 31);
+            em.P += total;
+            __syncwarp();
+        } else {
+            uint32_t val[5], len[5], zer[5];
+            val[0] = k; len[0] = p0; zer[0] = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++) { val[1 + i] = cv[i]; len[1 + i] = cl[i] ? k1 : 0u; zer[1 + i] = cl[i] ? q[i] : 0u; }
+            emit_fields<5>(out, em, val, len, zer, lane);
+        }
     }
     return em;
 }
+// Rice-coded residual section of a full frame, one RUN per lane: lane L codes the 128 residuals of its own block with a serial
+// bit writer (64-bit accumulator, no shuffles) and stores the words over the block it is reading, starting four words in front
+// of it (lane 0: at the end of the stream); count_block has checked that a run never overtakes its reads.  The words of a run
+// lie on the word grid of the stream and hold the lane's own bits only, so the runs are then moved down to their place one
+// after the other (the global in-place condition keeps a destination below every unread source) and the word two runs share
+// is OR-ed.
+struct RunWriter {
+    uint32_t hi, lo, nb;
+    uint32_t *wp;
+    __device__ __forceinline__ void word() { *wp++ = hi; hi = lo; lo = 0u; nb -= 32u; }
+    __device__ __forceinline__ void put(uint32_t v, uint32_t n) {        // n <= 32 bits, nb < 32 on entry
+        const uint64_t x = (uint64_t)v << (64u - n - nb);
+        hi |= (uint32_t)(x >> 32); lo |= (uint32_t)x;
+        nb += n;
+        if (nb >= 32u) word();
+        if (nb >= 32u) word();
+    }
+    __device__ __forceinline__ void code(uint32_t u, uint32_t k, uint32_t kmask, uint32_t kbit, uint32_t k1) {
+        nb += u >> k;                                                   // the unary zeros
+        if (nb > 64u - k1) { while (nb >= 32u) word(); }                // a long run of zeros: rare
+        put((u & kmask) | kbit, k1);
+    }
+};
+__device__ __noinline__ Emitter pack_runs(uint32_t *out, Emitter em, const SubDec &d, uint32_t *pcm, int lane) {
+    const int order = d.order, po = d.po;
+    const uint32_t pb = d.rice2 ? 5u : 4u;
+    const int psh = 12 - po, g0 = lane * BLK;
+    uint32_t *blk = pcm + lane * BLK_W;
+    const uint32_t k0 = d.k[g0 >> psh], k1 = d.k[(g0 + BLK / 2) >> psh];
+    const uint32_t pb0 = (g0 & ((1 << psh) - 1)) == 0 ? pb : 0u, pb1 = po == 6 ? pb : 0u;
+    bool ok;
+    uint32_t B = count_block(pcm, lane, k0, k1, pb0, pb1, ok);
+    if (lane == 0) B -= (uint32_t)order * (k0 + 1u);
+    uint32_t incl = B;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(FULLMASK, incl, o);
+        if (lane >= o) incl += n;
+    }
+    const uint32_t total = __shfl_sync(FULLMASK, incl, 31);
+    const uint32_t start = em.P + incl - B;
+    const uint32_t gw = start >> 5;
+    uint32_t *sp = lane == 0 ? out + gw : blk - 4;
+    RunWriter w;
+    w.hi = 0u; w.lo = 0u; w.nb = start & 31u; w.wp = sp;
+    {
+        uint32_t k = k0, kmask = (1u << k0) - 1u, kbit = 1u << k0, kk1 = k0 + 1u;
+        if (pb0) w.put(k0, pb);
+#pragma unroll 1
+        for (int it = 0; it < BLK / 4; it++) {
+            if (it == BLK / 8) {
+                k = k1; kmask = (1u << k1) - 1u; kbit = 1u << k1; kk1 = k1 + 1u;
+                if (pb1) w.put(k1, pb);
+            }
+            const uint4 v = *reinterpret_cast<const uint4 *>(blk + 4 * it);
+            const uint32_t u[4] = { v.x, v.y, v.z, v.w };
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                if (lane != 0 || 4 * it + i >= order) w.code(u[i], k, kmask, kbit, kk1);
+        }
+    }
+    if (w.nb) *w.wp = w.hi;                                  // the incomplete last word, own bits only
+    const uint32_t m = (uint32_t)(w.wp - sp) + (w.nb ? 1u : 0u);
+    __syncwarp();
+    if (lane == 0 && (em.P & 31u)) out[gw] |= em.carry;      // the bits in front of the first run
+    __syncwarp();
+    // move runs 1..31 down to their place
+#pragma unroll 1
+    for (int L = 1; L < 32; L++) {
+        const uint32_t gwL = __shfl_sync(FULLMASK, gw, L), mL = __shfl_sync(FULLMASK, m, L), shared = __shfl_sync(FULLMASK, start & 31u, L);
+        const uint32_t *src = pcm + L * BLK_W - 4;
+        uint32_t *dst = out + gwL;
+        for (uint32_t t = lane; t < mL; t += 32) {
+            uint32_t x = src[t];
+            if (t == 0 && shared) x |= dst[0];
+            __syncwarp(__activemask());
+            dst[t] = x;
+        }
+        __syncwarp();
+    }
+    em.P += total;
+    em.carry = (em.P & 31u) ? out[em.P >> 5] : 0u;
+    __syncwarp();
+    return em;
+}
+
 // VERBATIM body: the samples as sbps-bit fields
 __device__ __noinline__ Emitter pack_verbatim(uint32_t *out, Emitter em, const SubDec &d, uint32_t *pcm, int nsamp, int lane) {
     const uint32_t sbps = d.sbps;
@@ -1383,7 +1548,7 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
     bs.kind = BUF_PCM; bs.vch = vch; bs.type = 1; bs.order = 0;
     if (lane == 0) {
         d.type = 1; d.order = 0; d.wasted = (uint8_t)wasted; d.po = 0; d.rice2 = 0; d.precision = 0; d.sbps = (uint8_t)sbps; d.vch = (uint8_t)vch;
-        d.fast = fast ? 1 : 0; d.narrow = 1; d.shift = 0; d.bits = (uint32_t)verb_bits;
+        d.fast = fast ? 1 : 0; d.narrow = 1; d.runs = 0; d.shift = 0; d.bits = (uint32_t)verb_bits;
     }
     __syncwarp();
 
@@ -1510,15 +1675,14 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
     const uint32_t pb = rice2 ? 5u : 4u;
     const uint32_t hb = 8u + (uint32_t)wasted + (uint32_t)order * (uint32_t)sbps + (type == 3 ? 9u + (uint32_t)order * (uint32_t)lc.precision : 0u) + 6u;
     uint32_t total;
-    bool inplace_ok;
+    bool inplace_ok, runs_ok = false;
     if (fast) {
         const int psh = 12 - po;                                   // log2(samples per partition)
         const int g0 = lane * BLK;
         const uint32_t k0 = d.k[g0 >> psh], k1 = d.k[(g0 + BLK / 2) >> psh];
-        uint32_t c = count_full(pcm, lane, k0, k1);
+        bool lane_ok;
+        uint32_t c = count_block(pcm, lane, k0, k1, (g0 & ((1 << psh) - 1)) == 0 ? pb : 0u, po == 6 ? pb : 0u, lane_ok);
         if (lane == 0) c -= (uint32_t)order * (k0 + 1u);           // warm-up samples carry no code (their slots hold 0)
-        if ((g0 & ((1 << psh) - 1)) == 0) c += pb;
-        if (po == 6) c += pb;
         if (lane == 0) c += hb;
         uint32_t incl = c;
 #pragma unroll
@@ -1527,14 +1691,15 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
             if (lane >= o) incl += n;
         }
         total = __shfl_sync(FULLMASK, incl, 31);
-        inplace_ok = __all_sync(FULLMASK, startbits + incl <= 32u * (SLACK_W + BLK_W * ((uint32_t)lane + 1u)));
+        inplace_ok = __all_sync(FULLMASK, startbits + incl <= 32u * (SLACK_W + BLK_W * ((uint32_t)lane + 1u) - 4u));
+        runs_ok = __all_sync(FULLMASK, lane_ok);
     } else {
         total = hb + count_generic(pcm, d.k, nsamp, order, nsamp >> po, pb, startbits + hb, inplace_ok, lane);
     }
     if ((uint64_t)total >= verb_bits || !inplace_ok) {
         // the Rice-coded subframe would not beat VERBATIM (or cannot be packed in place): write it verbatim
         if (lane == 0) { d.type = 1; d.order = 0; d.bits = (uint32_t)verb_bits; }
-    } else if (lane == 0) d.bits = total;
+    } else if (lane == 0) { d.bits = total; d.runs = runs_ok ? 1 : 0; }
     __syncwarp();
 }
 
@@ -1658,7 +1823,7 @@ __global__ void __launch_bounds__(ENC_CTA, 1) frx_encode_kernel(const EncArgs a)
             const SubDec &d = ws.dec[c == 0 ? sub0 : (c == 1 ? sub1 : c)];
             materialise<WIDE, H>(a, ws, buf, d, phase, bs, lane);
             em = pack_subframe_header(ws, buf, em, d, pcm, lane);
-            if (d.type >= 2) em = pack_rice(buf, em, d, pcm, nsamp, lane);
+            if (d.type >= 2) em = d.runs ? pack_runs(buf, em, d, pcm, lane) : pack_rice(buf, em, d, pcm, nsamp, lane);
             else if (d.type == 1) em = pack_verbatim(buf, em, d, pcm, nsamp, lane);
             bs.kind = BUF_JUNK;                     // the packed bits now lie over the samples
             if (c + 1 < nsub) {

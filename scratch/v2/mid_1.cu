@@ -87,7 +87,8 @@ struct FrameDesc {
 };
 struct SubDec {                                  // decision record of one subframe
     uint8_t type, order, wasted, po, rice2, precision, sbps, vch;   // type: 0 CONSTANT 1 VERBATIM 2 FIXED 3 LPC; vch: virtual channel
-    uint8_t fast, narrow, pad0, pad1;            // fast: full frame of lean data (blocked 32-bit passes); narrow: 32-bit LPC accumulate
+    uint8_t fast, narrow, runs, pad1;            // fast: full frame of lean data (blocked 32-bit passes); narrow: 32-bit LPC accumulate;
+                                                 // runs: every lane may pack its own block as one run (pack_runs)
     int32_t shift;
     uint32_t bits;                               // exact size of the subframe
     int16_t qlp[FRX_MAX_LPC];

@@ -96,18 +96,31 @@ __device__ __noinline__ void fixed_inplace_full(uint32_t *pcm, int order, int la
     __syncwarp();
 }
 
-// exact Rice bits of the lane's block: k0 / k1 = parameters of its two halves
-__device__ __forceinline__ uint32_t count_full(const uint32_t *pcm, int lane, uint32_t k0, uint32_t k1) {
+// Exact Rice bits of the lane's block in stream order (k0 / k1 = parameters of its two halves, pb0 / pb1 = parameter bits in
+// front of them) and the lane-local condition of pack_runs: a lane that writes its run over its own block, starting four
+// words in front of it, never overtakes its reads when the bits through every group of four samples stay within
+// 128 t + 224.
+__device__ __forceinline__ uint32_t count_block(const uint32_t *pcm, int lane, uint32_t k0, uint32_t k1, uint32_t pb0, uint32_t pb1, bool &ok) {
     const uint32_t *blk = pcm + lane * BLK_W;
-    uint32_t c0 = 0, c1 = 0;
+    uint32_t c = pb0, lim = 224u, bad = 0;
+    const uint32_t s0 = 4u * (k0 + 1u), s1 = 4u * (k1 + 1u);
 #pragma unroll 4
     for (int it = 0; it < BLK / 8; it++) {
         const uint4 v = *reinterpret_cast<const uint4 *>(blk + 4 * it);
-        const uint4 w = *reinterpret_cast<const uint4 *>(blk + BLK / 2 + 4 * it);
-        c0 += (v.x >> k0) + (v.y >> k0) + (v.z >> k0) + (v.w >> k0);
-        c1 += (w.x >> k1) + (w.y >> k1) + (w.z >> k1) + (w.w >> k1);
+        c += s0 + ((v.x >> k0) + (v.y >> k0)) + ((v.z >> k0) + (v.w >> k0));
+        bad |= (c > lim) ? 1u : 0u;
+        lim += 128u;
     }
-    return c0 + c1 + (BLK / 2) * (k0 + 1u) + (BLK / 2) * (k1 + 1u);
+    c += pb1;
+#pragma unroll 4
+    for (int it = BLK / 8; it < BLK / 4; it++) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(blk + 4 * it);
+        c += s1 + ((v.x >> k1) + (v.y >> k1)) + ((v.z >> k1) + (v.w >> k1));
+        bad |= (c > lim) ? 1u : 0u;
+        lim += 128u;
+    }
+    ok = bad == 0u;
+    return c;
 }
 
 // ==========================================================================================

@@ -65,7 +65,7 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
     bs.kind = BUF_PCM; bs.vch = vch; bs.type = 1; bs.order = 0;
     if (lane == 0) {
         d.type = 1; d.order = 0; d.wasted = (uint8_t)wasted; d.po = 0; d.rice2 = 0; d.precision = 0; d.sbps = (uint8_t)sbps; d.vch = (uint8_t)vch;
-        d.fast = fast ? 1 : 0; d.narrow = 1; d.shift = 0; d.bits = (uint32_t)verb_bits;
+        d.fast = fast ? 1 : 0; d.narrow = 1; d.runs = 0; d.shift = 0; d.bits = (uint32_t)verb_bits;
     }
     __syncwarp();
 
@@ -192,15 +192,14 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
     const uint32_t pb = rice2 ? 5u : 4u;
     const uint32_t hb = 8u + (uint32_t)wasted + (uint32_t)order * (uint32_t)sbps + (type == 3 ? 9u + (uint32_t)order * (uint32_t)lc.precision : 0u) + 6u;
     uint32_t total;
-    bool inplace_ok;
+    bool inplace_ok, runs_ok = false;
     if (fast) {
         const int psh = 12 - po;                                   // log2(samples per partition)
         const int g0 = lane * BLK;
         const uint32_t k0 = d.k[g0 >> psh], k1 = d.k[(g0 + BLK / 2) >> psh];
-        uint32_t c = count_full(pcm, lane, k0, k1);
+        bool lane_ok;
+        uint32_t c = count_block(pcm, lane, k0, k1, (g0 & ((1 << psh) - 1)) == 0 ? pb : 0u, po == 6 ? pb : 0u, lane_ok);
         if (lane == 0) c -= (uint32_t)order * (k0 + 1u);           // warm-up samples carry no code (their slots hold 0)
-        if ((g0 & ((1 << psh) - 1)) == 0) c += pb;
-        if (po == 6) c += pb;
         if (lane == 0) c += hb;
         uint32_t incl = c;
 #pragma unroll
@@ -209,14 +208,15 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
             if (lane >= o) incl += n;
         }
         total = __shfl_sync(FULLMASK, incl, 31);
-        inplace_ok = __all_sync(FULLMASK, startbits + incl <= 32u * (SLACK_W + BLK_W * ((uint32_t)lane + 1u)));
+        inplace_ok = __all_sync(FULLMASK, startbits + incl <= 32u * (SLACK_W + BLK_W * ((uint32_t)lane + 1u) - 4u));
+        runs_ok = __all_sync(FULLMASK, lane_ok);
     } else {
         total = hb + count_generic(pcm, d.k, nsamp, order, nsamp >> po, pb, startbits + hb, inplace_ok, lane);
     }
     if ((uint64_t)total >= verb_bits || !inplace_ok) {
         // the Rice-coded subframe would not beat VERBATIM (or cannot be packed in place): write it verbatim
         if (lane == 0) { d.type = 1; d.order = 0; d.bits = (uint32_t)verb_bits; }
-    } else if (lane == 0) d.bits = total;
+    } else if (lane == 0) { d.bits = total; d.runs = runs_ok ? 1 : 0; }
     __syncwarp();
 }
 

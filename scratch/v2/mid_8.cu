@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(ENC_CTA, 1) frx_encode_kernel(const EncArgs a)
             const SubDec &d = ws.dec[c == 0 ? sub0 : (c == 1 ? sub1 : c)];
             materialise<WIDE, H>(a, ws, buf, d, phase, bs, lane);
             em = pack_subframe_header(ws, buf, em, d, pcm, lane);
-            if (d.type >= 2) em = pack_rice(buf, em, d, pcm, nsamp, lane);
+            if (d.type >= 2) em = d.runs ? pack_runs(buf, em, d, pcm, lane) : pack_rice(buf, em, d, pcm, nsamp, lane);
             else if (d.type == 1) em = pack_verbatim(buf, em, d, pcm, nsamp, lane);
             bs.kind = BUF_JUNK;                     // the packed bits now lie over the samples
             if (c + 1 < nsub) {
