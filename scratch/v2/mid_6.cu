@@ -204,18 +204,23 @@ __device__ __noinline__ Emitter pack_rice(uint32_t *out, Emitter em, const SubDe
 // is OR-ed.
 struct RunWriter {
     uint32_t hi, lo, nb;
-    uint32_t *wp;
-    __device__ __forceinline__ void word() { *wp++ = hi; hi = lo; lo = 0u; nb -= 32u; }
+    uint32_t wa;                                                         // shared-memory byte address of the next word
+    // store the completed word when there is one: predicated, no branch (lanes complete their words at different samples)
+    __device__ __forceinline__ void word_if_full() {
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ge.u32 p, %2, 32;\n\t@p st.shared.u32 [%0], %1;\n\t}" ::"r"(wa), "r"(hi), "r"(nb) : "memory");
+        const bool f = nb >= 32u;
+        wa += f ? 4u : 0u; hi = f ? lo : hi; lo = f ? 0u : lo; nb -= f ? 32u : 0u;
+    }
     __device__ __forceinline__ void put(uint32_t v, uint32_t n) {        // n <= 32 bits, nb < 32 on entry
         const uint64_t x = (uint64_t)v << (64u - n - nb);
         hi |= (uint32_t)(x >> 32); lo |= (uint32_t)x;
         nb += n;
-        if (nb >= 32u) word();
-        if (nb >= 32u) word();
+        word_if_full();
     }
     __device__ __forceinline__ void code(uint32_t u, uint32_t k, uint32_t kmask, uint32_t kbit, uint32_t k1) {
         nb += u >> k;                                                   // the unary zeros
-        if (nb > 64u - k1) { while (nb >= 32u) word(); }                // a long run of zeros: rare
+        if (nb >= 64u) { while (nb >= 64u) { nb -= 32u; word_if_full(); nb += 32u; } }   // a long run of zeros: rare
+        word_if_full();
         put((u & kmask) | kbit, k1);
     }
 };
@@ -240,7 +245,7 @@ __device__ __noinline__ Emitter pack_runs(uint32_t *out, Emitter em, const SubDe
     const uint32_t gw = start >> 5;
     uint32_t *sp = lane == 0 ? out + gw : blk - 4;
     RunWriter w;
-    w.hi = 0u; w.lo = 0u; w.nb = start & 31u; w.wp = sp;
+    w.hi = 0u; w.lo = 0u; w.nb = start & 31u; w.wa = smem_u32(sp);
     {
         uint32_t k = k0, kmask = (1u << k0) - 1u, kbit = 1u << k0, kk1 = k0 + 1u;
         if (pb0) w.put(k0, pb);
@@ -257,8 +262,9 @@ __device__ __noinline__ Emitter pack_runs(uint32_t *out, Emitter em, const SubDe
                 if (lane != 0 || 4 * it + i >= order) w.code(u[i], k, kmask, kbit, kk1);
         }
     }
-    if (w.nb) *w.wp = w.hi;                                  // the incomplete last word, own bits only
-    const uint32_t m = (uint32_t)(w.wp - sp) + (w.nb ? 1u : 0u);
+    const uint32_t nwhole = (w.wa - smem_u32(sp)) >> 2;
+    if (w.nb) sp[nwhole] = w.hi;                             // the incomplete last word, own bits only
+    const uint32_t m = nwhole + (w.nb ? 1u : 0u);
     __syncwarp();
     if (lane == 0 && (em.P & 31u)) out[gw] |= em.carry;      // the bits in front of the first run
     __syncwarp();
@@ -268,9 +274,14 @@ __device__ __noinline__ Emitter pack_runs(uint32_t *out, Emitter em, const SubDe
         const uint32_t gwL = __shfl_sync(FULLMASK, gw, L), mL = __shfl_sync(FULLMASK, m, L), shared = __shfl_sync(FULLMASK, start & 31u, L);
         const uint32_t *src = pcm + L * BLK_W - 4;
         uint32_t *dst = out + gwL;
-        for (uint32_t t = lane; t < mL; t += 32) {
-            uint32_t x = src[t];
-            if (t == 0 && shared) x |= dst[0];
+        // (a run of a full block has 4..132 words: two batches of 32 cover the usual ones)
+        uint32_t x0 = lane < mL ? src[lane] : 0u, x1 = lane + 32u < mL ? src[lane + 32u] : 0u;
+        if (lane == 0 && shared) x0 |= dst[0];
+        __syncwarp();
+        if (lane < mL) dst[lane] = x0;
+        if (lane + 32u < mL) dst[lane + 32u] = x1;
+        for (uint32_t t = lane + 64u; t < mL; t += 32) {
+            const uint32_t x = src[t];
             __syncwarp(__activemask());
             dst[t] = x;
         }
