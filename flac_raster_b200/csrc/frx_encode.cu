@@ -434,9 +434,10 @@ __device__ __forceinline__ int32_t quant_one(typename FrxElem<DT>::T v, const Fr
 }
 
 // in-place expansion of one block: raw elements sit end-aligned in the block's first 512 bytes + 16, PCM words grow from
-// its start (a 16-byte read is always ahead of the words written so far)
-template <int DT>
-__device__ __forceinline__ void quantize_block(uint32_t *blk, const FrxQuant &qz, int mode, int nvalid, uint32_t &orv, uint32_t &ora) {
+// its start (a 16-byte read is always ahead of the words written so far).  FULL: all 128 samples are valid.
+// F32SAFE: float32 reference mode with the stream-wide guarantee that x * 8388607 fits int32 (no per-sample range check).
+template <int DT, bool FULL, bool F32SAFE>
+__device__ __forceinline__ void quantize_block_t(uint32_t *blk, const FrxQuant &qz, int mode, int nvalid, uint32_t &orv, uint32_t &ora) {
     typedef typename FrxElem<DT>::T T;
     constexpr int ESZ = (int)sizeof(T);
     constexpr int EPV = 16 / ESZ;                           // elements per 16-byte load
@@ -449,8 +450,9 @@ __device__ __forceinline__ void quantize_block(uint32_t *blk, const FrxQuant &qz
         int32_t x[EPV];
 #pragma unroll
         for (int i = 0; i < EPV; i++) {
-            x[i] = quant_one<DT>(e[i], qz, mode);
-            if (t * EPV + i >= nvalid) x[i] = 0;
+            if (F32SAFE) x[i] = __float2int_rz(__fmul_rn((float)e[i], 8388607.0f));
+            else x[i] = quant_one<DT>(e[i], qz, mode);
+            if (!FULL && t * EPV + i >= nvalid) x[i] = 0;
             orv |= (uint32_t)x[i];
             ora |= (uint32_t)(x[i] ^ (x[i] >> 31));
         }
@@ -458,6 +460,13 @@ __device__ __forceinline__ void quantize_block(uint32_t *blk, const FrxQuant &qz
         for (int i = 0; i < EPV / 4; i++)
             *reinterpret_cast<uint4 *>(blk + t * EPV + 4 * i) = make_uint4((uint32_t)x[4 * i], (uint32_t)x[4 * i + 1], (uint32_t)x[4 * i + 2], (uint32_t)x[4 * i + 3]);   // same type as the read: ordered
     }
+}
+template <int DT>
+__device__ __forceinline__ void quantize_block(uint32_t *blk, const FrxQuant &qz, int mode, int nvalid, uint32_t &orv, uint32_t &ora) {
+    if (nvalid == BLK) {
+        if (DT == FRX_F32 && mode == FRX_PCM_REFERENCE && (qz.flags & FRX_QF_F32_SAFE)) quantize_block_t<DT, true, DT == FRX_F32>(blk, qz, mode, nvalid, orv, ora);
+        else quantize_block_t<DT, true, false>(blk, qz, mode, nvalid, orv, ora);
+    } else quantize_block_t<DT, false, false>(blk, qz, mode, nvalid, orv, ora);
 }
 __device__ __noinline__ void quantize_block_any(int dtype, uint32_t *blk, const FrxQuant &qz, int mode, int nvalid, uint32_t &orv, uint32_t &ora) {
     switch (dtype) {   // the dtypes the benchmarks do not use share one out-of-line copy
@@ -556,6 +565,11 @@ __device__ __noinline__ uint2 load_channel(const EncArgs &a, WarpSh &ws, uint32_
 // best order's parameters to kparam[] and returns (estimated bits incl. the 6-bit method/order field, best order, RICE2).
 // ------------------------------------------------------------------------------------------
 struct RiceChoice { uint64_t bits; int po; bool rice2; };
+// sum of per-lane bit estimates: one redux when they are small (always, unless a partition is hopeless), exact otherwise
+__device__ __forceinline__ uint64_t warp_sum_bits(uint64_t b) {
+    if (__all_sync(FULLMASK, b < (1ull << 26))) return (uint64_t)__reduce_add_sync(FULLMASK, (uint32_t)b);
+    return warp_sum_u64(b);
+}
 __device__ __noinline__ RiceChoice analyse_partitions(uint8_t *kparam, uint64_t sumA, uint64_t sumB, int nsamp, int pred_order, int po_max,
                                                       int F, uint32_t kmax) {
     const int lane = threadIdx.x & 31;
@@ -567,7 +581,7 @@ __device__ __noinline__ RiceChoice analyse_partitions(uint8_t *kparam, uint64_t 
         const uint32_t n0 = (uint32_t)(nsamp >> 6) - (lane == 0 ? (uint32_t)pred_order : 0u), n1 = (uint32_t)(nsamp >> 6);
         const uint32_t k0 = rice_param(n0, sumA, kmax), k1 = rice_param(n1, sumB, kmax);
         uint64_t b = rice_estimate(k0, n0, sumA) + rice_estimate(k1, n1, sumB);
-        b = warp_sum_u64(b) + 6;
+        b = warp_sum_bits(b) + 6;
         best = b; best_po = 6; kbest0 = k0; kbest1 = k1;
     }
     for (int L = F; L >= 0; L--) {
@@ -579,7 +593,7 @@ __device__ __noinline__ RiceChoice analyse_partitions(uint8_t *kparam, uint64_t 
         uint64_t b = 0;
         if (L <= po_max) {
             if (mine) { k = rice_param(n, sum, kmax); b = rice_estimate(k, n, sum); }
-            b = warp_sum_u64(b) + 6;
+            b = warp_sum_bits(b) + 6;
             if (b < best) { best = b; best_po = L; kbest0 = k; }
         }
         if (L > 0) {
