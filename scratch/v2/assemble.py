@@ -11,6 +11,8 @@ def find(s):
 head = "\n".join(r1[:find("// bit writer into the zero-initialised shared frame buffer") - 1])
 tail = "\n".join(r1[find("// K0+K1 alone (frx_quantize): interleaved int32 PCM of one tile") - 1:])
 head = (Path(__file__).parent / "header.txt").read_text() + head[head.index("#include <math_constants.h>"):]
+head = head.replace("    q[i] = o;\n", "    o.rcp = o.range != 0.0 ? 1.0 / o.range : 0.0;   // correctly rounded (IEEE division)\n    q[i] = o;\n")
+assert "o.rcp" in head
 head = head.replace("#define HIST FRX_MAX_LPC\n#define NWARPS (FRX_ENC_THREADS / 32)   // compute warps\n", "")
 old = tail[tail.index("size_t frx_enc_smem_bytes"):tail.index("size_t frx_minmax_raw_size()")]
 tail = tail.replace(old, """size_t frx_enc_smem_bytes(int frame_words, int dtype) {

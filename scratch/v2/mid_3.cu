@@ -72,6 +72,55 @@ __device__ __noinline__ int32_t gather_any(const EncArgs &a, const FrameDesc &d,
     }
 }
 
+// Mid / side of a two-channel frame, aligned rows: every lane reads the 128 samples of its block from both band planes with
+// 16-byte loads, quantises both and stores mid or side as PCM (no raw staging: the buffer holds one channel at a time)
+template <int DT>
+__device__ __forceinline__ void load_ms_block(const EncArgs &a, const FrameDesc &d, uint32_t *blk, int lane, int vch, int nvalid, uint32_t &orv, uint32_t &ora) {
+    typedef typename FrxElem<DT>::T T;
+    constexpr int EPV = 16 / (int)sizeof(T);
+    const long long w = d.t.w;
+    const long long t0 = d.s0 + (long long)lane * BLK;
+    long long row = t0 / w, col = t0 - row * w;
+    const T *L = (const T *)a.raster + (long long)d.t.first_band * a.band_stride + (long long)d.t.row_off * a.row_stride + d.t.col_off;
+    const T *R = L + a.band_stride;
+#pragma unroll 1
+    for (int i = 0; i < BLK; i += EPV) {
+        int32_t x[EPV];
+        if (i < nvalid) {
+            const long long e = row * a.row_stride + col;
+            const uint4 vl = __ldg(reinterpret_cast<const uint4 *>(L + e)), vr = __ldg(reinterpret_cast<const uint4 *>(R + e));
+            T el[EPV], er[EPV];
+            memcpy(el, &vl, 16); memcpy(er, &vr, 16);
+#pragma unroll
+            for (int j = 0; j < EPV; j++) {
+                const int32_t l = quant_one<DT>(el[j], d.q, a.pcm_mode), r = quant_one<DT>(er[j], d.q, a.pcm_mode);
+                x[j] = vch == 8 ? ((l + r) >> 1) : (l - r);
+                if (i + j >= nvalid) x[j] = 0;
+                orv |= (uint32_t)x[j];
+                ora |= (uint32_t)(x[j] ^ (x[j] >> 31));
+            }
+            col += EPV;
+            if (col >= w) { col = 0; row++; }
+        } else {
+#pragma unroll
+            for (int j = 0; j < EPV; j++) x[j] = 0;
+        }
+#pragma unroll
+        for (int j = 0; j < EPV / 4; j++)
+            *reinterpret_cast<uint4 *>(blk + i + 4 * j) = make_uint4((uint32_t)x[4 * j], (uint32_t)x[4 * j + 1], (uint32_t)x[4 * j + 2], (uint32_t)x[4 * j + 3]);
+    }
+}
+__device__ __noinline__ void load_ms_block_any(const EncArgs &a, const FrameDesc &d, uint32_t *blk, int lane, int vch, int nvalid, uint32_t &orv, uint32_t &ora) {
+    switch (a.dtype) {
+        case FRX_U8: load_ms_block<FRX_U8>(a, d, blk, lane, vch, nvalid, orv, ora); break;
+        case FRX_I16: load_ms_block<FRX_I16>(a, d, blk, lane, vch, nvalid, orv, ora); break;
+        case FRX_U16: load_ms_block<FRX_U16>(a, d, blk, lane, vch, nvalid, orv, ora); break;
+        case FRX_I32: load_ms_block<FRX_I32>(a, d, blk, lane, vch, nvalid, orv, ora); break;
+        case FRX_U32: load_ms_block<FRX_U32>(a, d, blk, lane, vch, nvalid, orv, ora); break;
+        default: load_ms_block<FRX_F32>(a, d, blk, lane, vch, nvalid, orv, ora); break;
+    }
+}
+
 // Stage virtual channel `vch` of the frame as PCM in buf[SLACK_W + PIDX(g)].  Returns (OR of the samples, OR of their
 // magnitudes), warp-uniform.  The samples behind a short frame are zero up to the next block boundary + one block.
 __device__ __noinline__ uint2 load_channel(const EncArgs &a, WarpSh &ws, uint32_t *buf, int vch, uint32_t &phase, int lane) {
@@ -113,6 +162,11 @@ __device__ __noinline__ uint2 load_channel(const EncArgs &a, WarpSh &ws, uint32_
             uint32_t *blk = pcm + lane * BLK_W;
             for (int i = 0; i < BLK; i += 4) *reinterpret_cast<int4 *>(blk + i) = make_int4(0, 0, 0, 0);
         }
+    } else if (d.tma) {
+        // mid / side (vch >= 8) of aligned rows
+        uint32_t o1 = 0, o2 = 0;
+        if (lane <= nblk && lane < 32) load_ms_block_any(a, d, pcm + lane * BLK_W, lane, vch, max(0, min(BLK, nsamp - lane * BLK)), o1, o2);
+        orv = o1; ora = o2;
     } else {
         const int b0 = d.t.first_band;
         for (int g = lane; g < nsamp; g += 32) {
