@@ -144,16 +144,17 @@ class Codec:
                                           int(samples_per_pixel), 1 if swap_bytes else 0, C.byref(r), self._stream(stream)))
         return out
 
-    def read_tiff(self, src, row0: int = 0, row1: int | None = None):
-        """Rows [row0, row1) of an open raster as a band-planar CUDA tensor.  With the built-in GeoTIFF reader the file
-        bytes go to the device as they are and frx_tiff_unpack rearranges them there; any other dataset object
-        (rasterio) is read on the host and uploaded."""
+    def read_tiff(self, src, row0: int = 0, row1: int | None = None, bands=None):
+        """Rows [row0, row1) of an open raster as a band-planar CUDA tensor (only the 0-based `bands` when given).  With the
+        built-in GeoTIFF reader the file bytes go to the device as they are and frx_tiff_unpack rearranges them there; any
+        other dataset object (rasterio) is read on the host and uploaded."""
         if hasattr(src, "read_device") and src.dtypes[0] in L.DTYPE_CODE:
-            return src.read_device(self, row0, row1)
+            return src.read_device(self, row0, row1, bands)
         from .rio import Window
         from .synth import from_numpy
         row1 = src.height if row1 is None else row1
-        return from_numpy(src.read(window=Window(0, row0, src.width, row1 - row0)), device=f"cuda:{self.device}")
+        idx = None if bands is None else [b + 1 for b in bands]
+        return from_numpy(src.read(indexes=idx, window=Window(0, row0, src.width, row1 - row0)), device=f"cuda:{self.device}")
 
     def encode_tiles_any(self, raster, tiles, level: int = 5, blocksize: int = 4096, sample_rate: int = 44100,
                          pcm_mode: str = "reference") -> EncodeResult:

@@ -315,15 +315,28 @@ class DatasetReader:
                                         b - a, cw, tw, c))
         return out
 
-    def read_device(self, codec, row0: int = 0, row1: int | None = None):
+    def read_device(self, codec, row0: int = 0, row1: int | None = None, bands=None):
         """read() without the host-side rearrangement: the byte span of the file that holds the chunks goes to the
-        device as it is (pinned staging buffer, one H2D copy) and frx_tiff_unpack lays it out as (count, rows, width)."""
+        device as it is (pinned staging buffer, one H2D copy) and frx_tiff_unpack lays it out as (count, rows, width).
+        bands: 0-based band indices wanted; a band-planar file (PlanarConfiguration 2) then uploads only those bands' chunks
+        (pixel-interleaved files hold every band in every byte run, so all of it travels and the unwanted planes are dropped
+        on the device)."""
         import torch
         row1 = self.height if row1 is None else row1
         chunks = self.chunk_table(row0, row1)
+        if bands is not None and all(c[6] >= 0 for c in chunks):
+            pos = {int(b): i for i, b in enumerate(bands)}
+            chunks = [tuple(c[:6]) + (pos[c[6]],) for c in chunks if c[6] in pos]
+            return self._upload_and_unpack(codec, chunks, len(pos), 1, row0, row1)
+        out = self._upload_and_unpack(codec, chunks, self.count, self.count, row0, row1)
+        return out if bands is None else torch.cat([out[b:b + 1] for b in bands])   # (no fancy indexing for unsigned dtypes)
+
+    def _upload_and_unpack(self, codec, chunks, count, spp, row0, row1):
+        """chunks -> (count, row1 - row0, width) on the device; spp = bands stored per pixel in interleaved chunks."""
+        import torch
         esz = self._dtype.itemsize
         lo = min(c[0] for c in chunks)
-        hi = max(c[0] + ((c[3] - 1) * c[5] + c[4]) * (self.count if c[6] < 0 else 1) * esz for c in chunks)
+        hi = max(c[0] + ((c[3] - 1) * c[5] + c[4]) * (spp if c[6] < 0 else 1) * esz for c in chunks)
         lo_al = lo & ~255                       # keeps the file's own alignment phase on the device
         try:
             host = torch.empty(hi - lo_al, dtype=torch.uint8, pin_memory=True)
@@ -336,7 +349,7 @@ class DatasetReader:
         dev = host.to(f"cuda:{codec.device}", non_blocking=True)
         rel = [(c[0] - lo_al,) + tuple(c[1:]) for c in chunks]
         swap = (self._bo == ">") != (__import__("sys").byteorder == "big")
-        return codec.tiff_unpack(dev, rel, self.dtypes[0], self.count, row1 - row0, self.width, self.count, swap_bytes=swap)
+        return codec.tiff_unpack(dev, rel, self.dtypes[0], count, row1 - row0, self.width, spp, swap_bytes=swap)
 
     def read(self, indexes=None, window=None):
         if window is None:

@@ -62,7 +62,7 @@ def tile_bbox(transform, col_off, row_off, tw, th):
 
 
 def encode_streaming_tiles(raster: np.ndarray, tiles, crs, transform, nodata=None, bands: str = "first",
-                           pcm_mode: str = "reference", device: int = 0, row_base: int = 0) -> Tuple[List[bytes], List[int]]:
+                           pcm_mode: str = "reference", device: int = 0, row_base: int = 0, codec=None) -> Tuple[List[bytes], List[int]]:
     """Encode `tiles` [(row_off,col_off,h,w)] of the host raster (bands,H,W) into complete per-tile FLAC files.
     `row_base`: raster row 0 is row `row_base` of the full image (a rank holding only its own rows).
     Each tile is what RasterFLACConverter.tiff_to_flac(level 5) makes of the tile's own GeoTIFF
@@ -81,8 +81,8 @@ def encode_streaming_tiles(raster: np.ndarray, tiles, crs, transform, nodata=Non
     for sr in sorted(rates):
         sel = [i for i, t in enumerate(tiles) if sample_rate_for(nch, t[2]) == sr]
         units = [(tiles[i][0] - row_base, tiles[i][1], tiles[i][2], tiles[i][3], 0, nch) for i in sel]
-        res = get_codec(device).encode_tiles_any(raster, units, level=STREAMING_LEVEL, blocksize=BLOCKSIZE, sample_rate=sr,
-                                                 pcm_mode=pcm_mode)
+        res = (codec or get_codec(device)).encode_tiles_any(raster, units, level=STREAMING_LEVEL, blocksize=BLOCKSIZE, sample_rate=sr,
+                                                            pcm_mode=pcm_mode)
         data = res.bytes[:int(res.total_bytes[0])]
         fpos = 0
         for k, i in enumerate(sel):
@@ -121,25 +121,49 @@ def write_streaming_file(path, index: Dict, chunks: Iterable[bytes]) -> int:
     return len(index_json)
 
 
+_make_codec = None   # tests substitute the oracle-backed fake here
+
+
+def _new_codec(dev):
+    from .codec import Codec
+    return Codec(dev)
+
+
+def _encode_shard(input_file, dev, own_codec, tiles, lo, hi, crs, transform, nodata, bands, pcm_mode):
+    """One device's part of create-streaming: its own file handle and (when several shards run at once) its own libfrx context;
+    only the raster rows the tile range touches -- and, in band-1 mode, only band 1 -- are ingested."""
+    if lo == hi:
+        return [], []
+    codec = (_make_codec or _new_codec)(dev) if own_codec else get_codec(dev)
+    try:
+        with rio.open(input_file) as src:
+            r0 = min(t[0] for t in tiles[lo:hi])
+            r1 = max(t[0] + t[2] for t in tiles[lo:hi])
+            raster = codec.read_tiff(src, r0, r1, bands=[0] if bands == "first" else None)
+        return encode_streaming_tiles(raster, tiles[lo:hi], crs, transform, nodata, bands, pcm_mode, dev, row_base=r0, codec=codec)
+    finally:
+        if own_codec:
+            codec.close()
+
+
 def create_streaming(input_file, output_file, tile_size: int = 1024, bands: str = "first", pcm_mode: str = "reference",
                      devices: Sequence[int] = (0,)) -> Dict:
-    """create-streaming (cli.py:620-804).  `devices`: GPUs of this process; tile ranges are sharded over them
-    (one libfrx context each) and merged on the host."""
+    """create-streaming (cli.py:620-804).  `devices`: GPUs of this process; contiguous tile ranges are sharded over them and
+    encoded CONCURRENTLY, one thread and one libfrx context per device (the C-ABI allows one context per thread), then merged on
+    the host by offset concatenation."""
     with rio.open(input_file) as src:
         crs, transform, nodata = src.crs, src.transform, getattr(src, "nodata", None)
         width, height = src.width, src.height
-        tiles = calculate_tiles(height, width, tile_size)
-        shards = []
-        for k, dev in enumerate(devices):
-            lo, hi = shard_range(len(tiles), len(devices), k)
-            if lo == hi:
-                shards.append(([], []))
-                continue
-            # each device ingests only the raster rows its tile range touches (file bytes -> device -> frx_tiff_unpack)
-            r0 = min(t[0] for t in tiles[lo:hi])
-            r1 = max(t[0] + t[2] for t in tiles[lo:hi])
-            raster = get_codec(dev).read_tiff(src, r0, r1)
-            shards.append(encode_streaming_tiles(raster, tiles[lo:hi], crs, transform, nodata, bands, pcm_mode, dev, row_base=r0))
+    tiles = calculate_tiles(height, width, tile_size)
+    ranges = [shard_range(len(tiles), len(devices), k) for k in range(len(devices))]
+    if len(devices) == 1:
+        shards = [_encode_shard(input_file, devices[0], False, tiles, ranges[0][0], ranges[0][1], crs, transform, nodata, bands, pcm_mode)]
+    else:
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=len(devices)) as ex:
+            futs = [ex.submit(_encode_shard, input_file, dev, True, tiles, lo, hi, crs, transform, nodata, bands, pcm_mode)
+                    for dev, (lo, hi) in zip(devices, ranges)]
+            shards = [f.result() for f in futs]
     chunks, offsets, sizes = merge_shards(shards)
     index = build_index(crs, transform, width, height, tile_size, tiles, offsets, sizes)
     write_streaming_file(output_file, index, chunks)

@@ -36,18 +36,24 @@ def _lossless_inv(pcm, dtype):
 class OracleCodec:
     device = 0
 
-    def read_tiff(self, src, row0=0, row1=None):
+    def close(self):
+        pass
+
+    def read_tiff(self, src, row0=0, row1=None, bands=None):
         """Codec.read_tiff through the numpy restatement of frx_tiff_unpack (oracle/tiff_unpack.py)."""
+        import numpy as np
         from oracle import tiff_unpack
         row1 = src.height if row1 is None else row1
         if not hasattr(src, "chunk_table"):
             from flac_raster_b200.rio import Window
-            return src.read(window=Window(0, row0, src.width, row1 - row0))
-        chunks = src.chunk_table(row0, row1)
-        with open(src.name, "rb") as f:
-            data = f.read()
-        return tiff_unpack.unpack(data, chunks, src.dtypes[0], src.count, row1 - row0, src.width, src.count,
-                                  swap_bytes=(src._bo == ">"))
+            out = src.read(window=Window(0, row0, src.width, row1 - row0))
+        else:
+            chunks = src.chunk_table(row0, row1)
+            with open(src.name, "rb") as f:
+                data = f.read()
+            out = tiff_unpack.unpack(data, chunks, src.dtypes[0], src.count, row1 - row0, src.width, src.count,
+                                     swap_bytes=(src._bo == ">"))
+        return out if bands is None else np.ascontiguousarray(out[list(bands)])
 
     def encode_tiles_any(self, raster, tiles, **kw):
         return self.encode_tiles_host(raster, tiles, **kw)

@@ -57,3 +57,24 @@ def test_pyflac_shim(tmp_path):
 
 def test_cli(tmp_path):
     hs.cli_commands(tmp_path)
+
+
+def test_streaming_band1_of_planar_file_uploads_one_band(tmp_path, monkeypatch):
+    """create-streaming in the reference's band-1 mode on a band-planar TIFF (PlanarConfiguration 2): only band 1's strips go
+    to the device, and the file written equals the one made from the pixel-interleaved layout of the same raster."""
+    from helpers import write_tiff_variant
+    from flac_raster_b200 import geotiff, streaming
+    arr = hs.synthetic(3, 300, 420, "uint16")
+    write_tiff_variant(tmp_path / "planar.tif", arr, rows_per_strip=7, planar=2)
+    write_tiff_variant(tmp_path / "chunky.tif", arr, rows_per_strip=7, planar=1)
+    sent = []
+    real = geotiff.DatasetReader._upload_and_unpack
+
+    def spy(self, codec, chunks, count, spp, row0, row1):
+        sent.append((count, sum(c[3] * c[4] for c in chunks)))
+        return real(self, codec, chunks, count, spp, row0, row1)
+    monkeypatch.setattr(geotiff.DatasetReader, "_upload_and_unpack", spy)
+    streaming.create_streaming(tmp_path / "planar.tif", tmp_path / "p.flac", tile_size=128, bands="first")
+    assert sent == [(1, 300 * 420)]                       # one band's pixels, not three
+    streaming.create_streaming(tmp_path / "chunky.tif", tmp_path / "c.flac", tile_size=128, bands="first")
+    assert (tmp_path / "p.flac").read_bytes() == (tmp_path / "c.flac").read_bytes()

@@ -24,6 +24,7 @@ def fake(monkeypatch):
     c = OracleCodec()
     for m in (conv, sp, st, shim):
         monkeypatch.setattr(m, "get_codec", lambda device=0: c)
+    monkeypatch.setattr(st, "_make_codec", lambda dev: OracleCodec())
     monkeypatch.setattr(st.StreamingFile, "decode", _host_decode)
     return c
 
