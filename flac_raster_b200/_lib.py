@@ -67,7 +67,7 @@ class DTile(C.Structure):
 EXPORTS = ["frx_version", "frx_last_error", "frx_device_count", "frx_ctx_create", "frx_ctx_destroy",
            "frx_encode_bound", "frx_pcm_bps", "frx_encode_tiles", "frx_decode_tiles", "frx_quantize",
            "frx_dequantize", "frx_encode_tiles_host", "frx_decode_tiles_host", "frx_launch_count",
-           "frx_last_kernel_ms", "frx_tiff_unpack", "frx_decode_tiles_noalloc"]
+           "frx_last_kernel_ms", "frx_tiff_unpack", "frx_decode_tiles_noalloc", "frx_tile_md5"]
 NOALLOC_MAX_TILES, NOALLOC_MAX_FRAMES = 128, 32768   # include/frx.h FRX_NOALLOC_MAX_*
 
 _lib = None
@@ -110,6 +110,8 @@ def lib():
                                        C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
         L.frx_decode_tiles_noalloc.restype = C.c_int
         L.frx_decode_tiles_noalloc.argtypes = L.frx_decode_tiles.argtypes
+        L.frx_tile_md5.restype = C.c_int
+        L.frx_tile_md5.argtypes = [C.c_void_p, C.POINTER(Raster), C.POINTER(Tile), C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
         L.frx_quantize.restype = C.c_int
         L.frx_quantize.argtypes = [C.c_void_p, C.POINTER(Raster), C.POINTER(Tile), C.c_int32, C.c_void_p, C.c_void_p,
                                    C.c_void_p]

@@ -254,6 +254,21 @@ class Codec:
                                        C.c_void_p(mm.data_ptr()), self._stream()))
         return pcm, mm
 
+    def tile_md5(self, raster, tiles, pcm_mode: str = "reference", dtype: str | None = None) -> np.ndarray:
+        """MD5 signatures (n_tiles, 16) uint8 of the tiles' PCM, as STREAMINFO wants them.  raster: CUDA tensor or numpy array."""
+        torch = _torch()
+        if isinstance(raster, np.ndarray):
+            from .synth import from_numpy
+            raster = from_numpy(raster, device=f"cuda:{self.device}")
+        dtype = dtype or dtype_name(raster)
+        bands, H, W = raster.shape
+        arr = L.make_tiles(tiles)
+        out = torch.zeros((len(arr), 16), dtype=torch.uint8, device=raster.device)
+        r = self._raster_desc(raster.data_ptr(), dtype, bands, H, W)
+        L.check(self._lib.frx_tile_md5(self._h, C.byref(r), arr, len(arr), L.PCM_MODE[pcm_mode], C.c_void_p(out.data_ptr()), self._stream()))
+        torch.cuda.synchronize(raster.device)
+        return out.cpu().numpy()
+
     def dequantize(self, pcm, h, w, channels, bps, out_dtype: str, dmin: float, dmax: float,
                    pcm_mode: str = "reference"):
         """K12 only: int32 PCM (h*w, channels) -> (channels,h,w) raster tensor."""

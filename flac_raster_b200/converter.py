@@ -112,13 +112,15 @@ def raster_metadata(width, height, count, dtype, crs, transform, bounds, data_mi
 
 
 def stream_header(channels: int, bps: int, sample_rate: int, total_samples: int, frame_sizes, comments,
-                  blocksize: int = BLOCKSIZE, frame_table: bool = True, padding=None) -> bytes:
+                  blocksize: int = BLOCKSIZE, frame_table: bool = True, padding=None, md5: Optional[bytes] = None) -> bytes:
     """fLaC + STREAMINFO (finalised: total samples and min/max frame size, which the reference leaves 0,
-    SURVEY 0.10) + optional frxT frame-size table + VORBIS_COMMENT."""
+    SURVEY 0.10; the MD5 signature of the PCM when the caller computed one, Codec.tile_md5) + optional frxT frame-size
+    table + VORBIS_COMMENT."""
     fs = np.asarray(frame_sizes)
     si = flacmeta.StreamInfo(min_blocksize=blocksize, max_blocksize=blocksize,
                              min_framesize=int(fs.min()) if fs.size else 0, max_framesize=int(fs.max()) if fs.size else 0,
-                             sample_rate=sample_rate, channels=channels, bps=bps, total_samples=int(total_samples))
+                             sample_rate=sample_rate, channels=channels, bps=bps, total_samples=int(total_samples),
+                             md5=bytes(md5) if md5 is not None else b"\0" * 16)
     apps = {flacmeta.FRAME_TABLE_APP_ID: flacmeta.pack_frame_table(blocksize, fs)} if frame_table else None
     return flacmeta.build_header(si, comments, padding=padding, applications=apps)
 
@@ -176,11 +178,12 @@ def decode_stream(blob, metadata: Dict, device: int = 0, offset: int = 0) -> np.
 class RasterFLACConverter:
     """Drop-in for flac_raster.RasterFLACConverter (converter.py:17)."""
 
-    def __init__(self, device: int = 0, pcm_mode: str = "reference"):
+    def __init__(self, device: int = 0, pcm_mode: str = "reference", md5: bool = False):
         self.metadata_key = "RASTER_METADATA"
         self.logger = logging.getLogger("flac_raster.converter")
         self.device = device
         self.pcm_mode = pcm_mode
+        self.md5 = md5   # fill STREAMINFO's MD5 signature (the reference's files carry zeros, SURVEY 0.10)
 
     def _calculate_audio_params(self, raster_data: np.ndarray, dtype) -> Tuple[int, int]:
         """converter.py:25-54"""
@@ -207,7 +210,8 @@ class RasterFLACConverter:
         frames, frame_sizes, dmin, dmax, bps = encode_array(data, compression_level, sample_rate, self.pcm_mode, self.device)
         md = raster_metadata(meta["width"], meta["height"], meta["count"], meta["dtype"], crs, transform, bounds, dmin, dmax,
                              meta.get("nodata"), meta.get("driver", "GTiff"))
-        header = stream_header(count, bps, sample_rate, h * w, frame_sizes, metadata_comments(md, self.pcm_mode))
+        sig = get_codec(self.device).tile_md5(data, [(0, 0, h, w, 0, count)], self.pcm_mode)[0].tobytes() if self.md5 else None
+        header = stream_header(count, bps, sample_rate, h * w, frame_sizes, metadata_comments(md, self.pcm_mode), md5=sig)
         with open(flac_path, "wb") as f:
             f.write(header)
             f.write(frames.tobytes())

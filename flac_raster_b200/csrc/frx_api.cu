@@ -401,7 +401,7 @@ int frx_quantize(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *tile,
 
 static int decode_core(frx_ctx *c, const uint8_t *bytes_dev, uint64_t n_bytes, const frx_dtile *tiles, int32_t n_tiles,
                        const uint32_t *frame_size_dev, int32_t blocksize, int32_t out_dtype, int32_t pcm_mode, void *out_dev,
-                       int32_t *tile_status_dev, cudaStream_t st) {
+                       int32_t *tile_status_dev, cudaStream_t st, uint64_t out_elems = 0) {
     if (!bytes_dev || !tiles || n_tiles <= 0 || !out_dev || !tile_status_dev) return set_err(FRX_E_INVALID, "NULL argument");
     if (blocksize < 16 || blocksize > 65535) return set_err(FRX_E_INVALID, "bad blocksize %d", blocksize);
     if (out_dtype < FRX_U8 || out_dtype > FRX_F32) return set_err(FRX_E_INVALID, "bad out_dtype %d", out_dtype);
@@ -412,7 +412,14 @@ static int decode_core(frx_ctx *c, const uint8_t *bytes_dev, uint64_t n_bytes, c
         const frx_dtile &t = tiles[i];
         if (t.channels < 1 || t.channels > FRX_MAX_CH || t.h <= 0 || t.w <= 0 || (t.bps != 16 && t.bps != 32 && t.bps != 8 && t.bps != 24 && t.bps != 12 && t.bps != 20))
             return set_err(FRX_E_INVALID, "tile %d: bad geometry/bps", i);
-        if (t.byte_offset + t.byte_size > n_bytes) return set_err(FRX_E_INVALID, "tile %d: byte range outside the buffer", i);
+        if (t.byte_offset > n_bytes || t.byte_size > n_bytes - t.byte_offset) return set_err(FRX_E_INVALID, "tile %d: byte range outside the buffer", i);
+        if (out_elems) {   // the caller told us the size of the output: every element the tile writes must lie inside it
+            if (t.out_band_stride < 0 || t.out_row_stride < 0) return set_err(FRX_E_INVALID, "tile %d: negative output stride", i);
+            const unsigned __int128 last = (unsigned __int128)t.out_offset + (unsigned __int128)(t.channels - 1) * (uint64_t)t.out_band_stride +
+                                           (unsigned __int128)(t.h - 1) * (uint64_t)t.out_row_stride + (uint64_t)t.w;
+            if (last > (unsigned __int128)out_elems) return set_err(FRX_E_INVALID, "tile %d: output block ends at element %llu, beyond the %llu the output holds", i,
+                                                                     (unsigned long long)last, (unsigned long long)out_elems);
+        }
         uint64_t expect = ((uint64_t)t.h * t.w + blocksize - 1) / blocksize;
         if (t.n_frames != expect) return set_err(FRX_E_INVALID, "tile %d: n_frames %u != ceil(h*w/blocksize) %llu", i, t.n_frames, (unsigned long long)expect);
         if (t.first_frame != 0xFFFFFFFFu && !frame_size_dev) return set_err(FRX_E_INVALID, "tile %d needs frame_size", i);
@@ -472,6 +479,23 @@ int frx_decode_tiles(frx_ctx *c, const uint8_t *bytes_dev, uint64_t n_bytes, con
     CK(cudaSetDevice(c->device));
     return decode_core(c, bytes_dev, n_bytes, tiles, n_tiles, frame_size_dev, blocksize, out_dtype, pcm_mode, out_dev, tile_status_dev,
                        (cudaStream_t)stream);
+}
+
+int frx_tile_md5(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *tiles, int32_t n_tiles, int32_t pcm_mode, uint8_t *md5_dev, void *stream) {
+    if (!c) return set_err(FRX_E_INVALID, "ctx is NULL");
+    int rc = check_raster(raster_dev); if (rc) return rc;
+    if (!md5_dev) return set_err(FRX_E_INVALID, "md5_dev is NULL");
+    frx_raster r = normalise_raster(raster_dev);
+    rc = check_tiles(tiles, n_tiles, r.bands, r.height, r.width); if (rc) return rc;
+    CK(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    frx_encode_params p = { 5, 4096, 44100, pcm_mode };
+    rc = check_params(&p); if (rc) return rc;
+    EncPrep prep;
+    rc = encode_prepare(c, r, tiles, n_tiles, &p, prep, st); if (rc) return rc;   // K0: the quantiser needs each stream's min/max
+    CK(frx_launch_md5(r, (const frx_tile *)c->tiles.p, (const FrxQuant *)c->quant.p, n_tiles, pcm_mode, prep.bps, md5_dev, st));
+    c->launches += 1;
+    return FRX_OK;
 }
 
 int frx_dequantize(frx_ctx *c, const int32_t *pcm_dev, int32_t h, int32_t w, int32_t channels, int32_t bps, int32_t out_dtype,
@@ -681,7 +705,7 @@ int frx_decode_tiles_host(frx_ctx *c, const uint8_t *bytes_host, uint64_t n_byte
         CK(cudaMemcpyAsync(fs_dev, frame_size_host, sizeof(uint32_t) * (size_t)nfs, cudaMemcpyHostToDevice, st));
     }
     int rc = decode_core(c, (const uint8_t *)c->h_bytes.p, n_bytes, tiles, n_tiles, fs_dev, blocksize, out_dtype, pcm_mode, c->h_out.p,
-                         status_dev, st);
+                         status_dev, st, out_elems);
     if (rc) return rc;
     CK(cudaMemcpyAsync(out_host, c->h_out.p, out_elems * esz, cudaMemcpyDeviceToHost, st));
     std::vector<int32_t> status(n_tiles);

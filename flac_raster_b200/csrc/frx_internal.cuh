@@ -66,6 +66,8 @@ cudaError_t frx_launch_tile_index(const uint32_t *frame_prefix, const uint32_t *
 cudaError_t frx_launch_quantize(const frx_raster &r, const frx_tile &t, const FrxQuant *q, int mode, int32_t *pcm, double *minmax,
                                 cudaStream_t st);
 void frx_make_crc16_tables(uint16_t *tab);
+cudaError_t frx_launch_md5(const frx_raster &r, const frx_tile *tiles_dev, const FrxQuant *quant, int n_tiles, int mode, int bps, uint8_t *out,
+                           cudaStream_t st);
 cudaError_t frx_launch_frame_pos(const DecArgs &a, cudaStream_t st);
 cudaError_t frx_launch_discover(const DecArgs &a, const uint32_t *unit_prefix, const int32_t *unit_tiles, int n_scan_tiles,
                                 uint32_t total_units, cudaStream_t st);

@@ -104,6 +104,11 @@ class SpatialFLACEncoder:
         self.logger = logging.getLogger("flac_raster.spatial_encoder")
         self.frames: List[SpatialFrame] = []
         self.device = device
+        if pcm_mode not in ("lossless", "reference_spatial"):
+            # converter.py's min/max stretch ("reference") would be applied per tile here, while the file keeps one global
+            # GEOSPATIAL_DATA_MIN/MAX: integer rasters would come back wrong.  The reference's --spatial path never uses it.
+            raise ValueError(f"pcm_mode {pcm_mode!r} is not available for spatial files: use 'lossless' (default) or "
+                             "'reference_spatial' (the reference's own --spatial mapping)")
         self.pcm_mode = pcm_mode
 
     def _calculate_tiles(self, height, width):

@@ -62,7 +62,7 @@ def tile_bbox(transform, col_off, row_off, tw, th):
 
 
 def encode_streaming_tiles(raster: np.ndarray, tiles, crs, transform, nodata=None, bands: str = "first",
-                           pcm_mode: str = "reference", device: int = 0, row_base: int = 0, codec=None) -> Tuple[List[bytes], List[int]]:
+                           pcm_mode: str = "reference", device: int = 0, row_base: int = 0, codec=None, md5: bool = False) -> Tuple[List[bytes], List[int]]:
     """Encode `tiles` [(row_off,col_off,h,w)] of the host raster (bands,H,W) into complete per-tile FLAC files.
     `row_base`: raster row 0 is row `row_base` of the full image (a rank holding only its own rows).
     Each tile is what RasterFLACConverter.tiff_to_flac(level 5) makes of the tile's own GeoTIFF
@@ -84,6 +84,7 @@ def encode_streaming_tiles(raster: np.ndarray, tiles, crs, transform, nodata=Non
         res = (codec or get_codec(device)).encode_tiles_any(raster, units, level=STREAMING_LEVEL, blocksize=BLOCKSIZE, sample_rate=sr,
                                                             pcm_mode=pcm_mode)
         data = res.bytes[:int(res.total_bytes[0])]
+        sigs = (codec or get_codec(device)).tile_md5(raster, units, pcm_mode) if md5 else None
         fpos = 0
         for k, i in enumerate(sel):
             r, c, th, tw = tiles[i]
@@ -93,7 +94,7 @@ def encode_streaming_tiles(raster: np.ndarray, tiles, crs, transform, nodata=Non
             bbox, tt = tile_bbox(transform, c, r, tw, th)
             md = raster_metadata(tw, th, nch, dtype, crs, tt, BoundingBox(bbox[0], bbox[1], bbox[2], bbox[3]),
                                  float(res.tile_minmax[k, 0]), float(res.tile_minmax[k, 1]), nodata)
-            hdr = stream_header(nch, res.bps, sr, th * tw, fs, metadata_comments(md, pcm_mode))
+            hdr = stream_header(nch, res.bps, sr, th * tw, fs, metadata_comments(md, pcm_mode), md5=None if sigs is None else sigs[k].tobytes())
             off, size = int(res.tile_offset[k]), int(res.tile_size[k])
             blobs[i] = hdr + data[off:off + size].tobytes()
     return blobs, [len(b) for b in blobs]
@@ -129,7 +130,7 @@ def _new_codec(dev):
     return Codec(dev)
 
 
-def _encode_shard(input_file, dev, own_codec, tiles, lo, hi, crs, transform, nodata, bands, pcm_mode):
+def _encode_shard(input_file, dev, own_codec, tiles, lo, hi, crs, transform, nodata, bands, pcm_mode, md5=False):
     """One device's part of create-streaming: its own file handle and (when several shards run at once) its own libfrx context;
     only the raster rows the tile range touches -- and, in band-1 mode, only band 1 -- are ingested."""
     if lo == hi:
@@ -140,14 +141,14 @@ def _encode_shard(input_file, dev, own_codec, tiles, lo, hi, crs, transform, nod
             r0 = min(t[0] for t in tiles[lo:hi])
             r1 = max(t[0] + t[2] for t in tiles[lo:hi])
             raster = codec.read_tiff(src, r0, r1, bands=[0] if bands == "first" else None)
-        return encode_streaming_tiles(raster, tiles[lo:hi], crs, transform, nodata, bands, pcm_mode, dev, row_base=r0, codec=codec)
+        return encode_streaming_tiles(raster, tiles[lo:hi], crs, transform, nodata, bands, pcm_mode, dev, row_base=r0, codec=codec, md5=md5)
     finally:
         if own_codec:
             codec.close()
 
 
 def create_streaming(input_file, output_file, tile_size: int = 1024, bands: str = "first", pcm_mode: str = "reference",
-                     devices: Sequence[int] = (0,)) -> Dict:
+                     devices: Sequence[int] = (0,), md5: bool = False) -> Dict:
     """create-streaming (cli.py:620-804).  `devices`: GPUs of this process; contiguous tile ranges are sharded over them and
     encoded CONCURRENTLY, one thread and one libfrx context per device (the C-ABI allows one context per thread), then merged on
     the host by offset concatenation."""
@@ -157,11 +158,11 @@ def create_streaming(input_file, output_file, tile_size: int = 1024, bands: str 
     tiles = calculate_tiles(height, width, tile_size)
     ranges = [shard_range(len(tiles), len(devices), k) for k in range(len(devices))]
     if len(devices) == 1:
-        shards = [_encode_shard(input_file, devices[0], False, tiles, ranges[0][0], ranges[0][1], crs, transform, nodata, bands, pcm_mode)]
+        shards = [_encode_shard(input_file, devices[0], False, tiles, ranges[0][0], ranges[0][1], crs, transform, nodata, bands, pcm_mode, md5)]
     else:
         from concurrent.futures import ThreadPoolExecutor
         with ThreadPoolExecutor(max_workers=len(devices)) as ex:
-            futs = [ex.submit(_encode_shard, input_file, dev, True, tiles, lo, hi, crs, transform, nodata, bands, pcm_mode)
+            futs = [ex.submit(_encode_shard, input_file, dev, True, tiles, lo, hi, crs, transform, nodata, bands, pcm_mode, md5)
                     for dev, (lo, hi) in zip(devices, ranges)]
             shards = [f.result() for f in futs]
     chunks, offsets, sizes = merge_shards(shards)

@@ -143,6 +143,12 @@ int frx_decode_tiles(frx_ctx *ctx, const uint8_t *bytes_dev, uint64_t n_bytes, c
 /* K0+K1 alone: PCM (int32, channel-interleaved like pyFLAC's input, dump:1994) of one tile. */
 int frx_quantize(frx_ctx *ctx, const frx_raster *raster_dev, const frx_tile *tile_host, int32_t pcm_mode,
                  int32_t *pcm_dev, double *minmax_dev, void *stream);
+/* STREAMINFO's MD5 signature of every tile's PCM (the channel-interleaved samples as little-endian bytes of the effective
+ * sample size; layout docs/sonos-pyflac.txt:3938-3949): md5_dev[n_tiles][16].  The reference leaves the field zero
+ * (libFLAC computes it only when the stream is finalised through seek callbacks, which converter.py:201-216 does not
+ * supply), so this is opt-in; one thread per tile, MD5 being a serial chain -- not part of the timed path.             */
+int frx_tile_md5(frx_ctx *ctx, const frx_raster *raster_dev, const frx_tile *tiles_host, int32_t n_tiles, int32_t pcm_mode,
+                 uint8_t *md5_dev, void *stream);
 /* K12 alone: int32 channel-interleaved PCM -> (channels,h,w) raster block. */
 int frx_dequantize(frx_ctx *ctx, const int32_t *pcm_dev, int32_t h, int32_t w, int32_t channels, int32_t bps,
                    int32_t out_dtype, int32_t pcm_mode, double dmin, double dmax, void *out_dev, void *stream);

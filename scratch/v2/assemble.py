@@ -41,5 +41,6 @@ static cudaError_t launch_encode_t(const EncArgs &a, int sm_count, cudaStream_t 
 """)
 tail = tail[:tail.index('#ifdef FRX_DBG\nextern "C" void frx_debug_trace')]
 mid = "".join((Path(__file__).parent / f"mid_{i}.cu").read_text() for i in range(1, 9))
-(root / "flac_raster_b200" / "csrc" / "frx_encode.cu").write_text(head + mid + "\n" + tail)
+mid9 = (Path(__file__).parent / "mid_9.cu").read_text()
+(root / "flac_raster_b200" / "csrc" / "frx_encode.cu").write_text(head + mid + "\n" + tail + mid9)
 print("assembled")

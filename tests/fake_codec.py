@@ -55,6 +55,18 @@ class OracleCodec:
                                      swap_bytes=(src._bo == ">"))
         return out if bands is None else np.ascontiguousarray(out[list(bands)])
 
+    def tile_md5(self, raster, tiles, pcm_mode="reference"):
+        """hashlib over the oracle's PCM (what libFLAC's MD5 covers: interleaved little-endian samples)."""
+        import hashlib
+        import numpy as np
+        from oracle import quant
+        out = []
+        for (r0, c0, h, w, b0, nch) in tiles:
+            assert pcm_mode == "reference"
+            pcm, bps, *_ = quant.reference_pcm(np.asarray(raster)[b0:b0 + nch, r0:r0 + h, c0:c0 + w])
+            out.append(np.frombuffer(hashlib.md5(pcm.astype("<i2" if bps == 16 else "<i4").tobytes()).digest(), dtype=np.uint8))
+        return np.stack(out)
+
     def encode_tiles_any(self, raster, tiles, **kw):
         return self.encode_tiles_host(raster, tiles, **kw)
 

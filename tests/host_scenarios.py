@@ -77,6 +77,20 @@ def convert_rgb_fixture_roundtrip(tmp):
     assert tuple(bsrc.transform)[:6] == tuple(src.transform)[:6] and str(bsrc.crs) == str(src.crs)
 
 
+def convert_writes_md5_when_asked(tmp):
+    """STREAMINFO's MD5: opt-in; equals the MD5 of the reference PCM's little-endian bytes -- for sample_rgb.tif
+    that is the fingerprint of the libFLAC-written fixture's own PCM."""
+    import hashlib
+    flac = tmp / "rgb_md5.flac"
+    RasterFLACConverter(md5=True).tiff_to_flac(GOLDEN / "sample_rgb.tif", flac)
+    si = flacmeta.parse_header(flac.read_bytes()).streaminfo
+    assert si.md5.hex() == "4bf5483c1452f8c591c813b52db99491"
+    pcm = oracle.decode_stream(flac.read_bytes())[0]
+    assert hashlib.md5(pcm.astype("<i2").tobytes()).digest() == si.md5
+    RasterFLACConverter().tiff_to_flac(GOLDEN / "sample_rgb.tif", tmp / "rgb_nomd5.flac")
+    assert flacmeta.parse_header((tmp / "rgb_nomd5.flac").read_bytes()).streaminfo.md5 == b"\0" * 16     # the reference's default
+
+
 def convert_reference_fixture_decodes(tmp):
     """flac_to_tiff on the reference-written sample_rgb.flac (+ its .json sidecar, no embedded comments, no
     frame table -> frame discovery) reproduces sample_rgb_reconstructed.tif."""
@@ -208,6 +222,20 @@ def spatial_roundtrip(tmp, bands=12, dtype="int16"):
         assert np.array_equal(a, arr[:, wd.row_off:wd.row_off + wd.height, wd.col_off:wd.col_off + wd.width])
     RasterFLACConverter().flac_to_tiff(out, tmp / "ms_back.tif")
     assert np.array_equal(read_tif(tmp / "ms_back.tif")[0], arr)
+
+
+def spatial_rejects_per_tile_stretch(tmp):
+    """converter.py's min/max stretch would be applied per tile while the file keeps one global DATA_MIN/MAX:
+    the spatial encoder refuses it, from the API and from the CLI."""
+    import pytest
+    from typer.testing import CliRunner
+    from flac_raster_b200.cli import app
+    with pytest.raises(ValueError, match="not available for spatial files"):
+        SpatialFLACEncoder(tile_size=64, pcm_mode="reference")
+    import shutil
+    shutil.copy(GOLDEN / "sample_dem.tif", tmp / "dem.tif")
+    r = CliRunner().invoke(app, ["convert", str(tmp / "dem.tif"), "-o", str(tmp / "sp.flac"), "--spatial", "--pcm-mode", "reference"])
+    assert r.exit_code == 1 and not (tmp / "sp.flac").exists()
 
 
 def spatial_reference_mode_reproduces_fixture(tmp):

@@ -17,6 +17,10 @@ def test_convert_rgb_fixture_roundtrip(tmp_path):
     hs.convert_rgb_fixture_roundtrip(tmp_path)
 
 
+def test_convert_writes_md5_when_asked(tmp_path):
+    hs.convert_writes_md5_when_asked(tmp_path)
+
+
 def test_convert_reference_fixture_decodes(tmp_path):
     hs.convert_reference_fixture_decodes(tmp_path)
 
@@ -47,6 +51,10 @@ def test_spatial_roundtrip(tmp_path, bands):
     hs.spatial_roundtrip(tmp_path, bands)
 
 
+def test_spatial_rejects_per_tile_stretch(tmp_path):
+    hs.spatial_rejects_per_tile_stretch(tmp_path)
+
+
 def test_spatial_reference_mode(tmp_path):
     hs.spatial_reference_mode_reproduces_fixture(tmp_path)
 
@@ -57,6 +65,14 @@ def test_pyflac_shim(tmp_path):
 
 def test_cli(tmp_path):
     hs.cli_commands(tmp_path)
+
+
+def test_unmodified_reference_converter_over_the_shim(tmp_path):
+    """SURVEY 8(b), GPU side: runs where /root/reference is mounted (not on the GPU box)."""
+    import reference_dropin as rd
+    if not rd.available():
+        pytest.skip("/root/reference is not mounted on this machine")
+    rd.reference_converter_roundtrip(tmp_path)
 
 
 def test_streaming_band1_of_planar_file_uploads_one_band(tmp_path, monkeypatch):

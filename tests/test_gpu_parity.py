@@ -285,3 +285,38 @@ def test_more_than_8_channels_is_rejected(codec):
     t = torch.zeros((12, 64, 64), dtype=torch.int16, device="cuda")
     with pytest.raises(FrxUnsupported):
         codec.encode_tiles(t, [(0, 0, 64, 64, 0, 12)])
+
+
+def test_host_decode_rejects_output_blocks_outside_the_buffer(codec, golden):
+    """frx_decode_tiles_host knows the size of the output: a descriptor whose block does not fit is refused before any launch."""
+    from flac_raster_b200._lib import FrxError
+    from flac_raster_b200.codec import make_dtiles
+    r = golden["in_dem"]
+    tiles = tiles_for(r, 256, "all")
+    res = codec.encode_tiles_host(r, tiles)
+    total = int(res.total_bytes[0])
+    e = dict(byte_offset=res.tile_offset[0], byte_size=res.tile_size[0], out_offset=0, out_band_stride=256 * 256, out_row_stride=256, h=256, w=256,
+             channels=1, bps=res.bps, dmin=res.tile_minmax[0, 0], dmax=res.tile_minmax[0, 1], first_frame=0, n_frames=16)
+    out = np.zeros(256 * 256, dtype=r.dtype)
+    fs = res.frame_size.astype(np.uint32)
+    assert not codec.decode_tiles_host(res.bytes[:total], make_dtiles([e]), out, frame_size=fs).any()
+    for bad in (dict(e, out_offset=1), dict(e, out_row_stride=257), dict(e, byte_offset=total - 10, byte_size=11)):
+        with pytest.raises(FrxError):
+            codec.decode_tiles_host(res.bytes[:total], make_dtiles([bad]), out, frame_size=fs)
+
+
+@pytest.mark.parametrize("name,tile,mode", [("rgb", 256, "reference"), ("rgb", 100, "reference"), ("f32_dem", 48, "reference"),
+                                            ("i16_dem", 37, "lossless"), ("u8_narrow", 5, "reference"), ("i32_mid", 50, "lossless")])
+def test_tile_md5_matches_hashlib(codec, golden, name, tile, mode):
+    """frx_tile_md5 == MD5 of the stream's PCM as little-endian bytes (what libFLAC stores in STREAMINFO); tile sizes with odd
+    sample counts put the pad byte in the middle of a word."""
+    import hashlib
+    from tests.helpers import lossless_pcm
+    r = golden[f"in_{name}"]
+    tiles = tiles_for(r, tile, "all")
+    got = codec.tile_md5(_torch_raster(r), tiles, pcm_mode=mode)
+    for (r0, c0, h, w, b0, nch), sig in zip(tiles, got):
+        block = r[b0:b0 + nch, r0:r0 + h, c0:c0 + w]
+        pcm, bps, *_ = (quant.reference_pcm(block) if mode == "reference" else lossless_pcm(block))
+        want = hashlib.md5(pcm.astype("<i2" if bps == 16 else "<i4").tobytes()).digest()
+        assert bytes(sig) == want, (name, (r0, c0, h, w))

@@ -51,6 +51,10 @@ def test_convert_rgb_fixture_roundtrip(fake, tmp_path):
     hs.convert_rgb_fixture_roundtrip(tmp_path)
 
 
+def test_convert_writes_md5_when_asked(fake, tmp_path):
+    hs.convert_writes_md5_when_asked(tmp_path)
+
+
 def test_convert_reference_fixture_decodes(fake, tmp_path):
     hs.convert_reference_fixture_decodes(tmp_path)
 
@@ -80,6 +84,10 @@ def test_spatial_roundtrip(fake, tmp_path, bands):
     hs.spatial_roundtrip(tmp_path, bands)
 
 
+def test_spatial_rejects_per_tile_stretch(fake, tmp_path):
+    hs.spatial_rejects_per_tile_stretch(tmp_path)
+
+
 def test_spatial_reference_mode(fake, tmp_path):
     hs.spatial_reference_mode_reproduces_fixture(tmp_path)
 
@@ -90,6 +98,14 @@ def test_pyflac_shim(fake, tmp_path):
 
 def test_cli(fake, tmp_path):
     hs.cli_commands(tmp_path)
+
+
+def test_unmodified_reference_converter_over_the_shim(fake, tmp_path):
+    """the reference's own converter.py, unmodified, on top of the pyflac-shaped shim."""
+    import reference_dropin as rd
+    if not rd.available():
+        pytest.skip("/root/reference is not mounted on this machine")
+    rd.reference_converter_roundtrip(tmp_path)
 
 
 def test_shard_ranges_cover_and_are_contiguous():
