@@ -374,60 +374,50 @@ __device__ __noinline__ void build_frame_desc(const EncArgs &a, FrameDesc &d, ui
 
 // K8: decoupled look-back over the frame sizes (whole warp).  A descriptor word carries flag and value together (A: the
 // frame's size, P: the inclusive byte prefix), so relaxed device-scope accesses are enough.  512 descriptors are examined
-// per round trip (16 consecutive ones per lane, nearest first).  When the walk meets a frame that has not published yet,
-// only that single word is polled.
-#define LB_PER_LANE 16
+// per round trip, as 16 rows of 32 consecutive words (one coalesced 256-byte load per row, all 16 in flight together); the
+// rows are then walked nearest-first with two ballots each.  When the walk meets a frame that has not published yet, only
+// that single word is polled.
+#define LB_ROWS 16
 struct LookBack {
     long long pos;        // nearest descriptor not yet accounted for
     uint64_t exclusive;   // bytes summed so far
     bool blocked;         // desc[pos] had not been published at the last visit
 };
-#ifdef FRX_DBG
-__device__ unsigned long long g_frx_dbg[16];
-#define DBG_ADD(i, v) do { if (lane == 0) atomicAdd(&g_frx_dbg[i], (unsigned long long)(v)); } while (0)
-#else
-#define DBG_ADD(i, v) do {} while (0)
-#endif
 __device__ __noinline__ bool lookback_step(const EncArgs &a, LookBack &lb, int lane) {
     const uint64_t FLAG_P = 2ull << 62, VMASK = (1ull << 62) - 1;
     if (lb.pos < 0) return true;
     if (lb.blocked) {
-        DBG_ADD(0, 1);
         uint64_t w = 0;
         if (lane == 0) w = frx_ld_relaxed_u64(&a.desc[lb.pos]);
         w = __shfl_sync(FULLMASK, w, 0);
         if ((w >> 62) == 0ull) return false;
         lb.blocked = false;
     }
-    DBG_ADD(1, 1);
-    uint64_t v[LB_PER_LANE];
-    const long long base = lb.pos - (long long)lane * LB_PER_LANE;
+    uint64_t v[LB_ROWS];
+    const long long base = lb.pos - lane;
 #pragma unroll
-    for (int k = 0; k < LB_PER_LANE; k++) {
-        const long long idx = base - k;
-        v[k] = idx >= 0 ? frx_ld_relaxed_u64(&a.desc[idx]) : FLAG_P;
+    for (int k = 0; k < LB_ROWS; k++) {
+        const long long idx = base - 32 * k;
+        v[k] = idx >= 0 ? frx_ld_relaxed_u64(&a.desc[idx]) : FLAG_P;      // in front of frame 0: an inclusive prefix of 0
     }
     uint64_t sum = 0;
-    int state = 0;                     // 0: all 16 ready, no P   1: stopped at a P   2: stopped at a not-ready entry
+    int result = 0;                    // 0: all 512 were sizes   1: reached an inclusive prefix   2: met an unpublished frame
     int taken = 0;
 #pragma unroll
-    for (int k = 0; k < LB_PER_LANE; k++) {
-        if (state == 0) {
+    for (int k = 0; k < LB_ROWS; k++) {
+        if (result == 0) {
             const uint32_t flag = (uint32_t)(v[k] >> 62);
-            if (flag == 0u) state = 2;
-            else { sum += v[k] & VMASK; taken++; if (flag == 2u) state = 1; }
+            const uint32_t mP = __ballot_sync(FULLMASK, flag == 2u), mN = __ballot_sync(FULLMASK, flag == 0u);
+            const int firstP = mP ? (__ffs((int)mP) - 1) : 32, firstN = mN ? (__ffs((int)mN) - 1) : 32;
+            const int stop = min(firstP, firstN);
+            if (lane < stop || (lane == stop && firstP < firstN)) sum += v[k] & VMASK;
+            if (stop < 32) { result = firstP < firstN ? 1 : 2; taken = 32 * k + stop; }
         }
     }
-    const uint32_t mP = __ballot_sync(FULLMASK, state == 1), mN = __ballot_sync(FULLMASK, state == 2);
-    const int firstP = mP ? (__ffs((int)mP) - 1) : 32, firstN = mN ? (__ffs((int)mN) - 1) : 32;
-    const int stop = min(firstP, firstN);
-    lb.exclusive += warp_sum_u64((lane <= stop) ? sum : 0ull);
-    if (firstP < firstN) return true;  // reached an inclusive prefix
-    if (firstN < 32) {
-        const int tk = __shfl_sync(FULLMASK, taken, firstN);
-        lb.pos -= (long long)firstN * LB_PER_LANE + tk;      // the frame that has not published its size yet
-        lb.blocked = true;
-    } else lb.pos -= 32 * LB_PER_LANE;
+    lb.exclusive += warp_sum_u64(sum);
+    if (result == 1) return true;
+    if (result == 2) { lb.pos -= taken; lb.blocked = true; }   // the frame that has not published its size yet
+    else lb.pos -= 32 * LB_ROWS;
     return false;
 }
 
@@ -561,7 +551,6 @@ __device__ __noinline__ uint2 load_channel(const EncArgs &a, WarpSh &ws, uint32_
     uint32_t *pcm = buf + SLACK_W;
     uint32_t orv = 0, ora = 0;
     const int nblk = (nsamp + BLK - 1) / BLK;
-    DBG_ADD(8, 1);
     if (d.tma && vch < 8) {
         const int esz = frx_dtype_size(a.dtype);
         const long long w = d.t.w;
@@ -930,15 +919,13 @@ __device__ __forceinline__ void pass1_full(uint32_t *pcm, int lane, uint64_t (&f
 
 // ---- K5: LPC residuals of the lane's block with all H taps (coefficients beyond the order are zero), zig-zag folded and
 //      stored in place of the samples; |r| sums per half.  MODE 0: 32-bit accumulate, 1: 64-bit accumulate ----
-// PACK (16-bit PCM only): the word keeps the sample in its low half next to the residual in its high half, so a fixed
-// predictor can still be applied afterwards without staging the channel again; `ovf` collects residuals that need more than 16 bits
-template <int H, int MODE, bool WIDE, bool PACK>
+template <int H, int MODE, bool WIDE>
 struct P2 {
     static constexpr int W = H + 4;
     int32_t s[W];
     int32_t q[H];
     int shift;
-    uint32_t acc32, ovf;
+    uint32_t acc32;
     uint64_t acc64;
     uint64_t cur, first;
     template <int P>
@@ -962,7 +949,6 @@ struct P2 {
             }
             u[i] = zigzag(r);
             if (WIDE) acc64 += (uint32_t)abs(r); else acc32 += (uint32_t)abs(r);
-            if (PACK) { ovf |= u[i]; u[i] = (u[i] << 16) | ((uint32_t)s[(4 * P + H + i) % W] & 0xFFFFu); }
         }
         *reinterpret_cast<uint4 *>(p) = make_uint4(u[0], u[1], u[2], u[3]);
     }
@@ -979,10 +965,10 @@ struct P2 {
         for (int k = 0; k < W; k++) s[k] = t[k];
     }
 };
-template <int H, int MODE, bool WIDE, bool PACK>
-__device__ __forceinline__ bool lpc_inplace_full(WarpSh &ws, uint32_t *pcm, int shift, int lane, uint64_t &sumA, uint64_t &sumB) {
+template <int H, int MODE, bool WIDE>
+__device__ __forceinline__ void lpc_inplace_full(WarpSh &ws, uint32_t *pcm, int shift, int lane, uint64_t &sumA, uint64_t &sumB) {
     uint32_t *blk = pcm + lane * BLK_W;
-    P2<H, MODE, WIDE, PACK> st;
+    P2<H, MODE, WIDE> st;
     int32_t hs[H];
     load_history<H>(blk, lane, hs);
     __syncwarp();                      // every lane holds its history before any lane overwrites samples
@@ -990,29 +976,22 @@ __device__ __forceinline__ bool lpc_inplace_full(WarpSh &ws, uint32_t *pcm, int 
     for (int k = 0; k < H; k++) st.s[k] = hs[k];
 #pragma unroll
     for (int j = 0; j < H; j++) st.q[j] = j < FRX_MAX_LPC ? ws.qlp[j] : 0;
-    st.shift = shift; st.acc32 = 0; st.ovf = 0; st.acc64 = 0; st.cur = 0; st.first = 0;
+    st.shift = shift; st.acc32 = 0; st.acc64 = 0; st.cur = 0; st.first = 0;
     walk_block<H>(st, blk);
     sumA = st.first; sumB = st.cur;
     __syncwarp();
-    return !PACK || __all_sync(FULLMASK, (st.ovf >> 16) == 0u);     // PACK: every residual fitted its half word
 }
 template <int H, bool WIDE>
-__device__ __noinline__ bool lpc_inplace_full_any(WarpSh &ws, uint32_t *pcm, int shift, int narrow, bool pack, int lane, uint64_t &sumA, uint64_t &sumB) {
-    if (!WIDE && pack) return lpc_inplace_full<H, 0, WIDE, !WIDE>(ws, pcm, shift, lane, sumA, sumB);
-    if (!WIDE || narrow) return lpc_inplace_full<H, 0, WIDE, false>(ws, pcm, shift, lane, sumA, sumB);
-    return lpc_inplace_full<H, 1, WIDE, false>(ws, pcm, shift, lane, sumA, sumB);
+__device__ __noinline__ void lpc_inplace_full_any(WarpSh &ws, uint32_t *pcm, int shift, int narrow, int lane, uint64_t &sumA, uint64_t &sumB) {
+    if (!WIDE || narrow) lpc_inplace_full<H, 0, WIDE>(ws, pcm, shift, lane, sumA, sumB);
+    else lpc_inplace_full<H, 1, WIDE>(ws, pcm, shift, lane, sumA, sumB);
 }
 
-// fixed predictor of order `order` (0..4), residuals zig-zag folded in place (32-bit arithmetic: lean data).  unpack16: the
-// words are the packed form the LPC trial left behind (sample in the low half)
-__device__ __noinline__ void fixed_inplace_full(uint32_t *pcm, int order, bool unpack16, int lane) {
+// fixed predictor of order `order` (0..4), residuals zig-zag folded in place (32-bit arithmetic: lean data)
+__device__ __noinline__ void fixed_inplace_full(uint32_t *pcm, int order, int lane) {
     uint32_t *blk = pcm + lane * BLK_W;
     int32_t hs[4];
     load_history<4>(blk, lane, hs);
-    if (unpack16) {
-#pragma unroll
-        for (int k = 0; k < 4; k++) hs[k] = (int32_t)(int16_t)hs[k];
-    }
     __syncwarp();
     int32_t prev = hs[3], d1p = hs[3] - hs[2];
     const int32_t dm2 = hs[2] - hs[1], dm3 = hs[1] - hs[0];
@@ -1020,11 +999,7 @@ __device__ __noinline__ void fixed_inplace_full(uint32_t *pcm, int order, bool u
 #pragma unroll 2
     for (int it = 0; it < BLK / 4; it++) {
         const uint4 v = *reinterpret_cast<const uint4 *>(blk + 4 * it);
-        int32_t x[4] = { (int32_t)v.x, (int32_t)v.y, (int32_t)v.z, (int32_t)v.w };
-        if (unpack16) {
-#pragma unroll
-            for (int i = 0; i < 4; i++) x[i] = (int32_t)(int16_t)x[i];
-        }
+        const int32_t x[4] = { (int32_t)v.x, (int32_t)v.y, (int32_t)v.z, (int32_t)v.w };
         uint32_t u[4];
 #pragma unroll
         for (int i = 0; i < 4; i++) {
@@ -1043,11 +1018,10 @@ __device__ __noinline__ void fixed_inplace_full(uint32_t *pcm, int order, bool u
 // front of them) and the lane-local condition of pack_runs: a lane that writes its run over its own block, starting four
 // words in front of it, never overtakes its reads when the bits through every group of four samples stay within
 // 128 t + 224.
-__device__ __forceinline__ uint32_t count_block(const uint32_t *pcm, int lane, uint32_t k0, uint32_t k1, uint32_t pb0, uint32_t pb1, uint32_t sh16, bool &ok) {
+__device__ __forceinline__ uint32_t count_block(const uint32_t *pcm, int lane, uint32_t k0, uint32_t k1, uint32_t pb0, uint32_t pb1, bool &ok) {
     const uint32_t *blk = pcm + lane * BLK_W;
     uint32_t c = pb0, lim = 224u, bad = 0;
     const uint32_t s0 = 4u * (k0 + 1u), s1 = 4u * (k1 + 1u);
-    k0 += sh16; k1 += sh16;                          // packed words carry the residual in their high half
 #pragma unroll 4
     for (int it = 0; it < BLK / 8; it++) {
         const uint4 v = *reinterpret_cast<const uint4 *>(blk + 4 * it);
@@ -1318,7 +1292,7 @@ __device__ __forceinline__ void append128(uint32_t &w3, uint32_t &w2, uint32_t &
     w3 = __funnelshift_lc(w2, w3, n); w2 = __funnelshift_lc(w1, w2, n); w1 = __funnelshift_lc(w0, w1, n);
     w0 = __funnelshift_lc(0u, w0, n) | v;
 }
-__device__ __noinline__ Emitter pack_rice(uint32_t *out, Emitter em, const SubDec &d, uint32_t *pcm, int nsamp, uint32_t sh16, int lane) {
+__device__ __noinline__ Emitter pack_rice(uint32_t *out, Emitter em, const SubDec &d, uint32_t *pcm, int nsamp, int lane) {
     const int order = d.order, po = d.po;
     const int psize = nsamp >> po;
     const uint32_t pb = d.rice2 ? 5u : 4u;
@@ -1329,7 +1303,7 @@ __device__ __noinline__ Emitter pack_rice(uint32_t *out, Emitter em, const SubDe
         const int g = BLK * c + 4 * lane;
         const uint4 v = *reinterpret_cast<const uint4 *>(pcm + PIDX(g));
         __syncwarp();
-        const uint32_t u[4] = { v.x >> sh16, v.y >> sh16, v.z >> sh16, v.w >> sh16 };
+        const uint32_t u[4] = { v.x, v.y, v.z, v.w };
         const bool allcoded = (c > 0 || order == 0) && BLK * (c + 1) <= nsamp;      // warp-uniform
         int pi;
         if (pow2) pi = g >> psh;
@@ -1425,15 +1399,14 @@ struct RunWriter {
         nb += n;
         word_if_full();
     }
-    __device__ __forceinline__ void code(uint32_t w, uint32_t sh16, uint32_t k, uint32_t kmask, uint32_t kbit, uint32_t k1) {
-        const uint32_t u = w >> sh16;                                   // (packed words: the residual is the high half)
+    __device__ __forceinline__ void code(uint32_t u, uint32_t k, uint32_t kmask, uint32_t kbit, uint32_t k1) {
         nb += u >> k;                                                   // the unary zeros
         if (nb >= 64u) { while (nb >= 64u) { nb -= 32u; word_if_full(); nb += 32u; } }   // a long run of zeros: rare
         word_if_full();
         put((u & kmask) | kbit, k1);
     }
 };
-__device__ __noinline__ Emitter pack_runs(uint32_t *out, Emitter em, const SubDec &d, uint32_t *pcm, uint32_t sh16, int lane) {
+__device__ __noinline__ Emitter pack_runs(uint32_t *out, Emitter em, const SubDec &d, uint32_t *pcm, int lane) {
     const int order = d.order, po = d.po;
     const uint32_t pb = d.rice2 ? 5u : 4u;
     const int psh = 12 - po, g0 = lane * BLK;
@@ -1441,7 +1414,7 @@ __device__ __noinline__ Emitter pack_runs(uint32_t *out, Emitter em, const SubDe
     const uint32_t k0 = d.k[g0 >> psh], k1 = d.k[(g0 + BLK / 2) >> psh];
     const uint32_t pb0 = (g0 & ((1 << psh) - 1)) == 0 ? pb : 0u, pb1 = po == 6 ? pb : 0u;
     bool ok;
-    uint32_t B = count_block(pcm, lane, k0, k1, pb0, pb1, sh16, ok);
+    uint32_t B = count_block(pcm, lane, k0, k1, pb0, pb1, ok);
     if (lane == 0) B -= (uint32_t)order * (k0 + 1u);
     uint32_t incl = B;
 #pragma unroll
@@ -1468,7 +1441,7 @@ __device__ __noinline__ Emitter pack_runs(uint32_t *out, Emitter em, const SubDe
             const uint32_t u[4] = { v.x, v.y, v.z, v.w };
 #pragma unroll
             for (int i = 0; i < 4; i++)
-                if (lane != 0 || 4 * it + i >= order) w.code(u[i], sh16, k, kmask, kbit, kk1);
+                if (lane != 0 || 4 * it + i >= order) w.code(u[i], k, kmask, kbit, kk1);
         }
     }
     const uint32_t nwhole = (w.wa - smem_u32(sp)) >> 2;
@@ -1594,7 +1567,7 @@ __device__ __forceinline__ void copy_words_out(uint8_t *dst, const uint32_t *bit
 #define BUF_PCM 0
 #define BUF_RES 1
 #define BUF_JUNK 2
-struct BufState { int kind, vch, type, order; uint32_t sh16; };   // sh16 = 16: residual words in the packed form (sample in the low half)
+struct BufState { int kind, vch, type, order; };
 
 __device__ __forceinline__ void shift_wasted(uint32_t *pcm, int nsamp, int wasted, int lane) {
     const int gend = min(FRX_MAX_BLOCK, ((nsamp + BLK - 1) / BLK) * BLK);
@@ -1609,24 +1582,19 @@ __device__ __forceinline__ void save_warmup(WarpSh &ws, const uint32_t *pcm, int
 // residuals of the recorded decision into the buffer (the buffer holds the PCM of d.vch, wasted bits already shifted out)
 template <bool WIDE, int H>
 __device__ __forceinline__ bool residuals_inplace(WarpSh &ws, uint32_t *buf, const SubDec &d, int nsamp, unsigned long long *bins, int psf, int lane,
-                                                  uint64_t &sumA, uint64_t &sumB, bool pack = false, bool unpack16 = false) {
+                                                  uint64_t &sumA, uint64_t &sumB) {
     uint32_t *pcm = buf + SLACK_W;
     const int type = d.type, order = d.order, shift = d.shift, narrow = d.narrow;
     const bool fast = d.fast != 0;
-    if (unpack16) { if (lane < order) ws.warm[lane] = (int32_t)(int16_t)pcm[PIDX(lane)]; __syncwarp(); }
-    else save_warmup(ws, pcm, order, lane);
+    save_warmup(ws, pcm, order, lane);
     bool ok = true;
     sumA = 0; sumB = 0;
     if (fast) {
-        if (type == 3) ok = lpc_inplace_full_any<H, WIDE>(ws, pcm, shift, narrow, pack, lane, sumA, sumB);
-        else fixed_inplace_full(pcm, order, unpack16, lane);
+        if (type == 3) lpc_inplace_full_any<H, WIDE>(ws, pcm, shift, narrow, lane, sumA, sumB);
+        else fixed_inplace_full(pcm, order, lane);
         // warm-up samples are not coded: take their |r| out of the first half's sum and zero them
-        const bool packed = !WIDE && pack && type == 3;
         uint32_t wv = 0;
-        if (lane < order) {
-            wv = unzig_abs(packed ? pcm[lane] >> 16 : pcm[lane]);
-            pcm[lane] = packed ? (pcm[lane] & 0xFFFFu) : 0u;
-        }
+        if (lane < order) { wv = unzig_abs(pcm[lane]); pcm[lane] = 0u; }
         const uint64_t wsum = warp_sum_u64(wv);
         if (lane == 0 && type == 3) sumA -= wsum;
         __syncwarp();
@@ -1655,7 +1623,7 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
     const int po_max = fd.po_max;
     const int max_lpc = min((int)fd.max_lpc, H);
     const uint64_t verb_bits = 8ull + (uint64_t)wasted + (uint64_t)nsamp * (uint64_t)sbps;
-    bs.kind = BUF_PCM; bs.vch = vch; bs.type = 1; bs.order = 0; bs.sh16 = 0;
+    bs.kind = BUF_PCM; bs.vch = vch; bs.type = 1; bs.order = 0;
     if (lane == 0) {
         d.type = 1; d.order = 0; d.wasted = (uint8_t)wasted; d.po = 0; d.rice2 = 0; d.precision = 0; d.sbps = (uint8_t)sbps; d.vch = (uint8_t)vch;
         d.fast = fast ? 1 : 0; d.narrow = 1; d.runs = 0; d.shift = 0; d.bits = (uint32_t)verb_bits;
@@ -1745,16 +1713,7 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
         __syncwarp();
         uint64_t sA = 0, sB = 0;
         if (!fast) { bins[lane] = 0ull; __syncwarp(); }
-        const bool pack = !WIDE && fast;              // 16-bit PCM: keep the samples beside the residuals
-        bool ok = residuals_inplace<WIDE, H>(ws, buf, d, nsamp, bins, psf, lane, sA, sB, pack);
-        if (!ok && pack) {
-            DBG_ADD(9, 1);
-            // a residual wider than 16 bits (a wild predictor): stage the channel again and run the plain form
-            (void)load_channel(a, ws, buf, vch, phase, lane);
-            if (wasted) shift_wasted(pcm, nsamp, wasted, lane);
-            ok = residuals_inplace<WIDE, H>(ws, buf, d, nsamp, bins, psf, lane, sA, sB, false);
-            bs.sh16 = 0;
-        } else bs.sh16 = pack ? 16u : 0u;
+        const bool ok = residuals_inplace<WIDE, H>(ws, buf, d, nsamp, bins, psf, lane, sA, sB);
         bs.kind = ok ? BUF_RES : BUF_JUNK; bs.type = 3; bs.order = lc.order;
         if (ok) {
             RiceChoice rl;
@@ -1782,14 +1741,13 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
     d.k[lane] = ws.kparam[cand][lane]; d.k[lane + 32] = ws.kparam[cand][lane + 32];
     __syncwarp();
     if (type == 2) {
-        const bool unpack = bs.kind == BUF_RES && bs.sh16 == 16u;       // the LPC trial kept the samples: no second staging
-        if (bs.kind != BUF_PCM && !unpack) {
+        if (bs.kind != BUF_PCM) {
             (void)load_channel(a, ws, buf, vch, phase, lane);
             if (wasted) shift_wasted(pcm, nsamp, wasted, lane);
         }
         uint64_t x0, x1;
-        (void)residuals_inplace<WIDE, H>(ws, buf, d, nsamp, nullptr, psf, lane, x0, x1, false, unpack);
-        bs.kind = BUF_RES; bs.type = 2; bs.order = order; bs.sh16 = 0;
+        (void)residuals_inplace<WIDE, H>(ws, buf, d, nsamp, nullptr, psf, lane, x0, x1);
+        bs.kind = BUF_RES; bs.type = 2; bs.order = order;
     }
     // ---- exact size ----
     const uint32_t pb = rice2 ? 5u : 4u;
@@ -1801,7 +1759,7 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
         const int g0 = lane * BLK;
         const uint32_t k0 = d.k[g0 >> psh], k1 = d.k[(g0 + BLK / 2) >> psh];
         bool lane_ok;
-        uint32_t c = count_block(pcm, lane, k0, k1, (g0 & ((1 << psh) - 1)) == 0 ? pb : 0u, po == 6 ? pb : 0u, bs.sh16, lane_ok);
+        uint32_t c = count_block(pcm, lane, k0, k1, (g0 & ((1 << psh) - 1)) == 0 ? pb : 0u, po == 6 ? pb : 0u, lane_ok);
         if (lane == 0) c -= (uint32_t)order * (k0 + 1u);           // warm-up samples carry no code (their slots hold 0)
         if (lane == 0) c += hb;
         uint32_t incl = c;
@@ -1834,7 +1792,7 @@ __device__ __noinline__ void materialise(const EncArgs &a, WarpSh &ws, uint32_t 
     uint32_t *pcm = buf + SLACK_W;
     (void)load_channel(a, ws, buf, d.vch, phase, lane);
     if (d.wasted) shift_wasted(pcm, ws.fd.nsamp, d.wasted, lane);
-    bs.kind = BUF_PCM; bs.vch = d.vch; bs.sh16 = 0;
+    bs.kind = BUF_PCM; bs.vch = d.vch;
     if (want_res) {
         if (lane < FRX_MAX_LPC) ws.qlp[lane] = d.qlp[lane];
         __syncwarp();
@@ -1867,22 +1825,16 @@ __global__ void __launch_bounds__(ENC_CTA, 1) frx_encode_kernel(const EncArgs a)
     int ti = 0;
     const bool stereo = a.stereo != 0;
 
-#ifdef FRX_DBG
-    const long long tk0 = clock64();
-#endif
     for (;;) {
         uint32_t f = 0;
         if (lane == 0) f = atomicAdd(a.ticket, 1u);
         f = __shfl_sync(FULLMASK, f, 0);
         if (f >= a.total_frames) break;
-#ifdef FRX_DBG
-        const long long ta0 = clock64();
-#endif
         build_frame_desc(a, ws.fd, f, ti, lane);
         const int nsamp = ws.fd.nsamp;
         const int n_ch = ws.fd.t.n_channels;
         BufState bs;
-        bs.kind = BUF_JUNK; bs.vch = -1; bs.type = 0; bs.order = 0; bs.sh16 = 0;
+        bs.kind = BUF_JUNK; bs.vch = -1; bs.type = 0; bs.order = 0;
 
         // ---- sweep 1: search every subframe, exact sizes ----
         const int nsub = n_ch;
@@ -1908,10 +1860,6 @@ __global__ void __launch_bounds__(ENC_CTA, 1) frx_encode_kernel(const EncArgs a)
         for (int c = 0; c < nsub; c++) frame_bits += ws.dec[c == 0 ? sub0 : (c == 1 ? sub1 : c)].bits;
         const uint32_t body_bytes = (frame_bits + 7u) >> 3;
         const uint32_t nbytes = body_bytes + 2u;
-#ifdef FRX_DBG
-        { const long long dt = clock64() - ta0; const int ty = ws.dec[0].type;
-          DBG_ADD(5, ty == 2 ? dt : 0); DBG_ADD(6, ty == 2 ? 1 : 0); DBG_ADD(7, dt); }
-#endif
         if (lane == 0) {
             // the frame's size is final: publish it, the look-back of the frames behind this one can proceed
             if (f != 0) frx_st_relaxed_u64(&a.desc[f], (1ull << 62) | (uint64_t)nbytes);
@@ -1936,13 +1884,7 @@ __global__ void __launch_bounds__(ENC_CTA, 1) frx_encode_kernel(const EncArgs a)
         auto get_offset = [&]() {
             LookBack lb;
             lb.pos = (long long)f - 1; lb.exclusive = 0; lb.blocked = false;
-#ifdef FRX_DBG
-            const long long t0 = clock64();
-#endif
             while (!lookback_step(a, lb, lane)) { if (lb.blocked) __nanosleep(100); }
-#ifdef FRX_DBG
-            DBG_ADD(2, clock64() - t0); DBG_ADD(3, 1);
-#endif
             off = lb.exclusive;
             if (lane == 0) {
                 frx_st_relaxed_u64(&a.desc[f], (2ull << 62) | (off + (uint64_t)nbytes));
@@ -1959,7 +1901,7 @@ __global__ void __launch_bounds__(ENC_CTA, 1) frx_encode_kernel(const EncArgs a)
             const SubDec &d = ws.dec[c == 0 ? sub0 : (c == 1 ? sub1 : c)];
             materialise<WIDE, H>(a, ws, buf, d, phase, bs, lane);
             em = pack_subframe_header(ws, buf, em, d, pcm, lane);
-            if (d.type >= 2) em = d.runs ? pack_runs(buf, em, d, pcm, bs.sh16, lane) : pack_rice(buf, em, d, pcm, nsamp, bs.sh16, lane);
+            if (d.type >= 2) em = d.runs ? pack_runs(buf, em, d, pcm, lane) : pack_rice(buf, em, d, pcm, nsamp, lane);
             else if (d.type == 1) em = pack_verbatim(buf, em, d, pcm, nsamp, lane);
             bs.kind = BUF_JUNK;                     // the packed bits now lie over the samples
             if (c + 1 < nsub) {
@@ -2002,17 +1944,7 @@ __global__ void __launch_bounds__(ENC_CTA, 1) frx_encode_kernel(const EncArgs a)
         }
         __syncwarp();
     }
-#ifdef FRX_DBG
-    DBG_ADD(4, clock64() - tk0);
-#endif
 }
-#ifdef FRX_DBG
-extern "C" void frx_debug_read(unsigned long long *out, int reset) {
-    cudaDeviceSynchronize();
-    cudaMemcpyFromSymbol(out, g_frx_dbg, sizeof(unsigned long long) * 16);
-    if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(g_frx_dbg, z, sizeof(z)); }
-}
-#endif
 
 // ------------------------------------------------------------------------------------------
 // K0+K1 alone (frx_quantize): interleaved int32 PCM of one tile

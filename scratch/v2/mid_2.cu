@@ -92,9 +92,10 @@ __device__ __noinline__ void build_frame_desc(const EncArgs &a, FrameDesc &d, ui
 
 // K8: decoupled look-back over the frame sizes (whole warp).  A descriptor word carries flag and value together (A: the
 // frame's size, P: the inclusive byte prefix), so relaxed device-scope accesses are enough.  512 descriptors are examined
-// per round trip (16 consecutive ones per lane, nearest first).  When the walk meets a frame that has not published yet,
-// only that single word is polled.
-#define LB_PER_LANE 16
+// per round trip, as 16 rows of 32 consecutive words (one coalesced 256-byte load per row, all 16 in flight together); the
+// rows are then walked nearest-first with two ballots each.  When the walk meets a frame that has not published yet, only
+// that single word is polled.
+#define LB_ROWS 16
 struct LookBack {
     long long pos;        // nearest descriptor not yet accounted for
     uint64_t exclusive;   // bytes summed so far
@@ -110,33 +111,30 @@ __device__ __noinline__ bool lookback_step(const EncArgs &a, LookBack &lb, int l
         if ((w >> 62) == 0ull) return false;
         lb.blocked = false;
     }
-    uint64_t v[LB_PER_LANE];
-    const long long base = lb.pos - (long long)lane * LB_PER_LANE;
+    uint64_t v[LB_ROWS];
+    const long long base = lb.pos - lane;
 #pragma unroll
-    for (int k = 0; k < LB_PER_LANE; k++) {
-        const long long idx = base - k;
-        v[k] = idx >= 0 ? frx_ld_relaxed_u64(&a.desc[idx]) : FLAG_P;
+    for (int k = 0; k < LB_ROWS; k++) {
+        const long long idx = base - 32 * k;
+        v[k] = idx >= 0 ? frx_ld_relaxed_u64(&a.desc[idx]) : FLAG_P;      // in front of frame 0: an inclusive prefix of 0
     }
     uint64_t sum = 0;
-    int state = 0;                     // 0: all 16 ready, no P   1: stopped at a P   2: stopped at a not-ready entry
+    int result = 0;                    // 0: all 512 were sizes   1: reached an inclusive prefix   2: met an unpublished frame
     int taken = 0;
 #pragma unroll
-    for (int k = 0; k < LB_PER_LANE; k++) {
-        if (state == 0) {
+    for (int k = 0; k < LB_ROWS; k++) {
+        if (result == 0) {
             const uint32_t flag = (uint32_t)(v[k] >> 62);
-            if (flag == 0u) state = 2;
-            else { sum += v[k] & VMASK; taken++; if (flag == 2u) state = 1; }
+            const uint32_t mP = __ballot_sync(FULLMASK, flag == 2u), mN = __ballot_sync(FULLMASK, flag == 0u);
+            const int firstP = mP ? (__ffs((int)mP) - 1) : 32, firstN = mN ? (__ffs((int)mN) - 1) : 32;
+            const int stop = min(firstP, firstN);
+            if (lane < stop || (lane == stop && firstP < firstN)) sum += v[k] & VMASK;
+            if (stop < 32) { result = firstP < firstN ? 1 : 2; taken = 32 * k + stop; }
         }
     }
-    const uint32_t mP = __ballot_sync(FULLMASK, state == 1), mN = __ballot_sync(FULLMASK, state == 2);
-    const int firstP = mP ? (__ffs((int)mP) - 1) : 32, firstN = mN ? (__ffs((int)mN) - 1) : 32;
-    const int stop = min(firstP, firstN);
-    lb.exclusive += warp_sum_u64((lane <= stop) ? sum : 0ull);
-    if (firstP < firstN) return true;  // reached an inclusive prefix
-    if (firstN < 32) {
-        const int tk = __shfl_sync(FULLMASK, taken, firstN);
-        lb.pos -= (long long)firstN * LB_PER_LANE + tk;      // the frame that has not published its size yet
-        lb.blocked = true;
-    } else lb.pos -= 32 * LB_PER_LANE;
+    lb.exclusive += warp_sum_u64(sum);
+    if (result == 1) return true;
+    if (result == 2) { lb.pos -= taken; lb.blocked = true; }   // the frame that has not published its size yet
+    else lb.pos -= 32 * LB_ROWS;
     return false;
 }
