@@ -846,8 +846,8 @@ struct P1 {
             const int32_t d1 = x[i] - prev;
             const int32_t d2 = d1 - d1p, d3 = d2 - d2p, d4 = d3 - d3p;
             prev = x[i]; d1p = d1; d2p = d2; d3p = d3;
-            f[0] += (uint32_t)abs(x[i]); f[1] += (uint32_t)abs(d1); f[2] += (uint32_t)abs(d2);
-            f[3] += (uint32_t)abs(d3); f[4] += (uint32_t)abs(d4);
+            f[0] = __sad(x[i], 0, f[0]); f[1] = __sad(d1, 0, f[1]); f[2] = __sad(d2, 0, f[2]);      // |e| + f in one VABSDIFF each
+            f[3] = __sad(d3, 0, f[3]); f[4] = __sad(d4, 0, f[4]);
             const float cn = fmaf(twoc, c1, -c0);
             const float wv = fmaf(-wb, c1, wa);
             c0 = c1; c1 = cn;
@@ -948,7 +948,7 @@ struct P2 {
                 r = (int32_t)((long long)s[(4 * P + H + i) % W] - (a >> shift));
             }
             u[i] = zigzag(r);
-            if (WIDE) acc64 += (uint32_t)abs(r); else acc32 += (uint32_t)abs(r);
+            if (WIDE) acc64 += (uint32_t)abs(r); else acc32 = __sad(r, 0, acc32);
         }
         *reinterpret_cast<uint4 *>(p) = make_uint4(u[0], u[1], u[2], u[3]);
     }
@@ -1385,7 +1385,7 @@ __device__ __noinline__ Emitter pack_rice(uint32_t *out, Emitter em, const SubDe
 // after the other (the global in-place condition keeps a destination below every unread source) and the word two runs share
 // is OR-ed.
 struct RunWriter {
-    uint32_t hi, lo, nb;
+    uint32_t hi, lo, nb;                                                 // 64-bit accumulator, nb bits used (< 64 between samples)
     uint32_t wa;                                                         // shared-memory byte address of the next word
     // store the completed word when there is one: predicated, no branch (lanes complete their words at different samples)
     __device__ __forceinline__ void word_if_full() {
@@ -1393,18 +1393,21 @@ struct RunWriter {
         const bool f = nb >= 32u;
         wa += f ? 4u : 0u; hi = f ? lo : hi; lo = f ? 0u : lo; nb -= f ? 32u : 0u;
     }
-    __device__ __forceinline__ void put(uint32_t v, uint32_t n) {        // n <= 32 bits, nb < 32 on entry
+    // append n <= 32 bits; on entry nb + n <= 64
+    __device__ __forceinline__ void bits(uint32_t v, uint32_t n) {
         const uint64_t x = (uint64_t)v << (64u - n - nb);
         hi |= (uint32_t)(x >> 32); lo |= (uint32_t)x;
         nb += n;
-        word_if_full();
     }
+    __device__ __forceinline__ void put(uint32_t v, uint32_t n) { word_if_full(); bits(v, n); }     // nb < 64 on entry
+    // one Rice code: at most one word leaves per sample; a run of zeros that would not fit takes the loop (rare)
     __device__ __forceinline__ void code(uint32_t u, uint32_t k, uint32_t kmask, uint32_t kbit, uint32_t k1) {
+        word_if_full();                                                 // nb < 32
         nb += u >> k;                                                   // the unary zeros
-        if (nb >= 64u) { while (nb >= 64u) { nb -= 32u; word_if_full(); nb += 32u; } }   // a long run of zeros: rare
-        word_if_full();
-        put((u & kmask) | kbit, k1);
+        if (nb + k1 > 63u) { while (nb >= 32u) word_if_full(); }
+        bits((u & kmask) | kbit, k1);                                   // nb <= 63
     }
+    __device__ __forceinline__ void finish() { word_if_full(); }        // nb < 32: the incomplete last word is in hi
 };
 __device__ __noinline__ Emitter pack_runs(uint32_t *out, Emitter em, const SubDec &d, uint32_t *pcm, int lane) {
     const int order = d.order, po = d.po;
@@ -1431,6 +1434,8 @@ __device__ __noinline__ Emitter pack_runs(uint32_t *out, Emitter em, const SubDe
     {
         uint32_t k = k0, kmask = (1u << k0) - 1u, kbit = 1u << k0, kk1 = k0 + 1u;
         if (pb0) w.put(k0, pb);
+        // lane 0 skips the warm-up samples (their slots hold 0, they carry no code): only the first groups need the test
+        const int skip = lane == 0 ? order : 0;
 #pragma unroll 1
         for (int it = 0; it < BLK / 4; it++) {
             if (it == BLK / 8) {
@@ -1439,10 +1444,16 @@ __device__ __noinline__ Emitter pack_runs(uint32_t *out, Emitter em, const SubDe
             }
             const uint4 v = *reinterpret_cast<const uint4 *>(blk + 4 * it);
             const uint32_t u[4] = { v.x, v.y, v.z, v.w };
+            if (4 * it >= skip) {
 #pragma unroll
-            for (int i = 0; i < 4; i++)
-                if (lane != 0 || 4 * it + i >= order) w.code(u[i], k, kmask, kbit, kk1);
+                for (int i = 0; i < 4; i++) w.code(u[i], k, kmask, kbit, kk1);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+                    if (4 * it + i >= skip) w.code(u[i], k, kmask, kbit, kk1);
+            }
         }
+        w.finish();
     }
     const uint32_t nwhole = (w.wa - smem_u32(sp)) >> 2;
     if (w.nb) sp[nwhole] = w.hi;                             // the incomplete last word, own bits only

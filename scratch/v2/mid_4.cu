@@ -179,8 +179,8 @@ struct P1 {
             const int32_t d1 = x[i] - prev;
             const int32_t d2 = d1 - d1p, d3 = d2 - d2p, d4 = d3 - d3p;
             prev = x[i]; d1p = d1; d2p = d2; d3p = d3;
-            f[0] += (uint32_t)abs(x[i]); f[1] += (uint32_t)abs(d1); f[2] += (uint32_t)abs(d2);
-            f[3] += (uint32_t)abs(d3); f[4] += (uint32_t)abs(d4);
+            f[0] = __sad(x[i], 0, f[0]); f[1] = __sad(d1, 0, f[1]); f[2] = __sad(d2, 0, f[2]);      // |e| + f in one VABSDIFF each
+            f[3] = __sad(d3, 0, f[3]); f[4] = __sad(d4, 0, f[4]);
             const float cn = fmaf(twoc, c1, -c0);
             const float wv = fmaf(-wb, c1, wa);
             c0 = c1; c1 = cn;

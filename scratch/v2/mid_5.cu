@@ -30,7 +30,7 @@ struct P2 {
                 r = (int32_t)((long long)s[(4 * P + H + i) % W] - (a >> shift));
             }
             u[i] = zigzag(r);
-            if (WIDE) acc64 += (uint32_t)abs(r); else acc32 += (uint32_t)abs(r);
+            if (WIDE) acc64 += (uint32_t)abs(r); else acc32 = __sad(r, 0, acc32);
         }
         *reinterpret_cast<uint4 *>(p) = make_uint4(u[0], u[1], u[2], u[3]);
     }
