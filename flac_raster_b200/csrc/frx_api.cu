@@ -678,6 +678,11 @@ int frx_encode_tiles_host(frx_ctx *c, const frx_raster *raster_host, const frx_t
     return FRX_OK;
 }
 
+// Host buffers in, host buffers out, pipelined like the encode side: the tiles are cut into groups of consecutive tiles (at
+// least FRX_HOST_GROUP_BYTES of compressed bytes, extended while the next tile's output block interleaves with the group's);
+// while group k is decoded, the bytes of the groups behind it are still arriving and the rasters of group k-1 are already
+// leaving, each on its own stream.  Output ranges of different groups may overlap (tiles of one raster): copies run in group
+// order, so every element's last copy is made after the group that owns it has finished.
 int frx_decode_tiles_host(frx_ctx *c, const uint8_t *bytes_host, uint64_t n_bytes, const frx_dtile *tiles, int32_t n_tiles,
                           const uint32_t *frame_size_host, int32_t blocksize, int32_t out_dtype, int32_t pcm_mode, void *out_host,
                           uint64_t out_elems, int32_t *tile_status_host) {
@@ -685,32 +690,80 @@ int frx_decode_tiles_host(frx_ctx *c, const uint8_t *bytes_host, uint64_t n_byte
     if (!bytes_host || !out_host || !tiles || n_tiles <= 0) return set_err(FRX_E_INVALID, "NULL argument");
     if (out_dtype < FRX_U8 || out_dtype > FRX_F32) return set_err(FRX_E_INVALID, "bad out_dtype %d", out_dtype);
     CK(cudaSetDevice(c->device));
-    cudaStream_t st = 0;
+    for (int i = 0; i < 3; i++) if (!c->hs[i]) CK(cudaStreamCreateWithFlags(&c->hs[i], cudaStreamNonBlocking));
+    cudaStream_t s_in = c->hs[0], s_cmp = c->hs[1], s_out = c->hs[2];
     const size_t esz = (size_t)frx_dtype_size(out_dtype);
     uint64_t nfs = 0;
-    for (int i = 0; i < n_tiles; i++)
-        if (tiles[i].first_frame != 0xFFFFFFFFu && (uint64_t)tiles[i].first_frame + tiles[i].n_frames > nfs) nfs = (uint64_t)tiles[i].first_frame + tiles[i].n_frames;
+    for (int i = 0; i < n_tiles; i++) {
+        const frx_dtile &t = tiles[i];
+        if (t.first_frame != 0xFFFFFFFFu && (uint64_t)t.first_frame + t.n_frames > nfs) nfs = (uint64_t)t.first_frame + t.n_frames;
+        if (t.byte_offset > n_bytes || t.byte_size > n_bytes - t.byte_offset) return set_err(FRX_E_INVALID, "tile %d: byte range outside the buffer", i);
+        if (t.channels < 1 || t.h <= 0 || t.w <= 0 || t.out_band_stride < 0 || t.out_row_stride < 0) return set_err(FRX_E_INVALID, "tile %d: bad geometry", i);
+    }
+    if (nfs && !frame_size_host) return set_err(FRX_E_INVALID, "frame_size_host is NULL");
     ENSURE(c->h_bytes, n_bytes + 16);
     ENSURE(c->h_out, out_elems * esz + 16);
-    ENSURE(c->h_small, sizeof(uint32_t) * (size_t)nfs + sizeof(int32_t) * (size_t)n_tiles + 64);
-    uint32_t *fs_dev = nullptr;
+    const size_t st_bytes = ((size_t)n_tiles * 4 + 63) & ~(size_t)63;
+    ENSURE(c->h_small, st_bytes + sizeof(uint32_t) * (size_t)nfs + 64);
     int32_t *status_dev = (int32_t *)c->h_small.p;
-    CK(cudaMemcpyAsync(c->h_bytes.p, bytes_host, n_bytes, cudaMemcpyHostToDevice, st));
-    if (nfs) {
-        if (!frame_size_host) return set_err(FRX_E_INVALID, "frame_size_host is NULL");
-        fs_dev = (uint32_t *)((char *)c->h_small.p + (((size_t)n_tiles * 4 + 63) & ~(size_t)63));
-        ENSURE(c->h_small, (((size_t)n_tiles * 4 + 63) & ~(size_t)63) + sizeof(uint32_t) * (size_t)nfs + 64);
-        status_dev = (int32_t *)c->h_small.p;
-        fs_dev = (uint32_t *)((char *)c->h_small.p + (((size_t)n_tiles * 4 + 63) & ~(size_t)63));
-        CK(cudaMemcpyAsync(fs_dev, frame_size_host, sizeof(uint32_t) * (size_t)nfs, cudaMemcpyHostToDevice, st));
+    uint32_t *fs_dev = nfs ? (uint32_t *)((char *)c->h_small.p + st_bytes) : nullptr;
+    // ---- groups ----
+    struct Group { int t0, t1; uint64_t b0, b1, o0, o1; };
+    auto out_last = [&](const frx_dtile &t) {
+        return t.out_offset + (uint64_t)(t.channels - 1) * (uint64_t)t.out_band_stride + (uint64_t)(t.h - 1) * (uint64_t)t.out_row_stride + (uint64_t)t.w;
+    };
+    std::vector<Group> groups;
+    {
+        // a decode launch costs a frame time (~3 ms: a frame is decoded by one lane) however few frames it holds, so the groups are
+        // large: a handful per call is enough to overlap the copies, which are what bounds this entry point
+        uint64_t group_bytes = 192ull << 20;
+        if (const char *e = getenv("FRX_HOST_GROUP_BYTES")) { const long long v = atoll(e); if (v > 0) group_bytes = (uint64_t)v; }
+        int t0 = 0;
+        while (t0 < n_tiles) {
+            Group g = { t0, t0, tiles[t0].byte_offset, tiles[t0].byte_offset + tiles[t0].byte_size, tiles[t0].out_offset, out_last(tiles[t0]) };
+            uint64_t bytes = 0;
+            int t = t0;
+            while (t < n_tiles) {
+                const uint64_t o0 = tiles[t].out_offset, o1 = out_last(tiles[t]);
+                const bool interleaved = o0 < g.o1 && o1 > g.o0;
+                if (t > t0 && bytes >= group_bytes && !interleaved) break;
+                if (tiles[t].byte_offset < g.b0) g.b0 = tiles[t].byte_offset;
+                if (tiles[t].byte_offset + tiles[t].byte_size > g.b1) g.b1 = tiles[t].byte_offset + tiles[t].byte_size;
+                if (o0 < g.o0) g.o0 = o0;
+                if (o1 > g.o1) g.o1 = o1;
+                bytes += tiles[t].byte_size;
+                t++;
+            }
+            g.t1 = t;
+            if (g.o1 > out_elems) return set_err(FRX_E_INVALID, "tile output blocks end at element %llu, beyond the %llu the output holds",
+                                                  (unsigned long long)g.o1, (unsigned long long)out_elems);
+            groups.push_back(g);
+            t0 = t;
+        }
     }
-    int rc = decode_core(c, (const uint8_t *)c->h_bytes.p, n_bytes, tiles, n_tiles, fs_dev, blocksize, out_dtype, pcm_mode, c->h_out.p,
-                         status_dev, st, out_elems);
-    if (rc) return rc;
-    CK(cudaMemcpyAsync(out_host, c->h_out.p, out_elems * esz, cudaMemcpyDeviceToHost, st));
+    const int ng = (int)groups.size();
+    while ((int)c->hev.size() < 2 * ng) { cudaEvent_t e; CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); c->hev.push_back(e); }
+    if (nfs) CK(cudaMemcpyAsync(fs_dev, frame_size_host, sizeof(uint32_t) * (size_t)nfs, cudaMemcpyHostToDevice, s_in));
+    for (int k = 0; k < ng; k++) {      // copy-in of every group's byte range, queued up front on its own stream
+        const Group &g = groups[k];
+        CK(cudaMemcpyAsync((uint8_t *)c->h_bytes.p + g.b0, bytes_host + g.b0, g.b1 - g.b0, cudaMemcpyHostToDevice, s_in));
+        CK(cudaEventRecord(c->hev[k], s_in));
+    }
+    for (int k = 0; k < ng; k++) {
+        const Group &g = groups[k];
+        CK(cudaStreamWaitEvent(s_cmp, c->hev[k], 0));
+        // (decode_core synchronises its stream once while staging the tile tables: group k-1 is finished after it)
+        int rc = decode_core(c, (const uint8_t *)c->h_bytes.p, n_bytes, tiles + g.t0, g.t1 - g.t0, fs_dev, blocksize, out_dtype, pcm_mode, c->h_out.p,
+                             status_dev + g.t0, s_cmp, out_elems);
+        if (rc) { cudaStreamSynchronize(s_in); cudaStreamSynchronize(s_out); return rc; }
+        CK(cudaEventRecord(c->hev[ng + k], s_cmp));
+        CK(cudaStreamWaitEvent(s_out, c->hev[ng + k], 0));
+        CK(cudaMemcpyAsync((char *)out_host + g.o0 * esz, (const char *)c->h_out.p + g.o0 * esz, (g.o1 - g.o0) * esz, cudaMemcpyDeviceToHost, s_out));
+    }
     std::vector<int32_t> status(n_tiles);
-    CK(cudaMemcpyAsync(status.data(), status_dev, sizeof(int32_t) * n_tiles, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
+    CK(cudaMemcpyAsync(status.data(), status_dev, sizeof(int32_t) * n_tiles, cudaMemcpyDeviceToHost, s_out));
+    CK(cudaStreamSynchronize(s_out));
+    CK(cudaStreamSynchronize(s_in));
     int worst = 0;
     for (int i = 0; i < n_tiles; i++) {
         if (tile_status_host) tile_status_host[i] = status[i];

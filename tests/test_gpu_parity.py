@@ -320,3 +320,40 @@ def test_tile_md5_matches_hashlib(codec, golden, name, tile, mode):
         pcm, bps, *_ = (quant.reference_pcm(block) if mode == "reference" else lossless_pcm(block))
         want = hashlib.md5(pcm.astype("<i2" if bps == 16 else "<i4").tobytes()).digest()
         assert bytes(sig) == want, (name, (r0, c0, h, w))
+
+
+def test_host_decode_pipeline_groups_equal_single_call(codec, monkeypatch):
+    """frx_decode_tiles_host cuts the tiles into groups that overlap copy-in, decode and copy-out; however the groups fall --
+    with packed outputs or with tiles written into one raster, where the output ranges of neighbouring groups interleave --
+    the rasters must equal the device path's."""
+    import torch
+    from flac_raster_b200 import synth
+    from flac_raster_b200.codec import make_dtiles
+    H, W = 700, 900
+    dev = synth.dem_f32(H, W, seed=6)
+    tiles = tiles_for(synth.to_numpy(dev), 256, "all")
+    res, data, toff, tsize, mm, fsize = _encode(codec, synth.to_numpy(dev), tiles)
+    packed, mosaic, ff, oe = [], [], 0, 0
+    for i, (r0, c0, h, w, b0, nch) in enumerate(tiles):
+        nfr = (h * w + 4095) // 4096
+        base = dict(byte_offset=toff[i], byte_size=tsize[i], h=h, w=w, channels=1, bps=res.bps, dmin=mm[i, 0], dmax=mm[i, 1], first_frame=ff, n_frames=nfr)
+        packed.append(dict(base, out_offset=oe, out_band_stride=h * w, out_row_stride=w))
+        mosaic.append(dict(base, out_offset=r0 * W + c0, out_band_stride=H * W, out_row_stride=W))
+        ff += nfr; oe += h * w
+    want_m = torch.zeros(H * W, dtype=torch.float32, device="cuda")
+    st = codec.decode_tiles(res.bytes, make_dtiles(mosaic), want_m, out_dtype="float32", frame_size=res.frame_size, n_bytes=len(data))
+    torch.cuda.synchronize()
+    assert not st.cpu().numpy().any()
+    want_m = want_m.cpu().numpy()
+    fs = fsize.astype(np.uint32)
+    for group_bytes in ("1", "200000", "1000000000"):
+        monkeypatch.setenv("FRX_HOST_GROUP_BYTES", group_bytes)
+        out = np.full(H * W, np.nan, dtype=np.float32)
+        assert not codec.decode_tiles_host(data, make_dtiles(mosaic), out, frame_size=fs).any()
+        assert np.array_equal(out, want_m)
+        outp = np.full(oe, np.nan, dtype=np.float32)
+        assert not codec.decode_tiles_host(data, make_dtiles(packed), outp, frame_size=fs).any()
+        for e, m in zip(packed, mosaic):
+            r0, c0 = divmod(m["out_offset"], W)
+            assert np.array_equal(outp[e["out_offset"]:e["out_offset"] + e["h"] * e["w"]].reshape(e["h"], e["w"]),
+                                  want_m.reshape(H, W)[r0:r0 + e["h"], c0:c0 + e["w"]])
