@@ -19,6 +19,7 @@ tail = tail.replace(old, """size_t frx_enc_smem_bytes(int frame_words, int dtype
     (void)frame_words; (void)dtype;
     return 2048 + (size_t)ENC_WARPS * WARP_BYTES;
 }
+int frx_enc_warps_per_cta() { return ENC_WARPS; }
 
 """)
 old = tail[tail.index("template <bool WIDE, int HISTN>\nstatic cudaError_t launch_encode_t"):tail.index("cudaError_t frx_launch_encode(")]

@@ -388,3 +388,20 @@ __device__ __forceinline__ void copy_words_out(uint8_t *dst, const uint32_t *bit
         dst[b] = (uint8_t)((bits[b >> 2] >> (24 - 8 * (b & 3))) & 0xFFu);
     }
 }
+// a finished frame from the warp's slot (16-byte aligned, global memory, written by this warp) to its final place (any byte
+// alignment): aligned 32-bit stores, every destination word funnel-shifted out of two slot words
+__device__ __noinline__ void copy_slot_out(uint8_t *dst, const uint8_t *slot, uint32_t nbytes, int lane) {
+    __syncwarp();
+    const uint32_t head = min(nbytes, (uint32_t)((4u - (uint32_t)((uintptr_t)dst & 3u)) & 3u));
+    if (lane < (int)head) dst[lane] = __ldcg(slot + lane);
+    const uint32_t nwords = (nbytes - head) >> 2;
+    uint32_t *dw = reinterpret_cast<uint32_t *>(dst + head);
+    const uint32_t *sw = reinterpret_cast<const uint32_t *>(slot);
+    const uint32_t sh8 = head * 8u;
+    for (uint32_t j = lane; j < nwords; j += 32) {
+        const uint32_t w0 = __ldcg(sw + j), w1 = head ? __ldcg(sw + j + 1) : 0u;
+        dw[j] = head ? __funnelshift_r(w0, w1, sh8) : w0;      // little-endian words: bytes [head + 4j, head + 4j + 4)
+    }
+    const uint32_t tail0 = head + (nwords << 2);
+    if (lane < (int)(nbytes - tail0)) dst[tail0 + lane] = __ldcg(slot + tail0 + lane);
+}
