@@ -34,7 +34,7 @@ struct frx_ctx {
     int device = 0;
     int sm_count = 148;
     uint64_t launches = 0;
-    Buf tiles, prefix, unit_prefix, mmraw, quant, desc, misc, xpow, crctab, fsize, foff;
+    Buf tiles, prefix, unit_prefix, mmraw, quant, desc, misc, xpow, crctab, fsize, foff, slots;
     Buf dtiles, dprefix, fpos, flen, stereo, scan_prefix, scan_tiles, ing_chunks, ing_prefix;
     Buf h_raster, h_bytes, h_small, h_out;  // device staging for the *_host entry points
     int xpow_L = -1;
@@ -127,7 +127,7 @@ void frx_ctx_destroy(frx_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     Buf *all[] = { &c->tiles, &c->prefix, &c->unit_prefix, &c->mmraw, &c->quant, &c->desc, &c->misc, &c->xpow,
-                   &c->crctab, &c->fsize, &c->foff, &c->dtiles, &c->dprefix, &c->fpos, &c->flen, &c->stereo, &c->scan_prefix, &c->scan_tiles, &c->ing_chunks, &c->ing_prefix,
+                   &c->crctab, &c->fsize, &c->foff, &c->slots, &c->dtiles, &c->dprefix, &c->fpos, &c->flen, &c->stereo, &c->scan_prefix, &c->scan_tiles, &c->ing_chunks, &c->ing_prefix,
                    &c->h_raster, &c->h_bytes, &c->h_small, &c->h_out };
     for (Buf *b : all) if (b->p) cudaFree(b->p);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
@@ -327,6 +327,16 @@ int frx_encode_tiles(frx_ctx *c, const frx_raster *raster_dev, const frx_tile *t
     {
         static const int lvl_ms[9] = { 0, 1, 1, 0, 1, 1, 1, 1, 1 };   // libFLAC presets with mid-side coding (dump:6926-6934)
         a.stereo = (lvl_ms[p->compression_level] && prep.bps <= 16) ? 1 : 0;
+    }
+    {
+        // two slots per resident frame warp (streamed and parked frames, frx_encode.cu): each holds the largest frame of this
+        // call (all channels verbatim + headers), 16-byte multiples
+        const uint32_t stride = (uint32_t)((((uint64_t)prep.max_channels * ((uint64_t)p->blocksize * 4u + 16u) + 64u) + 15u) & ~15ull);
+        ENSURE(c->slots, 2u * (size_t)stride * (size_t)c->sm_count * (size_t)frx_enc_warps_per_cta());
+        a.slots = (uint8_t *)c->slots.p; a.slot_stride = stride;
+        // per channel: four barriers in the analysis, one after packing; a stereo frame analyses four virtual channels
+        a.bars_per_frame = 5 * prep.max_channels;
+        if (a.stereo && a.bars_per_frame < 18) a.bars_per_frame = 18;
     }
     CK(cudaEventRecord(c->ev[0], st));
     CK(frx_launch_encode(a, r.dtype, c->sm_count, st));

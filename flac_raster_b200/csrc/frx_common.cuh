@@ -48,7 +48,11 @@ struct FrxQuant {
     double rcp;             // RN(1 / range): the 16-bit dtypes divide by multiplying (frx_div16)
     int degenerate;         // dmax == dmin  -> zeros (converter.py:73-75)
     int flags;              // FRX_QF_*
+    int irange;             // FRX_QF_INT16: max - min as an integer, 1..65535
+    float rcpf;             // FRX_QF_INT16: RZ(1 / irange) in float32
 };
+#define FRX_QF_INT16 2      // 8/16-bit dtypes whose max - min and x - min do not wrap in the raster dtype: 0 <= x - min <= range <=
+                            // 65535, the case the integer form of the quantiser is proven for (oracle/quant16_check.c)
 #define FRX_QF_F32_SAFE 1   // float32 reference mode: no NaN and |x| * 8388607 < 2^31 for the whole stream, so the
                             // x86 "integer indefinite" check of frx_trunc_i32f can never fire
 
@@ -78,11 +82,29 @@ __device__ __forceinline__ double frx_div16(double a, double b, double rcp) {
     return __fma_rn(r, rcp, y0);
 }
 
+// Integer form of the 16-bit float64 chain of frx_quant_ref (only under FRX_QF_INT16): with v = x - min and R = max - min the
+// chain's value is N / R for N = (2 v - R) * 32767 (|N| < 2^31) up to rounding errors far smaller than 1 / R, so truncating
+// the exact quotient gives the same integer unless N / R is itself an integer -- then (quotients 0 and +-32767 apart) the
+// chain decides, and `exact` is set.  oracle/quant16_check.c proves both statements over all 2^31 (R, v) pairs, and that
+// the float32 product below is floor(|N| / R) or one less.
+template <int DT>
+__device__ __forceinline__ int32_t frx_quant16_int(typename FrxElem<DT>::T d, const FrxQuant &q, bool &exact) {
+    typedef typename FrxElem<DT>::T T;
+    const int iv = (int)(T)((T)d - (T)q.imin);
+    const int N = (2 * iv - q.irange) * 32767;
+    const uint32_t M = (uint32_t)abs(N), R = (uint32_t)q.irange;
+    uint32_t qh = __float2uint_rz(__fmul_rz(__uint2float_rz(M), q.rcpf));
+    uint32_t rem = M - qh * R;
+    if (rem >= R) { qh++; rem -= R; }
+    exact |= rem == 0u && qh - 1u < 32766u;
+    return N < 0 ? -(int32_t)qh : (int32_t)qh;
+}
+
 // K1 quantiser, FRX_PCM_REFERENCE: bit-exact restatement of
 // RasterFLACConverter._normalize_to_audio (converter.py:56-86) followed by pyFLAC's
 // astype(int32) (dump:1994).  Every floating-point op is a separately rounded IEEE op.
 template <int DT>
-__device__ __forceinline__ int32_t frx_quant_ref(typename FrxElem<DT>::T d, const FrxQuant &q) {
+__device__ __forceinline__ int32_t frx_quant_ref_chain(typename FrxElem<DT>::T d, const FrxQuant &q) {
     if (DT == FRX_F32) {
         // float data "as-is"; float32 array * python int 8388607 stays float32 (NEP 50)
         float y = __fmul_rn((float)d, 8388607.0f);
@@ -99,6 +121,15 @@ __device__ __forceinline__ int32_t frx_quant_ref(typename FrxElem<DT>::T d, cons
             return frx_trunc_i32(__dmul_rn(norm, 8388607.0));
         }
     }
+}
+template <int DT>
+__device__ __forceinline__ int32_t frx_quant_ref(typename FrxElem<DT>::T d, const FrxQuant &q) {
+    if ((DT == FRX_U8 || DT == FRX_I16 || DT == FRX_U16) && (q.flags & FRX_QF_INT16)) {
+        bool exact = false;
+        const int32_t r = frx_quant16_int<DT>(d, q, exact);
+        if (!exact) return r;
+    }
+    return frx_quant_ref_chain<DT>(d, q);
 }
 
 // FRX_PCM_LOSSLESS: identity mapping into a signed PCM of the effective width.

@@ -154,6 +154,11 @@ __global__ void frx_quant_setup_kernel(const MinMaxRaw *mm, FrxQuant *q, int n, 
         }
     }
     o.rcp = o.range != 0.0 ? 1.0 / o.range : 0.0;   // correctly rounded (IEEE division)
+    o.irange = 0; o.rcpf = 0.f;
+    if ((dtype == FRX_U8 || dtype == FRX_U16 || dtype == FRX_I16) && !o.degenerate && o.imax - o.imin <= (dtype == FRX_I16 ? 32767 : 65535)) {
+        // neither max - min nor any x - min wraps in the raster dtype: the integer form of the quantiser applies
+        o.irange = (int)(o.imax - o.imin); o.rcpf = __fdiv_rz(1.0f, (float)o.irange); o.flags |= FRX_QF_INT16;
+    }
     q[i] = o;
 }
 
@@ -185,7 +190,18 @@ __global__ void frx_tile_index_kernel(const uint32_t *frame_prefix, const uint32
 // exact bit count is known, so the byte offset arrives while the frame is being packed and checksummed.
 // ==========================================================================================
 #define FULLMASK 0xFFFFFFFFu
+#ifdef FRX_DBG
+// development counters (cycles, events) summed over all frame warps; read and cleared by frx_debug_read
+__device__ unsigned long long g_frx_dbg[16];
+#define DBG_ADD(i, v) do { if (lane == 0) atomicAdd(&g_frx_dbg[i], (unsigned long long)(v)); } while (0)
+#define DBG_CLK() clock64()
+#else
+#define DBG_ADD(i, v) do { } while (0)
+#define DBG_CLK() 0ll
+#endif
+#ifndef ENC_WARPS
 #define ENC_WARPS 12
+#endif
 #define ENC_CTA (ENC_WARPS * 32)
 #define SLACK_W 64                                   // words in front of the PCM area: the packed stream runs ahead by its headers
 #define BLK 128                                      // samples per lane block of a full frame = samples per pack chunk
@@ -193,6 +209,23 @@ __global__ void frx_tile_index_kernel(const uint32_t *frame_prefix, const uint32
 #define PIDX(g) ((g) + 4 * ((g) >> 7))               // word of sample g inside the PCM area
 #define PCM_W (FRX_MAX_BLOCK + 4 * (FRX_MAX_BLOCK / BLK))
 #define WBUF_W (SLACK_W + PCM_W + 12)
+// Phase alignment (kernels with ALIGNED = true, see frx_encode_kernel): the frame warps of a CTA are split into groups of
+// ALIGN_GROUP warps that take their frames together and meet again at the phase boundaries of the frame (one named barrier
+// per group).  Every warp of a group passes exactly EncArgs.bars_per_frame barriers per frame, whatever path its frame takes.
+#ifndef ALIGN_GROUP
+#define ALIGN_GROUP 6
+#endif
+static_assert(ENC_WARPS % ALIGN_GROUP == 0, "groups must tile the CTA");
+__device__ __forceinline__ void group_bar() {
+    asm volatile("bar.sync %0, %1;" :: "r"(1 + (int)(threadIdx.x >> 5) / ALIGN_GROUP), "r"(ALIGN_GROUP * 32) : "memory");
+}
+__device__ __forceinline__ bool group_or(bool pred) {
+    int r;
+    asm volatile("{ .reg .pred p, q; setp.ne.s32 q, %3, 0; bar.red.or.pred p, %1, %2, q; selp.s32 %0, 1, 0, p; }"
+                 : "=r"(r) : "r"(1 + (int)(threadIdx.x >> 5) / ALIGN_GROUP), "r"(ALIGN_GROUP * 32), "r"((int)pred) : "memory");
+    return r != 0;
+}
+#define ALIGN_BAR(n) do { if (ALIGNED) { group_bar(); (n)++; } } while (0)
 
 __device__ __forceinline__ uint64_t warp_sum_u64(uint64_t v) {
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULLMASK, v, o);
@@ -435,7 +468,8 @@ __device__ __forceinline__ int32_t quant_one(typename FrxElem<DT>::T v, const Fr
 // in-place expansion of one block: raw elements sit end-aligned in the block's first 512 bytes + 16, PCM words grow from
 // its start (a 16-byte read is always ahead of the words written so far).  FULL: all 128 samples are valid.
 // F32SAFE: float32 reference mode with the stream-wide guarantee that x * 8388607 fits int32 (no per-sample range check).
-template <int DT, bool FULL, bool F32SAFE>
+// INT16: 8/16-bit reference mode of a tile under FRX_QF_INT16 (frx_common.cuh).
+template <int DT, bool FULL, bool F32SAFE, bool INT16 = false>
 __device__ __forceinline__ void quantize_block_t(uint32_t *blk, const FrxQuant &qz, int mode, int nvalid, uint32_t &orv, uint32_t &ora) {
     typedef typename FrxElem<DT>::T T;
     constexpr int ESZ = (int)sizeof(T);
@@ -447,9 +481,21 @@ __device__ __forceinline__ void quantize_block_t(uint32_t *blk, const FrxQuant &
         T e[EPV];
         memcpy(e, &v, 16);
         int32_t x[EPV];
+        if (INT16) {
+            // integer form of the 16-bit quantiser for all the elements of the load, one (rare) branch for those whose
+            // quotient is exact and needs the float64 chain
+            bool exact = false;
+#pragma unroll
+            for (int i = 0; i < EPV; i++) x[i] = frx_quant16_int<DT>(e[i], qz, exact);
+            if (exact) {
+#pragma unroll
+                for (int i = 0; i < EPV; i++) x[i] = frx_quant_ref_chain<DT>(e[i], qz);
+            }
+        }
 #pragma unroll
         for (int i = 0; i < EPV; i++) {
-            if (F32SAFE) x[i] = __float2int_rz(__fmul_rn((float)e[i], 8388607.0f));
+            if (INT16) { }
+            else if (F32SAFE) x[i] = __float2int_rz(__fmul_rn((float)e[i], 8388607.0f));
             else x[i] = quant_one<DT>(e[i], qz, mode);
             if (!FULL && t * EPV + i >= nvalid) x[i] = 0;
             orv |= (uint32_t)x[i];
@@ -464,6 +510,8 @@ template <int DT>
 __device__ __forceinline__ void quantize_block(uint32_t *blk, const FrxQuant &qz, int mode, int nvalid, uint32_t &orv, uint32_t &ora) {
     if (nvalid == BLK) {
         if (DT == FRX_F32 && mode == FRX_PCM_REFERENCE && (qz.flags & FRX_QF_F32_SAFE)) quantize_block_t<DT, true, DT == FRX_F32>(blk, qz, mode, nvalid, orv, ora);
+        else if ((DT == FRX_U8 || DT == FRX_I16 || DT == FRX_U16) && mode == FRX_PCM_REFERENCE && (qz.flags & FRX_QF_INT16))
+            quantize_block_t<DT, true, false, DT == FRX_U8 || DT == FRX_I16 || DT == FRX_U16>(blk, qz, mode, nvalid, orv, ora);
         else quantize_block_t<DT, true, false>(blk, qz, mode, nvalid, orv, ora);
     } else quantize_block_t<DT, false, false>(blk, qz, mode, nvalid, orv, ora);
 }
@@ -513,9 +561,22 @@ __device__ __forceinline__ void load_ms_block(const EncArgs &a, const FrameDesc 
             const uint4 vl = __ldg(reinterpret_cast<const uint4 *>(L + e)), vr = __ldg(reinterpret_cast<const uint4 *>(R + e));
             T el[EPV], er[EPV];
             memcpy(el, &vl, 16); memcpy(er, &vr, 16);
+            int32_t ql[EPV], qr[EPV];
+            if ((DT == FRX_U8 || DT == FRX_I16 || DT == FRX_U16) && a.pcm_mode == FRX_PCM_REFERENCE && (d.q.flags & FRX_QF_INT16)) {
+                bool exact = false;
+#pragma unroll
+                for (int j = 0; j < EPV; j++) { ql[j] = frx_quant16_int<DT>(el[j], d.q, exact); qr[j] = frx_quant16_int<DT>(er[j], d.q, exact); }
+                if (exact) {
+#pragma unroll
+                    for (int j = 0; j < EPV; j++) { ql[j] = frx_quant_ref_chain<DT>(el[j], d.q); qr[j] = frx_quant_ref_chain<DT>(er[j], d.q); }
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < EPV; j++) { ql[j] = quant_one<DT>(el[j], d.q, a.pcm_mode); qr[j] = quant_one<DT>(er[j], d.q, a.pcm_mode); }
+            }
 #pragma unroll
             for (int j = 0; j < EPV; j++) {
-                const int32_t l = quant_one<DT>(el[j], d.q, a.pcm_mode), r = quant_one<DT>(er[j], d.q, a.pcm_mode);
+                const int32_t l = ql[j], r = qr[j];
                 x[j] = vch == 8 ? ((l + r) >> 1) : (l - r);
                 if (i + j >= nvalid) x[j] = 0;
                 orv |= (uint32_t)x[j];
@@ -1570,6 +1631,31 @@ __device__ __forceinline__ void copy_words_out(uint8_t *dst, const uint32_t *bit
         dst[b] = (uint8_t)((bits[b >> 2] >> (24 - 8 * (b & 3))) & 0xFFu);
     }
 }
+// a finished frame from the warp's slot (16-byte aligned, global memory, written by this warp) to its final place (any byte
+// alignment): aligned 32-bit stores, every destination word funnel-shifted out of two slot words
+__device__ __noinline__ void copy_slot_out(uint8_t *dst, const uint8_t *slot, uint32_t nbytes, int lane) {
+    __syncwarp();
+    const uint32_t head = min(nbytes, (uint32_t)((4u - (uint32_t)((uintptr_t)dst & 3u)) & 3u));
+    if (lane < (int)head) dst[lane] = __ldcg(slot + lane);
+    const uint32_t nwords = (nbytes - head) >> 2;
+    uint32_t *dw = reinterpret_cast<uint32_t *>(dst + head);
+    const uint32_t *sw = reinterpret_cast<const uint32_t *>(slot);
+    const uint32_t sh8 = head * 8u;
+    uint32_t j = lane;
+    for (; j + 7u * 32u < nwords; j += 8u * 32u) {            // eight independent L2 round trips in flight per lane
+        uint32_t w0[8], w1[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) { w0[k] = __ldcg(sw + j + 32 * k); w1[k] = head ? __ldcg(sw + j + 32 * k + 1) : 0u; }
+#pragma unroll
+        for (int k = 0; k < 8; k++) dw[j + 32 * k] = head ? __funnelshift_r(w0[k], w1[k], sh8) : w0[k];
+    }
+    for (; j < nwords; j += 32) {
+        const uint32_t w0 = __ldcg(sw + j), w1 = head ? __ldcg(sw + j + 1) : 0u;
+        dw[j] = head ? __funnelshift_r(w0, w1, sh8) : w0;      // little-endian words: bytes [head + 4j, head + 4j + 4)
+    }
+    const uint32_t tail0 = head + (nwords << 2);
+    if (lane < (int)(nbytes - tail0)) dst[tail0 + lane] = __ldcg(slot + tail0 + lane);
+}
 
 // ==========================================================================================
 // per-subframe search: CONSTANT / VERBATIM / best FIXED order / LPC, each Rice-coded candidate costed from its partition
@@ -1616,15 +1702,19 @@ __device__ __forceinline__ bool residuals_inplace(WarpSh &ws, uint32_t *buf, con
 }
 
 template <bool WIDE, int H>
-__device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint32_t *buf, int vch, int ci, uint32_t startbits, uint32_t &phase,
+__device__ __noinline__ int analyse_channel(const EncArgs &a, WarpSh &ws, uint32_t *buf, int vch, int ci, uint32_t startbits, uint32_t &phase,
                                              BufState &bs, int lane) {
     SubDec &d = ws.dec[ci];
     const FrameDesc &fd = ws.fd;
     uint32_t *pcm = buf + SLACK_W;
     const int nsamp = fd.nsamp;
     const bool full = nsamp == FRX_MAX_BLOCK;
+    const long long t_0 = DBG_CLK();
+    constexpr bool ALIGNED = !WIDE;
+    int nbar = 0;                     // group barriers passed (phase alignment of the frame warps, see the kernel)
     const uint2 st = load_channel(a, ws, buf, vch, phase, lane);
     const uint32_t orv = st.x, ora = st.y;
+    DBG_ADD(5, DBG_CLK() - t_0); DBG_ADD(15, 1);
     const int wasted = orv ? (__ffs((int)orv) - 1) : 0;
     if (wasted) shift_wasted(pcm, nsamp, wasted, lane);
     const int magbits = 32 - __clz((int)(ora >> wasted));          // |sample| <= 2^magbits
@@ -1641,7 +1731,9 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
     }
     __syncwarp();
 
+    ALIGN_BAR(nbar);
     // ---- K2 + K3 ----
+    const long long t_1 = DBG_CLK();
     uint64_t tot[5];
     uint64_t fsl[5][2];
     uint32_t badmask = 0;
@@ -1676,11 +1768,13 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
         for (int k = 0; k <= H; k++) autoc[k] = ws.g_ac[k];
         badmask = ws.g_bad;
     }
+    DBG_ADD(6, DBG_CLK() - t_1);
     if (tot[1] == 0 && !(badmask & 2u)) {     // sum |s[g] - s[g-1]| == 0  <=>  all samples equal
         if (lane == 0) { d.type = 0; d.bits = 8u + (uint32_t)wasted + (uint32_t)sbps; }
         __syncwarp();
-        return;
+        return nbar;
     }
+    ALIGN_BAR(nbar);
     int fixed_order = -1;
     if (nsamp > 4) {
         uint64_t bestv = ~0ull;
@@ -1691,7 +1785,10 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
     // ---- K4 ----
     LpcChoice lc;
     lc.ok = 0; lc.order = 0; lc.shift = 0; lc.precision = 0; lc.narrow = 1;
+    const long long t_2 = DBG_CLK();
     if (max_lpc > 0 && nsamp > 4) lc = lpc_design<WIDE, H>(ws, autoc, max_lpc, nsamp, sbps, a.qlp_precision, magbits, lane);
+    DBG_ADD(7, DBG_CLK() - t_2);
+    const long long t_3 = DBG_CLK();
 
     unsigned long long *bins = reinterpret_cast<unsigned long long *>(buf);   // generic path: 32 sums in the slack words
     const int Fg = po_max > 5 ? 5 : po_max;
@@ -1718,6 +1815,9 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
         const uint64_t b = 8ull + wasted + (uint64_t)fixed_order * sbps + rf.bits;
         if (b < best_bits) { best_bits = b; type = 2; order = fixed_order; po = rf.po; rice2 = rf.rice2; cand = 0; }
     }
+    DBG_ADD(8, DBG_CLK() - t_3);
+    const long long t_4 = DBG_CLK();
+    ALIGN_BAR(nbar);
     // ---- LPC candidate: residuals in place (the usual winner), cost from their partition sums ----
     if (lc.ok) {
         if (lane == 0) { d.type = 3; d.order = (uint8_t)lc.order; d.shift = lc.shift; d.narrow = (uint8_t)lc.narrow; d.precision = (uint8_t)lc.precision; }
@@ -1738,11 +1838,14 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
             if (b < best_bits) { best_bits = b; type = 3; order = lc.order; po = rl.po; rice2 = rl.rice2; cand = 1; }
         }
     }
+    DBG_ADD(9, DBG_CLK() - t_4);
+    ALIGN_BAR(nbar);
     if (type == 1) {
         if (lane == 0) { d.type = 1; d.order = 0; }
         __syncwarp();
-        return;
+        return nbar;
     }
+    const long long t_5 = DBG_CLK();
     // ---- record the winner; make the buffer hold its residuals ----
     if (lane == 0) {
         d.type = (uint8_t)type; d.order = (uint8_t)order; d.po = (uint8_t)po; d.rice2 = rice2 ? 1 : 0;
@@ -1760,6 +1863,8 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
         (void)residuals_inplace<WIDE, H>(ws, buf, d, nsamp, nullptr, psf, lane, x0, x1);
         bs.kind = BUF_RES; bs.type = 2; bs.order = order;
     }
+    DBG_ADD(10, DBG_CLK() - t_5);
+    const long long t_6 = DBG_CLK();
     // ---- exact size ----
     const uint32_t pb = rice2 ? 5u : 4u;
     const uint32_t hb = 8u + (uint32_t)wasted + (uint32_t)order * (uint32_t)sbps + (type == 3 ? 9u + (uint32_t)order * (uint32_t)lc.precision : 0u) + 6u;
@@ -1790,6 +1895,8 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
         if (lane == 0) { d.type = 1; d.order = 0; d.bits = (uint32_t)verb_bits; }
     } else if (lane == 0) { d.bits = total; d.runs = runs_ok ? 1 : 0; }
     __syncwarp();
+    DBG_ADD(11, DBG_CLK() - t_6);
+    return nbar;
 }
 
 // make the buffer hold what packing subframe d needs: its PCM (CONSTANT / VERBATIM) or its residuals
@@ -1835,97 +1942,162 @@ __global__ void __launch_bounds__(ENC_CTA, 1) frx_encode_kernel(const EncArgs a)
     uint32_t phase = 0;
     int ti = 0;
     const bool stereo = a.stereo != 0;
+    // Phase alignment for the narrow kernels: with the frame warps of an SM each in a phase of its own, the 8/16-bit
+    // workloads ran 1.6-2.3x slower (instruction fetch: 18 % of the stall samples were no_instruction, all phases stretched,
+    // and the frames drifted so far apart that nearly every look-back had to wait); in step they share the instruction cache
+    // and publish their sizes together.  The wide kernels (float32 / 32-bit) lose a few per cent to the waiting at the
+    // barriers instead (their load phase is exposed), so they run free (profiles/r2_encode_experiments.md).
+    constexpr bool ALIGNED = !WIDE;
+
+    // Where the bytes go.  A frame's place in the output is the sum of the sizes of all frames in front of it (decoupled
+    // look-back over the descriptors), and a frame whose predecessors have not all published their sizes must not hold up the
+    // warp: it is PARKED in one of the warp's two slots in global memory (L2-resident) and the warp goes on to its next frame;
+    // the parked frame is sent to its final place as soon as a (non-blocking) look-back completes, at the latest when the next
+    // frame is finished -- a whole frame of slack, so that the blocking wait is practically never taken.
+    // Multi-channel frames are STREAMED: a channel is packed right after its analysis (the buffer holds one channel at a time,
+    // packing later would mean staging and predicting it a second time) and the complete words go to the current slot; the
+    // frame's size is published when its last channel has been analysed.  Single-channel frames and stereo frames (whose
+    // channel assignment needs all four analyses) run two sweeps: analyse, publish the size, pack.
+    uint8_t *slots2 = a.slots + (size_t)(blockIdx.x * ENC_WARPS + warp) * 2u * a.slot_stride;
+    int cur = 0;                          // the slot the next streamed / parked frame uses
+    bool pend = false;                    // a parked frame waits in pend_slot
+    uint32_t pend_f = 0, pend_nbytes = 0;
+    uint8_t *pend_slot = slots2;
+    LookBack plb;                         // its look-back, resumed where it stopped
+    plb.pos = -1; plb.exclusive = 0; plb.blocked = false;
+    auto lb_run = [&](LookBack &lb, bool block) -> bool {      // true: lb.exclusive is the byte offset
+        for (;;) {
+            if (lookback_step(a, lb, lane)) return true;
+            if (lb.blocked) {
+                if (!block) return false;
+                DBG_ADD(1, 1);
+                __nanosleep(100);
+            }
+        }
+    };
+    auto lb_commit = [&](uint32_t ff, uint32_t nb, uint64_t off) -> bool {     // publishes the inclusive prefix; true on overflow
+        if (lane == 0) {
+            frx_st_relaxed_u64(&a.desc[ff], (2ull << 62) | (off + (uint64_t)nb));
+            if (a.frame_offset) a.frame_offset[ff] = off;
+            if (ff == a.total_frames - 1 && a.total_bytes) *a.total_bytes = off + nb;
+        }
+        const bool ovf = off + nb > a.capacity;
+        if (ovf && lane == 0) atomicExch(a.status, FRX_E_OVERFLOW);
+        return ovf;
+    };
+    auto finish_pending = [&](bool block) {
+        const long long tl0 = DBG_CLK();
+        const bool ok = lb_run(plb, block);
+        if (block) DBG_ADD(0, DBG_CLK() - tl0);
+        if (!ok) return;
+        const bool ovf = lb_commit(pend_f, pend_nbytes, plb.exclusive);
+        const long long ts0 = DBG_CLK();
+        if (!ovf) copy_slot_out(a.bytes + plb.exclusive, pend_slot, pend_nbytes, lane);
+        DBG_ADD(2, DBG_CLK() - ts0);
+        pend = false;
+    };
 
     for (;;) {
         uint32_t f = 0;
         if (lane == 0) f = atomicAdd(a.ticket, 1u);
         f = __shfl_sync(FULLMASK, f, 0);
-        if (f >= a.total_frames) break;
+        if (ALIGNED) {
+            if (!group_or(f < a.total_frames)) break;          // the group's frames start together
+            if (f >= a.total_frames) {
+                for (int k = 0; k < a.bars_per_frame; k++) group_bar();
+                continue;
+            }
+        } else if (f >= a.total_frames) break;
+        const long long tf0 = DBG_CLK();
         build_frame_desc(a, ws.fd, f, ti, lane);
         const int nsamp = ws.fd.nsamp;
         const int n_ch = ws.fd.t.n_channels;
+        const bool two_sweeps = n_ch == 1 || (n_ch == 2 && stereo);
         BufState bs;
         bs.kind = BUF_JUNK; bs.vch = -1; bs.type = 0; bs.order = 0;
-
-        // ---- sweep 1: search every subframe, exact sizes ----
-        const int nsub = n_ch;
-        int sub0 = 0, sub1 = 1;     // decision records of the first two subframes (the stereo choice permutes them)
-        if (n_ch == 2 && stereo) {
-            // left, right, mid, side; the cheapest of L/R, L/S, S/R, M/S (libFLAC's exhaustive stereo decision)
-            analyse_channel<WIDE, H>(a, ws, buf, 0, 0, ws.fd.hdr_bits, phase, bs, lane);
-            analyse_channel<WIDE, H>(a, ws, buf, 1, 1, ws.fd.hdr_bits, phase, bs, lane);
-            analyse_channel<WIDE, H>(a, ws, buf, 8, 2, ws.fd.hdr_bits, phase, bs, lane);
-            analyse_channel<WIDE, H>(a, ws, buf, 9, 3, ws.fd.hdr_bits, phase, bs, lane);
-            const uint32_t bL = ws.dec[0].bits, bR = ws.dec[1].bits, bM = ws.dec[2].bits, bS = ws.dec[3].bits;
-            uint32_t best = bL + bR; int ca = 1; sub0 = 0; sub1 = 1;
-            if (bL + bS < best) { best = bL + bS; ca = 8; sub0 = 0; sub1 = 3; }
-            if (bR + bS < best) { best = bR + bS; ca = 9; sub0 = 3; sub1 = 1; }
-            if (bM + bS < best) { best = bM + bS; ca = 10; sub0 = 2; sub1 = 3; }
-            if (lane == 0) make_frame_header(a, ws.fd, ca);
-            __syncwarp();
-        } else {
-            for (int c = 0; c < n_ch; c++)
-                analyse_channel<WIDE, H>(a, ws, buf, c, c, c == 0 ? ws.fd.hdr_bits : 32u, phase, bs, lane);
-        }
-        uint32_t frame_bits = ws.fd.hdr_bits;
-        for (int c = 0; c < nsub; c++) frame_bits += ws.dec[c == 0 ? sub0 : (c == 1 ? sub1 : c)].bits;
-        const uint32_t body_bytes = (frame_bits + 7u) >> 3;
-        const uint32_t nbytes = body_bytes + 2u;
-        if (lane == 0) {
-            // the frame's size is final: publish it, the look-back of the frames behind this one can proceed
-            if (f != 0) frx_st_relaxed_u64(&a.desc[f], (1ull << 62) | (uint64_t)nbytes);
-            if (a.frame_size) a.frame_size[f] = nbytes;
-        }
-
-        // ---- sweep 2: pack ----
+        int nbar = 0;
         Emitter em;
         em.P = 0; em.carry = 0;
-        {
+        uint8_t *const slot = slots2 + (size_t)cur * a.slot_stride;
+        uint32_t done = 0;          // bytes of the frame already in the slot
+        uint32_t crc_run = 0;
+        uint32_t nbytes = 0;
+        auto emit_frame_header = [&]() {
             uint32_t val[1], len[1], zer[1] = { 0 };
             const uint32_t hbits = ws.fd.hdr_bits;
             val[0] = lane < 4 ? ws.fd.hdr[lane] : 0u;
             len[0] = (uint32_t)max(0, min(32, (int)hbits - 32 * lane));
             if (len[0] < 32u && len[0] > 0u) val[0] >>= (32u - len[0]);
             emit_fields<1>(buf, em, val, len, zer, lane);
-        }
-        bool have_off = false, overflow = false;
-        uint64_t off = 0;
-        uint32_t done = 0;          // bytes of the frame already copied out (multi-channel frames go out subframe by subframe)
-        uint32_t crc_run = 0;
-        auto get_offset = [&]() {
-            LookBack lb;
-            lb.pos = (long long)f - 1; lb.exclusive = 0; lb.blocked = false;
-            while (!lookback_step(a, lb, lane)) { if (lb.blocked) __nanosleep(100); }
-            off = lb.exclusive;
+        };
+        auto publish_size = [&](uint32_t frame_bits) {
+            nbytes = ((frame_bits + 7u) >> 3) + 2u;
             if (lane == 0) {
-                frx_st_relaxed_u64(&a.desc[f], (2ull << 62) | (off + (uint64_t)nbytes));
-                if (a.frame_offset) a.frame_offset[f] = off;
-                if (f == a.total_frames - 1 && a.total_bytes) *a.total_bytes = off + nbytes;
-            }
-            have_off = true;
-            if (off + nbytes > a.capacity) {
-                overflow = true;
-                if (lane == 0) atomicExch(a.status, FRX_E_OVERFLOW);
+                // the frame's size is final: the look-back of the frames behind this one can proceed
+                if (f != 0) frx_st_relaxed_u64(&a.desc[f], (1ull << 62) | (uint64_t)nbytes);
+                if (a.frame_size) a.frame_size[f] = nbytes;
             }
         };
-        for (int c = 0; c < nsub; c++) {
-            const SubDec &d = ws.dec[c == 0 ? sub0 : (c == 1 ? sub1 : c)];
-            materialise<WIDE, H>(a, ws, buf, d, phase, bs, lane);
+        auto pack_subframe = [&](const SubDec &d) {
             em = pack_subframe_header(ws, buf, em, d, pcm, lane);
             if (d.type >= 2) em = d.runs ? pack_runs(buf, em, d, pcm, lane) : pack_rice(buf, em, d, pcm, nsamp, lane);
             else if (d.type == 1) em = pack_verbatim(buf, em, d, pcm, nsamp, lane);
             bs.kind = BUF_JUNK;                     // the packed bits now lie over the samples
-            if (c + 1 < nsub) {
-                // the next subframe needs the whole buffer: send the complete words of the stream on their way
-                if (!have_off) get_offset();
-                const uint32_t nw = em.P >> 5;
+            ALIGN_BAR(nbar);
+        };
+        auto flush_words = [&]() {                   // the next channel needs the whole buffer: the complete words go to the slot
+            const uint32_t nw = em.P >> 5;
+            __syncwarp();
+            const uint32_t cs = crc_words(a, crc_tab, buf, nw, lane);
+            crc_run = (done ? frx_gf16_mulmod(crc_run, gf16_xpow32(nw)) : 0u) ^ cs;
+            copy_words_out(slot + done, buf, nw, lane);
+            done += nw * 4u;
+            em.P &= 31u;
+            __syncwarp();
+        };
+
+        if (two_sweeps) {
+            // ---- sweep 1: search every subframe, exact sizes ----
+            int sub0 = 0, sub1 = 1;     // decision records of the two subframes (the stereo choice permutes them)
+            if (n_ch == 2) {
+                // left, right, mid, side; the cheapest of L/R, L/S, S/R, M/S (libFLAC's exhaustive stereo decision)
+                nbar += analyse_channel<WIDE, H>(a, ws, buf, 0, 0, ws.fd.hdr_bits, phase, bs, lane);
+                nbar += analyse_channel<WIDE, H>(a, ws, buf, 1, 1, ws.fd.hdr_bits, phase, bs, lane);
+                if (pend) finish_pending(false);
+                nbar += analyse_channel<WIDE, H>(a, ws, buf, 8, 2, ws.fd.hdr_bits, phase, bs, lane);
+                nbar += analyse_channel<WIDE, H>(a, ws, buf, 9, 3, ws.fd.hdr_bits, phase, bs, lane);
+                const uint32_t bL = ws.dec[0].bits, bR = ws.dec[1].bits, bM = ws.dec[2].bits, bS = ws.dec[3].bits;
+                uint32_t best = bL + bR; int ca = 1; sub0 = 0; sub1 = 1;
+                if (bL + bS < best) { best = bL + bS; ca = 8; sub0 = 0; sub1 = 3; }
+                if (bR + bS < best) { best = bR + bS; ca = 9; sub0 = 3; sub1 = 1; }
+                if (bM + bS < best) { best = bM + bS; ca = 10; sub0 = 2; sub1 = 3; }
+                if (lane == 0) make_frame_header(a, ws.fd, ca);
                 __syncwarp();
-                const uint32_t cs = crc_words(a, crc_tab, buf, nw, lane);
-                crc_run = (done ? frx_gf16_mulmod(crc_run, gf16_xpow32(nw)) : 0u) ^ cs;
-                if (!overflow) copy_words_out(a.bytes + off + done, buf, nw, lane);
-                done += nw * 4u;
-                em.P &= 31u;
-                __syncwarp();
+                publish_size(ws.fd.hdr_bits + ws.dec[sub0].bits + ws.dec[sub1].bits);
+            } else {
+                nbar += analyse_channel<WIDE, H>(a, ws, buf, 0, 0, ws.fd.hdr_bits, phase, bs, lane);
+                publish_size(ws.fd.hdr_bits + ws.dec[0].bits);
+            }
+            if (pend) finish_pending(false);
+            // ---- sweep 2: pack ----
+            emit_frame_header();
+            for (int c = 0; c < n_ch; c++) {
+                const SubDec &d = ws.dec[c == 0 ? sub0 : sub1];
+                materialise<WIDE, H>(a, ws, buf, d, phase, bs, lane);
+                pack_subframe(d);
+                if (c + 1 < n_ch) flush_words();
+            }
+        } else {
+            // ---- streamed: analyse, pack and send each channel on its way ----
+            for (int c = 0; c < n_ch; c++) {
+                nbar += analyse_channel<WIDE, H>(a, ws, buf, c, 0, c == 0 ? ws.fd.hdr_bits : (em.P & 31u), phase, bs, lane);
+                const SubDec &d = ws.dec[0];
+                if (c == 0) emit_frame_header();
+                if (c + 1 == n_ch) publish_size(done * 8u + em.P + d.bits);
+                if (pend) finish_pending(false);
+                materialise<WIDE, H>(a, ws, buf, d, phase, bs, lane);      // (a no-op unless the subframe fell back to VERBATIM)
+                pack_subframe(d);
+                if (c + 1 < n_ch) flush_words();
             }
         }
         // ---- frame footer: zero padding to a byte boundary, CRC-16 ----
@@ -1945,16 +2117,34 @@ __global__ void __launch_bounds__(ENC_CTA, 1) frx_encode_kernel(const EncArgs a)
             const uint32_t byte = (em.carry >> (24 - 8 * b)) & 0xFFu;
             crc = ((crc << 8) ^ crc_tab[0][((crc >> 8) ^ byte) & 0xFFu]) & 0xFFFFu;
         }
-        if (!have_off) get_offset();
-        if (!overflow) {
-            uint8_t *dst = a.bytes + off + done;
+        // ---- out: to its final place when the offset is there, else parked ----
+        if (pend) finish_pending(true);              // (the frame before this one: it has had this whole frame's time)
+        LookBack lb;
+        lb.pos = (long long)f - 1; lb.exclusive = 0; lb.blocked = false;
+        const bool have = lb_run(lb, false);
+        bool skip = false;
+        uint8_t *dst = slot + done;
+        if (have) {
+            skip = lb_commit(f, nbytes, lb.exclusive);
+            if (!skip && done) copy_slot_out(a.bytes + lb.exclusive, slot, done, lane);
+            dst = a.bytes + lb.exclusive + done;
+        }
+        if (!skip) {
             copy_words_out(dst, buf, nw, lane);
             if (lane < (int)tb) dst[nw * 4u + lane] = (uint8_t)((em.carry >> (24 - 8 * lane)) & 0xFFu);
             if (lane == 4) dst[nw * 4u + tb] = (uint8_t)(crc >> 8);
             if (lane == 5) dst[nw * 4u + tb + 1u] = (uint8_t)crc;
         }
+        if (!have) {
+            pend = true; pend_f = f; pend_nbytes = nbytes; pend_slot = slot; plb = lb;
+            cur ^= 1;
+            DBG_ADD(12, 1);
+        }
         __syncwarp();
+        if (ALIGNED) { while (nbar < a.bars_per_frame) ALIGN_BAR(nbar); }      // the same number of barriers for every frame
+        DBG_ADD(3, DBG_CLK() - tf0); DBG_ADD(4, 1);
     }
+    if (pend) finish_pending(true);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1990,6 +2180,7 @@ size_t frx_enc_smem_bytes(int frame_words, int dtype) {
     (void)frame_words; (void)dtype;
     return 2048 + (size_t)ENC_WARPS * WARP_BYTES;
 }
+int frx_enc_warps_per_cta() { return ENC_WARPS; }
 
 size_t frx_minmax_raw_size() { return sizeof(MinMaxRaw); }
 
@@ -2168,3 +2359,11 @@ cudaError_t frx_launch_md5(const frx_raster &r, const frx_tile *tiles_dev, const
     frx_md5_kernel<<<(n_tiles + 31) / 32, 32, 0, st>>>(r.data, r.band_stride, r.row_stride, tiles_dev, quant, n_tiles, r.dtype, mode, bps, out);
     return cudaGetLastError();
 }
+
+#ifdef FRX_DBG
+extern "C" void frx_debug_read(unsigned long long *out16, int reset) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out16, g_frx_dbg, sizeof(unsigned long long) * 16);
+    if (reset) { unsigned long long z[16] = { 0 }; cudaMemcpyToSymbol(g_frx_dbg, z, sizeof(z)); }
+}
+#endif

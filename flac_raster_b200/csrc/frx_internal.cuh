@@ -15,6 +15,9 @@ struct EncArgs {
     const uint16_t *crc_tab;    // [4][256] slicing-by-4 CRC-16 tables
     uint8_t *bytes;
     uint64_t capacity;
+    uint8_t *slots;             // two slots of slot_stride bytes per resident frame warp: streamed channels and parked frames
+    uint32_t slot_stride;
+    int bars_per_frame;         // CTA barriers every frame warp passes per frame (phase alignment; padded to this count)
     uint32_t *frame_size;
     uint64_t *frame_offset;
     uint64_t *desc;
@@ -55,6 +58,7 @@ struct DecArgs {
     int verify_crc;
 };
 size_t frx_enc_smem_bytes(int frame_words, int dtype);
+int frx_enc_warps_per_cta();
 cudaError_t frx_launch_crc_check(const DecArgs &a, const uint16_t *xpow, int sm_count, cudaStream_t st);
 size_t frx_minmax_raw_size();
 cudaError_t frx_launch_minmax(const frx_raster &r, const frx_tile *tiles_dev, const uint32_t *unit_prefix_dev, int n_tiles,

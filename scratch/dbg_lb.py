@@ -12,12 +12,16 @@ def rd(reset=1):
     out = (ctypes.c_ulonglong * 16)()
     lib.frx_debug_read(out, reset)
     return list(out)
-for name, r, nch in (("f32", synth.dem_f32(H, H, seed=1), 1), ("u16", synth.rgb_u16(H, H, seed=40000), 1), ("u16x3", synth.rgb_u16(H, H, seed=40000), 3)):
+names = {0: "lookback", 2: "slot copy", 3: "frame", 5: "load", 6: "pass1", 7: "lpc_design", 8: "fixed cand", 9: "lpc resid+cost", 10: "winner fixed redo", 11: "count", 12: "materialise"}
+cases = [("f32", synth.dem_f32(H, H, seed=1), 1), ("u16x1", synth.rgb_u16(H, H, seed=40000), 1), ("u16x3", synth.rgb_u16(H, H, seed=40000), 3)]
+for name, r, nch in cases:
     tiles = tile_grid(H, H, 1024, 0, nch)
     res = codec.encode_tiles(r, tiles)
     torch.cuda.synchronize(); rd()
     codec.encode_tiles(r, tiles, out=res)
     torch.cuda.synchronize()
     d = rd()
-    nf = H * H // 4096
-    print(f"{name}: kernel {codec.last_kernel_ms()[0]:.2f} ms; per frame: polls {d[0]/nf:.1f} steps {d[1]/nf:.2f} lookback cycles {d[2]/max(1,d[3]):.0f} (frames {d[3]}), warp total cycles/frame {d[4]/nf:.0f}; analysis cycles: all {d[7]/nf:.0f}, fixed-winner frames {d[5]/max(1,d[6]):.0f} ({d[6]} frames), others {(d[7]-d[5])/max(1,nf-d[6]):.0f}; channel loads/frame {d[8]/nf:.2f}, 16-bit overflows {d[9]}")
+    nf = max(1, d[4]); ns = max(1, d[15])
+    print(f"{name}: kernel {codec.last_kernel_ms()[0]:.2f} ms; frames {d[4]} analyses {d[15]}; frames parked {d[12]/nf:.3f}; blocked polls/frame {d[1]/nf:.2f}")
+    print("   cycles per frame: " + ", ".join(f"{n} {d[i]/nf:.0f}" for i, n in names.items() if i in (0, 2, 3)))
+    print("   cycles per analysis: " + ", ".join(f"{n} {d[i]/ns:.0f}" for i, n in names.items() if i not in (0, 2, 3, 12)))

@@ -13,6 +13,13 @@ tail = "\n".join(r1[find("// K0+K1 alone (frx_quantize): interleaved int32 PCM o
 head = (Path(__file__).parent / "header.txt").read_text() + head[head.index("#include <math_constants.h>"):]
 head = head.replace("    q[i] = o;\n", "    o.rcp = o.range != 0.0 ? 1.0 / o.range : 0.0;   // correctly rounded (IEEE division)\n    q[i] = o;\n")
 assert "o.rcp" in head
+head = head.replace("    q[i] = o;\n", """    o.irange = 0; o.rcpf = 0.f;
+    if ((dtype == FRX_U8 || dtype == FRX_U16 || dtype == FRX_I16) && !o.degenerate && o.imax - o.imin <= (dtype == FRX_I16 ? 32767 : 65535)) {
+        // neither max - min nor any x - min wraps in the raster dtype: the integer form of the quantiser applies
+        o.irange = (int)(o.imax - o.imin); o.rcpf = __fdiv_rz(1.0f, (float)o.irange); o.flags |= FRX_QF_INT16;
+    }
+    q[i] = o;\n""")
+assert "o.irange" in head
 head = head.replace("#define HIST FRX_MAX_LPC\n#define NWARPS (FRX_ENC_THREADS / 32)   // compute warps\n", "")
 old = tail[tail.index("size_t frx_enc_smem_bytes"):tail.index("size_t frx_minmax_raw_size()")]
 tail = tail.replace(old, """size_t frx_enc_smem_bytes(int frame_words, int dtype) {

@@ -12,7 +12,18 @@
 // exact bit count is known, so the byte offset arrives while the frame is being packed and checksummed.
 // ==========================================================================================
 #define FULLMASK 0xFFFFFFFFu
+#ifdef FRX_DBG
+// development counters (cycles, events) summed over all frame warps; read and cleared by frx_debug_read
+__device__ unsigned long long g_frx_dbg[16];
+#define DBG_ADD(i, v) do { if (lane == 0) atomicAdd(&g_frx_dbg[i], (unsigned long long)(v)); } while (0)
+#define DBG_CLK() clock64()
+#else
+#define DBG_ADD(i, v) do { } while (0)
+#define DBG_CLK() 0ll
+#endif
+#ifndef ENC_WARPS
 #define ENC_WARPS 12
+#endif
 #define ENC_CTA (ENC_WARPS * 32)
 #define SLACK_W 64                                   // words in front of the PCM area: the packed stream runs ahead by its headers
 #define BLK 128                                      // samples per lane block of a full frame = samples per pack chunk
@@ -20,6 +31,23 @@
 #define PIDX(g) ((g) + 4 * ((g) >> 7))               // word of sample g inside the PCM area
 #define PCM_W (FRX_MAX_BLOCK + 4 * (FRX_MAX_BLOCK / BLK))
 #define WBUF_W (SLACK_W + PCM_W + 12)
+// Phase alignment (kernels with ALIGNED = true, see frx_encode_kernel): the frame warps of a CTA are split into groups of
+// ALIGN_GROUP warps that take their frames together and meet again at the phase boundaries of the frame (one named barrier
+// per group).  Every warp of a group passes exactly EncArgs.bars_per_frame barriers per frame, whatever path its frame takes.
+#ifndef ALIGN_GROUP
+#define ALIGN_GROUP 6
+#endif
+static_assert(ENC_WARPS % ALIGN_GROUP == 0, "groups must tile the CTA");
+__device__ __forceinline__ void group_bar() {
+    asm volatile("bar.sync %0, %1;" :: "r"(1 + (int)(threadIdx.x >> 5) / ALIGN_GROUP), "r"(ALIGN_GROUP * 32) : "memory");
+}
+__device__ __forceinline__ bool group_or(bool pred) {
+    int r;
+    asm volatile("{ .reg .pred p, q; setp.ne.s32 q, %3, 0; bar.red.or.pred p, %1, %2, q; selp.s32 %0, 1, 0, p; }"
+                 : "=r"(r) : "r"(1 + (int)(threadIdx.x >> 5) / ALIGN_GROUP), "r"(ALIGN_GROUP * 32), "r"((int)pred) : "memory");
+    return r != 0;
+}
+#define ALIGN_BAR(n) do { if (ALIGNED) { group_bar(); (n)++; } } while (0)
 
 __device__ __forceinline__ uint64_t warp_sum_u64(uint64_t v) {
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULLMASK, v, o);

@@ -13,7 +13,8 @@ __device__ __forceinline__ int32_t quant_one(typename FrxElem<DT>::T v, const Fr
 // in-place expansion of one block: raw elements sit end-aligned in the block's first 512 bytes + 16, PCM words grow from
 // its start (a 16-byte read is always ahead of the words written so far).  FULL: all 128 samples are valid.
 // F32SAFE: float32 reference mode with the stream-wide guarantee that x * 8388607 fits int32 (no per-sample range check).
-template <int DT, bool FULL, bool F32SAFE>
+// INT16: 8/16-bit reference mode of a tile under FRX_QF_INT16 (frx_common.cuh).
+template <int DT, bool FULL, bool F32SAFE, bool INT16 = false>
 __device__ __forceinline__ void quantize_block_t(uint32_t *blk, const FrxQuant &qz, int mode, int nvalid, uint32_t &orv, uint32_t &ora) {
     typedef typename FrxElem<DT>::T T;
     constexpr int ESZ = (int)sizeof(T);
@@ -25,9 +26,21 @@ __device__ __forceinline__ void quantize_block_t(uint32_t *blk, const FrxQuant &
         T e[EPV];
         memcpy(e, &v, 16);
         int32_t x[EPV];
+        if (INT16) {
+            // integer form of the 16-bit quantiser for all the elements of the load, one (rare) branch for those whose
+            // quotient is exact and needs the float64 chain
+            bool exact = false;
+#pragma unroll
+            for (int i = 0; i < EPV; i++) x[i] = frx_quant16_int<DT>(e[i], qz, exact);
+            if (exact) {
+#pragma unroll
+                for (int i = 0; i < EPV; i++) x[i] = frx_quant_ref_chain<DT>(e[i], qz);
+            }
+        }
 #pragma unroll
         for (int i = 0; i < EPV; i++) {
-            if (F32SAFE) x[i] = __float2int_rz(__fmul_rn((float)e[i], 8388607.0f));
+            if (INT16) { }
+            else if (F32SAFE) x[i] = __float2int_rz(__fmul_rn((float)e[i], 8388607.0f));
             else x[i] = quant_one<DT>(e[i], qz, mode);
             if (!FULL && t * EPV + i >= nvalid) x[i] = 0;
             orv |= (uint32_t)x[i];
@@ -42,6 +55,8 @@ template <int DT>
 __device__ __forceinline__ void quantize_block(uint32_t *blk, const FrxQuant &qz, int mode, int nvalid, uint32_t &orv, uint32_t &ora) {
     if (nvalid == BLK) {
         if (DT == FRX_F32 && mode == FRX_PCM_REFERENCE && (qz.flags & FRX_QF_F32_SAFE)) quantize_block_t<DT, true, DT == FRX_F32>(blk, qz, mode, nvalid, orv, ora);
+        else if ((DT == FRX_U8 || DT == FRX_I16 || DT == FRX_U16) && mode == FRX_PCM_REFERENCE && (qz.flags & FRX_QF_INT16))
+            quantize_block_t<DT, true, false, DT == FRX_U8 || DT == FRX_I16 || DT == FRX_U16>(blk, qz, mode, nvalid, orv, ora);
         else quantize_block_t<DT, true, false>(blk, qz, mode, nvalid, orv, ora);
     } else quantize_block_t<DT, false, false>(blk, qz, mode, nvalid, orv, ora);
 }
@@ -91,9 +106,22 @@ __device__ __forceinline__ void load_ms_block(const EncArgs &a, const FrameDesc 
             const uint4 vl = __ldg(reinterpret_cast<const uint4 *>(L + e)), vr = __ldg(reinterpret_cast<const uint4 *>(R + e));
             T el[EPV], er[EPV];
             memcpy(el, &vl, 16); memcpy(er, &vr, 16);
+            int32_t ql[EPV], qr[EPV];
+            if ((DT == FRX_U8 || DT == FRX_I16 || DT == FRX_U16) && a.pcm_mode == FRX_PCM_REFERENCE && (d.q.flags & FRX_QF_INT16)) {
+                bool exact = false;
+#pragma unroll
+                for (int j = 0; j < EPV; j++) { ql[j] = frx_quant16_int<DT>(el[j], d.q, exact); qr[j] = frx_quant16_int<DT>(er[j], d.q, exact); }
+                if (exact) {
+#pragma unroll
+                    for (int j = 0; j < EPV; j++) { ql[j] = frx_quant_ref_chain<DT>(el[j], d.q); qr[j] = frx_quant_ref_chain<DT>(er[j], d.q); }
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < EPV; j++) { ql[j] = quant_one<DT>(el[j], d.q, a.pcm_mode); qr[j] = quant_one<DT>(er[j], d.q, a.pcm_mode); }
+            }
 #pragma unroll
             for (int j = 0; j < EPV; j++) {
-                const int32_t l = quant_one<DT>(el[j], d.q, a.pcm_mode), r = quant_one<DT>(er[j], d.q, a.pcm_mode);
+                const int32_t l = ql[j], r = qr[j];
                 x[j] = vch == 8 ? ((l + r) >> 1) : (l - r);
                 if (i + j >= nvalid) x[j] = 0;
                 orv |= (uint32_t)x[j];

@@ -398,7 +398,15 @@ __device__ __noinline__ void copy_slot_out(uint8_t *dst, const uint8_t *slot, ui
     uint32_t *dw = reinterpret_cast<uint32_t *>(dst + head);
     const uint32_t *sw = reinterpret_cast<const uint32_t *>(slot);
     const uint32_t sh8 = head * 8u;
-    for (uint32_t j = lane; j < nwords; j += 32) {
+    uint32_t j = lane;
+    for (; j + 7u * 32u < nwords; j += 8u * 32u) {            // eight independent L2 round trips in flight per lane
+        uint32_t w0[8], w1[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) { w0[k] = __ldcg(sw + j + 32 * k); w1[k] = head ? __ldcg(sw + j + 32 * k + 1) : 0u; }
+#pragma unroll
+        for (int k = 0; k < 8; k++) dw[j + 32 * k] = head ? __funnelshift_r(w0[k], w1[k], sh8) : w0[k];
+    }
+    for (; j < nwords; j += 32) {
         const uint32_t w0 = __ldcg(sw + j), w1 = head ? __ldcg(sw + j + 1) : 0u;
         dw[j] = head ? __funnelshift_r(w0, w1, sh8) : w0;      // little-endian words: bytes [head + 4j, head + 4j + 4)
     }

@@ -44,15 +44,19 @@ __device__ __forceinline__ bool residuals_inplace(WarpSh &ws, uint32_t *buf, con
 }
 
 template <bool WIDE, int H>
-__device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint32_t *buf, int vch, int ci, uint32_t startbits, uint32_t &phase,
+__device__ __noinline__ int analyse_channel(const EncArgs &a, WarpSh &ws, uint32_t *buf, int vch, int ci, uint32_t startbits, uint32_t &phase,
                                              BufState &bs, int lane) {
     SubDec &d = ws.dec[ci];
     const FrameDesc &fd = ws.fd;
     uint32_t *pcm = buf + SLACK_W;
     const int nsamp = fd.nsamp;
     const bool full = nsamp == FRX_MAX_BLOCK;
+    const long long t_0 = DBG_CLK();
+    constexpr bool ALIGNED = !WIDE;
+    int nbar = 0;                     // group barriers passed (phase alignment of the frame warps, see the kernel)
     const uint2 st = load_channel(a, ws, buf, vch, phase, lane);
     const uint32_t orv = st.x, ora = st.y;
+    DBG_ADD(5, DBG_CLK() - t_0); DBG_ADD(15, 1);
     const int wasted = orv ? (__ffs((int)orv) - 1) : 0;
     if (wasted) shift_wasted(pcm, nsamp, wasted, lane);
     const int magbits = 32 - __clz((int)(ora >> wasted));          // |sample| <= 2^magbits
@@ -69,7 +73,9 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
     }
     __syncwarp();
 
+    ALIGN_BAR(nbar);
     // ---- K2 + K3 ----
+    const long long t_1 = DBG_CLK();
     uint64_t tot[5];
     uint64_t fsl[5][2];
     uint32_t badmask = 0;
@@ -104,11 +110,13 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
         for (int k = 0; k <= H; k++) autoc[k] = ws.g_ac[k];
         badmask = ws.g_bad;
     }
+    DBG_ADD(6, DBG_CLK() - t_1);
     if (tot[1] == 0 && !(badmask & 2u)) {     // sum |s[g] - s[g-1]| == 0  <=>  all samples equal
         if (lane == 0) { d.type = 0; d.bits = 8u + (uint32_t)wasted + (uint32_t)sbps; }
         __syncwarp();
-        return;
+        return nbar;
     }
+    ALIGN_BAR(nbar);
     int fixed_order = -1;
     if (nsamp > 4) {
         uint64_t bestv = ~0ull;
@@ -119,7 +127,10 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
     // ---- K4 ----
     LpcChoice lc;
     lc.ok = 0; lc.order = 0; lc.shift = 0; lc.precision = 0; lc.narrow = 1;
+    const long long t_2 = DBG_CLK();
     if (max_lpc > 0 && nsamp > 4) lc = lpc_design<WIDE, H>(ws, autoc, max_lpc, nsamp, sbps, a.qlp_precision, magbits, lane);
+    DBG_ADD(7, DBG_CLK() - t_2);
+    const long long t_3 = DBG_CLK();
 
     unsigned long long *bins = reinterpret_cast<unsigned long long *>(buf);   // generic path: 32 sums in the slack words
     const int Fg = po_max > 5 ? 5 : po_max;
@@ -146,6 +157,9 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
         const uint64_t b = 8ull + wasted + (uint64_t)fixed_order * sbps + rf.bits;
         if (b < best_bits) { best_bits = b; type = 2; order = fixed_order; po = rf.po; rice2 = rf.rice2; cand = 0; }
     }
+    DBG_ADD(8, DBG_CLK() - t_3);
+    const long long t_4 = DBG_CLK();
+    ALIGN_BAR(nbar);
     // ---- LPC candidate: residuals in place (the usual winner), cost from their partition sums ----
     if (lc.ok) {
         if (lane == 0) { d.type = 3; d.order = (uint8_t)lc.order; d.shift = lc.shift; d.narrow = (uint8_t)lc.narrow; d.precision = (uint8_t)lc.precision; }
@@ -166,11 +180,14 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
             if (b < best_bits) { best_bits = b; type = 3; order = lc.order; po = rl.po; rice2 = rl.rice2; cand = 1; }
         }
     }
+    DBG_ADD(9, DBG_CLK() - t_4);
+    ALIGN_BAR(nbar);
     if (type == 1) {
         if (lane == 0) { d.type = 1; d.order = 0; }
         __syncwarp();
-        return;
+        return nbar;
     }
+    const long long t_5 = DBG_CLK();
     // ---- record the winner; make the buffer hold its residuals ----
     if (lane == 0) {
         d.type = (uint8_t)type; d.order = (uint8_t)order; d.po = (uint8_t)po; d.rice2 = rice2 ? 1 : 0;
@@ -188,6 +205,8 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
         (void)residuals_inplace<WIDE, H>(ws, buf, d, nsamp, nullptr, psf, lane, x0, x1);
         bs.kind = BUF_RES; bs.type = 2; bs.order = order;
     }
+    DBG_ADD(10, DBG_CLK() - t_5);
+    const long long t_6 = DBG_CLK();
     // ---- exact size ----
     const uint32_t pb = rice2 ? 5u : 4u;
     const uint32_t hb = 8u + (uint32_t)wasted + (uint32_t)order * (uint32_t)sbps + (type == 3 ? 9u + (uint32_t)order * (uint32_t)lc.precision : 0u) + 6u;
@@ -218,6 +237,8 @@ __device__ __noinline__ void analyse_channel(const EncArgs &a, WarpSh &ws, uint3
         if (lane == 0) { d.type = 1; d.order = 0; d.bits = (uint32_t)verb_bits; }
     } else if (lane == 0) { d.bits = total; d.runs = runs_ok ? 1 : 0; }
     __syncwarp();
+    DBG_ADD(11, DBG_CLK() - t_6);
+    return nbar;
 }
 
 // make the buffer hold what packing subframe d needs: its PCM (CONSTANT / VERBATIM) or its residuals

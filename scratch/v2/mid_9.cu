@@ -88,3 +88,11 @@ cudaError_t frx_launch_md5(const frx_raster &r, const frx_tile *tiles_dev, const
     frx_md5_kernel<<<(n_tiles + 31) / 32, 32, 0, st>>>(r.data, r.band_stride, r.row_stride, tiles_dev, quant, n_tiles, r.dtype, mode, bps, out);
     return cudaGetLastError();
 }
+
+#ifdef FRX_DBG
+extern "C" void frx_debug_read(unsigned long long *out16, int reset) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out16, g_frx_dbg, sizeof(unsigned long long) * 16);
+    if (reset) { unsigned long long z[16] = { 0 }; cudaMemcpyToSymbol(g_frx_dbg, z, sizeof(z)); }
+}
+#endif
