@@ -359,14 +359,12 @@ __device__ __noinline__ uint32_t crc_words(const EncArgs &a, const uint16_t (*ta
     if (z && c) c = frx_gf16_mulmod(c, (uint32_t)__ldg(&a.crc_xinv[z]));
     return c;
 }
-// x^(32 n) mod P
-__device__ __noinline__ uint32_t gf16_xpow32(uint32_t n) {
-    uint32_t r = 1, b = frx_gf16_mulmod(0x8005u, 0x8005u);     // x^16 = 0x8005 (mod P), squared
-    while (n) {
-        if (n & 1u) r = frx_gf16_mulmod(r, b);
-        b = frx_gf16_mulmod(b, b);
-        n >>= 1;
-    }
+// x^(32 n) mod P, n < 32768, from the CRC chunk tables: n = 128 j1 + 4 j0 + b, x^(32 n) = x^(128 * 32 * j1) * x^(128 * j0) * x^(32 b)
+__device__ __noinline__ uint32_t gf16_xpow32(const EncArgs &a, uint32_t n) {
+    const uint32_t j1 = (n >> 7) & 255u, j0 = (n >> 2) & 31u, b = n & 3u;
+    uint32_t r = (uint32_t)__ldg(&a.crc_xpow[31 * 256 + j1]);                    // row Lq = 32
+    if (j0) r = frx_gf16_mulmod(r, (uint32_t)__ldg(&a.crc_xpow[j0]));           // row Lq = 1
+    if (b) r = frx_gf16_mulmod(r, b == 1u ? 0x8017u : (b == 2u ? 0x8113u : 0x9543u));   // x^32, x^64, x^96
     return r;
 }
 // words [0, nw) of the warp buffer -> dst (any byte alignment), big-endian byte order

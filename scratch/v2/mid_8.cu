@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(ENC_CTA, 1) frx_encode_kernel(const EncArgs a)
             const uint32_t nw = em.P >> 5;
             __syncwarp();
             const uint32_t cs = crc_words(a, crc_tab, buf, nw, lane);
-            crc_run = (done ? frx_gf16_mulmod(crc_run, gf16_xpow32(nw)) : 0u) ^ cs;
+            crc_run = (done ? frx_gf16_mulmod(crc_run, gf16_xpow32(a, nw)) : 0u) ^ cs;
             copy_words_out(slot + done, buf, nw, lane);
             done += nw * 4u;
             em.P &= 31u;
@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(ENC_CTA, 1) frx_encode_kernel(const EncArgs a)
         const uint32_t nw = em.P >> 5, tb = (em.P & 31u) >> 3;
         __syncwarp();
         uint32_t crc = crc_words(a, crc_tab, buf, nw, lane);
-        if (done) crc ^= frx_gf16_mulmod(crc_run, gf16_xpow32(nw));
+        if (done) crc ^= frx_gf16_mulmod(crc_run, gf16_xpow32(a, nw));
         for (uint32_t b = 0; b < tb; b++) {
             const uint32_t byte = (em.carry >> (24 - 8 * b)) & 0xFFu;
             crc = ((crc << 8) ^ crc_tab[0][((crc >> 8) ^ byte) & 0xFFu]) & 0xFFFFu;
