@@ -357,3 +357,29 @@ def test_host_decode_pipeline_groups_equal_single_call(codec, monkeypatch):
             r0, c0 = divmod(m["out_offset"], W)
             assert np.array_equal(outp[e["out_offset"]:e["out_offset"] + e["h"] * e["w"]].reshape(e["h"], e["w"]),
                                   want_m.reshape(H, W)[r0:r0 + e["h"], c0:c0 + e["w"]])
+
+
+@pytest.mark.parametrize("dtype,lo,rng_", [("uint16", 100, 32767), ("uint16", 0, 65534), ("uint16", 7, 4340), ("uint16", 1000, 453),
+                                           ("uint16", 0, 65535), ("uint8", 0, 255), ("uint8", 3, 217), ("int16", -16000, 32767),
+                                           ("int16", -5, 31 * 151), ("int16", -20000, 40000)])
+def test_integer_quantiser_on_ranges_full_of_exact_quotients(codec, dtype, lo, rng_):
+    """The 8/16-bit quantiser's integer form (frx_common.cuh frx_quant16_int) against the reference's float64 chain on
+    tiles that hold EVERY value of their range, with ranges sharing factors with 32767 = 7 * 31 * 151 so that many quotients
+    are exact integers (the samples that take the float64 branch), and an int16 range that wraps (the chain only).  Both
+    kernels that quantise are covered: frx_quantize (per sample) and the encoder's block loader (per 16-byte load)."""
+    import torch
+    n_val = rng_ + 1
+    w = 512
+    h = (n_val + w - 1) // w + 3
+    vals = (lo + (np.arange(h * w, dtype=np.int64) % n_val))
+    rs = np.random.default_rng(rng_)
+    vals[n_val:] = lo + rs.integers(0, n_val, h * w - n_val)              # every value once, then a random refill
+    r = vals.astype(np.int64).astype(dtype).reshape(1, h, w)
+    from oracle import quant
+    want, bps, dmin, dmax, _ = quant.reference_pcm(r)
+    pcm, mm = codec.quantize(_torch_raster(r), (0, 0, h, w, 0, 1))
+    torch.cuda.synchronize()
+    assert np.array_equal(pcm.cpu().numpy().reshape(-1), want.reshape(-1))
+    tiles = [(0, 0, h, w, 0, 1)]
+    _, data, toff, tsize, tmm, fsize = _encode(codec, r, tiles)
+    check_encode_against_oracle(r, tiles, data, toff, tsize, tmm, fsize)
