@@ -2,13 +2,13 @@
 //
 // Kernels (SURVEY.md section 8a ids):
 //   K0  frx_minmax_kernel        per-stream min/max                      (converter.py:67-68, 152-153)
-//   K1..K8 frx_encode_kernel     one WARP per 4096-sample frame, twelve independent warps per SM, persistent grid,
+//   K1..K8 frx_encode_kernel     one WARP per 4096-sample frame, twelve frame warps per SM, persistent grid,
 //        ticket-ordered:
 //        K1 tile cut + band->channel gather (TMA bulk copies) + PCM quantise   (converter.py:56-86, 185-194; cli.py:691-699)
 //        K2 fixed-order 0..4 trial            K3 windowed autocorrelation
 //        K4 Levinson-Durbin + order pick + coefficient quantisation    K5 residual (in place)
 //        K6 Rice partition sums, parameter + partition-order choice    K7 bit packing (in place) + CRC-8/16
-//        K8 decoupled look-back over frame sizes -> final byte offset, frame copied straight to its place
+//        K8 decoupled look-back over frame sizes -> final byte offset; frame copied to its place, at once or from its slot
 //   frx_tile_index_kernel        per-tile offset/size/minmax from the per-frame table
 //
 // What libFLAC does per frame (process_subframe_; restated in oracle/flac_oracle.c) is kept in spirit:
@@ -178,16 +178,18 @@ __global__ void frx_tile_index_kernel(const uint32_t *frame_prefix, const uint32
 }
 
 // ==========================================================================================
-// Frame encoder, round 2: ONE WARP PER FRAME, twelve independent warps per SM.
+// Frame encoder, round 2: ONE WARP PER FRAME, twelve frame warps per SM.
 //
-// A warp owns a 4096-sample frame from ticket to copy-out; nothing in the frame loop is a block-wide barrier.  A lane
-// owns a contiguous block of 128 samples, so every search stage is a register sliding window over shared memory that is
-// read with 16-byte loads, the level-5 Rice partitions ARE the lanes, and all reductions are shuffles.  Per warp the
-// shared memory is one 16.9 KB buffer that holds, in turn and in place: the raw samples as TMA delivered them, the
-// PCM, the zig-zag residuals of the winning predictor, and finally the packed frame (the packer reads a chunk of 128
-// residuals into registers before it writes the bits of that chunk, and the bits never overtake the reader: checked per
-// subframe from the exact bit counts, VERBATIM otherwise).  Frame sizes go through the decoupled look-back as soon as the
-// exact bit count is known, so the byte offset arrives while the frame is being packed and checksummed.
+// A warp owns a 4096-sample frame from ticket to copy-out.  A lane owns a contiguous block of 128 samples, so every search
+// stage is a register sliding window over shared memory that is read with 16-byte loads, the level-5 Rice partitions ARE
+// the lanes, and all reductions are shuffles.  Per warp the shared memory is one 16.9 KB buffer that holds, in turn and in
+// place: the raw samples as TMA delivered them, the PCM, the zig-zag residuals of the winning predictor, and finally the
+// packed frame (the packer reads a chunk of 128 residuals into registers before it writes the bits of that chunk, and the
+// bits never overtake the reader: checked per subframe from the exact bit counts, VERBATIM otherwise).  Frame sizes go
+// through the decoupled look-back as soon as the exact bit count is known; a frame whose offset is not there when it is
+// packed is parked in a slot in global memory instead of waiting (see the kernel).  The warps of the wide (32-bit PCM)
+// kernels run free; those of the narrow kernels walk the phases of their frames in step, in groups of ALIGN_GROUP, because
+// twelve warps at twelve places of this kernel overrun the instruction cache (see the kernel).
 // ==========================================================================================
 #define FULLMASK 0xFFFFFFFFu
 #ifdef FRX_DBG
