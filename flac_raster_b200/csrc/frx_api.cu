@@ -587,7 +587,7 @@ int frx_encode_tiles_host(frx_ctx *c, const frx_raster *raster_host, const frx_t
         max_bytes = bb;
     }
     const int ng = (int)groups.size();
-    while ((int)c->hev.size() < ng) { cudaEvent_t e; CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); c->hev.push_back(e); }
+    while ((int)c->hev.size() < 2 * ng) { cudaEvent_t e; CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); c->hev.push_back(e); }
     if (c->pin_small_cap < (size_t)ng * 16) {
         if (c->pin_small) cudaFreeHost(c->pin_small);
         c->pin_small = nullptr; c->pin_small_cap = 0;
@@ -625,8 +625,11 @@ int frx_encode_tiles_host(frx_ctx *c, const frx_raster *raster_host, const frx_t
                 for (long long b = 0; b < nb; b++) {
                     const char *src = (const char *)r.data + ((size_t)(b0 + b) * (size_t)r.band_stride + (size_t)(r0 + y0) * (size_t)r.row_stride) * esz;
                     char *dst = (char *)c->h_raster.p + ((size_t)b * plane + (size_t)y0 * (size_t)r.width) * esz;
-                    CK(cudaMemcpy2DAsync(dst, (size_t)r.width * esz, src, (size_t)r.row_stride * esz, (size_t)r.width * esz, (size_t)(y1 - y0),
-                                         cudaMemcpyHostToDevice, s_in));
+                    if (r.row_stride == r.width)      // contiguous rows: one linear copy (the 2-D path of the copy engine is slower)
+                        CK(cudaMemcpyAsync(dst, src, (size_t)r.width * esz * (size_t)(y1 - y0), cudaMemcpyHostToDevice, s_in));
+                    else
+                        CK(cudaMemcpy2DAsync(dst, (size_t)r.width * esz, src, (size_t)r.row_stride * esz, (size_t)r.width * esz, (size_t)(y1 - y0),
+                                             cudaMemcpyHostToDevice, s_in));
                 }
             }
             CK(cudaEventRecord(c->hev[k], s_in));
@@ -659,11 +662,14 @@ int frx_encode_tiles_host(frx_ctx *c, const frx_raster *raster_host, const frx_t
         od.total_bytes = &tot_dev[k].total; od.status = &tot_dev[k].status;
         od.tile_offset = d_tile_offset + g.t0; od.tile_size = d_tile_size + g.t0; od.tile_minmax = d_tile_minmax + 2 * (size_t)g.t0;
         od.frame_offset = d_frame_offset + g.frame_base; od.frame_size = d_frame_size + g.frame_base;
+        // group k-1 goes home as soon as IT is done -- not when the rows of group k have arrived, which is what the stream
+        // synchronisation inside frx_encode_tiles below waits for (it sits behind the wait on hev[k]): one group earlier,
+        // so that only the last group's bytes are still to travel when the last rows have come in
+        if (k > 0) { CK(cudaEventSynchronize(c->hev[ng + k - 1])); rc = copy_out_group(k - 1); if (rc) return rc; }
         CK(cudaStreamWaitEvent(s_cmp, c->hev[k], 0));
-        // (frx_encode_tiles synchronises its stream once while staging the tile tables: group k-1 is finished after it)
         rc = frx_encode_tiles(c, &rd, lt.data(), g.t1 - g.t0, p, &od, s_cmp); if (rc) return rc;
         CK(cudaMemcpyAsync(&tot[k], &tot_dev[k], sizeof(Tot), cudaMemcpyDeviceToHost, s_cmp));
-        if (k > 0) { rc = copy_out_group(k - 1); if (rc) return rc; }
+        CK(cudaEventRecord(c->hev[ng + k], s_cmp));
     }
     CK(cudaStreamSynchronize(s_cmp));
     rc = copy_out_group(ng - 1); if (rc) return rc;
