@@ -25,7 +25,10 @@
  * The caller owns every buffer passed in; the library keeps only per-context scratch.
  * "dev" pointers are CUDA device pointers on the context's device; `stream` is a
  * cudaStream_t (pass 0 for the legacy default stream).  Device entry points are
- * asynchronous with respect to the host and ordered on `stream`.
+ * ordered on `stream` and return with their kernels still running; frx_encode_tiles,
+ * frx_decode_tiles, frx_tile_md5 and frx_quantize synchronise `stream` ONCE on the way in
+ * (the tile tables are staged from host vectors), so work queued on that stream earlier
+ * has finished when they return.
  * There is NO CPU fallback: without a CUDA device every compute entry point fails.
  */
 #ifndef FRX_H
