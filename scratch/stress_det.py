@@ -9,18 +9,20 @@ runs = int(sys.argv[2]) if len(sys.argv) > 2 else 20
 from flac_raster_b200 import synth
 from flac_raster_b200.codec import Codec, tile_grid
 codec = Codec(0)
-cases = [("f32", synth.dem_f32(20000, 20000, seed=1), 20000, 1), ("u16x3", synth.rgb_u16(8192, 8192, seed=40000), 8192, 3)]
+cases = [("f32", synth.dem_f32(20000, 20000, seed=1), 20000, 1, 1024, {}), ("u16x3", synth.rgb_u16(8192, 8192, seed=40000), 8192, 3, 1024, {}),
+         ("u16x1", synth.rgb_u16(8192, 8192, seed=7), 8192, 1, 1024, {}), ("u16x2", synth.rgb_u16(8192, 8192, seed=8), 8192, 2, 1024, {}),
+         ("u16x3_t200", synth.rgb_u16(4000, 4000, seed=9), 4000, 3, 200, {}), ("u16x3_lossless_t256", synth.rgb_u16(4096, 4096, seed=10), 4096, 3, 256, {"pcm_mode": "lossless"})]
 if len(sys.argv) > 3:
     cases = [c for c in cases if c[0] == sys.argv[3]]
-for name, r, H, nch in cases:
-    tiles = tile_grid(H, H, 1024, 0, nch)
-    res = codec.encode_tiles(r, tiles)
+for name, r, H, nch, tile, kw in cases:
+    tiles = tile_grid(H, H, tile, 0, nch)
+    res = codec.encode_tiles(r, tiles, **kw)
     torch.cuda.synchronize()
     fs0 = res.frame_size.clone(); tb0 = int(res.total_bytes.item()); b0 = res.bytes[:tb0].clone()
     bad = 0
     for i in range(runs):
         res.bytes.zero_()
-        codec.encode_tiles(r, tiles, out=res)
+        codec.encode_tiles(r, tiles, out=res, **kw)
         torch.cuda.synchronize()
         tb = int(res.total_bytes.item())
         d = (res.frame_size != fs0).nonzero().flatten()

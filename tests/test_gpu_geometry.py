@@ -184,3 +184,27 @@ def test_c1_wide_convert_frame_shorter_than_row(codec, tmp_path):
     conv.flac_to_tiff(tmp_path / "wide.flac", tmp_path / "wide_back.tif")
     got, _ = read_tif(tmp_path / "wide_back.tif")
     assert np.array_equal(got, _reference_roundtrip(arr))
+
+
+@pytest.mark.parametrize("kind,nch,tile", [("f32", 1, 1024), ("u16", 3, 1024), ("u16", 2, 512), ("u16", 1, 200)])
+def test_encode_is_deterministic_across_calls(codec, kind, nch, tile):
+    """The frame warps take tickets, park frames and (narrow kernels) meet at barriers in an order that differs from run to run;
+    the bytes must not.  Twenty encodes of the same raster, compared byte for byte (sizes, offsets, stream)."""
+    import torch
+    from flac_raster_b200 import synth
+    from flac_raster_b200.codec import tile_grid
+    H = 3000
+    r = synth.dem_f32(H, H, seed=5) if kind == "f32" else synth.rgb_u16(H, H, seed=6)
+    tiles = tile_grid(H, H, tile, 0, nch)
+    res = codec.encode_tiles(r, tiles)
+    torch.cuda.synchronize()
+    assert int(res.status.item()) == 0
+    total = int(res.total_bytes.item())
+    ref_bytes, ref_fs, ref_fo = res.bytes[:total].clone(), res.frame_size.clone(), res.frame_offset.clone()
+    for _ in range(20):
+        res.bytes.zero_()
+        codec.encode_tiles(r, tiles, out=res)
+        torch.cuda.synchronize()
+        assert int(res.total_bytes.item()) == total
+        assert torch.equal(res.frame_size, ref_fs) and torch.equal(res.frame_offset, ref_fo)
+        assert torch.equal(res.bytes[:total], ref_bytes)
