@@ -448,9 +448,10 @@ static int decode_core(frx_ctx *c, const uint8_t *bytes_dev, uint64_t n_bytes, c
     ENSURE(c->dprefix, sizeof(uint32_t) * (n_tiles + 1));
     ENSURE(c->fpos, sizeof(uint64_t) * (size_t)(nf + 1));
     ENSURE(c->flen, sizeof(uint32_t) * (size_t)(nf + 1));
-    bool two_ch = false;
-    for (int i = 0; i < n_tiles; i++) two_ch = two_ch || tiles[i].channels == 2;
-    if (two_ch) ENSURE(c->stereo, sizeof(int32_t) * (size_t)nf * (size_t)blocksize);   // scratch rows for stereo decorrelation
+    bool two_ch = false, two_ch_32 = false;
+    for (int i = 0; i < n_tiles; i++) { two_ch = two_ch || tiles[i].channels == 2; two_ch_32 = two_ch_32 || (tiles[i].channels == 2 && tiles[i].bps == 32); }
+    // scratch rows for stereo decorrelation: int32 per sample, int64 when a 33-bit side channel can occur
+    if (two_ch) ENSURE(c->stereo, (two_ch_32 ? sizeof(int64_t) : sizeof(int32_t)) * (size_t)nf * (size_t)blocksize);
     ENSURE(c->scan_prefix, sizeof(uint32_t) * sprefix.size());
     ENSURE(c->scan_tiles, sizeof(int32_t) * (stiles.size() + 1));
     { int rc2 = ensure_crctab(c); if (rc2) return rc2; }

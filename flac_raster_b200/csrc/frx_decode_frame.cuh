@@ -234,6 +234,97 @@ __device__ __noinline__ void restore_subframe_generic(BitR &br, RiceState &rs, t
     }
 }
 
+// Stereo-decorrelated frames at 32 bits per sample (libFLAC 1.4 writes them for two-band int32 / uint32 / float32 rasters:
+// the side channel is a 33-bit signal).  Rare and outside the 32-bit lockstep machinery, so the lane that holds such a frame
+// decodes it on its own, sequentially, in 64-bit arithmetic: channel 0 into the frame's scratch row (int64 here), channel 1
+// combined with it sample by sample, both band planes written with scattered stores.  Returns false on a malformed frame.
+__device__ __forceinline__ long long dec_sget64(BitR &br, int n) {      // signed, n in 1..33
+    unsigned long long v;
+    if (n > 32) { const unsigned long long hi = br.get(n - 32); v = (hi << 32) | (unsigned long long)br.get(32); }
+    else v = br.get(n);
+    return (long long)(v << (64 - n)) >> (64 - n);
+}
+template <int DT>
+__device__ __noinline__ bool decode_frame_stereo_wide(BitR &br, typename FrxElem<DT>::T *base0, long long band_stride, long long row_stride, int w,
+                                                      long long px, int nsamp, int bps, uint32_t stereo, long long *scr, const FrxDequant &dq,
+                                                      int mode) {
+    typedef typename FrxElem<DT>::T T;
+    for (int c = 0; c < 2; c++) {
+        const uint32_t hdr = br.get(8);
+        const uint32_t type = (hdr >> 1) & 0x3Fu;
+        if (hdr & 0x80u) return false;
+        int wasted = 0;
+        if (hdr & 1u) wasted = (int)br.unary() + 1;
+        const int side = ((stereo == 1u && c == 1) || (stereo == 2u && c == 0) || (stereo == 3u && c == 1)) ? 1 : 0;
+        const int sbps = bps + side - wasted;
+        if (sbps <= 0) return false;
+        int order = 0, shift = 0, kind;                    // kind: 0 constant, 1 verbatim, 2 predictive
+        int32_t coef[32];
+        long long h[32];
+        long long cval = 0;
+        RiceState rs;
+        rs.k = 0; rs.left = 0; rs.pbits = 4; rs.esc = 15u; rs.rawbits = -1; rs.psize = 1;
+        if (type == 0) { kind = 0; cval = dec_sget64(br, sbps); }
+        else if (type == 1) kind = 1;
+        else {
+            bool lpc = false;
+            if (type >= 8 && type <= 12) order = (int)type - 8;
+            else if (type >= 32) { order = (int)(type & 31u) + 1; lpc = true; }
+            else return false;
+            if (order > nsamp) return false;
+            kind = 2;
+            for (int i = 0; i < 32; i++) { coef[i] = 0; h[i] = 0; }
+            for (int i = 0; i < order; i++) h[i] = dec_sget64(br, sbps);
+            if (lpc) {
+                const int prec = (int)br.get(4) + 1;
+                shift = br.sget(5);
+                if (prec == 16 || shift < 0) return false;
+                for (int j = 0; j < order; j++) coef[j] = br.sget(prec);
+            } else {
+                if (order == 1) { coef[0] = 1; }
+                else if (order == 2) { coef[0] = 2; coef[1] = -1; }
+                else if (order == 3) { coef[0] = 3; coef[1] = -3; coef[2] = 1; }
+                else if (order == 4) { coef[0] = 4; coef[1] = -6; coef[2] = 4; coef[3] = -1; }
+            }
+            const uint32_t method = br.get(2), po = br.get(4);
+            if (method > 1u || (po > 0 && ((uint32_t)nsamp >> po) << po != (uint32_t)nsamp) || ((uint32_t)nsamp >> po) < (uint32_t)order) return false;
+            rs.pbits = method ? 5 : 4; rs.esc = method ? 31u : 15u; rs.psize = (uint32_t)nsamp >> po;
+            rs.k = br.get(rs.pbits);
+            rs.left = rs.psize - (uint32_t)order;
+            rs.rawbits = -1;
+            if (rs.k == rs.esc) rs.rawbits = (int)br.get(5);
+        }
+        int row = (int)(px / w), col = (int)(px - (long long)row * w);
+        for (int n = 0; n < nsamp; n++) {
+            long long v;
+            if (kind == 0) v = cval;
+            else if (kind == 1) v = dec_sget64(br, sbps);
+            else if (n < order) v = h[n];
+            else {
+                const long long r = (long long)rice_next(br, rs);
+                long long acc = 0;
+                for (int j = 0; j < order; j++) acc += (long long)coef[j] * h[(n - 1 - j) & 31];
+                v = r + (acc >> shift);
+                h[n & 31] = v;
+            }
+            v = (long long)((unsigned long long)v << wasted);
+            if (c == 0) scr[n] = v;
+            else {
+                const long long a0 = scr[n], a1 = v;
+                long long L, R;
+                if (stereo == 1u) { L = a0; R = a0 - a1; }                 // left, side
+                else if (stereo == 2u) { R = a1; L = a0 + a1; }            // side, right
+                else { const long long mid = (long long)(((unsigned long long)a0 << 1) | ((unsigned long long)a1 & 1ull)); L = (mid + a1) >> 1; R = (mid - a1) >> 1; }
+                T *p = base0 + (long long)row * row_stride + col;
+                p[0] = frx_dequant<DT>((int32_t)L, bps, dq, mode);
+                p[band_stride] = frx_dequant<DT>((int32_t)R, bps, dq, mode);
+                if (++col == w) { col = 0; row++; }
+            }
+        }
+    }
+    return true;
+}
+
 template <int DT>
 __device__ __forceinline__ uint32_t dec_pack(typename FrxElem<DT>::T v) {
     typedef typename FrxElem<DT>::T T;
@@ -426,6 +517,7 @@ __global__ void __launch_bounds__(32 * DEC_WARPS, FRX_DEC_CTAS) frx_decode_kerne
     long long s0 = 0;
     int nsamp = 0, channels = 0, bps = 0;
     uint32_t stereo = 0;
+    bool wide_stereo_done = false;
     FrxDequant dq;
     dq.range_f = 0.f; dq.dmin_f = 0.f;
     BitR br;
@@ -471,11 +563,23 @@ __global__ void __launch_bounds__(32 * DEC_WARPS, FRX_DEC_CTAS) frx_decode_kerne
         if (nsamp != expect || bps != t.bps || channels != t.channels || ch_code > 10u) bad = true;
         if (ch_code >= 8u && !bad) {
             stereo = ch_code - 7u;                       // 1 left/side, 2 side/right, 3 mid/side
-            if (!a.stereo_scratch || bps >= 32) { bad = true; status = FRX_E_UNSUPPORTED; }
+            if (!a.stereo_scratch) { bad = true; status = FRX_E_UNSUPPORTED; }
+            else if (bps >= 32) {
+                // 33-bit side channel: this lane decodes the whole frame on its own and idles through the lockstep part
+                // (the scratch rows are int64 for such calls, frx_api.cu decode_core)
+                BitR brl = br;      // only the copy's address escapes: br itself stays in registers
+                const bool ok = decode_frame_stereo_wide<DT>(brl, (T *)a.out + t.out_offset, t.out_band_stride, t.out_row_stride, t.w, s0, nsamp, bps,
+                                                             stereo, reinterpret_cast<long long *>(a.stereo_scratch) + (size_t)f * (size_t)a.blocksize,
+                                                             dq, a.pcm_mode);
+                br = brl;
+                if (!ok) bad = true;
+                wide_stereo_done = true;
+                stereo = 0;
+            }
         }
     }
-    int my_n = (live && !bad) ? nsamp : 0;
-    const int my_ch = (live && !bad) ? channels : 0;
+    int my_n = (live && !bad && !wide_stereo_done) ? nsamp : 0;
+    const int my_ch = (live && !bad && !wide_stereo_done) ? channels : 0;
     const int nmax = __reduce_max_sync(0xFFFFFFFFu, my_n), chmax = __reduce_max_sync(0xFFFFFFFFu, my_ch);
     const bool any_stereo = __any_sync(0xFFFFFFFFu, stereo != 0u && my_n > 0);
     const int w = my_n ? t.w : (1 << 30);

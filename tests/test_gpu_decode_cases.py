@@ -113,3 +113,29 @@ def test_decode_escaped_partitions(codec, bps):
             got = _gpu_decode(codec, data, fsizes, h, w, 1, bps, table)
             assert np.array_equal(got[0], pcm), (bps, mod, table)
     assert total_esc > 20, total_esc
+
+
+@pytest.mark.parametrize("table", [True, False])
+def test_decode_stereo_at_32_bits(codec, table):
+    """Two-channel streams at 32 bits per sample as libFLAC 1.4 writes them at level 5: left/side, side/right and mid/side
+    frames whose side channel is a 33-bit signal (the oracle's encoder restates that search).  Includes full-scale samples
+    of opposite sign (side = 2^32 - 1), a constant and a verbatim side channel."""
+    h, w = 30, 400
+    n = h * w
+    rng = np.random.default_rng(12)
+    t = np.arange(n)
+    base = (np.sin(t / 50.0) * 1.5e9).astype(np.int64)
+    L = np.clip(base + rng.integers(-1000, 1000, n), -2 ** 31, 2 ** 31 - 1)
+    R = np.clip(base // 3 * 2 + rng.integers(-1000, 1000, n), -2 ** 31, 2 ** 31 - 1)
+    # frame 1: extremes of opposite sign; frame 2 (tail): noise that no predictor helps
+    L[4096:8192] = np.where(t[4096:8192] % 2 == 0, 2 ** 31 - 1, -2 ** 31)
+    R[4096:8192] = -L[4096:8192] - 1
+    L[8192:] = rng.integers(-2 ** 31, 2 ** 31 - 1, n - 8192)
+    R[8192:] = rng.integers(-2 ** 31, 2 ** 31 - 1, n - 8192)
+    pcm = np.stack([L, R], axis=1).astype(np.int32)
+    data, fsizes = oracle.encode_stream(pcm, 32, level=5)
+    ref, _si, frames = oracle.decode_stream(data)[:3]
+    assert np.array_equal(ref, pcm)
+    assert any(f["chan_assign"] >= 8 for f in frames), [f["chan_assign"] for f in frames]
+    got = _gpu_decode(codec, data, fsizes, h, w, 2, 32, table)
+    assert np.array_equal(got[0], pcm[:, 0]) and np.array_equal(got[1], pcm[:, 1])
