@@ -139,3 +139,43 @@ def test_decode_stereo_at_32_bits(codec, table):
     assert any(f["chan_assign"] >= 8 for f in frames), [f["chan_assign"] for f in frames]
     got = _gpu_decode(codec, data, fsizes, h, w, 2, 32, table)
     assert np.array_equal(got[0], pcm[:, 0]) and np.array_equal(got[1], pcm[:, 1])
+
+
+@pytest.mark.parametrize("warps_per_sm", [20.5, 21.5])
+def test_decode_copies_for_calls_that_just_miss_one_wave(codec, warps_per_sm):
+    """frx_launch_decode picks another copy of the frame decoder when a call needs between 20 and 21 (one 21-warp CTA per SM,
+    warps of a scheduler in step) or between 21 and 22 warps per SM (22 one-warp CTAs); smaller calls take the 20-CTA copy.
+    A call in each window must produce exactly what the same tiles give when they are decoded a few at a time."""
+    import torch
+    from flac_raster_b200 import synth
+    from flac_raster_b200.codec import make_dtiles, tile_grid
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    n_tiles = int(warps_per_sm * sms * 32) // 256               # 256 frames per 1024 x 1024 tile
+    cols = 20
+    rows = (n_tiles + cols - 1) // cols
+    n_tiles = rows * cols
+    warps = n_tiles * 256 / 32 / sms
+    if not (int(warps_per_sm) < warps <= int(warps_per_sm) + 1):
+        pytest.skip(f"no 20-column tile grid lands in the window on {sms} SMs ({warps:.2f} warps per SM)")
+    H, W = rows * 1024, cols * 1024
+    r = synth.rgb_u16(H, W, seed=77)[:1].contiguous()
+    tiles = tile_grid(H, W, 1024, 0, 1)
+    res = codec.encode_tiles(r, tiles)
+    torch.cuda.synchronize()
+    assert int(res.status.item()) == 0
+    total = int(res.total_bytes.item())
+    toff, tsize, mm = res.tile_offset.cpu().numpy(), res.tile_size.cpu().numpy(), res.tile_minmax.cpu().numpy()
+    entries = []
+    for i, (r0, c0, h, w, b0, nch) in enumerate(tiles):
+        entries.append(dict(byte_offset=toff[i], byte_size=tsize[i], out_offset=r0 * W + c0, out_band_stride=H * W, out_row_stride=W, h=h, w=w,
+                            channels=1, bps=16, dmin=mm[i, 0], dmax=mm[i, 1], first_frame=i * 256, n_frames=256))
+    big = torch.zeros((1, H, W), dtype=torch.uint16, device="cuda")
+    st = codec.decode_tiles(res.bytes, make_dtiles(entries), big, out_dtype="uint16", frame_size=res.frame_size, n_bytes=total)
+    torch.cuda.synchronize()
+    assert not st.cpu().numpy().any()
+    small = torch.zeros_like(big)
+    for i0 in range(0, len(entries), 64):
+        st = codec.decode_tiles(res.bytes, make_dtiles(entries[i0:i0 + 64]), small, out_dtype="uint16", frame_size=res.frame_size, n_bytes=total)
+        torch.cuda.synchronize()
+        assert not st.cpu().numpy().any()
+    assert torch.equal(big.view(torch.int16), small.view(torch.int16))
