@@ -586,6 +586,36 @@ def e2e_decode(env, codec, wl, units, res, hb, steps):
             "h2d_bytes_per_step": total + fs.nbytes, "d2h_bytes_per_step": oe * wl["itemsize"], "api": "frx_decode_tiles_host, pinned host buffers"}
 
 
+def device_decode_leg(env, codec, wl, units, res, steps, peak):
+    """The whole stream the timed loop wrote, decoded device to device in one frx_decode_tiles call (K9-K12)."""
+    import numpy as np
+    from flac_raster_b200.codec import _tdtype, make_dtiles
+    torch = env.torch
+    total = int(res.total_bytes.item())
+    res_np = (res.tile_offset.cpu().numpy(), res.tile_size.cpu().numpy(), res.tile_minmax.cpu().numpy(), res.frames_per_tile)
+    entries, oe = decode_entries(units, res_np, res.bps)
+    dt = make_dtiles(entries)
+    out = torch.empty(oe, dtype=_tdtype(wl["dtype"]), device=env.dev)
+    status = torch.zeros(len(units), dtype=torch.int32, device=env.dev)
+    ms, kms = [], []
+    for i in range(steps + 1):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        codec.decode_tiles(res.bytes, dt, out, out_dtype=wl["dtype"], frame_size=res.frame_size, pcm_mode=wl["pcm_mode"], status=status, n_bytes=total)
+        e1.record()
+        torch.cuda.synchronize()
+        if i:                                              # first call: warm-up
+            ms.append(e0.elapsed_time(e1)); kms.append(codec.last_kernel_ms()[1])
+    assert not status.cpu().numpy().any()
+    step_ms, kernel_ms = float(np.mean(ms)), float(np.mean(kms))
+    alg = total + oe * wl["itemsize"]
+    return {"metric": "decode_tiles_per_s", "value": round(len(units) / (step_ms * 1e-3), 1), "unit": "tiles/s", "ms_per_step": round(step_ms, 3),
+            "msample_per_s": round(oe / (step_ms * 1e-3) / 1e6, 1), "api": "frx_decode_tiles, device buffers, one call",
+            "roofline": {"bound": "hbm", "achieved": round(alg / (kernel_ms * 1e-3) / 1e9, 2), "peak": peak, "unit": "GB/s",
+                         "frac": round(alg / (kernel_ms * 1e-3) / 1e9 / peak, 4), "kernel": "frx_decode_kernel", "kernel_ms": round(kernel_ms, 4),
+                         "algorithmic_bytes": alg, "note": "B_dec = compressed bytes read + raster bytes written"}}
+
+
 def ingest_leg(env, codec, wl, raster, steps, peak):
     """the raster as a pixel-interleaved, one-row-per-strip TIFF image in device memory (GDAL's default layout for
     rasters this wide) -> band-planar raster; checked against the raster it came from."""
@@ -710,8 +740,10 @@ def main_ours(args):
     e2e = {"value": round(px_step / (e2e_ms * 1e-3) / 1e6, 1), "unit": "MPixel/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
            "ms_per_step": round(e2e_ms, 3), "floor_ms": round(floor_ms, 3), "over_floor": round(e2e_ms / floor_ms, 3),
            "api": "frx_encode_tiles_host, pinned host buffers; floor = the same H2D + D2H bytes copied concurrently, no kernels"}
+    decode_own = None
     if wl["name"] == "c2" and world == 1:
         e2e["decode"] = e2e_decode(env, codec, wl, units, res, hb, max(2, min(args.steps, 5)))
+        decode_own = device_decode_leg(env, codec, wl, units, res, max(2, min(args.steps, 5)), peak)
     cpu = None
     if world == 1 and not args.no_cpu:
         import oracle
@@ -756,6 +788,8 @@ def main_ours(args):
             "parity_check": par, "size_vs_oracle": None if ratio is None else round(ratio, 5),
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_all, "clocks": clocks, "decode": decode, "ingest": ingest,
         }
+        if decode_own:
+            line["decode_own_stream"] = decode_own
         if merged:
             line["merged_index"] = merged
         line.update(extra)
