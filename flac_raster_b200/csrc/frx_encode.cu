@@ -59,19 +59,23 @@ __global__ void __launch_bounds__(256) frx_minmax_kernel(const void *raster, lon
     long long vrows = (long long)t.n_channels * t.h;
     long long vrow1 = min(vrows, vrow0 + rpu);
     long long imin = LLONG_MAX, imax = LLONG_MIN;
+    // integer dtypes accumulate in 32 bits (one min and one max instruction per element; 64-bit min/max made K0 compute-bound on
+    // 16-bit rasters): biased to unsigned order for uint32, widened to int64 once per thread at the end
+    uint32_t amin = 0xFFFFFFFFu, amax = 0u;
     float fmin = CUDART_INF_F, fmax = -CUDART_INF_F;
     int nan = 0;
     // 16-byte loads when the tile rows allow it (every thread keeps several in flight), element loads otherwise
     constexpr int VEC = 16 / (int)sizeof(T);
-    const bool vec_ok = (((uintptr_t)base & 15u) == 0) && (band_stride % VEC) == 0 && (row_stride % VEC) == 0 && (t.col_off % VEC) == 0 && (t.w % VEC) == 0;
+    const bool vec_ok = (((uintptr_t)base & 15u) == 0) && (band_stride % VEC) == 0 && (row_stride % VEC) == 0 && (t.col_off % VEC) == 0 && (t.w % VEC) == 0 &&
+                        vrows < 0x7FFFFFFFLL;     // (the vector path indexes the tile's virtual rows in 32 bits)
     auto take = [&](T v) {
         if (DT == FRX_F32) {
             const float f = (float)v;
             if (f != f) nan = 1;
             fmin = fminf(fmin, f); fmax = fmaxf(fmax, f);
         } else {
-            const long long iv = (long long)v;
-            imin = min(imin, iv); imax = max(imax, iv);
+            const uint32_t iv = DT == FRX_U32 ? (uint32_t)v : ((uint32_t)(int32_t)v ^ 0x80000000u);     // order-preserving
+            amin = min(amin, iv); amax = max(amax, iv);
         }
     };
     auto row_ptr = [&](long long vr) {
@@ -80,17 +84,48 @@ __global__ void __launch_bounds__(256) frx_minmax_kernel(const void *raster, lon
         return base + (long long)(t.first_band + c) * band_stride + (long long)(t.row_off + r) * row_stride + t.col_off;
     };
     if (vec_ok) {
+        // the unit's 16-byte vectors, rows x (w / VEC), spread over the whole CTA with eight loads in flight per thread (narrow
+        // tiles: with one row per pass only w / VEC of the 256 threads had work -- C4's 256-wide tiles ran at 0.7 TB/s)
         const int n4 = t.w / VEC;
-        for (long long vr = vrow0; vr < vrow1; vr += 4) {     // four rows at a time: four independent loads per thread
-            const uint4 *rp[4];
+        const int items = (int)(vrow1 - vrow0) * n4;                 // <= rows_per_unit_elems / VEC
+        const int th = t.h;
+        if (n4 >= (int)blockDim.x) {
+            // wide rows: every thread has work in every row; four rows at a time, row pointers computed once per pass
+            for (long long vr = vrow0; vr < vrow1; vr += 4) {
+                const uint4 *rp[4];
 #pragma unroll
-            for (int k = 0; k < 4; k++) rp[k] = reinterpret_cast<const uint4 *>(row_ptr(min(vr + k, vrow1 - 1)));
-            for (int x = threadIdx.x; x < n4; x += blockDim.x) {
-                uint4 q[4];
+                for (int k = 0; k < 4; k++) rp[k] = reinterpret_cast<const uint4 *>(row_ptr(min(vr + k, vrow1 - 1)));
+                for (int x = threadIdx.x; x < n4; x += blockDim.x) {
+                    uint4 q[4];
 #pragma unroll
-                for (int k = 0; k < 4; k++) q[k] = __ldg(rp[k] + x);
+                    for (int k = 0; k < 4; k++) q[k] = __ldg(rp[k] + x);
 #pragma unroll
-                for (int k = 0; k < 4; k++) {
+                    for (int k = 0; k < 4; k++) {
+                        T e[VEC];
+                        memcpy(e, &q[k], 16);
+#pragma unroll
+                        for (int j = 0; j < VEC; j++) take(e[j]);
+                    }
+                }
+            }
+        } else
+        for (int i0 = threadIdx.x; i0 < items; i0 += 8 * (int)blockDim.x) {
+            uint4 q[8];
+            bool ok[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const int i = i0 + k * (int)blockDim.x;
+                ok[k] = i < items;
+                if (ok[k]) {
+                    const int rr = i / n4, x = i - rr * n4;
+                    const int vr = (int)vrow0 + rr, c = vr / th, r = vr - c * th;
+                    q[k] = __ldg(reinterpret_cast<const uint4 *>(base + (long long)(t.first_band + c) * band_stride +
+                                                                 (long long)(t.row_off + r) * row_stride + t.col_off) + x);
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                if (ok[k]) {
                     T e[VEC];
                     memcpy(e, &q[k], 16);
 #pragma unroll
@@ -103,6 +138,10 @@ __global__ void __launch_bounds__(256) frx_minmax_kernel(const void *raster, lon
             const T *row = row_ptr(vr);
             for (int x = threadIdx.x; x < t.w; x += blockDim.x) take(row[x]);
         }
+    }
+    if (DT != FRX_F32 && amin <= amax) {
+        imin = DT == FRX_U32 ? (long long)amin : (long long)(int32_t)(amin ^ 0x80000000u);
+        imax = DT == FRX_U32 ? (long long)amax : (long long)(int32_t)(amax ^ 0x80000000u);
     }
     // warp reduce
     for (int o = 16; o > 0; o >>= 1) {
