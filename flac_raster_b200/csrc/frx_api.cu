@@ -35,7 +35,7 @@ struct frx_ctx {
     int sm_count = 148;
     uint64_t launches = 0;
     Buf tiles, prefix, unit_prefix, mmraw, quant, desc, misc, xpow, crctab, fsize, foff, slots;
-    Buf dtiles, dprefix, fpos, flen, stereo, scan_prefix, scan_tiles, ing_chunks, ing_prefix;
+    Buf dtiles, dprefix, fpos, flen, stereo, scan_prefix, scan_tiles, ing_chunks, ing_prefix, d3sub, d3blk, d3res;
     Buf h_raster, h_bytes, h_small, h_out;  // device staging for the *_host entry points
     int xpow_L = -1;
     bool crctab_ready = false;
@@ -127,7 +127,7 @@ void frx_ctx_destroy(frx_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     Buf *all[] = { &c->tiles, &c->prefix, &c->unit_prefix, &c->mmraw, &c->quant, &c->desc, &c->misc, &c->xpow,
-                   &c->crctab, &c->fsize, &c->foff, &c->slots, &c->dtiles, &c->dprefix, &c->fpos, &c->flen, &c->stereo, &c->scan_prefix, &c->scan_tiles, &c->ing_chunks, &c->ing_prefix,
+                   &c->crctab, &c->fsize, &c->foff, &c->slots, &c->d3sub, &c->d3blk, &c->d3res, &c->dtiles, &c->dprefix, &c->fpos, &c->flen, &c->stereo, &c->scan_prefix, &c->scan_tiles, &c->ing_chunks, &c->ing_prefix,
                    &c->h_raster, &c->h_bytes, &c->h_small, &c->h_out };
     for (Buf *b : all) if (b->p) cudaFree(b->p);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
@@ -475,7 +475,27 @@ static int decode_core(frx_ctx *c, const uint8_t *bytes_dev, uint64_t n_bytes, c
         c->launches += 1;
     }
     CK(cudaEventRecord(c->ev[2], st));
-    CK(frx_launch_decode(a, out_dtype, c->sm_count, st));
+    // Small multi-channel calls are latency-bound: one lane walks a whole frame, channel after channel (5.5 ms for one
+    // 1024 x 1024 x 3 tile however idle the GPU is).  They take the phased decoder (frx_decode3.cu: codes scanned, then the
+    // residuals of all channels decoded 128 samples per lane, the recurrence restored per subframe, output written -- four
+    // short kernels; 4.45 ms for that tile), up to 2048 frames per call, where the single kernel's throughput takes over
+    // (profiles/r2_decode_experiments.md).  FRX_D3_MAX_FRAMES=n forces it for every call of up to n frames (0: never).
+    static const long long d3_env = getenv("FRX_D3_MAX_FRAMES") ? atoll(getenv("FRX_D3_MAX_FRAMES")) : -1;
+    int chmax = 1;
+    for (int i = 0; i < n_tiles; i++) chmax = tiles[i].channels > chmax ? tiles[i].channels : chmax;
+    const bool phased = frx_decode3_supports(blocksize) && !two_ch_32 &&      // (33-bit side channels: single-kernel decoder only)
+                        (d3_env >= 0 ? (long long)nf <= d3_env : (chmax >= 3 && nf <= 2048));
+    if (phased) {
+        size_t sb, bb, rb;
+        frx_decode3_scratch((uint32_t)((nf + 31ull) / 32ull * 32ull), chmax, blocksize, &sb, &bb, &rb);
+        ENSURE(c->d3sub, sb);
+        ENSURE(c->d3blk, bb);
+        ENSURE(c->d3res, rb);
+        CK(frx_launch_decode3(a, c->d3sub.p, c->d3blk.p, c->d3res.p, 0u, (uint32_t)nf, chmax, out_dtype, st));
+        c->launches += 3;
+    } else {
+        CK(frx_launch_decode(a, out_dtype, c->sm_count, st));
+    }
     if (c->verify_crc) { CK(frx_launch_crc_check(a, (const uint16_t *)c->xpow.p, c->sm_count, st)); c->launches += 1; }
     CK(cudaEventRecord(c->ev[3], st));
     c->dec_timed = true;

@@ -1,4 +1,4 @@
-// frx_decode3.cu -- the phased frame decoder (K10-K12 as four kernels).
+// frx_decode3.cu -- the phased frame decoder (K10-K12 as four kernels), used for small multi-channel calls (frx_api.cu decode_core).
 //
 // Rice codes and the predictor recurrence are both serial inside a subframe, but they are serial in different ways, and
 // the single-kernel decoder (frx_decode_frame.cuh: one lane walks one frame from its first bit to its last sample) pays for

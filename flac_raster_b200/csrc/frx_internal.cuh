@@ -76,6 +76,11 @@ cudaError_t frx_launch_frame_pos(const DecArgs &a, cudaStream_t st);
 cudaError_t frx_launch_discover(const DecArgs &a, const uint32_t *unit_prefix, const int32_t *unit_tiles, int n_scan_tiles,
                                 uint32_t total_units, cudaStream_t st);
 cudaError_t frx_launch_decode(const DecArgs &a, int out_dtype, int sm_count, cudaStream_t st);
+// the phased decoder (frx_decode3.cu): scan, residuals, restore, output over the frames [f0, f0 + nf) of the call
+void frx_decode3_scratch(uint32_t frames, int chmax, int blocksize, size_t *sub_bytes, size_t *blk_bytes, size_t *res_bytes);
+bool frx_decode3_supports(int blocksize);
+cudaError_t frx_launch_decode3(const DecArgs &a, void *sub, void *blk, void *res, uint32_t f0, uint32_t nf, int chmax, int out_dtype,
+                               cudaStream_t st);
 cudaError_t frx_launch_dequantize(const int32_t *pcm, int h, int w, int channels, int bps, int out_dtype, int mode, double dmin,
                                   double dmax, void *out, cudaStream_t st);
 // frx_tiff_unpack work split, shared by the host (unit counts) and the kernel: a chunk whose rows are short is cut into runs of
