@@ -475,16 +475,22 @@ static int decode_core(frx_ctx *c, const uint8_t *bytes_dev, uint64_t n_bytes, c
         c->launches += 1;
     }
     CK(cudaEventRecord(c->ev[2], st));
-    // Small multi-channel calls are latency-bound: one lane walks a whole frame, channel after channel (5.5 ms for one
-    // 1024 x 1024 x 3 tile however idle the GPU is).  They take the phased decoder (frx_decode3.cu: codes scanned, then the
-    // residuals of all channels decoded 128 samples per lane, the recurrence restored per subframe, output written -- four
-    // short kernels; 4.45 ms for that tile), up to 2048 frames per call, where the single kernel's throughput takes over
-    // (profiles/r2_decode_experiments.md).  FRX_D3_MAX_FRAMES=n forces it for every call of up to n frames (0: never).
+    // Small calls are latency-bound: one lane of the single-kernel decoder walks a whole frame, channel after channel (1.7 ms for
+    // one 1024 x 1024 float32 tile, 5.5 ms for a three-band uint16 tile, however idle the GPU is).  They take the phased decoder
+    // (frx_decode3.cu: codes scanned, then the residuals of all channels decoded 128 samples per lane, the recurrence restored per
+    // subframe, output written -- four short kernels: 1.4 and 3.0 ms for those tiles).  Its throughput is lower, so it is used up to
+    // 8192 frames per channel of the widest tile (the measured crossovers: 32 one-band tiles, 128 three-band tiles of 256 frames;
+    // profiles/r2_decode_experiments.md) and 2 GB of scratch rows.  FRX_D3_MAX_FRAMES=n forces it for every call of up to n frames
+    // (0: never).
     static const long long d3_env = getenv("FRX_D3_MAX_FRAMES") ? atoll(getenv("FRX_D3_MAX_FRAMES")) : -1;
     int chmax = 1;
     for (int i = 0; i < n_tiles; i++) chmax = tiles[i].channels > chmax ? tiles[i].channels : chmax;
-    const bool phased = frx_decode3_supports(blocksize) && !two_ch_32 &&      // (33-bit side channels: single-kernel decoder only)
-                        (d3_env >= 0 ? (long long)nf <= d3_env : (chmax >= 3 && nf <= 2048));
+    bool phased = frx_decode3_supports(blocksize) && !two_ch_32;      // (33-bit side channels: single-kernel decoder only)
+    if (phased) {
+        size_t sb, bb, rb;
+        frx_decode3_scratch((uint32_t)((nf + 31ull) / 32ull * 32ull), chmax, blocksize, &sb, &bb, &rb);
+        phased = d3_env >= 0 ? (long long)nf <= d3_env : (nf <= 8192ull * (uint64_t)chmax && rb <= (2ull << 30));
+    }
     if (phased) {
         size_t sb, bb, rb;
         frx_decode3_scratch((uint32_t)((nf + 31ull) / 32ull * 32ull), chmax, blocksize, &sb, &bb, &rb);

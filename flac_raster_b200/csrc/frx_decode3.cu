@@ -66,6 +66,7 @@ struct RingR {
     const uint8_t *lo, *hi, *np;
     uint32_t *ring;
     uint32_t rd, wr;
+    uint32_t nx;                // ring word `rd`, fetched ahead so that a refill has no shared-memory load on its critical path
     uint64_t acc;
     int cnt;
     uint32_t start_bits;
@@ -91,11 +92,13 @@ struct RingR {
             for (int k = 0; k < 4; k++) if ((uint32_t)k < free_blocks) push16(v[k]);
             if (!__any_sync(0xFFFFFFFFu, free_blocks > 4u)) break;
         }
+        nx = ring[(rd % D3_RING) * 32];
     }
     __device__ __forceinline__ uint32_t pop() {
-        if (rd == wr) push16(load16());
-        const uint32_t w = ring[(rd % D3_RING) * 32];
+        if (rd == wr) { push16(load16()); nx = ring[(rd % D3_RING) * 32]; }     // ring ran dry inside a chunk: fetch on demand
+        const uint32_t w = nx;
         rd++;
+        nx = ring[(rd % D3_RING) * 32];      // (stale when rd == wr: reloaded when the words arrive)
         return w;
     }
     __device__ __forceinline__ void init(const uint8_t *base, uint64_t n_bytes, uint64_t pos, uint32_t *ring_col, bool live) {
@@ -103,10 +106,11 @@ struct RingR {
         const uintptr_t addr = (uintptr_t)(base + pos);
         const int lead = (int)(addr & 15u);
         np = (const uint8_t *)(addr - lead);
-        ring = ring_col; rd = 0; wr = 0; start_bits = (uint32_t)lead * 8u; acc = 0; cnt = 0;
+        ring = ring_col; rd = 0; wr = 0; nx = 0; start_bits = (uint32_t)lead * 8u; acc = 0; cnt = 0;
         topup(live);
         if (live) {
             rd = (uint32_t)(lead >> 2);
+            nx = ring[(rd % D3_RING) * 32];
             const int lb = 8 * (lead & 3);
             acc = (uint64_t)pop() << (32 + lb);
             cnt = 32 - lb;
@@ -380,7 +384,17 @@ __global__ void __launch_bounds__(32) d3_scan_kernel(const DecArgs a, const D3Ar
         const int first = type == 2 ? order : 0;
         for (int n0 = 0; n0 < nmax; n0 += 32) {
             br.topup(walk && n0 < my_n);
-            if (walk) {
+            // chunks in which every lane walks 32 codes need no per-sample bounds; a block boundary can only be their first sample
+            const bool steady = __all_sync(0xFFFFFFFFu, walk && n0 >= first && n0 > 0 && n0 + 32 <= my_n);
+            if (steady) {
+                if ((n0 & (D3_BLK - 1)) == 0) {
+                    D3Block e;
+                    e.bitoff = br.consumed(); e.state = pack_state(rs);
+                    bk[n0 >> 7] = e;
+                }
+#pragma unroll 8
+                for (int i = 0; i < 32; i++) rice_skip(br, rs);
+            } else if (walk) {
 #pragma unroll 4
                 for (int i = 0; i < 32; i++) {
                     const int n = n0 + i;

@@ -6,7 +6,7 @@ from flac_raster_b200 import synth
 from flac_raster_b200.codec import Codec, tile_grid, make_dtiles
 kind = sys.argv[1] if len(sys.argv) > 1 else "f32"
 codec = Codec(0)
-H = 8192
+H = int(sys.argv[2]) if len(sys.argv) > 2 else 8192
 if kind == "f32":
     r, nch, dt_name, bps = synth.dem_f32(H, H, seed=3), 1, "float32", 32
 else:
@@ -22,7 +22,7 @@ for i, (r0, c0, h, w, b0, n) in enumerate(tiles):
 out = torch.zeros_like(r)
 ref = None
 line = []
-for nt in (1, 2, 4, 8, 16, 32, 64):
+for nt in [int(x) for x in (sys.argv[3].split(",") if len(sys.argv) > 3 else "1,4,16,32,64".split(","))]:
     dt = make_dtiles(entries[:nt])
     st = torch.zeros(nt, dtype=torch.int32, device='cuda')
     ms = []

@@ -41,6 +41,14 @@ def _both(codec, res, entries, oe, dtype, check_free=False):
     got.view(torch.uint8).fill_(7)
     status = torch.full((len(entries),), -99, dtype=torch.int32, device="cuda")
     torch.cuda.synchronize()
+    if check_free:
+        # the driver loads a kernel's image on its first launch (lazy module loading), which takes device memory that is not ours:
+        # one unmeasured call first, then the measured one
+        codec.decode_tiles_noalloc(res.bytes, dt, got, status, out_dtype=dtype, frame_size=res.frame_size, n_bytes=nb)
+        torch.cuda.synchronize()
+        got.view(torch.uint8).fill_(7)
+        status.fill_(-99)
+        torch.cuda.synchronize()
     free0 = torch.cuda.mem_get_info()[0]
     codec.decode_tiles_noalloc(res.bytes, dt, got, status, out_dtype=dtype, frame_size=res.frame_size, n_bytes=nb)
     torch.cuda.synchronize()
