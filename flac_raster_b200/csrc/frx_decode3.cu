@@ -238,6 +238,26 @@ template <class R> __device__ __forceinline__ void rice_skip(R &br, RiceState &r
     (void)rd_unary(br);
     (void)rd_get(br, (int)rs.k);
 }
+// the scan's walk over one code with the ring reader: the common case (inside a Rice partition, window topped up from the word
+// fetched ahead, code within 32 bits) is straight-line code with selects; everything else goes through rice_skip
+__device__ __forceinline__ void rice_skip_ring(RingR &br, RiceState &rs) {
+    const bool need = br.cnt <= 32;
+    if (rs.left == 0 || rs.rawbits >= 0 || (need && br.rd == br.wr)) { rice_skip(br, rs); return; }
+    rs.left--;
+    const uint64_t add = (uint64_t)br.nx << ((32 - br.cnt) & 31);
+    br.acc |= need ? add : 0ull;
+    br.cnt += need ? 32 : 0;
+    if (need) { br.rd++; br.nx = br.ring[(br.rd % D3_RING) * 32]; }
+    const uint32_t hi = (uint32_t)(br.acc >> 32);
+    const int used = __clz((int)hi) + 1 + (int)rs.k;          // hi == 0: clz = 32, used > 32
+    if (used <= 32) {
+        br.acc = (br.acc << (used - 1)) << 1;
+        br.cnt -= used;
+        return;
+    }
+    (void)rd_unary(br);
+    (void)rd_get(br, (int)rs.k);
+}
 __device__ __forceinline__ uint32_t pack_state(const RiceState &rs) {
     return rs.k | (rs.rawbits >= 0 ? 1u << 5 : 0u) | ((uint32_t)(rs.rawbits >= 0 ? rs.rawbits : 0) << 6) | (min(rs.left, 0xFFFFFu) << 12);
 }
@@ -393,7 +413,7 @@ __global__ void __launch_bounds__(32) d3_scan_kernel(const DecArgs a, const D3Ar
                     bk[n0 >> 7] = e;
                 }
 #pragma unroll 8
-                for (int i = 0; i < 32; i++) rice_skip(br, rs);
+                for (int i = 0; i < 32; i++) rice_skip_ring(br, rs);
             } else if (walk) {
 #pragma unroll 4
                 for (int i = 0; i < 32; i++) {
