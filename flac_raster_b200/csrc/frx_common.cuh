@@ -181,7 +181,9 @@ __device__ __forceinline__ typename FrxElem<DT>::T frx_dequant_ref(int32_t s, in
     int16_t s16 = (bps == 32) ? (int16_t)(s >> 16) : (int16_t)s;
     float x = (float)s16 * 3.0517578125e-05f;  // exact: int16 / 32768
     if (DT == FRX_F32) return (T)x;
-    float den = __fadd_rn(__fmul_rn(__fdiv_rn(__fadd_rn(x, 1.0f), 2.0f), q.range_f), q.dmin_f);
+    // (x + 1) / 2 as a multiplication by 0.5: the same float for every x here (x + 1 is 0 or lies in [2^-15, 2), halving is exact),
+    // and one instruction instead of the IEEE division sequence with its range check and slow-path call
+    float den = __fadd_rn(__fmul_rn(__fmul_rn(__fadd_rn(x, 1.0f), 0.5f), q.range_f), q.dmin_f);
     float r = rintf(den);  // np.round: half to even
     if (DT == FRX_U32) return (T)(uint32_t)__float2ll_rz(r);
     return (T)frx_trunc_i32f(r);
