@@ -203,20 +203,16 @@ cudaError_t frx_launch_crc_check(const DecArgs &a, const uint16_t *xpow, int sm_
 }
 
 cudaError_t frx_launch_decode_w22(const DecArgs &a, int out_dtype, cudaStream_t st);   // frx_decode_w22.cu
-cudaError_t frx_launch_decode_al(const DecArgs &a, int out_dtype, cudaStream_t st);    // frx_decode_al.cu
 
-// Which copy: a frame takes milliseconds on its lane, so what matters is whether the call fits ONE wave.  Up to 20 warps per SM
-// (and beyond 22, where several waves are needed anyway: C3 63 vs 68 ms) the 96-register copy of one-warp CTAs; between 20 and 21
-// the 21-warp CTA (C2: 20.6 warps per SM, 4.58 ms against 5.07 ms); between 21 and 22 the 22-CTA copy.
-// FRX_DECODE_COPY=20|21|22 forces one (A/B runs).
+// Which copy: a frame takes milliseconds on its lane, so what matters is whether the call fits ONE wave.  The 22-per-SM copy
+// exactly when it turns two waves into one (C2: 20.6 warps per SM); otherwise the 96-register copy (C3: 63 vs 68 ms).
+// FRX_DECODE_COPY=20|22 forces one (A/B runs, tests of both).
 cudaError_t frx_launch_decode(const DecArgs &a, int out_dtype, int sm_count, cudaStream_t st) {
     const uint32_t warps = (a.total_frames + 31u) / 32u;
     static const int forced = getenv("FRX_DECODE_COPY") ? atoi(getenv("FRX_DECODE_COPY")) : 0;
-    if (forced == 21) return frx_launch_decode_al(a, out_dtype, st);
     if (forced == 22) return frx_launch_decode_w22(a, out_dtype, st);
     if (forced == 20) return dec_w20::launch(a, out_dtype, st);
-    if (warps > 20u * (uint32_t)sm_count && warps <= 21u * (uint32_t)sm_count) return frx_launch_decode_al(a, out_dtype, st);
-    if (warps > 21u * (uint32_t)sm_count && warps <= 22u * (uint32_t)sm_count) return frx_launch_decode_w22(a, out_dtype, st);
+    if (warps > 20u * (uint32_t)sm_count && warps <= 22u * (uint32_t)sm_count) return frx_launch_decode_w22(a, out_dtype, st);
     return dec_w20::launch(a, out_dtype, st);
 }
 

@@ -2,10 +2,7 @@
 //   FRX_DEC_CTAS 20, FRX_DEC_RINGW 32 (96 registers): fewer spills, the better throughput when the frames need several waves;
 //   FRX_DEC_CTAS 22, FRX_DEC_RINGW 24 (80 registers): 3 256 warps resident, for calls that then fit ONE wave -- a frame takes
 //   ~3 ms on its lane whatever else runs, so a few warps left over for a second wave cost a whole frame time.
-//   FRX_DEC_WARPS 21, FRX_DEC_CTAS 1 (80 registers, 32-word rings): ONE CTA of 21 warps per SM for calls that need between 20 and 21
-//   warps per SM (C2: 20.6) -- the per-CTA shared-memory reserve is paid once, so 21 warps keep the 32-word rings and the early-issued
-//   ring loads, and the warps of a scheduler meet at every chunk (dec_bar): C2 5.07 -> 4.58 ms against the 22-CTA copy.
-// The including translation unit defines FRX_DEC_CTAS, FRX_DEC_RINGW and FRX_DEC_NS (namespace of this copy), optionally FRX_DEC_WARPS.
+// The including translation unit defines FRX_DEC_CTAS, FRX_DEC_RINGW and FRX_DEC_NS (namespace of this copy).
 #include "frx_decode_common.cuh"
 #ifndef FRX_DEC_EARLY_ISSUE
 #define FRX_DEC_EARLY_ISSUE 1
@@ -219,11 +216,7 @@ __device__ __forceinline__ int ilog2_u32(uint32_t v) { return 31 - __clz((int)v)
 // go through a shared-memory transpose so that every global store is one full line of one frame's raster row, instead of
 // 32 lanes scattering single elements 16 KB apart.
 // ------------------------------------------------------------------------------------------
-#ifdef FRX_DEC_WARPS
-#define DEC_WARPS FRX_DEC_WARPS   // aligned copy: one CTA per SM, the warps of a scheduler walk the chunks together (see dec_bar)
-#else
 #define DEC_WARPS 1     // one warp per CTA: a frame takes milliseconds on its lane, so the grid should fit one wave; small CTAs pack the SMs evenly
-#endif
 #define DEC_MAXORD 16
 struct DecWarpSmem {
     uint32_t ring[DEC_RING][32];     // input rings, one column per lane
@@ -449,16 +442,6 @@ __device__ __forceinline__ void flush_chunk_stereo(DecWarpSmem &ws, int lane, in
     __syncwarp();
 }
 
-// Aligned copy (DEC_WARPS > 1): the warps that share a scheduler (warp & 3) meet before every chunk, so that they walk the
-// 17 KB hot loop together and share the scheduler's instruction cache.  Every warp of the CTA passes the same number of
-// barriers: the chunk and channel counts are made CTA-uniform in the kernel.
-__device__ __forceinline__ void dec_bar() {
-#if DEC_WARPS > 1
-    const int cls = (int)((threadIdx.x >> 5) & 3);
-    asm volatile("bar.sync %0, %1;" :: "r"(1 + cls), "r"(32 * ((DEC_WARPS - cls + 3) / 4)) : "memory");
-#endif
-}
-
 // lockstep restore of one channel for the 32 frames of a warp; ORD = history length (multiple of 4 dividing 32),
 // WIDE = 64-bit accumulate.  Uniform control flow: lanes whose subframe is not predictive ride along predicated.
 template <int DT, int ORD, bool WIDE, bool ST>
@@ -468,7 +451,6 @@ __device__ __forceinline__ void run_chunks(BitR &br, SubF &sf, int32_t *coef, in
                                            long long band_stride_bytes = 0) {
     typedef typename FrxElem<DT>::T T;
     for (int n0 = 0; n0 < nmax; n0 += 32) {
-        dec_bar();
         br.topup(n0 < my_n);
         // where this lane's chunk lands
         ws.ptr[lane] = base_addr + (unsigned long long)((long long)row * row_stride + col) * sizeof(T);
@@ -550,19 +532,9 @@ __device__ __forceinline__ void run_chunks(BitR &br, SubF &sf, int32_t *coef, in
 }
 
 template <int DT>
-// (DEC_WARPS = 21: registers are handed out to four warps at a time, so ptxas budgets for 768 threads and stops at 80 -- 21 warps at
-// 96 registers do not launch)
 __global__ void __launch_bounds__(32 * DEC_WARPS, FRX_DEC_CTAS) frx_decode_kernel(const DecArgs a) {
     typedef typename FrxElem<DT>::T T;
-#if DEC_WARPS > 1
-    extern __shared__ __align__(16) unsigned char dec_smem_raw[];
-    DecWarpSmem *wsm = reinterpret_cast<DecWarpSmem *>(dec_smem_raw);
-    __shared__ int cta_nmax, cta_chmax;
-    if (threadIdx.x == 0) { cta_nmax = 0; cta_chmax = 0; }
-    __syncthreads();
-#else
     __shared__ DecWarpSmem wsm[DEC_WARPS];
-#endif
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     DecWarpSmem &ws = wsm[warp];
     const uint32_t f = (blockIdx.x * DEC_WARPS + warp) * 32u + (uint32_t)lane;
@@ -639,16 +611,7 @@ __global__ void __launch_bounds__(32 * DEC_WARPS, FRX_DEC_CTAS) frx_decode_kerne
     }
     int my_n = (live && !bad && !wide_stereo_done) ? nsamp : 0;
     const int my_ch = (live && !bad && !wide_stereo_done) ? channels : 0;
-#if DEC_WARPS > 1
-    {
-        const int wn = __reduce_max_sync(0xFFFFFFFFu, my_n), wc = __reduce_max_sync(0xFFFFFFFFu, my_ch);
-        if ((threadIdx.x & 31) == 0) { atomicMax(&cta_nmax, wn); atomicMax(&cta_chmax, wc); }
-        __syncthreads();
-    }
-    const int nmax = cta_nmax, chmax = cta_chmax;
-#else
     const int nmax = __reduce_max_sync(0xFFFFFFFFu, my_n), chmax = __reduce_max_sync(0xFFFFFFFFu, my_ch);
-#endif
     const bool any_stereo = __any_sync(0xFFFFFFFFu, stereo != 0u && my_n > 0);
     const int w = my_n ? t.w : (1 << 30);
     const int row0 = my_n ? (int)(s0 / t.w) : 0, col0 = my_n ? (int)(s0 - (long long)row0 * t.w) : 0;
@@ -775,15 +738,7 @@ static cudaError_t launch_decode_t(const DecArgs &a, unsigned grid, cudaStream_t
         if (e != cudaSuccess) return e;
         if (dev >= 0 && dev < 64) configured[dev] = true;
     }
-#if DEC_WARPS > 1
-    {
-        cudaError_t e = cudaFuncSetAttribute(frx_decode_kernel<DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(DecWarpSmem) * DEC_WARPS));
-        if (e != cudaSuccess) return e;
-    }
-    frx_decode_kernel<DT><<<grid, 32 * DEC_WARPS, sizeof(DecWarpSmem) * DEC_WARPS, st>>>(a);
-#else
     frx_decode_kernel<DT><<<grid, 32 * DEC_WARPS, 0, st>>>(a);
-#endif
     return cudaGetLastError();
 }
 

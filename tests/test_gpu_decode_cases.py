@@ -143,9 +143,9 @@ def test_decode_stereo_at_32_bits(codec, table):
 
 @pytest.mark.parametrize("warps_per_sm", [20.5, 21.5])
 def test_decode_copies_for_calls_that_just_miss_one_wave(codec, warps_per_sm):
-    """frx_launch_decode picks another copy of the frame decoder when a call needs between 20 and 21 (one 21-warp CTA per SM,
-    warps of a scheduler in step) or between 21 and 22 warps per SM (22 one-warp CTAs); smaller calls take the 20-CTA copy.
-    A call in each window must produce exactly what the same tiles give when they are decoded a few at a time."""
+    """frx_launch_decode picks the 22-CTA copy of the frame decoder when a call needs between 20 and 22 warps per SM (it then fits
+    one wave); other calls take the 20-CTA copy.  Calls inside that window must produce exactly what the same tiles give when
+    they are decoded a few at a time."""
     import torch
     from flac_raster_b200 import synth
     from flac_raster_b200.codec import make_dtiles, tile_grid
